@@ -1,0 +1,402 @@
+/*
+ * sdct_oracle.c - CPU restatement of the 8x8 block-DCT hot path.  TEST INFRASTRUCTURE ONLY.
+ * See sdct_oracle.h for the parity status of every entry point.  Build with
+ *   gcc -std=c11 -O2 -fno-fast-math -ffp-contract=off     (oracle/Makefile)
+ * so that every float operation below is one IEEE-754 binary32 operation, rounded to nearest
+ * even, in exactly the order written (fmaf() calls are explicit single-rounding FMAs).
+ *
+ * All file:line citations are into /root/reference/src/simd_dct.cpp unless stated otherwise.
+ */
+#include "sdct_oracle.h"
+
+#include <limits.h>
+#include <math.h>
+#include <string.h>
+
+/* 8-point constants, :140-146 (narrowed to float exactly as the reference's literals are). */
+static const float K_A = 1.3870398453221474618216191915664f;  /* sqrt2 cos(1pi/16) */
+static const float K_B = 1.3065629648763765278566431734272f;  /* sqrt2 cos(2pi/16) */
+static const float K_C = 1.1758756024193587169744671046113f;  /* sqrt2 cos(3pi/16) */
+static const float K_D = 0.78569495838710218127789736765722f; /* sqrt2 cos(5pi/16) */
+static const float K_E = 0.54119610014619698439972320536639f; /* sqrt2 cos(6pi/16) */
+static const float K_F = 0.27589937928294301233595756366937f; /* sqrt2 cos(7pi/16) */
+static const float K_N = 0.35355339059327376220042218105242f; /* 1/sqrt8 */
+static const float K_VR = 0.95f;                              /* :191, :906, :2066 */
+
+/* ---------------------------------------------------------------------------------------
+ * 8-point forward kernels
+ * ------------------------------------------------------------------------------------- */
+
+/* :138-172.  Odd outputs are summed left to right: ((t0 - t1) + t2) - t3. */
+void sdct_oracle_dct8_scalar(float v[8])
+{
+    const float s07 = v[0] + v[7], s16 = v[1] + v[6], s25 = v[2] + v[5], s34 = v[3] + v[4];
+    const float d07 = v[0] - v[7], d61 = v[6] - v[1], d25 = v[2] - v[5], d43 = v[4] - v[3];
+    const float pp = s07 + s34, pm = s07 - s34, qq = s16 + s25, qm = s16 - s25;
+
+    v[0] = K_N * (pp + qq);
+    v[2] = K_N * (K_B * pm + K_E * qm);
+    v[4] = K_N * (pp - qq);
+    v[6] = K_N * (K_E * pm - K_B * qm);
+    v[1] = K_N * (((K_A * d07 - K_C * d61) + K_D * d25) - K_F * d43);
+    v[3] = K_N * (((K_C * d07 + K_F * d61) - K_A * d25) + K_D * d43);
+    v[5] = K_N * (((K_D * d07 + K_A * d61) + K_F * d25) - K_C * d43);
+    v[7] = K_N * (((K_F * d07 + K_D * d61) + K_C * d25) + K_A * d43);
+}
+
+/* :2160-2183 (AVX2) == :1965-1988 (AVX-512VL) lane arithmetic.  Odd outputs are summed
+ * pairwise, (t0 op t1) op (t2 op t3).  quirk_x3 != 0 reproduces the reference's X3 line
+ * (:2181), which subtracts (A*d25 + D*d43) where the true DCT needs (A*d25 - D*d43). */
+void sdct_oracle_dct8_paired(float v[8], int quirk_x3)
+{
+    const float s07 = v[0] + v[7], s16 = v[1] + v[6], s25 = v[2] + v[5], s34 = v[3] + v[4];
+    const float d07 = v[0] - v[7], d61 = v[6] - v[1], d25 = v[2] - v[5], d43 = v[4] - v[3];
+    const float pp = s07 + s34, pm = s07 - s34, qq = s16 + s25, qm = s16 - s25;
+
+    v[0] = K_N * (pp + qq);
+    v[4] = K_N * (pp - qq);
+    v[2] = K_N * (K_B * pm + K_E * qm);
+    v[6] = K_N * (K_E * pm - K_B * qm);
+    v[1] = K_N * ((K_A * d07 - K_C * d61) + (K_D * d25 - K_F * d43));
+    if (quirk_x3)
+        v[3] = K_N * ((K_C * d07 + K_F * d61) - (K_A * d25 + K_D * d43));
+    else
+        v[3] = K_N * ((K_C * d07 + K_F * d61) - (K_A * d25 - K_D * d43));
+    v[5] = K_N * ((K_D * d07 + K_A * d61) + (K_F * d25 - K_C * d43));
+    v[7] = K_N * ((K_F * d07 + K_D * d61) + (K_C * d25 + K_A * d43));
+}
+
+/* ---------------------------------------------------------------------------------------
+ * This repo's own arithmetic definitions (no reference counterpart): the FMA-contracted
+ * "fast" forward and the inverse.  Both are *defined* here and the CUDA kernels reproduce
+ * them operation for operation, so GPU-vs-oracle is bit-exact for them as well.
+ * ------------------------------------------------------------------------------------- */
+
+/* Unnormalised forward (the two 1/sqrt8 factors = 1/8 per 2-D transform are folded into the
+ * quantiser scale).  34 operations instead of 56. */
+void sdct_oracle_dct8_fast(float v[8])
+{
+    const float s07 = v[0] + v[7], s16 = v[1] + v[6], s25 = v[2] + v[5], s34 = v[3] + v[4];
+    const float d07 = v[0] - v[7], d61 = v[6] - v[1], d25 = v[2] - v[5], d43 = v[4] - v[3];
+    const float pp = s07 + s34, pm = s07 - s34, qq = s16 + s25, qm = s16 - s25;
+
+    v[0] = pp + qq;
+    v[4] = pp - qq;
+    v[2] = fmaf(K_B, pm, K_E * qm);
+    v[6] = fmaf(K_E, pm, -(K_B * qm));
+    v[1] = fmaf(-K_F, d43, fmaf(K_D, d25, fmaf(-K_C, d61, K_A * d07)));
+    v[3] = fmaf(K_D, d43, fmaf(-K_A, d25, fmaf(K_F, d61, K_C * d07)));
+    v[5] = fmaf(-K_C, d43, fmaf(K_F, d25, fmaf(K_A, d61, K_D * d07)));
+    v[7] = fmaf(K_A, d43, fmaf(K_C, d25, fmaf(K_D, d61, K_F * d07)));
+}
+
+/* Unnormalised inverse 8-point (transposed flow graph of :148-171, SURVEY A.6, with the
+ * scalar factors folded into the dequantiser scale).  x = 2*sqrt2 * C^T X. */
+void sdct_oracle_idct8(float v[8])
+{
+    const float e0 = v[0] + v[4], e1 = v[0] - v[4];
+    const float e2 = fmaf(K_B, v[2], K_E * v[6]);
+    const float e3 = fmaf(K_E, v[2], -(K_B * v[6]));
+    const float a0 = e0 + e2, a3 = e0 - e2, a1 = e1 + e3, a2 = e1 - e3;
+    const float o0 = fmaf(K_F, v[7], fmaf(K_D, v[5], fmaf(K_C, v[3], K_A * v[1])));
+    const float o1 = fmaf(K_D, v[7], fmaf(K_A, v[5], fmaf(K_F, v[3], -(K_C * v[1]))));
+    const float o2 = fmaf(K_C, v[7], fmaf(K_F, v[5], fmaf(-K_A, v[3], K_D * v[1])));
+    const float o3 = fmaf(K_A, v[7], fmaf(-K_C, v[5], fmaf(K_D, v[3], -(K_F * v[1]))));
+    v[0] = a0 + o0; v[7] = a0 - o0;
+    v[1] = a1 - o1; v[6] = a1 + o1;
+    v[2] = a2 + o2; v[5] = a2 - o2;
+    v[3] = a3 - o3; v[4] = a3 + o3;
+}
+
+/* ---------------------------------------------------------------------------------------
+ * Quantisers
+ * ------------------------------------------------------------------------------------- */
+
+/* the reference's _clamp template, :45-49: NaN falls to `lo` */
+static float clamp_ref(float x, float lo, float hi) { return x > lo ? (x < hi ? x : hi) : lo; }
+
+/* scalar paths, :245 / :362 : reciprocal table 1/(lut*vr), bias 127/255, roundf (half away) */
+static uint8_t quant_scalar(float c, float rq)
+{
+    const float bias = 127.0f / 255.0f;
+    return (uint8_t)roundf(clamp_ref(c * rq + bias, 0.f, 1.f) * 255.f);
+}
+
+/* _mm256_cvtps_epi32 semantics: round to nearest even; NaN / out of range -> INT_MIN */
+static int32_t cvtps_epi32(float x)
+{
+    if (!(x >= -2147483648.0f && x < 2147483648.0f)) return INT_MIN;
+    return (int32_t)lrintf(x);     /* default rounding mode = nearest even */
+}
+
+/* AVX2 / AVX-512VL path, :2224 : scale 255/(lut*vr), integer bias after the conversion */
+static uint8_t quant_avx(float c, float q)
+{
+    int64_t r = (int64_t)cvtps_epi32(c * q) + 127;
+    return (uint8_t)(r > 255 ? 255 : (r < 0 ? 0 : r));
+}
+
+/* saturate to [0,1]; NaN -> 0 (PTX .sat semantics) */
+static float sat01(float x) { return x > 0.f ? (x < 1.f ? x : 1.f) : 0.f; }
+
+/* this repo's fast quantiser / pixel rounding: rne(255 * sat(.)) via the 1.5*2^23 trick */
+static uint8_t unit_to_u8(float y01)
+{
+    const float t = fmaf(y01, 255.f, 12582912.f);
+    uint32_t bits;
+    memcpy(&bits, &t, 4);
+    return (uint8_t)(bits & 0xffu);
+}
+static uint8_t quant_fast(float c, float qs) { return unit_to_u8(sat01(fmaf(c, qs, 127.0f / 255.0f))); }
+
+void sdct_oracle_tables(const float lut[64], int layout, float out[64], int which)
+{
+    for (int i = 0; i < 64; i++) {
+        const float d = lut[i] * K_VR;
+        switch (which) {
+        case SDCT_O_TAB_SCALAR: out[i] = 1.f / d; break;                 /* :194-212 */
+        case SDCT_O_TAB_AVX:    out[i] = 255.0f / d; break;              /* :2236-2239 */
+        case SDCT_O_TAB_FAST:   /* fwd fast: 1/8 (two passes) and, for A/C, the input 1/255 */
+            out[i] = (layout == SDCT_O_LAYOUT_B) ? 0.125f * (1.f / d) : (0.125f * (1.f / d)) / 255.f;
+            break;
+        default:                /* SDCT_O_TAB_INVERSE: -> pixel/255 units, 1/8 folded in */
+            out[i] = (layout == SDCT_O_LAYOUT_B) ? ((d / 255.f) * 0.125f) / 255.f : (d * 0.125f) / 255.f;
+            break;
+        }
+    }
+}
+
+/* ---------------------------------------------------------------------------------------
+ * Per-block 2-D transforms.  `px` points at the block's top-left pixel, row pitch `pitch`.
+ * Results are written to o[64] in the index order of the respective layout.
+ * ------------------------------------------------------------------------------------- */
+
+static void transpose8(float b[64])
+{
+    for (int i = 0; i < 8; i++)
+        for (int j = i + 1; j < 8; j++) { float t = b[i * 8 + j]; b[i * 8 + j] = b[j * 8 + i]; b[j * 8 + i] = t; }
+}
+
+/* layout A, :343-362 : x/255.f, row pass, swap, row pass; NOT swapped back */
+static void block_fwd_a(const uint8_t *px, size_t pitch, const float rq[64], uint8_t o[64])
+{
+    float b[64];
+    for (int r = 0; r < 8; r++)
+        for (int c = 0; c < 8; c++) b[r * 8 + c] = px[r * pitch + c] / 255.f;
+    for (int r = 0; r < 8; r++) sdct_oracle_dct8_scalar(b + r * 8);
+    transpose8(b);
+    for (int r = 0; r < 8; r++) sdct_oracle_dct8_scalar(b + r * 8);
+    for (int i = 0; i < 64; i++) o[i] = quant_scalar(b[i], rq[i]);
+}
+
+/* layout C, :220-247 : x/255.f, swap, row pass (= vertical), swap, row pass (= horizontal) */
+static void block_fwd_c(const uint8_t *px, size_t pitch, const float rq[64], uint8_t o[64])
+{
+    float b[64];
+    for (int r = 0; r < 8; r++)
+        for (int c = 0; c < 8; c++) b[r * 8 + c] = px[r * pitch + c] / 255.f;
+    transpose8(b);
+    for (int r = 0; r < 8; r++) sdct_oracle_dct8_scalar(b + r * 8);
+    transpose8(b);
+    for (int r = 0; r < 8; r++) sdct_oracle_dct8_scalar(b + r * 8);
+    for (int i = 0; i < 64; i++) o[i] = quant_scalar(b[i], rq[i]);
+}
+
+/* layout B, :2107-2228 : (float)x, horizontal pass, vertical pass, natural order */
+static void block_fwd_b(const uint8_t *px, size_t pitch, const float q[64], int quirks, uint8_t o[64])
+{
+    float b[64], col[8];
+    for (int r = 0; r < 8; r++)
+        for (int c = 0; c < 8; c++) b[r * 8 + c] = (float)px[r * pitch + c];
+    for (int r = 0; r < 8; r++) sdct_oracle_dct8_paired(b + r * 8, quirks & SDCT_O_QUIRK_AVX_X3);
+    for (int c = 0; c < 8; c++) {
+        for (int r = 0; r < 8; r++) col[r] = b[r * 8 + c];
+        sdct_oracle_dct8_paired(col, quirks & SDCT_O_QUIRK_AVX_X3);
+        for (int r = 0; r < 8; r++) b[r * 8 + c] = col[r];
+    }
+    for (int i = 0; i < 64; i++) o[i] = quant_avx(b[i], q[i]);
+}
+
+/* fast mode (this repo): (float)x, horizontal pass, vertical pass, unnormalised; the output
+ * order is natural (u*8+v) or, for layout A, transposed (v*8+u) with the LUT at that index */
+static void block_fwd_fast(const uint8_t *px, size_t pitch, const float qs[64], int transposed, uint8_t o[64])
+{
+    float b[64], col[8];
+    for (int r = 0; r < 8; r++)
+        for (int c = 0; c < 8; c++) b[r * 8 + c] = (float)px[r * pitch + c];
+    for (int r = 0; r < 8; r++) sdct_oracle_dct8_fast(b + r * 8);
+    for (int c = 0; c < 8; c++) {
+        for (int r = 0; r < 8; r++) col[r] = b[r * 8 + c];
+        sdct_oracle_dct8_fast(col);
+        for (int r = 0; r < 8; r++) b[r * 8 + c] = col[r];
+    }
+    for (int u = 0; u < 8; u++)
+        for (int v = 0; v < 8; v++) {
+            const int i = transposed ? v * 8 + u : u * 8 + v;
+            o[i] = quant_fast(b[u * 8 + v], qs[i]);
+        }
+}
+
+/* inverse (this repo): dequantise, vertical pass, horizontal pass, rne(255*sat(.)) */
+static void block_inv(const uint8_t q[64], const float tab[64], int transposed, uint8_t *px, size_t pitch)
+{
+    float b[64], col[8];
+    for (int u = 0; u < 8; u++)
+        for (int v = 0; v < 8; v++) {
+            const int i = transposed ? v * 8 + u : u * 8 + v;
+            b[u * 8 + v] = (float)((int)q[i] - 127) * tab[i];
+        }
+    for (int c = 0; c < 8; c++) {
+        for (int r = 0; r < 8; r++) col[r] = b[r * 8 + c];
+        sdct_oracle_idct8(col);
+        for (int r = 0; r < 8; r++) b[r * 8 + c] = col[r];
+    }
+    for (int r = 0; r < 8; r++) sdct_oracle_idct8(b + r * 8);
+    for (int r = 0; r < 8; r++)
+        for (int c = 0; c < 8; c++) px[r * pitch + c] = unit_to_u8(sat01(b[r * 8 + c]));
+}
+
+/* ---------------------------------------------------------------------------------------
+ * Plane-level entry points ("native" semantics: every band of the plane is processed)
+ * ------------------------------------------------------------------------------------- */
+
+static void gather_block(const uint8_t *src, size_t pitch, size_t xstep, uint8_t tile[64])
+{
+    for (int r = 0; r < 8; r++)
+        for (int c = 0; c < 8; c++) tile[r * 8 + c] = src[r * pitch + (size_t)c * xstep];
+}
+
+/* where block (band, eye, bx) of an image `width` wide puts coefficient i */
+static uint8_t *coef_addr(int layout, uint8_t *out, size_t plane_stride, size_t width, int eyes,
+                          size_t band, int eye, size_t bx, int i)
+{
+    const size_t bpr = width / 8;
+    switch (layout) {
+    case SDCT_O_LAYOUT_A: return out + (band * bpr + bx) * 64 + i;                        /* :361-365 */
+    case SDCT_O_LAYOUT_B: return out + band * 8 * width + (bx / 8) * 512 + i * 8 + (bx % 8); /* :2221-2230 */
+    default:              return out + (size_t)i * plane_stride + (band * eyes + eye) * bpr + bx; /* :256-264, :289-296 */
+    }
+}
+
+static void forward_band(int layout, int mode, int quirks, const uint8_t *in, size_t pitch, size_t xstep,
+                         size_t width, size_t band, int eyes, size_t eye_stride, const float tab[64],
+                         uint8_t *out, size_t plane_stride)
+{
+    uint8_t tile[64], o[64];
+    for (int eye = 0; eye < eyes; eye++)
+        for (size_t bx = 0; bx < width / 8; bx++) {
+            gather_block(in + (size_t)eye * eye_stride + band * 8 * pitch + bx * 8 * xstep, pitch, xstep, tile);
+            if (mode == SDCT_O_MODE_FAST) block_fwd_fast(tile, 8, tab, layout == SDCT_O_LAYOUT_A, o);
+            else if (layout == SDCT_O_LAYOUT_A) block_fwd_a(tile, 8, tab, o);
+            else if (layout == SDCT_O_LAYOUT_B) block_fwd_b(tile, 8, tab, quirks, o);
+            else block_fwd_c(tile, 8, tab, o);
+            for (int i = 0; i < 64; i++) *coef_addr(layout, out, plane_stride, width, eyes, band, eye, bx, i) = o[i];
+        }
+}
+
+static void forward_table(int layout, int mode, const float lut[64], float tab[64])
+{
+    const int which = mode == SDCT_O_MODE_FAST ? SDCT_O_TAB_FAST
+                    : layout == SDCT_O_LAYOUT_B ? SDCT_O_TAB_AVX : SDCT_O_TAB_SCALAR;
+    sdct_oracle_tables(lut, layout, tab, which);
+}
+
+void sdct_oracle_forward(int layout, int mode, int quirks, const uint8_t *in, size_t pitch, size_t xstep,
+                         size_t width, size_t height, int eyes, size_t eye_stride, const float lut[64],
+                         uint8_t *out, size_t plane_stride)
+{
+    float tab[64];
+    forward_table(layout, mode, lut, tab);
+    if (layout != SDCT_O_LAYOUT_C) eyes = 1;
+    for (size_t band = 0; band < height / 8; band++)
+        forward_band(layout, mode, quirks, in, pitch, xstep, width, band, eyes, eye_stride, tab, out, plane_stride);
+}
+
+void sdct_oracle_inverse(int layout, const uint8_t *coef, size_t plane_stride, size_t width, size_t height,
+                         int eyes, size_t eye_stride, const float lut[64], uint8_t *out, size_t pitch, size_t xstep)
+{
+    float tab[64];
+    uint8_t q[64], tile[64];
+    sdct_oracle_tables(lut, layout, tab, SDCT_O_TAB_INVERSE);
+    if (layout != SDCT_O_LAYOUT_C) eyes = 1;
+    for (size_t band = 0; band < height / 8; band++)
+        for (int eye = 0; eye < eyes; eye++)
+            for (size_t bx = 0; bx < width / 8; bx++) {
+                for (int i = 0; i < 64; i++)
+                    q[i] = *coef_addr(layout, (uint8_t *)coef, plane_stride, width, eyes, band, eye, bx, i);
+                block_inv(q, tab, layout == SDCT_O_LAYOUT_A, tile, 8);
+                uint8_t *dst = out + (size_t)eye * eye_stride + band * 8 * pitch + bx * 8 * xstep;
+                for (int r = 0; r < 8; r++)
+                    for (int c = 0; c < 8; c++) dst[r * pitch + (size_t)c * xstep] = tile[r * 8 + c];
+            }
+}
+
+/* component reorder: interleaved rows (ncomp bytes per pixel) <-> ncomp planar planes */
+void sdct_oracle_deinterleave(const uint8_t *in, size_t pitch, size_t width, size_t height, int ncomp, uint8_t *out)
+{
+    for (int k = 0; k < ncomp; k++)
+        for (size_t y = 0; y < height; y++)
+            for (size_t x = 0; x < width; x++)
+                out[((size_t)k * height + y) * width + x] = in[y * pitch + x * ncomp + k];
+}
+
+void sdct_oracle_interleave(const uint8_t *planes, size_t width, size_t height, int ncomp, uint8_t *out, size_t pitch)
+{
+    for (int k = 0; k < ncomp; k++)
+        for (size_t y = 0; y < height; y++)
+            for (size_t x = 0; x < width; x++)
+                out[y * pitch + x * ncomp + k] = planes[((size_t)k * height + y) * width + x];
+}
+
+/* ---------------------------------------------------------------------------------------
+ * The reference's call semantics: sizeY is the stereo (double) height, only rows below
+ * sizeY/2 are visited (:268, :375, :2243), and [startY, endY] is an inclusive window.
+ * Return values follow simdDctResult (src/simd_dct.h:22-27).
+ * ------------------------------------------------------------------------------------- */
+
+int sdct_oracle_ref_encode_quantize_buffer(const uint8_t *from, uint8_t *to, const float *lut,
+                                           size_t size_x, size_t size_y, size_t start_y, size_t end_y)
+{
+    float tab[64];
+    if (!from || !to) return 1;                               /* :97 */
+    if ((size_x & 7) || (size_y & 7)) return 2;               /* :98 */
+    forward_table(SDCT_O_LAYOUT_A, SDCT_O_MODE_EXACT, lut, tab);
+    for (size_t y = 0; y < size_y / 2; y += 8) {
+        if (y < start_y) continue;                            /* :377 - compares y, not 2y */
+        if (y > end_y) break;                                 /* :384 */
+        forward_band(SDCT_O_LAYOUT_A, SDCT_O_MODE_EXACT, 0, from, size_x, 1, size_x, y / 8, 1, 0, tab, to, 0);
+    }
+    return 0;
+}
+
+int sdct_oracle_ref_encode_quantize32_reorder_buffer(const uint8_t *from, uint8_t *to, const float *lut,
+                                                     size_t size_x, size_t size_y, size_t start_y, size_t end_y,
+                                                     int quirks)
+{
+    float tab[64];
+    if (!from || !to) return 1;                               /* :117 */
+    if ((size_x & 63) || (size_y & 7)) return 2;              /* :118 */
+    forward_table(SDCT_O_LAYOUT_B, SDCT_O_MODE_EXACT, lut, tab);
+    for (size_t y = 0; y < size_y / 2; y += 8) {
+        if (y * 2 < start_y) continue;                        /* :2245 */
+        if (y * 2 > end_y) break;                             /* :2252 */
+        forward_band(SDCT_O_LAYOUT_B, SDCT_O_MODE_EXACT, quirks, from, size_x, 1, size_x, y / 8, 1, 0, tab, to, 0);
+    }
+    return 0;
+}
+
+int sdct_oracle_ref_encode_quantize_reorder_stereo_buffer(const uint8_t *from, uint8_t *to, const float *lut,
+                                                          size_t size_x, size_t size_y, size_t start_y, size_t end_y)
+{
+    float tab[64];
+    if (!from || !to) return 1;                               /* :75 */
+    if ((size_x & 7) || (size_y & 7)) return 2;               /* :76 */
+    forward_table(SDCT_O_LAYOUT_C, SDCT_O_MODE_EXACT, lut, tab);
+    for (size_t y = 0; y < size_y / 2; y += 8) {
+        if (y * 2 < start_y) continue;                        /* :270 */
+        if (y * 2 > end_y) break;                             /* :280 */
+        forward_band(SDCT_O_LAYOUT_C, SDCT_O_MODE_EXACT, 0, from, size_x, 1, size_x, y / 8, 2,
+                     size_x * size_y / 2, tab, to, size_x * size_y / 64);
+    }
+    return 0;
+}
