@@ -1,0 +1,141 @@
+/*
+ * sdct.h - C ABI of the B200 (sm_100a) 8x8 block-DCT library (libsdct.so).
+ *
+ * This is the drop-in boundary behind the reference's public header: plain pointers and
+ * sizes, no C++ or torch types.  Each entry point cites the reference interface it replaces
+ * (paths are into rainerzufalldererste/simd_dct).  The three C++-linkage functions of
+ * src/simd_dct.h:29-31 are exported by the same library (simd_dct_b200/csrc/simd_dct_shim.cpp,
+ * declared in include/simd_dct.h) and forward to the sdct_ref_* functions below.
+ *
+ * There is no CPU fallback: every compute entry point returns SDCT_NO_DEVICE / SDCT_CUDA_ERROR
+ * (and sets sdct_last_error()) when no usable sm_100 device is present.
+ */
+#ifndef SDCT_H
+#define SDCT_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SDCT_ABI_VERSION 1
+
+/* status: values 0..2 are the reference's simdDctResult (src/simd_dct.h:22-27) */
+enum {
+    SDCT_OK = 0,
+    SDCT_INVALID_PARAMETER = 1,
+    SDCT_NOT_SUPPORTED = 2,
+    SDCT_CUDA_ERROR = 3,
+    SDCT_NO_DEVICE = 4
+};
+
+/* coefficient layouts */
+enum {
+    SDCT_LAYOUT_A = 0, /* block-contiguous, 64 B per block, byte [v*8+u]  - simdDCT_EncodeQuantizeBuffer (src/simd_dct.cpp:300-395) */
+    SDCT_LAYOUT_B = 1, /* 8-block groups, 512 B, byte [i*8+blk]           - simdDCT_EncodeQuantize32ReorderBuffer (:2064-2262) */
+    SDCT_LAYOUT_C = 2  /* 64 coefficient planes, eyes interleaved per band - simdDCT_EncodeQuantizeReorderStereoBuffer (:177-298) */
+};
+
+/* flags */
+enum {
+    SDCT_EXACT = 0,         /* the reference's fp32 operation order; byte-identical to its CPU output */
+    SDCT_FAST = 1,          /* FMA-contracted arithmetic defined in oracle/sdct_oracle.c (<= 1 LSB from SDCT_EXACT) */
+    SDCT_QUIRK_AVX_X3 = 2   /* layout B: reproduce the reference's X3 sign (src/simd_dct.cpp:2181); see DESIGN.md */
+};
+
+typedef struct sdct_context sdct_context;
+
+/*
+ * One batched job over device-resident buffers.
+ *
+ * Pixel side:  frame f, eye e, component k, pixel (y, x) lives at
+ *     pixels[f*pixel_frame_stride + e*eye_stride + y*pitch + x*components + k]
+ * Coefficient side: the coefficient set of (frame f, component k) starts at
+ *     coefs[f*coef_frame_stride + k*coef_comp_stride]
+ * and has width*height*eyes bytes in the chosen layout (layout C: plane i at + i*coef_plane_stride).
+ * Only bands [band_begin, band_end) (a band = 8 pixel rows) are processed; band_end = 0 means
+ * height/8.  Outputs of unprocessed bands are left untouched, as in the reference's
+ * startY/endY window (src/simd_dct.cpp:268-282).
+ */
+typedef struct sdct_job {
+    int32_t layout;
+    int32_t flags;
+    int32_t components;        /* 1 = planar plane, 3 = interleaved 3-component pixels */
+    int32_t eyes;              /* layout C: 1 or 2; other layouts: 1 */
+    uint64_t width, height;    /* one plane of one eye, in pixels; width%8==0 (B: %64), height%8==0 */
+    uint64_t pitch;            /* bytes between pixel rows */
+    uint64_t eye_stride;       /* bytes between the eyes' pixel planes (layout C, eyes == 2) */
+    uint64_t frames;
+    uint64_t pixel_frame_stride;
+    uint64_t coef_frame_stride;
+    uint64_t coef_comp_stride;
+    uint64_t coef_plane_stride;
+    uint64_t band_begin, band_end;
+} sdct_job;
+
+/* fills strides for a dense batch: frames x [eyes x] height x width x components pixels */
+void sdct_job_dense(sdct_job *job, int layout, int flags, int components, int eyes,
+                    uint64_t width, uint64_t height, uint64_t frames);
+
+/* context = one device + its streams, staging buffers and launch counters
+ * (replaces the caller-side _DetectCPUFeatures() contract, src/simd_platform.h:131) */
+int sdct_create(int device, sdct_context **out);
+void sdct_destroy(sdct_context *ctx);
+const char *sdct_last_error(void);
+int sdct_abi_version(void);
+int sdct_device_count(void);
+int sdct_sm_count(const sdct_context *ctx);
+/* number of kernel launches issued through this context so far */
+uint64_t sdct_kernel_launches(const sdct_context *ctx);
+
+/* device-resident operations; `stream` is a cudaStream_t (NULL = the context's own stream).
+ * lut = the caller's 64-entry quantisation table in host memory (pQuantizeLUT of
+ * src/simd_dct.h:29-31); the scale tables are derived from it exactly as
+ * src/simd_dct.cpp:194-212 / :2236-2239 do. */
+int sdct_forward_device(sdct_context *ctx, const sdct_job *job, const void *d_pixels, const float *lut,
+                        void *d_coefs, void *stream);
+int sdct_inverse_device(sdct_context *ctx, const sdct_job *job, const void *d_coefs, const float *lut,
+                        void *d_pixels, void *stream);
+/* fused forward -> quantise -> dequantise -> inverse; coefficients never leave the SM */
+int sdct_roundtrip_device(sdct_context *ctx, const sdct_job *job, const void *d_pixels_in, const float *lut,
+                          void *d_pixels_out, void *stream);
+
+/* host-buffer operations: pinned staging + chunked H2D -> kernel -> D2H pipeline on 3 streams */
+int sdct_forward_host(sdct_context *ctx, const sdct_job *job, const void *h_pixels, const float *lut,
+                      void *h_coefs);
+int sdct_inverse_host(sdct_context *ctx, const sdct_job *job, const void *h_coefs, const float *lut,
+                      void *h_pixels);
+
+/* synchronise the context's streams */
+int sdct_synchronize(sdct_context *ctx);
+
+/* pinned host memory helpers for callers that want zero-copy staging */
+void *sdct_host_alloc(size_t bytes);
+void sdct_host_free(void *p);
+
+/*
+ * The reference's call semantics on HOST buffers, used by the simd_dct.h shim:
+ * sizeY is the stereo (double) height, only rows below sizeY/2 are visited, [startY, endY] is
+ * the inclusive window of src/simd_dct.cpp:268-282 / :375-387 / :2243-2255, return value is
+ * the reference's simdDctResult.  They run on a lazily created process-wide context
+ * (device = $SDCT_DEVICE or 0).
+ */
+int sdct_ref_encode_quantize_buffer(const uint8_t *from, uint8_t *to, const float *lut,
+                                    size_t size_x, size_t size_y, size_t start_y, size_t end_y);        /* src/simd_dct.h:29 */
+int sdct_ref_encode_quantize_reorder_stereo_buffer(const uint8_t *from, uint8_t *to, const float *lut,
+                                                   size_t size_x, size_t size_y, size_t start_y, size_t end_y); /* :30 */
+int sdct_ref_encode_quantize32_reorder_buffer(const uint8_t *from, uint8_t *to, const float *lut,
+                                              size_t size_x, size_t size_y, size_t start_y, size_t end_y);      /* :31 */
+/* flags applied by the three functions above (default SDCT_EXACT | SDCT_QUIRK_AVX_X3 = reference bytes) */
+void sdct_ref_set_flags(int flags);
+int sdct_ref_get_flags(void);
+
+/* contiguous shard [begin, end) of `total` units for `rank` of `world` (frames or bands; no collective) */
+void sdct_shard_range(uint64_t total, int rank, int world, uint64_t *begin, uint64_t *end);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SDCT_H */

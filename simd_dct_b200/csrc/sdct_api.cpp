@@ -1,0 +1,232 @@
+// sdct_api.cpp - host side of the C ABI declared in include/sdct.h: contexts, job validation,
+// scale-table construction, the chunked host<->device pipeline and the reference-call wrappers.
+// No compute happens here and there is no CPU fallback: every path ends in sdct_k_launch().
+#include "sdct_internal.h"
+
+#include <algorithm>
+#include <atomic>
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <mutex>
+#include <vector>
+
+namespace {
+thread_local char g_err[512] = "";
+}
+
+int sdct_fail(int code, const char *fmt, ...)
+{
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+    return code;
+}
+
+int sdct_validate(const sdct_job *j, Geometry *g)
+{
+    if (!j) return fail(SDCT_INVALID_PARAMETER, "job is null");
+    if (j->layout < SDCT_LAYOUT_A || j->layout > SDCT_LAYOUT_C) return fail(SDCT_INVALID_PARAMETER, "unknown layout %d", j->layout);
+    if (j->components != 1 && j->components != 3) return fail(SDCT_NOT_SUPPORTED, "components must be 1 or 3 (got %d)", j->components);
+    const int eyes = j->layout == SDCT_LAYOUT_C ? j->eyes : 1;
+    if (eyes != 1 && eyes != 2) return fail(SDCT_INVALID_PARAMETER, "eyes must be 1 or 2 (got %d)", j->eyes);
+    // src/simd_dct.cpp:76 / :98 (multiple of 8) and :118 (layout B: multiple of 64)
+    if ((j->width & 7) || (j->height & 7)) return fail(SDCT_NOT_SUPPORTED, "width and height must be multiples of 8");
+    if (j->layout == SDCT_LAYOUT_B && (j->width & 63)) return fail(SDCT_NOT_SUPPORTED, "layout B needs width %% 64 == 0");
+    if (j->width / 8 > 0x7fffffffull || j->height / 8 * eyes > 0x7fffffffull || j->frames > 0x7fffffffull)
+        return fail(SDCT_NOT_SUPPORTED, "image too large");
+    if ((j->width / 8) * (j->height / 8) * eyes > 0xffffffffull) return fail(SDCT_NOT_SUPPORTED, "more than 2^32 blocks per plane");
+    if (j->pitch < j->width * (uint64_t)j->components) return fail(SDCT_INVALID_PARAMETER, "pitch smaller than a pixel row");
+    g->bpr = (uint32_t)(j->width / 8);
+    g->bands_total = (uint32_t)(j->height / 8);
+    g->band_begin = (uint32_t)std::min<uint64_t>(j->band_begin, g->bands_total);
+    g->band_end = j->band_end == 0 ? g->bands_total : (uint32_t)std::min<uint64_t>(j->band_end, g->bands_total);
+    if (g->band_end < g->band_begin) g->band_end = g->band_begin;
+    g->eyes = (uint32_t)eyes;
+    g->comps = (uint32_t)j->components;
+    return SDCT_OK;
+}
+
+namespace {
+
+// scale tables, in float exactly as the reference builds them
+int build_tables(const sdct_job *j, const float *lut, int op, float tab[64], float tab2[64])
+{
+    if (!lut) return fail(SDCT_INVALID_PARAMETER, "quantisation LUT is null");
+    const bool fast = (j->flags & SDCT_FAST) != 0;
+    for (int i = 0; i < 64; i++) {
+        const float d = lut[i] * 0.95f;                               // vr, src/simd_dct.cpp:191
+        float f;
+        if (fast) f = j->layout == SDCT_LAYOUT_B ? 0.125f * (1.f / d) : (0.125f * (1.f / d)) / 255.f;
+        else if (j->layout == SDCT_LAYOUT_B) f = 255.0f / d;          // :2236-2239
+        else f = 1.f / d;                                             // :194-212
+        const float inv = j->layout == SDCT_LAYOUT_B ? ((d / 255.f) * 0.125f) / 255.f : (d * 0.125f) / 255.f;
+        if (op == SDCT_K_OP_INVERSE) { tab[i] = inv; tab2[i] = 0.f; }
+        else { tab[i] = f; tab2[i] = inv; }
+        if (!std::isfinite(tab[i]) || !std::isfinite(tab2[i]))
+            return fail(SDCT_INVALID_PARAMETER, "LUT entry %d (%g) gives a non-finite scale", i, (double)lut[i]);
+    }
+    return SDCT_OK;
+}
+
+bool aligned(const void *p, uint64_t a) { return (reinterpret_cast<uintptr_t>(p) & (a - 1)) == 0; }
+
+int run_device(sdct_context *ctx, int op, const sdct_job *j, const uint8_t *pixels, uint8_t *coefs,
+               uint8_t *pixels_out, const float *lut, cudaStream_t stream)
+{
+    Geometry g;
+    int rc = sdct_validate(j, &g);
+    if (rc) return rc;
+    if (!ctx) return fail(SDCT_INVALID_PARAMETER, "context is null");
+    if (!pixels || (op != SDCT_K_OP_ROUNDTRIP && !coefs) || (op == SDCT_K_OP_ROUNDTRIP && !pixels_out))
+        return fail(SDCT_INVALID_PARAMETER, "null buffer");
+    KParams p;
+    memset(&p, 0, sizeof(p));
+    rc = build_tables(j, lut, op, p.tab, p.tab2);
+    if (rc) return rc;
+    p.pixels = pixels; p.coefs = coefs; p.pixels_out = pixels_out;
+    p.pitch = j->pitch; p.eye_stride = j->eye_stride; p.pixel_frame_stride = j->pixel_frame_stride;
+    p.coef_frame_stride = j->coef_frame_stride; p.coef_comp_stride = j->coef_comp_stride;
+    p.coef_plane_stride = j->coef_plane_stride;
+    p.bpr = g.bpr; p.eyes = g.eyes; p.comps = g.comps; p.frames = (uint32_t)j->frames;
+    p.row0 = g.band_begin * g.eyes;
+    p.rows = (g.band_end - g.band_begin) * g.eyes;
+    const uint64_t blocks = (uint64_t)p.rows * p.bpr;
+    p.chunks = (uint32_t)((blocks + SDCT_TB - 1) / SDCT_TB);
+    const uint64_t pstr = j->pitch | j->eye_stride | j->pixel_frame_stride;
+    p.pixels_aligned8 = aligned(pixels, 8) && (pstr & 7) == 0 && (op != SDCT_K_OP_ROUNDTRIP || aligned(pixels_out, 8));
+    const uint64_t cstr = j->coef_frame_stride | j->coef_comp_stride;
+    p.coef_aligned16 = coefs && aligned(coefs, 16) && (cstr & 15) == 0;
+    p.coef_aligned4 = coefs && aligned(coefs, 4) && ((cstr | j->coef_plane_stride) & 3) == 0;
+    if (blocks == 0 || j->frames == 0) return SDCT_OK;
+    CU_TRY(cudaSetDevice(ctx->device));
+    const int mode = (j->flags & SDCT_FAST) ? SDCT_K_FAST : SDCT_K_EXACT;
+    const int x3 = (j->flags & SDCT_QUIRK_AVX_X3) ? 1 : 0;
+    CU_TRY(sdct_k_launch(op, j->layout, mode, x3, &p, stream ? stream : ctx->stream));
+    ctx->launches.fetch_add(1, std::memory_order_relaxed);
+    return SDCT_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+void sdct_job_dense(sdct_job *job, int layout, int flags, int components, int eyes, uint64_t width,
+                    uint64_t height, uint64_t frames)
+{
+    memset(job, 0, sizeof(*job));
+    if (layout != SDCT_LAYOUT_C) eyes = 1;
+    job->layout = layout; job->flags = flags; job->components = components; job->eyes = eyes;
+    job->width = width; job->height = height; job->frames = frames;
+    job->pitch = width * components;
+    job->eye_stride = job->pitch * height;
+    job->pixel_frame_stride = job->eye_stride * eyes;
+    job->coef_plane_stride = width * height * eyes / 64;
+    job->coef_comp_stride = width * height * eyes;
+    job->coef_frame_stride = job->coef_comp_stride * components;
+}
+
+const char *sdct_last_error(void) { return g_err; }
+int sdct_abi_version(void) { return SDCT_ABI_VERSION; }
+
+int sdct_device_count(void)
+{
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+    return n;
+}
+
+int sdct_create(int device, sdct_context **out)
+{
+    if (!out) return fail(SDCT_INVALID_PARAMETER, "out is null");
+    *out = nullptr;
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess || n == 0) {
+        cudaGetLastError();
+        return fail(SDCT_NO_DEVICE, "no CUDA device visible - this library has no CPU fallback");
+    }
+    if (device < 0 || device >= n) return fail(SDCT_INVALID_PARAMETER, "device %d out of range (0..%d)", device, n - 1);
+    cudaDeviceProp prop;
+    CU_TRY(cudaGetDeviceProperties(&prop, device));
+    if (prop.major != 10) return fail(SDCT_NO_DEVICE, "device %d is sm_%d%d; kernels are built for sm_100a only", device, prop.major, prop.minor);
+    CU_TRY(cudaSetDevice(device));
+    sdct_context *c = new sdct_context();
+    c->device = device;
+    c->sm_count = prop.multiProcessorCount;
+    CU_TRY(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+    for (Slot &s : c->slots) {
+        CU_TRY(cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking));
+        CU_TRY(cudaEventCreateWithFlags(&s.done, cudaEventDisableTiming));
+    }
+    *out = c;
+    return SDCT_OK;
+}
+
+void sdct_destroy(sdct_context *c)
+{
+    if (!c) return;
+    cudaSetDevice(c->device);
+    for (Slot &s : c->slots) {
+        if (s.stream) { cudaStreamSynchronize(s.stream); cudaStreamDestroy(s.stream); }
+        if (s.done) cudaEventDestroy(s.done);
+        cudaFree(s.d_pix); cudaFree(s.d_coef);
+        cudaFreeHost(s.h_in); cudaFreeHost(s.h_out);
+    }
+    if (c->stream) { cudaStreamSynchronize(c->stream); cudaStreamDestroy(c->stream); }
+    delete c;
+}
+
+int sdct_sm_count(const sdct_context *c) { return c ? c->sm_count : 0; }
+uint64_t sdct_kernel_launches(const sdct_context *c) { return c ? c->launches.load() : 0; }
+
+int sdct_synchronize(sdct_context *c)
+{
+    if (!c) return fail(SDCT_INVALID_PARAMETER, "context is null");
+    CU_TRY(cudaSetDevice(c->device));
+    CU_TRY(cudaStreamSynchronize(c->stream));
+    for (Slot &s : c->slots) CU_TRY(cudaStreamSynchronize(s.stream));
+    return SDCT_OK;
+}
+
+int sdct_forward_device(sdct_context *c, const sdct_job *j, const void *d_pixels, const float *lut, void *d_coefs, void *stream)
+{
+    return run_device(c, SDCT_K_OP_FORWARD, j, (const uint8_t *)d_pixels, (uint8_t *)d_coefs, nullptr, lut, (cudaStream_t)stream);
+}
+
+int sdct_inverse_device(sdct_context *c, const sdct_job *j, const void *d_coefs, const float *lut, void *d_pixels, void *stream)
+{
+    return run_device(c, SDCT_K_OP_INVERSE, j, (const uint8_t *)d_pixels, (uint8_t *)const_cast<void *>(d_coefs), nullptr, lut, (cudaStream_t)stream);
+}
+
+int sdct_roundtrip_device(sdct_context *c, const sdct_job *j, const void *d_in, const float *lut, void *d_out, void *stream)
+{
+    return run_device(c, SDCT_K_OP_ROUNDTRIP, j, (const uint8_t *)d_in, nullptr, (uint8_t *)d_out, lut, (cudaStream_t)stream);
+}
+
+void *sdct_host_alloc(size_t bytes)
+{
+    void *p = nullptr;
+    if (cudaHostAlloc(&p, bytes ? bytes : 1, cudaHostAllocDefault) != cudaSuccess) {
+        fail(SDCT_CUDA_ERROR, "cudaHostAlloc(%zu) failed: %s", bytes, cudaGetErrorString(cudaGetLastError()));
+        return nullptr;
+    }
+    return p;
+}
+
+void sdct_host_free(void *p) { if (p) cudaFreeHost(p); }
+
+void sdct_shard_range(uint64_t total, int rank, int world, uint64_t *begin, uint64_t *end)
+{
+    if (world < 1) world = 1;
+    if (rank < 0) rank = 0;
+    if (rank >= world) rank = world - 1;
+    const uint64_t q = total / (uint64_t)world, r = total % (uint64_t)world;
+    const uint64_t b = q * (uint64_t)rank + std::min<uint64_t>((uint64_t)rank, r);
+    if (begin) *begin = b;
+    if (end) *end = b + q + ((uint64_t)rank < r ? 1 : 0);
+}
+
+}  // extern "C"

@@ -1,0 +1,35 @@
+// sdct_kernels.h - launch interface between the C-ABI host layer (sdct_api.cpp) and the
+// sm_100a kernels (sdct_kernels.cu).  Internal; the public surface is include/sdct.h.
+#pragma once
+#include <cstdint>
+#include <cuda_runtime.h>
+
+#define SDCT_TB 128  // threads per CTA = 8x8 blocks per CTA
+
+#define SDCT_K_LAYOUT_A 0
+#define SDCT_K_LAYOUT_B 1
+#define SDCT_K_LAYOUT_C 2
+#define SDCT_K_EXACT 0
+#define SDCT_K_FAST 1
+#define SDCT_K_OP_FORWARD 0
+#define SDCT_K_OP_INVERSE 1
+#define SDCT_K_OP_ROUNDTRIP 2
+
+struct KParams {
+    const uint8_t *pixels;    // forward/roundtrip: input; inverse: output
+    uint8_t *coefs;           // forward: output; inverse: input (unused by roundtrip)
+    uint8_t *pixels_out;      // roundtrip output
+    uint64_t pitch, eye_stride, pixel_frame_stride;
+    uint64_t coef_frame_stride, coef_comp_stride, coef_plane_stride;
+    uint32_t bpr;             // 8x8 blocks per pixel row
+    uint32_t eyes;
+    uint32_t row0, rows;      // block-row window: row = band*eyes + eye
+    uint32_t comps;
+    uint32_t frames;
+    uint32_t chunks;          // CTAs per (frame, component)
+    uint32_t pixels_aligned8, coef_aligned16, coef_aligned4;
+    float tab[64];            // forward: quantiser scale; inverse: dequantiser scale
+    float tab2[64];           // roundtrip: dequantiser scale
+};
+
+extern "C" cudaError_t sdct_k_launch(int op, int layout, int mode, int x3, const KParams *p, cudaStream_t s);

@@ -1,0 +1,272 @@
+"""GPU parity: the CUDA path (through the C ABI) against the CPU oracle on identical inputs.
+Bar: byte-identical for every forward mode and for the inverse (integer outputs)."""
+import numpy as np
+import pytest
+
+import oraclelib as ol
+from conftest import make_image
+
+pytestmark = pytest.mark.gpu
+
+torch = pytest.importorskip("torch")
+import simd_dct_b200 as sd  # noqa: E402
+
+LAYOUTS = [sd.LAYOUT_A, sd.LAYOUT_B, sd.LAYOUT_C]
+
+
+def dev(a):
+    return torch.from_numpy(np.ascontiguousarray(a)).cuda()
+
+
+def gpu_forward(ctx, img, lut, layout, flags=sd.EXACT, eyes=1, comps=1, **kw):
+    h = img.shape[0] // eyes
+    w = img.shape[1]
+    job = sd.dense_job(layout, w, h, frames=1, components=comps, eyes=eyes, flags=flags, **kw)
+    out = ctx.forward(dev(img), lut, job)
+    torch.cuda.synchronize()
+    return out.cpu().numpy()
+
+
+def rt_lut(layout):
+    """a LUT under which a round trip is meaningful: the reference applies no level shift, so
+    the DC entry must be large enough for DC (<= 8 normalised) not to saturate the u8 range."""
+    t = ol.lut(4).copy()
+    t[0] = 20.0
+    return (t * np.float32(255)).astype(np.float32) if layout == sd.LAYOUT_B else t
+
+
+def flags_for(layout, quirk=True):
+    return sd.EXACT | (sd.QUIRK_AVX_X3 if (layout == sd.LAYOUT_B and quirk) else 0)
+
+
+@pytest.mark.parametrize("kind", ["rand", "smooth"])
+@pytest.mark.parametrize("scale", [1, 8, 255])
+@pytest.mark.parametrize("layout", LAYOUTS)
+def test_config1_forward_exact(ctx, oracle, kind, scale, layout):
+    """BASELINE config 1: 512x512 single plane, default LUT x1 / x8 / x255."""
+    img = make_image(kind, 512, 512)
+    lut = ol.lut(scale)
+    for quirk in ([True, False] if layout == sd.LAYOUT_B else [True]):
+        got = gpu_forward(ctx, img, lut, layout, flags_for(layout, quirk))
+        want = oracle.forward(layout, img, lut, quirks=ol.QUIRK_AVX_X3 if quirk else 0)
+        assert np.array_equal(got, want), f"{np.count_nonzero(got != want)} bytes differ"
+
+
+@pytest.mark.parametrize("layout", LAYOUTS)
+def test_forward_fast_matches_its_definition_and_stays_close_to_exact(ctx, oracle, layout):
+    img = make_image("smooth", 512, 512, seed=3)
+    for scale in (8, 64, 255):
+        lut = ol.lut(scale)
+        got = gpu_forward(ctx, img, lut, layout, sd.FAST)
+        want = oracle.forward(layout, img, lut, mode=ol.MODE_FAST)
+        assert np.array_equal(got, want)
+        exact = oracle.forward(layout, img, lut)  # true DCT (no X3 quirk)
+        d = np.abs(got.astype(int) - exact.astype(int))
+        assert d.max() <= 1
+        assert np.mean(d != 0) <= 1e-3, np.mean(d != 0)
+
+
+@pytest.mark.parametrize("layout", LAYOUTS)
+def test_stereo_and_mono_layouts_small_and_ragged(ctx, oracle, layout):
+    """edge shapes: one block, one group, non-multiple-of-CTA tails, eyes = 2 for layout C."""
+    shapes = [(8, 64), (16, 64), (24, 192), (8, 1024), (136, 320)]
+    if layout != sd.LAYOUT_B:
+        shapes += [(8, 8), (24, 40), (72, 1000)]
+    lut = ol.lut(16)
+    for (h, w) in shapes:
+        for eyes in ([1, 2] if layout == sd.LAYOUT_C else [1]):
+            img = make_image("rand", h * eyes, w, seed=h + w)
+            got = gpu_forward(ctx, img, lut, layout, flags_for(layout), eyes=eyes)
+            want = oracle.forward(layout, img, lut, quirks=ol.QUIRK_AVX_X3, eyes=eyes)
+            assert np.array_equal(got, want), (h, w, eyes)
+
+
+@pytest.mark.parametrize("layout", LAYOUTS)
+def test_band_window_leaves_other_bands_untouched(ctx, oracle, layout):
+    h, w = 128, 256
+    img = make_image("smooth", h, w, seed=5)
+    lut = ol.lut(32)
+    full = oracle.forward(layout, img, lut, quirks=ol.QUIRK_AVX_X3)
+    job = sd.dense_job(layout, w, h, flags=flags_for(layout), band_begin=3, band_end=11)
+    out = torch.full((h * w,), 0xA5, dtype=torch.uint8, device="cuda")
+    ctx.forward(dev(img), lut, job, out=out)
+    got = out.cpu().numpy()
+    # expected: window bands from the oracle, everything else still 0xA5
+    want = np.full(h * w, 0xA5, dtype=np.uint8)
+    bpr = w // 8
+    n0, n1 = 3 * bpr, 11 * bpr
+    if layout == sd.LAYOUT_C:
+        ps = h * w // 64
+        for i in range(64):
+            want[i * ps + n0:i * ps + n1] = full[i * ps + n0:i * ps + n1]
+    else:
+        want[n0 * 64:n1 * 64] = full[n0 * 64:n1 * 64]
+    assert np.array_equal(got, want)
+
+
+@pytest.mark.parametrize("layout", LAYOUTS)
+def test_interleaved_rgb_forward(ctx, oracle, layout):
+    """component reorder fused into the load: interleaved RGB -> 3 planar coefficient sets."""
+    h, w = 64, 192
+    img = make_image("smooth", h, w, seed=9, comps=3)
+    lut = ol.lut(24)
+    for flags, mode in ((flags_for(layout), ol.MODE_EXACT), (sd.FAST, ol.MODE_FAST)):
+        got = gpu_forward(ctx, img, lut, layout, flags, comps=3)
+        quirks = ol.QUIRK_AVX_X3 if mode == ol.MODE_EXACT else 0
+        want = np.concatenate([oracle.forward(layout, img, lut, mode=mode, quirks=quirks, comp=k) for k in range(3)])
+        assert np.array_equal(got, want)
+        planes = oracle.deinterleave(img)
+        want2 = np.concatenate([oracle.forward(layout, planes[k], lut, mode=mode, quirks=quirks) for k in range(3)])
+        assert np.array_equal(want, want2)
+
+
+@pytest.mark.parametrize("layout", LAYOUTS)
+def test_unaligned_pointers_and_padded_pitch(ctx, oracle, layout):
+    h, w, pitch = 40, 128, 128 + 13
+    img = make_image("rand", h, w, seed=11)
+    lut = ol.lut(8)
+    buf = torch.zeros(h * pitch + 64, dtype=torch.uint8, device="cuda")
+    view = buf[3:3 + h * pitch].view(h, pitch)
+    view[:, :w] = dev(img)
+    job = sd.dense_job(layout, w, h, flags=flags_for(layout))
+    job.pitch = pitch
+    outbuf = torch.zeros(h * w + 64, dtype=torch.uint8, device="cuda")
+    ctx.forward(buf[3:], lut, job, out=outbuf[1:])
+    got = outbuf[1:1 + h * w].cpu().numpy()
+    assert np.array_equal(got, oracle.forward(layout, img, lut, quirks=ol.QUIRK_AVX_X3))
+
+
+@pytest.mark.parametrize("layout", LAYOUTS)
+def test_inverse_and_fused_roundtrip(ctx, oracle, layout):
+    h, w = 256, 512
+    lut = rt_lut(layout)
+    for kind in ("smooth", "rand"):
+        for eyes in ([1, 2] if layout == sd.LAYOUT_C else [1]):
+            img = make_image(kind, h * eyes, w, seed=2)
+            coef = oracle.forward(layout, img, lut, eyes=eyes)
+            job = sd.dense_job(layout, w, h, eyes=eyes, flags=sd.EXACT)
+            got = ctx.inverse(dev(coef), lut, job).cpu().numpy().reshape(h * eyes, w)
+            want = oracle.inverse(layout, coef, w, h, lut, eyes=eyes)
+            assert np.array_equal(got, want)
+            rt = ctx.roundtrip(dev(img), lut, job).cpu().numpy().reshape(h * eyes, w)
+            assert np.array_equal(rt, want)
+            if kind == "smooth":
+                mse = np.mean((rt.astype(float) - img.astype(float)) ** 2)
+                assert 10 * np.log10(255 ** 2 / mse) > 30
+
+
+def test_roundtrip_error_no_worse_than_float64_inverse(ctx, oracle):
+    """SURVEY 8c acceptance test for the (unpinned) inverse: GPU fwd->inv error must not exceed
+    the error of oracle-forward -> float64 textbook inverse on the same input."""
+    h, w = 128, 128
+    img = make_image("smooth", h, w, seed=4)
+    n = np.arange(8)
+    Cm = np.sqrt(2 / 8) * np.cos((2 * n[None, :] + 1) * n[:, None] * np.pi / 16)
+    Cm[0] /= np.sqrt(2)
+    for layout in LAYOUTS:
+        lut = rt_lut(layout)
+        coef = oracle.forward(layout, img, lut)
+        job = sd.dense_job(layout, w, h)
+        got = ctx.inverse(dev(coef), lut, job).cpu().numpy().reshape(h, w).astype(float)
+        d = (lut.astype(np.float64) * np.float64(np.float32(0.95)))
+        ref = np.zeros((h, w))
+        bpr = w // 8
+        for by in range(h // 8):
+            for bx in range(bpr):
+                nblk = by * bpr + bx
+                if layout == sd.LAYOUT_A:
+                    q = coef[nblk * 64:(nblk + 1) * 64].astype(float)
+                    c = ((q - 127) / 255 * d).reshape(8, 8).T
+                elif layout == sd.LAYOUT_B:
+                    g = coef[(nblk // 8) * 512:(nblk // 8 + 1) * 512].reshape(64, 8)[:, nblk % 8].astype(float)
+                    c = ((g - 127) * d / 255).reshape(8, 8) / 255
+                else:
+                    q = coef.reshape(64, -1)[:, nblk].astype(float)
+                    c = ((q - 127) / 255 * d).reshape(8, 8)
+                ref[by * 8:by * 8 + 8, bx * 8:bx * 8 + 8] = np.clip(np.rint(Cm.T @ c @ Cm * 255), 0, 255)
+        err_gpu = np.abs(got - img).max(), np.mean((got - img) ** 2)
+        err_ref = np.abs(ref - img).max(), np.mean((ref - img) ** 2)
+        assert np.abs(got - ref).max() <= 1
+        assert err_gpu[0] <= err_ref[0] + 1 and err_gpu[1] <= err_ref[1] * 1.01 + 1e-3
+
+
+def test_batch_of_frames_equals_per_frame_and_shards(ctx, oracle):
+    """frames are independent: a batch equals the concatenation of its frames / of its shards."""
+    f, h, w = 6, 64, 128
+    imgs = np.stack([make_image("smooth", h, w, seed=s) for s in range(f)])
+    lut = ol.lut(16)
+    for layout in LAYOUTS:
+        job = sd.dense_job(layout, w, h, frames=f, flags=flags_for(layout))
+        got = ctx.forward(dev(imgs), lut, job).cpu().numpy().reshape(f, -1)
+        for k in range(f):
+            assert np.array_equal(got[k], oracle.forward(layout, imgs[k], lut, quirks=ol.QUIRK_AVX_X3))
+        parts = []
+        for r in range(4):
+            b, e = sd.shard_range(f, r, 4)
+            if e > b:
+                j = sd.dense_job(layout, w, h, frames=e - b, flags=flags_for(layout))
+                parts.append(ctx.forward(dev(imgs[b:e]), lut, j).cpu().numpy())
+        assert np.array_equal(np.concatenate(parts), got.reshape(-1))
+
+
+@pytest.mark.parametrize("name,layout", [("A", sd.LAYOUT_A), ("B", sd.LAYOUT_B), ("C", sd.LAYOUT_C)])
+def test_reference_entry_points_host_buffers(oracle, name, layout):
+    """the three simd_dct.h symbols on host buffers: same bytes, windows and result codes as
+    the reference-semantics oracle (and as the compiled reference when oracle/_ref travelled)."""
+    fn = {"A": sd.simdDCT_EncodeQuantizeBuffer, "B": sd.simdDCT_EncodeQuantize32ReorderBuffer,
+          "C": sd.simdDCT_EncodeQuantizeReorderStereoBuffer}[name]
+    sx, sy = 256, 128
+    img = make_image("rand", sy, sx, seed=21)
+    lut = ol.lut(8)
+    ref = ol.Reference("strict") if ol.have_reference("strict") else None
+    for (s, e) in ((0, sy), (0, 64), (64, 128), (16, 16), (40, 100), (300, 400)):
+        out = np.full(sx * sy, 7, dtype=np.uint8)
+        rc = fn(img.reshape(-1), out, lut, sx, sy, s, e)
+        rc2, want = oracle.ref_call(name, img, lut, sx, sy, s, e, fill=7)
+        assert rc == rc2 == 0
+        assert np.array_equal(out, want), (s, e)
+        if ref is not None and (name != "B" or "avx2" in ol.cpu_flags()):
+            ref.set_isa("avx2" if name == "B" else "scalar")
+            rc3, want3 = ref.call(name, img, lut, sx, sy, s, e, fill=7)
+            assert rc3 == 0 and np.array_equal(out, want3), (s, e)
+    out = np.zeros(sx * sy, dtype=np.uint8)
+    assert fn(None, out, lut, sx, sy, 0, sy) == sd.sdr_InvalidParameter
+    assert fn(img.reshape(-1), None, lut, sx, sy, 0, sy) == sd.sdr_InvalidParameter
+    assert fn(img.reshape(-1), out, lut, sx - 4, sy, 0, sy) == sd.sdr_NotSupported
+    assert fn(img.reshape(-1), out, lut, sx, sy - 4, 0, sy) == sd.sdr_NotSupported
+
+
+@pytest.mark.parametrize("layout", LAYOUTS)
+def test_host_pipeline_matches_device_path(ctx, oracle, layout, monkeypatch):
+    monkeypatch.setenv("SDCT_HOST_CHUNK_MB", "1")
+    lut = ol.lut(12)
+    for (f, h, w, eyes) in ((9, 256, 512, 1), (1, 1080 - 1080 % 8, 1920, 1), (2, 128, 256, 2)):
+        if eyes == 2 and layout != sd.LAYOUT_C:
+            continue
+        imgs = np.stack([make_image("smooth", h * eyes, w, seed=s) for s in range(f)])
+        job = sd.dense_job(layout, w, h, frames=f, eyes=eyes, flags=flags_for(layout))
+        dev_out = ctx.forward(dev(imgs), lut, job).cpu().numpy()
+        host_out = ctx.forward_host(imgs, lut, job)
+        assert np.array_equal(dev_out, host_out)
+        back_dev = ctx.inverse(dev(dev_out), lut, job).cpu().numpy()
+        back_host = ctx.inverse_host(host_out, lut, job)
+        assert np.array_equal(back_dev, back_host)
+
+
+def test_full_size_1080p_batch_properties(ctx, oracle):
+    """BASELINE config 2 size (1080p luma; 8 of the 64 frames here): oracle parity on two
+    frames, and batch == shards on all (size-independent property)."""
+    f, h, w = 8, 1080, 1920
+    imgs = np.stack([make_image("smooth" if s % 2 else "rand", h, w, seed=s) for s in range(f)])
+    lut = ol.lut(8)
+    d = dev(imgs)
+    for layout in (sd.LAYOUT_B, sd.LAYOUT_A):
+        job = sd.dense_job(layout, w, h, frames=f, flags=flags_for(layout))
+        got = ctx.forward(d, lut, job)
+        for k in (0, 5):
+            want = oracle.forward(layout, imgs[k], lut, quirks=ol.QUIRK_AVX_X3)
+            assert np.array_equal(got.view(f, -1)[k].cpu().numpy(), want)
+        half = sd.dense_job(layout, w, h, frames=f // 2, flags=flags_for(layout))
+        lo = ctx.forward(d[:f // 2], lut, half)
+        hi = ctx.forward(d[f // 2:], lut, half)
+        assert torch.equal(torch.cat([lo, hi]), got)
