@@ -52,46 +52,81 @@ def synth_frames(frames, h, w, seed):
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md)."""
-    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
-         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+    """SM clock / throttle reasons sampled through NVML while the GPU runs the timed work
+    (B200_PROFILING.md "clocks line").  NVML is polled from a thread (about 1 kHz) because the
+    timed region of this workload lasts milliseconds, far below nvidia-smi's sampling period."""
+    REASONS = {0x8: "hw_slowdown", 0x40: "hw_thermal_slowdown", 0x20: "sw_thermal_slowdown", 0x4: "sw_power_cap"}
 
-    def __init__(self, index):
-        self.index = index
-        self.proc = None
+    def __init__(self, torch_index):
+        self.samples = []       # (t, sm_mhz, reasons_mask, power_w)
+        self.marks = {}
+        self.h = None
+        self.err = None
+        try:
+            import pynvml
+            import torch
+            self.nv = pynvml
+            pynvml.nvmlInit()
+            uuid = str(torch.cuda.get_device_properties(torch_index).uuid)
+            if not uuid.startswith("GPU-"):
+                uuid = "GPU-" + uuid
+            try:
+                self.h = pynvml.nvmlDeviceGetHandleByUUID(uuid)
+            except Exception:
+                self.h = pynvml.nvmlDeviceGetHandleByIndex(torch_index)
+            self.max_mhz = float(pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM))
+        except Exception as e:  # noqa: BLE001
+            self.err = repr(e)
+        self._stop = threading.Event()
+        self.thread = None
+
+    def _reasons(self):
+        nv = self.nv
+        for name in ("nvmlDeviceGetCurrentClocksEventReasons", "nvmlDeviceGetCurrentClocksThrottleReasons"):
+            fn = getattr(nv, name, None)
+            if fn is not None:
+                try:
+                    return int(fn(self.h))
+                except Exception:  # noqa: BLE001
+                    continue
+        return 0
+
+    def _loop(self):
+        nv = self.nv
+        while not self._stop.is_set():
+            try:
+                mhz = float(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                try:
+                    pw = nv.nvmlDeviceGetPowerUsage(self.h) / 1000.0
+                except Exception:  # noqa: BLE001
+                    pw = None
+                self.samples.append((time.perf_counter(), mhz, self._reasons(), pw))
+            except Exception as e:  # noqa: BLE001
+                self.err = repr(e)
+                return
+            time.sleep(0.0005)
 
     def start(self):
-        try:
-            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
-                                          "-lms", "50", "-i", str(self.index)], stdout=subprocess.PIPE,
-                                         stderr=subprocess.DEVNULL, text=True)
-        except Exception:
-            self.proc = None
+        if self.h is not None:
+            self.thread = threading.Thread(target=self._loop, daemon=True)
+            self.thread.start()
 
-    def stop(self):
-        if self.proc is None:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        time.sleep(0.06)
-        self.proc.terminate()
-        try:
-            out, _ = self.proc.communicate(timeout=5)
-        except Exception:
-            self.proc.kill()
-            out = ""
-        sm, mx, reasons = [], [], set()
-        for line in out.splitlines():
-            f = [x.strip() for x in line.split(",")]
-            if len(f) < 9:
-                continue
-            try:
-                sm.append(float(f[1])); mx.append(float(f[2]))
-            except ValueError:
-                continue
-            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[5:9]):
-                if v.lower().startswith("active"):
-                    reasons.add(name)
-        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": sorted(reasons), "samples": len(sm)}
+    def mark(self, name):
+        self.marks[name] = time.perf_counter()
+
+    def stop(self, t0=None, t1=None):
+        if self.thread is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvml unavailable: %s" % self.err]}
+        self._stop.set()
+        self.thread.join(timeout=2)
+        sel = [x for x in self.samples if (t0 is None or x[0] >= t0) and (t1 is None or x[0] <= t1)]
+        mask = 0
+        for x in sel:
+            mask |= x[2]
+        pw = [x[3] for x in sel if x[3] is not None]
+        return {"sm_mhz": statistics.median(x[1] for x in sel) if sel else None, "sm_min_mhz": min((x[1] for x in sel), default=None),
+                "sm_max_mhz": self.max_mhz, "reasons": sorted(v for k, v in self.REASONS.items() if mask & k),
+                "samples": len(sel), "power_w_max": max(pw) if pw else None}
 
 
 # ---- CPU reference arm --------------------------------------------------------------------------
@@ -169,6 +204,8 @@ def main():
     ap.add_argument("--frames", type=int, default=64)
     ap.add_argument("--width", type=int, default=1920)
     ap.add_argument("--height", type=int, default=1080)
+    ap.add_argument("--preheat", type=float, default=0.4, help="seconds of untimed back-to-back steps before the timed region (clock ramp)")
+    ap.add_argument("--no-e2e", action="store_true", help="skip the host-buffer leg (profiling runs)")
     ap.add_argument("--no-variants", action="store_true", help="skip the secondary (non-headline) measurements")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
@@ -236,6 +273,7 @@ def main():
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
+    os.environ["SDCT_DEVICE"] = str(local_rank)  # device of the simd_dct.h shim's process-wide context
     ctx = sd.Context(local_rank)
     frames_np = synth_frames(F, H, W, seed=1234 + rank)
     d_in = torch.from_numpy(frames_np).cuda()
@@ -243,26 +281,43 @@ def main():
     job = sd.dense_job(sd.LAYOUT_B, W, H, frames=F, flags=flags)
     d_out = torch.empty(F * H * W, dtype=torch.uint8, device="cuda")
 
-    def timed(fn, steps, warmup):
+    def timed(fn, steps, warmup, preheat_s=0.0):
+        """warm-up (>= `warmup` steps, plus `preheat_s` seconds of the same step so that the SM
+        clock has ramped), then exactly `steps` steps between two CUDA events recorded on the
+        stream the kernels are launched on (torch's current stream - Context passes it through)."""
         for _ in range(warmup):
             fn()
+        torch.cuda.synchronize()
+        t_end = time.perf_counter() + preheat_s
+        while time.perf_counter() < t_end:
+            for _ in range(50):
+                fn()
+            torch.cuda.synchronize()
         barrier()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         n0 = ctx.kernel_launches
+        w0 = time.perf_counter()
         e0.record()
         for _ in range(steps):
             fn()
         e1.record()
         torch.cuda.synchronize()
+        w1 = time.perf_counter()
         ms = e0.elapsed_time(e1)
         barrier()
-        return max_over_ranks(ms) / steps, ctx.kernel_launches - n0
+        return max_over_ranks(ms) / steps, ctx.kernel_launches - n0, (w0, w1)
 
     sampler = ClockSampler(local_rank)
     if rank == 0:
         sampler.start()
-    ms_step, launches = timed(lambda: ctx.forward(d_in, lut, job, out=d_out), args.steps, args.warmup)
-    clocks = sampler.stop() if rank == 0 else None
+    t_heat = time.perf_counter()
+    ms_step, launches, (w0, w1) = timed(lambda: ctx.forward(d_in, lut, job, out=d_out), args.steps, args.warmup, preheat_s=args.preheat)
+    clocks = None
+    if rank == 0:
+        # the same kernel runs back to back from t_heat + warm-up to w1: the clock samples of that
+        # window are "under load"; the timed region itself is its last `steps` launches
+        clocks = sampler.stop(t_heat + 0.1, w1)
+        clocks["window"] = "0.3 s of back-to-back launches of the timed kernel ending with the timed region (%.2f ms)" % ((w1 - w0) * 1e3)
     value = world * blocks_per_rank / (ms_step * 1e-3)
 
     # roofline of the dominant (only) kernel: algorithmic bytes per launch / average launch duration
@@ -279,22 +334,34 @@ def main():
                 "traffic": traffic, "peak_source": peak_src, "kernel": "sdct::forward_kernel<layout B, exact, X3>",
                 "algorithmic_bytes_per_launch": blocks_per_rank * BYTES_PER_BLOCK}
 
-    # e2e: host buffers through the public API, H2D + kernel + D2H inside the timed region
-    h_in = torch.from_numpy(frames_np).pin_memory()
-    h_out = torch.empty(F * H * W, dtype=torch.uint8).pin_memory()
-    e2e_steps = max(3, min(args.steps, 8))
-    for _ in range(2):
-        ctx.forward_host(h_in, lut, job, out=h_out)
-    barrier()
-    t0 = time.perf_counter()
-    for _ in range(e2e_steps):
-        ctx.forward_host(h_in, lut, job, out=h_out)
-    dt = max_over_ranks((time.perf_counter() - t0) / e2e_steps)
-    barrier()
-    e2e = {"value": world * blocks_per_rank / dt, "unit": UNIT, "h2d_bytes_per_step": F * H * W,
-           "d2h_bytes_per_step": F * H * W, "ms_per_step": dt * 1e3, "steps": e2e_steps,
-           "api": "sdct_forward_host (pinned host buffers, 4-slot H2D/kernel/D2H pipeline)"}
-    assert torch.equal(h_out.cuda(), d_out), "host pipeline and device path disagree"
+    # e2e: HOST buffers through the reference-facing call (the simd_dct.h symbol exported by
+    # libsdct.so), H2D + kernel + D2H inside the timed region.  The batch is handed over the way a
+    # caller of the reference would hand it over: the F frames stacked into one plane of F*H rows
+    # (blocks are independent, so the bytes equal the per-frame results), sizeY = 2*F*H because the
+    # reference visits only rows below sizeY/2 (src/simd_dct.cpp:2243).
+    e2e = None
+    if not args.no_e2e:
+        h_in = torch.from_numpy(frames_np).pin_memory()
+        h_out = torch.empty(F * H * W, dtype=torch.uint8).pin_memory()
+        e2e_steps = max(3, min(args.steps, 10))
+
+        def e2e_step():
+            rc = sd.simdDCT_EncodeQuantize32ReorderBuffer(h_in, h_out, lut, W, 2 * F * H, 0, 2 * F * H)
+            assert rc == sd.sdr_Success, sd.last_error()
+        for _ in range(3):
+            e2e_step()
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(e2e_steps):
+            e2e_step()
+        dt = max_over_ranks((time.perf_counter() - t0) / e2e_steps)
+        barrier()
+        e2e = {"value": world * blocks_per_rank / dt, "unit": UNIT, "h2d_bytes_per_step": F * H * W,
+               "d2h_bytes_per_step": F * H * W, "ms_per_step": dt * 1e3, "steps": e2e_steps,
+               "gbps_each_way": F * H * W / dt / 1e9,
+               "api": "simdDCT_EncodeQuantize32ReorderBuffer (simd_dct.h shim of libsdct.so) on pinned host buffers; "
+                      "synchronous call = chunked H2D / kernel / D2H pipeline, wall clock"}
+        assert torch.equal(h_out.cuda(), d_out), "host pipeline and device path disagree"
 
     # secondary measurements (same batch; informative, not the headline)
     variants = {}
@@ -302,7 +369,7 @@ def main():
         vs = max(3, args.steps // 4)
 
         def add(name, fn, bytes_per_block=BYTES_PER_BLOCK, nblocks=blocks_per_rank):
-            ms, _ = timed(fn, vs, 2)
+            ms, _, _ = timed(fn, vs, 3)
             variants[name] = {"blocks_per_s": world * nblocks / (ms * 1e-3), "ms_per_step": ms,
                               "gbps_per_gpu": nblocks * bytes_per_block / (ms * 1e-3) / 1e9,
                               "frac_of_hbm_peak": nblocks * bytes_per_block / (ms * 1e-3) / 1e9 / peak}

@@ -129,8 +129,11 @@ class Context:
 
     @staticmethod
     def _stream():
+        """torch's current stream, so that torch events and tensors order with the launch.  The
+        legacy default stream has handle 0, which the C ABI reads as "the context's own stream";
+        pass cudaStreamLegacy (handle 1) for it instead."""
         import torch
-        return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+        return C.c_void_p(torch.cuda.current_stream().cuda_stream or 1)
 
     def _coef_bytes(self, job: Job) -> int:
         return int(job.frames * job.coef_frame_stride)
