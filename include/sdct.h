@@ -90,7 +90,8 @@ int sdct_sm_count(const sdct_context *ctx);
 /* number of kernel launches issued through this context so far */
 uint64_t sdct_kernel_launches(const sdct_context *ctx);
 
-/* device-resident operations; `stream` is a cudaStream_t (NULL = the context's own stream).
+/* device-resident operations; `stream` is a cudaStream_t (NULL = the context's own non-blocking stream;
+ * pass cudaStreamLegacy, i.e. (void *)1, for the legacy default stream).
  * lut = the caller's 64-entry quantisation table in host memory (pQuantizeLUT of
  * src/simd_dct.h:29-31); the scale tables are derived from it exactly as
  * src/simd_dct.cpp:194-212 / :2236-2239 do. */
@@ -107,6 +108,13 @@ int sdct_forward_host(sdct_context *ctx, const sdct_job *job, const void *h_pixe
                       void *h_coefs);
 int sdct_inverse_host(sdct_context *ctx, const sdct_job *job, const void *h_coefs, const float *lut,
                       void *h_pixels);
+
+/* test hook: runs one of the device 8-point kernels on n vectors of 8 floats (host memory, in place)
+ * so that tests can compare the GPU arithmetic bit for bit with the CPU restatement.
+ * kind: 0 forward/scalar order (src/simd_dct.cpp:148-171), 1 forward/AVX2 order (:2160-2183),
+ * 2 = 1 with the reference's X3 sign (:2181), 3 forward/FAST, 4 inverse, 5 element-wise x/255.f;
+ * kinds 8, 9, 10 are 0, 1, 2 in their second-pass form (first butterfly stage issued as scalar adds) */
+int sdct_selftest_dct8(sdct_context *ctx, int kind, float *h_data, size_t n);
 
 /* synchronise the context's streams */
 int sdct_synchronize(sdct_context *ctx);

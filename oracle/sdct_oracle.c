@@ -136,18 +136,21 @@ static uint8_t quant_avx(float c, float q)
     return (uint8_t)(r > 255 ? 255 : (r < 0 ? 0 : r));
 }
 
-/* saturate to [0,1]; NaN -> 0 (PTX .sat semantics) */
-static float sat01(float x) { return x > 0.f ? (x < 1.f ? x : 1.f) : 0.f; }
-
-/* this repo's fast quantiser / pixel rounding: rne(255 * sat(.)) via the 1.5*2^23 trick */
-static uint8_t unit_to_u8(float y01)
+/* this repo's fast quantiser: the AVX2 path's form with a single pre-folded scale,
+ * clamp(rne(fl(c * qs)) + 127, 0, 255).  |c * qs| < 2^31 is guaranteed by the library's table check. */
+static uint8_t quant_fast(float c, float qs)
 {
-    const float t = fmaf(y01, 255.f, 12582912.f);
-    uint32_t bits;
-    memcpy(&bits, &t, 4);
-    return (uint8_t)(bits & 0xffu);
+    long r = lrintf(c * qs) + 127;     /* default rounding mode = nearest even */
+    return (uint8_t)(r > 255 ? 255 : (r < 0 ? 0 : r));
 }
-static uint8_t quant_fast(float c, float qs) { return unit_to_u8(sat01(fmaf(c, qs, 127.0f / 255.0f))); }
+
+/* this repo's pixel rounding for the inverse: clamp(rne(x), 0, 255), x in pixel units */
+static uint8_t pixel_u8(float x)
+{
+    if (!(x > 0.f)) return 0;
+    if (x >= 255.f) return 255;
+    return (uint8_t)lrintf(x);
+}
 
 void sdct_oracle_tables(const float lut[64], int layout, float out[64], int which)
 {
@@ -156,11 +159,12 @@ void sdct_oracle_tables(const float lut[64], int layout, float out[64], int whic
         switch (which) {
         case SDCT_O_TAB_SCALAR: out[i] = 1.f / d; break;                 /* :194-212 */
         case SDCT_O_TAB_AVX:    out[i] = 255.0f / d; break;              /* :2236-2239 */
-        case SDCT_O_TAB_FAST:   /* fwd fast: 1/8 (two passes) and, for A/C, the input 1/255 */
-            out[i] = (layout == SDCT_O_LAYOUT_B) ? 0.125f * (1.f / d) : (0.125f * (1.f / d)) / 255.f;
+        case SDCT_O_TAB_FAST:   /* fwd fast on raw pixels: 1/8 of the two unnormalised passes folded in;
+                                   A/C: 255 * (1/255) cancels, B: the AVX path's 255/d */
+            out[i] = (layout == SDCT_O_LAYOUT_B) ? 0.125f * (255.0f / d) : 0.125f * (1.f / d);
             break;
-        default:                /* SDCT_O_TAB_INVERSE: -> pixel/255 units, 1/8 folded in */
-            out[i] = (layout == SDCT_O_LAYOUT_B) ? ((d / 255.f) * 0.125f) / 255.f : (d * 0.125f) / 255.f;
+        default:                /* SDCT_O_TAB_INVERSE: level -> coefficient in pixel units, 1/8 folded in */
+            out[i] = (layout == SDCT_O_LAYOUT_B) ? (d / 255.f) * 0.125f : d * 0.125f;
             break;
         }
     }
@@ -237,14 +241,15 @@ static void block_fwd_fast(const uint8_t *px, size_t pitch, const float qs[64], 
         }
 }
 
-/* inverse (this repo): dequantise, vertical pass, horizontal pass, rne(255*sat(.)) */
+/* inverse (this repo): dequantise with one FMA, (q - 127) * tab = fma(q, tab, -(127 * tab)),
+ * vertical pass, horizontal pass, clamp(rne(.), 0, 255) */
 static void block_inv(const uint8_t q[64], const float tab[64], int transposed, uint8_t *px, size_t pitch)
 {
     float b[64], col[8];
     for (int u = 0; u < 8; u++)
         for (int v = 0; v < 8; v++) {
             const int i = transposed ? v * 8 + u : u * 8 + v;
-            b[u * 8 + v] = (float)((int)q[i] - 127) * tab[i];
+            b[u * 8 + v] = fmaf((float)q[i], tab[i], -(127.f * tab[i]));
         }
     for (int c = 0; c < 8; c++) {
         for (int r = 0; r < 8; r++) col[r] = b[r * 8 + c];
@@ -253,7 +258,7 @@ static void block_inv(const uint8_t q[64], const float tab[64], int transposed, 
     }
     for (int r = 0; r < 8; r++) sdct_oracle_idct8(b + r * 8);
     for (int r = 0; r < 8; r++)
-        for (int c = 0; c < 8; c++) px[r * pitch + c] = unit_to_u8(sat01(b[r * 8 + c]));
+        for (int c = 0; c < 8; c++) px[r * pitch + c] = pixel_u8(b[r * 8 + c]);
 }
 
 /* ---------------------------------------------------------------------------------------

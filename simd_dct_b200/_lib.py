@@ -39,6 +39,7 @@ SYMBOLS = {
     "sdct_roundtrip_device": (C.c_int, [_vp, _JP, _vp, _fp, _vp, _vp]),
     "sdct_forward_host": (C.c_int, [_vp, _JP, _vp, _fp, _vp]),
     "sdct_inverse_host": (C.c_int, [_vp, _JP, _vp, _fp, _vp]),
+    "sdct_selftest_dct8": (C.c_int, [_vp, C.c_int, _fp, _sz]),
     "sdct_synchronize": (C.c_int, [_vp]),
     "sdct_host_alloc": (_vp, [_sz]),
     "sdct_host_free": (None, [_vp]),

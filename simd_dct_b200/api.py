@@ -124,6 +124,14 @@ class Context:
     def kernel_launches(self) -> int:
         return self._lib.sdct_kernel_launches(self._h)
 
+    def selftest_dct8(self, kind: int, vectors):
+        """runs one device 8-point kernel on (n, 8) float32 vectors; returns the transformed copy"""
+        v = np.ascontiguousarray(vectors, dtype=np.float32).copy()
+        if v.ndim != 2 or v.shape[1] != 8:
+            raise ValueError("vectors must have shape (n, 8)")
+        check(self._lib.sdct_selftest_dct8(self._h, kind, v.ctypes.data_as(C.POINTER(C.c_float)), v.shape[0]))
+        return v
+
     def synchronize(self):
         check(self._lib.sdct_synchronize(self._h))
 

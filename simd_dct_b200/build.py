@@ -10,6 +10,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libsdct.so")
+KERNEL_PARTS = 8  # sdct_kernels.cu is compiled once per -DSDCT_PART (parallel template instantiation)
 SOURCES = ["sdct_kernels.cu", "sdct_api.cpp", "sdct_host.cpp", "simd_dct_shim.cpp"]
 HEADERS = ["sdct_kernels.h", "sdct_math.cuh", "sdct_internal.h", "../../include/sdct.h", "../../include/simd_dct.h"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
@@ -38,9 +39,12 @@ def build(force: bool = False, verbose: bool = False) -> str:
     os.makedirs(objdir, exist_ok=True)
     objs = []
     procs = []
-    for src in SOURCES:
-        obj = os.path.join(objdir, os.path.splitext(src)[0] + ".o")
-        cmd = [nvcc] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-c", os.path.join(CSRC, src), "-o", obj]
+    units = [(src, None) for src in SOURCES if src != "sdct_kernels.cu"] + [("sdct_kernels.cu", k) for k in range(KERNEL_PARTS)]
+    for src, part in units:
+        stem = os.path.splitext(src)[0] + ("" if part is None else ".part%d" % part)
+        obj = os.path.join(objdir, stem + ".o")
+        cmd = [nvcc] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ([] if part is None else ["-DSDCT_PART=%d" % part])
+        cmd += ["-c", os.path.join(CSRC, src), "-o", obj]
         procs.append((cmd, subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)))
         objs.append(obj)
     for cmd, p in procs:

@@ -52,22 +52,30 @@ int sdct_validate(const sdct_job *j, Geometry *g)
 
 namespace {
 
-// scale tables, in float exactly as the reference builds them
-int build_tables(const sdct_job *j, const float *lut, int op, float tab[64], float tab2[64])
+// scale tables, in float exactly as the reference builds them (EXACT) or as oracle/sdct_oracle.c
+// defines them (FAST, inverse); every value is duplicated for the two packed lanes of the kernels
+int build_tables(const sdct_job *j, const float *lut, int op, float2 tab[64], float2 tab2[64], float2 off[64])
 {
     if (!lut) return fail(SDCT_INVALID_PARAMETER, "quantisation LUT is null");
     const bool fast = (j->flags & SDCT_FAST) != 0;
+    const bool lb = j->layout == SDCT_LAYOUT_B;
     for (int i = 0; i < 64; i++) {
         const float d = lut[i] * 0.95f;                               // vr, src/simd_dct.cpp:191
-        float f;
-        if (fast) f = j->layout == SDCT_LAYOUT_B ? 0.125f * (1.f / d) : (0.125f * (1.f / d)) / 255.f;
-        else if (j->layout == SDCT_LAYOUT_B) f = 255.0f / d;          // :2236-2239
+        float f, cmax = 0.f;
+        if (fast) { f = lb ? 0.125f * (255.0f / d) : 0.125f * (1.f / d); cmax = 16384.f; }
+        else if (lb) { f = 255.0f / d; cmax = 2048.f; }               // :2236-2239
         else f = 1.f / d;                                             // :194-212
-        const float inv = j->layout == SDCT_LAYOUT_B ? ((d / 255.f) * 0.125f) / 255.f : (d * 0.125f) / 255.f;
-        if (op == SDCT_K_OP_INVERSE) { tab[i] = inv; tab2[i] = 0.f; }
-        else { tab[i] = f; tab2[i] = inv; }
-        if (!std::isfinite(tab[i]) || !std::isfinite(tab2[i]))
+        const float inv = lb ? (d / 255.f) * 0.125f : d * 0.125f;     // -> pixel units after the unnormalised passes
+        const float o = -(127.f * inv);
+        if (!std::isfinite(f) || !std::isfinite(inv))
             return fail(SDCT_INVALID_PARAMETER, "LUT entry %d (%g) gives a non-finite scale", i, (double)lut[i]);
+        // the round-to-nearest quantisers are exact while |coefficient * scale| < 2^31 (beyond that the
+        // reference's cvtps_epi32 returns INT_MIN, src/simd_dct.cpp:2224, which is not reproduced)
+        if (op != SDCT_K_OP_INVERSE && cmax != 0.f && std::fabs(f) * cmax >= 2147483648.f)
+            return fail(SDCT_INVALID_PARAMETER, "LUT entry %d (%g) is too small: |coefficient * scale| could reach 2^31", i, (double)lut[i]);
+        if (op == SDCT_K_OP_INVERSE) { tab[i] = make_float2(inv, inv); tab2[i] = make_float2(0.f, 0.f); }
+        else { tab[i] = make_float2(f, f); tab2[i] = make_float2(inv, inv); }
+        off[i] = make_float2(o, o);
     }
     return SDCT_OK;
 }
@@ -85,7 +93,7 @@ int run_device(sdct_context *ctx, int op, const sdct_job *j, const uint8_t *pixe
         return fail(SDCT_INVALID_PARAMETER, "null buffer");
     KParams p;
     memset(&p, 0, sizeof(p));
-    rc = build_tables(j, lut, op, p.tab, p.tab2);
+    rc = build_tables(j, lut, op, p.tab, p.tab2, p.off);
     if (rc) return rc;
     p.pixels = pixels; p.coefs = coefs; p.pixels_out = pixels_out;
     p.pitch = j->pitch; p.eye_stride = j->eye_stride; p.pixel_frame_stride = j->pixel_frame_stride;
@@ -95,12 +103,17 @@ int run_device(sdct_context *ctx, int op, const sdct_job *j, const uint8_t *pixe
     p.row0 = g.band_begin * g.eyes;
     p.rows = (g.band_end - g.band_begin) * g.eyes;
     const uint64_t blocks = (uint64_t)p.rows * p.bpr;
-    p.chunks = (uint32_t)((blocks + SDCT_TB - 1) / SDCT_TB);
+    p.chunks = (uint32_t)((blocks + SDCT_CTA_BLOCKS - 1) / SDCT_CTA_BLOCKS);
     const uint64_t pstr = j->pitch | j->eye_stride | j->pixel_frame_stride;
-    p.pixels_aligned8 = aligned(pixels, 8) && (pstr & 7) == 0 && (op != SDCT_K_OP_ROUNDTRIP || aligned(pixels_out, 8));
+    auto pix_aligned = [&](uint64_t a) {
+        return aligned(pixels, a) && (pstr & (a - 1)) == 0 && (op != SDCT_K_OP_ROUNDTRIP || aligned(pixels_out, a));
+    };
+    p.pixel_vec = (pix_aligned(16) && g.comps == 1 && (g.bpr & 1) == 0) ? 2 : (pix_aligned(8) ? 1 : 0);
     const uint64_t cstr = j->coef_frame_stride | j->coef_comp_stride;
     p.coef_aligned16 = coefs && aligned(coefs, 16) && (cstr & 15) == 0;
     p.coef_aligned4 = coefs && aligned(coefs, 4) && ((cstr | j->coef_plane_stride) & 3) == 0;
+    if (j->layout == SDCT_LAYOUT_C)  // 16-byte plane segments: every plane and the window start must be aligned too
+        p.coef_aligned16 = p.coef_aligned16 && (j->coef_plane_stride & 15) == 0 && (((uint64_t)p.row0 * p.bpr) & 15) == 0;
     if (blocks == 0 || j->frames == 0) return SDCT_OK;
     CU_TRY(cudaSetDevice(ctx->device));
     const int mode = (j->flags & SDCT_FAST) ? SDCT_K_FAST : SDCT_K_EXACT;
@@ -204,6 +217,24 @@ int sdct_inverse_device(sdct_context *c, const sdct_job *j, const void *d_coefs,
 int sdct_roundtrip_device(sdct_context *c, const sdct_job *j, const void *d_in, const float *lut, void *d_out, void *stream)
 {
     return run_device(c, SDCT_K_OP_ROUNDTRIP, j, (const uint8_t *)d_in, nullptr, (uint8_t *)d_out, lut, (cudaStream_t)stream);
+}
+
+int sdct_selftest_dct8(sdct_context *c, int kind, float *h_data, size_t n)
+{
+    if (!c || !h_data) return fail(SDCT_INVALID_PARAMETER, "null argument");
+    if (n == 0) return SDCT_OK;
+    if (n > 0x7fffffffu / 8) return fail(SDCT_NOT_SUPPORTED, "too many vectors");
+    CU_TRY(cudaSetDevice(c->device));
+    float *d = nullptr;
+    CU_TRY(cudaMalloc((void **)&d, n * 8 * sizeof(float)));
+    cudaError_t e = cudaMemcpyAsync(d, h_data, n * 8 * sizeof(float), cudaMemcpyHostToDevice, c->stream);
+    if (e == cudaSuccess) e = sdct_k_selftest(d, (uint32_t)n, kind, c->stream);
+    if (e == cudaSuccess) c->launches.fetch_add(1, std::memory_order_relaxed);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(h_data, d, n * 8 * sizeof(float), cudaMemcpyDeviceToHost, c->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+    cudaFree(d);
+    if (e != cudaSuccess) return fail(SDCT_CUDA_ERROR, "selftest failed: %s", cudaGetErrorString(e));
+    return SDCT_OK;
 }
 
 void *sdct_host_alloc(size_t bytes)

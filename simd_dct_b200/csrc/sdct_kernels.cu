@@ -1,29 +1,46 @@
 // sdct_kernels.cu - sm_100a kernels of the 8x8 block-DCT hot path and their launchers.
 //
-// Work decomposition (all kernels): the blocks of one coefficient set (one frame, one
-// component) form a linear sequence n = (band*eyes + eye)*blocks_per_row + bx, which is also
-// the order of every output layout (A: n*64, B: (n/8)*512, C: byte n of each of 64 planes).
-// A CTA owns SDCT_TB consecutive blocks of that sequence, one 8x8 block per thread, both
-// butterfly passes in registers; results are staged in shared memory in the final layout and
-// leave the SM as full-line coalesced stores.
+// Work decomposition (all kernels): the blocks of one coefficient set (one frame, one component)
+// form a linear sequence n = (band*eyes + eye)*blocks_per_row + bx, which is also the order of
+// every output layout (A: n*64, B: (n/8)*512, C: byte n of each of 64 planes).  A CTA owns
+// SDCT_CTA_BLOCKS = 256 consecutive blocks of that sequence; each of its 128 threads owns two of
+// them (P, Q) and runs both butterfly passes of both blocks in registers as packed-fp32 pairs
+// (sdct_math.cuh).  Quantised levels leave the registers through the saturating pack, are staged in
+// shared memory as the byte image of the CTA's output, and reach HBM as 16-byte coalesced stores;
+// pixels are read with 16-byte loads (one per row for the two adjacent blocks of a thread).
+//   layouts B, C: P, Q = blocks 2t, 2t+1 (adjacent: bytes (P,Q) of one coefficient are adjacent too)
+//   layout  A   : P, Q = blocks t, t+128 (a block's 64 bytes are contiguous; bank-friendly slots)
 #include "sdct_kernels.h"
 #include "sdct_math.cuh"
 
+// This file is compiled once per SDCT_PART (simd_dct_b200/build.py) so that the template
+// instantiations build in parallel: part 0 = dispatcher + self-test kernel, parts 1..8 = one
+// (operation, layout / mode) family each.
+#ifndef SDCT_PART
+#error "compile with -DSDCT_PART=<0..8>"
+#endif
+
 namespace sdct {
 
-constexpr int TB = SDCT_TB;  // threads (= blocks) per CTA
+constexpr int TB = SDCT_TB;              // threads per CTA
+constexpr int CB = SDCT_CTA_BLOCKS;      // 8x8 blocks per CTA
+
+// staging image of one CTA's coefficients
+constexpr int B_GROUP_PITCH = 528;       // layout B: 512 B group + 16 B pad (conflict-free STS.U16)
+constexpr int A_SLOT = 80;               // layout A: 64 B block + 16 B pad (conflict-free STS.128)
+constexpr int C_PITCH = CB;              // layout C: 64 rows of CB bytes
+constexpr int STAGE_BYTES = 32 * B_GROUP_PITCH > CB * A_SLOT ? 32 * B_GROUP_PITCH : CB * A_SLOT;
 
 struct BlockPos {
-    bool valid;
-    uint32_t n_local;   // index inside the processed window
-    uint64_t n_out;     // index inside the coefficient set
-    const uint8_t *px;  // top-left pixel (component 0) of the block
-    uint8_t *coef;      // start of the coefficient set of (frame, comp)
+    const uint8_t *px[2];   // top-left pixel (component 0) of blocks P, Q
+    bool valid[2];
+    uint8_t *coef;          // start of the coefficient set of (frame, comp)
     uint32_t comp;
-    uint32_t n0;        // first n_local of this CTA
-    uint32_t count;     // valid blocks in this CTA
+    uint32_t n0;            // first n_local of this CTA
+    uint32_t count;         // valid blocks in this CTA
 };
 
+template <int LAYOUT>
 SDCT_DEV BlockPos locate(const KParams &p)
 {
     BlockPos b;
@@ -32,24 +49,28 @@ SDCT_DEV BlockPos locate(const KParams &p)
     b.comp = fc % p.comps;
     const uint32_t frame = fc / p.comps;
     const uint32_t total = p.rows * p.bpr;
-    b.n0 = chunk * TB;
-    b.count = min((uint32_t)TB, total - b.n0);
-    b.n_local = b.n0 + threadIdx.x;
-    b.valid = threadIdx.x < b.count;
-    const uint32_t nl = b.valid ? b.n_local : b.n0;  // keep addresses in range
-    const uint32_t row = nl / p.bpr + p.row0;
-    const uint32_t bx = nl - (nl / p.bpr) * p.bpr;
-    const uint32_t band = row / p.eyes, eye = row - band * p.eyes;
-    b.n_out = (uint64_t)p.row0 * p.bpr + nl;
-    b.px = p.pixels + (uint64_t)frame * p.pixel_frame_stride + (uint64_t)eye * p.eye_stride +
-           (uint64_t)band * 8 * p.pitch + (uint64_t)bx * 8 * p.comps;
+    b.n0 = chunk * CB;
+    b.count = min((uint32_t)CB, total - b.n0);
+    const uint8_t *base = p.pixels + (uint64_t)frame * p.pixel_frame_stride;
+#pragma unroll
+    for (int k = 0; k < 2; k++) {
+        const uint32_t slot = (LAYOUT == SDCT_K_LAYOUT_A) ? threadIdx.x + k * TB : 2 * threadIdx.x + k;
+        b.valid[k] = slot < b.count;
+        const uint32_t nl = b.n0 + (b.valid[k] ? slot : 0);  // keep addresses in range
+        const uint32_t r = nl / p.bpr;
+        const uint32_t bx = nl - r * p.bpr;
+        const uint32_t row = r + p.row0;
+        const uint32_t band = row / p.eyes, eye = row - band * p.eyes;
+        b.px[k] = base + (uint64_t)eye * p.eye_stride + (uint64_t)band * 8 * p.pitch + (uint64_t)bx * 8 * p.comps;
+    }
     b.coef = p.coefs + (uint64_t)frame * p.coef_frame_stride + (uint64_t)b.comp * p.coef_comp_stride;
     return b;
 }
 
-// ---- pixel block -> 16 words (row r = words 2r, 2r+1), component extraction fused ----------
-template <int COMPS, bool VEC>
-SDCT_DEV void load_block_bytes(const uint8_t *px, uint64_t pitch, uint32_t comp, uint32_t w[16])
+// ---- pixel block -> 16 words (row r = words 2r, 2r+1), component extraction fused ----------------
+// VEC: 0 = byte loads, 1 = 8-byte loads, 2 = one 16-byte load per row for the adjacent pair (P, Q)
+template <int COMPS, int VEC>
+SDCT_DEV void load_block(const uint8_t *px, uint64_t pitch, uint32_t comp, uint32_t w[16])
 {
     if (COMPS == 1) {
 #pragma unroll
@@ -93,14 +114,36 @@ SDCT_DEV void load_block_bytes(const uint8_t *px, uint64_t pitch, uint32_t comp,
     }
 }
 
-// ---- forward transform of one block: bytes -> 16 packed coefficient words in layout order --
-template <int LAYOUT, int MODE, bool X3>
-SDCT_DEV void forward_block(const uint32_t w[16], const float *tab, uint32_t o[16])
+template <int COMPS, int VEC>
+SDCT_DEV void load_pair(const BlockPos &b, uint64_t pitch, uint32_t wp[16], uint32_t wq[16])
 {
-    float b[64];
+    if (COMPS == 1 && VEC == 2) {
+#pragma unroll
+        for (int r = 0; r < 8; r++) {
+            const uint4 v = __ldg(reinterpret_cast<const uint4 *>(b.px[0] + r * pitch));
+            wp[2 * r] = v.x; wp[2 * r + 1] = v.y; wq[2 * r] = v.z; wq[2 * r + 1] = v.w;
+        }
+    } else {
+        load_block<COMPS, (VEC ? 1 : 0)>(b.px[0], pitch, b.comp, wp);
+        load_block<COMPS, (VEC ? 1 : 0)>(b.px[1], pitch, b.comp, wq);
+    }
+}
+
+// ---- forward transform of the pair: pixel words -> 64 level bit patterns, b[u*8+v] ---------------
+// (u = vertical, v = horizontal frequency).  TABIDX maps the natural index to the layout's.
+template <int LAYOUT>
+SDCT_DEV constexpr int tab_index(int nat) { return LAYOUT == SDCT_K_LAYOUT_A ? (nat & 7) * 8 + (nat >> 3) : nat; }
+
+// does this (layout, mode) produce complemented levels (255 - q)?
+template <int LAYOUT, int MODE>
+SDCT_DEV constexpr bool complemented() { return MODE == SDCT_K_FAST || LAYOUT == SDCT_K_LAYOUT_B; }
+
+template <int LAYOUT, int MODE, bool X3>
+SDCT_DEV void forward_pair(const uint32_t wp[16], const uint32_t wq[16], const float2 *tab, F2 b[64])
+{
 #pragma unroll
     for (int i = 0; i < 64; i++) {
-        const float x = byte_to_float(w[i >> 2], i & 3);
+        const F2 x = make_float2(byte_to_float(wp[i >> 2], i & 3), byte_to_float(wq[i >> 2], i & 3));
         b[i] = (MODE == SDCT_K_EXACT && LAYOUT != SDCT_K_LAYOUT_B) ? div255(x) : x;
     }
     if (MODE == SDCT_K_FAST) {
@@ -110,171 +153,210 @@ SDCT_DEV void forward_block(const uint32_t w[16], const float *tab, uint32_t o[1
         for (int c = 0; c < 8; c++) dct8_fast<8>(b + c);
     } else if (LAYOUT == SDCT_K_LAYOUT_A) {  // rows, then columns (:343-358)
 #pragma unroll
-        for (int r = 0; r < 8; r++) dct8_scalar<1>(b + 8 * r);
+        for (int r = 0; r < 8; r++) dct8_scalar<1, false>(b + 8 * r);
 #pragma unroll
-        for (int c = 0; c < 8; c++) dct8_scalar<8>(b + c);
+        for (int c = 0; c < 8; c++) dct8_scalar<8, true>(b + c);
     } else if (LAYOUT == SDCT_K_LAYOUT_C) {  // columns, then rows (:224-241)
 #pragma unroll
-        for (int c = 0; c < 8; c++) dct8_scalar<8>(b + c);
+        for (int c = 0; c < 8; c++) dct8_scalar<8, false>(b + c);
 #pragma unroll
-        for (int r = 0; r < 8; r++) dct8_scalar<1>(b + 8 * r);
+        for (int r = 0; r < 8; r++) dct8_scalar<1, true>(b + 8 * r);
     } else {                                 // layout B: rows, then columns (:2158-2215)
 #pragma unroll
-        for (int r = 0; r < 8; r++) dct8_paired<1, X3>(b + 8 * r);
+        for (int r = 0; r < 8; r++) dct8_paired<1, false, X3>(b + 8 * r);
 #pragma unroll
-        for (int c = 0; c < 8; c++) dct8_paired<8, X3>(b + c);
+        for (int c = 0; c < 8; c++) dct8_paired<8, true, X3>(b + c);
     }
-    // b[u*8+v] = coefficient (u vertical, v horizontal).  Output byte i: A -> (u,v) = (i%8, i/8)
 #pragma unroll
-    for (int j = 0; j < 16; j++) {
-        uint32_t q[4];
-#pragma unroll
-        for (int k = 0; k < 4; k++) {
-            const int i = 4 * j + k;
-            const int src = (LAYOUT == SDCT_K_LAYOUT_A) ? (i & 7) * 8 + (i >> 3) : i;
-            if (MODE == SDCT_K_FAST) q[k] = quant_fast(b[src], tab[i]);
-            else if (LAYOUT == SDCT_K_LAYOUT_B) q[k] = quant_avx(b[src], tab[i]);
-            else q[k] = quant_scalar(b[src], tab[i]);
-        }
-        o[j] = pack4(q[0], q[1], q[2], q[3]);
+    for (int i = 0; i < 64; i++) {
+        const F2 t = tab[tab_index<LAYOUT>(i)];
+        b[i] = (MODE == SDCT_K_EXACT && LAYOUT != SDCT_K_LAYOUT_B) ? quant_scalar(b[i], t) : quant_rne_c(b[i], t);
     }
 }
 
-// ---- staging: thread's 16 words -> shared memory image of the CTA's output -----------------
+// ---- staging: level bit patterns -> shared-memory byte image of the CTA's output -----------------
 template <int LAYOUT>
-SDCT_DEV void stage_coefs(uint8_t *sm, const uint32_t o[16])
+SDCT_DEV void stage_levels(uint8_t *sm, const F2 b[64])
 {
     const uint32_t t = threadIdx.x;
-    if (LAYOUT == SDCT_K_LAYOUT_A) {
-        uint4 *d = reinterpret_cast<uint4 *>(sm + t * 64);
+    if (LAYOUT == SDCT_K_LAYOUT_B) {
+        // blocks 2t, 2t+1 of group t/4: coefficient i -> bytes [i*8 + 2(t%4), +1]
+        uint16_t *d = reinterpret_cast<uint16_t *>(sm + (t >> 2) * B_GROUP_PITCH + 2 * (t & 3));
 #pragma unroll
-        for (int j = 0; j < 4; j++) d[j ^ ((t >> 1) & 3)] = make_uint4(o[4 * j], o[4 * j + 1], o[4 * j + 2], o[4 * j + 3]);
-    } else if (LAYOUT == SDCT_K_LAYOUT_B) {
-        uint8_t *d = sm + (t >> 3) * 512 + (t & 7);
+        for (int i = 0; i < 64; i++) d[i * 4] = (uint16_t)pack_pq(b[i]);
+    } else if (LAYOUT == SDCT_K_LAYOUT_C) {
+        uint16_t *d = reinterpret_cast<uint16_t *>(sm + 2 * t);
 #pragma unroll
-        for (int i = 0; i < 64; i++) d[i * 8] = (uint8_t)(o[i >> 2] >> (8 * (i & 3)));
+        for (int i = 0; i < 64; i++) d[i * (C_PITCH / 2)] = (uint16_t)pack_pq(b[i]);
     } else {
+        // byte i of a block = coefficient (u, v) = (i%8, i/8): 16-byte chunk j holds v = 2j, 2j+1
 #pragma unroll
-        for (int i = 0; i < 64; i++) sm[i * TB + t] = (uint8_t)(o[i >> 2] >> (8 * (i & 3)));
+        for (int k = 0; k < 2; k++) {
+            uint4 *d = reinterpret_cast<uint4 *>(sm + (t + k * TB) * A_SLOT);
+#pragma unroll
+            for (int j = 0; j < 4; j++) {
+                uint32_t w[4];
+#pragma unroll
+                for (int q = 0; q < 4; q++) {
+                    const int v = 2 * j + (q >> 1), u0 = 4 * (q & 1);
+#define SDCT_L(u) (k ? b[(u) * 8 + v].y : b[(u) * 8 + v].x)
+                    w[q] = pack4_sat(SDCT_L(u0), SDCT_L(u0 + 1), SDCT_L(u0 + 2), SDCT_L(u0 + 3));
+#undef SDCT_L
+                }
+                d[j] = make_uint4(w[0], w[1], w[2], w[3]);
+            }
+        }
     }
 }
 
-template <int LAYOUT>
+SDCT_DEV uint4 xor4(uint4 v, uint32_t m) { return make_uint4(v.x ^ m, v.y ^ m, v.z ^ m, v.w ^ m); }
+
+// shared-memory image -> global memory, coalesced; COMPL undoes the complemented levels
+template <int LAYOUT, bool COMPL>
 SDCT_DEV void flush_coefs(const uint8_t *sm, const KParams &p, const BlockPos &b)
 {
     const uint32_t t = threadIdx.x;
     const uint64_t n_first = (uint64_t)p.row0 * p.bpr + b.n0;
+    const uint32_t m32 = COMPL ? 0xffffffffu : 0u;
     if (LAYOUT != SDCT_K_LAYOUT_C) {
         uint8_t *dst = b.coef + n_first * 64;
         const uint32_t chunks16 = b.count * 4;
+        auto src_off = [](uint32_t k) -> uint32_t {  // 16-byte chunk k of the output image
+            return LAYOUT == SDCT_K_LAYOUT_A ? (k >> 2) * A_SLOT + (k & 3) * 16 : (k >> 5) * B_GROUP_PITCH + (k & 31) * 16;
+        };
         if (p.coef_aligned16) {
-            for (uint32_t k = t; k < chunks16; k += TB) {
-                uint32_t src = k;
-                if (LAYOUT == SDCT_K_LAYOUT_A) src = (k & ~3u) | ((k & 3) ^ ((k >> 3) & 3));
-                reinterpret_cast<uint4 *>(dst)[k] = reinterpret_cast<const uint4 *>(sm)[src];
-            }
+#pragma unroll 4
+            for (uint32_t k = t; k < chunks16; k += TB)
+                reinterpret_cast<uint4 *>(dst)[k] = xor4(*reinterpret_cast<const uint4 *>(sm + src_off(k)), m32);
         } else {
-            for (uint32_t k = t; k < chunks16 * 16; k += TB) {
-                uint32_t c = k >> 4;
-                if (LAYOUT == SDCT_K_LAYOUT_A) c = (c & ~3u) | ((c & 3) ^ ((c >> 3) & 3));
-                dst[k] = sm[c * 16 + (k & 15)];
-            }
+            for (uint32_t k = t; k < chunks16 * 16; k += TB) dst[k] = sm[src_off(k >> 4) + (k & 15)] ^ (uint8_t)m32;
         }
     } else {
-        const uint32_t warp = t >> 5, lane = t & 31;
-        for (uint32_t i = warp; i < 64; i += TB / 32) {
-            uint8_t *dst = b.coef + (uint64_t)i * p.coef_plane_stride + n_first;
-            if (p.coef_aligned4 && (b.count & 3) == 0) {
-                for (uint32_t k = lane; k < b.count / 4; k += 32)
-                    reinterpret_cast<uint32_t *>(dst)[k] = reinterpret_cast<const uint32_t *>(sm + i * TB)[k];
-            } else {
-                for (uint32_t k = lane; k < b.count; k += 32) dst[k] = sm[i * TB + k];
+        if (p.coef_aligned16 && (b.count & 15) == 0) {
+            // 16 chunks per plane row: a warp writes two 256-byte row segments per instruction
+            const uint32_t per_row = b.count >> 4;
+            for (uint32_t k = t; k < 64 * per_row; k += TB) {
+                const uint32_t i = k / per_row, c = k - i * per_row;
+                uint8_t *dst = b.coef + (uint64_t)i * p.coef_plane_stride + n_first;
+                reinterpret_cast<uint4 *>(dst)[c] = xor4(*reinterpret_cast<const uint4 *>(sm + i * C_PITCH + c * 16), m32);
+            }
+        } else {
+            const uint32_t warp = t >> 5, lane = t & 31;
+            for (uint32_t i = warp; i < 64; i += TB / 32) {
+                uint8_t *dst = b.coef + (uint64_t)i * p.coef_plane_stride + n_first;
+                if (p.coef_aligned4 && (b.count & 3) == 0) {
+                    for (uint32_t k = lane; k < b.count / 4; k += 32)
+                        reinterpret_cast<uint32_t *>(dst)[k] = reinterpret_cast<const uint32_t *>(sm + i * C_PITCH)[k] ^ m32;
+                } else {
+                    for (uint32_t k = lane; k < b.count; k += 32) dst[k] = sm[i * C_PITCH + k] ^ (uint8_t)m32;
+                }
             }
         }
     }
 }
 
-template <int LAYOUT, int MODE, bool X3, int COMPS, bool VEC>
-__global__ void __launch_bounds__(SDCT_TB) forward_kernel(const __grid_constant__ KParams p)
+template <int LAYOUT, int MODE, bool X3, int COMPS, int VEC>
+__global__ void __launch_bounds__(SDCT_TB, 3) forward_kernel(const __grid_constant__ KParams p)
 {
-    __shared__ __align__(16) uint8_t sm[TB * 64];
-    const BlockPos b = locate(p);
-    uint32_t w[16], o[16];
-    load_block_bytes<COMPS, VEC>(b.px, p.pitch, b.comp, w);
-    forward_block<LAYOUT, MODE, X3>(w, p.tab, o);
-    stage_coefs<LAYOUT>(sm, o);
+    __shared__ __align__(16) uint8_t sm[STAGE_BYTES];
+    const BlockPos b = locate<LAYOUT>(p);
+    uint32_t wp[16], wq[16];
+    load_pair<COMPS, VEC>(b, p.pitch, wp, wq);
+    F2 v[64];
+    forward_pair<LAYOUT, MODE, X3>(wp, wq, p.tab, v);
+    stage_levels<LAYOUT>(sm, v);
     __syncthreads();
-    flush_coefs<LAYOUT>(sm, p, b);
+    flush_coefs<LAYOUT, complemented<LAYOUT, MODE>()>(sm, p, b);
 }
 
-// ---- inverse ------------------------------------------------------------------------------
-// coefficient bytes of this thread's block -> 16 words in natural order (word j = i 4j..4j+3)
+// ---- inverse ---------------------------------------------------------------------------------------
+// global coefficient bytes of this CTA -> shared-memory image (same image as the forward staging)
 template <int LAYOUT>
-SDCT_DEV void load_coefs(uint8_t *sm, const KParams &p, const BlockPos &b, uint32_t o[16])
+SDCT_DEV void fetch_coefs(uint8_t *sm, const KParams &p, const BlockPos &b)
 {
     const uint32_t t = threadIdx.x;
     const uint64_t n_first = (uint64_t)p.row0 * p.bpr + b.n0;
     if (LAYOUT != SDCT_K_LAYOUT_C) {
         const uint8_t *src = b.coef + n_first * 64;
         const uint32_t chunks16 = b.count * 4;
+        auto dst_off = [](uint32_t k) -> uint32_t {
+            return LAYOUT == SDCT_K_LAYOUT_A ? (k >> 2) * A_SLOT + (k & 3) * 16 : (k >> 5) * B_GROUP_PITCH + (k & 31) * 16;
+        };
         if (p.coef_aligned16) {
+#pragma unroll 4
             for (uint32_t k = t; k < chunks16; k += TB)
-                reinterpret_cast<uint4 *>(sm)[k] = __ldg(reinterpret_cast<const uint4 *>(src) + k);
+                *reinterpret_cast<uint4 *>(sm + dst_off(k)) = __ldg(reinterpret_cast<const uint4 *>(src) + k);
         } else {
-            for (uint32_t k = t; k < chunks16 * 16; k += TB) sm[k] = __ldg(src + k);
+            for (uint32_t k = t; k < chunks16 * 16; k += TB) sm[dst_off(k >> 4) + (k & 15)] = __ldg(src + k);
         }
     } else {
-        const uint32_t warp = t >> 5, lane = t & 31;
-        for (uint32_t i = warp; i < 64; i += TB / 32) {
-            const uint8_t *src = b.coef + (uint64_t)i * p.coef_plane_stride + n_first;
-            if (p.coef_aligned4 && (b.count & 3) == 0) {
-                for (uint32_t k = lane; k < b.count / 4; k += 32)
-                    reinterpret_cast<uint32_t *>(sm + i * TB)[k] = __ldg(reinterpret_cast<const uint32_t *>(src) + k);
-            } else {
-                for (uint32_t k = lane; k < b.count; k += 32) sm[i * TB + k] = __ldg(src + k);
+        if (p.coef_aligned16 && (b.count & 15) == 0) {
+            const uint32_t per_row = b.count >> 4;
+            for (uint32_t k = t; k < 64 * per_row; k += TB) {
+                const uint32_t i = k / per_row, c = k - i * per_row;
+                const uint8_t *src = b.coef + (uint64_t)i * p.coef_plane_stride + n_first;
+                *reinterpret_cast<uint4 *>(sm + i * C_PITCH + c * 16) = __ldg(reinterpret_cast<const uint4 *>(src) + c);
+            }
+        } else {
+            const uint32_t warp = t >> 5, lane = t & 31;
+            for (uint32_t i = warp; i < 64; i += TB / 32) {
+                const uint8_t *src = b.coef + (uint64_t)i * p.coef_plane_stride + n_first;
+                for (uint32_t k = lane; k < b.count; k += 32) sm[i * C_PITCH + k] = __ldg(src + k);
             }
         }
     }
-    __syncthreads();
-    if (LAYOUT == SDCT_K_LAYOUT_A) {
-        const uint32_t *s = reinterpret_cast<const uint32_t *>(sm + t * 64);
-#pragma unroll
-        for (int j = 0; j < 16; j++) o[j] = s[j];
-    } else if (LAYOUT == SDCT_K_LAYOUT_B) {
-        const uint8_t *s = sm + (t >> 3) * 512 + (t & 7);
-#pragma unroll
-        for (int j = 0; j < 16; j++)
-            o[j] = pack4(s[(4 * j) * 8], s[(4 * j + 1) * 8], s[(4 * j + 2) * 8], s[(4 * j + 3) * 8]);
-    } else {
-#pragma unroll
-        for (int j = 0; j < 16; j++)
-            o[j] = pack4(sm[(4 * j) * TB + t], sm[(4 * j + 1) * TB + t], sm[(4 * j + 2) * TB + t], sm[(4 * j + 3) * TB + t]);
-    }
 }
 
-// 16 coefficient words (layout order) -> 16 pixel words (row r = words 2r, 2r+1)
+// shared-memory image -> the pair's levels as floats, natural index b[u*8+v]
 template <int LAYOUT>
-SDCT_DEV void inverse_block(const uint32_t o[16], const float *tab, uint32_t w[16])
+SDCT_DEV void unstage_levels(const uint8_t *sm, F2 b[64])
 {
-    float b[64];
+    const uint32_t t = threadIdx.x;
+    if (LAYOUT == SDCT_K_LAYOUT_A) {
 #pragma unroll
-    for (int i = 0; i < 64; i++) {
-        const int dst = (LAYOUT == SDCT_K_LAYOUT_A) ? (i & 7) * 8 + (i >> 3) : i;
-        // (q - 127) exactly: byte into the mantissa of 2^23, subtract 2^23 + 127
-        const float q = __uint_as_float(__byte_perm(o[i >> 2], 0x4B000000u, 0x7650 + (i & 3))) - 8388735.0f;
-        b[dst] = fmul(q, tab[i]);
+        for (int k = 0; k < 2; k++) {
+            const uint4 *s = reinterpret_cast<const uint4 *>(sm + (t + k * TB) * A_SLOT);
+#pragma unroll
+            for (int j = 0; j < 4; j++) {
+                const uint4 q = s[j];
+                const uint32_t w[4] = {q.x, q.y, q.z, q.w};
+#pragma unroll
+                for (int e = 0; e < 16; e++) {
+                    const int i = 16 * j + e, u = i & 7, v = i >> 3;
+                    const float f = byte_to_float(w[e >> 2], e & 3);
+                    if (k) b[u * 8 + v].y = f; else b[u * 8 + v].x = f;
+                }
+            }
+        }
+    } else {
+        const uint16_t *s = LAYOUT == SDCT_K_LAYOUT_B
+                                ? reinterpret_cast<const uint16_t *>(sm + (t >> 2) * B_GROUP_PITCH + 2 * (t & 3))
+                                : reinterpret_cast<const uint16_t *>(sm + 2 * t);
+        constexpr int step = LAYOUT == SDCT_K_LAYOUT_B ? 4 : C_PITCH / 2;
+#pragma unroll
+        for (int i = 0; i < 64; i++) {
+            const uint32_t h = s[i * step];
+            b[i] = make_float2(byte_to_float(h, 0), byte_to_float(h, 1));
+        }
     }
-#pragma unroll
-    for (int c = 0; c < 8; c++) idct8<8, false>(b + c);
-#pragma unroll
-    for (int r = 0; r < 8; r++) idct8<1, true>(b + 8 * r);
-#pragma unroll
-    for (int j = 0; j < 16; j++)
-        w[j] = pack4(unit_to_u8(b[4 * j]), unit_to_u8(b[4 * j + 1]), unit_to_u8(b[4 * j + 2]), unit_to_u8(b[4 * j + 3]));
 }
 
-template <int COMPS, bool VEC>
-SDCT_DEV void store_block_bytes(uint8_t *px, uint64_t pitch, uint32_t comp, const uint32_t w[16])
+// levels (as floats, natural index) -> pixel bit patterns, b[y*8+x]
+template <int LAYOUT>
+SDCT_DEV void inverse_pair(const float2 *tab, const float2 *off, F2 b[64])
+{
+#pragma unroll
+    for (int i = 0; i < 64; i++) b[i] = fma2(b[i], tab[tab_index<LAYOUT>(i)], off[tab_index<LAYOUT>(i)]);
+#pragma unroll
+    for (int c = 0; c < 8; c++) idct8<8>(b + c);
+#pragma unroll
+    for (int r = 0; r < 8; r++) idct8<1>(b + 8 * r);
+#pragma unroll
+    for (int i = 0; i < 64; i++) b[i] = pixel_bits(b[i]);
+}
+
+template <int COMPS, int VEC>
+SDCT_DEV void store_block(uint8_t *px, uint64_t pitch, uint32_t comp, const uint32_t w[16])
 {
 #pragma unroll
     for (int r = 0; r < 8; r++) {
@@ -288,95 +370,193 @@ SDCT_DEV void store_block_bytes(uint8_t *px, uint64_t pitch, uint32_t comp, cons
     }
 }
 
-template <int LAYOUT, int COMPS, bool VEC>
-__global__ void __launch_bounds__(SDCT_TB) inverse_kernel(const __grid_constant__ KParams p)
+// pixel bit patterns of the pair -> global memory
+template <int COMPS, int VEC>
+SDCT_DEV void store_pair(const BlockPos &b, const uint8_t *in_base, uint8_t *out_base, uint64_t pitch, const F2 v[64])
 {
-    __shared__ __align__(16) uint8_t sm[TB * 64];
-    const BlockPos b = locate(p);
-    uint32_t o[16], w[16];
-    load_coefs<LAYOUT>(sm, p, b, o);
-    inverse_block<LAYOUT>(o, p.tab, w);
-    if (b.valid) store_block_bytes<COMPS, VEC>(const_cast<uint8_t *>(b.px), p.pitch, b.comp, w);
-}
-
-// fused forward -> quantise -> dequantise -> inverse: coefficients stay in registers
-template <int LAYOUT, int MODE, bool X3, int COMPS, bool VEC>
-__global__ void __launch_bounds__(SDCT_TB) roundtrip_kernel(const __grid_constant__ KParams p)
-{
-    const BlockPos b = locate(p);
-    uint32_t w[16], o[16];
-    load_block_bytes<COMPS, VEC>(b.px, p.pitch, b.comp, w);
-    forward_block<LAYOUT, MODE, X3>(w, p.tab, o);
-    inverse_block<LAYOUT>(o, p.tab2, w);
-    if (b.valid) {
-        uint8_t *dst = p.pixels_out + (b.px - p.pixels);
-        store_block_bytes<COMPS, VEC>(dst, p.pitch, b.comp, w);
+    uint32_t wp[16], wq[16];
+#pragma unroll
+    for (int j = 0; j < 16; j++) {
+        wp[j] = pack4_sat(v[4 * j].x, v[4 * j + 1].x, v[4 * j + 2].x, v[4 * j + 3].x);
+        wq[j] = pack4_sat(v[4 * j].y, v[4 * j + 1].y, v[4 * j + 2].y, v[4 * j + 3].y);
+    }
+    uint8_t *dp = out_base + (b.px[0] - in_base), *dq = out_base + (b.px[1] - in_base);
+    if (COMPS == 1 && VEC == 2) {
+        if (b.valid[0]) {  // VEC == 2 implies an even count: P valid <=> Q valid
+#pragma unroll
+            for (int r = 0; r < 8; r++)
+                *reinterpret_cast<uint4 *>(dp + r * pitch) = make_uint4(wp[2 * r], wp[2 * r + 1], wq[2 * r], wq[2 * r + 1]);
+        }
+    } else {
+        if (b.valid[0]) store_block<COMPS, (VEC ? 1 : 0)>(dp, pitch, b.comp, wp);
+        if (b.valid[1]) store_block<COMPS, (VEC ? 1 : 0)>(dq, pitch, b.comp, wq);
     }
 }
 
+template <int LAYOUT, int COMPS, int VEC>
+__global__ void __launch_bounds__(SDCT_TB, 3) inverse_kernel(const __grid_constant__ KParams p)
+{
+    __shared__ __align__(16) uint8_t sm[STAGE_BYTES];
+    const BlockPos b = locate<LAYOUT>(p);
+    fetch_coefs<LAYOUT>(sm, p, b);
+    __syncthreads();
+    F2 v[64];
+    unstage_levels<LAYOUT>(sm, v);
+    inverse_pair<LAYOUT>(p.tab, p.off, v);
+    store_pair<COMPS, VEC>(b, p.pixels, const_cast<uint8_t *>(p.pixels), p.pitch, v);
+}
+
+// fused forward -> quantise -> dequantise -> inverse: coefficients never leave the registers
+template <int LAYOUT, int MODE, bool X3, int COMPS, int VEC>
+__global__ void __launch_bounds__(SDCT_TB, 3) roundtrip_kernel(const __grid_constant__ KParams p)
+{
+    const BlockPos b = locate<LAYOUT>(p);
+    uint32_t wp[16], wq[16];
+    load_pair<COMPS, VEC>(b, p.pitch, wp, wq);
+    F2 v[64];
+    forward_pair<LAYOUT, MODE, X3>(wp, wq, p.tab, v);
+    // bit patterns -> saturated levels -> floats (the level a decoder would read back)
+#pragma unroll
+    for (int i = 0; i < 64; i++) {
+        uint32_t h = pack_pq(v[i]);
+        if (complemented<LAYOUT, MODE>()) h = ~h;
+        v[i] = make_float2(byte_to_float(h, 0), byte_to_float(h, 1));
+    }
+    inverse_pair<LAYOUT>(p.tab2, p.off, v);
+    store_pair<COMPS, VEC>(b, p.pixels, p.pixels_out, p.pitch, v);
+}
+
+#if SDCT_PART == 0
+// ---- self-test: the 8-point kernels on raw floats (bitwise oracle comparison in tests/) ----------
+// data: n vectors of 8 floats, transformed in place.  kind: 0 scalar, 1 paired, 2 paired+X3,
+// 3 fast, 4 idct, 5 = x/255 of element value (div255), +8 = "second pass" variant (scalar first stage)
+__global__ void dct8_selftest_kernel(float *data, uint32_t n, int kind)
+{
+    const uint32_t i = (blockIdx.x * blockDim.x + threadIdx.x) * 2;
+    if (i >= n) return;
+    const uint32_t j = min(i + 1, n - 1);
+    F2 v[8];
+#pragma unroll
+    for (int k = 0; k < 8; k++) v[k] = make_float2(data[i * 8 + k], data[j * 8 + k]);
+    switch (kind) {
+    case 0: dct8_scalar<1, false>(v); break;
+    case 8: dct8_scalar<1, true>(v); break;
+    case 1: dct8_paired<1, false, false>(v); break;
+    case 9: dct8_paired<1, true, false>(v); break;
+    case 2: dct8_paired<1, false, true>(v); break;
+    case 10: dct8_paired<1, true, true>(v); break;
+    case 3: dct8_fast<1>(v); break;
+    case 4: idct8<1>(v); break;
+    case 5:
+#pragma unroll
+        for (int k = 0; k < 8; k++) v[k] = div255(v[k]);
+        break;
+    default: break;
+    }
+#pragma unroll
+    for (int k = 0; k < 8; k++) {
+        data[i * 8 + k] = v[k].x;
+        if (j != i) data[j * 8 + k] = v[k].y;
+    }
+}
+
+#endif  // SDCT_PART == 0
+
 }  // namespace sdct
 
-// ---- launchers ------------------------------------------------------------------------------
+// ---- launchers ------------------------------------------------------------------------------------
 using namespace sdct;
+
+typedef cudaError_t (*part_fn)(int op, int x3, const KParams &p, unsigned grid, cudaStream_t s);
+#define SDCT_DECL(name) cudaError_t name(int op, int x3, const KParams &p, unsigned grid, cudaStream_t s)
+SDCT_DECL(sdct_part_exact_a); SDCT_DECL(sdct_part_exact_b); SDCT_DECL(sdct_part_exact_c);
+SDCT_DECL(sdct_part_fast_a); SDCT_DECL(sdct_part_fast_b); SDCT_DECL(sdct_part_fast_c);
+SDCT_DECL(sdct_part_inverse);
 
 template <int LAYOUT, int MODE, bool X3>
 static cudaError_t launch_fwd2(int op, const KParams &p, unsigned grid, cudaStream_t s)
 {
-    const bool vec = p.pixels_aligned8 != 0;
 #define SDCT_GO(K, C, V)                                                     \
     do {                                                                     \
         K<LAYOUT, MODE, X3, C, V><<<grid, SDCT_TB, 0, s>>>(p);               \
         return cudaGetLastError();                                           \
     } while (0)
-    if (op == SDCT_K_OP_FORWARD) {
-        if (p.comps == 1) { if (vec) SDCT_GO(forward_kernel, 1, true); else SDCT_GO(forward_kernel, 1, false); }
-        else              { if (vec) SDCT_GO(forward_kernel, 3, true); else SDCT_GO(forward_kernel, 3, false); }
-    } else {
-        if (p.comps == 1) { if (vec) SDCT_GO(roundtrip_kernel, 1, true); else SDCT_GO(roundtrip_kernel, 1, false); }
-        else              { if (vec) SDCT_GO(roundtrip_kernel, 3, true); else SDCT_GO(roundtrip_kernel, 3, false); }
-    }
+#define SDCT_PICK(K)                                                                                   \
+    do {                                                                                               \
+        if (p.comps == 1) {                                                                            \
+            if (p.pixel_vec == 2 && LAYOUT != SDCT_K_LAYOUT_A) SDCT_GO(K, 1, 2);                      \
+            else if (p.pixel_vec >= 1) SDCT_GO(K, 1, 1);                                               \
+            else SDCT_GO(K, 1, 0);                                                                     \
+        } else {                                                                                       \
+            if (p.pixel_vec >= 1) SDCT_GO(K, 3, 1); else SDCT_GO(K, 3, 0);                             \
+        }                                                                                              \
+    } while (0)
+    if (op == SDCT_K_OP_FORWARD) SDCT_PICK(forward_kernel);
+    else SDCT_PICK(roundtrip_kernel);
+#undef SDCT_PICK
 #undef SDCT_GO
 }
 
 template <int LAYOUT>
 static cudaError_t launch_inv2(const KParams &p, unsigned grid, cudaStream_t s)
 {
-    const bool vec = p.pixels_aligned8 != 0;
     if (p.comps == 1) {
-        if (vec) inverse_kernel<LAYOUT, 1, true><<<grid, SDCT_TB, 0, s>>>(p);
-        else inverse_kernel<LAYOUT, 1, false><<<grid, SDCT_TB, 0, s>>>(p);
+        if (p.pixel_vec == 2 && LAYOUT != SDCT_K_LAYOUT_A) inverse_kernel<LAYOUT, 1, 2><<<grid, SDCT_TB, 0, s>>>(p);
+        else if (p.pixel_vec >= 1) inverse_kernel<LAYOUT, 1, 1><<<grid, SDCT_TB, 0, s>>>(p);
+        else inverse_kernel<LAYOUT, 1, 0><<<grid, SDCT_TB, 0, s>>>(p);
     } else {
-        inverse_kernel<LAYOUT, 3, false><<<grid, SDCT_TB, 0, s>>>(p);
+        inverse_kernel<LAYOUT, 3, 0><<<grid, SDCT_TB, 0, s>>>(p);
     }
     return cudaGetLastError();
 }
 
+#if SDCT_PART == 1
+SDCT_DECL(sdct_part_exact_a) { (void)x3; return launch_fwd2<SDCT_K_LAYOUT_A, SDCT_K_EXACT, false>(op, p, grid, s); }
+#elif SDCT_PART == 2
+SDCT_DECL(sdct_part_exact_b)
+{
+    return x3 ? launch_fwd2<SDCT_K_LAYOUT_B, SDCT_K_EXACT, true>(op, p, grid, s)
+              : launch_fwd2<SDCT_K_LAYOUT_B, SDCT_K_EXACT, false>(op, p, grid, s);
+}
+#elif SDCT_PART == 3
+SDCT_DECL(sdct_part_exact_c) { (void)x3; return launch_fwd2<SDCT_K_LAYOUT_C, SDCT_K_EXACT, false>(op, p, grid, s); }
+#elif SDCT_PART == 4
+SDCT_DECL(sdct_part_fast_a) { (void)x3; return launch_fwd2<SDCT_K_LAYOUT_A, SDCT_K_FAST, false>(op, p, grid, s); }
+#elif SDCT_PART == 5
+SDCT_DECL(sdct_part_fast_b) { (void)x3; return launch_fwd2<SDCT_K_LAYOUT_B, SDCT_K_FAST, false>(op, p, grid, s); }
+#elif SDCT_PART == 6
+SDCT_DECL(sdct_part_fast_c) { (void)x3; return launch_fwd2<SDCT_K_LAYOUT_C, SDCT_K_FAST, false>(op, p, grid, s); }
+#elif SDCT_PART == 7
+SDCT_DECL(sdct_part_inverse)
+{
+    (void)op; (void)x3;
+    switch (p.layout) {
+    case SDCT_K_LAYOUT_A: return launch_inv2<SDCT_K_LAYOUT_A>(p, grid, s);
+    case SDCT_K_LAYOUT_B: return launch_inv2<SDCT_K_LAYOUT_B>(p, grid, s);
+    default: return launch_inv2<SDCT_K_LAYOUT_C>(p, grid, s);
+    }
+}
+#elif SDCT_PART == 0
 extern "C" cudaError_t sdct_k_launch(int op, int layout, int mode, int x3, const KParams *pp, cudaStream_t s)
 {
-    const KParams &p = *pp;
+    KParams p = *pp;
+    p.layout = (uint32_t)layout;
     const unsigned long long grid64 = (unsigned long long)p.chunks * p.comps * p.frames;
     if (grid64 == 0) return cudaSuccess;
     if (grid64 > 0x7fffffffull) return cudaErrorInvalidConfiguration;
     const unsigned grid = (unsigned)grid64;
-    if (op == SDCT_K_OP_INVERSE) {
-        switch (layout) {
-        case SDCT_K_LAYOUT_A: return launch_inv2<SDCT_K_LAYOUT_A>(p, grid, s);
-        case SDCT_K_LAYOUT_B: return launch_inv2<SDCT_K_LAYOUT_B>(p, grid, s);
-        default: return launch_inv2<SDCT_K_LAYOUT_C>(p, grid, s);
-        }
-    }
-    if (mode == SDCT_K_FAST) {
-        switch (layout) {
-        case SDCT_K_LAYOUT_A: return launch_fwd2<SDCT_K_LAYOUT_A, SDCT_K_FAST, false>(op, p, grid, s);
-        case SDCT_K_LAYOUT_B: return launch_fwd2<SDCT_K_LAYOUT_B, SDCT_K_FAST, false>(op, p, grid, s);
-        default: return launch_fwd2<SDCT_K_LAYOUT_C, SDCT_K_FAST, false>(op, p, grid, s);
-        }
-    }
-    switch (layout) {
-    case SDCT_K_LAYOUT_A: return launch_fwd2<SDCT_K_LAYOUT_A, SDCT_K_EXACT, false>(op, p, grid, s);
-    case SDCT_K_LAYOUT_B:
-        return x3 ? launch_fwd2<SDCT_K_LAYOUT_B, SDCT_K_EXACT, true>(op, p, grid, s)
-                  : launch_fwd2<SDCT_K_LAYOUT_B, SDCT_K_EXACT, false>(op, p, grid, s);
-    default: return launch_fwd2<SDCT_K_LAYOUT_C, SDCT_K_EXACT, false>(op, p, grid, s);
-    }
+    if (op == SDCT_K_OP_INVERSE) return sdct_part_inverse(op, x3, p, grid, s);
+    static const part_fn exact[3] = {sdct_part_exact_a, sdct_part_exact_b, sdct_part_exact_c};
+    static const part_fn fast[3] = {sdct_part_fast_a, sdct_part_fast_b, sdct_part_fast_c};
+    if (layout < 0 || layout > 2) return cudaErrorInvalidValue;
+    return (mode == SDCT_K_FAST ? fast : exact)[layout](op, x3, p, grid, s);
 }
+
+extern "C" cudaError_t sdct_k_selftest(float *d_data, uint32_t n, int kind, cudaStream_t s)
+{
+    if (n == 0) return cudaSuccess;
+    const unsigned threads = 128, pairs = (n + 1) / 2;
+    dct8_selftest_kernel<<<(pairs + threads - 1) / threads, threads, 0, s>>>(d_data, n, kind);
+    return cudaGetLastError();
+}
+#endif

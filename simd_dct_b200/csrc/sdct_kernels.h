@@ -4,7 +4,8 @@
 #include <cstdint>
 #include <cuda_runtime.h>
 
-#define SDCT_TB 128  // threads per CTA = 8x8 blocks per CTA
+#define SDCT_TB 128          // threads per CTA
+#define SDCT_CTA_BLOCKS 256  // 8x8 blocks per CTA (two per thread)
 
 #define SDCT_K_LAYOUT_A 0
 #define SDCT_K_LAYOUT_B 1
@@ -26,10 +27,16 @@ struct KParams {
     uint32_t row0, rows;      // block-row window: row = band*eyes + eye
     uint32_t comps;
     uint32_t frames;
+    uint32_t layout;          // SDCT_K_LAYOUT_* (filled in by sdct_k_launch)
     uint32_t chunks;          // CTAs per (frame, component)
-    uint32_t pixels_aligned8, coef_aligned16, coef_aligned4;
-    float tab[64];            // forward: quantiser scale; inverse: dequantiser scale
-    float tab2[64];           // roundtrip: dequantiser scale
+    uint32_t pixel_vec;       // 0 = byte access, 1 = 8-byte rows, 2 = 16-byte rows for an adjacent block pair
+    uint32_t coef_aligned16, coef_aligned4;
+    // scale tables, each value duplicated for the two packed lanes (P, Q)
+    float2 tab[64];           // forward: quantiser scale; inverse: dequantiser scale
+    float2 tab2[64];          // roundtrip: dequantiser scale
+    float2 off[64];           // inverse / roundtrip: -127 * dequantiser scale
 };
 
 extern "C" cudaError_t sdct_k_launch(int op, int layout, int mode, int x3, const KParams *p, cudaStream_t s);
+// the 8-point kernels on n raw 8-float vectors (device memory, in place); see dct8_selftest_kernel
+extern "C" cudaError_t sdct_k_selftest(float *d_data, uint32_t n, int kind, cudaStream_t s);

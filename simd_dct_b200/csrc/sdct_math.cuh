@@ -1,12 +1,23 @@
 // sdct_math.cuh - per-thread fp32 arithmetic of the 8x8 block-DCT hot path (sm_100a).
 //
-// Three arithmetic definitions live here:
-//   EXACT / scalar : the reference's scalar flow graph, src/simd_dct.cpp:138-172, every
-//                    operation an individually rounded IEEE binary32 op (no FMA contraction)
+// A thread owns TWO 8x8 blocks, P and Q, held as 64 packed pairs (F2 = {P value, Q value}), and
+// every operation of the two blocks is issued once as a Blackwell packed-fp32 instruction
+// (add/sub/mul/fma.f32x2 -> FADD2 / FMUL2 / FFMA2).  The packed forms do not raise the fp32 rate
+// (the FMA pipe still retires 128 lanes/clk/SM, profiles/r01_probe2_issue_rates.txt) but they
+// halve the issue slots the arithmetic needs, which is what bounds this kernel: the conversion
+// (XU pipe), packing (ALU pipe) and staging (LSU) instructions then issue in the shadow of the
+// FMA pipe.  The "transposes" between the row and the column pass are index renamings.
+//
+// Arithmetic definitions:
+//   EXACT / scalar : the reference's scalar flow graph, src/simd_dct.cpp:138-172
 //   EXACT / paired : the reference's AVX2 lane arithmetic, src/simd_dct.cpp:2160-2183
-//   FAST / inverse : this repo's FMA-contracted forms, defined in oracle/sdct_oracle.c
-// A thread owns a whole 8x8 block in registers (float b[64], statically indexed), so the
-// "transposes" between the row and the column pass of the reference are index renamings.
+//     every operation an individually rounded IEEE binary32 op, in the reference's order.
+//   FAST / inverse : this repo's FMA-contracted forms, defined in oracle/sdct_oracle.c.
+//
+// ptxas 12.9 contracts `mul.rn.f32x2` + `add.rn.f32x2` into FFMA2 even though both carry .rn and
+// --fmad=false is given (it does not do that to the scalar forms).  In the EXACT graphs every add
+// that consumes a product is therefore issued as two scalar FADDs on the halves (sadd/ssub below);
+// tests/test_gpu_parity.py::test_dct8_bitwise checks the result bit for bit against the oracle.
 #pragma once
 #include <cstdint>
 #include <cuda_runtime.h>
@@ -24,146 +35,182 @@ namespace sdct {
 
 #define SDCT_DEV __device__ __forceinline__
 
-SDCT_DEV float fadd(float a, float b) { return __fadd_rn(a, b); }
-SDCT_DEV float fsub(float a, float b) { return __fsub_rn(a, b); }
-SDCT_DEV float fmul(float a, float b) { return __fmul_rn(a, b); }
+typedef float2 F2;
 
-// ---- 8-point forward, reference scalar order (:148-171); v[0], v[S], ... v[7S] ----------
-template <int S>
-SDCT_DEV void dct8_scalar(float *v)
-{
-    const float s07 = fadd(v[0], v[7 * S]), s16 = fadd(v[S], v[6 * S]);
-    const float s25 = fadd(v[2 * S], v[5 * S]), s34 = fadd(v[3 * S], v[4 * S]);
-    const float d07 = fsub(v[0], v[7 * S]), d61 = fsub(v[6 * S], v[S]);
-    const float d25 = fsub(v[2 * S], v[5 * S]), d43 = fsub(v[4 * S], v[3 * S]);
-    const float pp = fadd(s07, s34), pm = fsub(s07, s34), qq = fadd(s16, s25), qm = fsub(s16, s25);
-
-    v[0] = fmul(SDCT_KN, fadd(pp, qq));
-    v[2 * S] = fmul(SDCT_KN, fadd(fmul(SDCT_KB, pm), fmul(SDCT_KE, qm)));
-    v[4 * S] = fmul(SDCT_KN, fsub(pp, qq));
-    v[6 * S] = fmul(SDCT_KN, fsub(fmul(SDCT_KE, pm), fmul(SDCT_KB, qm)));
-    v[S] = fmul(SDCT_KN, fsub(fadd(fsub(fmul(SDCT_KA, d07), fmul(SDCT_KC, d61)), fmul(SDCT_KD, d25)), fmul(SDCT_KF, d43)));
-    v[3 * S] = fmul(SDCT_KN, fadd(fsub(fadd(fmul(SDCT_KC, d07), fmul(SDCT_KF, d61)), fmul(SDCT_KA, d25)), fmul(SDCT_KD, d43)));
-    v[5 * S] = fmul(SDCT_KN, fsub(fadd(fadd(fmul(SDCT_KD, d07), fmul(SDCT_KA, d61)), fmul(SDCT_KF, d25)), fmul(SDCT_KC, d43)));
-    v[7 * S] = fmul(SDCT_KN, fadd(fadd(fadd(fmul(SDCT_KF, d07), fmul(SDCT_KD, d61)), fmul(SDCT_KC, d25)), fmul(SDCT_KA, d43)));
-}
-
-// ---- 8-point forward, reference AVX2 lane order (:2160-2183); X3 = true keeps :2181's sign
-template <int S, bool X3>
-SDCT_DEV void dct8_paired(float *v)
-{
-    const float s07 = fadd(v[0], v[7 * S]), s16 = fadd(v[S], v[6 * S]);
-    const float s25 = fadd(v[2 * S], v[5 * S]), s34 = fadd(v[3 * S], v[4 * S]);
-    const float d07 = fsub(v[0], v[7 * S]), d61 = fsub(v[6 * S], v[S]);
-    const float d25 = fsub(v[2 * S], v[5 * S]), d43 = fsub(v[4 * S], v[3 * S]);
-    const float pp = fadd(s07, s34), pm = fsub(s07, s34), qq = fadd(s16, s25), qm = fsub(s16, s25);
-
-    v[0] = fmul(SDCT_KN, fadd(pp, qq));
-    v[4 * S] = fmul(SDCT_KN, fsub(pp, qq));
-    v[2 * S] = fmul(SDCT_KN, fadd(fmul(SDCT_KB, pm), fmul(SDCT_KE, qm)));
-    v[6 * S] = fmul(SDCT_KN, fsub(fmul(SDCT_KE, pm), fmul(SDCT_KB, qm)));
-    v[S] = fmul(SDCT_KN, fadd(fsub(fmul(SDCT_KA, d07), fmul(SDCT_KC, d61)), fsub(fmul(SDCT_KD, d25), fmul(SDCT_KF, d43))));
-    const float x3r = X3 ? fadd(fmul(SDCT_KA, d25), fmul(SDCT_KD, d43)) : fsub(fmul(SDCT_KA, d25), fmul(SDCT_KD, d43));
-    v[3 * S] = fmul(SDCT_KN, fsub(fadd(fmul(SDCT_KC, d07), fmul(SDCT_KF, d61)), x3r));
-    v[5 * S] = fmul(SDCT_KN, fadd(fadd(fmul(SDCT_KD, d07), fmul(SDCT_KA, d61)), fsub(fmul(SDCT_KF, d25), fmul(SDCT_KC, d43))));
-    v[7 * S] = fmul(SDCT_KN, fadd(fadd(fmul(SDCT_KF, d07), fmul(SDCT_KD, d61)), fadd(fmul(SDCT_KC, d25), fmul(SDCT_KA, d43))));
-}
-
-// ---- 8-point forward, FAST (oracle/sdct_oracle.c: sdct_oracle_dct8_fast), unnormalised -----
-template <int S>
-SDCT_DEV void dct8_fast(float *v)
-{
-    const float s07 = fadd(v[0], v[7 * S]), s16 = fadd(v[S], v[6 * S]);
-    const float s25 = fadd(v[2 * S], v[5 * S]), s34 = fadd(v[3 * S], v[4 * S]);
-    const float d07 = fsub(v[0], v[7 * S]), d61 = fsub(v[6 * S], v[S]);
-    const float d25 = fsub(v[2 * S], v[5 * S]), d43 = fsub(v[4 * S], v[3 * S]);
-    const float pp = fadd(s07, s34), pm = fsub(s07, s34), qq = fadd(s16, s25), qm = fsub(s16, s25);
-
-    v[0] = fadd(pp, qq);
-    v[4 * S] = fsub(pp, qq);
-    v[2 * S] = __fmaf_rn(SDCT_KB, pm, fmul(SDCT_KE, qm));
-    v[6 * S] = __fmaf_rn(SDCT_KE, pm, -fmul(SDCT_KB, qm));
-    v[S] = __fmaf_rn(-SDCT_KF, d43, __fmaf_rn(SDCT_KD, d25, __fmaf_rn(-SDCT_KC, d61, fmul(SDCT_KA, d07))));
-    v[3 * S] = __fmaf_rn(SDCT_KD, d43, __fmaf_rn(-SDCT_KA, d25, __fmaf_rn(SDCT_KF, d61, fmul(SDCT_KC, d07))));
-    v[5 * S] = __fmaf_rn(-SDCT_KC, d43, __fmaf_rn(SDCT_KF, d25, __fmaf_rn(SDCT_KA, d61, fmul(SDCT_KD, d07))));
-    v[7 * S] = __fmaf_rn(SDCT_KA, d43, __fmaf_rn(SDCT_KC, d25, __fmaf_rn(SDCT_KD, d61, fmul(SDCT_KF, d07))));
-}
-
-// ---- 8-point inverse (oracle/sdct_oracle.c: sdct_oracle_idct8), unnormalised ----------------
-// SAT = true saturates the eight outputs to [0,1] in the final add (the pixel clamp).
-template <int S, bool SAT>
-SDCT_DEV void idct8(float *v)
-{
-    const float e0 = fadd(v[0], v[4 * S]), e1 = fsub(v[0], v[4 * S]);
-    const float e2 = __fmaf_rn(SDCT_KB, v[2 * S], fmul(SDCT_KE, v[6 * S]));
-    const float e3 = __fmaf_rn(SDCT_KE, v[2 * S], -fmul(SDCT_KB, v[6 * S]));
-    const float a0 = fadd(e0, e2), a3 = fsub(e0, e2), a1 = fadd(e1, e3), a2 = fsub(e1, e3);
-    const float o0 = __fmaf_rn(SDCT_KF, v[7 * S], __fmaf_rn(SDCT_KD, v[5 * S], __fmaf_rn(SDCT_KC, v[3 * S], fmul(SDCT_KA, v[S]))));
-    const float o1 = __fmaf_rn(SDCT_KD, v[7 * S], __fmaf_rn(SDCT_KA, v[5 * S], __fmaf_rn(SDCT_KF, v[3 * S], -fmul(SDCT_KC, v[S]))));
-    const float o2 = __fmaf_rn(SDCT_KC, v[7 * S], __fmaf_rn(SDCT_KF, v[5 * S], __fmaf_rn(-SDCT_KA, v[3 * S], fmul(SDCT_KD, v[S]))));
-    const float o3 = __fmaf_rn(SDCT_KA, v[7 * S], __fmaf_rn(-SDCT_KC, v[5 * S], __fmaf_rn(SDCT_KD, v[3 * S], -fmul(SDCT_KF, v[S]))));
-    if (SAT) {
-        v[0] = __saturatef(fadd(a0, o0)); v[7 * S] = __saturatef(fsub(a0, o0));
-        v[S] = __saturatef(fsub(a1, o1)); v[6 * S] = __saturatef(fadd(a1, o1));
-        v[2 * S] = __saturatef(fadd(a2, o2)); v[5 * S] = __saturatef(fsub(a2, o2));
-        v[3 * S] = __saturatef(fsub(a3, o3)); v[4 * S] = __saturatef(fadd(a3, o3));
-    } else {
-        v[0] = fadd(a0, o0); v[7 * S] = fsub(a0, o0);
-        v[S] = fsub(a1, o1); v[6 * S] = fadd(a1, o1);
-        v[2 * S] = fadd(a2, o2); v[5 * S] = fsub(a2, o2);
-        v[3 * S] = fsub(a3, o3); v[4 * S] = fadd(a3, o3);
+#define SDCT_OP2(name, ins)                                                                          \
+    SDCT_DEV F2 name(F2 a, F2 b)                                                                     \
+    {                                                                                                \
+        F2 d;                                                                                        \
+        asm("{.reg .b64 ra, rb, rd;\n\tmov.b64 ra, {%2,%3};\n\tmov.b64 rb, {%4,%5};\n\t" ins         \
+            " rd, ra, rb;\n\tmov.b64 {%0,%1}, rd;}"                                                  \
+            : "=f"(d.x), "=f"(d.y)                                                                   \
+            : "f"(a.x), "f"(a.y), "f"(b.x), "f"(b.y));                                               \
+        return d;                                                                                    \
     }
+SDCT_OP2(add2, "add.rn.f32x2")
+SDCT_OP2(sub2, "sub.rn.f32x2")
+SDCT_OP2(mul2, "mul.rn.f32x2")
+SDCT_OP2(mul2_rd, "mul.rm.f32x2")
+#undef SDCT_OP2
+
+SDCT_DEV F2 fma2(F2 a, F2 b, F2 c)
+{
+    F2 d;
+    asm("{.reg .b64 ra, rb, rc, rd;\n\tmov.b64 ra, {%2,%3};\n\tmov.b64 rb, {%4,%5};\n\tmov.b64 rc, {%6,%7};\n\t"
+        "fma.rn.f32x2 rd, ra, rb, rc;\n\tmov.b64 {%0,%1}, rd;}"
+        : "=f"(d.x), "=f"(d.y)
+        : "f"(a.x), "f"(a.y), "f"(b.x), "f"(b.y), "f"(c.x), "f"(c.y));
+    return d;
 }
 
-// ---- u8 -> f32 --------------------------------------------------------------------------
-// byte k of w as an exact float: PRMT the byte into the mantissa of 2^23, subtract 2^23.
-SDCT_DEV float byte_to_float(uint32_t w, int k)
+SDCT_DEV F2 splat(float k) { return make_float2(k, k); }
+SDCT_DEV F2 mulk(F2 a, float k) { return mul2(a, splat(k)); }
+SDCT_DEV F2 fmak(float k, F2 a, F2 c) { return fma2(a, splat(k), c); }   // k*a + c
+// two scalar instructions: the only safe consumer of a packed product in the EXACT graphs
+SDCT_DEV F2 sadd(F2 a, F2 b) { return make_float2(__fadd_rn(a.x, b.x), __fadd_rn(a.y, b.y)); }
+SDCT_DEV F2 ssub(F2 a, F2 b) { return make_float2(__fsub_rn(a.x, b.x), __fsub_rn(a.y, b.y)); }
+
+// first butterfly stage: packed when the inputs are not products (converted pixels), scalar when
+// they are (the second pass reads the first pass's K_N * (...) results)
+template <bool PROD_IN> SDCT_DEV F2 add_in(F2 a, F2 b) { return PROD_IN ? sadd(a, b) : add2(a, b); }
+template <bool PROD_IN> SDCT_DEV F2 sub_in(F2 a, F2 b) { return PROD_IN ? ssub(a, b) : sub2(a, b); }
+
+// ---- 8-point forward, reference scalar order (:148-171); v[0], v[S], ... v[7S] ----------------
+template <int S, bool PROD_IN>
+SDCT_DEV void dct8_scalar(F2 *v)
 {
-    return __uint_as_float(__byte_perm(w, 0x4B000000u, 0x7650 + k)) - 8388608.0f;
+    const F2 s07 = add_in<PROD_IN>(v[0], v[7 * S]), s16 = add_in<PROD_IN>(v[S], v[6 * S]);
+    const F2 s25 = add_in<PROD_IN>(v[2 * S], v[5 * S]), s34 = add_in<PROD_IN>(v[3 * S], v[4 * S]);
+    const F2 d07 = sub_in<PROD_IN>(v[0], v[7 * S]), d61 = sub_in<PROD_IN>(v[6 * S], v[S]);
+    const F2 d25 = sub_in<PROD_IN>(v[2 * S], v[5 * S]), d43 = sub_in<PROD_IN>(v[4 * S], v[3 * S]);
+    const F2 pp = add2(s07, s34), pm = sub2(s07, s34), qq = add2(s16, s25), qm = sub2(s16, s25);
+
+    v[0] = mulk(add2(pp, qq), SDCT_KN);
+    v[2 * S] = mulk(sadd(mulk(pm, SDCT_KB), mulk(qm, SDCT_KE)), SDCT_KN);
+    v[4 * S] = mulk(sub2(pp, qq), SDCT_KN);
+    v[6 * S] = mulk(ssub(mulk(pm, SDCT_KE), mulk(qm, SDCT_KB)), SDCT_KN);
+    // odd outputs, left to right: ((t0 op t1) op t2) op t3 - every add has a product operand
+    v[S] = mulk(ssub(sadd(ssub(mulk(d07, SDCT_KA), mulk(d61, SDCT_KC)), mulk(d25, SDCT_KD)), mulk(d43, SDCT_KF)), SDCT_KN);
+    v[3 * S] = mulk(sadd(ssub(sadd(mulk(d07, SDCT_KC), mulk(d61, SDCT_KF)), mulk(d25, SDCT_KA)), mulk(d43, SDCT_KD)), SDCT_KN);
+    v[5 * S] = mulk(ssub(sadd(sadd(mulk(d07, SDCT_KD), mulk(d61, SDCT_KA)), mulk(d25, SDCT_KF)), mulk(d43, SDCT_KC)), SDCT_KN);
+    v[7 * S] = mulk(sadd(sadd(sadd(mulk(d07, SDCT_KF), mulk(d61, SDCT_KD)), mulk(d25, SDCT_KC)), mulk(d43, SDCT_KA)), SDCT_KN);
 }
+
+// ---- 8-point forward, reference AVX2 lane order (:2160-2183); X3 = true keeps :2181's sign -----
+template <int S, bool PROD_IN, bool X3>
+SDCT_DEV void dct8_paired(F2 *v)
+{
+    const F2 s07 = add_in<PROD_IN>(v[0], v[7 * S]), s16 = add_in<PROD_IN>(v[S], v[6 * S]);
+    const F2 s25 = add_in<PROD_IN>(v[2 * S], v[5 * S]), s34 = add_in<PROD_IN>(v[3 * S], v[4 * S]);
+    const F2 d07 = sub_in<PROD_IN>(v[0], v[7 * S]), d61 = sub_in<PROD_IN>(v[6 * S], v[S]);
+    const F2 d25 = sub_in<PROD_IN>(v[2 * S], v[5 * S]), d43 = sub_in<PROD_IN>(v[4 * S], v[3 * S]);
+    const F2 pp = add2(s07, s34), pm = sub2(s07, s34), qq = add2(s16, s25), qm = sub2(s16, s25);
+
+    v[0] = mulk(add2(pp, qq), SDCT_KN);
+    v[4 * S] = mulk(sub2(pp, qq), SDCT_KN);
+    v[2 * S] = mulk(sadd(mulk(pm, SDCT_KB), mulk(qm, SDCT_KE)), SDCT_KN);
+    v[6 * S] = mulk(ssub(mulk(pm, SDCT_KE), mulk(qm, SDCT_KB)), SDCT_KN);
+    // odd outputs, pairwise: (t0 op t1) op (t2 op t3); the outer add sees two sums -> packed
+    v[S] = mulk(add2(ssub(mulk(d07, SDCT_KA), mulk(d61, SDCT_KC)), ssub(mulk(d25, SDCT_KD), mulk(d43, SDCT_KF))), SDCT_KN);
+    const F2 x3r = X3 ? sadd(mulk(d25, SDCT_KA), mulk(d43, SDCT_KD)) : ssub(mulk(d25, SDCT_KA), mulk(d43, SDCT_KD));
+    v[3 * S] = mulk(sub2(sadd(mulk(d07, SDCT_KC), mulk(d61, SDCT_KF)), x3r), SDCT_KN);
+    v[5 * S] = mulk(add2(sadd(mulk(d07, SDCT_KD), mulk(d61, SDCT_KA)), ssub(mulk(d25, SDCT_KF), mulk(d43, SDCT_KC))), SDCT_KN);
+    v[7 * S] = mulk(add2(sadd(mulk(d07, SDCT_KF), mulk(d61, SDCT_KD)), sadd(mulk(d25, SDCT_KC), mulk(d43, SDCT_KA))), SDCT_KN);
+}
+
+// ---- 8-point forward, FAST (oracle/sdct_oracle.c: sdct_oracle_dct8_fast), unnormalised ---------
+// explicit FMAs; no multiply feeds a plain add, so there is nothing left for ptxas to contract
+template <int S>
+SDCT_DEV void dct8_fast(F2 *v)
+{
+    const F2 s07 = add2(v[0], v[7 * S]), s16 = add2(v[S], v[6 * S]);
+    const F2 s25 = add2(v[2 * S], v[5 * S]), s34 = add2(v[3 * S], v[4 * S]);
+    const F2 d07 = sub2(v[0], v[7 * S]), d61 = sub2(v[6 * S], v[S]);
+    const F2 d25 = sub2(v[2 * S], v[5 * S]), d43 = sub2(v[4 * S], v[3 * S]);
+    const F2 pp = add2(s07, s34), pm = sub2(s07, s34), qq = add2(s16, s25), qm = sub2(s16, s25);
+
+    v[0] = add2(pp, qq);
+    v[4 * S] = sub2(pp, qq);
+    v[2 * S] = fmak(SDCT_KB, pm, mulk(qm, SDCT_KE));
+    v[6 * S] = fmak(SDCT_KE, pm, mulk(qm, -SDCT_KB));
+    v[S] = fmak(-SDCT_KF, d43, fmak(SDCT_KD, d25, fmak(-SDCT_KC, d61, mulk(d07, SDCT_KA))));
+    v[3 * S] = fmak(SDCT_KD, d43, fmak(-SDCT_KA, d25, fmak(SDCT_KF, d61, mulk(d07, SDCT_KC))));
+    v[5 * S] = fmak(-SDCT_KC, d43, fmak(SDCT_KF, d25, fmak(SDCT_KA, d61, mulk(d07, SDCT_KD))));
+    v[7 * S] = fmak(SDCT_KA, d43, fmak(SDCT_KC, d25, fmak(SDCT_KD, d61, mulk(d07, SDCT_KF))));
+}
+
+// ---- 8-point inverse (oracle/sdct_oracle.c: sdct_oracle_idct8), unnormalised -------------------
+template <int S>
+SDCT_DEV void idct8(F2 *v)
+{
+    const F2 e0 = add2(v[0], v[4 * S]), e1 = sub2(v[0], v[4 * S]);
+    const F2 e2 = fmak(SDCT_KB, v[2 * S], mulk(v[6 * S], SDCT_KE));
+    const F2 e3 = fmak(SDCT_KE, v[2 * S], mulk(v[6 * S], -SDCT_KB));
+    const F2 a0 = add2(e0, e2), a3 = sub2(e0, e2), a1 = add2(e1, e3), a2 = sub2(e1, e3);
+    const F2 o0 = fmak(SDCT_KF, v[7 * S], fmak(SDCT_KD, v[5 * S], fmak(SDCT_KC, v[3 * S], mulk(v[S], SDCT_KA))));
+    const F2 o1 = fmak(SDCT_KD, v[7 * S], fmak(SDCT_KA, v[5 * S], fmak(SDCT_KF, v[3 * S], mulk(v[S], -SDCT_KC))));
+    const F2 o2 = fmak(SDCT_KC, v[7 * S], fmak(SDCT_KF, v[5 * S], fmak(-SDCT_KA, v[3 * S], mulk(v[S], SDCT_KD))));
+    const F2 o3 = fmak(SDCT_KA, v[7 * S], fmak(-SDCT_KC, v[5 * S], fmak(SDCT_KD, v[3 * S], mulk(v[S], -SDCT_KF))));
+    v[0] = add2(a0, o0); v[7 * S] = sub2(a0, o0);
+    v[S] = sub2(a1, o1); v[6 * S] = add2(a1, o1);
+    v[2 * S] = add2(a2, o2); v[5 * S] = sub2(a2, o2);
+    v[3 * S] = sub2(a3, o3); v[4 * S] = add2(a3, o3);
+}
+
+// ---- u8 -> f32 -----------------------------------------------------------------------------------
+// I2F.U8 with a byte selector: one XU-pipe instruction per sample, none on the FMA or ALU pipe
+SDCT_DEV float byte_to_float(uint32_t w, int k) { return (float)((w >> (8 * k)) & 0xffu); }
 
 // x / 255.f correctly rounded (the reference's `u8 / 255.f`, :217 / :340) without a divide:
-// q0 = x*r, residual by FMA, one correction.  Verified for all 256 inputs against IEEE
-// division in tests/test_math_identities.py (CPU) and tests/test_gpu_parity.py (GPU).
-SDCT_DEV float div255(float x)
+// fma(x, r, x * rl) with r = fl(1/255), rl = fl(1/255 - r).  Equal to IEEE division for all 256
+// inputs (tests/test_math_identities.py on the CPU, tests/test_gpu_parity.py on the GPU).
+#define SDCT_R255_HI 0.003921568859368562698364257812500f
+#define SDCT_R255_LO (-2.319175823606300543e-10f)
+SDCT_DEV F2 div255(F2 x) { return fma2(x, splat(SDCT_R255_HI), mulk(x, SDCT_R255_LO)); }
+
+// ---- quantisers ------------------------------------------------------------------------------------
+// All of them return the quantised level as a *bit pattern*: multiplying by 2^-149 (the smallest
+// denormal) makes the FMA pipe's own rounding the round-to-integer step, and the result's bits
+// are the integer itself (sign-magnitude), ready for the saturating pack.  COMPLEMENTED levels
+// (255 - q) are produced where the reference's "+127 after rounding" would otherwise cost an
+// integer add per sample: sat_u8(128 - rne(v)) == 255 - clamp(rne(v) + 127, 0, 255).
+#define SDCT_DENORM_MIN __int_as_float(0x00000001)        /*  2^-149 */
+#define SDCT_NEG_DENORM_MIN __int_as_float(0x80000001u)   /* -2^-149 */
+#define SDCT_128_DENORM __int_as_float(0x00000080)        /*  128 * 2^-149 */
+
+// reference AVX2 path (:2224): max(min(127 + cvtps_epi32(c*q), 255), 0), cvtps = nearest even.
+// bits = 128 - rne(fl(c*q)) (complemented level before saturation).  Exact for |c*q| < 2^23;
+// sdct_api.cpp rejects tables that could exceed that.
+SDCT_DEV F2 quant_rne_c(F2 c, F2 q) { return fma2(mul2(c, q), splat(SDCT_NEG_DENORM_MIN), splat(SDCT_128_DENORM)); }
+
+// reference scalar path (:245 / :362): (u8)roundf(clamp(c*rq + 127/255, 0, 1) * 255).
+// roundf (half away from zero) of y in [0,255] = floor(y + 0.5) with the sum rounded DOWN, which
+// cannot cross an integer.  bits = the level itself (not complemented).
+SDCT_DEV F2 quant_scalar(F2 c, F2 rq)
 {
-    const float r = 1.0f / 255.0f;
-    const float q0 = fmul(x, r);
-    const float e = __fmaf_rn(-q0, 255.0f, x);
-    return __fmaf_rn(e, r, q0);
+    const F2 p = mul2(c, rq);
+    const F2 s = make_float2(__saturatef(__fadd_rn(p.x, 127.0f / 255.0f)), __saturatef(__fadd_rn(p.y, 127.0f / 255.0f)));
+    const F2 y = mulk(s, 255.0f);
+    const F2 u = make_float2(__fadd_rd(y.x, 0.5f), __fadd_rd(y.y, 0.5f));
+    return mul2_rd(u, splat(SDCT_DENORM_MIN));
 }
 
-// ---- quantisers -> integer in [0,255] -----------------------------------------------------
-// reference scalar path (:245 / :362): (u8)roundf(clamp(c*rq + 127/255, 0, 1) * 255)
-SDCT_DEV uint32_t quant_scalar(float c, float rq)
+// inverse: pixel level = clamp(rne(x), 0, 255): bits = rne(x) for x >= 0, sign bit set otherwise
+SDCT_DEV F2 pixel_bits(F2 x) { return mulk(x, SDCT_DENORM_MIN); }
+
+// ---- saturating pack (ALU pipe): d = (c & 0xffff) << 16 | sat_u8(a) << 8 | sat_u8(b) ---------------
+SDCT_DEV uint32_t pack_sat(uint32_t a, uint32_t b, uint32_t c)
 {
-    const float y = fmul(__saturatef(fadd(fmul(c, rq), 127.0f / 255.0f)), 255.0f);
-    // roundf = half away from zero.  t = rne(y) via the 2^23 trick (0 <= y <= 255); the only
-    // case where rne differs from half-away is an exact tie that rne resolved downwards.
-    const float t = fadd(y, 8388608.0f);
-    const float rn = fsub(t, 8388608.0f);
-    uint32_t n = __float_as_uint(t) & 0x1ffu;
-    if (fsub(y, rn) == 0.5f) n += 1;
-    return n;
+    uint32_t d;
+    asm("cvt.pack.sat.u8.s32.b32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+    return d;
 }
-
-// reference AVX2 path (:2224): max(min(127 + cvtps_epi32(c*q), 255), 0), cvtps = nearest even
-SDCT_DEV uint32_t quant_avx(float c, float q)
+// low 16 bits = [sat(lo), sat(hi)] = bytes (P, Q)
+SDCT_DEV uint32_t pack_pq(F2 bits) { return pack_sat(__float_as_uint(bits.y), __float_as_uint(bits.x), 0u); }
+// bytes [b0, b1, b2, b3] in memory order
+SDCT_DEV uint32_t pack4_sat(float b0, float b1, float b2, float b3)
 {
-    // bits(v + 1.5*2^23) - bits(1.5*2^23) == rne(v) for |v| < 2^22 and stays monotone in v
-    // beyond that, so the integer clamp below is exact for every finite v < 2^31.
-    const float t = fadd(fmul(c, q), 12582912.0f);
-    const int r = (int)__float_as_uint(t) - (0x4B400000 - 127);
-    return (uint32_t)min(max(r, 0), 255);
-}
-
-// FAST forward quantiser and inverse pixel rounding: rne(255 * sat(.)) through 1.5*2^23
-SDCT_DEV uint32_t unit_to_u8(float y01) { return __float_as_uint(__fmaf_rn(y01, 255.0f, 12582912.0f)) & 0xffu; }
-SDCT_DEV uint32_t quant_fast(float c, float qs) { return unit_to_u8(__saturatef(__fmaf_rn(c, qs, 127.0f / 255.0f))); }
-
-SDCT_DEV uint32_t pack4(uint32_t b0, uint32_t b1, uint32_t b2, uint32_t b3)
-{
-    return b0 | (b1 << 8) | (b2 << 16) | (b3 << 24);
+    return pack_sat(__float_as_uint(b1), __float_as_uint(b0), pack_sat(__float_as_uint(b3), __float_as_uint(b2), 0u));
 }
 
 }  // namespace sdct

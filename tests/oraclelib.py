@@ -111,6 +111,18 @@ class Oracle:
             getattr(self.lib, "sdct_oracle_" + kind)(_pf(v))
         return v
 
+    def dct8_many(self, kind, vs, quirk=0):
+        vs = np.ascontiguousarray(vs, dtype=np.float32).copy()
+        fn = self.lib.sdct_oracle_dct8_paired if kind == "paired" else getattr(self.lib, "sdct_oracle_" + kind)
+        base = vs.ctypes.data
+        for k in range(vs.shape[0]):
+            ptr = C.cast(C.c_void_p(base + 32 * k), _f32p)
+            if kind == "paired":
+                fn(ptr, quirk)
+            else:
+                fn(ptr)
+        return vs
+
     def deinterleave(self, img):
         h, w, nc = img.shape
         img = np.ascontiguousarray(img)

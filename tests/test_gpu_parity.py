@@ -39,6 +39,36 @@ def flags_for(layout, quirk=True):
     return sd.EXACT | (sd.QUIRK_AVX_X3 if (layout == sd.LAYOUT_B and quirk) else 0)
 
 
+def _dct8_inputs():
+    rng = np.random.default_rng(7)
+    ints = rng.integers(0, 256, (60000, 8)).astype(np.float32)            # first-pass inputs of layout B
+    unit = (rng.integers(0, 256, (60000, 8)).astype(np.float32) / np.float32(255))  # ... of layouts A / C
+    wide = (rng.standard_normal((60000, 8)) * 300).astype(np.float32)     # second-pass-like inputs
+    edge = np.array([[0] * 8, [255] * 8, [255, 0] * 4, [0, 0, 0, 0, 255, 255, 255, 255], [1e-30] * 8], dtype=np.float32)
+    return np.concatenate([ints, unit, wide, edge])
+
+
+@pytest.mark.parametrize("kind,name,quirk", [(0, "dct8_scalar", 0), (8, "dct8_scalar", 0), (1, "paired", 0), (9, "paired", 0),
+                                             (2, "paired", 1), (10, "paired", 1), (3, "dct8_fast", 0), (4, "idct8", 0)])
+def test_dct8_bitwise(ctx, oracle, kind, name, quirk):
+    """the device 8-point kernels (packed fp32, sdct_math.cuh) reproduce the CPU restatement bit for
+    bit - in particular no multiply-add contraction sneaks into the EXACT graphs."""
+    x = _dct8_inputs()
+    got = ctx.selftest_dct8(kind, x)
+    want = np.stack([oracle.dct8(name, v, quirk) for v in x[:4000]])
+    assert np.array_equal(got[:4000].view(np.uint32), want.view(np.uint32))
+    want_all = oracle.dct8_many(name, x, quirk)
+    bad = np.flatnonzero((got.view(np.uint32) != want_all.view(np.uint32)).any(axis=1))
+    assert bad.size == 0, (bad[:5], got[bad[:1]], want_all[bad[:1]])
+
+
+def test_div255_bitwise(ctx):
+    """x / 255.f (src/simd_dct.cpp:217, :340) as two FMA-pipe operations: all 256 inputs"""
+    x = np.arange(256, dtype=np.float32).reshape(32, 8)
+    got = ctx.selftest_dct8(5, x)
+    assert np.array_equal(got.view(np.uint32), (x / np.float32(255)).astype(np.float32).view(np.uint32))
+
+
 @pytest.mark.parametrize("kind", ["rand", "smooth"])
 @pytest.mark.parametrize("scale", [1, 8, 255])
 @pytest.mark.parametrize("layout", LAYOUTS)

@@ -1,0 +1,7 @@
+#!/bin/bash
+# usage: gpu_ncu.sh <outname> <kernel-regex> <prof_run names...>
+out=$1; shift; rx=$1; shift
+mkdir -p gpurun_out
+python tools/prof_run.py "$@" > gpurun_out/${out}_plain.log 2>&1 &&
+ncu --set full --clock-control none --import-source on -k regex:$rx -s 2 -c 2 -f -o gpurun_out/$out python tools/prof_run.py "$@" > gpurun_out/${out}_ncu.log 2>&1
+echo "ncu rc=$?"; cat gpurun_out/${out}_plain.log; tail -3 gpurun_out/${out}_ncu.log
