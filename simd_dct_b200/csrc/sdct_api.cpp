@@ -100,6 +100,7 @@ int run_device(sdct_context *ctx, int op, const sdct_job *j, const uint8_t *pixe
     p.coef_frame_stride = j->coef_frame_stride; p.coef_comp_stride = j->coef_comp_stride;
     p.coef_plane_stride = j->coef_plane_stride;
     p.bpr = g.bpr; p.eyes = g.eyes; p.comps = g.comps; p.frames = (uint32_t)j->frames;
+    p.sm_count = (uint32_t)ctx->sm_count;
     p.row0 = g.band_begin * g.eyes;
     p.rows = (g.band_end - g.band_begin) * g.eyes;
     const uint64_t blocks = (uint64_t)p.rows * p.bpr;

@@ -31,40 +31,93 @@ constexpr int A_SLOT = 80;               // layout A: 64 B block + 16 B pad (con
 constexpr int C_PITCH = CB;              // layout C: 64 rows of CB bytes
 constexpr int STAGE_BYTES = 32 * B_GROUP_PITCH > CB * A_SLOT ? 32 * B_GROUP_PITCH : CB * A_SLOT;
 
-struct BlockPos {
-    const uint8_t *px[2];   // top-left pixel (component 0) of blocks P, Q
-    bool valid[2];
+constexpr int IN_STAGE_BYTES = 8 * TB * 16;   // prefetched pixels of one tile: 8 rows x 128 threads x (P 8 B | Q 8 B)
+
+// one tile = the CB consecutive blocks [n0, n0 + count) of one coefficient set; CTA-uniform
+struct Tile {
+    const uint8_t *pix;     // pixel base of the frame
     uint8_t *coef;          // start of the coefficient set of (frame, comp)
     uint32_t comp;
-    uint32_t n0;            // first n_local of this CTA
-    uint32_t count;         // valid blocks in this CTA
+    uint32_t n0;            // first n_local of this tile
+    uint32_t count;         // valid blocks in this tile
+};
+
+SDCT_DEV Tile tile_info(const KParams &p, uint32_t tile)
+{
+    Tile t;
+    const uint32_t chunk = tile % p.chunks;
+    const uint32_t fc = tile / p.chunks;
+    t.comp = fc % p.comps;
+    const uint32_t frame = fc / p.comps;
+    t.n0 = chunk * CB;
+    t.count = min((uint32_t)CB, p.rows * p.bpr - t.n0);
+    t.pix = p.pixels + (uint64_t)frame * p.pixel_frame_stride;
+    t.coef = p.coefs + (uint64_t)frame * p.coef_frame_stride + (uint64_t)t.comp * p.coef_comp_stride;
+    return t;
+}
+
+// this thread's two blocks of a tile: P, Q = slots 2t, 2t+1 (layouts B, C) or t, t+128 (layout A)
+struct BlockPos {
+    const uint8_t *px[2];   // top-left pixel (component 0)
+    bool valid[2];
+    uint32_t comp;
 };
 
 template <int LAYOUT>
-SDCT_DEV BlockPos locate(const KParams &p)
+SDCT_DEV BlockPos locate(const KParams &p, const Tile &t)
 {
     BlockPos b;
-    const uint32_t chunk = blockIdx.x % p.chunks;
-    const uint32_t fc = blockIdx.x / p.chunks;
-    b.comp = fc % p.comps;
-    const uint32_t frame = fc / p.comps;
-    const uint32_t total = p.rows * p.bpr;
-    b.n0 = chunk * CB;
-    b.count = min((uint32_t)CB, total - b.n0);
-    const uint8_t *base = p.pixels + (uint64_t)frame * p.pixel_frame_stride;
+    b.comp = t.comp;
 #pragma unroll
     for (int k = 0; k < 2; k++) {
         const uint32_t slot = (LAYOUT == SDCT_K_LAYOUT_A) ? threadIdx.x + k * TB : 2 * threadIdx.x + k;
-        b.valid[k] = slot < b.count;
-        const uint32_t nl = b.n0 + (b.valid[k] ? slot : 0);  // keep addresses in range
+        b.valid[k] = slot < t.count;
+        const uint32_t nl = t.n0 + (b.valid[k] ? slot : 0);  // keep addresses in range
         const uint32_t r = nl / p.bpr;
         const uint32_t bx = nl - r * p.bpr;
         const uint32_t row = r + p.row0;
-        const uint32_t band = row / p.eyes, eye = row - band * p.eyes;
-        b.px[k] = base + (uint64_t)eye * p.eye_stride + (uint64_t)band * 8 * p.pitch + (uint64_t)bx * 8 * p.comps;
+        const uint32_t band = p.eyes == 2 ? row >> 1 : row, eye = p.eyes == 2 ? row & 1 : 0;
+        b.px[k] = t.pix + (uint64_t)eye * p.eye_stride + (uint64_t)band * 8 * p.pitch + (uint64_t)bx * 8 * p.comps;
     }
-    b.coef = p.coefs + (uint64_t)frame * p.coef_frame_stride + (uint64_t)b.comp * p.coef_comp_stride;
     return b;
+}
+
+// ---- asynchronous pixel prefetch (cp.async): each thread copies the rows of ITS two blocks into
+// ITS 16-byte slots of the stage, so no barrier is needed between the copy and the read ---------
+SDCT_DEV void cp_async16(void *smem, const void *gmem)
+{
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(smem)), "l"(gmem) : "memory");
+}
+SDCT_DEV void cp_async8(void *smem, const void *gmem)
+{
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"((uint32_t)__cvta_generic_to_shared(smem)), "l"(gmem) : "memory");
+}
+SDCT_DEV void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N> SDCT_DEV void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
+template <int VEC>
+SDCT_DEV void prefetch_pair(uint8_t *stage, const BlockPos &b, uint64_t pitch)
+{
+    uint8_t *slot = stage + threadIdx.x * 16;
+#pragma unroll
+    for (int r = 0; r < 8; r++) {
+        if (VEC == 2) {
+            cp_async16(slot + r * (TB * 16), b.px[0] + r * pitch);
+        } else {
+            cp_async8(slot + r * (TB * 16), b.px[0] + r * pitch);
+            cp_async8(slot + r * (TB * 16) + 8, b.px[1] + r * pitch);
+        }
+    }
+}
+
+SDCT_DEV void read_prefetched(const uint8_t *stage, uint32_t wp[16], uint32_t wq[16])
+{
+    const uint8_t *slot = stage + threadIdx.x * 16;
+#pragma unroll
+    for (int r = 0; r < 8; r++) {
+        const uint4 v = *reinterpret_cast<const uint4 *>(slot + r * (TB * 16));
+        wp[2 * r] = v.x; wp[2 * r + 1] = v.y; wq[2 * r] = v.z; wq[2 * r + 1] = v.w;
+    }
 }
 
 // ---- pixel block -> 16 words (row r = words 2r, 2r+1), component extraction fused ----------------
@@ -213,7 +266,7 @@ SDCT_DEV uint4 xor4(uint4 v, uint32_t m) { return make_uint4(v.x ^ m, v.y ^ m, v
 
 // shared-memory image -> global memory, coalesced; COMPL undoes the complemented levels
 template <int LAYOUT, bool COMPL>
-SDCT_DEV void flush_coefs(const uint8_t *sm, const KParams &p, const BlockPos &b)
+SDCT_DEV void flush_coefs(const uint8_t *sm, const KParams &p, const Tile &b)
 {
     const uint32_t t = threadIdx.x;
     const uint64_t n_first = (uint64_t)p.row0 * p.bpr + b.n0;
@@ -255,24 +308,48 @@ SDCT_DEV void flush_coefs(const uint8_t *sm, const KParams &p, const BlockPos &b
     }
 }
 
+// Persistent CTAs: tile = blockIdx.x, + gridDim.x, ...  The pixels of tile k+1 are prefetched with
+// cp.async while tile k is transformed; the output staging image is double-buffered so that one
+// barrier per tile suffices (the image written in iteration k is flushed before barrier k+1, and
+// written again only after it).
+template <int COMPS, int VEC> __host__ __device__ constexpr bool prefetchable() { return COMPS == 1 && VEC >= 1; }
+
 template <int LAYOUT, int MODE, bool X3, int COMPS, int VEC>
 __global__ void __launch_bounds__(SDCT_TB, 3) forward_kernel(const __grid_constant__ KParams p)
 {
-    __shared__ __align__(16) uint8_t sm[STAGE_BYTES];
-    const BlockPos b = locate<LAYOUT>(p);
-    uint32_t wp[16], wq[16];
-    load_pair<COMPS, VEC>(b, p.pitch, wp, wq);
-    F2 v[64];
-    forward_pair<LAYOUT, MODE, X3>(wp, wq, p.tab, v);
-    stage_levels<LAYOUT>(sm, v);
-    __syncthreads();
-    flush_coefs<LAYOUT, complemented<LAYOUT, MODE>()>(sm, p, b);
+    extern __shared__ __align__(16) uint8_t smem[];
+    constexpr bool PF = prefetchable<COMPS, VEC>();
+    uint8_t *stage_in = smem + 2 * STAGE_BYTES;
+    uint32_t tile = blockIdx.x;
+    if (PF) {
+        if (tile < p.tiles) prefetch_pair<VEC>(stage_in, locate<LAYOUT>(p, tile_info(p, tile)), p.pitch);
+        cp_async_commit();
+    }
+    for (uint32_t it = 0; tile < p.tiles; it++, tile += gridDim.x) {
+        const Tile t = tile_info(p, tile);
+        uint32_t wp[16], wq[16];
+        if (PF) {
+            const uint32_t next = tile + gridDim.x;
+            if (next < p.tiles) prefetch_pair<VEC>(stage_in + ((it + 1) & 1) * IN_STAGE_BYTES, locate<LAYOUT>(p, tile_info(p, next)), p.pitch);
+            cp_async_commit();
+            cp_async_wait<1>();
+            read_prefetched(stage_in + (it & 1) * IN_STAGE_BYTES, wp, wq);
+        } else {
+            load_pair<COMPS, VEC>(locate<LAYOUT>(p, t), p.pitch, wp, wq);
+        }
+        F2 v[64];
+        forward_pair<LAYOUT, MODE, X3>(wp, wq, p.tab, v);
+        uint8_t *sm = smem + (it & 1) * STAGE_BYTES;
+        stage_levels<LAYOUT>(sm, v);
+        __syncthreads();
+        flush_coefs<LAYOUT, complemented<LAYOUT, MODE>()>(sm, p, t);
+    }
 }
 
 // ---- inverse ---------------------------------------------------------------------------------------
 // global coefficient bytes of this CTA -> shared-memory image (same image as the forward staging)
 template <int LAYOUT>
-SDCT_DEV void fetch_coefs(uint8_t *sm, const KParams &p, const BlockPos &b)
+SDCT_DEV void fetch_coefs(uint8_t *sm, const KParams &p, const Tile &b)
 {
     const uint32_t t = threadIdx.x;
     const uint64_t n_first = (uint64_t)p.row0 * p.bpr + b.n0;
@@ -396,34 +473,55 @@ SDCT_DEV void store_pair(const BlockPos &b, const uint8_t *in_base, uint8_t *out
 template <int LAYOUT, int COMPS, int VEC>
 __global__ void __launch_bounds__(SDCT_TB, 3) inverse_kernel(const __grid_constant__ KParams p)
 {
-    __shared__ __align__(16) uint8_t sm[STAGE_BYTES];
-    const BlockPos b = locate<LAYOUT>(p);
-    fetch_coefs<LAYOUT>(sm, p, b);
-    __syncthreads();
-    F2 v[64];
-    unstage_levels<LAYOUT>(sm, v);
-    inverse_pair<LAYOUT>(p.tab, p.off, v);
-    store_pair<COMPS, VEC>(b, p.pixels, const_cast<uint8_t *>(p.pixels), p.pitch, v);
+    extern __shared__ __align__(16) uint8_t smem[];
+    for (uint32_t tile = blockIdx.x, it = 0; tile < p.tiles; it++, tile += gridDim.x) {
+        const Tile t = tile_info(p, tile);
+        uint8_t *sm = smem + (it & 1) * STAGE_BYTES;
+        fetch_coefs<LAYOUT>(sm, p, t);
+        __syncthreads();
+        F2 v[64];
+        unstage_levels<LAYOUT>(sm, v);
+        inverse_pair<LAYOUT>(p.tab, p.off, v);
+        store_pair<COMPS, VEC>(locate<LAYOUT>(p, t), p.pixels, const_cast<uint8_t *>(p.pixels), p.pitch, v);
+    }
 }
 
 // fused forward -> quantise -> dequantise -> inverse: coefficients never leave the registers
 template <int LAYOUT, int MODE, bool X3, int COMPS, int VEC>
 __global__ void __launch_bounds__(SDCT_TB, 3) roundtrip_kernel(const __grid_constant__ KParams p)
 {
-    const BlockPos b = locate<LAYOUT>(p);
-    uint32_t wp[16], wq[16];
-    load_pair<COMPS, VEC>(b, p.pitch, wp, wq);
-    F2 v[64];
-    forward_pair<LAYOUT, MODE, X3>(wp, wq, p.tab, v);
-    // bit patterns -> saturated levels -> floats (the level a decoder would read back)
-#pragma unroll
-    for (int i = 0; i < 64; i++) {
-        uint32_t h = pack_pq(v[i]);
-        if (complemented<LAYOUT, MODE>()) h = ~h;
-        v[i] = make_float2(byte_to_float(h, 0), byte_to_float(h, 1));
+    extern __shared__ __align__(16) uint8_t smem[];
+    constexpr bool PF = prefetchable<COMPS, VEC>();
+    uint8_t *stage_in = smem;
+    uint32_t tile = blockIdx.x;
+    if (PF) {
+        if (tile < p.tiles) prefetch_pair<VEC>(stage_in, locate<LAYOUT>(p, tile_info(p, tile)), p.pitch);
+        cp_async_commit();
     }
-    inverse_pair<LAYOUT>(p.tab2, p.off, v);
-    store_pair<COMPS, VEC>(b, p.pixels, p.pixels_out, p.pitch, v);
+    for (uint32_t it = 0; tile < p.tiles; it++, tile += gridDim.x) {
+        const Tile t = tile_info(p, tile);
+        uint32_t wp[16], wq[16];
+        if (PF) {
+            const uint32_t next = tile + gridDim.x;
+            if (next < p.tiles) prefetch_pair<VEC>(stage_in + ((it + 1) & 1) * IN_STAGE_BYTES, locate<LAYOUT>(p, tile_info(p, next)), p.pitch);
+            cp_async_commit();
+            cp_async_wait<1>();
+            read_prefetched(stage_in + (it & 1) * IN_STAGE_BYTES, wp, wq);
+        } else {
+            load_pair<COMPS, VEC>(locate<LAYOUT>(p, t), p.pitch, wp, wq);
+        }
+        F2 v[64];
+        forward_pair<LAYOUT, MODE, X3>(wp, wq, p.tab, v);
+        // bit patterns -> saturated levels -> floats (the level a decoder would read back)
+#pragma unroll
+        for (int i = 0; i < 64; i++) {
+            uint32_t h = pack_pq(v[i]);
+            if (complemented<LAYOUT, MODE>()) h = ~h;
+            v[i] = make_float2(byte_to_float(h, 0), byte_to_float(h, 1));
+        }
+        inverse_pair<LAYOUT>(p.tab2, p.off, v);
+        store_pair<COMPS, VEC>(locate<LAYOUT>(p, t), p.pixels, p.pixels_out, p.pitch, v);
+    }
 }
 
 #if SDCT_PART == 0
@@ -476,10 +574,18 @@ SDCT_DECL(sdct_part_inverse);
 template <int LAYOUT, int MODE, bool X3>
 static cudaError_t launch_fwd2(int op, const KParams &p, unsigned grid, cudaStream_t s)
 {
-#define SDCT_GO(K, C, V)                                                     \
-    do {                                                                     \
-        K<LAYOUT, MODE, X3, C, V><<<grid, SDCT_TB, 0, s>>>(p);               \
-        return cudaGetLastError();                                           \
+#define SDCT_GO(K, C, V)                                                                              \
+    do {                                                                                              \
+        const size_t smem = (op == SDCT_K_OP_FORWARD ? 2 * STAGE_BYTES : 0) +                         \
+                            (prefetchable<C, V>() ? 2 * IN_STAGE_BYTES : 0);                          \
+        static bool attr_done = false;                                                                \
+        if (!attr_done) {                                                                             \
+            cudaError_t e = cudaFuncSetAttribute(K<LAYOUT, MODE, X3, C, V>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
+            if (e != cudaSuccess) return e;                                                           \
+            attr_done = true;                                                                         \
+        }                                                                                             \
+        K<LAYOUT, MODE, X3, C, V><<<grid, SDCT_TB, smem, s>>>(p);                                     \
+        return cudaGetLastError();                                                                    \
     } while (0)
 #define SDCT_PICK(K)                                                                                   \
     do {                                                                                               \
@@ -500,14 +606,26 @@ static cudaError_t launch_fwd2(int op, const KParams &p, unsigned grid, cudaStre
 template <int LAYOUT>
 static cudaError_t launch_inv2(const KParams &p, unsigned grid, cudaStream_t s)
 {
+    const size_t smem = 2 * STAGE_BYTES;
+#define SDCT_INV(C, V)                                                                                                   \
+    do {                                                                                                                 \
+        static bool attr_done = false;                                                                                   \
+        if (!attr_done) {                                                                                                \
+            cudaError_t e = cudaFuncSetAttribute(inverse_kernel<LAYOUT, C, V>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
+            if (e != cudaSuccess) return e;                                                                              \
+            attr_done = true;                                                                                            \
+        }                                                                                                                \
+        inverse_kernel<LAYOUT, C, V><<<grid, SDCT_TB, smem, s>>>(p);                                                     \
+        return cudaGetLastError();                                                                                       \
+    } while (0)
     if (p.comps == 1) {
-        if (p.pixel_vec == 2 && LAYOUT != SDCT_K_LAYOUT_A) inverse_kernel<LAYOUT, 1, 2><<<grid, SDCT_TB, 0, s>>>(p);
-        else if (p.pixel_vec >= 1) inverse_kernel<LAYOUT, 1, 1><<<grid, SDCT_TB, 0, s>>>(p);
-        else inverse_kernel<LAYOUT, 1, 0><<<grid, SDCT_TB, 0, s>>>(p);
+        if (p.pixel_vec == 2 && LAYOUT != SDCT_K_LAYOUT_A) SDCT_INV(1, 2);
+        else if (p.pixel_vec >= 1) SDCT_INV(1, 1);
+        else SDCT_INV(1, 0);
     } else {
-        inverse_kernel<LAYOUT, 3, 0><<<grid, SDCT_TB, 0, s>>>(p);
+        SDCT_INV(3, 0);
     }
-    return cudaGetLastError();
+#undef SDCT_INV
 }
 
 #if SDCT_PART == 1
@@ -541,10 +659,13 @@ extern "C" cudaError_t sdct_k_launch(int op, int layout, int mode, int x3, const
 {
     KParams p = *pp;
     p.layout = (uint32_t)layout;
-    const unsigned long long grid64 = (unsigned long long)p.chunks * p.comps * p.frames;
-    if (grid64 == 0) return cudaSuccess;
-    if (grid64 > 0x7fffffffull) return cudaErrorInvalidConfiguration;
-    const unsigned grid = (unsigned)grid64;
+    const unsigned long long tiles = (unsigned long long)p.chunks * p.comps * p.frames;
+    if (tiles == 0) return cudaSuccess;
+    if (tiles > 0xfffffff0ull) return cudaErrorInvalidConfiguration;
+    p.tiles = (uint32_t)tiles;
+    // persistent CTAs: three per SM (168 registers/thread), each walking tiles blockIdx.x, +grid, ...
+    const unsigned resident = 3u * (p.sm_count ? p.sm_count : 148u);
+    const unsigned grid = (unsigned)(tiles < resident ? tiles : resident);
     if (op == SDCT_K_OP_INVERSE) return sdct_part_inverse(op, x3, p, grid, s);
     static const part_fn exact[3] = {sdct_part_exact_a, sdct_part_exact_b, sdct_part_exact_c};
     static const part_fn fast[3] = {sdct_part_fast_a, sdct_part_fast_b, sdct_part_fast_c};

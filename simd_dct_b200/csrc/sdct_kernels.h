@@ -28,7 +28,9 @@ struct KParams {
     uint32_t comps;
     uint32_t frames;
     uint32_t layout;          // SDCT_K_LAYOUT_* (filled in by sdct_k_launch)
-    uint32_t chunks;          // CTAs per (frame, component)
+    uint32_t chunks;          // tiles per (frame, component)
+    uint32_t tiles;           // chunks * comps * frames (filled in by sdct_k_launch)
+    uint32_t sm_count;        // SMs of the device (persistent grid size)
     uint32_t pixel_vec;       // 0 = byte access, 1 = 8-byte rows, 2 = 16-byte rows for an adjacent block pair
     uint32_t coef_aligned16, coef_aligned4;
     // scale tables, each value duplicated for the two packed lanes (P, Q)

@@ -1,0 +1,95 @@
+"""The arithmetic identities the CUDA kernels rely on (simd_dct_b200/csrc/sdct_math.cuh), proven on
+the CPU with exact rational arithmetic / IEEE binary32 emulation.  The GPU side of the same
+identities is tests/test_gpu_parity.py::test_dct8_bitwise, ::test_div255_bitwise and the parity tests."""
+from fractions import Fraction
+import math
+
+import numpy as np
+
+f32 = np.float32
+
+
+def rn32(fr: Fraction, mode="rn") -> np.float32:
+    """round an exact rational to binary32 (normal or denormal), nearest-even or toward -inf"""
+    if fr == 0:
+        return f32(0)
+    s = -1 if fr < 0 else 1
+    a = abs(fr)
+    e = max(math.floor(math.log2(a)) if a >= 1 else -math.ceil(math.log2(1 / a)), -126)
+    while e > -126 and Fraction(2) ** e > a:
+        e -= 1
+    while Fraction(2) ** (e + 1) <= a:
+        e += 1
+    ulp = Fraction(2) ** (e - 23)
+    q = a / ulp
+    n = q.numerator // q.denominator
+    rem = q - n
+    if mode == "rn":
+        if rem > Fraction(1, 2) or (rem == Fraction(1, 2) and (n & 1)):
+            n += 1
+    else:  # toward -inf
+        if s < 0 and rem != 0:
+            n += 1
+    return f32(s * float(Fraction(n) * ulp))
+
+
+def F(x) -> Fraction:
+    return Fraction(float(x))
+
+
+def test_div255_two_operation_form_is_ieee_division():
+    """q = fma(x, r, fl(x * rl)), r = fl(1/255), rl = fl(1/255 - r)  ==  x / 255.f for x = 0..255"""
+    r = f32(0.003921568859368562698364257812500)
+    rl = f32(-2.319175823606300543e-10)
+    assert r == f32(1) / f32(255)
+    assert rl == rn32(Fraction(1, 255) - F(r))
+    for x in range(256):
+        t = rn32(F(f32(x)) * F(rl))
+        q = rn32(F(f32(x)) * F(r) + F(t))
+        assert q == f32(x) / f32(255), x
+    assert sum(1 for x in range(256) if f32(x) * r != f32(x) / f32(255)) == 126  # why one multiply is not enough
+
+
+def bits(x: np.float32) -> int:
+    return int(np.array(x, dtype=np.float32).view(np.int32))
+
+
+def sat_u8(s32: int) -> int:
+    return 0 if s32 < 0 else (255 if s32 > 255 else s32)
+
+
+def test_denormal_scaled_fma_is_round_to_nearest_even_plus_bias_and_clamp():
+    """bits(fma(v, -2^-149, 128 * 2^-149)) saturated to u8 == 255 - clamp(rne(v) + 127, 0, 255): the
+    reference's AVX2 quantiser (src/simd_dct.cpp:2224) without an integer add"""
+    dmin = Fraction(1, 2 ** 149)
+    rng = np.random.default_rng(0)
+    vs = list((rng.standard_normal(4000) * 200).astype(f32))
+    vs += [f32(k + h) for k in range(-131, 131) for h in (0.0, 0.5, -0.5, 0.25, 0.75)]
+    vs += [f32(x) for x in (1e6, -1e6, 8388607.5, -8388608.0, 3e9, -3e9, 2 ** 31 - 128, -(2.0 ** 31))]
+    for v in vs:
+        w = rn32(-F(v) * dmin + 128 * dmin)
+        want = 255 - sat_u8(int(np.rint(np.float64(v))) + 127)
+        assert sat_u8(bits(w)) == want, float(v)
+
+
+def test_roundf_as_two_round_down_operations():
+    """roundf(y) for y in [0, 255] == bits(mul_rd(add_rd(y, 0.5), 2^-149)): floor(y + 0.5) cannot be
+    fooled by the sum's rounding because round-down never crosses an integer"""
+    dmin = Fraction(1, 2 ** 149)
+    ys = [f32(k) + f32(d) for k in range(0, 256) for d in (0, 0.5, 0.49999997, 0.50000006, 0.25)]
+    ys += [np.nextafter(f32(k + 0.5), f32(0)) for k in range(0, 255)] + [np.nextafter(f32(k + 0.5), f32(300)) for k in range(0, 255)]
+    ys = [y for y in ys if 0 <= y <= 255]
+    for y in ys:
+        u = rn32(F(y) + Fraction(1, 2), "rd")
+        n = bits(rn32(F(u) * dmin, "rd"))
+        # C roundf: half away from zero (float(y) + 0.5 is exact in binary64)
+        assert n == int(math.floor(float(y) + 0.5)), float(y)
+
+
+def test_pixel_rounding_by_denormal_multiply():
+    """bits(x * 2^-149) saturated == clamp(rne(x), 0, 255) (inverse transform output)"""
+    dmin = Fraction(1, 2 ** 149)
+    for x in [f32(v) for v in (-3.2, -0.4, -0.0, 0.0, 0.4, 0.5, 1.5, 2.5, 254.5, 254.50002, 255.0, 255.6, 1e5, -1e5, 127.49999)]:
+        w = rn32(F(x) * dmin)
+        want = int(min(255, max(0, np.rint(np.float64(x)))))
+        assert sat_u8(bits(w)) == want, float(x)
