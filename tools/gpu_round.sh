@@ -1,0 +1,24 @@
+#!/bin/bash
+# full GPU pass: parity tests, smoke, bench (both arms), launch list, ncu --set full of the headline kernel
+mkdir -p gpurun_out
+nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm,power.draw --format=csv > gpurun_out/smi.txt 2>&1
+nproc > gpurun_out/nproc.txt; lscpu | grep -E "Model name|^CPU\(s\)|Flags" | cut -c1-400 >> gpurun_out/nproc.txt
+timeout 900 python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.txt 2>&1; echo "pytest rc=$?"; tail -8 gpurun_out/pytest_gpu.txt
+timeout 300 python __graft_entry__.py smoke > gpurun_out/smoke.txt 2>&1; echo "smoke rc=$?"; tail -2 gpurun_out/smoke.txt
+timeout 600 python bench.py --steps 20 --warmup 3 > gpurun_out/bench.json 2> gpurun_out/bench.err; echo "bench rc=$?"
+tail -5 gpurun_out/bench.err
+python - <<'PY'
+import json
+d=json.load(open('gpurun_out/bench.json'))
+print('headline ms', d['ms_per_step'], 'GB/s', d['gbps'], 'frac', d['roofline']['frac'])
+print('e2e', d['e2e']['ms_per_step'], d['e2e']['gbps_each_way'])
+for k,v in d['variants'].items(): print(k, round(v['ms_per_step'],4), round(v['gbps_per_gpu']), round(v['frac_of_hbm_peak'],3))
+print(d['clocks']); print(d.get('cpu_baseline'))
+PY
+timeout 300 python bench.py --impl reference --steps 5 --warmup 3 > gpurun_out/bench_ref.json 2>> gpurun_out/bench.err; echo "ref rc=$?"
+timeout 300 python bench.py --steps 3 --warmup 3 --no-variants > gpurun_out/plain.log 2>&1 &&
+timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 200 --csv --log-file gpurun_out/launches.csv python bench.py --steps 3 --warmup 3 --no-variants > gpurun_out/ncu.log 2>&1
+echo "ncu launches rc=$?"
+for k in fwd_B_exact fwd_B_fast; do
+  bash tools/gpu_ncu.sh $k forward_kernel $k
+done
