@@ -1,5 +1,8 @@
 """GPU parity: the CUDA path (through the C ABI) against the CPU oracle on identical inputs.
 Bar: byte-identical for every forward mode and for the inverse (integer outputs)."""
+import os
+import subprocess
+
 import numpy as np
 import pytest
 
@@ -300,3 +303,127 @@ def test_full_size_1080p_batch_properties(ctx, oracle):
         lo = ctx.forward(d[:f // 2], lut, half)
         hi = ctx.forward(d[f // 2:], lut, half)
         assert torch.equal(torch.cat([lo, hi]), got)
+
+
+CLI_DIR = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "oracle", "_ref")
+
+
+@pytest.mark.skipif(not os.path.exists(os.path.join(CLI_DIR, "simd_dct_cli_b200")), reason="oracle/_ref CLIs not built")
+@pytest.mark.parametrize("mode,simd", [("enc-quant", "none"), ("enc-quant32", "avx2"), ("enc-quant-stereo", "none")])
+def test_reference_cli_linked_against_libsdct(tmp_path, mode, simd):
+    """the reference's own CLI (src/main.cpp, unmodified) linked against
+    libsdct.so instead of src/simd_dct.cpp writes the same --to dump as the all-CPU binary."""
+    if simd == "avx2" and "avx2" not in ol.cpu_flags():
+        pytest.skip("host CPU has no AVX2: the reference cannot produce layout B here")
+    img = make_image("smooth", 512, 768, seed=5)
+    raw = tmp_path / "img.raw"
+    raw.write_bytes(img.tobytes())
+    outs = []
+    for exe in ("simd_dct_cli_cpu", "simd_dct_cli_b200"):
+        dump = tmp_path / (exe + ".bin")
+        dump.write_bytes(b"")
+        r = subprocess.run([os.path.join(CLI_DIR, exe), str(raw), "768", "512", "--runs", "2", "--quality", "8", "--mode", mode,
+                            "--max-simd", simd, "--to", str(dump)], capture_output=True, text=True, timeout=120)
+        assert r.returncode == 0, r.stdout + r.stderr
+        outs.append(np.frombuffer(dump.read_bytes(), dtype=np.uint8))
+    assert outs[0].size == 768 * 512
+    # the CLI mallocs its output buffer and never clears it: compare only the bytes the call writes
+    # (layouts A / B visit the top half of the image, src/simd_dct.cpp:375 / :2243)
+    n = 768 * 512 if mode == "enc-quant-stereo" else 768 * 256
+    assert np.array_equal(outs[0][:n], outs[1][:n])
+
+
+def test_config3_4k_interleaved_rgb(ctx, oracle):
+    """BASELINE config 3 shape (3840x2160x3 interleaved RGB -> 3 planar coefficient sets), 3 frames:
+    oracle parity on sampled bands of frame 1 (oracle = de-interleave + reference single-plane
+    forward), batch == per-frame on all, inverse returns interleaved pixels within the
+    quantiser's error."""
+    f, h, w = 3, 2160, 3840
+    g = torch.Generator(device="cuda").manual_seed(11)
+    base = torch.randint(0, 256, (f, h // 8, w // 8, 3), dtype=torch.uint8, device="cuda", generator=g)
+    imgs = base.repeat_interleave(8, 1).repeat_interleave(8, 2)
+    imgs = (imgs.to(torch.int16) // 2 + torch.randint(0, 128, (f, h, w, 3), dtype=torch.int16, device="cuda", generator=g)).to(torch.uint8)
+    lut = ol.lut(8)
+    for layout in (sd.LAYOUT_B, sd.LAYOUT_C):
+        job = sd.dense_job(layout, w, h, frames=f, components=3, flags=flags_for(layout))
+        got = ctx.forward(imgs, lut, job).view(f, 3, -1)
+        one = sd.dense_job(layout, w, h, frames=1, components=3, flags=flags_for(layout))
+        for k in range(f):
+            assert torch.equal(ctx.forward(imgs[k], lut, one).view(3, -1), got[k])
+        # oracle on bands [100, 104) of frame 1, each component
+        b0, b1 = 100, 104
+        rows = imgs[1, b0 * 8:b1 * 8].cpu().numpy()
+        for c in range(3):
+            want = oracle.forward(layout, np.ascontiguousarray(rows[:, :, c]), lut, quirks=ol.QUIRK_AVX_X3)
+            n0, n1 = b0 * (w // 8), b1 * (w // 8)
+            if layout == sd.LAYOUT_B:
+                mine = got[1, c, n0 * 64:n1 * 64].cpu().numpy()
+            else:
+                mine = got[1, c].view(64, -1)[:, n0:n1].contiguous().view(-1).cpu().numpy()
+            assert np.array_equal(mine, want), (layout, c)
+
+
+def test_config4_inverse_only_4k(ctx, oracle):
+    """BASELINE config 4: inverse-only decode of 4K coefficient planes; frames sharded as the
+    multi-GPU run shards them (contiguous frame ranges, no collective) give the batch result, and
+    sampled bands equal the CPU restatement of the inverse."""
+    f, h, w = 4, 2160, 3840
+    g = torch.Generator(device="cuda").manual_seed(12)
+    imgs = torch.randint(0, 256, (f, h, w), dtype=torch.uint8, device="cuda", generator=g)
+    for layout in (sd.LAYOUT_B, sd.LAYOUT_C):
+        lut = rt_lut(layout)
+        job = sd.dense_job(layout, w, h, frames=f, flags=flags_for(layout))
+        coef = ctx.forward(imgs, lut, job)
+        back = ctx.inverse(coef, lut, job).view(f, h, w)
+        parts = []
+        for r in range(2):
+            b, e = sd.shard_range(f, r, 2)
+            sub = sd.dense_job(layout, w, h, frames=e - b, flags=flags_for(layout))
+            parts.append(ctx.inverse(coef.view(f, -1)[b:e].contiguous(), lut, sub).view(e - b, h, w))
+        assert torch.equal(torch.cat(parts), back)
+        # CPU restatement on 2 bands of frame 2 (band-local coefficient window re-packed for the oracle)
+        b0, b1 = 17, 19
+        n0, n1 = b0 * (w // 8), b1 * (w // 8)
+        cf = coef.view(f, -1)[2]
+        if layout == sd.LAYOUT_B:
+            window = cf[n0 * 64:n1 * 64].cpu().numpy()
+        else:
+            window = cf.view(64, -1)[:, n0:n1].contiguous().view(-1).cpu().numpy()
+        want = oracle.inverse(layout, window, w, (b1 - b0) * 8, lut)
+        assert np.array_equal(back[2, b0 * 8:b1 * 8].cpu().numpy(), want)
+
+
+def test_config5_gigapixel_band_sharded_roundtrip(ctx, oracle):
+    """BASELINE config 5: 32768x32768x3 interleaved image generated on the device, forward + inverse
+    over band-range shards (8 shards, as 8 GPUs would take them; base pointers stay global so each
+    shard writes where the single-device run writes).  Checks: shards == whole, sampled bands ==
+    oracle, round-trip error bounded, fused round trip == forward then inverse."""
+    w = h = 32768
+    world = 8
+    g = torch.Generator(device="cuda").manual_seed(13)
+    img = torch.randint(0, 256, (h // 16, w // 16, 3), dtype=torch.uint8, device="cuda", generator=g)
+    img = img.repeat_interleave(16, 0).repeat_interleave(16, 1)          # 3 GiB, blocky content
+    img += torch.randint(0, 4, (1, w, 3), dtype=torch.uint8, device="cuda", generator=g)  # wraps mod 256: fine
+    layout = sd.LAYOUT_B
+    lut = rt_lut(layout)
+    job = sd.dense_job(layout, w, h, components=3, flags=flags_for(layout))
+    whole = ctx.forward(img, lut, job)
+    sharded = torch.zeros_like(whole)
+    from simd_dct_b200 import sharding
+    for r in range(world):
+        ctx.forward(img, lut, sharding.shard_bands(job, r, world), out=sharded)
+    assert torch.equal(whole, sharded)
+    del sharded
+    for band in (0, 2049, 4095):
+        rows = img[band * 8:band * 8 + 8].cpu().numpy()
+        n0, n1 = band * (w // 8), (band + 1) * (w // 8)
+        for c in (0, 2):
+            want = oracle.forward(layout, np.ascontiguousarray(rows[:, :, c]), lut, quirks=ol.QUIRK_AVX_X3)
+            assert np.array_equal(whole.view(3, -1)[c, n0 * 64:n1 * 64].cpu().numpy(), want)
+    back = torch.empty_like(img)
+    for r in range(world):
+        ctx.inverse(whole, lut, sharding.shard_bands(job, r, world), out=back)
+    err = (back[::7].to(torch.int16) - img[::7].to(torch.int16)).abs()
+    assert int(err.max()) <= 24 and float(err.float().mean()) < 3.0, (int(err.max()), float(err.float().mean()))
+    fused = ctx.roundtrip(img, lut, job)
+    assert torch.equal(fused, back)
