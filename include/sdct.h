@@ -42,7 +42,9 @@ enum {
 enum {
     SDCT_EXACT = 0,         /* the reference's fp32 operation order; byte-identical to its CPU output */
     SDCT_FAST = 1,          /* FMA-contracted arithmetic defined in oracle/sdct_oracle.c (<= 1 LSB from SDCT_EXACT) */
-    SDCT_QUIRK_AVX_X3 = 2   /* layout B: reproduce the reference's X3 sign (src/simd_dct.cpp:2181); see DESIGN.md */
+    SDCT_QUIRK_AVX_X3 = 2,  /* layout B: reproduce the reference's X3 sign (src/simd_dct.cpp:2181); see DESIGN.md */
+    SDCT_TENSOR = 4         /* tensor-core (tcgen05) integer form of the true DCT, defined in oracle/sdct_oracle.c mode TENSOR
+                               (<= 1 LSB from SDCT_EXACT); forward only for now */
 };
 
 typedef struct sdct_context sdct_context;
@@ -115,6 +117,10 @@ int sdct_inverse_host(sdct_context *ctx, const sdct_job *job, const void *h_coef
  * 2 = 1 with the reference's X3 sign (:2181), 3 forward/FAST, 4 inverse, 5 element-wise x/255.f;
  * kinds 8, 9, 10 are 0, 1, 2 in their second-pass form (first butterfly stage issued as scalar adds) */
 int sdct_selftest_dct8(sdct_context *ctx, int kind, float *h_data, size_t n);
+
+/* test hook (no device needed): the integer matrix K[c*64+p] = round(2^22 C[u][y] C[v][x]) of the
+ * SDCT_TENSOR form, as the library builds it; tests compare it with the oracle's restatement */
+void sdct_tensor_matrix(int32_t *k4096);
 
 /* synchronise the context's streams */
 int sdct_synchronize(sdct_context *ctx);

@@ -163,6 +163,9 @@ void sdct_oracle_tables(const float lut[64], int layout, float out[64], int whic
                                    A/C: 255 * (1/255) cancels, B: the AVX path's 255/d */
             out[i] = (layout == SDCT_O_LAYOUT_B) ? 0.125f * (255.0f / d) : 0.125f * (1.f / d);
             break;
+        case SDCT_O_TAB_TENSOR: /* the matrix carries 2^22; A/C: 255 * (1/255) cancels, B: the AVX path's 255/d */
+            out[i] = ldexpf((layout == SDCT_O_LAYOUT_B) ? 255.0f / d : 1.f / d, -22);
+            break;
         default:                /* SDCT_O_TAB_INVERSE: level -> coefficient in pixel units, 1/8 folded in */
             out[i] = (layout == SDCT_O_LAYOUT_B) ? (d / 255.f) * 0.125f : d * 0.125f;
             break;
@@ -241,6 +244,55 @@ static void block_fwd_fast(const uint8_t *px, size_t pitch, const float qs[64], 
         }
 }
 
+/* mode TENSOR (this repo; simd_dct_b200/csrc/sdct_tc.cu): K = round(2^22 C (x) C) as an integer
+ * matrix, entries of C = the reference's constants (:140-146) as doubles.  Per coefficient:
+ * exact integer sums D1 = sum x*hi, D0 = sum x*lo (|.| < 2^24, so the GPU's fp32 tensor-core
+ * accumulation is exact too), t = fma(D1, 1024, D0), level = clamp(rne(t * qs) + 127). */
+static double dct_entry(int u, int y)
+{
+    static const double V[9] = {1.4142135623730950488016887242097, 1.3870398453221474618216191915664,
+                                1.3065629648763765278566431734272, 1.1758756024193587169744671046113, 1.0,
+                                0.78569495838710218127789736765722, 0.54119610014619698439972320536639,
+                                0.27589937928294301233595756366937, 0.0};
+    const double N = 0.35355339059327376220042218105242;
+    if (u == 0) return N;
+    int m = ((2 * y + 1) * u) % 32;
+    double sign = 1.0;
+    if (m > 16) m = 32 - m;
+    if (m > 8) { m = 16 - m; sign = -1.0; }
+    return N * (sign * V[m]);
+}
+
+void sdct_oracle_tensor_matrix(int32_t K[64 * 64])
+{
+    for (int u = 0; u < 8; u++)
+        for (int v = 0; v < 8; v++)
+            for (int y = 0; y < 8; y++)
+                for (int x = 0; x < 8; x++)
+                    K[(u * 8 + v) * 64 + y * 8 + x] = (int32_t)llrint(ldexp(dct_entry(u, y) * dct_entry(v, x), 22));
+}
+
+static void block_fwd_tensor(const uint8_t *px, size_t pitch, const float qs[64], int transposed, uint8_t o[64])
+{
+    static int32_t K[64 * 64];
+    static int have = 0;
+    if (!have) { sdct_oracle_tensor_matrix(K); have = 1; }
+    for (int u = 0; u < 8; u++)
+        for (int v = 0; v < 8; v++) {
+            int32_t d1 = 0, d0 = 0;
+            for (int p = 0; p < 64; p++) {
+                const int32_t full = K[(u * 8 + v) * 64 + p];
+                const int32_t hi = (full + 512) >> 10, lo = full - hi * 1024;
+                const int32_t x = px[(p >> 3) * pitch + (p & 7)];
+                d1 += x * hi;
+                d0 += x * lo;
+            }
+            const float t = fmaf((float)d1, 1024.f, (float)d0);
+            const int i = transposed ? v * 8 + u : u * 8 + v;
+            o[i] = quant_fast(t, qs[i]);
+        }
+}
+
 /* inverse (this repo): dequantise with one FMA, (q - 127) * tab = fma(q, tab, -(127 * tab)),
  * vertical pass, horizontal pass, clamp(rne(.), 0, 255) */
 static void block_inv(const uint8_t q[64], const float tab[64], int transposed, uint8_t *px, size_t pitch)
@@ -291,7 +343,8 @@ static void forward_band(int layout, int mode, int quirks, const uint8_t *in, si
     for (int eye = 0; eye < eyes; eye++)
         for (size_t bx = 0; bx < width / 8; bx++) {
             gather_block(in + (size_t)eye * eye_stride + band * 8 * pitch + bx * 8 * xstep, pitch, xstep, tile);
-            if (mode == SDCT_O_MODE_FAST) block_fwd_fast(tile, 8, tab, layout == SDCT_O_LAYOUT_A, o);
+            if (mode == SDCT_O_MODE_TENSOR) block_fwd_tensor(tile, 8, tab, layout == SDCT_O_LAYOUT_A, o);
+            else if (mode == SDCT_O_MODE_FAST) block_fwd_fast(tile, 8, tab, layout == SDCT_O_LAYOUT_A, o);
             else if (layout == SDCT_O_LAYOUT_A) block_fwd_a(tile, 8, tab, o);
             else if (layout == SDCT_O_LAYOUT_B) block_fwd_b(tile, 8, tab, quirks, o);
             else block_fwd_c(tile, 8, tab, o);
@@ -301,7 +354,7 @@ static void forward_band(int layout, int mode, int quirks, const uint8_t *in, si
 
 static void forward_table(int layout, int mode, const float lut[64], float tab[64])
 {
-    const int which = mode == SDCT_O_MODE_FAST ? SDCT_O_TAB_FAST
+    const int which = mode == SDCT_O_MODE_TENSOR ? SDCT_O_TAB_TENSOR : mode == SDCT_O_MODE_FAST ? SDCT_O_TAB_FAST
                     : layout == SDCT_O_LAYOUT_B ? SDCT_O_TAB_AVX : SDCT_O_TAB_SCALAR;
     sdct_oracle_tables(lut, layout, tab, which);
 }

@@ -16,6 +16,8 @@
  *       validated by round-trip error against a float64 model, not by reference bytes.
  *   forward, mode FAST : this repo's FMA-contracted arithmetic (no reference counterpart);
  *       pinned only relative to mode EXACT (<= 1 LSB on a measured fraction of bytes).
+ *   forward, mode TENSOR : this repo's integer-matrix form of the true DCT (exact integer sums, one
+ *       fma + one multiply + round); no reference counterpart, pinned relative to mode EXACT.
  *   interleaved 3-component input : extension, defined by composition (deinterleave, then
  *       the pinned single-plane forward per component).
  *
@@ -37,15 +39,20 @@ extern "C" {
 #endif
 
 enum { SDCT_O_LAYOUT_A = 0, SDCT_O_LAYOUT_B = 1, SDCT_O_LAYOUT_C = 2 };
-enum { SDCT_O_MODE_EXACT = 0, SDCT_O_MODE_FAST = 1 };
+enum { SDCT_O_MODE_EXACT = 0, SDCT_O_MODE_FAST = 1, SDCT_O_MODE_TENSOR = 2 };
 enum { SDCT_O_QUIRK_NONE = 0, SDCT_O_QUIRK_AVX_X3 = 1 };
-enum { SDCT_O_TAB_SCALAR = 0, SDCT_O_TAB_AVX = 1, SDCT_O_TAB_FAST = 2, SDCT_O_TAB_INVERSE = 3 };
+enum { SDCT_O_TAB_SCALAR = 0, SDCT_O_TAB_AVX = 1, SDCT_O_TAB_FAST = 2, SDCT_O_TAB_INVERSE = 3, SDCT_O_TAB_TENSOR = 4 };
 
 /* 8-point kernels --------------------------------------------------------------------- */
 void sdct_oracle_dct8_scalar(float v[8]);                 /* src/simd_dct.cpp:138-172 */
 void sdct_oracle_dct8_paired(float v[8], int quirk_x3);   /* src/simd_dct.cpp:2160-2183 */
 void sdct_oracle_dct8_fast(float v[8]);                   /* this repo: FMA form, unnormalised */
 void sdct_oracle_idct8(float v[8]);                       /* this repo, unnormalised */
+
+/* mode TENSOR (this repo): the integer matrix K[c*64+p] = round(2^22 C[u][y] C[v][x]), c = u*8+v,
+ * p = y*8+x, of the tensor-core form (simd_dct_b200/csrc/sdct_tc.cu); its two digits are
+ * hi = floor((K + 512) / 1024), lo = K - 1024 hi */
+void sdct_oracle_tensor_matrix(int32_t K[64 * 64]);
 
 /* quantiser / dequantiser scale tables (64 floats) derived from the caller's LUT */
 void sdct_oracle_tables(const float lut[64], int layout, float out[64], int which);

@@ -10,7 +10,7 @@ LIB_PATH = os.path.join(HERE, "libsdct.so")
 
 OK, INVALID_PARAMETER, NOT_SUPPORTED, CUDA_ERROR, NO_DEVICE = range(5)
 LAYOUT_A, LAYOUT_B, LAYOUT_C = 0, 1, 2
-EXACT, FAST, QUIRK_AVX_X3 = 0, 1, 2
+EXACT, FAST, QUIRK_AVX_X3, TENSOR = 0, 1, 2, 4
 
 
 class Job(C.Structure):
@@ -40,6 +40,7 @@ SYMBOLS = {
     "sdct_forward_host": (C.c_int, [_vp, _JP, _vp, _fp, _vp]),
     "sdct_inverse_host": (C.c_int, [_vp, _JP, _vp, _fp, _vp]),
     "sdct_selftest_dct8": (C.c_int, [_vp, C.c_int, _fp, _sz]),
+    "sdct_tensor_matrix": (None, [C.POINTER(C.c_int32)]),
     "sdct_synchronize": (C.c_int, [_vp]),
     "sdct_host_alloc": (_vp, [_sz]),
     "sdct_host_free": (None, [_vp]),

@@ -54,6 +54,23 @@ namespace {
 
 // scale tables, in float exactly as the reference builds them (EXACT) or as oracle/sdct_oracle.c
 // defines them (FAST, inverse); every value is duplicated for the two packed lanes of the kernels
+// tensor-core form: tab[j] = quantiser scale of D column j with 2^-22 (the matrix scaling) folded in
+int build_tc_tables(const sdct_job *j, const float *lut, float2 tab[64])
+{
+    if (!lut) return fail(SDCT_INVALID_PARAMETER, "quantisation LUT is null");
+    const bool lb = j->layout == SDCT_LAYOUT_B;
+    for (int c = 0; c < 64; c++) {
+        const int pos = sdct_tc_column_position(j->layout, c);
+        const float d = lut[pos] * 0.95f;                                   // vr, src/simd_dct.cpp:191
+        const float f = std::ldexp(lb ? 255.0f / d : 1.f / d, -22);         // :2236-2239 / :194-212 (x255 and /255 cancel)
+        // |t| <= 255 * 64 * 2^20 < 2^34
+        if (!std::isfinite(f) || std::fabs(f) * 17179869184.f >= 2147483648.f)
+            return fail(SDCT_INVALID_PARAMETER, "LUT entry %d (%g) gives an unusable scale", pos, (double)lut[pos]);
+        tab[c] = make_float2(f, f);
+    }
+    return SDCT_OK;
+}
+
 int build_tables(const sdct_job *j, const float *lut, int op, float2 tab[64], float2 tab2[64], float2 off[64])
 {
     if (!lut) return fail(SDCT_INVALID_PARAMETER, "quantisation LUT is null");
@@ -93,7 +110,10 @@ int run_device(sdct_context *ctx, int op, const sdct_job *j, const uint8_t *pixe
         return fail(SDCT_INVALID_PARAMETER, "null buffer");
     KParams p;
     memset(&p, 0, sizeof(p));
-    rc = build_tables(j, lut, op, p.tab, p.tab2, p.off);
+    const bool tensor = (j->flags & SDCT_TENSOR) != 0;
+    if (tensor && op != SDCT_K_OP_FORWARD) return fail(SDCT_NOT_SUPPORTED, "SDCT_TENSOR is implemented for the forward transform only");
+    if (tensor && (j->flags & (SDCT_FAST | SDCT_QUIRK_AVX_X3))) return fail(SDCT_INVALID_PARAMETER, "SDCT_TENSOR excludes SDCT_FAST and SDCT_QUIRK_AVX_X3");
+    rc = tensor ? build_tc_tables(j, lut, p.tab) : build_tables(j, lut, op, p.tab, p.tab2, p.off);
     if (rc) return rc;
     p.pixels = pixels; p.coefs = coefs; p.pixels_out = pixels_out;
     p.pitch = j->pitch; p.eye_stride = j->eye_stride; p.pixel_frame_stride = j->pixel_frame_stride;
@@ -119,7 +139,12 @@ int run_device(sdct_context *ctx, int op, const sdct_job *j, const uint8_t *pixe
     CU_TRY(cudaSetDevice(ctx->device));
     const int mode = (j->flags & SDCT_FAST) ? SDCT_K_FAST : SDCT_K_EXACT;
     const int x3 = (j->flags & SDCT_QUIRK_AVX_X3) ? 1 : 0;
-    CU_TRY(sdct_k_launch(op, j->layout, mode, x3, &p, stream ? stream : ctx->stream));
+    if (tensor) {
+        p.tc_matrix = ctx->d_tc_matrix[j->layout == SDCT_LAYOUT_A ? 0 : 1];
+        CU_TRY(sdct_k_launch_tc(op, j->layout, &p, stream ? stream : ctx->stream));
+    } else {
+        CU_TRY(sdct_k_launch(op, j->layout, mode, x3, &p, stream ? stream : ctx->stream));
+    }
     ctx->launches.fetch_add(1, std::memory_order_relaxed);
     return SDCT_OK;
 }
@@ -175,6 +200,15 @@ int sdct_create(int device, sdct_context **out)
         CU_TRY(cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking));
         CU_TRY(cudaEventCreateWithFlags(&s.done, cudaEventDisableTiming));
     }
+    {   // tensor-core B operands (16 KiB each)
+        static uint16_t op[128 * 64];
+        const int layouts[2] = {SDCT_K_LAYOUT_A, SDCT_K_LAYOUT_B};
+        for (int i = 0; i < 2; i++) {
+            sdct_tc_operand(layouts[i], op);
+            CU_TRY(cudaMalloc(&c->d_tc_matrix[i], sizeof(op)));
+            CU_TRY(cudaMemcpy(c->d_tc_matrix[i], op, sizeof(op), cudaMemcpyHostToDevice));
+        }
+    }
     *out = c;
     return SDCT_OK;
 }
@@ -190,6 +224,7 @@ void sdct_destroy(sdct_context *c)
         cudaFreeHost(s.h_in); cudaFreeHost(s.h_out);
     }
     if (c->stream) { cudaStreamSynchronize(c->stream); cudaStreamDestroy(c->stream); }
+    cudaFree(c->d_tc_matrix[0]); cudaFree(c->d_tc_matrix[1]);
     delete c;
 }
 
@@ -219,6 +254,8 @@ int sdct_roundtrip_device(sdct_context *c, const sdct_job *j, const void *d_in, 
 {
     return run_device(c, SDCT_K_OP_ROUNDTRIP, j, (const uint8_t *)d_in, nullptr, (uint8_t *)d_out, lut, (cudaStream_t)stream);
 }
+
+void sdct_tensor_matrix(int32_t *k4096) { if (k4096) sdct_tc_integer_matrix(k4096); }
 
 int sdct_selftest_dct8(sdct_context *c, int kind, float *h_data, size_t n)
 {

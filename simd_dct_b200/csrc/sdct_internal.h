@@ -37,9 +37,15 @@ struct sdct_context {
     Slot slots[kSlots];
     std::atomic<uint64_t> launches{0};
     std::mutex host_mu;  // the host pipeline owns the slots
+    void *d_tc_matrix[2] = {nullptr, nullptr};  // tensor-core B operand: [0] layout-A column order, [1] natural order
 };
 
 struct Geometry {
     uint32_t bpr, bands_total, band_begin, band_end, eyes, comps;
 };
 int sdct_validate(const sdct_job *j, Geometry *g);
+
+// tensor-core form: K[c][p] = round(2^22 * C[u][y] * C[v][x]), c = u*8+v, p = y*8+x (sdct_tc_matrix.cpp)
+void sdct_tc_integer_matrix(int32_t K[64 * 64]);
+// the 16 KiB B operand for `layout`: fp16 digits of K in the UMMA canonical K-major layout
+void sdct_tc_operand(int layout, uint16_t out[128 * 64]);

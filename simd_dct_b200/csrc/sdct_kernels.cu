@@ -12,6 +12,7 @@
 //   layout  A   : P, Q = blocks t, t+128 (a block's 64 bytes are contiguous; bank-friendly slots)
 #include "sdct_kernels.h"
 #include "sdct_math.cuh"
+#include "sdct_io.cuh"
 
 // This file is compiled once per SDCT_PART (simd_dct_b200/build.py) so that the template
 // instantiations build in parallel: part 0 = dispatcher + self-test kernel, parts 1..8 = one
@@ -32,29 +33,6 @@ constexpr int C_PITCH = CB;              // layout C: 64 rows of CB bytes
 constexpr int STAGE_BYTES = 32 * B_GROUP_PITCH > CB * A_SLOT ? 32 * B_GROUP_PITCH : CB * A_SLOT;
 
 constexpr int IN_STAGE_BYTES = 8 * TB * 16;   // prefetched pixels of one tile: 8 rows x 128 threads x (P 8 B | Q 8 B)
-
-// one tile = the CB consecutive blocks [n0, n0 + count) of one coefficient set; CTA-uniform
-struct Tile {
-    const uint8_t *pix;     // pixel base of the frame
-    uint8_t *coef;          // start of the coefficient set of (frame, comp)
-    uint32_t comp;
-    uint32_t n0;            // first n_local of this tile
-    uint32_t count;         // valid blocks in this tile
-};
-
-SDCT_DEV Tile tile_info(const KParams &p, uint32_t tile)
-{
-    Tile t;
-    const uint32_t chunk = tile % p.chunks;
-    const uint32_t fc = tile / p.chunks;
-    t.comp = fc % p.comps;
-    const uint32_t frame = fc / p.comps;
-    t.n0 = chunk * CB;
-    t.count = min((uint32_t)CB, p.rows * p.bpr - t.n0);
-    t.pix = p.pixels + (uint64_t)frame * p.pixel_frame_stride;
-    t.coef = p.coefs + (uint64_t)frame * p.coef_frame_stride + (uint64_t)t.comp * p.coef_comp_stride;
-    return t;
-}
 
 // this thread's two blocks of a tile: P, Q = slots 2t, 2t+1 (layouts B, C) or t, t+128 (layout A)
 struct BlockPos {
@@ -117,53 +95,6 @@ SDCT_DEV void read_prefetched(const uint8_t *stage, uint32_t wp[16], uint32_t wq
     for (int r = 0; r < 8; r++) {
         const uint4 v = *reinterpret_cast<const uint4 *>(slot + r * (TB * 16));
         wp[2 * r] = v.x; wp[2 * r + 1] = v.y; wq[2 * r] = v.z; wq[2 * r + 1] = v.w;
-    }
-}
-
-// ---- pixel block -> 16 words (row r = words 2r, 2r+1), component extraction fused ----------------
-// VEC: 0 = byte loads, 1 = 8-byte loads, 2 = one 16-byte load per row for the adjacent pair (P, Q)
-template <int COMPS, int VEC>
-SDCT_DEV void load_block(const uint8_t *px, uint64_t pitch, uint32_t comp, uint32_t w[16])
-{
-    if (COMPS == 1) {
-#pragma unroll
-        for (int r = 0; r < 8; r++) {
-            if (VEC) {
-                const uint2 v = __ldg(reinterpret_cast<const uint2 *>(px + r * pitch));
-                w[2 * r] = v.x; w[2 * r + 1] = v.y;
-            } else {
-                uint32_t lo = 0, hi = 0;
-#pragma unroll
-                for (int c = 0; c < 4; c++) {
-                    lo |= (uint32_t)__ldg(px + r * pitch + c) << (8 * c);
-                    hi |= (uint32_t)__ldg(px + r * pitch + 4 + c) << (8 * c);
-                }
-                w[2 * r] = lo; w[2 * r + 1] = hi;
-            }
-        }
-    } else {
-        // 8 interleaved pixels = 24 bytes; component k sits at bytes k, k+3, ..., k+21.
-        // Two PRMTs per output word; the selectors repeat every 12 bytes (= 3 words).
-        const uint32_t selT = comp == 0 ? 0x0630u : (comp == 1 ? 0x0741u : 0x0052u);
-        const uint32_t selU = comp == 0 ? 0x5210u : (comp == 1 ? 0x6210u : 0x7410u);
-#pragma unroll
-        for (int r = 0; r < 8; r++) {
-            uint32_t s[6];
-            if (VEC) {
-                const uint2 *q = reinterpret_cast<const uint2 *>(px + r * pitch);
-                const uint2 a = __ldg(q), b = __ldg(q + 1), c = __ldg(q + 2);
-                s[0] = a.x; s[1] = a.y; s[2] = b.x; s[3] = b.y; s[4] = c.x; s[5] = c.y;
-            } else {
-#pragma unroll
-                for (int k = 0; k < 6; k++) {
-                    s[k] = 0;
-#pragma unroll
-                    for (int c = 0; c < 4; c++) s[k] |= (uint32_t)__ldg(px + r * pitch + 4 * k + c) << (8 * c);
-                }
-            }
-            w[2 * r] = __byte_perm(__byte_perm(s[0], s[1], selT), s[2], selU);
-            w[2 * r + 1] = __byte_perm(__byte_perm(s[3], s[4], selT), s[5], selU);
-        }
     }
 }
 
@@ -322,15 +253,15 @@ __global__ void __launch_bounds__(SDCT_TB, 3) forward_kernel(const __grid_consta
     uint8_t *stage_in = smem + 2 * STAGE_BYTES;
     uint32_t tile = blockIdx.x;
     if (PF) {
-        if (tile < p.tiles) prefetch_pair<VEC>(stage_in, locate<LAYOUT>(p, tile_info(p, tile)), p.pitch);
+        if (tile < p.tiles) prefetch_pair<VEC>(stage_in, locate<LAYOUT>(p, tile_info<CB>(p, tile)), p.pitch);
         cp_async_commit();
     }
     for (uint32_t it = 0; tile < p.tiles; it++, tile += gridDim.x) {
-        const Tile t = tile_info(p, tile);
+        const Tile t = tile_info<CB>(p, tile);
         uint32_t wp[16], wq[16];
         if (PF) {
             const uint32_t next = tile + gridDim.x;
-            if (next < p.tiles) prefetch_pair<VEC>(stage_in + ((it + 1) & 1) * IN_STAGE_BYTES, locate<LAYOUT>(p, tile_info(p, next)), p.pitch);
+            if (next < p.tiles) prefetch_pair<VEC>(stage_in + ((it + 1) & 1) * IN_STAGE_BYTES, locate<LAYOUT>(p, tile_info<CB>(p, next)), p.pitch);
             cp_async_commit();
             cp_async_wait<1>();
             read_prefetched(stage_in + (it & 1) * IN_STAGE_BYTES, wp, wq);
@@ -475,7 +406,7 @@ __global__ void __launch_bounds__(SDCT_TB, 3) inverse_kernel(const __grid_consta
 {
     extern __shared__ __align__(16) uint8_t smem[];
     for (uint32_t tile = blockIdx.x, it = 0; tile < p.tiles; it++, tile += gridDim.x) {
-        const Tile t = tile_info(p, tile);
+        const Tile t = tile_info<CB>(p, tile);
         uint8_t *sm = smem + (it & 1) * STAGE_BYTES;
         fetch_coefs<LAYOUT>(sm, p, t);
         __syncthreads();
@@ -495,15 +426,15 @@ __global__ void __launch_bounds__(SDCT_TB, 3) roundtrip_kernel(const __grid_cons
     uint8_t *stage_in = smem;
     uint32_t tile = blockIdx.x;
     if (PF) {
-        if (tile < p.tiles) prefetch_pair<VEC>(stage_in, locate<LAYOUT>(p, tile_info(p, tile)), p.pitch);
+        if (tile < p.tiles) prefetch_pair<VEC>(stage_in, locate<LAYOUT>(p, tile_info<CB>(p, tile)), p.pitch);
         cp_async_commit();
     }
     for (uint32_t it = 0; tile < p.tiles; it++, tile += gridDim.x) {
-        const Tile t = tile_info(p, tile);
+        const Tile t = tile_info<CB>(p, tile);
         uint32_t wp[16], wq[16];
         if (PF) {
             const uint32_t next = tile + gridDim.x;
-            if (next < p.tiles) prefetch_pair<VEC>(stage_in + ((it + 1) & 1) * IN_STAGE_BYTES, locate<LAYOUT>(p, tile_info(p, next)), p.pitch);
+            if (next < p.tiles) prefetch_pair<VEC>(stage_in + ((it + 1) & 1) * IN_STAGE_BYTES, locate<LAYOUT>(p, tile_info<CB>(p, next)), p.pitch);
             cp_async_commit();
             cp_async_wait<1>();
             read_prefetched(stage_in + (it & 1) * IN_STAGE_BYTES, wp, wq);

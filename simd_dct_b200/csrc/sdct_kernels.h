@@ -6,12 +6,14 @@
 
 #define SDCT_TB 128          // threads per CTA
 #define SDCT_CTA_BLOCKS 256  // 8x8 blocks per CTA (two per thread)
+#define SDCT_TC_TILE 128     // tensor-core kernels: 8x8 blocks per tile (one per TMEM lane)
 
 #define SDCT_K_LAYOUT_A 0
 #define SDCT_K_LAYOUT_B 1
 #define SDCT_K_LAYOUT_C 2
 #define SDCT_K_EXACT 0
 #define SDCT_K_FAST 1
+#define SDCT_K_TENSOR 2
 #define SDCT_K_OP_FORWARD 0
 #define SDCT_K_OP_INVERSE 1
 #define SDCT_K_OP_ROUNDTRIP 2
@@ -37,8 +39,16 @@ struct KParams {
     float2 tab[64];           // forward: quantiser scale; inverse: dequantiser scale
     float2 tab2[64];          // roundtrip: dequantiser scale
     float2 off[64];           // inverse / roundtrip: -127 * dequantiser scale
+    const void *tc_matrix;    // tensor-core kernels: the 16 KiB B operand (fp16 digits of 2^22 C(x)C, UMMA canonical layout)
 };
 
 extern "C" cudaError_t sdct_k_launch(int op, int layout, int mode, int x3, const KParams *p, cudaStream_t s);
+// tensor-core form (sdct_tc.cu); p->tab holds the folded scales in D-column order
+extern "C" cudaError_t sdct_k_launch_tc(int op, int layout, const KParams *p, cudaStream_t s);
+// D column j of the tensor-core kernels -> coefficient position in the layout's own index order
+static inline int sdct_tc_column_position(int layout, int j)
+{
+    return layout == SDCT_K_LAYOUT_A ? 16 * ((j & 7) >> 1) + 2 * (j >> 3) + (j & 1) : j;
+}
 // the 8-point kernels on n raw 8-float vectors (device memory, in place); see dct8_selftest_kernel
 extern "C" cudaError_t sdct_k_selftest(float *d_data, uint32_t n, int kind, cudaStream_t s);

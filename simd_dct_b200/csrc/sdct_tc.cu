@@ -1,0 +1,387 @@
+// sdct_tc.cu - tensor-core (tcgen05 / TMEM) form of the 8x8 block transform for sm_100a.
+//
+// The 2-D DCT of a block is one matrix product, vec(Y) = (C (x) C) vec(X).  ncu shows the fp32
+// butterfly kernels are bound by the FMA pipe, not by HBM, so this file
+// moves the arithmetic to the 5th-generation tensor cores, in an error-free integer form:
+//
+//   * a tile = 128 consecutive blocks; block m of the tile is row m of the A operand: its 64
+//     pixels converted to fp16 (exact) and written by the owning thread straight into TENSOR
+//     MEMORY with tcgen05.st (A never touches shared memory);
+//   * the B operand is the 64x64 matrix K = round(2^22 * C (x) C) split into two fp16 "digits"
+//     K = 1024*K1 + K0 (|K1| <= 985, |K0| <= 512: exact in fp16), 128 rows x 64 columns,
+//     resident in shared memory in the canonical K-major no-swizzle UMMA layout;
+//   * tcgen05.mma.kind::f16 (M=128, N=128, K=16, x4) accumulates D1 = X*K1^T and D0 = X*K0^T in
+//     fp32 in TMEM.  Every product and every partial sum is an integer below 2^24, so the fp32
+//     accumulation is exact whatever the hardware's summation order: the result is restated
+//     bit for bit on the CPU (oracle/sdct_oracle.c, mode TENSOR);
+//   * epilogue: tcgen05.ld (16x256b: a thread receives 16 coefficients of two adjacent blocks),
+//     t = fma(D1, 1024, D0), one multiply by the folded quantiser scale, the denormal-FMA
+//     rounding + saturating pack of sdct_math.cuh, then the layout's store path.
+//
+// One CTA per SM, three warpgroups; each warpgroup walks its own tiles and owns 160 TMEM columns
+// (32 for A, 128 for D), a named barrier and an mbarrier, so the MMA of one warpgroup runs under
+// the epilogues of the other two.
+#include "sdct_io.cuh"
+
+namespace sdct {
+namespace tc {
+
+constexpr int WGS = 3;                      // warpgroups per CTA
+constexpr int THREADS = 128 * WGS;
+constexpr int TILE = SDCT_TC_TILE;          // blocks per tile = TMEM lanes
+constexpr int A_COLS = 32;                  // 64 fp16 per lane
+constexpr int D_COLS = 128;                 // hi digit: columns 0..63, lo digit: 64..127
+constexpr int WG_COLS = A_COLS + D_COLS;    // 160
+constexpr int TMEM_COLS = 512;
+
+constexpr int B_BYTES = 128 * 64 * 2;       // 16 KiB: N = 128 rows x K = 64 fp16
+constexpr int B_LBO = 128 * 16;             // bytes between the 16-byte K chunks of a row group: 2048
+constexpr int B_SBO = 128;                  // bytes between 8-row groups (core matrices are contiguous)
+
+// staging image of one warpgroup's 128 blocks (layouts B and C)
+constexpr int IMG_B_PITCH = 528;            // 512 B group + 16 B pad
+constexpr int IMG_C_PITCH = TILE + 16;      // plane row of 128 bytes + pad
+constexpr int IMG_BYTES = 64 * IMG_C_PITCH > 16 * IMG_B_PITCH ? 64 * IMG_C_PITCH : 16 * IMG_B_PITCH;
+
+constexpr int SMEM_B_OFF = 0;
+constexpr int SMEM_IMG_OFF = B_BYTES;
+constexpr int SMEM_BAR_OFF = SMEM_IMG_OFF + WGS * IMG_BYTES;     // WGS mbarriers (8 B) + tmem base (4 B)
+constexpr int SMEM_USED = SMEM_BAR_OFF + 64;
+// more than half of the SM's shared memory: exactly one CTA per SM (it allocates all of TMEM)
+constexpr int SMEM_BYTES = SMEM_USED > 120 * 1024 ? SMEM_USED : 120 * 1024;
+
+// ---- PTX wrappers ------------------------------------------------------------------------------
+SDCT_DEV uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+SDCT_DEV void tmem_alloc(uint32_t *slot_in_smem)
+{
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(slot_in_smem)), "n"(TMEM_COLS) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+SDCT_DEV void tmem_dealloc(uint32_t base)
+{
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(base), "n"(TMEM_COLS) : "memory");
+}
+SDCT_DEV void fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+SDCT_DEV void fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+SDCT_DEV void wg_barrier(int wg) { asm volatile("bar.sync %0, 128;" ::"r"(wg + 1) : "memory"); }
+
+SDCT_DEV void mbar_init(uint64_t *bar, uint32_t count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+SDCT_DEV void mbar_wait(uint64_t *bar, uint32_t parity)
+{
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "WAIT_%=:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+        "@p bra DONE_%=;\n\t"
+        "bra WAIT_%=;\n\t"
+        "DONE_%=:\n\t}" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+// completion of all previously issued tcgen05.mma of this thread -> one arrival on the mbarrier
+SDCT_DEV void mma_commit(uint64_t *bar)
+{
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+
+// D[tmem] (+)= A[tmem] * B[smem]^T, kind::f16, fp32 accumulate
+SDCT_DEV void mma_f16_ts(uint32_t d_tmem, uint32_t a_tmem, uint64_t b_desc, uint32_t idesc, uint32_t accumulate)
+{
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}" ::"r"(d_tmem), "r"(a_tmem), "l"(b_desc), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+
+// shared-memory matrix descriptor: K-major, no swizzle (cute::UMMA::SmemDescriptor, version 1)
+SDCT_DEV uint64_t b_descriptor(uint32_t smem_addr)
+{
+    uint64_t d = 0;
+    d |= (uint64_t)((smem_addr >> 4) & 0x3fff);
+    d |= (uint64_t)((B_LBO >> 4) & 0x3fff) << 16;
+    d |= (uint64_t)((B_SBO >> 4) & 0x3fff) << 32;
+    d |= (uint64_t)1 << 46;   // descriptor version (Blackwell)
+    return d;                 // base offset 0, layout type 0 = no swizzle
+}
+
+// instruction descriptor (cute::UMMA::InstrDescriptor): D = F32, A = B = F16, both K-major, M = 128, N = 128
+constexpr uint32_t IDESC = (1u << 4) | ((uint32_t)(D_COLS >> 3) << 17) | ((uint32_t)(TILE >> 4) << 24);
+
+SDCT_DEV void tmem_st32(uint32_t taddr, const uint32_t (&r)[32])
+{
+    asm volatile(
+        "tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, "
+        "%17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31, %32};" ::"r"(taddr),
+        "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]), "r"(r[8]), "r"(r[9]), "r"(r[10]),
+        "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15]), "r"(r[16]), "r"(r[17]), "r"(r[18]), "r"(r[19]), "r"(r[20]),
+        "r"(r[21]), "r"(r[22]), "r"(r[23]), "r"(r[24]), "r"(r[25]), "r"(r[26]), "r"(r[27]), "r"(r[28]), "r"(r[29]), "r"(r[30]),
+        "r"(r[31])
+        : "memory");
+}
+SDCT_DEV void tmem_wait_st() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+SDCT_DEV void tmem_wait_ld() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+
+// 16 lanes x 64 columns: thread (g = lane/4, q = lane%4) receives, for k = 0..7,
+//   r[4k], r[4k+1] = TMEM lane g,     columns 8k + 2q, 8k + 2q + 1
+//   r[4k+2], r[4k+3] = TMEM lane g + 8, same columns
+SDCT_DEV void tmem_ld_16x256b_x8(uint32_t taddr, float (&r)[32])
+{
+    asm volatile(
+        "tcgen05.ld.sync.aligned.16x256b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+        : "=f"(r[0]), "=f"(r[1]), "=f"(r[2]), "=f"(r[3]), "=f"(r[4]), "=f"(r[5]), "=f"(r[6]), "=f"(r[7]), "=f"(r[8]), "=f"(r[9]),
+          "=f"(r[10]), "=f"(r[11]), "=f"(r[12]), "=f"(r[13]), "=f"(r[14]), "=f"(r[15]), "=f"(r[16]), "=f"(r[17]), "=f"(r[18]),
+          "=f"(r[19]), "=f"(r[20]), "=f"(r[21]), "=f"(r[22]), "=f"(r[23]), "=f"(r[24]), "=f"(r[25]), "=f"(r[26]), "=f"(r[27]),
+          "=f"(r[28]), "=f"(r[29]), "=f"(r[30]), "=f"(r[31])
+        : "r"(taddr)
+        : "memory");
+}
+
+// ---- u8 -> fp16 (exact): 0x6400 | b = 1024 + b, minus 1024 ---------------------------------------
+SDCT_DEV uint32_t sub1024_h2(uint32_t h)
+{
+    uint32_t d;
+    asm("sub.rn.f16x2 %0, %1, %2;" : "=r"(d) : "r"(h), "r"(0x64006400u));
+    return d;
+}
+SDCT_DEV void bytes_to_half(const uint32_t (&w)[16], uint32_t (&h)[32])
+{
+#pragma unroll
+    for (int i = 0; i < 16; i++) {
+        h[2 * i] = sub1024_h2(__byte_perm(w[i], 0x64646464u, 0x5140));      // pixels 4i, 4i+1
+        h[2 * i + 1] = sub1024_h2(__byte_perm(w[i], 0x64646464u, 0x5342));  // pixels 4i+2, 4i+3
+    }
+}
+
+// ---- block <-> thread mapping -----------------------------------------------------------------------
+// TMEM lane L (= thread index inside the warpgroup) holds block slot(L) of the tile, chosen so that
+// the two lanes one 16x256b load hands to a thread (g, g + 8) are adjacent blocks.
+SDCT_DEV uint32_t slot_of_lane(uint32_t L) { return (L & ~15u) | ((L & 7u) << 1) | ((L >> 3) & 1u); }
+
+SDCT_DEV const uint8_t *block_pixels(const KParams &p, const Tile &t, uint32_t slot)
+{
+    const uint32_t nl = t.n0 + (slot < t.count ? slot : 0);  // keep addresses in range
+    const uint32_t r = nl / p.bpr;
+    const uint32_t bx = nl - r * p.bpr;
+    const uint32_t row = r + p.row0;
+    const uint32_t band = p.eyes == 2 ? row >> 1 : row, eye = p.eyes == 2 ? row & 1 : 0;
+    return t.pix + (uint64_t)eye * p.eye_stride + (uint64_t)band * 8 * p.pitch + (uint64_t)bx * 8 * p.comps;
+}
+
+// D column j of a thread's share -> coefficient position in the layout's own index order
+//   layouts B, C: position = natural index u*8+v = j
+//   layout A    : the 16 columns a thread receives (8k + 2q + e) are the 16 contiguous output bytes
+//                 16q + 2k + e of the block (position = v*8+u)
+template <int LAYOUT>
+__host__ __device__ constexpr int column_position(int j)
+{
+    return LAYOUT == SDCT_K_LAYOUT_A ? 16 * ((j & 7) >> 1) + 2 * (j >> 3) + (j & 1) : j;
+}
+
+template <int LAYOUT, int COMPS, int VEC>
+__global__ void __launch_bounds__(THREADS, 1) forward_tc_kernel(const __grid_constant__ KParams p)
+{
+    extern __shared__ __align__(128) uint8_t smem[];
+    const uint32_t wg = threadIdx.x >> 7, L = threadIdx.x & 127, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    uint64_t *bars = reinterpret_cast<uint64_t *>(smem + SMEM_BAR_OFF);
+    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(smem + SMEM_BAR_OFF + 32);
+
+    // B operand -> shared memory (prepared on the host in the canonical layout), barriers, TMEM
+    {
+        const uint4 *src = reinterpret_cast<const uint4 *>(p.tc_matrix);
+        uint4 *dst = reinterpret_cast<uint4 *>(smem + SMEM_B_OFF);
+        for (int i = threadIdx.x; i < B_BYTES / 16; i += THREADS) dst[i] = __ldg(src + i);
+    }
+    if (threadIdx.x == 0) {
+        for (int i = 0; i < WGS; i++) mbar_init(bars + i, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 0) tmem_alloc(tmem_slot);
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // B is read by the tensor core (async proxy)
+    fence_before();
+    __syncthreads();
+    fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+    const uint32_t lane_field = ((warp & 3u) * 32u) << 16;
+    const uint32_t tA = tmem_base + wg * WG_COLS, tD = tA + A_COLS;
+    const uint64_t bdesc = b_descriptor(smem_u32(smem + SMEM_B_OFF));
+    uint8_t *img = smem + SMEM_IMG_OFF + wg * IMG_BYTES;
+
+    // this thread's 16 scales: columns 8k + 2q + e of the table (in column order)
+    const uint32_t g = lane >> 2, q = lane & 3;
+    F2 scale[8];
+#pragma unroll
+    for (int k = 0; k < 8; k++) scale[k] = make_float2(p.tab[8 * k + 2 * q].x, p.tab[8 * k + 2 * q + 1].x);
+
+    const uint32_t stride = gridDim.x * WGS;
+    uint32_t tile = blockIdx.x * WGS + wg;
+    uint32_t w[16];
+    const uint32_t my_slot = slot_of_lane(L);
+    if (tile < p.tiles) {
+        const Tile t = tile_info<TILE>(p, tile);
+        load_block<COMPS, VEC>(block_pixels(p, t, my_slot), p.pitch, t.comp, w);
+    }
+    uint32_t parity = 0;
+    for (; tile < p.tiles; tile += stride) {
+        const Tile t = tile_info<TILE>(p, tile);
+        {
+            uint32_t h[32];
+            bytes_to_half(w, h);
+            tmem_st32(tA + lane_field, h);
+        }
+        tmem_wait_st();
+        fence_before();
+        wg_barrier(wg);
+        if (tile + stride < p.tiles) {  // prefetch the next tile's pixels into registers
+            const Tile tn = tile_info<TILE>(p, tile + stride);
+            load_block<COMPS, VEC>(block_pixels(p, tn, my_slot), p.pitch, tn.comp, w);
+        }
+        if (L == 0) {
+            fence_after();
+#pragma unroll
+            for (int ks = 0; ks < 4; ks++)   // K = 16 pixels per instruction: 8 TMEM columns of A, 2 K-chunks of B
+                mma_f16_ts(tD, tA + 8 * ks, bdesc + (uint64_t)((2 * ks * B_LBO) >> 4), IDESC, ks);
+            mma_commit(bars + wg);
+        }
+        mbar_wait(bars + wg, parity);
+        parity ^= 1;
+        fence_after();
+
+        const uint64_t n_first = (uint64_t)p.row0 * p.bpr + t.n0;
+#pragma unroll
+        for (int half = 0; half < 2; half++) {
+            float hi[32], lo[32];
+            const uint32_t ta = tD + lane_field + ((uint32_t)(16 * half) << 16);
+            tmem_ld_16x256b_x8(ta, hi);
+            tmem_ld_16x256b_x8(ta + 64, lo);
+            tmem_wait_ld();
+            // blocks P, Q = slots sp, sp + 1 of the tile
+            const uint32_t sp = (warp & 3u) * 32u + 16u * half + 2u * g;
+            F2 bp[8], bq[8];   // level bit patterns of columns (8k+2q, 8k+2q+1) for P and Q
+#pragma unroll
+            for (int k = 0; k < 8; k++) {
+                const F2 tp = fma2(make_float2(hi[4 * k], hi[4 * k + 1]), splat(1024.f), make_float2(lo[4 * k], lo[4 * k + 1]));
+                const F2 tq = fma2(make_float2(hi[4 * k + 2], hi[4 * k + 3]), splat(1024.f), make_float2(lo[4 * k + 2], lo[4 * k + 3]));
+                bp[k] = quant_rne_c(tp, scale[k]);
+                bq[k] = quant_rne_c(tq, scale[k]);
+            }
+            if (LAYOUT == SDCT_K_LAYOUT_A) {
+                // 16 contiguous output bytes 16q .. 16q+15 of each block: bytes 2k, 2k+1 = columns (8k+2q, +1)
+                uint4 vp, vq;
+                vp.x = ~pack4_sat(bp[0].x, bp[0].y, bp[1].x, bp[1].y); vp.y = ~pack4_sat(bp[2].x, bp[2].y, bp[3].x, bp[3].y);
+                vp.z = ~pack4_sat(bp[4].x, bp[4].y, bp[5].x, bp[5].y); vp.w = ~pack4_sat(bp[6].x, bp[6].y, bp[7].x, bp[7].y);
+                vq.x = ~pack4_sat(bq[0].x, bq[0].y, bq[1].x, bq[1].y); vq.y = ~pack4_sat(bq[2].x, bq[2].y, bq[3].x, bq[3].y);
+                vq.z = ~pack4_sat(bq[4].x, bq[4].y, bq[5].x, bq[5].y); vq.w = ~pack4_sat(bq[6].x, bq[6].y, bq[7].x, bq[7].y);
+                uint8_t *dst = t.coef + (n_first + sp) * 64 + 16 * q;
+                if (p.coef_aligned16) {
+                    if (sp < t.count) *reinterpret_cast<uint4 *>(dst) = vp;
+                    if (sp + 1 < t.count) *reinterpret_cast<uint4 *>(dst + 64) = vq;
+                } else {
+                    const uint32_t a[4] = {vp.x, vp.y, vp.z, vp.w}, b[4] = {vq.x, vq.y, vq.z, vq.w};
+#pragma unroll
+                    for (int i = 0; i < 16; i++) {
+                        if (sp < t.count) dst[i] = (uint8_t)(a[i >> 2] >> (8 * (i & 3)));
+                        if (sp + 1 < t.count) dst[64 + i] = (uint8_t)(b[i >> 2] >> (8 * (i & 3)));
+                    }
+                }
+            } else {
+                // bytes (P, Q) of one coefficient are adjacent in layouts B and C: 16-bit stores into the image
+#pragma unroll
+                for (int k = 0; k < 8; k++) {
+#pragma unroll
+                    for (int e = 0; e < 2; e++) {
+                        const int i = 8 * k + e;  // + 2q at run time
+                        const uint32_t pq = ~pack_sat(__float_as_uint(e ? bq[k].y : bq[k].x), __float_as_uint(e ? bp[k].y : bp[k].x), 0u);
+                        uint8_t *d = LAYOUT == SDCT_K_LAYOUT_B ? img + (sp >> 3) * IMG_B_PITCH + (i + 2 * q) * 8 + (sp & 7)
+                                                               : img + (i + 2 * q) * IMG_C_PITCH + sp;
+                        *reinterpret_cast<uint16_t *>(d) = (uint16_t)pq;
+                    }
+                }
+            }
+        }
+        fence_before();   // orders this thread's tcgen05.ld before the barrier that releases D and A
+        if (LAYOUT != SDCT_K_LAYOUT_A) {
+            wg_barrier(wg);
+            // image -> global memory, coalesced
+            if (LAYOUT == SDCT_K_LAYOUT_B) {
+                uint8_t *dst = t.coef + n_first * 64;
+                const uint32_t chunks16 = t.count * 4;
+                if (p.coef_aligned16) {
+                    for (uint32_t k = L; k < chunks16; k += 128)
+                        reinterpret_cast<uint4 *>(dst)[k] = *reinterpret_cast<const uint4 *>(img + (k >> 5) * IMG_B_PITCH + (k & 31) * 16);
+                } else {
+                    for (uint32_t k = L; k < chunks16 * 16; k += 128) dst[k] = img[(k >> 9) * IMG_B_PITCH + (k & 511)];
+                }
+            } else {
+                if (p.coef_aligned16 && (t.count & 15) == 0) {
+                    const uint32_t per_row = t.count >> 4;
+                    for (uint32_t k = L; k < 64 * per_row; k += 128) {
+                        const uint32_t i = k / per_row, c = k - i * per_row;
+                        uint8_t *dst = t.coef + (uint64_t)i * p.coef_plane_stride + n_first;
+                        reinterpret_cast<uint4 *>(dst)[c] = *reinterpret_cast<const uint4 *>(img + i * IMG_C_PITCH + c * 16);
+                    }
+                } else {
+                    for (uint32_t k = L; k < 64 * t.count; k += 128) {
+                        const uint32_t i = k / t.count, c = k - i * t.count;
+                        t.coef[(uint64_t)i * p.coef_plane_stride + n_first + c] = img[i * IMG_C_PITCH + c];
+                    }
+                }
+            }
+        }
+    }
+    fence_before();
+    __syncthreads();
+    if (warp == 0) tmem_dealloc(tmem_base);
+}
+
+}  // namespace tc
+}  // namespace sdct
+
+using namespace sdct;
+
+template <int LAYOUT>
+static cudaError_t launch_tc(const KParams &p, unsigned grid, cudaStream_t s)
+{
+#define SDCT_TC_GO(C, V)                                                                                             \
+    do {                                                                                                             \
+        static bool attr_done = false;                                                                               \
+        if (!attr_done) {                                                                                            \
+            cudaError_t e = cudaFuncSetAttribute(tc::forward_tc_kernel<LAYOUT, C, V>, cudaFuncAttributeMaxDynamicSharedMemorySize, tc::SMEM_BYTES); \
+            if (e != cudaSuccess) return e;                                                                          \
+            attr_done = true;                                                                                        \
+        }                                                                                                            \
+        tc::forward_tc_kernel<LAYOUT, C, V><<<grid, tc::THREADS, tc::SMEM_BYTES, s>>>(p);                            \
+        return cudaGetLastError();                                                                                   \
+    } while (0)
+    if (p.comps == 1) {
+        if (p.pixel_vec >= 1) SDCT_TC_GO(1, 1); else SDCT_TC_GO(1, 0);
+    } else {
+        if (p.pixel_vec >= 1) SDCT_TC_GO(3, 1); else SDCT_TC_GO(3, 0);
+    }
+#undef SDCT_TC_GO
+}
+
+extern "C" cudaError_t sdct_k_launch_tc(int op, int layout, const KParams *pp, cudaStream_t s)
+{
+    if (op != SDCT_K_OP_FORWARD) return cudaErrorNotSupported;
+    KParams p = *pp;
+    p.layout = (uint32_t)layout;
+    const unsigned long long blocks = (unsigned long long)p.rows * p.bpr;
+    p.chunks = (uint32_t)((blocks + SDCT_TC_TILE - 1) / SDCT_TC_TILE);
+    const unsigned long long tiles = (unsigned long long)p.chunks * p.comps * p.frames;
+    if (tiles == 0) return cudaSuccess;
+    if (tiles > 0xfffffff0ull) return cudaErrorInvalidConfiguration;
+    p.tiles = (uint32_t)tiles;
+    const unsigned sms = p.sm_count ? p.sm_count : 148u;
+    const unsigned want = (unsigned)((tiles + tc::WGS - 1) / tc::WGS);
+    const unsigned grid = want < sms ? want : sms;
+    switch (layout) {
+    case SDCT_K_LAYOUT_A: return launch_tc<SDCT_K_LAYOUT_A>(p, grid, s);
+    case SDCT_K_LAYOUT_B: return launch_tc<SDCT_K_LAYOUT_B>(p, grid, s);
+    case SDCT_K_LAYOUT_C: return launch_tc<SDCT_K_LAYOUT_C>(p, grid, s);
+    default: return cudaErrorInvalidValue;
+    }
+}

@@ -16,7 +16,7 @@ ORACLE_SO = os.path.join(ROOT, "oracle", "liboracle.so")
 REF_DIR = os.path.join(ROOT, "oracle", "_ref")
 
 LAYOUT_A, LAYOUT_B, LAYOUT_C = 0, 1, 2
-MODE_EXACT, MODE_FAST = 0, 1
+MODE_EXACT, MODE_FAST, MODE_TENSOR = 0, 1, 2
 QUIRK_NONE, QUIRK_AVX_X3 = 0, 1
 TAB_SCALAR, TAB_AVX, TAB_FAST, TAB_INVERSE = 0, 1, 2, 3
 
@@ -97,6 +97,11 @@ class Oracle:
         self.lib.sdct_oracle_inverse(layout, _p8(coef), eyes * h * w // 64, w, h, eyes, h * w, _pf(lut_),
                                      _p8(out), w, 1)
         return out
+
+    def tensor_matrix(self):
+        k = np.zeros(64 * 64, dtype=np.int32)
+        self.lib.sdct_oracle_tensor_matrix(k.ctypes.data_as(C.POINTER(C.c_int32)))
+        return k.reshape(64, 64)
 
     def tables(self, lut_, layout, which):
         out = np.zeros(64, dtype=np.float32)

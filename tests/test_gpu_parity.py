@@ -428,3 +428,38 @@ def test_config5_gigapixel_band_sharded_roundtrip(ctx, oracle):
     assert float(err.float().mean()) < 3.0, (int(err.max()), float(err.float().mean()))
     fused = ctx.roundtrip(img, lut, job)
     assert torch.equal(fused, back)
+
+
+@pytest.mark.parametrize("layout", LAYOUTS)
+def test_tensor_core_forward_is_bit_exact_to_its_cpu_restatement(ctx, oracle, layout):
+    """SDCT_TENSOR (tcgen05.mma + TMEM, sdct_tc.cu): integer-exact matrix form of the true DCT.
+    Byte-identical to oracle mode TENSOR (which proves the fp32 tensor-core accumulation is exact
+    for these bounded integer sums), on aligned, ragged (tail tile), stereo and RGB inputs."""
+    for (h, w, kind, scale) in ((512, 512, "rand", 1), (512, 512, "smooth", 8), (1080 - 1080 % 8, 1920, "rand", 255),
+                                (8, 64, "rand", 8), (24, 192, "smooth", 64), (72, 1088 - 1088 % 64, "rand", 16)):
+        img = make_image(kind, h, w, seed=h + w)
+        lut = ol.lut(scale)
+        got = gpu_forward(ctx, img, lut, layout, sd.TENSOR)
+        want = oracle.forward(layout, img, lut, mode=ol.MODE_TENSOR)
+        assert np.array_equal(got, want), (h, w, kind, scale, np.count_nonzero(got != want))
+    if layout == sd.LAYOUT_C:
+        img = make_image("rand", 2 * 64, 320, seed=9)
+        got = gpu_forward(ctx, img, ol.lut(8), layout, sd.TENSOR, eyes=2)
+        assert np.array_equal(got, oracle.forward(layout, img, ol.lut(8), mode=ol.MODE_TENSOR, eyes=2))
+    rgb = make_image("smooth", 64, 256, seed=4, comps=3)
+    job = sd.dense_job(layout, 256, 64, components=3, flags=sd.TENSOR)
+    got = ctx.forward(dev(rgb), ol.lut(8), job).cpu().numpy().reshape(3, -1)
+    for c in range(3):
+        assert np.array_equal(got[c], oracle.forward(layout, rgb, ol.lut(8), mode=ol.MODE_TENSOR, comp=c))
+    # unaligned base pointer and padded pitch (byte-granular load / store paths)
+    h, w, pitch = 40, 128, 128 + 24
+    buf = np.zeros(h * pitch + 3, dtype=np.uint8)
+    img = make_image("rand", h, w, seed=77)
+    view = buf[3:3 + h * pitch].reshape(h, pitch)
+    view[:, :w] = img
+    d = dev(buf)
+    job = sd.dense_job(layout, w, h, flags=sd.TENSOR)
+    job.pitch = pitch
+    out = torch.zeros(h * w + 1, dtype=torch.uint8, device="cuda")
+    ctx.forward(d[3:], ol.lut(8), job, out=out[1:])
+    assert np.array_equal(out[1:].cpu().numpy(), oracle.forward(layout, img, ol.lut(8), mode=ol.MODE_TENSOR))

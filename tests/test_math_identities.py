@@ -5,6 +5,7 @@ from fractions import Fraction
 import math
 
 import numpy as np
+import pytest
 
 f32 = np.float32
 
@@ -93,3 +94,41 @@ def test_pixel_rounding_by_denormal_multiply():
         w = rn32(F(x) * dmin)
         want = int(min(255, max(0, np.rint(np.float64(x)))))
         assert sat_u8(bits(w)) == want, float(x)
+
+
+def test_tensor_form_matrix_is_exact_and_bounded(oracle):
+    """mode TENSOR (sdct_tc.cu): the library and the oracle build the same integer matrix; its digits are
+    exact in fp16 and every partial sum of 255 * |digit| stays below 2^24, so fp32 accumulation on the
+    tensor cores is exact in any order; K / 2^22 is the true C (x) C to 2^-23."""
+    import ctypes as C
+    from simd_dct_b200 import _lib
+    k_lib = np.zeros(64 * 64, dtype=np.int32)
+    _lib.load().sdct_tensor_matrix(k_lib.ctypes.data_as(C.POINTER(C.c_int32)))
+    k = oracle.tensor_matrix()
+    assert np.array_equal(k_lib.reshape(64, 64), k)
+    hi = (k + 512) >> 10
+    lo = k - 1024 * hi
+    assert np.abs(hi).max() <= 1024 and lo.min() >= -512 and lo.max() <= 511
+    assert 255 * np.abs(hi).sum(axis=1).max() < 2 ** 24 and 255 * np.abs(lo).sum(axis=1).max() < 2 ** 24
+    n = np.arange(8)
+    c = np.cos((2 * n[None, :] + 1) * n[:, None] * np.pi / 16) * 0.5
+    c[0, :] = np.sqrt(1 / 8)
+    true = np.einsum("uy,vx->uvyx", c, c).reshape(64, 64)
+    assert np.abs(k / 2.0 ** 22 - true).max() <= 2.0 ** -23 + 1e-12
+
+
+@pytest.mark.parametrize("layout", [0, 1, 2])
+def test_tensor_mode_stays_within_one_lsb_of_exact(oracle, layout):
+    import oraclelib as ol
+    rng = np.random.default_rng(5)
+    y, x = np.mgrid[0:256, 0:512]
+    smooth = np.clip(128 + 60 * np.sin(.05 * x) + 50 * np.cos(.031 * y) + rng.integers(0, 9, (256, 512)), 0, 255).astype(np.uint8)
+    rand = rng.integers(0, 256, (256, 512), dtype=np.uint8)
+    for img in (smooth, rand):
+        for scale in (1, 8, 255):
+            lut = ol.lut(scale)
+            t = oracle.forward(layout, img, lut, mode=ol.MODE_TENSOR)
+            e = oracle.forward(layout, img, lut)
+            d = np.abs(t.astype(int) - e.astype(int))
+            assert d.max() <= 1
+            assert np.mean(d != 0) <= 2e-3, np.mean(d != 0)
