@@ -18,6 +18,8 @@
 #define SDCT_K_OP_INVERSE 1
 #define SDCT_K_OP_ROUNDTRIP 2
 
+struct KFastDiv { uint32_t m, sh1, sh2; };   // n / d = (t + ((n - t) >> sh1)) >> sh2, t = umulhi(n, m)
+
 struct KParams {
     const uint8_t *pixels;    // forward/roundtrip: input; inverse: output
     uint8_t *coefs;           // forward: output; inverse: input (unused by roundtrip)
@@ -39,6 +41,7 @@ struct KParams {
     float2 tab[64];           // forward: quantiser scale; inverse: dequantiser scale
     float2 tab2[64];          // roundtrip: dequantiser scale
     float2 off[64];           // inverse / roundtrip: -127 * dequantiser scale
+    KFastDiv div_chunks, div_bpr;  // tensor-core kernels
     const void *tc_matrix;    // tensor-core kernels: the 16 KiB B operand (fp16 digits of 2^22 C(x)C, UMMA canonical layout)
 };
 

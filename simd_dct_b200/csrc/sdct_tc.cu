@@ -122,23 +122,6 @@ SDCT_DEV void tmem_st32(uint32_t taddr, const uint32_t (&r)[32])
         : "memory");
 }
 SDCT_DEV void tmem_wait_st() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
-SDCT_DEV void tmem_wait_ld() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
-
-// 16 lanes x 64 columns: thread (g = lane/4, q = lane%4) receives, for k = 0..7,
-//   r[4k], r[4k+1] = TMEM lane g,     columns 8k + 2q, 8k + 2q + 1
-//   r[4k+2], r[4k+3] = TMEM lane g + 8, same columns
-SDCT_DEV void tmem_ld_16x256b_x8(uint32_t taddr, float (&r)[32])
-{
-    asm volatile(
-        "tcgen05.ld.sync.aligned.16x256b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
-        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
-        : "=f"(r[0]), "=f"(r[1]), "=f"(r[2]), "=f"(r[3]), "=f"(r[4]), "=f"(r[5]), "=f"(r[6]), "=f"(r[7]), "=f"(r[8]), "=f"(r[9]),
-          "=f"(r[10]), "=f"(r[11]), "=f"(r[12]), "=f"(r[13]), "=f"(r[14]), "=f"(r[15]), "=f"(r[16]), "=f"(r[17]), "=f"(r[18]),
-          "=f"(r[19]), "=f"(r[20]), "=f"(r[21]), "=f"(r[22]), "=f"(r[23]), "=f"(r[24]), "=f"(r[25]), "=f"(r[26]), "=f"(r[27]),
-          "=f"(r[28]), "=f"(r[29]), "=f"(r[30]), "=f"(r[31])
-        : "r"(taddr)
-        : "memory");
-}
 
 // ---- u8 -> fp16 (exact): 0x6400 | b = 1024 + b, minus 1024 ---------------------------------------
 SDCT_DEV uint32_t sub1024_h2(uint32_t h)
@@ -156,19 +139,69 @@ SDCT_DEV void bytes_to_half(const uint32_t (&w)[16], uint32_t (&h)[32])
     }
 }
 
+// ---- loads from TMEM: 16 lanes x 32 columns ------------------------------------------------------
+// thread (g = lane/4, q = lane%4) receives, for k = 0..3,
+//   r[4k], r[4k+1]   = TMEM lane g,     columns 8k + 2q, 8k + 2q + 1
+//   r[4k+2], r[4k+3] = TMEM lane g + 8, same columns
+SDCT_DEV void tmem_ld_16x256b_x4(uint32_t taddr, float (&r)[16])
+{
+    asm volatile(
+        "tcgen05.ld.sync.aligned.16x256b.x4.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+        : "=f"(r[0]), "=f"(r[1]), "=f"(r[2]), "=f"(r[3]), "=f"(r[4]), "=f"(r[5]), "=f"(r[6]), "=f"(r[7]), "=f"(r[8]), "=f"(r[9]),
+          "=f"(r[10]), "=f"(r[11]), "=f"(r[12]), "=f"(r[13]), "=f"(r[14]), "=f"(r[15])
+        : "r"(taddr)
+        : "memory");
+}
+// tcgen05.wait::ld with the loaded registers threaded through it, so that no use of them can be
+// scheduled above the wait
+SDCT_DEV void tmem_wait_ld(float (&a)[16], float (&b)[16])
+{
+    asm volatile("tcgen05.wait::ld.sync.aligned;"
+                 : "+f"(a[0]), "+f"(a[1]), "+f"(a[2]), "+f"(a[3]), "+f"(a[4]), "+f"(a[5]), "+f"(a[6]), "+f"(a[7]), "+f"(a[8]),
+                   "+f"(a[9]), "+f"(a[10]), "+f"(a[11]), "+f"(a[12]), "+f"(a[13]), "+f"(a[14]), "+f"(a[15]), "+f"(b[0]), "+f"(b[1]),
+                   "+f"(b[2]), "+f"(b[3]), "+f"(b[4]), "+f"(b[5]), "+f"(b[6]), "+f"(b[7]), "+f"(b[8]), "+f"(b[9]), "+f"(b[10]),
+                   "+f"(b[11]), "+f"(b[12]), "+f"(b[13]), "+f"(b[14]), "+f"(b[15])
+                 :
+                 : "memory");
+}
+
 // ---- block <-> thread mapping -----------------------------------------------------------------------
 // TMEM lane L (= thread index inside the warpgroup) holds block slot(L) of the tile, chosen so that
 // the two lanes one 16x256b load hands to a thread (g, g + 8) are adjacent blocks.
 SDCT_DEV uint32_t slot_of_lane(uint32_t L) { return (L & ~15u) | ((L & 7u) << 1) | ((L >> 3) & 1u); }
 
+// n / d for any 32-bit n (Granlund-Montgomery, magic computed by sdct_k_launch_tc)
+SDCT_DEV uint32_t fastdiv(uint32_t n, const KFastDiv &d)
+{
+    const uint32_t t = __umulhi(n, d.m);
+    return (t + ((n - t) >> d.sh1)) >> d.sh2;
+}
+
+template <int COMPS>
+SDCT_DEV Tile tile_of(const KParams &p, uint32_t tile)
+{
+    Tile t;
+    const uint32_t fc = fastdiv(tile, p.div_chunks);
+    const uint32_t chunk = tile - fc * p.chunks;
+    uint32_t frame = fc;
+    t.comp = 0;
+    if (COMPS != 1) { frame = fc / COMPS; t.comp = fc - frame * COMPS; }
+    t.n0 = chunk * TILE;
+    t.count = min((uint32_t)TILE, p.rows * p.bpr - t.n0);
+    t.pix = p.pixels + (uint64_t)frame * p.pixel_frame_stride;
+    t.coef = p.coefs + (uint64_t)frame * p.coef_frame_stride + (uint64_t)t.comp * p.coef_comp_stride;
+    return t;
+}
+
+template <int COMPS>
 SDCT_DEV const uint8_t *block_pixels(const KParams &p, const Tile &t, uint32_t slot)
 {
     const uint32_t nl = t.n0 + (slot < t.count ? slot : 0);  // keep addresses in range
-    const uint32_t r = nl / p.bpr;
+    const uint32_t r = fastdiv(nl, p.div_bpr);
     const uint32_t bx = nl - r * p.bpr;
     const uint32_t row = r + p.row0;
     const uint32_t band = p.eyes == 2 ? row >> 1 : row, eye = p.eyes == 2 ? row & 1 : 0;
-    return t.pix + (uint64_t)eye * p.eye_stride + (uint64_t)band * 8 * p.pitch + (uint64_t)bx * 8 * p.comps;
+    return t.pix + (uint64_t)eye * p.eye_stride + (uint64_t)band * 8 * p.pitch + (uint64_t)(bx * 8 * COMPS);
 }
 
 // D column j of a thread's share -> coefficient position in the layout's own index order
@@ -179,6 +212,66 @@ template <int LAYOUT>
 __host__ __device__ constexpr int column_position(int j)
 {
     return LAYOUT == SDCT_K_LAYOUT_A ? 16 * ((j & 7) >> 1) + 2 * (j >> 3) + (j & 1) : j;
+}
+
+// layout A: 16 contiguous output bytes 16q .. 16q+15 of blocks sp (P) and sp + 1 (Q)
+SDCT_DEV void store_a(const KParams &p, const Tile &t, uint64_t n_first, uint32_t sp, uint32_t q, const uint32_t (&wp)[4], const uint32_t (&wq)[4])
+{
+    uint8_t *dst = t.coef + (n_first + sp) * 64 + 16 * q;
+    if (p.coef_aligned16) {
+        if (sp < t.count) *reinterpret_cast<uint4 *>(dst) = make_uint4(wp[0], wp[1], wp[2], wp[3]);
+        if (sp + 1 < t.count) *reinterpret_cast<uint4 *>(dst + 64) = make_uint4(wq[0], wq[1], wq[2], wq[3]);
+    } else {
+#pragma unroll
+        for (int i = 0; i < 16; i++) {
+            if (sp < t.count) dst[i] = (uint8_t)(wp[i >> 2] >> (8 * (i & 3)));
+            if (sp + 1 < t.count) dst[64 + i] = (uint8_t)(wq[i >> 2] >> (8 * (i & 3)));
+        }
+    }
+}
+
+// layouts B, C: the warpgroup's staging image -> global memory, coalesced
+template <int LAYOUT>
+SDCT_DEV void flush_image(const KParams &p, const Tile &t, uint64_t n_first, const uint8_t *img, uint32_t L)
+{
+    if (LAYOUT == SDCT_K_LAYOUT_B) {
+        uint8_t *dst = t.coef + n_first * 64;
+        const uint32_t chunks16 = t.count * 4;
+        if (p.coef_aligned16) {
+#pragma unroll 4
+            for (uint32_t k = L; k < chunks16; k += 128)
+                reinterpret_cast<uint4 *>(dst)[k] = *reinterpret_cast<const uint4 *>(img + (k >> 5) * IMG_B_PITCH + (k & 31) * 16);
+        } else {
+            for (uint32_t k = L; k < chunks16 * 16; k += 128) dst[k] = img[(k >> 9) * IMG_B_PITCH + (k & 511)];
+        }
+    } else {
+        if (p.coef_aligned16 && t.count == TILE) {
+            // 8 x 16 bytes per plane row: thread L writes chunk (L & 7) of rows (L >> 3) + 16 j
+#pragma unroll
+            for (uint32_t j = 0; j < 4; j++) {
+                const uint32_t i = (L >> 3) + 16 * j, c = L & 7;
+                uint8_t *dst = t.coef + (uint64_t)i * p.coef_plane_stride + n_first;
+                reinterpret_cast<uint4 *>(dst)[c] = *reinterpret_cast<const uint4 *>(img + i * IMG_C_PITCH + c * 16);
+            }
+        } else {
+            for (uint32_t k = L; k < 64 * t.count; k += 128) {
+                const uint32_t i = k / t.count, c = k - i * t.count;
+                t.coef[(uint64_t)i * p.coef_plane_stride + n_first + c] = img[i * IMG_C_PITCH + c];
+            }
+        }
+    }
+}
+
+// one chunk = 32 D columns (k = 4kk .. 4kk+3) of the two blocks P, Q: complemented level bit patterns
+SDCT_DEV void chunk_levels(const float (&hi)[16], const float (&lo)[16], const F2 *scale, F2 (&bp)[4], F2 (&bq)[4])
+{
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        const F2 tp = fma2(make_float2(hi[4 * k], hi[4 * k + 1]), splat(1024.f), make_float2(lo[4 * k], lo[4 * k + 1]));
+        const F2 tq = fma2(make_float2(hi[4 * k + 2], hi[4 * k + 3]), splat(1024.f), make_float2(lo[4 * k + 2], lo[4 * k + 3]));
+        bp[k] = quant_rne_c(tp, scale[k]);
+        bq[k] = quant_rne_c(tq, scale[k]);
+    }
 }
 
 template <int LAYOUT, int COMPS, int VEC>
@@ -208,6 +301,7 @@ __global__ void __launch_bounds__(THREADS, 1) forward_tc_kernel(const __grid_con
     const uint32_t lane_field = ((warp & 3u) * 32u) << 16;
     const uint32_t tA = tmem_base + wg * WG_COLS, tD = tA + A_COLS;
     const uint64_t bdesc = b_descriptor(smem_u32(smem + SMEM_B_OFF));
+    uint64_t *bar = bars + wg;
     uint8_t *img = smem + SMEM_IMG_OFF + wg * IMG_BYTES;
 
     // this thread's 16 scales: columns 8k + 2q + e of the table (in column order)
@@ -220,13 +314,15 @@ __global__ void __launch_bounds__(THREADS, 1) forward_tc_kernel(const __grid_con
     uint32_t tile = blockIdx.x * WGS + wg;
     uint32_t w[16];
     const uint32_t my_slot = slot_of_lane(L);
+    Tile t;
     if (tile < p.tiles) {
-        const Tile t = tile_info<TILE>(p, tile);
-        load_block<COMPS, VEC>(block_pixels(p, t, my_slot), p.pitch, t.comp, w);
+        t = tile_of<COMPS>(p, tile);
+        load_block<COMPS, VEC>(block_pixels<COMPS>(p, t, my_slot), p.pitch, t.comp, w);
     }
     uint32_t parity = 0;
+    // blocks P, Q of this thread in the epilogue: slots sp0 (+1) in the first 16-lane half, sp0 + 16 (+1) in the second
+    const uint32_t sp0 = (warp & 3u) * 32u + 2u * g;
     for (; tile < p.tiles; tile += stride) {
-        const Tile t = tile_info<TILE>(p, tile);
         {
             uint32_t h[32];
             bytes_to_half(w, h);
@@ -235,101 +331,69 @@ __global__ void __launch_bounds__(THREADS, 1) forward_tc_kernel(const __grid_con
         tmem_wait_st();
         fence_before();
         wg_barrier(wg);
-        if (tile + stride < p.tiles) {  // prefetch the next tile's pixels into registers
-            const Tile tn = tile_info<TILE>(p, tile + stride);
-            load_block<COMPS, VEC>(block_pixels(p, tn, my_slot), p.pitch, tn.comp, w);
-        }
         if (L == 0) {
             fence_after();
 #pragma unroll
             for (int ks = 0; ks < 4; ks++)   // K = 16 pixels per instruction: 8 TMEM columns of A, 2 K-chunks of B
                 mma_f16_ts(tD, tA + 8 * ks, bdesc + (uint64_t)((2 * ks * B_LBO) >> 4), IDESC, ks);
-            mma_commit(bars + wg);
+            mma_commit(bar);
         }
-        mbar_wait(bars + wg, parity);
+        const Tile cur = t;
+        if (tile + stride < p.tiles) {  // prefetch the next tile's pixels into registers
+            t = tile_of<COMPS>(p, tile + stride);
+            load_block<COMPS, VEC>(block_pixels<COMPS>(p, t, my_slot), p.pitch, t.comp, w);
+        }
+        const uint64_t n_first = (uint64_t)p.row0 * p.bpr + cur.n0;
+        mbar_wait(bar, parity);
         parity ^= 1;
         fence_after();
 
-        const uint64_t n_first = (uint64_t)p.row0 * p.bpr + t.n0;
-#pragma unroll
-        for (int half = 0; half < 2; half++) {
-            float hi[32], lo[32];
-            const uint32_t ta = tD + lane_field + ((uint32_t)(16 * half) << 16);
-            tmem_ld_16x256b_x8(ta, hi);
-            tmem_ld_16x256b_x8(ta + 64, lo);
-            tmem_wait_ld();
-            // blocks P, Q = slots sp, sp + 1 of the tile
-            const uint32_t sp = (warp & 3u) * 32u + 16u * half + 2u * g;
-            F2 bp[8], bq[8];   // level bit patterns of columns (8k+2q, 8k+2q+1) for P and Q
-#pragma unroll
-            for (int k = 0; k < 8; k++) {
-                const F2 tp = fma2(make_float2(hi[4 * k], hi[4 * k + 1]), splat(1024.f), make_float2(lo[4 * k], lo[4 * k + 1]));
-                const F2 tq = fma2(make_float2(hi[4 * k + 2], hi[4 * k + 3]), splat(1024.f), make_float2(lo[4 * k + 2], lo[4 * k + 3]));
-                bp[k] = quant_rne_c(tp, scale[k]);
-                bq[k] = quant_rne_c(tq, scale[k]);
-            }
-            if (LAYOUT == SDCT_K_LAYOUT_A) {
-                // 16 contiguous output bytes 16q .. 16q+15 of each block: bytes 2k, 2k+1 = columns (8k+2q, +1)
-                uint4 vp, vq;
-                vp.x = ~pack4_sat(bp[0].x, bp[0].y, bp[1].x, bp[1].y); vp.y = ~pack4_sat(bp[2].x, bp[2].y, bp[3].x, bp[3].y);
-                vp.z = ~pack4_sat(bp[4].x, bp[4].y, bp[5].x, bp[5].y); vp.w = ~pack4_sat(bp[6].x, bp[6].y, bp[7].x, bp[7].y);
-                vq.x = ~pack4_sat(bq[0].x, bq[0].y, bq[1].x, bq[1].y); vq.y = ~pack4_sat(bq[2].x, bq[2].y, bq[3].x, bq[3].y);
-                vq.z = ~pack4_sat(bq[4].x, bq[4].y, bq[5].x, bq[5].y); vq.w = ~pack4_sat(bq[6].x, bq[6].y, bq[7].x, bq[7].y);
-                uint8_t *dst = t.coef + (n_first + sp) * 64 + 16 * q;
-                if (p.coef_aligned16) {
-                    if (sp < t.count) *reinterpret_cast<uint4 *>(dst) = vp;
-                    if (sp + 1 < t.count) *reinterpret_cast<uint4 *>(dst + 64) = vq;
-                } else {
-                    const uint32_t a[4] = {vp.x, vp.y, vp.z, vp.w}, b[4] = {vq.x, vq.y, vq.z, vq.w};
-#pragma unroll
-                    for (int i = 0; i < 16; i++) {
-                        if (sp < t.count) dst[i] = (uint8_t)(a[i >> 2] >> (8 * (i & 3)));
-                        if (sp + 1 < t.count) dst[64 + i] = (uint8_t)(b[i >> 2] >> (8 * (i & 3)));
-                    }
-                }
-            } else {
-                // bytes (P, Q) of one coefficient are adjacent in layouts B and C: 16-bit stores into the image
-#pragma unroll
-                for (int k = 0; k < 8; k++) {
-#pragma unroll
-                    for (int e = 0; e < 2; e++) {
-                        const int i = 8 * k + e;  // + 2q at run time
-                        const uint32_t pq = ~pack_sat(__float_as_uint(e ? bq[k].y : bq[k].x), __float_as_uint(e ? bp[k].y : bp[k].x), 0u);
-                        uint8_t *d = LAYOUT == SDCT_K_LAYOUT_B ? img + (sp >> 3) * IMG_B_PITCH + (i + 2 * q) * 8 + (sp & 7)
-                                                               : img + (i + 2 * q) * IMG_C_PITCH + sp;
-                        *reinterpret_cast<uint16_t *>(d) = (uint16_t)pq;
-                    }
-                }
-            }
+        // epilogue in four chunks of 32 columns x 16 lanes; the TMEM load of chunk c+1 is in flight while
+        // chunk c is quantised
+        float hiA[16], loA[16], hiB[16], loB[16];
+        const uint32_t td = tD + lane_field;
+        tmem_ld_16x256b_x4(td, hiA);
+        tmem_ld_16x256b_x4(td + 64, loA);
+        uint32_t wp[4], wq[4];   // layout A: the 16 output bytes of P and Q collected over two chunks
+#define SDCT_TC_CHUNK(C, HI, LO, NHI, NLO)                                                                            \
+        {                                                                                                             \
+            constexpr int half = (C) >> 1, kk = (C) & 1;                                                              \
+            tmem_wait_ld(HI, LO);                                                                                     \
+            if ((C) < 3) {                                                                                            \
+                const uint32_t tn = td + ((uint32_t)(16 * (((C) + 1) >> 1)) << 16) + 32 * (((C) + 1) & 1);            \
+                tmem_ld_16x256b_x4(tn, NHI);                                                                          \
+                tmem_ld_16x256b_x4(tn + 64, NLO);                                                                     \
+            }                                                                                                         \
+            F2 bp[4], bq[4];                                                                                          \
+            chunk_levels(HI, LO, scale + 4 * kk, bp, bq);                                                             \
+            const uint32_t sp = sp0 + 16 * half;                                                                      \
+            if (LAYOUT == SDCT_K_LAYOUT_A) {                                                                          \
+                wp[2 * kk] = ~pack4_sat(bp[0].x, bp[0].y, bp[1].x, bp[1].y);                                          \
+                wp[2 * kk + 1] = ~pack4_sat(bp[2].x, bp[2].y, bp[3].x, bp[3].y);                                      \
+                wq[2 * kk] = ~pack4_sat(bq[0].x, bq[0].y, bq[1].x, bq[1].y);                                          \
+                wq[2 * kk + 1] = ~pack4_sat(bq[2].x, bq[2].y, bq[3].x, bq[3].y);                                      \
+                if (kk == 1) store_a(p, cur, n_first, sp, q, wp, wq);                                                 \
+            } else {                                                                                                  \
+                _Pragma("unroll") for (int k = 0; k < 4; k++) {                                                       \
+                    _Pragma("unroll") for (int e = 0; e < 2; e++) {                                                   \
+                        const uint32_t i = 8 * (4 * kk + k) + e + 2 * q;                                              \
+                        const uint32_t pq = ~pack_sat(__float_as_uint(e ? bq[k].y : bq[k].x), __float_as_uint(e ? bp[k].y : bp[k].x), 0u); \
+                        uint8_t *d = LAYOUT == SDCT_K_LAYOUT_B ? img + (sp >> 3) * IMG_B_PITCH + i * 8 + (sp & 7)      \
+                                                               : img + i * IMG_C_PITCH + sp;                          \
+                        *reinterpret_cast<uint16_t *>(d) = (uint16_t)pq;                                              \
+                    }                                                                                                 \
+                }                                                                                                     \
+            }                                                                                                         \
         }
+        SDCT_TC_CHUNK(0, hiA, loA, hiB, loB)
+        SDCT_TC_CHUNK(1, hiB, loB, hiA, loA)
+        SDCT_TC_CHUNK(2, hiA, loA, hiB, loB)
+        SDCT_TC_CHUNK(3, hiB, loB, hiA, loA)
+#undef SDCT_TC_CHUNK
         fence_before();   // orders this thread's tcgen05.ld before the barrier that releases D and A
         if (LAYOUT != SDCT_K_LAYOUT_A) {
             wg_barrier(wg);
-            // image -> global memory, coalesced
-            if (LAYOUT == SDCT_K_LAYOUT_B) {
-                uint8_t *dst = t.coef + n_first * 64;
-                const uint32_t chunks16 = t.count * 4;
-                if (p.coef_aligned16) {
-                    for (uint32_t k = L; k < chunks16; k += 128)
-                        reinterpret_cast<uint4 *>(dst)[k] = *reinterpret_cast<const uint4 *>(img + (k >> 5) * IMG_B_PITCH + (k & 31) * 16);
-                } else {
-                    for (uint32_t k = L; k < chunks16 * 16; k += 128) dst[k] = img[(k >> 9) * IMG_B_PITCH + (k & 511)];
-                }
-            } else {
-                if (p.coef_aligned16 && (t.count & 15) == 0) {
-                    const uint32_t per_row = t.count >> 4;
-                    for (uint32_t k = L; k < 64 * per_row; k += 128) {
-                        const uint32_t i = k / per_row, c = k - i * per_row;
-                        uint8_t *dst = t.coef + (uint64_t)i * p.coef_plane_stride + n_first;
-                        reinterpret_cast<uint4 *>(dst)[c] = *reinterpret_cast<const uint4 *>(img + i * IMG_C_PITCH + c * 16);
-                    }
-                } else {
-                    for (uint32_t k = L; k < 64 * t.count; k += 128) {
-                        const uint32_t i = k / t.count, c = k - i * t.count;
-                        t.coef[(uint64_t)i * p.coef_plane_stride + n_first + c] = img[i * IMG_C_PITCH + c];
-                    }
-                }
-            }
+            flush_image<LAYOUT>(p, cur, n_first, img, L);
         }
     }
     fence_before();
@@ -341,6 +405,19 @@ __global__ void __launch_bounds__(THREADS, 1) forward_tc_kernel(const __grid_con
 }  // namespace sdct
 
 using namespace sdct;
+
+// Granlund-Montgomery magic for n / d, any 32-bit n, d >= 1
+static KFastDiv make_fastdiv(uint32_t d)
+{
+    KFastDiv r;
+    if (d == 0) d = 1;
+    uint32_t l = 0;
+    while ((1ull << l) < d) l++;   // ceil(log2 d)
+    r.m = (uint32_t)((((1ull << l) - d) << 32) / d + 1);
+    r.sh1 = l < 1 ? l : 1;
+    r.sh2 = l > 0 ? l - 1 : 0;
+    return r;
+}
 
 template <int LAYOUT>
 static cudaError_t launch_tc(const KParams &p, unsigned grid, cudaStream_t s)
@@ -375,6 +452,8 @@ extern "C" cudaError_t sdct_k_launch_tc(int op, int layout, const KParams *pp, c
     if (tiles == 0) return cudaSuccess;
     if (tiles > 0xfffffff0ull) return cudaErrorInvalidConfiguration;
     p.tiles = (uint32_t)tiles;
+    p.div_chunks = make_fastdiv(p.chunks);
+    p.div_bpr = make_fastdiv(p.bpr);
     const unsigned sms = p.sm_count ? p.sm_count : 148u;
     const unsigned want = (unsigned)((tiles + tc::WGS - 1) / tc::WGS);
     const unsigned grid = want < sms ? want : sms;
