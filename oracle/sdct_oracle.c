@@ -247,7 +247,15 @@ static void block_fwd_fast(const uint8_t *px, size_t pitch, const float qs[64], 
 /* mode TENSOR (this repo; simd_dct_b200/csrc/sdct_tc.cu): K = round(2^22 C (x) C) as an integer
  * matrix, entries of C = the reference's constants (:140-146) as doubles.  Per coefficient:
  * exact integer sums D1 = sum x*hi, D0 = sum x*lo (|.| < 2^24, so the GPU's fp32 tensor-core
- * accumulation is exact too), t = fma(D1, 1024, D0), level = clamp(rne(t * qs) + 127). */
+ * accumulation is exact too), t = fma(D1, 1024, D0), level = clamp(rne(fl(t * qs) + 127)). */
+/* mode TENSOR quantiser: clamp(rne(fl(t * qs) + 127), 0, 255) - the bias is added exactly before the
+ * single round-to-nearest-even (the GPU does both in one FMA onto the denormal grid) */
+static uint8_t quant_tensor(float t, float qs)
+{
+    const double r = rint((double)(t * qs) + 127.0);     /* float product, exact double sum, ties to even */
+    return (uint8_t)(r > 255.0 ? 255 : (r < 0.0 ? 0 : (int)r));
+}
+
 static double dct_entry(int u, int y)
 {
     static const double V[9] = {1.4142135623730950488016887242097, 1.3870398453221474618216191915664,
@@ -289,7 +297,7 @@ static void block_fwd_tensor(const uint8_t *px, size_t pitch, const float qs[64]
             }
             const float t = fmaf((float)d1, 1024.f, (float)d0);
             const int i = transposed ? v * 8 + u : u * 8 + v;
-            o[i] = quant_fast(t, qs[i]);
+            o[i] = quant_tensor(t, qs[i]);
         }
 }
 

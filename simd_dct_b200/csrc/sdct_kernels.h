@@ -42,6 +42,7 @@ struct KParams {
     float2 tab2[64];          // roundtrip: dequantiser scale
     float2 off[64];           // inverse / roundtrip: -127 * dequantiser scale
     KFastDiv div_chunks, div_bpr;  // tensor-core kernels
+    uint32_t tc_ablate;       // profiling only ($SDCT_TC_ABLATE): bit0 no MMA, 1 no A write, 2 no epilogue, 3 no stores, 4 no loads
     const void *tc_matrix;    // tensor-core kernels: the 16 KiB B operand (fp16 digits of 2^22 C(x)C, UMMA canonical layout)
 };
 

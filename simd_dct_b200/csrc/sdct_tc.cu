@@ -23,15 +23,23 @@
 // the epilogues of the other two.
 #include "sdct_io.cuh"
 
+#include <cstdlib>
+
 namespace sdct {
 namespace tc {
 
-constexpr int WGS = 3;                      // warpgroups per CTA
+// A operand: written by the owning threads into shared memory (canonical K-major layout; TMEM then
+// holds only the accumulators, so four warpgroups fit) or straight into TMEM (three warpgroups)
+#ifndef SDCT_TC_A_SMEM
+#define SDCT_TC_A_SMEM 0
+#endif
+constexpr bool A_IN_SMEM = SDCT_TC_A_SMEM != 0;
+constexpr int WGS = A_IN_SMEM ? 4 : 3;      // warpgroups per CTA
 constexpr int THREADS = 128 * WGS;
 constexpr int TILE = SDCT_TC_TILE;          // blocks per tile = TMEM lanes
-constexpr int A_COLS = 32;                  // 64 fp16 per lane
+constexpr int A_COLS = A_IN_SMEM ? 0 : 32;   // 64 fp16 per lane when A lives in TMEM
 constexpr int D_COLS = 128;                 // hi digit: columns 0..63, lo digit: 64..127
-constexpr int WG_COLS = A_COLS + D_COLS;    // 160
+constexpr int WG_COLS = A_COLS + D_COLS;    // 128 or 160
 constexpr int TMEM_COLS = 512;
 
 constexpr int B_BYTES = 128 * 64 * 2;       // 16 KiB: N = 128 rows x K = 64 fp16
@@ -39,12 +47,14 @@ constexpr int B_LBO = 128 * 16;             // bytes between the 16-byte K chunk
 constexpr int B_SBO = 128;                  // bytes between 8-row groups (core matrices are contiguous)
 
 // staging image of one warpgroup's 128 blocks (layouts B and C)
-constexpr int IMG_B_PITCH = 528;            // 512 B group + 16 B pad
+constexpr int IMG_B_PITCH = 576;            // 512 B group + 64 B pad: the two groups a warp's 16-bit stores touch fall on disjoint banks
 constexpr int IMG_C_PITCH = TILE + 16;      // plane row of 128 bytes + pad
 constexpr int IMG_BYTES = 64 * IMG_C_PITCH > 16 * IMG_B_PITCH ? 64 * IMG_C_PITCH : 16 * IMG_B_PITCH;
 
 constexpr int SMEM_B_OFF = 0;
-constexpr int SMEM_IMG_OFF = B_BYTES;
+constexpr int A_BYTES = 128 * 64 * 2;       // per warpgroup: M = 128 rows x K = 64 fp16, same canonical layout as B
+constexpr int SMEM_A_OFF = B_BYTES;
+constexpr int SMEM_IMG_OFF = SMEM_A_OFF + (A_IN_SMEM ? WGS * A_BYTES : 0);
 constexpr int SMEM_BAR_OFF = SMEM_IMG_OFF + WGS * IMG_BYTES;     // WGS mbarriers (8 B) + tmem base (4 B)
 constexpr int SMEM_USED = SMEM_BAR_OFF + 64;
 // more than half of the SM's shared memory: exactly one CTA per SM (it allocates all of TMEM)
@@ -93,6 +103,15 @@ SDCT_DEV void mma_f16_ts(uint32_t d_tmem, uint32_t a_tmem, uint64_t b_desc, uint
         "{\n\t.reg .pred p;\n\t"
         "setp.ne.b32 p, %4, 0;\n\t"
         "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}" ::"r"(d_tmem), "r"(a_tmem), "l"(b_desc), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+
+SDCT_DEV void mma_f16_ss(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t accumulate)
+{
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
         : "memory");
 }
 
@@ -218,7 +237,9 @@ __host__ __device__ constexpr int column_position(int j)
 SDCT_DEV void store_a(const KParams &p, const Tile &t, uint64_t n_first, uint32_t sp, uint32_t q, const uint32_t (&wp)[4], const uint32_t (&wq)[4])
 {
     uint8_t *dst = t.coef + (n_first + sp) * 64 + 16 * q;
-    if (p.coef_aligned16) {
+    if (p.tc_ablate & 8) {
+        if (wp[0] == 0x12345678u && wq[1] == 0x9abcdef0u) dst[0] = 1;
+    } else if (p.coef_aligned16) {
         if (sp < t.count) *reinterpret_cast<uint4 *>(dst) = make_uint4(wp[0], wp[1], wp[2], wp[3]);
         if (sp + 1 < t.count) *reinterpret_cast<uint4 *>(dst + 64) = make_uint4(wq[0], wq[1], wq[2], wq[3]);
     } else {
@@ -262,15 +283,20 @@ SDCT_DEV void flush_image(const KParams &p, const Tile &t, uint64_t n_first, con
     }
 }
 
-// one chunk = 32 D columns (k = 4kk .. 4kk+3) of the two blocks P, Q: complemented level bit patterns
+// mode TENSOR quantiser: level = clamp(rne(fl(t * s) + 127), 0, 255).  The FMA by 2^-149 adds the bias
+// exactly and rounds once onto the denormal grid, whose bit patterns are the integers themselves
+// (negative results carry the sign bit and saturate to 0 in the pack).
+SDCT_DEV F2 quant_rne_bias(F2 t, F2 s) { return fma2(mul2(t, s), splat(SDCT_DENORM_MIN), splat(__int_as_float(127))); }
+
+// one chunk = 32 D columns (k = 4kk .. 4kk+3) of the two blocks P, Q: level bit patterns
 SDCT_DEV void chunk_levels(const float (&hi)[16], const float (&lo)[16], const F2 *scale, F2 (&bp)[4], F2 (&bq)[4])
 {
 #pragma unroll
     for (int k = 0; k < 4; k++) {
         const F2 tp = fma2(make_float2(hi[4 * k], hi[4 * k + 1]), splat(1024.f), make_float2(lo[4 * k], lo[4 * k + 1]));
         const F2 tq = fma2(make_float2(hi[4 * k + 2], hi[4 * k + 3]), splat(1024.f), make_float2(lo[4 * k + 2], lo[4 * k + 3]));
-        bp[k] = quant_rne_c(tp, scale[k]);
-        bq[k] = quant_rne_c(tq, scale[k]);
+        bp[k] = quant_rne_bias(tp, scale[k]);
+        bq[k] = quant_rne_bias(tq, scale[k]);
     }
 }
 
@@ -301,6 +327,9 @@ __global__ void __launch_bounds__(THREADS, 1) forward_tc_kernel(const __grid_con
     const uint32_t lane_field = ((warp & 3u) * 32u) << 16;
     const uint32_t tA = tmem_base + wg * WG_COLS, tD = tA + A_COLS;
     const uint64_t bdesc = b_descriptor(smem_u32(smem + SMEM_B_OFF));
+    uint8_t *a_smem = smem + SMEM_A_OFF + (A_IN_SMEM ? wg * A_BYTES : 0);
+    const uint64_t adesc = b_descriptor(smem_u32(a_smem));
+    uint4 *a_row = reinterpret_cast<uint4 *>(a_smem + (L >> 3) * B_SBO + (L & 7) * 16);   // K chunk y: + y * B_LBO
     uint64_t *bar = bars + wg;
     uint8_t *img = smem + SMEM_IMG_OFF + wg * IMG_BYTES;
 
@@ -319,29 +348,38 @@ __global__ void __launch_bounds__(THREADS, 1) forward_tc_kernel(const __grid_con
         t = tile_of<COMPS>(p, tile);
         load_block<COMPS, VEC>(block_pixels<COMPS>(p, t, my_slot), p.pitch, t.comp, w);
     }
+    const uint32_t abl = p.tc_ablate;
     uint32_t parity = 0;
     // blocks P, Q of this thread in the epilogue: slots sp0 (+1) in the first 16-lane half, sp0 + 16 (+1) in the second
     const uint32_t sp0 = (warp & 3u) * 32u + 2u * g;
     for (; tile < p.tiles; tile += stride) {
-        {
+        if (!(abl & 2)) {
             uint32_t h[32];
             bytes_to_half(w, h);
-            tmem_st32(tA + lane_field, h);
+            if (A_IN_SMEM) {
+#pragma unroll
+                for (int y = 0; y < 8; y++) a_row[y * (B_LBO / 16)] = make_uint4(h[4 * y], h[4 * y + 1], h[4 * y + 2], h[4 * y + 3]);
+                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic-proxy writes -> tensor-core reads
+            } else {
+                tmem_st32(tA + lane_field, h);
+                tmem_wait_st();
+            }
         }
-        tmem_wait_st();
         fence_before();
         wg_barrier(wg);
         if (L == 0) {
             fence_after();
+            if (!(abl & 1))
 #pragma unroll
             for (int ks = 0; ks < 4; ks++)   // K = 16 pixels per instruction: 8 TMEM columns of A, 2 K-chunks of B
-                mma_f16_ts(tD, tA + 8 * ks, bdesc + (uint64_t)((2 * ks * B_LBO) >> 4), IDESC, ks);
+                if (A_IN_SMEM) mma_f16_ss(tD, adesc + (uint64_t)((2 * ks * B_LBO) >> 4), bdesc + (uint64_t)((2 * ks * B_LBO) >> 4), IDESC, ks);
+                else mma_f16_ts(tD, tA + 8 * ks, bdesc + (uint64_t)((2 * ks * B_LBO) >> 4), IDESC, ks);
             mma_commit(bar);
         }
         const Tile cur = t;
         if (tile + stride < p.tiles) {  // prefetch the next tile's pixels into registers
             t = tile_of<COMPS>(p, tile + stride);
-            load_block<COMPS, VEC>(block_pixels<COMPS>(p, t, my_slot), p.pitch, t.comp, w);
+            if (!(abl & 16)) load_block<COMPS, VEC>(block_pixels<COMPS>(p, t, my_slot), p.pitch, t.comp, w);
         }
         const uint64_t n_first = (uint64_t)p.row0 * p.bpr + cur.n0;
         mbar_wait(bar, parity);
@@ -350,6 +388,7 @@ __global__ void __launch_bounds__(THREADS, 1) forward_tc_kernel(const __grid_con
 
         // epilogue in four chunks of 32 columns x 16 lanes; the TMEM load of chunk c+1 is in flight while
         // chunk c is quantised
+        if (abl & 4) continue;
         float hiA[16], loA[16], hiB[16], loB[16];
         const uint32_t td = tD + lane_field;
         tmem_ld_16x256b_x4(td, hiA);
@@ -368,16 +407,16 @@ __global__ void __launch_bounds__(THREADS, 1) forward_tc_kernel(const __grid_con
             chunk_levels(HI, LO, scale + 4 * kk, bp, bq);                                                             \
             const uint32_t sp = sp0 + 16 * half;                                                                      \
             if (LAYOUT == SDCT_K_LAYOUT_A) {                                                                          \
-                wp[2 * kk] = ~pack4_sat(bp[0].x, bp[0].y, bp[1].x, bp[1].y);                                          \
-                wp[2 * kk + 1] = ~pack4_sat(bp[2].x, bp[2].y, bp[3].x, bp[3].y);                                      \
-                wq[2 * kk] = ~pack4_sat(bq[0].x, bq[0].y, bq[1].x, bq[1].y);                                          \
-                wq[2 * kk + 1] = ~pack4_sat(bq[2].x, bq[2].y, bq[3].x, bq[3].y);                                      \
+                wp[2 * kk] = pack4_sat(bp[0].x, bp[0].y, bp[1].x, bp[1].y);                                          \
+                wp[2 * kk + 1] = pack4_sat(bp[2].x, bp[2].y, bp[3].x, bp[3].y);                                      \
+                wq[2 * kk] = pack4_sat(bq[0].x, bq[0].y, bq[1].x, bq[1].y);                                          \
+                wq[2 * kk + 1] = pack4_sat(bq[2].x, bq[2].y, bq[3].x, bq[3].y);                                      \
                 if (kk == 1) store_a(p, cur, n_first, sp, q, wp, wq);                                                 \
             } else {                                                                                                  \
                 _Pragma("unroll") for (int k = 0; k < 4; k++) {                                                       \
                     _Pragma("unroll") for (int e = 0; e < 2; e++) {                                                   \
                         const uint32_t i = 8 * (4 * kk + k) + e + 2 * q;                                              \
-                        const uint32_t pq = ~pack_sat(__float_as_uint(e ? bq[k].y : bq[k].x), __float_as_uint(e ? bp[k].y : bp[k].x), 0u); \
+                        const uint32_t pq = pack_sat(__float_as_uint(e ? bq[k].y : bq[k].x), __float_as_uint(e ? bp[k].y : bp[k].x), 0u); \
                         uint8_t *d = LAYOUT == SDCT_K_LAYOUT_B ? img + (sp >> 3) * IMG_B_PITCH + i * 8 + (sp & 7)      \
                                                                : img + i * IMG_C_PITCH + sp;                          \
                         *reinterpret_cast<uint16_t *>(d) = (uint16_t)pq;                                              \
@@ -452,6 +491,7 @@ extern "C" cudaError_t sdct_k_launch_tc(int op, int layout, const KParams *pp, c
     if (tiles == 0) return cudaSuccess;
     if (tiles > 0xfffffff0ull) return cudaErrorInvalidConfiguration;
     p.tiles = (uint32_t)tiles;
+    { const char *e = getenv("SDCT_TC_ABLATE"); p.tc_ablate = e ? (uint32_t)atoi(e) : 0u; }
     p.div_chunks = make_fastdiv(p.chunks);
     p.div_bpr = make_fastdiv(p.bpr);
     const unsigned sms = p.sm_count ? p.sm_count : 148u;
