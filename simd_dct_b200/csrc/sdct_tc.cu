@@ -18,9 +18,16 @@
 //     t = fma(D1, 1024, D0), one multiply by the folded quantiser scale, the denormal-FMA
 //     rounding + saturating pack of sdct_math.cuh, then the layout's store path.
 //
-// One CTA per SM, three warpgroups; each warpgroup walks its own tiles and owns 160 TMEM columns
-// (32 for A, 128 for D), a named barrier and an mbarrier, so the MMA of one warpgroup runs under
-// the epilogues of the other two.
+// One CTA per SM, warp-specialised (416 threads), every role in its own loop over the CTA's tiles and
+// coupled only through mbarriers, so that no role ever waits for the whole load -> MMA -> store chain:
+//   warps 0-3   PRODUCER   pixels (cp.async into a 12-tile shared-memory ring, ~96 KiB of loads in flight
+//                          per SM) -> fp16 -> tcgen05.st into the stage's A columns; arrive on a_full[stage]
+//   warps 12-13 MMA        one thread each, alternate tiles: wait a_full / d_empty, 4 x tcgen05.mma,
+//                          tcgen05.commit onto d_full[stage] (which also tells the producer A is free)
+//   warps 4-11  CONSUMERS  two warpgroups taking alternate tiles: wait d_full, tcgen05.ld, quantise,
+//                          store (layout A: straight from registers; B, C: through a double-buffered
+//                          shared-memory image), arrive on d_empty[stage]
+// TMEM: 3 stages x (128 D columns + 32 A columns) = 480 of 512 columns.
 #include "sdct_io.cuh"
 
 #include <cstdlib>
@@ -28,37 +35,48 @@
 namespace sdct {
 namespace tc {
 
-// A operand: written by the owning threads into shared memory (canonical K-major layout; TMEM then
-// holds only the accumulators, so four warpgroups fit) or straight into TMEM (three warpgroups)
-#ifndef SDCT_TC_A_SMEM
-#define SDCT_TC_A_SMEM 0
-#endif
-constexpr bool A_IN_SMEM = SDCT_TC_A_SMEM != 0;
-constexpr int WGS = A_IN_SMEM ? 4 : 3;      // warpgroups per CTA
-constexpr int THREADS = 128 * WGS;
+constexpr int CONSUMER_WGS = 2;
+constexpr int MMA_WARPS = 2;                // each issues the MMAs of every MMA_WARPS-th tile (one elected thread)
+constexpr int THREADS = 128 * (1 + CONSUMER_WGS) + 32 * MMA_WARPS;   // producer WG, consumer WGs, MMA warps
+constexpr int MMA_WARP = 4 * (1 + CONSUMER_WGS);
 constexpr int TILE = SDCT_TC_TILE;          // blocks per tile = TMEM lanes
-constexpr int A_COLS = A_IN_SMEM ? 0 : 32;   // 64 fp16 per lane when A lives in TMEM
+constexpr int A_COLS = 32;                  // 64 fp16 per lane
 constexpr int D_COLS = 128;                 // hi digit: columns 0..63, lo digit: 64..127
-constexpr int WG_COLS = A_COLS + D_COLS;    // 128 or 160
+constexpr int STAGES = 3;                   // a stage = one A tile + its D tile in TMEM
+constexpr int TMEM_D_OFF = 0, TMEM_A_OFF = STAGES * D_COLS;
 constexpr int TMEM_COLS = 512;
+static_assert(TMEM_A_OFF + STAGES * A_COLS <= TMEM_COLS, "TMEM budget");
 
 constexpr int B_BYTES = 128 * 64 * 2;       // 16 KiB: N = 128 rows x K = 64 fp16
 constexpr int B_LBO = 128 * 16;             // bytes between the 16-byte K chunks of a row group: 2048
 constexpr int B_SBO = 128;                  // bytes between 8-row groups (core matrices are contiguous)
 
-// staging image of one warpgroup's 128 blocks (layouts B and C)
+// staging image of one tile's 128 blocks (layouts B and C), two per consumer warpgroup
 constexpr int IMG_B_PITCH = 576;            // 512 B group + 64 B pad: the two groups a warp's 16-bit stores touch fall on disjoint banks
 constexpr int IMG_C_PITCH = TILE + 16;      // plane row of 128 bytes + pad
 constexpr int IMG_BYTES = 64 * IMG_C_PITCH > 16 * IMG_B_PITCH ? 64 * IMG_C_PITCH : 16 * IMG_B_PITCH;
 
 constexpr int SMEM_B_OFF = 0;
-constexpr int A_BYTES = 128 * 64 * 2;       // per warpgroup: M = 128 rows x K = 64 fp16, same canonical layout as B
-constexpr int SMEM_A_OFF = B_BYTES;
-constexpr int SMEM_IMG_OFF = SMEM_A_OFF + (A_IN_SMEM ? WGS * A_BYTES : 0);
-constexpr int SMEM_BAR_OFF = SMEM_IMG_OFF + WGS * IMG_BYTES;     // WGS mbarriers (8 B) + tmem base (4 B)
-constexpr int SMEM_USED = SMEM_BAR_OFF + 64;
+constexpr int SMEM_IMG_OFF = B_BYTES;
+// pixel ring of the producer: cp.async lands the raw bytes of RING tiles ahead (8 rows x 128 threads x 8 B each)
+constexpr int RING = 12;
+constexpr int RING_TILE_BYTES = 8 * TILE * 8;
+constexpr int SMEM_RING_OFF = SMEM_IMG_OFF + CONSUMER_WGS * 2 * IMG_BYTES;
+constexpr int SMEM_BAR_OFF = SMEM_RING_OFF + RING * RING_TILE_BYTES;
+// barriers (8 B each): a_full[s] producer -> MMA, d_full[s] MMA -> consumer (and "A stage free" -> producer),
+// d_empty[s] consumer -> MMA; then the TMEM base address
+constexpr int BAR_A_FULL = 0, BAR_D_FULL = STAGES, BAR_D_EMPTY = 2 * STAGES;
+constexpr int NUM_BARS = 3 * STAGES;
+constexpr int SMEM_USED = SMEM_BAR_OFF + NUM_BARS * 8 + 16;
 // more than half of the SM's shared memory: exactly one CTA per SM (it allocates all of TMEM)
 constexpr int SMEM_BYTES = SMEM_USED > 120 * 1024 ? SMEM_USED : 120 * 1024;
+
+// profiling only ($SDCT_TC_ABLATE bit 5): clock64 stamps of CTA 0's roles, 8 per tile and role
+__device__ unsigned long long g_trace[3 * 8 * 256];
+SDCT_DEV void stamp(bool on, int role, uint32_t k, int slot)
+{
+    if (on && k < 256) g_trace[(role * 256 + k) * 8 + slot] = clock64();
+}
 
 // ---- PTX wrappers ------------------------------------------------------------------------------
 SDCT_DEV uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -74,21 +92,27 @@ SDCT_DEV void tmem_dealloc(uint32_t base)
 }
 SDCT_DEV void fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 SDCT_DEV void fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
-SDCT_DEV void wg_barrier(int wg) { asm volatile("bar.sync %0, 128;" ::"r"(wg + 1) : "memory"); }
+SDCT_DEV void named_barrier(int id) { asm volatile("bar.sync %0, 128;" ::"r"(id) : "memory"); }
 
 SDCT_DEV void mbar_init(uint64_t *bar, uint32_t count)
 {
     asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
 }
+// The suspend-time hint lets a waiting warp sleep until the phase completes instead of polling: polling
+// warps share issue slots with the warps they are waiting for.
 SDCT_DEV void mbar_wait(uint64_t *bar, uint32_t parity)
 {
     asm volatile(
         "{\n\t.reg .pred p;\n\t"
         "WAIT_%=:\n\t"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1, %2;\n\t"
         "@p bra DONE_%=;\n\t"
         "bra WAIT_%=;\n\t"
-        "DONE_%=:\n\t}" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+        "DONE_%=:\n\t}" ::"r"(smem_u32(bar)), "r"(parity), "r"(0x989680u) : "memory");
+}
+SDCT_DEV void mbar_arrive(uint64_t *bar)
+{
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
 // completion of all previously issued tcgen05.mma of this thread -> one arrival on the mbarrier
 SDCT_DEV void mma_commit(uint64_t *bar)
@@ -103,15 +127,6 @@ SDCT_DEV void mma_f16_ts(uint32_t d_tmem, uint32_t a_tmem, uint64_t b_desc, uint
         "{\n\t.reg .pred p;\n\t"
         "setp.ne.b32 p, %4, 0;\n\t"
         "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}" ::"r"(d_tmem), "r"(a_tmem), "l"(b_desc), "r"(idesc), "r"(accumulate)
-        : "memory");
-}
-
-SDCT_DEV void mma_f16_ss(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t accumulate)
-{
-    asm volatile(
-        "{\n\t.reg .pred p;\n\t"
-        "setp.ne.b32 p, %4, 0;\n\t"
-        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
         : "memory");
 }
 
@@ -300,97 +315,161 @@ SDCT_DEV void chunk_levels(const float (&hi)[16], const float (&lo)[16], const F
     }
 }
 
-template <int LAYOUT, int COMPS, int VEC>
-__global__ void __launch_bounds__(THREADS, 1) forward_tc_kernel(const __grid_constant__ KParams p)
+// ---- roles -------------------------------------------------------------------------------------------
+// The CTA's k-th tile is global tile blockIdx.x + k * gridDim.x; it uses stage k % STAGES (use count
+// u = k / STAGES), consumer warpgroup k % CONSUMER_WGS and MMA warp k % MMA_WARPS.  A barrier is waited on
+// with the parity of the use count when the waiter needs phase u itself (a_full, d_full for the consumer)
+// and with the opposite parity when it needs phase u - 1 (d_empty; d_full for the producer: the MMAs of
+// the stage's previous tile have read A); a fresh barrier passes the opposite-parity wait.
+
+SDCT_DEV void cp_async8(void *smem, const void *gmem)
 {
-    extern __shared__ __align__(128) uint8_t smem[];
-    const uint32_t wg = threadIdx.x >> 7, L = threadIdx.x & 127, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    uint64_t *bars = reinterpret_cast<uint64_t *>(smem + SMEM_BAR_OFF);
-    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(smem + SMEM_BAR_OFF + 32);
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(smem_u32(smem)), "l"(gmem) : "memory");
+}
+SDCT_DEV void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N> SDCT_DEV void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 
-    // B operand -> shared memory (prepared on the host in the canonical layout), barriers, TMEM
-    {
-        const uint4 *src = reinterpret_cast<const uint4 *>(p.tc_matrix);
-        uint4 *dst = reinterpret_cast<uint4 *>(smem + SMEM_B_OFF);
-        for (int i = threadIdx.x; i < B_BYTES / 16; i += THREADS) dst[i] = __ldg(src + i);
-    }
-    if (threadIdx.x == 0) {
-        for (int i = 0; i < WGS; i++) mbar_init(bars + i, 1);
-        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-    }
-    if (warp == 0) tmem_alloc(tmem_slot);
-    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // B is read by the tensor core (async proxy)
-    fence_before();
-    __syncthreads();
+// A rows of one tile: the thread's 64 pixels (16 words) -> fp16 -> its TMEM lane of the stage's A columns
+SDCT_DEV void publish_a(const KParams &p, uint64_t *bars, uint32_t tmem_base, uint32_t lane_field, uint32_t k, const uint32_t (&w)[16])
+{
+    const uint32_t stage = k % STAGES, u = k / STAGES;
+    const bool tr = (p.tc_ablate & 32) && blockIdx.x == 0 && threadIdx.x == 0;
+    uint32_t h[32];
+    bytes_to_half(w, h);
+    stamp(tr, 0, k, 0);
+    mbar_wait(bars + BAR_D_FULL + stage, (u & 1) ^ 1);   // the MMAs of tile k - STAGES have completed: A[stage] is free
     fence_after();
-    const uint32_t tmem_base = *tmem_slot;
-    const uint32_t lane_field = ((warp & 3u) * 32u) << 16;
-    const uint32_t tA = tmem_base + wg * WG_COLS, tD = tA + A_COLS;
-    const uint64_t bdesc = b_descriptor(smem_u32(smem + SMEM_B_OFF));
-    uint8_t *a_smem = smem + SMEM_A_OFF + (A_IN_SMEM ? wg * A_BYTES : 0);
-    const uint64_t adesc = b_descriptor(smem_u32(a_smem));
-    uint4 *a_row = reinterpret_cast<uint4 *>(a_smem + (L >> 3) * B_SBO + (L & 7) * 16);   // K chunk y: + y * B_LBO
-    uint64_t *bar = bars + wg;
-    uint8_t *img = smem + SMEM_IMG_OFF + wg * IMG_BYTES;
+    stamp(tr, 0, k, 1);
+    if (!(p.tc_ablate & 2)) {
+        tmem_st32(tmem_base + TMEM_A_OFF + stage * A_COLS + lane_field, h);
+        tmem_wait_st();
+    }
+    fence_before();
+    stamp(tr, 0, k, 2);
+    mbar_arrive(bars + BAR_A_FULL + stage);
+    stamp(tr, 0, k, 3);
+}
 
+template <int COMPS, int VEC>
+SDCT_DEV void producer_role(const KParams &p, uint64_t *bars, uint32_t tmem_base, uint8_t *ring, uint32_t L, uint32_t lane_field)
+{
+    const uint32_t my_slot = slot_of_lane(L);
+    if (COMPS == 1 && VEC >= 1) {
+        // 8-byte-aligned single-plane rows: cp.async ring, RING tiles ahead.  A thread copies and later
+        // reads only its own 8-byte slots (row r at r * 1024 + L * 8), so no barrier is involved.
+        uint8_t *mine = ring + L * 8;
+        auto issue = [&](uint32_t k) {
+            const uint32_t tile = blockIdx.x + k * gridDim.x;
+            if (tile < p.tiles && !(p.tc_ablate & 16)) {
+                const Tile t = tile_of<COMPS>(p, tile);
+                const uint8_t *px = block_pixels<COMPS>(p, t, my_slot);
+                uint8_t *dst = mine + (k % RING) * RING_TILE_BYTES;
+#pragma unroll
+                for (int r = 0; r < 8; r++) cp_async8(dst + r * (TILE * 8), px + r * p.pitch);
+            }
+            cp_async_commit();   // one group per tile, empty past the end, so that wait_group counts stay static
+        };
+        for (uint32_t k = 0; k < RING; k++) issue(k);
+        for (uint32_t k = 0;; k++) {
+            if (blockIdx.x + k * gridDim.x >= p.tiles) return;
+            cp_async_wait<RING - 1>();   // this thread's copies of tile k have landed
+            const uint8_t *src = mine + (k % RING) * RING_TILE_BYTES;
+            uint32_t w[16];
+#pragma unroll
+            for (int r = 0; r < 8; r++) {
+                const uint2 v = *reinterpret_cast<const uint2 *>(src + r * (TILE * 8));
+                w[2 * r] = v.x; w[2 * r + 1] = v.y;
+            }
+            publish_a(p, bars, tmem_base, lane_field, k, w);   // consumes w: the slot may be refilled now
+            issue(k + RING);
+        }
+    } else {
+        // interleaved or unaligned pixels: register prefetch, one 16-word set per stage
+        constexpr int PF = STAGES;
+        uint32_t w[PF][16];
+#pragma unroll
+        for (int j = 0; j < PF; j++) {
+            const uint32_t tile = blockIdx.x + j * gridDim.x;
+            if (tile < p.tiles) {
+                const Tile t = tile_of<COMPS>(p, tile);
+                load_block<COMPS, VEC>(block_pixels<COMPS>(p, t, my_slot), p.pitch, t.comp, w[j]);
+            }
+        }
+        for (uint32_t u = 0;; u++) {
+#pragma unroll
+            for (int j = 0; j < PF; j++) {
+                const uint32_t k = u * PF + j, tile = blockIdx.x + k * gridDim.x;
+                if (tile >= p.tiles) return;
+                uint32_t cur[16];
+#pragma unroll
+                for (int i = 0; i < 16; i++) cur[i] = w[j][i];
+                const uint32_t next = tile + PF * gridDim.x;
+                if (next < p.tiles) {
+                    const Tile tn = tile_of<COMPS>(p, next);
+                    load_block<COMPS, VEC>(block_pixels<COMPS>(p, tn, my_slot), p.pitch, tn.comp, w[j]);
+                }
+                publish_a(p, bars, tmem_base, lane_field, k, cur);
+            }
+        }
+    }
+}
+
+// one thread per MMA warp; warp m takes tiles k = m, m + MMA_WARPS, ...
+SDCT_DEV void mma_role(const KParams &p, uint64_t *bars, uint32_t tmem_base, uint64_t bdesc, uint32_t m)
+{
+    const bool no_mma = (p.tc_ablate & 1) != 0;
+    const uint64_t bd[4] = {bdesc, bdesc + (uint64_t)((2 * B_LBO) >> 4), bdesc + (uint64_t)((4 * B_LBO) >> 4), bdesc + (uint64_t)((6 * B_LBO) >> 4)};
+    uint32_t stage = m % STAGES, u = m / STAGES, k = m;
+    const bool tr = (p.tc_ablate & 32) && blockIdx.x == 0;
+    for (uint32_t tile = blockIdx.x + m * gridDim.x; tile < p.tiles; tile += MMA_WARPS * gridDim.x, k += MMA_WARPS) {
+        stamp(tr, 1, k, 0);
+        mbar_wait(bars + BAR_A_FULL + stage, u & 1);
+        stamp(tr, 1, k, 1);
+        mbar_wait(bars + BAR_D_EMPTY + stage, (u & 1) ^ 1);
+        fence_after();
+        stamp(tr, 1, k, 2);
+        const uint32_t tA = tmem_base + TMEM_A_OFF + stage * A_COLS, tD = tmem_base + TMEM_D_OFF + stage * D_COLS;
+        if (!no_mma) {
+#pragma unroll
+            for (int ks = 0; ks < 4; ks++)   // K = 16 pixels per instruction: 8 TMEM columns of A, 2 K-chunks of B
+                mma_f16_ts(tD, tA + 8 * ks, bd[ks], IDESC, ks);
+        }
+        stamp(tr, 1, k, 3);
+        mma_commit(bars + BAR_D_FULL + stage);
+        stamp(tr, 1, k, 4);
+        stage += MMA_WARPS;
+        if (stage >= STAGES) { stage -= STAGES; u++; }
+    }
+}
+
+template <int LAYOUT, int COMPS>
+SDCT_DEV void consumer_role(const KParams &p, uint64_t *bars, uint32_t tmem_base, uint8_t *img_base, uint32_t c, uint32_t L, uint32_t lane_field)
+{
+    const uint32_t lane = L & 31, g = lane >> 2, q = lane & 3;
     // this thread's 16 scales: columns 8k + 2q + e of the table (in column order)
-    const uint32_t g = lane >> 2, q = lane & 3;
     F2 scale[8];
 #pragma unroll
     for (int k = 0; k < 8; k++) scale[k] = make_float2(p.tab[8 * k + 2 * q].x, p.tab[8 * k + 2 * q + 1].x);
-
-    const uint32_t stride = gridDim.x * WGS;
-    uint32_t tile = blockIdx.x * WGS + wg;
-    uint32_t w[16];
-    const uint32_t my_slot = slot_of_lane(L);
-    Tile t;
-    if (tile < p.tiles) {
-        t = tile_of<COMPS>(p, tile);
-        load_block<COMPS, VEC>(block_pixels<COMPS>(p, t, my_slot), p.pitch, t.comp, w);
-    }
+    // blocks P, Q of this thread: slots sp0 (+1) in the first 16-lane half, sp0 + 16 (+1) in the second
+    const uint32_t sp0 = (L >> 5) * 32u + 2u * g;
     const uint32_t abl = p.tc_ablate;
-    uint32_t parity = 0;
-    // blocks P, Q of this thread in the epilogue: slots sp0 (+1) in the first 16-lane half, sp0 + 16 (+1) in the second
-    const uint32_t sp0 = (warp & 3u) * 32u + 2u * g;
-    for (; tile < p.tiles; tile += stride) {
-        if (!(abl & 2)) {
-            uint32_t h[32];
-            bytes_to_half(w, h);
-            if (A_IN_SMEM) {
-#pragma unroll
-                for (int y = 0; y < 8; y++) a_row[y * (B_LBO / 16)] = make_uint4(h[4 * y], h[4 * y + 1], h[4 * y + 2], h[4 * y + 3]);
-                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic-proxy writes -> tensor-core reads
-            } else {
-                tmem_st32(tA + lane_field, h);
-                tmem_wait_st();
-            }
-        }
-        fence_before();
-        wg_barrier(wg);
-        if (L == 0) {
-            fence_after();
-            if (!(abl & 1))
-#pragma unroll
-            for (int ks = 0; ks < 4; ks++)   // K = 16 pixels per instruction: 8 TMEM columns of A, 2 K-chunks of B
-                if (A_IN_SMEM) mma_f16_ss(tD, adesc + (uint64_t)((2 * ks * B_LBO) >> 4), bdesc + (uint64_t)((2 * ks * B_LBO) >> 4), IDESC, ks);
-                else mma_f16_ts(tD, tA + 8 * ks, bdesc + (uint64_t)((2 * ks * B_LBO) >> 4), IDESC, ks);
-            mma_commit(bar);
-        }
-        const Tile cur = t;
-        if (tile + stride < p.tiles) {  // prefetch the next tile's pixels into registers
-            t = tile_of<COMPS>(p, tile + stride);
-            if (!(abl & 16)) load_block<COMPS, VEC>(block_pixels<COMPS>(p, t, my_slot), p.pitch, t.comp, w);
-        }
+    for (uint32_t k = c;; k += CONSUMER_WGS) {
+        const uint32_t tile = blockIdx.x + k * gridDim.x;
+        if (tile >= p.tiles) break;
+        const uint32_t sd = k % STAGES, ud = k / STAGES;
+        const Tile cur = tile_of<COMPS>(p, tile);
         const uint64_t n_first = (uint64_t)p.row0 * p.bpr + cur.n0;
-        mbar_wait(bar, parity);
-        parity ^= 1;
+        uint8_t *img = img_base + ((k / CONSUMER_WGS) & 1) * IMG_BYTES;
+        const bool tr = (abl & 32) && blockIdx.x == 0 && L == 0;
+        stamp(tr, 2, k, 0);
+        mbar_wait(bars + BAR_D_FULL + sd, ud & 1);
         fence_after();
+        stamp(tr, 2, k, 1);
+        if (abl & 4) { fence_before(); mbar_arrive(bars + BAR_D_EMPTY + sd); continue; }
 
-        // epilogue in four chunks of 32 columns x 16 lanes; the TMEM load of chunk c+1 is in flight while
-        // chunk c is quantised
-        if (abl & 4) continue;
+        // four chunks of 32 columns x 16 lanes; the TMEM load of chunk c+1 is in flight while chunk c is quantised
         float hiA[16], loA[16], hiB[16], loB[16];
-        const uint32_t td = tD + lane_field;
+        const uint32_t td = tmem_base + TMEM_D_OFF + sd * D_COLS + lane_field;
         tmem_ld_16x256b_x4(td, hiA);
         tmem_ld_16x256b_x4(td + 64, loA);
         uint32_t wp[4], wq[4];   // layout A: the 16 output bytes of P and Q collected over two chunks
@@ -402,21 +481,25 @@ __global__ void __launch_bounds__(THREADS, 1) forward_tc_kernel(const __grid_con
                 const uint32_t tn = td + ((uint32_t)(16 * (((C) + 1) >> 1)) << 16) + 32 * (((C) + 1) & 1);            \
                 tmem_ld_16x256b_x4(tn, NHI);                                                                          \
                 tmem_ld_16x256b_x4(tn + 64, NLO);                                                                     \
+            } else {   /* every load of this thread has landed: hand the D stage back to the MMA warp */              \
+                fence_before();                                                                                       \
+                mbar_arrive(bars + BAR_D_EMPTY + sd);                                                                 \
+                stamp(tr, 2, k, 2);                                                                                   \
             }                                                                                                         \
             F2 bp[4], bq[4];                                                                                          \
             chunk_levels(HI, LO, scale + 4 * kk, bp, bq);                                                             \
             const uint32_t sp = sp0 + 16 * half;                                                                      \
             if (LAYOUT == SDCT_K_LAYOUT_A) {                                                                          \
-                wp[2 * kk] = pack4_sat(bp[0].x, bp[0].y, bp[1].x, bp[1].y);                                          \
-                wp[2 * kk + 1] = pack4_sat(bp[2].x, bp[2].y, bp[3].x, bp[3].y);                                      \
-                wq[2 * kk] = pack4_sat(bq[0].x, bq[0].y, bq[1].x, bq[1].y);                                          \
-                wq[2 * kk + 1] = pack4_sat(bq[2].x, bq[2].y, bq[3].x, bq[3].y);                                      \
+                wp[2 * kk] = pack4_sat(bp[0].x, bp[0].y, bp[1].x, bp[1].y);                                           \
+                wp[2 * kk + 1] = pack4_sat(bp[2].x, bp[2].y, bp[3].x, bp[3].y);                                       \
+                wq[2 * kk] = pack4_sat(bq[0].x, bq[0].y, bq[1].x, bq[1].y);                                           \
+                wq[2 * kk + 1] = pack4_sat(bq[2].x, bq[2].y, bq[3].x, bq[3].y);                                       \
                 if (kk == 1) store_a(p, cur, n_first, sp, q, wp, wq);                                                 \
             } else {                                                                                                  \
-                _Pragma("unroll") for (int k = 0; k < 4; k++) {                                                       \
+                _Pragma("unroll") for (int k2 = 0; k2 < 4; k2++) {                                                    \
                     _Pragma("unroll") for (int e = 0; e < 2; e++) {                                                   \
-                        const uint32_t i = 8 * (4 * kk + k) + e + 2 * q;                                              \
-                        const uint32_t pq = pack_sat(__float_as_uint(e ? bq[k].y : bq[k].x), __float_as_uint(e ? bp[k].y : bp[k].x), 0u); \
+                        const uint32_t i = 8 * (4 * kk + k2) + e + 2 * q;                                             \
+                        const uint32_t pq = pack_sat(__float_as_uint(e ? bq[k2].y : bq[k2].x), __float_as_uint(e ? bp[k2].y : bp[k2].x), 0u); \
                         uint8_t *d = LAYOUT == SDCT_K_LAYOUT_B ? img + (sp >> 3) * IMG_B_PITCH + i * 8 + (sp & 7)      \
                                                                : img + i * IMG_C_PITCH + sp;                          \
                         *reinterpret_cast<uint16_t *>(d) = (uint16_t)pq;                                              \
@@ -429,11 +512,52 @@ __global__ void __launch_bounds__(THREADS, 1) forward_tc_kernel(const __grid_con
         SDCT_TC_CHUNK(2, hiA, loA, hiB, loB)
         SDCT_TC_CHUNK(3, hiB, loB, hiA, loA)
 #undef SDCT_TC_CHUNK
-        fence_before();   // orders this thread's tcgen05.ld before the barrier that releases D and A
         if (LAYOUT != SDCT_K_LAYOUT_A) {
-            wg_barrier(wg);
+            named_barrier(1 + c);
+            stamp(tr, 2, k, 3);
             flush_image<LAYOUT>(p, cur, n_first, img, L);
         }
+        stamp(tr, 2, k, 4);
+    }
+}
+
+template <int LAYOUT, int COMPS, int VEC>
+__global__ void __launch_bounds__(THREADS, 1) forward_tc_kernel(const __grid_constant__ KParams p)
+{
+    extern __shared__ __align__(128) uint8_t smem[];
+    const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    uint64_t *bars = reinterpret_cast<uint64_t *>(smem + SMEM_BAR_OFF);
+    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(smem + SMEM_BAR_OFF + NUM_BARS * 8);
+
+    // B operand -> shared memory (prepared on the host in the canonical layout), barriers, TMEM
+    {
+        const uint4 *src = reinterpret_cast<const uint4 *>(p.tc_matrix);
+        uint4 *dst = reinterpret_cast<uint4 *>(smem + SMEM_B_OFF);
+        for (int i = threadIdx.x; i < B_BYTES / 16; i += THREADS) dst[i] = __ldg(src + i);
+    }
+    if (threadIdx.x == 0) {
+        for (int i = 0; i < STAGES; i++) {
+            mbar_init(bars + BAR_A_FULL + i, 128);
+            mbar_init(bars + BAR_D_FULL + i, 1);
+            mbar_init(bars + BAR_D_EMPTY + i, 128);
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 0) tmem_alloc(tmem_slot);
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // B is read by the tensor core (async proxy)
+    fence_before();
+    __syncthreads();
+    fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+    const uint32_t lane_field = ((warp & 3u) * 32u) << 16;
+
+    if (warp < 4) {
+        producer_role<COMPS, VEC>(p, bars, tmem_base, smem + SMEM_RING_OFF, threadIdx.x, lane_field);
+    } else if (warp < MMA_WARP) {
+        const uint32_t c = (warp >> 2) - 1;
+        consumer_role<LAYOUT, COMPS>(p, bars, tmem_base, smem + SMEM_IMG_OFF + c * 2 * IMG_BYTES, c, threadIdx.x & 127, lane_field);
+    } else if (lane == 0) {
+        mma_role(p, bars, tmem_base, b_descriptor(smem_u32(smem + SMEM_B_OFF)), warp - MMA_WARP);
     }
     fence_before();
     __syncthreads();
@@ -480,6 +604,12 @@ static cudaError_t launch_tc(const KParams &p, unsigned grid, cudaStream_t s)
 #undef SDCT_TC_GO
 }
 
+// profiling only: copies the clock64 trace of the last traced launch (3 roles x 256 tiles x 8 stamps)
+extern "C" int sdct_k_tc_trace(unsigned long long *host)
+{
+    return (int)cudaMemcpyFromSymbol(host, tc::g_trace, sizeof(tc::g_trace));
+}
+
 extern "C" cudaError_t sdct_k_launch_tc(int op, int layout, const KParams *pp, cudaStream_t s)
 {
     if (op != SDCT_K_OP_FORWARD) return cudaErrorNotSupported;
@@ -495,8 +625,7 @@ extern "C" cudaError_t sdct_k_launch_tc(int op, int layout, const KParams *pp, c
     p.div_chunks = make_fastdiv(p.chunks);
     p.div_bpr = make_fastdiv(p.bpr);
     const unsigned sms = p.sm_count ? p.sm_count : 148u;
-    const unsigned want = (unsigned)((tiles + tc::WGS - 1) / tc::WGS);
-    const unsigned grid = want < sms ? want : sms;
+    const unsigned grid = (unsigned)(tiles < sms ? tiles : sms);
     switch (layout) {
     case SDCT_K_LAYOUT_A: return launch_tc<SDCT_K_LAYOUT_A>(p, grid, s);
     case SDCT_K_LAYOUT_B: return launch_tc<SDCT_K_LAYOUT_B>(p, grid, s);

@@ -1,0 +1,37 @@
+#!/usr/bin/env python
+"""Profiling only: per-tile clock64 stamps of CTA 0's producer / MMA / consumer roles (SDCT_TC_ABLATE bit 5)."""
+import ctypes as C, os, sys
+import numpy as np, torch
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+abl = int(sys.argv[1]) if len(sys.argv) > 1 else 0
+layout_name = sys.argv[2] if len(sys.argv) > 2 else "A"
+os.environ["SDCT_TC_ABLATE"] = str(abl | 32)
+import simd_dct_b200 as sd
+from simd_dct_b200 import _lib
+ctx = sd.Context(0)
+L = {"A": sd.LAYOUT_A, "B": sd.LAYOUT_B, "C": sd.LAYOUT_C}[layout_name]
+job = sd.dense_job(L, 1920, 1080, frames=64, flags=sd.TENSOR)
+pix = torch.randint(0, 256, (64, 1080, 1920), dtype=torch.uint8, device="cuda")
+out = torch.empty(64 * 1080 * 1920, dtype=torch.uint8, device="cuda")
+for _ in range(3):
+    ctx.forward(pix, sd.quality_lut(1), job, out=out)
+torch.cuda.synchronize()
+tr = np.zeros(3 * 256 * 8, dtype=np.uint64)
+assert _lib.load().sdct_k_tc_trace(tr.ctypes.data_as(C.c_void_p)) == 0
+tr = tr.reshape(3, 256, 8).astype(np.int64)
+t0 = tr[0, 0, 0]
+names = ["producer", "mma", "consumer0"]
+print(f"ablate={abl} layout={layout_name}; cycles relative to producer tile 0")
+for role in range(3):
+    print(names[role])
+    ks = range(12, 30) if role < 2 else range(12, 30, 2)
+    prev = None
+    for k in ks:
+        row = tr[role, k]
+        if row[0] == 0:
+            continue
+        rel = [int(x - t0) if x else -1 for x in row[:6]]
+        d = "" if prev is None else f"  (+{rel[0] - prev} since previous)"
+        prev = rel[0]
+        print(f"  k={k:3d} " + " ".join(f"{x:8d}" for x in rel) + d)
