@@ -71,11 +71,16 @@ constexpr int SMEM_USED = SMEM_BAR_OFF + NUM_BARS * 8 + 16;
 // more than half of the SM's shared memory: exactly one CTA per SM (it allocates all of TMEM)
 constexpr int SMEM_BYTES = SMEM_USED > 120 * 1024 ? SMEM_USED : 120 * 1024;
 
-// profiling only ($SDCT_TC_ABLATE bit 5): clock64 stamps of CTA 0's roles, 8 per tile and role
+// profiling builds only (-DSDCT_TC_TRACE=1; $SDCT_TC_ABLATE then selects ablations, bit 5 = clock64 stamps of
+// CTA 0's roles, 8 per tile and role).  In the product build the stamps and ablation tests compile to nothing.
+#ifndef SDCT_TC_TRACE
+#define SDCT_TC_TRACE 0
+#endif
 __device__ unsigned long long g_trace[3 * 8 * 256];
+SDCT_DEV uint32_t ablate_bits(const KParams &p) { return SDCT_TC_TRACE ? p.tc_ablate : 0u; }
 SDCT_DEV void stamp(bool on, int role, uint32_t k, int slot)
 {
-    if (on && k < 256) g_trace[(role * 256 + k) * 8 + slot] = clock64();
+    if (SDCT_TC_TRACE && on && k < 256) g_trace[(role * 256 + k) * 8 + slot] = clock64();
 }
 
 // ---- PTX wrappers ------------------------------------------------------------------------------
@@ -211,16 +216,34 @@ SDCT_DEV uint32_t fastdiv(uint32_t n, const KFastDiv &d)
     return (t + ((n - t) >> d.sh1)) >> d.sh2;
 }
 
+// The CTA's tiles k = first, first + stride, ... are global tiles blockIdx.x + k * gridDim.x.  A walk carries
+// (tile / chunks, tile % chunks) from tile to tile, so that the per-tile bookkeeping has no division.
+struct TileWalk {
+    uint32_t tile, fc, chunk, step, dq, dr;
+    SDCT_DEV void init(const KParams &p, uint32_t first, uint32_t stride)
+    {
+        tile = blockIdx.x + first * gridDim.x;
+        fc = fastdiv(tile, p.div_chunks);
+        chunk = tile - fc * p.chunks;
+        step = stride * gridDim.x;
+        dq = fastdiv(step, p.div_chunks);
+        dr = step - dq * p.chunks;
+    }
+    SDCT_DEV void next(const KParams &p)
+    {
+        tile += step; fc += dq; chunk += dr;
+        if (chunk >= p.chunks) { chunk -= p.chunks; fc++; }
+    }
+};
+
 template <int COMPS>
-SDCT_DEV Tile tile_of(const KParams &p, uint32_t tile)
+SDCT_DEV Tile tile_at(const KParams &p, const TileWalk &w)
 {
     Tile t;
-    const uint32_t fc = fastdiv(tile, p.div_chunks);
-    const uint32_t chunk = tile - fc * p.chunks;
-    uint32_t frame = fc;
+    uint32_t frame = w.fc;
     t.comp = 0;
-    if (COMPS != 1) { frame = fc / COMPS; t.comp = fc - frame * COMPS; }
-    t.n0 = chunk * TILE;
+    if (COMPS != 1) { frame = w.fc / COMPS; t.comp = w.fc - frame * COMPS; }
+    t.n0 = w.chunk * TILE;
     t.count = min((uint32_t)TILE, p.rows * p.bpr - t.n0);
     t.pix = p.pixels + (uint64_t)frame * p.pixel_frame_stride;
     t.coef = p.coefs + (uint64_t)frame * p.coef_frame_stride + (uint64_t)t.comp * p.coef_comp_stride;
@@ -252,7 +275,7 @@ __host__ __device__ constexpr int column_position(int j)
 SDCT_DEV void store_a(const KParams &p, const Tile &t, uint64_t n_first, uint32_t sp, uint32_t q, const uint32_t (&wp)[4], const uint32_t (&wq)[4])
 {
     uint8_t *dst = t.coef + (n_first + sp) * 64 + 16 * q;
-    if (p.tc_ablate & 8) {
+    if (ablate_bits(p) & 8) {
         if (wp[0] == 0x12345678u && wq[1] == 0x9abcdef0u) dst[0] = 1;
     } else if (p.coef_aligned16) {
         if (sp < t.count) *reinterpret_cast<uint4 *>(dst) = make_uint4(wp[0], wp[1], wp[2], wp[3]);
@@ -326,6 +349,10 @@ SDCT_DEV void cp_async8(void *smem, const void *gmem)
 {
     asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(smem_u32(smem)), "l"(gmem) : "memory");
 }
+SDCT_DEV void cp_async16(void *smem, const void *gmem)
+{
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(smem)), "l"(gmem) : "memory");
+}
 SDCT_DEV void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 template <int N> SDCT_DEV void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 
@@ -333,14 +360,14 @@ template <int N> SDCT_DEV void cp_async_wait() { asm volatile("cp.async.wait_gro
 SDCT_DEV void publish_a(const KParams &p, uint64_t *bars, uint32_t tmem_base, uint32_t lane_field, uint32_t k, const uint32_t (&w)[16])
 {
     const uint32_t stage = k % STAGES, u = k / STAGES;
-    const bool tr = (p.tc_ablate & 32) && blockIdx.x == 0 && threadIdx.x == 0;
+    const bool tr = (ablate_bits(p) & 32) && blockIdx.x == 0 && threadIdx.x == 0;
     uint32_t h[32];
     bytes_to_half(w, h);
     stamp(tr, 0, k, 0);
     mbar_wait(bars + BAR_D_FULL + stage, (u & 1) ^ 1);   // the MMAs of tile k - STAGES have completed: A[stage] is free
     fence_after();
     stamp(tr, 0, k, 1);
-    if (!(p.tc_ablate & 2)) {
+    if (!(ablate_bits(p) & 2)) {
         tmem_st32(tmem_base + TMEM_A_OFF + stage * A_COLS + lane_field, h);
         tmem_wait_st();
     }
@@ -355,24 +382,42 @@ SDCT_DEV void producer_role(const KParams &p, uint64_t *bars, uint32_t tmem_base
 {
     const uint32_t my_slot = slot_of_lane(L);
     if (COMPS == 1 && VEC >= 1) {
-        // 8-byte-aligned single-plane rows: cp.async ring, RING tiles ahead.  A thread copies and later
-        // reads only its own 8-byte slots (row r at r * 1024 + L * 8), so no barrier is involved.
-        uint8_t *mine = ring + L * 8;
+        // aligned single-plane rows: cp.async ring, RING tiles ahead; row r of the block in slot s lies at
+        // r * 1024 + s * 8.  VEC == 1: a thread copies the eight 8-byte rows of its own block.  VEC == 2 (16-byte
+        // aligned rows, even blocks per row): the two threads of an adjacent block pair (lanes L, L ^ 8 of one
+        // warp) copy four 16-byte rows of the pair each, so a __syncwarp() stands between copy and use.
+        const uint32_t half = VEC == 2 ? (L >> 3) & 1u : 0u;
+        const uint32_t copy_slot = VEC == 2 ? my_slot & ~1u : my_slot;
+        constexpr int ROWS = VEC == 2 ? 4 : 8;
+        uint8_t *mine = ring + my_slot * 8;
+        uint8_t *copy_dst = ring + copy_slot * 8 + half * 4 * (TILE * 8);
+        const uint64_t row_off = (uint64_t)(half * 4) * p.pitch;
+        TileWalk wi;   // the tile whose copies are issued next
+        wi.init(p, 0, 1);
         auto issue = [&](uint32_t k) {
-            const uint32_t tile = blockIdx.x + k * gridDim.x;
-            if (tile < p.tiles && !(p.tc_ablate & 16)) {
-                const Tile t = tile_of<COMPS>(p, tile);
-                const uint8_t *px = block_pixels<COMPS>(p, t, my_slot);
-                uint8_t *dst = mine + (k % RING) * RING_TILE_BYTES;
+            const bool live = wi.tile < p.tiles && !(ablate_bits(p) & 16);
+            if (live) {
+                const Tile t = tile_at<COMPS>(p, wi);
+                const uint8_t *px = block_pixels<COMPS>(p, t, copy_slot) + row_off;
+                uint8_t *dst = copy_dst + (k % RING) * RING_TILE_BYTES;
 #pragma unroll
-                for (int r = 0; r < 8; r++) cp_async8(dst + r * (TILE * 8), px + r * p.pitch);
+                for (int r = 0; r < ROWS; r++, px += p.pitch) {
+                    if (VEC == 2) cp_async16(dst + r * (TILE * 8), px);
+                    else cp_async8(dst + r * (TILE * 8), px);
+                }
             }
+            wi.next(p);
             cp_async_commit();   // one group per tile, empty past the end, so that wait_group counts stay static
         };
         for (uint32_t k = 0; k < RING; k++) issue(k);
-        for (uint32_t k = 0;; k++) {
-            if (blockIdx.x + k * gridDim.x >= p.tiles) return;
+        uint32_t tile = blockIdx.x;
+        for (uint32_t k = 0;; k++, tile += gridDim.x) {
+            if (tile >= p.tiles) return;
+            const bool trp = (ablate_bits(p) & 32) && blockIdx.x == 0 && threadIdx.x == 0;
+            stamp(trp, 0, k, 5);
             cp_async_wait<RING - 1>();   // this thread's copies of tile k have landed
+            if (VEC == 2) __syncwarp();  // ... and its partner's
+            stamp(trp, 0, k, 6);
             const uint8_t *src = mine + (k % RING) * RING_TILE_BYTES;
             uint32_t w[16];
 #pragma unroll
@@ -381,19 +426,24 @@ SDCT_DEV void producer_role(const KParams &p, uint64_t *bars, uint32_t tmem_base
                 w[2 * r] = v.x; w[2 * r + 1] = v.y;
             }
             publish_a(p, bars, tmem_base, lane_field, k, w);   // consumes w: the slot may be refilled now
+            if (VEC == 2) __syncwarp();                        // ... once the partner has read it as well
+            stamp(trp, 0, k, 4);
             issue(k + RING);
+            stamp(trp, 0, k, 7);
         }
     } else {
         // interleaved or unaligned pixels: register prefetch, one 16-word set per stage
         constexpr int PF = STAGES;
         uint32_t w[PF][16];
+        TileWalk wl;   // the tile that is loaded next
+        wl.init(p, 0, 1);
 #pragma unroll
         for (int j = 0; j < PF; j++) {
-            const uint32_t tile = blockIdx.x + j * gridDim.x;
-            if (tile < p.tiles) {
-                const Tile t = tile_of<COMPS>(p, tile);
+            if (wl.tile < p.tiles) {
+                const Tile t = tile_at<COMPS>(p, wl);
                 load_block<COMPS, VEC>(block_pixels<COMPS>(p, t, my_slot), p.pitch, t.comp, w[j]);
             }
+            wl.next(p);
         }
         for (uint32_t u = 0;; u++) {
 #pragma unroll
@@ -403,11 +453,11 @@ SDCT_DEV void producer_role(const KParams &p, uint64_t *bars, uint32_t tmem_base
                 uint32_t cur[16];
 #pragma unroll
                 for (int i = 0; i < 16; i++) cur[i] = w[j][i];
-                const uint32_t next = tile + PF * gridDim.x;
-                if (next < p.tiles) {
-                    const Tile tn = tile_of<COMPS>(p, next);
+                if (wl.tile < p.tiles) {
+                    const Tile tn = tile_at<COMPS>(p, wl);
                     load_block<COMPS, VEC>(block_pixels<COMPS>(p, tn, my_slot), p.pitch, tn.comp, w[j]);
                 }
+                wl.next(p);
                 publish_a(p, bars, tmem_base, lane_field, k, cur);
             }
         }
@@ -417,10 +467,10 @@ SDCT_DEV void producer_role(const KParams &p, uint64_t *bars, uint32_t tmem_base
 // one thread per MMA warp; warp m takes tiles k = m, m + MMA_WARPS, ...
 SDCT_DEV void mma_role(const KParams &p, uint64_t *bars, uint32_t tmem_base, uint64_t bdesc, uint32_t m)
 {
-    const bool no_mma = (p.tc_ablate & 1) != 0;
+    const bool no_mma = (ablate_bits(p) & 1) != 0;
     const uint64_t bd[4] = {bdesc, bdesc + (uint64_t)((2 * B_LBO) >> 4), bdesc + (uint64_t)((4 * B_LBO) >> 4), bdesc + (uint64_t)((6 * B_LBO) >> 4)};
     uint32_t stage = m % STAGES, u = m / STAGES, k = m;
-    const bool tr = (p.tc_ablate & 32) && blockIdx.x == 0;
+    const bool tr = (ablate_bits(p) & 32) && blockIdx.x == 0;
     for (uint32_t tile = blockIdx.x + m * gridDim.x; tile < p.tiles; tile += MMA_WARPS * gridDim.x, k += MMA_WARPS) {
         stamp(tr, 1, k, 0);
         mbar_wait(bars + BAR_A_FULL + stage, u & 1);
@@ -452,12 +502,13 @@ SDCT_DEV void consumer_role(const KParams &p, uint64_t *bars, uint32_t tmem_base
     for (int k = 0; k < 8; k++) scale[k] = make_float2(p.tab[8 * k + 2 * q].x, p.tab[8 * k + 2 * q + 1].x);
     // blocks P, Q of this thread: slots sp0 (+1) in the first 16-lane half, sp0 + 16 (+1) in the second
     const uint32_t sp0 = (L >> 5) * 32u + 2u * g;
-    const uint32_t abl = p.tc_ablate;
-    for (uint32_t k = c;; k += CONSUMER_WGS) {
-        const uint32_t tile = blockIdx.x + k * gridDim.x;
-        if (tile >= p.tiles) break;
+    const uint32_t abl = ablate_bits(p);
+    TileWalk wk;
+    wk.init(p, c, CONSUMER_WGS);
+    for (uint32_t k = c;; k += CONSUMER_WGS, wk.next(p)) {
+        if (wk.tile >= p.tiles) break;
         const uint32_t sd = k % STAGES, ud = k / STAGES;
-        const Tile cur = tile_of<COMPS>(p, tile);
+        const Tile cur = tile_at<COMPS>(p, wk);
         const uint64_t n_first = (uint64_t)p.row0 * p.bpr + cur.n0;
         uint8_t *img = img_base + ((k / CONSUMER_WGS) & 1) * IMG_BYTES;
         const bool tr = (abl & 32) && blockIdx.x == 0 && L == 0;
@@ -597,7 +648,7 @@ static cudaError_t launch_tc(const KParams &p, unsigned grid, cudaStream_t s)
         return cudaGetLastError();                                                                                   \
     } while (0)
     if (p.comps == 1) {
-        if (p.pixel_vec >= 1) SDCT_TC_GO(1, 1); else SDCT_TC_GO(1, 0);
+        if (p.pixel_vec >= 2) SDCT_TC_GO(1, 2); else if (p.pixel_vec >= 1) SDCT_TC_GO(1, 1); else SDCT_TC_GO(1, 0);
     } else {
         if (p.pixel_vec >= 1) SDCT_TC_GO(3, 1); else SDCT_TC_GO(3, 0);
     }
@@ -619,7 +670,7 @@ extern "C" cudaError_t sdct_k_launch_tc(int op, int layout, const KParams *pp, c
     p.chunks = (uint32_t)((blocks + SDCT_TC_TILE - 1) / SDCT_TC_TILE);
     const unsigned long long tiles = (unsigned long long)p.chunks * p.comps * p.frames;
     if (tiles == 0) return cudaSuccess;
-    if (tiles > 0xfffffff0ull) return cudaErrorInvalidConfiguration;
+    if (tiles > 0xffff0000ull) return cudaErrorInvalidConfiguration;   // a TileWalk may step past the end without wrapping
     p.tiles = (uint32_t)tiles;
     { const char *e = getenv("SDCT_TC_ABLATE"); p.tc_ablate = e ? (uint32_t)atoi(e) : 0u; }
     p.div_chunks = make_fastdiv(p.chunks);

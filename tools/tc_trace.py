@@ -31,7 +31,7 @@ for role in range(3):
         row = tr[role, k]
         if row[0] == 0:
             continue
-        rel = [int(x - t0) if x else -1 for x in row[:6]]
+        rel = [int(x - t0) if x else -1 for x in row[:8]]
         d = "" if prev is None else f"  (+{rel[0] - prev} since previous)"
         prev = rel[0]
         print(f"  k={k:3d} " + " ".join(f"{x:8d}" for x in rel) + d)
