@@ -30,22 +30,35 @@
 // TMEM: 3 stages x (128 D columns + 32 A columns) = 480 of 512 columns.
 #include "sdct_io.cuh"
 
+#include <cmath>
 #include <cstdlib>
 
 namespace sdct {
 namespace tc {
 
+#ifndef SDCT_TC_PRODUCER_WGS
+#define SDCT_TC_PRODUCER_WGS 1
+#endif
+constexpr int PRODUCER_WGS = SDCT_TC_PRODUCER_WGS;
 constexpr int CONSUMER_WGS = 2;
 constexpr int MMA_WARPS = 2;                // each issues the MMAs of every MMA_WARPS-th tile (one elected thread)
-constexpr int THREADS = 128 * (1 + CONSUMER_WGS) + 32 * MMA_WARPS;   // producer WG, consumer WGs, MMA warps
-constexpr int MMA_WARP = 4 * (1 + CONSUMER_WGS);
+constexpr int THREADS = 128 * (PRODUCER_WGS + CONSUMER_WGS + 1);   // producer WGs, consumer WGs, the MMA warpgroup (two of its warps issue)
+// setmaxnreg moves registers inside the CTA's own allocation only (THREADS * LAUNCH_REGS <= 65536): what the
+// consumer warpgroups acquire, the producer warpgroups must have released
+constexpr int LAUNCH_REGS = PRODUCER_WGS == 2 ? 96 : 128, PRODUCER_REGS = 80, CONSUMER_REGS = 128, MMA_REGS = 56;
+constexpr bool MOVE_REGS = LAUNCH_REGS < CONSUMER_REGS;
+static_assert(THREADS * LAUNCH_REGS <= 65536, "register file");
+static_assert(!MOVE_REGS || PRODUCER_WGS * (LAUNCH_REGS - PRODUCER_REGS) + (LAUNCH_REGS - MMA_REGS) >= CONSUMER_WGS * (CONSUMER_REGS - LAUNCH_REGS), "setmaxnreg balance");
+constexpr int CONSUMER_WARP = 4 * PRODUCER_WGS;
+constexpr int MMA_WARP = 4 * (PRODUCER_WGS + CONSUMER_WGS);
 constexpr int TILE = SDCT_TC_TILE;          // blocks per tile = TMEM lanes
 constexpr int A_COLS = 32;                  // 64 fp16 per lane
 constexpr int D_COLS = 128;                 // hi digit: columns 0..63, lo digit: 64..127
-constexpr int STAGES = 3;                   // a stage = one A tile + its D tile in TMEM
-constexpr int TMEM_D_OFF = 0, TMEM_A_OFF = STAGES * D_COLS;
+constexpr int A_STAGES = 4, D_STAGES = 3;   // tile k uses A stage k % 4 and D stage k % 3
+constexpr int TMEM_D_OFF = 0, TMEM_A_OFF = D_STAGES * D_COLS;
 constexpr int TMEM_COLS = 512;
-static_assert(TMEM_A_OFF + STAGES * A_COLS <= TMEM_COLS, "TMEM budget");
+static_assert(TMEM_A_OFF + A_STAGES * A_COLS <= TMEM_COLS, "TMEM budget");
+static_assert(A_STAGES % 2 == 0, "an A stage belongs to one producer warpgroup and one MMA warp");
 
 constexpr int B_BYTES = 128 * 64 * 2;       // 16 KiB: N = 128 rows x K = 64 fp16
 constexpr int B_LBO = 128 * 16;             // bytes between the 16-byte K chunks of a row group: 2048
@@ -59,14 +72,19 @@ constexpr int IMG_BYTES = 64 * IMG_C_PITCH > 16 * IMG_B_PITCH ? 64 * IMG_C_PITCH
 constexpr int SMEM_B_OFF = 0;
 constexpr int SMEM_IMG_OFF = B_BYTES;
 // pixel ring of the producer: cp.async lands the raw bytes of RING tiles ahead (8 rows x 128 threads x 8 B each)
-constexpr int RING = 12;
+constexpr int RING = 12 / PRODUCER_WGS;      // tiles in flight per producer warpgroup
 constexpr int RING_TILE_BYTES = 8 * TILE * 8;
 constexpr int SMEM_RING_OFF = SMEM_IMG_OFF + CONSUMER_WGS * 2 * IMG_BYTES;
-constexpr int SMEM_BAR_OFF = SMEM_RING_OFF + RING * RING_TILE_BYTES;
-// barriers (8 B each): a_full[s] producer -> MMA, d_full[s] MMA -> consumer (and "A stage free" -> producer),
-// d_empty[s] consumer -> MMA; then the TMEM base address
-constexpr int BAR_A_FULL = 0, BAR_D_FULL = STAGES, BAR_D_EMPTY = 2 * STAGES;
-constexpr int NUM_BARS = 3 * STAGES;
+constexpr int SMEM_BAR_OFF = SMEM_RING_OFF + PRODUCER_WGS * RING * RING_TILE_BYTES;
+// barriers (8 B each), then the TMEM base address.  mbarrier waits tell phases apart by parity only, so every
+// barrier has ONE waiting agent that visits its phases in order (a waiter that skipped a phase could mistake
+// "phase u - 2 complete" for "phase u complete"):
+//   a_full[k % 4]           producer -> MMA warp k % 2       (128 arrivals)
+//   a_empty[k % 4]          MMA commit -> producer warpgroup k % 2
+//   d_full[k % 2][k % 3]    MMA commit -> consumer warpgroup k % 2
+//   d_empty[k % 2][k % 3]   consumer k % 2 -> the MMA warp of tile k + 3   (128 arrivals)
+constexpr int BAR_A_FULL = 0, BAR_A_EMPTY = A_STAGES, BAR_D_FULL = 2 * A_STAGES, BAR_D_EMPTY = 2 * A_STAGES + 2 * D_STAGES;
+constexpr int NUM_BARS = 2 * A_STAGES + 4 * D_STAGES;
 constexpr int SMEM_USED = SMEM_BAR_OFF + NUM_BARS * 8 + 16;
 // more than half of the SM's shared memory: exactly one CTA per SM (it allocates all of TMEM)
 constexpr int SMEM_BYTES = SMEM_USED > 120 * 1024 ? SMEM_USED : 120 * 1024;
@@ -162,19 +180,17 @@ SDCT_DEV void tmem_st32(uint32_t taddr, const uint32_t (&r)[32])
 }
 SDCT_DEV void tmem_wait_st() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
 
-// ---- u8 -> fp16 (exact): 0x6400 | b = 1024 + b, minus 1024 ---------------------------------------
-SDCT_DEV uint32_t sub1024_h2(uint32_t h)
-{
-    uint32_t d;
-    asm("sub.rn.f16x2 %0, %1, %2;" : "=r"(d) : "r"(h), "r"(0x64006400u));
-    return d;
-}
+// ---- u8 -> fp16 (exact): the byte zero-extended to 16 bits IS the fp16 subnormal b * 2^-24 -----------------
+// The tensor core multiplies subnormal inputs exactly, every product and partial sum is 2^-24 times an integer
+// below 2^24, so D is the exact integer result scaled by 2^-24; the power of two is folded into the quantiser
+// scale (sdct_k_launch_tc) and the levels are bit for bit those of the unscaled definition.
+constexpr int A_SCALE_LOG2 = 24;
 SDCT_DEV void bytes_to_half(const uint32_t (&w)[16], uint32_t (&h)[32])
 {
 #pragma unroll
     for (int i = 0; i < 16; i++) {
-        h[2 * i] = sub1024_h2(__byte_perm(w[i], 0x64646464u, 0x5140));      // pixels 4i, 4i+1
-        h[2 * i + 1] = sub1024_h2(__byte_perm(w[i], 0x64646464u, 0x5342));  // pixels 4i+2, 4i+3
+        h[2 * i] = __byte_perm(w[i], 0u, 0x4140);      // pixels 4i, 4i+1
+        h[2 * i + 1] = __byte_perm(w[i], 0u, 0x4342);  // pixels 4i+2, 4i+3
     }
 }
 
@@ -339,11 +355,11 @@ SDCT_DEV void chunk_levels(const float (&hi)[16], const float (&lo)[16], const F
 }
 
 // ---- roles -------------------------------------------------------------------------------------------
-// The CTA's k-th tile is global tile blockIdx.x + k * gridDim.x; it uses stage k % STAGES (use count
-// u = k / STAGES), consumer warpgroup k % CONSUMER_WGS and MMA warp k % MMA_WARPS.  A barrier is waited on
-// with the parity of the use count when the waiter needs phase u itself (a_full, d_full for the consumer)
-// and with the opposite parity when it needs phase u - 1 (d_empty; d_full for the producer: the MMAs of
-// the stage's previous tile have read A); a fresh barrier passes the opposite-parity wait.
+// The CTA's k-th tile is global tile blockIdx.x + k * gridDim.x.  It is produced by producer warpgroup k % 2,
+// multiplied by MMA warp k % 2 and stored by consumer warpgroup k % 2, through A stage k % 4 and D stage k % 3
+// (TMEM: 4 * 32 + 3 * 128 = 512 columns).  A barrier is waited on with the parity of its own phase count
+// when the waiter needs that phase (a_full, d_full) and with the opposite parity when it needs the phase
+// before (a_empty: the MMAs of tile k - 4 have read the A stage); a fresh barrier passes the latter.
 
 SDCT_DEV void cp_async8(void *smem, const void *gmem)
 {
@@ -359,12 +375,12 @@ template <int N> SDCT_DEV void cp_async_wait() { asm volatile("cp.async.wait_gro
 // A rows of one tile: the thread's 64 pixels (16 words) -> fp16 -> its TMEM lane of the stage's A columns
 SDCT_DEV void publish_a(const KParams &p, uint64_t *bars, uint32_t tmem_base, uint32_t lane_field, uint32_t k, const uint32_t (&w)[16])
 {
-    const uint32_t stage = k % STAGES, u = k / STAGES;
+    const uint32_t stage = k % A_STAGES, u = k / A_STAGES;
     const bool tr = (ablate_bits(p) & 32) && blockIdx.x == 0 && threadIdx.x == 0;
     uint32_t h[32];
     bytes_to_half(w, h);
     stamp(tr, 0, k, 0);
-    mbar_wait(bars + BAR_D_FULL + stage, (u & 1) ^ 1);   // the MMAs of tile k - STAGES have completed: A[stage] is free
+    mbar_wait(bars + BAR_A_EMPTY + stage, (u & 1) ^ 1);   // the MMAs of tile k - A_STAGES have completed: A[stage] is free
     fence_after();
     stamp(tr, 0, k, 1);
     if (!(ablate_bits(p) & 2)) {
@@ -378,8 +394,9 @@ SDCT_DEV void publish_a(const KParams &p, uint64_t *bars, uint32_t tmem_base, ui
 }
 
 template <int COMPS, int VEC>
-SDCT_DEV void producer_role(const KParams &p, uint64_t *bars, uint32_t tmem_base, uint8_t *ring, uint32_t L, uint32_t lane_field)
+SDCT_DEV void producer_role(const KParams &p, uint64_t *bars, uint32_t tmem_base, uint8_t *ring, uint32_t pw, uint32_t L, uint32_t lane_field)
 {
+    // warpgroup pw produces the CTA's tiles k = pw, pw + PRODUCER_WGS, ...; j counts its own tiles
     const uint32_t my_slot = slot_of_lane(L);
     if (COMPS == 1 && VEC >= 1) {
         // aligned single-plane rows: cp.async ring, RING tiles ahead; row r of the block in slot s lies at
@@ -393,13 +410,13 @@ SDCT_DEV void producer_role(const KParams &p, uint64_t *bars, uint32_t tmem_base
         uint8_t *copy_dst = ring + copy_slot * 8 + half * 4 * (TILE * 8);
         const uint64_t row_off = (uint64_t)(half * 4) * p.pitch;
         TileWalk wi;   // the tile whose copies are issued next
-        wi.init(p, 0, 1);
-        auto issue = [&](uint32_t k) {
+        wi.init(p, pw, PRODUCER_WGS);
+        auto issue = [&](uint32_t j) {
             const bool live = wi.tile < p.tiles && !(ablate_bits(p) & 16);
             if (live) {
                 const Tile t = tile_at<COMPS>(p, wi);
                 const uint8_t *px = block_pixels<COMPS>(p, t, copy_slot) + row_off;
-                uint8_t *dst = copy_dst + (k % RING) * RING_TILE_BYTES;
+                uint8_t *dst = copy_dst + (j % RING) * RING_TILE_BYTES;
 #pragma unroll
                 for (int r = 0; r < ROWS; r++, px += p.pitch) {
                     if (VEC == 2) cp_async16(dst + r * (TILE * 8), px);
@@ -409,16 +426,16 @@ SDCT_DEV void producer_role(const KParams &p, uint64_t *bars, uint32_t tmem_base
             wi.next(p);
             cp_async_commit();   // one group per tile, empty past the end, so that wait_group counts stay static
         };
-        for (uint32_t k = 0; k < RING; k++) issue(k);
-        uint32_t tile = blockIdx.x;
-        for (uint32_t k = 0;; k++, tile += gridDim.x) {
+        for (uint32_t j = 0; j < RING; j++) issue(j);
+        uint32_t tile = blockIdx.x + pw * gridDim.x;
+        for (uint32_t j = 0, k = pw;; j++, k += PRODUCER_WGS, tile += PRODUCER_WGS * gridDim.x) {
             if (tile >= p.tiles) return;
             const bool trp = (ablate_bits(p) & 32) && blockIdx.x == 0 && threadIdx.x == 0;
             stamp(trp, 0, k, 5);
             cp_async_wait<RING - 1>();   // this thread's copies of tile k have landed
             if (VEC == 2) __syncwarp();  // ... and its partner's
             stamp(trp, 0, k, 6);
-            const uint8_t *src = mine + (k % RING) * RING_TILE_BYTES;
+            const uint8_t *src = mine + (j % RING) * RING_TILE_BYTES;
             uint32_t w[16];
 #pragma unroll
             for (int r = 0; r < 8; r++) {
@@ -428,15 +445,15 @@ SDCT_DEV void producer_role(const KParams &p, uint64_t *bars, uint32_t tmem_base
             publish_a(p, bars, tmem_base, lane_field, k, w);   // consumes w: the slot may be refilled now
             if (VEC == 2) __syncwarp();                        // ... once the partner has read it as well
             stamp(trp, 0, k, 4);
-            issue(k + RING);
+            issue(j + RING);
             stamp(trp, 0, k, 7);
         }
     } else {
         // interleaved or unaligned pixels: register prefetch, one 16-word set per stage
-        constexpr int PF = STAGES;
+        constexpr int PF = 2;
         uint32_t w[PF][16];
         TileWalk wl;   // the tile that is loaded next
-        wl.init(p, 0, 1);
+        wl.init(p, pw, PRODUCER_WGS);
 #pragma unroll
         for (int j = 0; j < PF; j++) {
             if (wl.tile < p.tiles) {
@@ -448,7 +465,7 @@ SDCT_DEV void producer_role(const KParams &p, uint64_t *bars, uint32_t tmem_base
         for (uint32_t u = 0;; u++) {
 #pragma unroll
             for (int j = 0; j < PF; j++) {
-                const uint32_t k = u * PF + j, tile = blockIdx.x + k * gridDim.x;
+                const uint32_t k = pw + (u * PF + j) * PRODUCER_WGS, tile = blockIdx.x + k * gridDim.x;
                 if (tile >= p.tiles) return;
                 uint32_t cur[16];
 #pragma unroll
@@ -469,26 +486,27 @@ SDCT_DEV void mma_role(const KParams &p, uint64_t *bars, uint32_t tmem_base, uin
 {
     const bool no_mma = (ablate_bits(p) & 1) != 0;
     const uint64_t bd[4] = {bdesc, bdesc + (uint64_t)((2 * B_LBO) >> 4), bdesc + (uint64_t)((4 * B_LBO) >> 4), bdesc + (uint64_t)((6 * B_LBO) >> 4)};
-    uint32_t stage = m % STAGES, u = m / STAGES, k = m;
+    uint32_t k = m;
     const bool tr = (ablate_bits(p) & 32) && blockIdx.x == 0;
     for (uint32_t tile = blockIdx.x + m * gridDim.x; tile < p.tiles; tile += MMA_WARPS * gridDim.x, k += MMA_WARPS) {
+        const uint32_t sa = k % A_STAGES, ua = k / A_STAGES, sd = k % D_STAGES;
         stamp(tr, 1, k, 0);
-        mbar_wait(bars + BAR_A_FULL + stage, u & 1);
+        mbar_wait(bars + BAR_A_FULL + sa, ua & 1);
         stamp(tr, 1, k, 1);
-        mbar_wait(bars + BAR_D_EMPTY + stage, (u & 1) ^ 1);
+        if (k >= D_STAGES)   // tile k - 3 (other parity: the other consumer warpgroup) has left the D stage
+            mbar_wait(bars + BAR_D_EMPTY + ((k + 1) & 1) * D_STAGES + sd, ((k - D_STAGES) / (2 * D_STAGES)) & 1);
         fence_after();
         stamp(tr, 1, k, 2);
-        const uint32_t tA = tmem_base + TMEM_A_OFF + stage * A_COLS, tD = tmem_base + TMEM_D_OFF + stage * D_COLS;
+        const uint32_t tA = tmem_base + TMEM_A_OFF + sa * A_COLS, tD = tmem_base + TMEM_D_OFF + sd * D_COLS;
         if (!no_mma) {
 #pragma unroll
             for (int ks = 0; ks < 4; ks++)   // K = 16 pixels per instruction: 8 TMEM columns of A, 2 K-chunks of B
                 mma_f16_ts(tD, tA + 8 * ks, bd[ks], IDESC, ks);
         }
         stamp(tr, 1, k, 3);
-        mma_commit(bars + BAR_D_FULL + stage);
+        mma_commit(bars + BAR_A_EMPTY + sa);
+        mma_commit(bars + BAR_D_FULL + (k & 1) * D_STAGES + sd);
         stamp(tr, 1, k, 4);
-        stage += MMA_WARPS;
-        if (stage >= STAGES) { stage -= STAGES; u++; }
     }
 }
 
@@ -507,16 +525,17 @@ SDCT_DEV void consumer_role(const KParams &p, uint64_t *bars, uint32_t tmem_base
     wk.init(p, c, CONSUMER_WGS);
     for (uint32_t k = c;; k += CONSUMER_WGS, wk.next(p)) {
         if (wk.tile >= p.tiles) break;
-        const uint32_t sd = k % STAGES, ud = k / STAGES;
+        const uint32_t sd = k % D_STAGES, ud = k / (2 * D_STAGES);
+        uint64_t *d_full = bars + BAR_D_FULL + c * D_STAGES + sd, *d_empty = bars + BAR_D_EMPTY + c * D_STAGES + sd;
         const Tile cur = tile_at<COMPS>(p, wk);
         const uint64_t n_first = (uint64_t)p.row0 * p.bpr + cur.n0;
         uint8_t *img = img_base + ((k / CONSUMER_WGS) & 1) * IMG_BYTES;
         const bool tr = (abl & 32) && blockIdx.x == 0 && L == 0;
         stamp(tr, 2, k, 0);
-        mbar_wait(bars + BAR_D_FULL + sd, ud & 1);
+        mbar_wait(d_full, ud & 1);
         fence_after();
         stamp(tr, 2, k, 1);
-        if (abl & 4) { fence_before(); mbar_arrive(bars + BAR_D_EMPTY + sd); continue; }
+        if (abl & 4) { fence_before(); mbar_arrive(d_empty); continue; }
 
         // four chunks of 32 columns x 16 lanes; the TMEM load of chunk c+1 is in flight while chunk c is quantised
         float hiA[16], loA[16], hiB[16], loB[16];
@@ -534,7 +553,7 @@ SDCT_DEV void consumer_role(const KParams &p, uint64_t *bars, uint32_t tmem_base
                 tmem_ld_16x256b_x4(tn + 64, NLO);                                                                     \
             } else {   /* every load of this thread has landed: hand the D stage back to the MMA warp */              \
                 fence_before();                                                                                       \
-                mbar_arrive(bars + BAR_D_EMPTY + sd);                                                                 \
+                mbar_arrive(d_empty);                                                                                 \
                 stamp(tr, 2, k, 2);                                                                                   \
             }                                                                                                         \
             F2 bp[4], bq[4];                                                                                          \
@@ -587,8 +606,11 @@ __global__ void __launch_bounds__(THREADS, 1) forward_tc_kernel(const __grid_con
         for (int i = threadIdx.x; i < B_BYTES / 16; i += THREADS) dst[i] = __ldg(src + i);
     }
     if (threadIdx.x == 0) {
-        for (int i = 0; i < STAGES; i++) {
+        for (int i = 0; i < A_STAGES; i++) {
             mbar_init(bars + BAR_A_FULL + i, 128);
+            mbar_init(bars + BAR_A_EMPTY + i, 1);
+        }
+        for (int i = 0; i < 2 * D_STAGES; i++) {
             mbar_init(bars + BAR_D_FULL + i, 1);
             mbar_init(bars + BAR_D_EMPTY + i, 128);
         }
@@ -602,13 +624,18 @@ __global__ void __launch_bounds__(THREADS, 1) forward_tc_kernel(const __grid_con
     const uint32_t tmem_base = *tmem_slot;
     const uint32_t lane_field = ((warp & 3u) * 32u) << 16;
 
-    if (warp < 4) {
-        producer_role<COMPS, VEC>(p, bars, tmem_base, smem + SMEM_RING_OFF, threadIdx.x, lane_field);
+    if (warp < CONSUMER_WARP) {
+        if (MOVE_REGS) asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(PRODUCER_REGS));
+        const uint32_t pw = warp >> 2;
+        producer_role<COMPS, VEC>(p, bars, tmem_base, smem + SMEM_RING_OFF + pw * RING * RING_TILE_BYTES, pw, threadIdx.x & 127, lane_field);
     } else if (warp < MMA_WARP) {
-        const uint32_t c = (warp >> 2) - 1;
+        if (MOVE_REGS) asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(CONSUMER_REGS));
+        const uint32_t c = (warp - CONSUMER_WARP) >> 2;
         consumer_role<LAYOUT, COMPS>(p, bars, tmem_base, smem + SMEM_IMG_OFF + c * 2 * IMG_BYTES, c, threadIdx.x & 127, lane_field);
-    } else if (lane == 0) {
-        mma_role(p, bars, tmem_base, b_descriptor(smem_u32(smem + SMEM_B_OFF)), warp - MMA_WARP);
+    } else {
+        if (MOVE_REGS) asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(MMA_REGS));
+        if (warp < MMA_WARP + MMA_WARPS && lane == 0)
+            mma_role(p, bars, tmem_base, b_descriptor(smem_u32(smem + SMEM_B_OFF)), warp - MMA_WARP);
     }
     fence_before();
     __syncthreads();
@@ -673,6 +700,7 @@ extern "C" cudaError_t sdct_k_launch_tc(int op, int layout, const KParams *pp, c
     if (tiles > 0xffff0000ull) return cudaErrorInvalidConfiguration;   // a TileWalk may step past the end without wrapping
     p.tiles = (uint32_t)tiles;
     { const char *e = getenv("SDCT_TC_ABLATE"); p.tc_ablate = e ? (uint32_t)atoi(e) : 0u; }
+    for (int c = 0; c < 64; c++) p.tab[c].x = p.tab[c].y = ldexpf(p.tab[c].x, tc::A_SCALE_LOG2);   // see bytes_to_half
     p.div_chunks = make_fastdiv(p.chunks);
     p.div_bpr = make_fastdiv(p.bpr);
     const unsigned sms = p.sm_count ? p.sm_count : 148u;

@@ -436,7 +436,8 @@ def test_tensor_core_forward_is_bit_exact_to_its_cpu_restatement(ctx, oracle, la
     Byte-identical to oracle mode TENSOR (which proves the fp32 tensor-core accumulation is exact
     for these bounded integer sums), on aligned, ragged (tail tile), stereo and RGB inputs."""
     for (h, w, kind, scale) in ((512, 512, "rand", 1), (512, 512, "smooth", 8), (1080 - 1080 % 8, 1920, "rand", 255),
-                                (8, 64, "rand", 8), (24, 192, "smooth", 64), (72, 1088 - 1088 % 64, "rand", 16)):
+                                (8, 64, "rand", 8), (24, 192, "smooth", 64), (72, 1088 - 1088 % 64, "rand", 16),
+                                (8 * 1080, 1920, "rand", 64)):   # 2025 tiles: every CTA walks ~14 tiles through all stages
         img = make_image(kind, h, w, seed=h + w)
         lut = ol.lut(scale)
         got = gpu_forward(ctx, img, lut, layout, sd.TENSOR)
