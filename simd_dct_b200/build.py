@@ -44,6 +44,8 @@ def build(force: bool = False, verbose: bool = False) -> str:
         stem = os.path.splitext(src)[0] + ("" if part is None else ".part%d" % part)
         obj = os.path.join(objdir, stem + ".o")
         cmd = [nvcc] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ([] if part is None else ["-DSDCT_PART=%d" % part])
+        if os.environ.get("SDCT_NVCC_DEFS"):         # experiments: extra -D switches
+            cmd += ["-D" + d for d in os.environ["SDCT_NVCC_DEFS"].split(",")]
         if os.environ.get("SDCT_TC_TRACE") == "1":   # profiling build: role stamps + ablation switches in sdct_tc.cu
             cmd.append("-DSDCT_TC_TRACE=1")
         cmd += ["-c", os.path.join(CSRC, src), "-o", obj]

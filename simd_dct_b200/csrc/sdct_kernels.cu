@@ -17,6 +17,9 @@
 // This file is compiled once per SDCT_PART (simd_dct_b200/build.py) so that the template
 // instantiations build in parallel: part 0 = dispatcher + self-test kernel, parts 1..8 = one
 // (operation, layout / mode) family each.
+#ifndef SDCT_CONV_MAGIC
+#define SDCT_CONV_MAGIC 0
+#endif
 #ifndef SDCT_PART
 #error "compile with -DSDCT_PART=<0..8>"
 #endif
@@ -127,7 +130,14 @@ SDCT_DEV void forward_pair(const uint32_t wp[16], const uint32_t wq[16], const f
 {
 #pragma unroll
     for (int i = 0; i < 64; i++) {
+#if SDCT_CONV_MAGIC
+        // 2^23 + byte assembled by PRMT (ALU pipe), minus 2^23 (exact) on the FMA pipe: no XU conversion
+        const uint32_t sel = 0x7540u | (uint32_t)(i & 3);
+        const F2 m = make_float2(__uint_as_float(__byte_perm(wp[i >> 2], 0x4B000000u, sel)), __uint_as_float(__byte_perm(wq[i >> 2], 0x4B000000u, sel)));
+        const F2 x = sub2(m, splat(8388608.f));
+#else
         const F2 x = make_float2(byte_to_float(wp[i >> 2], i & 3), byte_to_float(wq[i >> 2], i & 3));
+#endif
         b[i] = (MODE == SDCT_K_EXACT && LAYOUT != SDCT_K_LAYOUT_B) ? div255(x) : x;
     }
     if (MODE == SDCT_K_FAST) {

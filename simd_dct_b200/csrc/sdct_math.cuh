@@ -16,7 +16,8 @@
 //
 // ptxas 12.9 contracts `mul.rn.f32x2` + `add.rn.f32x2` into FFMA2 even though both carry .rn and
 // --fmad=false is given (it does not do that to the scalar forms).  In the EXACT graphs every add
-// that consumes a product is therefore issued as two scalar FADDs on the halves (sadd/ssub below);
+// that consumes a product is therefore protected (mulx/sadd/ssub below: either the product becomes an
+// unfusable fma(a, k, -0.0), or the add is issued as two scalar FADDs on the halves);
 // tests/test_gpu_parity.py::test_dct8_bitwise checks the result bit for bit against the oracle.
 #pragma once
 #include <cstdint>
@@ -66,56 +67,64 @@ SDCT_DEV F2 fma2(F2 a, F2 b, F2 c)
 SDCT_DEV F2 splat(float k) { return make_float2(k, k); }
 SDCT_DEV F2 mulk(F2 a, float k) { return mul2(a, splat(k)); }
 SDCT_DEV F2 fmak(float k, F2 a, F2 c) { return fma2(a, splat(k), c); }   // k*a + c
-// two scalar instructions: the only safe consumer of a packed product in the EXACT graphs
-SDCT_DEV F2 sadd(F2 a, F2 b) { return make_float2(__fadd_rn(a.x, b.x), __fadd_rn(a.y, b.y)); }
-SDCT_DEV F2 ssub(F2 a, F2 b) { return make_float2(__fsub_rn(a.x, b.x), __fsub_rn(a.y, b.y)); }
+// EXACT graphs, two ways to keep ptxas from contracting a packed product into the add that consumes it:
+//   FP = true : the product is issued as fma(a, k, -0.0), which is fl(a * k) bit for bit (x + -0.0 == x for
+//               every x, signed zeros included) and cannot be fused any further, so the add stays a packed
+//               FADD2.  The -0.0 comes from constant memory: ptxas must not know its value, or it would
+//               simplify the FMA back into the multiply it is allowed to fuse.  (scalar-order graph: -12 %)
+//   FP = false: packed multiply, the add as two scalar FADDs on the halves.  (AVX-order graph: measured
+//               3 % faster than FP = true, its outer adds see two sums and are packed anyway)
+static __constant__ float c_neg_zero = -0.0f;
+template <bool FP> SDCT_DEV F2 mulx(F2 a, float k) { return FP ? fma2(a, splat(k), splat(c_neg_zero)) : mulk(a, k); }
+template <bool FP> SDCT_DEV F2 sadd(F2 a, F2 b) { return FP ? add2(a, b) : make_float2(__fadd_rn(a.x, b.x), __fadd_rn(a.y, b.y)); }
+template <bool FP> SDCT_DEV F2 ssub(F2 a, F2 b) { return FP ? sub2(a, b) : make_float2(__fsub_rn(a.x, b.x), __fsub_rn(a.y, b.y)); }
 
 // first butterfly stage: packed when the inputs are not products (converted pixels), scalar when
 // they are (the second pass reads the first pass's K_N * (...) results)
-template <bool PROD_IN> SDCT_DEV F2 add_in(F2 a, F2 b) { return PROD_IN ? sadd(a, b) : add2(a, b); }
-template <bool PROD_IN> SDCT_DEV F2 sub_in(F2 a, F2 b) { return PROD_IN ? ssub(a, b) : sub2(a, b); }
+template <bool PROD_IN, bool FP> SDCT_DEV F2 add_in(F2 a, F2 b) { return PROD_IN ? sadd<FP>(a, b) : add2(a, b); }
+template <bool PROD_IN, bool FP> SDCT_DEV F2 sub_in(F2 a, F2 b) { return PROD_IN ? ssub<FP>(a, b) : sub2(a, b); }
 
 // ---- 8-point forward, reference scalar order (:148-171); v[0], v[S], ... v[7S] ----------------
 template <int S, bool PROD_IN>
 SDCT_DEV void dct8_scalar(F2 *v)
 {
-    const F2 s07 = add_in<PROD_IN>(v[0], v[7 * S]), s16 = add_in<PROD_IN>(v[S], v[6 * S]);
-    const F2 s25 = add_in<PROD_IN>(v[2 * S], v[5 * S]), s34 = add_in<PROD_IN>(v[3 * S], v[4 * S]);
-    const F2 d07 = sub_in<PROD_IN>(v[0], v[7 * S]), d61 = sub_in<PROD_IN>(v[6 * S], v[S]);
-    const F2 d25 = sub_in<PROD_IN>(v[2 * S], v[5 * S]), d43 = sub_in<PROD_IN>(v[4 * S], v[3 * S]);
+    const F2 s07 = add_in<PROD_IN, true>(v[0], v[7 * S]), s16 = add_in<PROD_IN, true>(v[S], v[6 * S]);
+    const F2 s25 = add_in<PROD_IN, true>(v[2 * S], v[5 * S]), s34 = add_in<PROD_IN, true>(v[3 * S], v[4 * S]);
+    const F2 d07 = sub_in<PROD_IN, true>(v[0], v[7 * S]), d61 = sub_in<PROD_IN, true>(v[6 * S], v[S]);
+    const F2 d25 = sub_in<PROD_IN, true>(v[2 * S], v[5 * S]), d43 = sub_in<PROD_IN, true>(v[4 * S], v[3 * S]);
     const F2 pp = add2(s07, s34), pm = sub2(s07, s34), qq = add2(s16, s25), qm = sub2(s16, s25);
 
-    v[0] = mulk(add2(pp, qq), SDCT_KN);
-    v[2 * S] = mulk(sadd(mulk(pm, SDCT_KB), mulk(qm, SDCT_KE)), SDCT_KN);
-    v[4 * S] = mulk(sub2(pp, qq), SDCT_KN);
-    v[6 * S] = mulk(ssub(mulk(pm, SDCT_KE), mulk(qm, SDCT_KB)), SDCT_KN);
+    v[0] = mulx<true>(add2(pp, qq), SDCT_KN);
+    v[2 * S] = mulx<true>(sadd<true>(mulx<true>(pm, SDCT_KB), mulx<true>(qm, SDCT_KE)), SDCT_KN);
+    v[4 * S] = mulx<true>(sub2(pp, qq), SDCT_KN);
+    v[6 * S] = mulx<true>(ssub<true>(mulx<true>(pm, SDCT_KE), mulx<true>(qm, SDCT_KB)), SDCT_KN);
     // odd outputs, left to right: ((t0 op t1) op t2) op t3 - every add has a product operand
-    v[S] = mulk(ssub(sadd(ssub(mulk(d07, SDCT_KA), mulk(d61, SDCT_KC)), mulk(d25, SDCT_KD)), mulk(d43, SDCT_KF)), SDCT_KN);
-    v[3 * S] = mulk(sadd(ssub(sadd(mulk(d07, SDCT_KC), mulk(d61, SDCT_KF)), mulk(d25, SDCT_KA)), mulk(d43, SDCT_KD)), SDCT_KN);
-    v[5 * S] = mulk(ssub(sadd(sadd(mulk(d07, SDCT_KD), mulk(d61, SDCT_KA)), mulk(d25, SDCT_KF)), mulk(d43, SDCT_KC)), SDCT_KN);
-    v[7 * S] = mulk(sadd(sadd(sadd(mulk(d07, SDCT_KF), mulk(d61, SDCT_KD)), mulk(d25, SDCT_KC)), mulk(d43, SDCT_KA)), SDCT_KN);
+    v[S] = mulx<true>(ssub<true>(sadd<true>(ssub<true>(mulx<true>(d07, SDCT_KA), mulx<true>(d61, SDCT_KC)), mulx<true>(d25, SDCT_KD)), mulx<true>(d43, SDCT_KF)), SDCT_KN);
+    v[3 * S] = mulx<true>(sadd<true>(ssub<true>(sadd<true>(mulx<true>(d07, SDCT_KC), mulx<true>(d61, SDCT_KF)), mulx<true>(d25, SDCT_KA)), mulx<true>(d43, SDCT_KD)), SDCT_KN);
+    v[5 * S] = mulx<true>(ssub<true>(sadd<true>(sadd<true>(mulx<true>(d07, SDCT_KD), mulx<true>(d61, SDCT_KA)), mulx<true>(d25, SDCT_KF)), mulx<true>(d43, SDCT_KC)), SDCT_KN);
+    v[7 * S] = mulx<true>(sadd<true>(sadd<true>(sadd<true>(mulx<true>(d07, SDCT_KF), mulx<true>(d61, SDCT_KD)), mulx<true>(d25, SDCT_KC)), mulx<true>(d43, SDCT_KA)), SDCT_KN);
 }
 
 // ---- 8-point forward, reference AVX2 lane order (:2160-2183); X3 = true keeps :2181's sign -----
 template <int S, bool PROD_IN, bool X3>
 SDCT_DEV void dct8_paired(F2 *v)
 {
-    const F2 s07 = add_in<PROD_IN>(v[0], v[7 * S]), s16 = add_in<PROD_IN>(v[S], v[6 * S]);
-    const F2 s25 = add_in<PROD_IN>(v[2 * S], v[5 * S]), s34 = add_in<PROD_IN>(v[3 * S], v[4 * S]);
-    const F2 d07 = sub_in<PROD_IN>(v[0], v[7 * S]), d61 = sub_in<PROD_IN>(v[6 * S], v[S]);
-    const F2 d25 = sub_in<PROD_IN>(v[2 * S], v[5 * S]), d43 = sub_in<PROD_IN>(v[4 * S], v[3 * S]);
+    const F2 s07 = add_in<PROD_IN, false>(v[0], v[7 * S]), s16 = add_in<PROD_IN, false>(v[S], v[6 * S]);
+    const F2 s25 = add_in<PROD_IN, false>(v[2 * S], v[5 * S]), s34 = add_in<PROD_IN, false>(v[3 * S], v[4 * S]);
+    const F2 d07 = sub_in<PROD_IN, false>(v[0], v[7 * S]), d61 = sub_in<PROD_IN, false>(v[6 * S], v[S]);
+    const F2 d25 = sub_in<PROD_IN, false>(v[2 * S], v[5 * S]), d43 = sub_in<PROD_IN, false>(v[4 * S], v[3 * S]);
     const F2 pp = add2(s07, s34), pm = sub2(s07, s34), qq = add2(s16, s25), qm = sub2(s16, s25);
 
-    v[0] = mulk(add2(pp, qq), SDCT_KN);
-    v[4 * S] = mulk(sub2(pp, qq), SDCT_KN);
-    v[2 * S] = mulk(sadd(mulk(pm, SDCT_KB), mulk(qm, SDCT_KE)), SDCT_KN);
-    v[6 * S] = mulk(ssub(mulk(pm, SDCT_KE), mulk(qm, SDCT_KB)), SDCT_KN);
+    v[0] = mulx<false>(add2(pp, qq), SDCT_KN);
+    v[4 * S] = mulx<false>(sub2(pp, qq), SDCT_KN);
+    v[2 * S] = mulx<false>(sadd<false>(mulx<false>(pm, SDCT_KB), mulx<false>(qm, SDCT_KE)), SDCT_KN);
+    v[6 * S] = mulx<false>(ssub<false>(mulx<false>(pm, SDCT_KE), mulx<false>(qm, SDCT_KB)), SDCT_KN);
     // odd outputs, pairwise: (t0 op t1) op (t2 op t3); the outer add sees two sums -> packed
-    v[S] = mulk(add2(ssub(mulk(d07, SDCT_KA), mulk(d61, SDCT_KC)), ssub(mulk(d25, SDCT_KD), mulk(d43, SDCT_KF))), SDCT_KN);
-    const F2 x3r = X3 ? sadd(mulk(d25, SDCT_KA), mulk(d43, SDCT_KD)) : ssub(mulk(d25, SDCT_KA), mulk(d43, SDCT_KD));
-    v[3 * S] = mulk(sub2(sadd(mulk(d07, SDCT_KC), mulk(d61, SDCT_KF)), x3r), SDCT_KN);
-    v[5 * S] = mulk(add2(sadd(mulk(d07, SDCT_KD), mulk(d61, SDCT_KA)), ssub(mulk(d25, SDCT_KF), mulk(d43, SDCT_KC))), SDCT_KN);
-    v[7 * S] = mulk(add2(sadd(mulk(d07, SDCT_KF), mulk(d61, SDCT_KD)), sadd(mulk(d25, SDCT_KC), mulk(d43, SDCT_KA))), SDCT_KN);
+    v[S] = mulx<false>(add2(ssub<false>(mulx<false>(d07, SDCT_KA), mulx<false>(d61, SDCT_KC)), ssub<false>(mulx<false>(d25, SDCT_KD), mulx<false>(d43, SDCT_KF))), SDCT_KN);
+    const F2 x3r = X3 ? sadd<false>(mulx<false>(d25, SDCT_KA), mulx<false>(d43, SDCT_KD)) : ssub<false>(mulx<false>(d25, SDCT_KA), mulx<false>(d43, SDCT_KD));
+    v[3 * S] = mulx<false>(sub2(sadd<false>(mulx<false>(d07, SDCT_KC), mulx<false>(d61, SDCT_KF)), x3r), SDCT_KN);
+    v[5 * S] = mulx<false>(add2(sadd<false>(mulx<false>(d07, SDCT_KD), mulx<false>(d61, SDCT_KA)), ssub<false>(mulx<false>(d25, SDCT_KF), mulx<false>(d43, SDCT_KC))), SDCT_KN);
+    v[7 * S] = mulx<false>(add2(sadd<false>(mulx<false>(d07, SDCT_KF), mulx<false>(d61, SDCT_KD)), sadd<false>(mulx<false>(d25, SDCT_KC), mulx<false>(d43, SDCT_KA))), SDCT_KN);
 }
 
 // ---- 8-point forward, FAST (oracle/sdct_oracle.c: sdct_oracle_dct8_fast), unnormalised ---------

@@ -373,7 +373,9 @@ SDCT_DEV void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "mem
 template <int N> SDCT_DEV void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 
 // A rows of one tile: the thread's 64 pixels (16 words) -> fp16 -> its TMEM lane of the stage's A columns
-SDCT_DEV void publish_a(const KParams &p, uint64_t *bars, uint32_t tmem_base, uint32_t lane_field, uint32_t k, const uint32_t (&w)[16])
+// The two halves of publishing a tile's A rows; whatever the caller puts between them (the next copies and
+// their address arithmetic) runs in the shadow of the TMEM store.
+SDCT_DEV void store_a_rows(const KParams &p, uint64_t *bars, uint32_t tmem_base, uint32_t lane_field, uint32_t k, const uint32_t (&w)[16])
 {
     const uint32_t stage = k % A_STAGES, u = k / A_STAGES;
     const bool tr = (ablate_bits(p) & 32) && blockIdx.x == 0 && threadIdx.x == 0;
@@ -383,14 +385,21 @@ SDCT_DEV void publish_a(const KParams &p, uint64_t *bars, uint32_t tmem_base, ui
     mbar_wait(bars + BAR_A_EMPTY + stage, (u & 1) ^ 1);   // the MMAs of tile k - A_STAGES have completed: A[stage] is free
     fence_after();
     stamp(tr, 0, k, 1);
-    if (!(ablate_bits(p) & 2)) {
-        tmem_st32(tmem_base + TMEM_A_OFF + stage * A_COLS + lane_field, h);
-        tmem_wait_st();
-    }
+    if (!(ablate_bits(p) & 2)) tmem_st32(tmem_base + TMEM_A_OFF + stage * A_COLS + lane_field, h);
+}
+SDCT_DEV void signal_a_rows(const KParams &p, uint64_t *bars, uint32_t k)
+{
+    const bool tr = (ablate_bits(p) & 32) && blockIdx.x == 0 && threadIdx.x == 0;
+    tmem_wait_st();
     fence_before();
     stamp(tr, 0, k, 2);
-    mbar_arrive(bars + BAR_A_FULL + stage);
+    mbar_arrive(bars + BAR_A_FULL + k % A_STAGES);
     stamp(tr, 0, k, 3);
+}
+SDCT_DEV void publish_a(const KParams &p, uint64_t *bars, uint32_t tmem_base, uint32_t lane_field, uint32_t k, const uint32_t (&w)[16])
+{
+    store_a_rows(p, bars, tmem_base, lane_field, k, w);
+    signal_a_rows(p, bars, k);
 }
 
 template <int COMPS, int VEC>
@@ -442,11 +451,12 @@ SDCT_DEV void producer_role(const KParams &p, uint64_t *bars, uint32_t tmem_base
                 const uint2 v = *reinterpret_cast<const uint2 *>(src + r * (TILE * 8));
                 w[2 * r] = v.x; w[2 * r + 1] = v.y;
             }
-            publish_a(p, bars, tmem_base, lane_field, k, w);   // consumes w: the slot may be refilled now
-            if (VEC == 2) __syncwarp();                        // ... once the partner has read it as well
+            store_a_rows(p, bars, tmem_base, lane_field, k, w);   // consumes w: the slot may be refilled now
+            if (VEC == 2) __syncwarp();                           // ... once the partner has read it as well
             stamp(trp, 0, k, 4);
             issue(j + RING);
             stamp(trp, 0, k, 7);
+            signal_a_rows(p, bars, k);
         }
     } else {
         // interleaved or unaligned pixels: register prefetch, one 16-word set per stage
