@@ -44,6 +44,9 @@ struct KParams {
     KFastDiv div_chunks, div_bpr;  // tensor-core kernels
     uint32_t tc_ablate;       // profiling only ($SDCT_TC_ABLATE): bit0 no MMA, 1 no A write, 2 no epilogue, 3 no stores, 4 no loads
     const void *tc_matrix;    // tensor-core kernels: the 16 KiB B operand (fp16 digits of 2^22 C(x)C, UMMA canonical layout)
+    // tensor-core kernels, TMA pixel path: CUtensorMap over the pixels as u32[frame][eye][row][W / 4]
+    // (filled in by sdct_k_launch_tc; must stay 64-byte aligned inside the kernel parameter block)
+    alignas(64) unsigned char tc_tensor_map[128];
 };
 
 extern "C" cudaError_t sdct_k_launch(int op, int layout, int mode, int x3, const KParams *p, cudaStream_t s);

@@ -32,6 +32,8 @@
 
 #include <cmath>
 #include <cstdlib>
+#include <cstring>
+#include <cuda.h>   // CUtensorMap and its enums only: the encoder is fetched through cudaGetDriverEntryPoint
 
 namespace sdct {
 namespace tc {
@@ -42,7 +44,7 @@ namespace tc {
 constexpr int PRODUCER_WGS = SDCT_TC_PRODUCER_WGS;
 constexpr int CONSUMER_WGS = 2;
 constexpr int MMA_WARPS = 2;                // each issues the MMAs of every MMA_WARPS-th tile (one elected thread)
-constexpr int THREADS = 128 * (PRODUCER_WGS + CONSUMER_WGS + 1);   // producer WGs, consumer WGs, the MMA warpgroup (two of its warps issue)
+constexpr int THREADS = 128 * (PRODUCER_WGS + CONSUMER_WGS + 1);   // producer WGs, consumer WGs, the MMA warpgroup (two MMA warps, the TMA warp)
 // setmaxnreg moves registers inside the CTA's own allocation only (THREADS * LAUNCH_REGS <= 65536): what the
 // consumer warpgroups acquire, the producer warpgroups must have released
 constexpr int LAUNCH_REGS = PRODUCER_WGS == 2 ? 96 : 128, PRODUCER_REGS = 80, CONSUMER_REGS = 128, MMA_REGS = 56;
@@ -51,6 +53,12 @@ static_assert(THREADS * LAUNCH_REGS <= 65536, "register file");
 static_assert(!MOVE_REGS || PRODUCER_WGS * (LAUNCH_REGS - PRODUCER_REGS) + (LAUNCH_REGS - MMA_REGS) >= CONSUMER_WGS * (CONSUMER_REGS - LAUNCH_REGS), "setmaxnreg balance");
 constexpr int CONSUMER_WARP = 4 * PRODUCER_WGS;
 constexpr int MMA_WARP = 4 * (PRODUCER_WGS + CONSUMER_WGS);
+constexpr int TMA_WARP = MMA_WARP + MMA_WARPS;   // one thread: bulk tensor copies of the pixel tiles (VEC == VEC_TMA)
+constexpr int VEC_TMA = 3;
+#ifndef SDCT_TC_DIRECT_B
+#define SDCT_TC_DIRECT_B 1
+#endif
+constexpr bool DIRECT_B = SDCT_TC_DIRECT_B;
 constexpr int TILE = SDCT_TC_TILE;          // blocks per tile = TMEM lanes
 constexpr int A_COLS = 32;                  // 64 fp16 per lane
 constexpr int D_COLS = 128;                 // hi digit: columns 0..63, lo digit: 64..127
@@ -84,8 +92,14 @@ constexpr int SMEM_BAR_OFF = SMEM_RING_OFF + PRODUCER_WGS * RING * RING_TILE_BYT
 //   d_full[k % 2][k % 3]    MMA commit -> consumer warpgroup k % 2
 //   d_empty[k % 2][k % 3]   consumer k % 2 -> the MMA warp of tile k + 3   (128 arrivals)
 constexpr int BAR_A_FULL = 0, BAR_A_EMPTY = A_STAGES, BAR_D_FULL = 2 * A_STAGES, BAR_D_EMPTY = 2 * A_STAGES + 2 * D_STAGES;
-constexpr int NUM_BARS = 2 * A_STAGES + 4 * D_STAGES;
-constexpr int SMEM_USED = SMEM_BAR_OFF + NUM_BARS * 8 + 16;
+//   ring_full[j % 6]        TMA (complete_tx) -> producer warpgroup; ring_empty[j % 6]: its four warps -> TMA thread
+constexpr int TMA_RING = 6;                       // slots of two 8 KiB boxes: 8 rows x 1024 bytes of this / of the next block row
+constexpr int TMA_BOX_BYTES = 8 * TILE * 8, TMA_SLOT_BYTES = 2 * TMA_BOX_BYTES;
+constexpr int BAR_RING_FULL = 2 * A_STAGES + 4 * D_STAGES, BAR_RING_EMPTY = BAR_RING_FULL + TMA_RING;
+constexpr int NUM_BARS = BAR_RING_EMPTY + TMA_RING;
+static_assert(TMA_RING * TMA_SLOT_BYTES <= PRODUCER_WGS * RING * RING_TILE_BYTES, "the TMA ring lives in the cp.async ring's space");
+constexpr int SMEM_META_OFF = SMEM_BAR_OFF + NUM_BARS * 8 + 16;   // TMA ring: blocks of the tile that lie in the first box
+constexpr int SMEM_USED = SMEM_META_OFF + TMA_RING * 4;
 // more than half of the SM's shared memory: exactly one CTA per SM (it allocates all of TMEM)
 constexpr int SMEM_BYTES = SMEM_USED > 120 * 1024 ? SMEM_USED : 120 * 1024;
 
@@ -141,6 +155,18 @@ SDCT_DEV void mbar_arrive(uint64_t *bar)
 SDCT_DEV void mma_commit(uint64_t *bar)
 {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+
+SDCT_DEV void mbar_expect_tx(uint64_t *bar, uint32_t bytes)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+// one box of the 4-D pixel tensor (u32 x, pixel row, eye, frame) -> shared memory, completion bytes onto the mbarrier
+SDCT_DEV void tma_load_box(void *smem_dst, const void *tensor_map, uint64_t *bar, int32_t x, int32_t y, int32_t eye, int32_t frame)
+{
+    asm volatile("cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];"
+                 ::"r"(smem_u32(smem_dst)), "l"(tensor_map), "r"(smem_u32(bar)), "r"(x), "r"(y), "r"(eye), "r"(frame)
+                 : "memory");
 }
 
 // D[tmem] (+)= A[tmem] * B[smem]^T, kind::f16, fp32 accumulate
@@ -407,7 +433,31 @@ SDCT_DEV void producer_role(const KParams &p, uint64_t *bars, uint32_t tmem_base
 {
     // warpgroup pw produces the CTA's tiles k = pw, pw + PRODUCER_WGS, ...; j counts its own tiles
     const uint32_t my_slot = slot_of_lane(L);
-    if (COMPS == 1 && VEC >= 1) {
+    if (VEC == VEC_TMA) {
+        // The TMA thread (tma_role) lands the tile's pixel rows in ring slot j % TMA_RING: row r of the block in
+        // slot s lies at r * 1024 + s * 8 of the first box while s < split (the blocks left in this block row),
+        // and at r * 1024 + (s - split) * 8 of the second box (the next block row from its left edge) otherwise.
+        // (launched only when PRODUCER_WGS == 1: one warpgroup consumes the ring in tile order)
+        const uint32_t *meta = reinterpret_cast<const uint32_t *>(ring - SMEM_RING_OFF + SMEM_META_OFF);
+        uint32_t tile = blockIdx.x;
+        for (uint32_t k = 0;; k++, tile += gridDim.x) {
+            if (tile >= p.tiles) return;
+            const uint32_t rs = k % TMA_RING, ru = k / TMA_RING;
+            mbar_wait(bars + BAR_RING_FULL + rs, ru & 1);
+            const uint32_t split = meta[rs];
+            const uint8_t *src = ring + rs * TMA_SLOT_BYTES + (my_slot < split ? my_slot * 8 : TMA_BOX_BYTES + (my_slot - split) * 8);
+            uint32_t w[16];
+#pragma unroll
+            for (int r = 0; r < 8; r++) {
+                const uint2 v = *reinterpret_cast<const uint2 *>(src + r * (TILE * 8));
+                w[2 * r] = v.x; w[2 * r + 1] = v.y;
+            }
+            store_a_rows(p, bars, tmem_base, lane_field, k, w);   // consumes w
+            __syncwarp();
+            if ((L & 31) == 0) mbar_arrive(bars + BAR_RING_EMPTY + rs);   // this warp has read the slot
+            signal_a_rows(p, bars, k);
+        }
+    } else if (COMPS == 1 && VEC >= 1) {
         // aligned single-plane rows: cp.async ring, RING tiles ahead; row r of the block in slot s lies at
         // r * 1024 + s * 8.  VEC == 1: a thread copies the eight 8-byte rows of its own block.  VEC == 2 (16-byte
         // aligned rows, even blocks per row): the two threads of an adjacent block pair (lanes L, L ^ 8 of one
@@ -491,6 +541,32 @@ SDCT_DEV void producer_role(const KParams &p, uint64_t *bars, uint32_t tmem_base
     }
 }
 
+// one thread: the bulk tensor copies of the CTA's tiles, TMA_RING tiles ahead of the producer warpgroup
+SDCT_DEV void tma_role(const KParams &p, uint64_t *bars, uint8_t *ring, uint32_t *meta)
+{
+    const void *map = p.tc_tensor_map;
+    TileWalk w;
+    w.init(p, 0, 1);
+    const uint32_t blocks = p.rows * p.bpr;
+    for (uint32_t k = 0; w.tile < p.tiles; k++, w.next(p)) {
+        const uint32_t rs = k % TMA_RING, ru = k / TMA_RING;
+        const uint32_t n0 = w.chunk * TILE, count = min((uint32_t)TILE, blocks - n0);
+        const uint32_t r = fastdiv(n0, p.div_bpr), bx0 = n0 - r * p.bpr;
+        const uint32_t split = min((uint32_t)TILE, p.bpr - bx0);
+        const bool two = count > split;                     // the tile runs on into the next block row
+        const uint32_t row = r + p.row0, row2 = row + 1;
+        const bool stereo = p.eyes == 2;
+        uint8_t *dst = ring + rs * TMA_SLOT_BYTES;
+        uint64_t *full = bars + BAR_RING_FULL + rs;
+        mbar_wait(bars + BAR_RING_EMPTY + rs, (ru & 1) ^ 1);   // the producer has read the slot's previous tile
+        meta[rs] = split;
+        mbar_expect_tx(full, two ? 2 * TMA_BOX_BYTES : TMA_BOX_BYTES);
+        tma_load_box(dst, map, full, (int32_t)(bx0 * 2), (int32_t)((stereo ? row >> 1 : row) * 8), (int32_t)(stereo ? row & 1 : 0), (int32_t)w.fc);
+        if (two)
+            tma_load_box(dst + TMA_BOX_BYTES, map, full, 0, (int32_t)((stereo ? row2 >> 1 : row2) * 8), (int32_t)(stereo ? row2 & 1 : 0), (int32_t)w.fc);
+    }
+}
+
 // one thread per MMA warp; warp m takes tiles k = m, m + MMA_WARPS, ...
 SDCT_DEV void mma_role(const KParams &p, uint64_t *bars, uint32_t tmem_base, uint64_t bdesc, uint32_t m)
 {
@@ -553,7 +629,7 @@ SDCT_DEV void consumer_role(const KParams &p, uint64_t *bars, uint32_t tmem_base
         tmem_ld_16x256b_x4(td, hiA);
         tmem_ld_16x256b_x4(td + 64, loA);
         uint32_t wp[4], wq[4];   // layout A: the 16 output bytes of P and Q collected over two chunks
-#define SDCT_TC_CHUNK(C, HI, LO, NHI, NLO)                                                                            \
+#define SDCT_TC_CHUNK(C, HI, LO, NHI, NLO, DIRECT)                                                                    \
         {                                                                                                             \
             constexpr int half = (C) >> 1, kk = (C) & 1;                                                              \
             tmem_wait_ld(HI, LO);                                                                                     \
@@ -580,17 +656,31 @@ SDCT_DEV void consumer_role(const KParams &p, uint64_t *bars, uint32_t tmem_base
                     _Pragma("unroll") for (int e = 0; e < 2; e++) {                                                   \
                         const uint32_t i = 8 * (4 * kk + k2) + e + 2 * q;                                             \
                         const uint32_t pq = pack_sat(__float_as_uint(e ? bq[k2].y : bq[k2].x), __float_as_uint(e ? bp[k2].y : bp[k2].x), 0u); \
-                        uint8_t *d = LAYOUT == SDCT_K_LAYOUT_B ? img + (sp >> 3) * IMG_B_PITCH + i * 8 + (sp & 7)      \
-                                                               : img + i * IMG_C_PITCH + sp;                          \
+                        uint8_t *d = LAYOUT == SDCT_K_LAYOUT_B                                                         \
+                                         ? ((DIRECT) ? gdst + (sp >> 3) * 512 : img + (sp >> 3) * IMG_B_PITCH) + i * 8 + (sp & 7) \
+                                         : img + i * IMG_C_PITCH + sp;                                                \
                         *reinterpret_cast<uint16_t *>(d) = (uint16_t)pq;                                              \
                     }                                                                                                 \
                 }                                                                                                     \
             }                                                                                                         \
         }
-        SDCT_TC_CHUNK(0, hiA, loA, hiB, loB)
-        SDCT_TC_CHUNK(1, hiB, loB, hiA, loA)
-        SDCT_TC_CHUNK(2, hiA, loA, hiB, loB)
-        SDCT_TC_CHUNK(3, hiB, loB, hiA, loA)
+        // layout B, full tile, 2-byte-aligned output: the (P, Q) byte pairs go straight to global memory (the two
+        // stores of a coefficient pair complete 8-byte runs, L2 merges them into full sectors) - no staging
+        // image, no warpgroup barrier, no flush
+        // (layout C keeps the staging image: its byte pairs would scatter over 64 planes, measured 7 % slower)
+        uint8_t *gdst = cur.coef + n_first * 64;
+        const bool direct = DIRECT_B && LAYOUT == SDCT_K_LAYOUT_B && cur.count == TILE && p.coef_aligned4 && !(abl & 8);
+        if (direct) {
+            SDCT_TC_CHUNK(0, hiA, loA, hiB, loB, true)
+            SDCT_TC_CHUNK(1, hiB, loB, hiA, loA, true)
+            SDCT_TC_CHUNK(2, hiA, loA, hiB, loB, true)
+            SDCT_TC_CHUNK(3, hiB, loB, hiA, loA, true)
+            continue;
+        }
+        SDCT_TC_CHUNK(0, hiA, loA, hiB, loB, false)
+        SDCT_TC_CHUNK(1, hiB, loB, hiA, loA, false)
+        SDCT_TC_CHUNK(2, hiA, loA, hiB, loB, false)
+        SDCT_TC_CHUNK(3, hiB, loB, hiA, loA, false)
 #undef SDCT_TC_CHUNK
         if (LAYOUT != SDCT_K_LAYOUT_A) {
             named_barrier(1 + c);
@@ -624,6 +714,10 @@ __global__ void __launch_bounds__(THREADS, 1) forward_tc_kernel(const __grid_con
             mbar_init(bars + BAR_D_FULL + i, 1);
             mbar_init(bars + BAR_D_EMPTY + i, 128);
         }
+        for (int i = 0; i < TMA_RING; i++) {
+            mbar_init(bars + BAR_RING_FULL + i, 1);
+            mbar_init(bars + BAR_RING_EMPTY + i, 4);
+        }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 0) tmem_alloc(tmem_slot);
@@ -646,6 +740,8 @@ __global__ void __launch_bounds__(THREADS, 1) forward_tc_kernel(const __grid_con
         if (MOVE_REGS) asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(MMA_REGS));
         if (warp < MMA_WARP + MMA_WARPS && lane == 0)
             mma_role(p, bars, tmem_base, b_descriptor(smem_u32(smem + SMEM_B_OFF)), warp - MMA_WARP);
+        else if (VEC == VEC_TMA && warp == TMA_WARP && lane == 0)
+            tma_role(p, bars, smem + SMEM_RING_OFF, reinterpret_cast<uint32_t *>(smem + SMEM_META_OFF));
     }
     fence_before();
     __syncthreads();
@@ -670,8 +766,44 @@ static KFastDiv make_fastdiv(uint32_t d)
     return r;
 }
 
+// The pixels as a 4-D tensor of u32 [frame][eye][pixel row][W / 4] for the TMA path; box = 256 x 8 x 1 x 1 =
+// the 8 rows x 1024 bytes of 128 consecutive blocks of one block row.  Returns false when the geometry does
+// not fit a tensor map (the cp.async path is used instead).
+static bool make_pixel_tensor_map(KParams &p)
+{
+    typedef CUresult (*EncodeFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *,
+                                 const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                 CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+    static EncodeFn encode = nullptr;
+    static bool looked = false;
+    if (!looked) {
+        looked = true;
+        void *fn = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &q) == cudaSuccess && q == cudaDriverEntryPointSuccess)
+            encode = reinterpret_cast<EncodeFn>(fn);
+    }
+    if (!encode || tc::PRODUCER_WGS != 1 || getenv("SDCT_TC_NO_TMA")) return false;
+    if (p.comps != 1 || p.pixel_vec < 2 || p.bpr < (uint32_t)tc::TILE || (p.eyes != 1 && p.eyes != 2)) return false;
+    const uint64_t band_rows = ((uint64_t)p.row0 + p.rows + p.eyes - 1) / p.eyes * 8;   // pixel rows of one eye that the window reaches
+    const uint64_t plane = p.pitch * band_rows;
+    const cuuint64_t dims[4] = {(cuuint64_t)p.bpr * 2, band_rows, p.eyes, p.frames};
+    const cuuint64_t strides[3] = {p.pitch, p.eyes == 2 ? p.eye_stride : plane, p.frames > 1 ? p.pixel_frame_stride : plane * p.eyes};
+    for (int i = 0; i < 3; i++)
+        if (strides[i] == 0 || (strides[i] & 15) || strides[i] >= (1ull << 40)) return false;
+    if (((uintptr_t)p.pixels & 15) || band_rows >= (1ull << 31) || p.frames >= (1u << 31)) return false;
+    const cuuint32_t box[4] = {256, 8, 1, 1}, estr[4] = {1, 1, 1, 1};
+    CUtensorMap map;
+    if (encode(&map, CU_TENSOR_MAP_DATA_TYPE_UINT32, 4, const_cast<uint8_t *>(p.pixels), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+               CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
+        return false;
+    static_assert(sizeof(map) == sizeof(p.tc_tensor_map), "CUtensorMap size");
+    memcpy(p.tc_tensor_map, &map, sizeof(map));
+    return true;
+}
+
 template <int LAYOUT>
-static cudaError_t launch_tc(const KParams &p, unsigned grid, cudaStream_t s)
+static cudaError_t launch_tc(const KParams &p, unsigned grid, bool tma, cudaStream_t s)
 {
 #define SDCT_TC_GO(C, V)                                                                                             \
     do {                                                                                                             \
@@ -685,6 +817,7 @@ static cudaError_t launch_tc(const KParams &p, unsigned grid, cudaStream_t s)
         return cudaGetLastError();                                                                                   \
     } while (0)
     if (p.comps == 1) {
+        if (tma) SDCT_TC_GO(1, tc::VEC_TMA);
         if (p.pixel_vec >= 2) SDCT_TC_GO(1, 2); else if (p.pixel_vec >= 1) SDCT_TC_GO(1, 1); else SDCT_TC_GO(1, 0);
     } else {
         if (p.pixel_vec >= 1) SDCT_TC_GO(3, 1); else SDCT_TC_GO(3, 0);
@@ -715,10 +848,12 @@ extern "C" cudaError_t sdct_k_launch_tc(int op, int layout, const KParams *pp, c
     p.div_bpr = make_fastdiv(p.bpr);
     const unsigned sms = p.sm_count ? p.sm_count : 148u;
     const unsigned grid = (unsigned)(tiles < sms ? tiles : sms);
+    // measured: the TMA pixel path wins for layouts A and B; layout C (staging image + flush) is faster on the cp.async ring
+    const bool tma = layout != SDCT_K_LAYOUT_C && make_pixel_tensor_map(p);
     switch (layout) {
-    case SDCT_K_LAYOUT_A: return launch_tc<SDCT_K_LAYOUT_A>(p, grid, s);
-    case SDCT_K_LAYOUT_B: return launch_tc<SDCT_K_LAYOUT_B>(p, grid, s);
-    case SDCT_K_LAYOUT_C: return launch_tc<SDCT_K_LAYOUT_C>(p, grid, s);
+    case SDCT_K_LAYOUT_A: return launch_tc<SDCT_K_LAYOUT_A>(p, grid, tma, s);
+    case SDCT_K_LAYOUT_B: return launch_tc<SDCT_K_LAYOUT_B>(p, grid, tma, s);
+    case SDCT_K_LAYOUT_C: return launch_tc<SDCT_K_LAYOUT_C>(p, grid, tma, s);
     default: return cudaErrorInvalidValue;
     }
 }

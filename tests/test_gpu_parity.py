@@ -464,3 +464,44 @@ def test_tensor_core_forward_is_bit_exact_to_its_cpu_restatement(ctx, oracle, la
     out = torch.zeros(h * w + 1, dtype=torch.uint8, device="cuda")
     ctx.forward(d[3:], ol.lut(8), job, out=out[1:])
     assert np.array_equal(out[1:].cpu().numpy(), oracle.forward(layout, img, ol.lut(8), mode=ol.MODE_TENSOR))
+
+
+@pytest.mark.parametrize("layout", LAYOUTS)
+def test_tensor_core_wide_images_tma_pixel_path(ctx, oracle, layout):
+    """Images at least 128 blocks wide with 16-byte-aligned rows take the TMA pixel path of sdct_tc.cu (layouts
+    A, B; bulk tensor copies of 8 rows x 1024 bytes, a second box where a tile runs on into the next block
+    row) and, for layout B, the direct byte-pair stores: batch of frames with a ragged tail tile, band
+    window whose first block is not a multiple of 8, padded pitch, two eyes."""
+    f, h, w = 3, 40, 1088            # 136 blocks per row (layout B needs width % 64 == 0): every tile straddles block rows; 680 = 5 * 128 + 40 blocks per frame
+    imgs = np.stack([make_image("rand", h, w, seed=40 + s) for s in range(f)])
+    lut = ol.lut(16)
+    job = sd.dense_job(layout, w, h, frames=f, flags=sd.TENSOR)
+    got = ctx.forward(dev(imgs), lut, job).cpu().numpy().reshape(f, -1)
+    want = [oracle.forward(layout, imgs[k], lut, mode=ol.MODE_TENSOR) for k in range(f)]
+    for k in range(f):
+        assert np.array_equal(got[k], want[k]), (k, np.count_nonzero(got[k] != want[k]))
+    # band window: bands 1..3 of frame 0 only, the rest of the output untouched
+    job = sd.dense_job(layout, w, h, flags=sd.TENSOR, band_begin=1, band_end=4)
+    out = torch.full((h * w,), 0x5A, dtype=torch.uint8, device="cuda")
+    ctx.forward(dev(imgs[0]), lut, job, out=out)
+    expect = np.full(h * w, 0x5A, dtype=np.uint8)
+    bpr = w // 8
+    n0, n1 = 1 * bpr, 4 * bpr
+    if layout == sd.LAYOUT_C:
+        ps = h * w // 64
+        for i in range(64):
+            expect[i * ps + n0:i * ps + n1] = want[0][i * ps + n0:i * ps + n1]
+    else:
+        expect[n0 * 64:n1 * 64] = want[0][n0 * 64:n1 * 64]
+    assert np.array_equal(out.cpu().numpy(), expect)
+    # padded pitch (still 16-byte aligned)
+    pitch = w + 48
+    buf = np.zeros((h, pitch), dtype=np.uint8)
+    buf[:, :w] = imgs[1]
+    job = sd.dense_job(layout, w, h, flags=sd.TENSOR)
+    job.pitch = pitch
+    assert np.array_equal(ctx.forward(dev(buf), lut, job).cpu().numpy(), want[1])
+    if layout == sd.LAYOUT_C:   # two eyes (block rows alternate between the eyes; only layout C has them)
+        img2 = make_image("smooth", 2 * 24, w, seed=91)
+        got2 = gpu_forward(ctx, img2, ol.lut(8), layout, sd.TENSOR, eyes=2)
+        assert np.array_equal(got2, oracle.forward(layout, img2, ol.lut(8), mode=ol.MODE_TENSOR, eyes=2))
