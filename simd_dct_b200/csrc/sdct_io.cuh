@@ -30,6 +30,60 @@ SDCT_DEV Tile tile_info(const KParams &p, uint32_t tile)
     return t;
 }
 
+// ---- division-free tile walk -------------------------------------------------------------------------
+// n / d for any 32-bit n (Granlund-Montgomery, magic computed by make_fastdiv on the host)
+SDCT_DEV uint32_t fastdiv(uint32_t n, const KFastDiv &d)
+{
+    const uint32_t t = __umulhi(n, d.m);
+    return (t + ((n - t) >> d.sh1)) >> d.sh2;
+}
+static inline KFastDiv make_fastdiv(uint32_t d)
+{
+    KFastDiv r;
+    if (d == 0) d = 1;
+    uint32_t l = 0;
+    while ((1ull << l) < d) l++;   // ceil(log2 d)
+    r.m = (uint32_t)((((1ull << l) - d) << 32) / d + 1);
+    r.sh1 = l < 1 ? l : 1;
+    r.sh2 = l > 0 ? l - 1 : 0;
+    return r;
+}
+
+// A persistent CTA's tiles k = first, first + stride, ... are global tiles blockIdx.x + k * gridDim.x.  A walk
+// carries (tile / chunks, tile % chunks) from tile to tile, so that the per-tile bookkeeping has no division.
+// (the launcher rejects tile counts above 0xffff0000, so a walk may step past the end without wrapping)
+struct TileWalk {
+    uint32_t tile, fc, chunk, step, dq, dr;
+    SDCT_DEV void init(const KParams &p, uint32_t first, uint32_t stride)
+    {
+        tile = blockIdx.x + first * gridDim.x;
+        fc = fastdiv(tile, p.div_chunks);
+        chunk = tile - fc * p.chunks;
+        step = stride * gridDim.x;
+        dq = fastdiv(step, p.div_chunks);
+        dr = step - dq * p.chunks;
+    }
+    SDCT_DEV void next(const KParams &p)
+    {
+        tile += step; fc += dq; chunk += dr;
+        if (chunk >= p.chunks) { chunk -= p.chunks; fc++; }
+    }
+};
+
+template <int COMPS, int CB>
+SDCT_DEV Tile tile_at(const KParams &p, const TileWalk &w)
+{
+    Tile t;
+    uint32_t frame = w.fc;
+    t.comp = 0;
+    if (COMPS != 1) { frame = w.fc / COMPS; t.comp = w.fc - frame * COMPS; }
+    t.n0 = w.chunk * CB;
+    t.count = min((uint32_t)CB, p.rows * p.bpr - t.n0);
+    t.pix = p.pixels + (uint64_t)frame * p.pixel_frame_stride;
+    t.coef = p.coefs + (uint64_t)frame * p.coef_frame_stride + (uint64_t)t.comp * p.coef_comp_stride;
+    return t;
+}
+
 // ---- pixel block -> 16 words (row r = words 2r, 2r+1), component extraction fused ----------------
 // VEC: 0 = byte loads, 1 = 8-byte loads, 2 = one 16-byte load per row for the adjacent pair (P, Q)
 template <int COMPS, int VEC>

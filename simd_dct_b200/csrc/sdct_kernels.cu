@@ -54,7 +54,7 @@ SDCT_DEV BlockPos locate(const KParams &p, const Tile &t)
         const uint32_t slot = (LAYOUT == SDCT_K_LAYOUT_A) ? threadIdx.x + k * TB : 2 * threadIdx.x + k;
         b.valid[k] = slot < t.count;
         const uint32_t nl = t.n0 + (b.valid[k] ? slot : 0);  // keep addresses in range
-        const uint32_t r = nl / p.bpr;
+        const uint32_t r = fastdiv(nl, p.div_bpr);
         const uint32_t bx = nl - r * p.bpr;
         const uint32_t row = r + p.row0;
         const uint32_t band = p.eyes == 2 ? row >> 1 : row, eye = p.eyes == 2 ? row & 1 : 0;
@@ -261,17 +261,22 @@ __global__ void __launch_bounds__(SDCT_TB, 3) forward_kernel(const __grid_consta
     extern __shared__ __align__(16) uint8_t smem[];
     constexpr bool PF = prefetchable<COMPS, VEC>();
     uint8_t *stage_in = smem + 2 * STAGE_BYTES;
-    uint32_t tile = blockIdx.x;
+    TileWalk w;   // the tile after the current one (the one whose pixels are prefetched)
+    w.init(p, 0, 1);
+    if (w.tile >= p.tiles) return;
+    Tile t = tile_at<COMPS, CB>(p, w);
     if (PF) {
-        if (tile < p.tiles) prefetch_pair<VEC>(stage_in, locate<LAYOUT>(p, tile_info<CB>(p, tile)), p.pitch);
+        prefetch_pair<VEC>(stage_in, locate<LAYOUT>(p, t), p.pitch);
         cp_async_commit();
     }
-    for (uint32_t it = 0; tile < p.tiles; it++, tile += gridDim.x) {
-        const Tile t = tile_info<CB>(p, tile);
+    w.next(p);
+    for (uint32_t it = 0;; it++, w.next(p)) {
+        const bool more = w.tile < p.tiles;
+        Tile tn = t;
+        if (more) tn = tile_at<COMPS, CB>(p, w);
         uint32_t wp[16], wq[16];
         if (PF) {
-            const uint32_t next = tile + gridDim.x;
-            if (next < p.tiles) prefetch_pair<VEC>(stage_in + ((it + 1) & 1) * IN_STAGE_BYTES, locate<LAYOUT>(p, tile_info<CB>(p, next)), p.pitch);
+            if (more) prefetch_pair<VEC>(stage_in + ((it + 1) & 1) * IN_STAGE_BYTES, locate<LAYOUT>(p, tn), p.pitch);
             cp_async_commit();
             cp_async_wait<1>();
             read_prefetched(stage_in + (it & 1) * IN_STAGE_BYTES, wp, wq);
@@ -284,6 +289,8 @@ __global__ void __launch_bounds__(SDCT_TB, 3) forward_kernel(const __grid_consta
         stage_levels<LAYOUT>(sm, v);
         __syncthreads();
         flush_coefs<LAYOUT, complemented<LAYOUT, MODE>()>(sm, p, t);
+        if (!more) break;
+        t = tn;
     }
 }
 
@@ -602,8 +609,10 @@ extern "C" cudaError_t sdct_k_launch(int op, int layout, int mode, int x3, const
     p.layout = (uint32_t)layout;
     const unsigned long long tiles = (unsigned long long)p.chunks * p.comps * p.frames;
     if (tiles == 0) return cudaSuccess;
-    if (tiles > 0xfffffff0ull) return cudaErrorInvalidConfiguration;
+    if (tiles > 0xffff0000ull) return cudaErrorInvalidConfiguration;
     p.tiles = (uint32_t)tiles;
+    p.div_chunks = make_fastdiv(p.chunks);
+    p.div_bpr = make_fastdiv(p.bpr);
     // persistent CTAs: three per SM (168 registers/thread), each walking tiles blockIdx.x, +grid, ...
     const unsigned resident = 3u * (p.sm_count ? p.sm_count : 148u);
     const unsigned grid = (unsigned)(tiles < resident ? tiles : resident);

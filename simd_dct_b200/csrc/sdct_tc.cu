@@ -251,47 +251,6 @@ SDCT_DEV void tmem_wait_ld(float (&a)[16], float (&b)[16])
 // the two lanes one 16x256b load hands to a thread (g, g + 8) are adjacent blocks.
 SDCT_DEV uint32_t slot_of_lane(uint32_t L) { return (L & ~15u) | ((L & 7u) << 1) | ((L >> 3) & 1u); }
 
-// n / d for any 32-bit n (Granlund-Montgomery, magic computed by sdct_k_launch_tc)
-SDCT_DEV uint32_t fastdiv(uint32_t n, const KFastDiv &d)
-{
-    const uint32_t t = __umulhi(n, d.m);
-    return (t + ((n - t) >> d.sh1)) >> d.sh2;
-}
-
-// The CTA's tiles k = first, first + stride, ... are global tiles blockIdx.x + k * gridDim.x.  A walk carries
-// (tile / chunks, tile % chunks) from tile to tile, so that the per-tile bookkeeping has no division.
-struct TileWalk {
-    uint32_t tile, fc, chunk, step, dq, dr;
-    SDCT_DEV void init(const KParams &p, uint32_t first, uint32_t stride)
-    {
-        tile = blockIdx.x + first * gridDim.x;
-        fc = fastdiv(tile, p.div_chunks);
-        chunk = tile - fc * p.chunks;
-        step = stride * gridDim.x;
-        dq = fastdiv(step, p.div_chunks);
-        dr = step - dq * p.chunks;
-    }
-    SDCT_DEV void next(const KParams &p)
-    {
-        tile += step; fc += dq; chunk += dr;
-        if (chunk >= p.chunks) { chunk -= p.chunks; fc++; }
-    }
-};
-
-template <int COMPS>
-SDCT_DEV Tile tile_at(const KParams &p, const TileWalk &w)
-{
-    Tile t;
-    uint32_t frame = w.fc;
-    t.comp = 0;
-    if (COMPS != 1) { frame = w.fc / COMPS; t.comp = w.fc - frame * COMPS; }
-    t.n0 = w.chunk * TILE;
-    t.count = min((uint32_t)TILE, p.rows * p.bpr - t.n0);
-    t.pix = p.pixels + (uint64_t)frame * p.pixel_frame_stride;
-    t.coef = p.coefs + (uint64_t)frame * p.coef_frame_stride + (uint64_t)t.comp * p.coef_comp_stride;
-    return t;
-}
-
 template <int COMPS>
 SDCT_DEV const uint8_t *block_pixels(const KParams &p, const Tile &t, uint32_t slot)
 {
@@ -473,7 +432,7 @@ SDCT_DEV void producer_role(const KParams &p, uint64_t *bars, uint32_t tmem_base
         auto issue = [&](uint32_t j) {
             const bool live = wi.tile < p.tiles && !(ablate_bits(p) & 16);
             if (live) {
-                const Tile t = tile_at<COMPS>(p, wi);
+                const Tile t = tile_at<COMPS, TILE>(p, wi);
                 const uint8_t *px = block_pixels<COMPS>(p, t, copy_slot) + row_off;
                 uint8_t *dst = copy_dst + (j % RING) * RING_TILE_BYTES;
 #pragma unroll
@@ -517,7 +476,7 @@ SDCT_DEV void producer_role(const KParams &p, uint64_t *bars, uint32_t tmem_base
 #pragma unroll
         for (int j = 0; j < PF; j++) {
             if (wl.tile < p.tiles) {
-                const Tile t = tile_at<COMPS>(p, wl);
+                const Tile t = tile_at<COMPS, TILE>(p, wl);
                 load_block<COMPS, VEC>(block_pixels<COMPS>(p, t, my_slot), p.pitch, t.comp, w[j]);
             }
             wl.next(p);
@@ -531,7 +490,7 @@ SDCT_DEV void producer_role(const KParams &p, uint64_t *bars, uint32_t tmem_base
 #pragma unroll
                 for (int i = 0; i < 16; i++) cur[i] = w[j][i];
                 if (wl.tile < p.tiles) {
-                    const Tile tn = tile_at<COMPS>(p, wl);
+                    const Tile tn = tile_at<COMPS, TILE>(p, wl);
                     load_block<COMPS, VEC>(block_pixels<COMPS>(p, tn, my_slot), p.pitch, tn.comp, w[j]);
                 }
                 wl.next(p);
@@ -613,7 +572,7 @@ SDCT_DEV void consumer_role(const KParams &p, uint64_t *bars, uint32_t tmem_base
         if (wk.tile >= p.tiles) break;
         const uint32_t sd = k % D_STAGES, ud = k / (2 * D_STAGES);
         uint64_t *d_full = bars + BAR_D_FULL + c * D_STAGES + sd, *d_empty = bars + BAR_D_EMPTY + c * D_STAGES + sd;
-        const Tile cur = tile_at<COMPS>(p, wk);
+        const Tile cur = tile_at<COMPS, TILE>(p, wk);
         const uint64_t n_first = (uint64_t)p.row0 * p.bpr + cur.n0;
         uint8_t *img = img_base + ((k / CONSUMER_WGS) & 1) * IMG_BYTES;
         const bool tr = (abl & 32) && blockIdx.x == 0 && L == 0;
@@ -752,19 +711,6 @@ __global__ void __launch_bounds__(THREADS, 1) forward_tc_kernel(const __grid_con
 }  // namespace sdct
 
 using namespace sdct;
-
-// Granlund-Montgomery magic for n / d, any 32-bit n, d >= 1
-static KFastDiv make_fastdiv(uint32_t d)
-{
-    KFastDiv r;
-    if (d == 0) d = 1;
-    uint32_t l = 0;
-    while ((1ull << l) < d) l++;   // ceil(log2 d)
-    r.m = (uint32_t)((((1ull << l) - d) << 32) / d + 1);
-    r.sh1 = l < 1 ? l : 1;
-    r.sh2 = l > 0 ? l - 1 : 0;
-    return r;
-}
 
 // The pixels as a 4-D tensor of u32 [frame][eye][pixel row][W / 4] for the TMA path; box = 256 x 8 x 1 x 1 =
 // the 8 rows x 1024 bytes of 128 consecutive blocks of one block row.  Returns false when the geometry does
