@@ -15,21 +15,6 @@ struct Tile {
     uint32_t count;         // valid blocks in this tile
 };
 
-template <int CB>
-SDCT_DEV Tile tile_info(const KParams &p, uint32_t tile)
-{
-    Tile t;
-    const uint32_t chunk = tile % p.chunks;
-    const uint32_t fc = tile / p.chunks;
-    t.comp = fc % p.comps;
-    const uint32_t frame = fc / p.comps;
-    t.n0 = chunk * CB;
-    t.count = min((uint32_t)CB, p.rows * p.bpr - t.n0);
-    t.pix = p.pixels + (uint64_t)frame * p.pixel_frame_stride;
-    t.coef = p.coefs + (uint64_t)frame * p.coef_frame_stride + (uint64_t)t.comp * p.coef_comp_stride;
-    return t;
-}
-
 // ---- division-free tile walk -------------------------------------------------------------------------
 // n / d for any 32-bit n (Granlund-Montgomery, magic computed by make_fastdiv on the host)
 SDCT_DEV uint32_t fastdiv(uint32_t n, const KFastDiv &d)

@@ -422,8 +422,10 @@ template <int LAYOUT, int COMPS, int VEC>
 __global__ void __launch_bounds__(SDCT_TB, 3) inverse_kernel(const __grid_constant__ KParams p)
 {
     extern __shared__ __align__(16) uint8_t smem[];
-    for (uint32_t tile = blockIdx.x, it = 0; tile < p.tiles; it++, tile += gridDim.x) {
-        const Tile t = tile_info<CB>(p, tile);
+    TileWalk w;
+    w.init(p, 0, 1);
+    for (uint32_t it = 0; w.tile < p.tiles; it++, w.next(p)) {
+        const Tile t = tile_at<COMPS, CB>(p, w);
         uint8_t *sm = smem + (it & 1) * STAGE_BYTES;
         fetch_coefs<LAYOUT>(sm, p, t);
         __syncthreads();
@@ -441,17 +443,22 @@ __global__ void __launch_bounds__(SDCT_TB, 3) roundtrip_kernel(const __grid_cons
     extern __shared__ __align__(16) uint8_t smem[];
     constexpr bool PF = prefetchable<COMPS, VEC>();
     uint8_t *stage_in = smem;
-    uint32_t tile = blockIdx.x;
+    TileWalk w;   // the tile after the current one
+    w.init(p, 0, 1);
+    if (w.tile >= p.tiles) return;
+    Tile t = tile_at<COMPS, CB>(p, w);
     if (PF) {
-        if (tile < p.tiles) prefetch_pair<VEC>(stage_in, locate<LAYOUT>(p, tile_info<CB>(p, tile)), p.pitch);
+        prefetch_pair<VEC>(stage_in, locate<LAYOUT>(p, t), p.pitch);
         cp_async_commit();
     }
-    for (uint32_t it = 0; tile < p.tiles; it++, tile += gridDim.x) {
-        const Tile t = tile_info<CB>(p, tile);
+    w.next(p);
+    for (uint32_t it = 0;; it++, w.next(p)) {
+        const bool more = w.tile < p.tiles;
+        Tile tn = t;
+        if (more) tn = tile_at<COMPS, CB>(p, w);
         uint32_t wp[16], wq[16];
         if (PF) {
-            const uint32_t next = tile + gridDim.x;
-            if (next < p.tiles) prefetch_pair<VEC>(stage_in + ((it + 1) & 1) * IN_STAGE_BYTES, locate<LAYOUT>(p, tile_info<CB>(p, next)), p.pitch);
+            if (more) prefetch_pair<VEC>(stage_in + ((it + 1) & 1) * IN_STAGE_BYTES, locate<LAYOUT>(p, tn), p.pitch);
             cp_async_commit();
             cp_async_wait<1>();
             read_prefetched(stage_in + (it & 1) * IN_STAGE_BYTES, wp, wq);
@@ -469,6 +476,8 @@ __global__ void __launch_bounds__(SDCT_TB, 3) roundtrip_kernel(const __grid_cons
         }
         inverse_pair<LAYOUT>(p.tab2, p.off, v);
         store_pair<COMPS, VEC>(locate<LAYOUT>(p, t), p.pixels, p.pixels_out, p.pitch, v);
+        if (!more) break;
+        t = tn;
     }
 }
 
