@@ -380,6 +380,8 @@ def main():
                 add(f"forward_{lname}_exact", lambda j=j: ctx.forward(d_in, lut, j, out=d_out))
             jf = sd.dense_job(layout, W, H, frames=F, flags=sd.FAST)
             add(f"forward_{lname}_fast", lambda jf=jf: ctx.forward(d_in, lut, jf, out=d_out))
+            jt = sd.dense_job(layout, W, H, frames=F, flags=sd.TENSOR)   # tcgen05 form (own exact-integer definition, not the reference's fp32 rounding)
+            add(f"forward_{lname}_tensor", lambda jt=jt: ctx.forward(d_in, lut, jt, out=d_out))
             ctx.forward(d_in, lut, j, out=d_out)
             d_back = torch.empty_like(d_in)
             add(f"inverse_{lname}", lambda j=j, d_back=d_back: ctx.inverse(d_out, lut, j, out=d_back))
