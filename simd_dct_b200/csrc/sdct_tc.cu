@@ -55,6 +55,8 @@ constexpr int CONSUMER_WARP = 4 * PRODUCER_WGS;
 constexpr int MMA_WARP = 4 * (PRODUCER_WGS + CONSUMER_WGS);
 constexpr int TMA_WARP = MMA_WARP + MMA_WARPS;   // one thread: bulk tensor copies of the pixel tiles (VEC == VEC_TMA)
 constexpr int VEC_TMA = 3;
+constexpr int VEC_RGB = 4;                   // interleaved RGB, 16-byte-aligned rows: one pixel tile feeds the three components' tiles
+constexpr int RGB_RING = 4, RGB_ROW_BYTES = 24 * SDCT_TC_TILE;   // ring slots of 8 rows x 3072 bytes
 #ifndef SDCT_TC_DIRECT_B
 #define SDCT_TC_DIRECT_B 1
 #endif
@@ -98,6 +100,7 @@ constexpr int TMA_BOX_BYTES = 8 * TILE * 8, TMA_SLOT_BYTES = 2 * TMA_BOX_BYTES;
 constexpr int BAR_RING_FULL = 2 * A_STAGES + 4 * D_STAGES, BAR_RING_EMPTY = BAR_RING_FULL + TMA_RING;
 constexpr int NUM_BARS = BAR_RING_EMPTY + TMA_RING;
 static_assert(TMA_RING * TMA_SLOT_BYTES <= PRODUCER_WGS * RING * RING_TILE_BYTES, "the TMA ring lives in the cp.async ring's space");
+static_assert(RGB_RING * 8 * RGB_ROW_BYTES <= PRODUCER_WGS * RING * RING_TILE_BYTES, "... and so does the RGB ring");
 constexpr int SMEM_META_OFF = SMEM_BAR_OFF + NUM_BARS * 8 + 16;   // TMA ring: blocks of the tile that lie in the first box
 constexpr int SMEM_USED = SMEM_META_OFF + TMA_RING * 4;
 // more than half of the SM's shared memory: exactly one CTA per SM (it allocates all of TMEM)
@@ -360,17 +363,21 @@ template <int N> SDCT_DEV void cp_async_wait() { asm volatile("cp.async.wait_gro
 // A rows of one tile: the thread's 64 pixels (16 words) -> fp16 -> its TMEM lane of the stage's A columns
 // The two halves of publishing a tile's A rows; whatever the caller puts between them (the next copies and
 // their address arithmetic) runs in the shadow of the TMEM store.
-SDCT_DEV void store_a_rows(const KParams &p, uint64_t *bars, uint32_t tmem_base, uint32_t lane_field, uint32_t k, const uint32_t (&w)[16])
+SDCT_DEV void store_a_halves(const KParams &p, uint64_t *bars, uint32_t tmem_base, uint32_t lane_field, uint32_t k, const uint32_t (&h)[32])
 {
     const uint32_t stage = k % A_STAGES, u = k / A_STAGES;
     const bool tr = (ablate_bits(p) & 32) && blockIdx.x == 0 && threadIdx.x == 0;
-    uint32_t h[32];
-    bytes_to_half(w, h);
     stamp(tr, 0, k, 0);
     mbar_wait(bars + BAR_A_EMPTY + stage, (u & 1) ^ 1);   // the MMAs of tile k - A_STAGES have completed: A[stage] is free
     fence_after();
     stamp(tr, 0, k, 1);
     if (!(ablate_bits(p) & 2)) tmem_st32(tmem_base + TMEM_A_OFF + stage * A_COLS + lane_field, h);
+}
+SDCT_DEV void store_a_rows(const KParams &p, uint64_t *bars, uint32_t tmem_base, uint32_t lane_field, uint32_t k, const uint32_t (&w)[16])
+{
+    uint32_t h[32];
+    bytes_to_half(w, h);
+    store_a_halves(p, bars, tmem_base, lane_field, k, h);
 }
 SDCT_DEV void signal_a_rows(const KParams &p, uint64_t *bars, uint32_t k)
 {
@@ -387,12 +394,102 @@ SDCT_DEV void publish_a(const KParams &p, uint64_t *bars, uint32_t tmem_base, ui
     signal_a_rows(p, bars, k);
 }
 
+// interleaved RGB: the 24 bytes (6 words) of a block row -> the 4 fp16-pair words of component C
+// (pixel x of component C is byte 3x + C; a pair whose two bytes lie in one word takes one PRMT with zero
+// bytes from a zero operand, a pair that spans two words a PRMT and a mask)
+template <int C>
+SDCT_DEV void rgb_row_to_half(const uint32_t (&s)[6], uint32_t *h)
+{
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+        constexpr int dummy = 0; (void)dummy;
+        const int B0 = 6 * j + C, B1 = B0 + 3;
+        const int w0 = B0 >> 2, b0 = B0 & 3, w1 = B1 >> 2, b1 = B1 & 3;
+        if (w0 == w1) h[j] = __byte_perm(s[w0], 0u, (uint32_t)(b0 | (4 << 4) | (b1 << 8) | (4 << 12)));
+        else h[j] = __byte_perm(s[w0], s[w1], (uint32_t)(b0 | (b0 << 4) | ((4 + b1) << 8) | ((4 + b1) << 12))) & 0x00ff00ffu;
+    }
+}
+
+// base address of block row r (relative to the window's first row) of a tile's frame
+SDCT_DEV const uint8_t *block_row_base(const KParams &p, const Tile &t, uint32_t r)
+{
+    const uint32_t row = r + p.row0;
+    const uint32_t band = p.eyes == 2 ? row >> 1 : row, eye = p.eyes == 2 ? row & 1 : 0;
+    return t.pix + (uint64_t)eye * p.eye_stride + (uint64_t)band * 8 * p.pitch;
+}
+
 template <int COMPS, int VEC>
 SDCT_DEV void producer_role(const KParams &p, uint64_t *bars, uint32_t tmem_base, uint8_t *ring, uint32_t pw, uint32_t L, uint32_t lane_field)
 {
     // warpgroup pw produces the CTA's tiles k = pw, pw + PRODUCER_WGS, ...; j counts its own tiles
     const uint32_t my_slot = slot_of_lane(L);
-    if (VEC == VEC_TMA) {
+    if (COMPS == 3 && VEC == VEC_RGB) {
+        // Fused components: p.tiles counts PIXEL tiles; pixel tile j of the CTA feeds its tiles k = 3j, 3j+1, 3j+2
+        // (components 0, 1, 2).  The interleaved rows of the tile's 128 blocks (8 rows x 3072 bytes, the
+        // tile's part of the next block row appended where it runs on) are copied ONCE, as coalesced 16-byte
+        // cp.async pieces spread over the warpgroup, into a 4-slot ring; one warpgroup barrier per pixel tile
+        // publishes the copies and frees the slot read before.  Each thread then reads the 24-byte rows of
+        // its block and extracts the three components in registers.
+        uint32_t off[3], rsel[3];   // this thread's three 16-byte pieces of a row pair (192 pieces per row)
+#pragma unroll
+        for (int m = 0; m < 3; m++) {
+            const uint32_t l2 = L + 128u * m;
+            rsel[m] = l2 >= 192u;
+            off[m] = 16u * (l2 - 192u * rsel[m]);
+        }
+        TileWalk wi;
+        wi.init(p, 0, 1);
+        auto issue = [&](uint32_t j) {
+            if (wi.tile < p.tiles && !(ablate_bits(p) & 16)) {
+                const Tile t = tile_at<1, TILE>(p, wi);
+                const uint32_t r = fastdiv(t.n0, p.div_bpr), bx0 = t.n0 - r * p.bpr;
+                const uint32_t c1 = min((uint32_t)TILE, p.bpr - bx0) * 24u, cb = t.count * 24u;
+                const uint8_t *base1 = block_row_base(p, t, r) + bx0 * 24u, *base2 = block_row_base(p, t, r + 1);
+                uint8_t *dst = ring + (j % RGB_RING) * (8 * RGB_ROW_BYTES);
+#pragma unroll
+                for (int m = 0; m < 3; m++) {
+                    if (off[m] < cb) {
+                        const uint8_t *src = (off[m] < c1 ? base1 + off[m] : base2 + (off[m] - c1)) + rsel[m] * p.pitch;
+                        uint8_t *d = dst + rsel[m] * RGB_ROW_BYTES + off[m];
+#pragma unroll
+                        for (int rp = 0; rp < 4; rp++) cp_async16(d + rp * 2 * RGB_ROW_BYTES, src + (uint64_t)(2 * rp) * p.pitch);
+                    }
+                }
+            }
+            wi.next(p);
+            cp_async_commit();
+        };
+        for (uint32_t j = 0; j + 1 < RGB_RING; j++) issue(j);
+        uint32_t tile = blockIdx.x;
+        for (uint32_t j = 0;; j++, tile += gridDim.x) {
+            if (tile >= p.tiles) return;
+            cp_async_wait<RGB_RING - 2>();   // this thread's pieces of pixel tile j have landed
+            named_barrier(3);                // ... and everybody's; everybody has read pixel tile j - 1
+            issue(j + RGB_RING - 1);         // into the slot of pixel tile j - 1
+            const uint8_t *src = ring + (j % RGB_RING) * (8 * RGB_ROW_BYTES) + my_slot * 24u;
+            uint32_t s[8][6];
+#pragma unroll
+            for (int r = 0; r < 8; r++) {
+#pragma unroll
+                for (int e = 0; e < 3; e++) {
+                    const uint2 v = *reinterpret_cast<const uint2 *>(src + r * RGB_ROW_BYTES + 8 * e);
+                    s[r][2 * e] = v.x; s[r][2 * e + 1] = v.y;
+                }
+            }
+#pragma unroll
+            for (int c = 0; c < 3; c++) {
+                uint32_t h[32];
+#pragma unroll
+                for (int r = 0; r < 8; r++) {
+                    if (c == 0) rgb_row_to_half<0>(s[r], h + 4 * r);
+                    else if (c == 1) rgb_row_to_half<1>(s[r], h + 4 * r);
+                    else rgb_row_to_half<2>(s[r], h + 4 * r);
+                }
+                store_a_halves(p, bars, tmem_base, lane_field, 3 * j + c, h);
+                signal_a_rows(p, bars, 3 * j + c);
+            }
+        }
+    } else if (VEC == VEC_TMA) {
         // The TMA thread (tma_role) lands the tile's pixel rows in ring slot j % TMA_RING: row r of the block in
         // slot s lies at r * 1024 + s * 8 of the first box while s < split (the blocks left in this block row),
         // and at r * 1024 + (s - split) * 8 of the second box (the next block row from its left edge) otherwise.
@@ -527,13 +624,16 @@ SDCT_DEV void tma_role(const KParams &p, uint64_t *bars, uint8_t *ring, uint32_t
 }
 
 // one thread per MMA warp; warp m takes tiles k = m, m + MMA_WARPS, ...
+// CF = tiles per pixel tile (3 for the fused RGB path, where p.tiles counts pixel tiles; 1 otherwise)
+template <int CF>
 SDCT_DEV void mma_role(const KParams &p, uint64_t *bars, uint32_t tmem_base, uint64_t bdesc, uint32_t m)
 {
     const bool no_mma = (ablate_bits(p) & 1) != 0;
     const uint64_t bd[4] = {bdesc, bdesc + (uint64_t)((2 * B_LBO) >> 4), bdesc + (uint64_t)((4 * B_LBO) >> 4), bdesc + (uint64_t)((6 * B_LBO) >> 4)};
     uint32_t k = m;
     const bool tr = (ablate_bits(p) & 32) && blockIdx.x == 0;
-    for (uint32_t tile = blockIdx.x + m * gridDim.x; tile < p.tiles; tile += MMA_WARPS * gridDim.x, k += MMA_WARPS) {
+    for (;; k += MMA_WARPS) {
+        if (blockIdx.x + (k / CF) * gridDim.x >= p.tiles) break;
         const uint32_t sa = k % A_STAGES, ua = k / A_STAGES, sd = k % D_STAGES;
         stamp(tr, 1, k, 0);
         mbar_wait(bars + BAR_A_FULL + sa, ua & 1);
@@ -555,7 +655,7 @@ SDCT_DEV void mma_role(const KParams &p, uint64_t *bars, uint32_t tmem_base, uin
     }
 }
 
-template <int LAYOUT, int COMPS>
+template <int LAYOUT, int COMPS, int CF>
 SDCT_DEV void consumer_role(const KParams &p, uint64_t *bars, uint32_t tmem_base, uint8_t *img_base, uint32_t c, uint32_t L, uint32_t lane_field)
 {
     const uint32_t lane = L & 31, g = lane >> 2, q = lane & 3;
@@ -566,13 +666,22 @@ SDCT_DEV void consumer_role(const KParams &p, uint64_t *bars, uint32_t tmem_base
     // blocks P, Q of this thread: slots sp0 (+1) in the first 16-lane half, sp0 + 16 (+1) in the second
     const uint32_t sp0 = (L >> 5) * 32u + 2u * g;
     const uint32_t abl = ablate_bits(p);
+    // CF == 1: wk walks this warpgroup's tiles.  CF == 3: wk walks the CTA's pixel tiles, comp = k % 3.
+    static_assert(CF == 1 || (CF == 3 && CONSUMER_WGS == 2), "fused components");
     TileWalk wk;
-    wk.init(p, c, CONSUMER_WGS);
-    for (uint32_t k = c;; k += CONSUMER_WGS, wk.next(p)) {
+    if (CF == 1) wk.init(p, c, CONSUMER_WGS); else wk.init(p, 0, 1);
+    uint32_t comp = CF == 1 ? 0u : c;
+    auto advance = [&]() {
+        if (CF == 1) { wk.next(p); return; }
+        comp += CONSUMER_WGS;
+        if (comp >= (uint32_t)CF) { comp -= CF; wk.next(p); }
+    };
+    for (uint32_t k = c;; k += CONSUMER_WGS, advance()) {
         if (wk.tile >= p.tiles) break;
         const uint32_t sd = k % D_STAGES, ud = k / (2 * D_STAGES);
         uint64_t *d_full = bars + BAR_D_FULL + c * D_STAGES + sd, *d_empty = bars + BAR_D_EMPTY + c * D_STAGES + sd;
-        const Tile cur = tile_at<COMPS, TILE>(p, wk);
+        Tile cur = tile_at<(CF == 1 ? COMPS : 1), TILE>(p, wk);
+        if (CF != 1) { cur.comp = comp; cur.coef += (uint64_t)comp * p.coef_comp_stride; }
         const uint64_t n_first = (uint64_t)p.row0 * p.bpr + cur.n0;
         uint8_t *img = img_base + ((k / CONSUMER_WGS) & 1) * IMG_BYTES;
         const bool tr = (abl & 32) && blockIdx.x == 0 && L == 0;
@@ -654,6 +763,7 @@ template <int LAYOUT, int COMPS, int VEC>
 __global__ void __launch_bounds__(THREADS, 1) forward_tc_kernel(const __grid_constant__ KParams p)
 {
     extern __shared__ __align__(128) uint8_t smem[];
+    constexpr int CF = (COMPS == 3 && VEC == VEC_RGB) ? 3 : 1;
     const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     uint64_t *bars = reinterpret_cast<uint64_t *>(smem + SMEM_BAR_OFF);
     uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(smem + SMEM_BAR_OFF + NUM_BARS * 8);
@@ -694,11 +804,11 @@ __global__ void __launch_bounds__(THREADS, 1) forward_tc_kernel(const __grid_con
     } else if (warp < MMA_WARP) {
         if (MOVE_REGS) asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(CONSUMER_REGS));
         const uint32_t c = (warp - CONSUMER_WARP) >> 2;
-        consumer_role<LAYOUT, COMPS>(p, bars, tmem_base, smem + SMEM_IMG_OFF + c * 2 * IMG_BYTES, c, threadIdx.x & 127, lane_field);
+        consumer_role<LAYOUT, COMPS, CF>(p, bars, tmem_base, smem + SMEM_IMG_OFF + c * 2 * IMG_BYTES, c, threadIdx.x & 127, lane_field);
     } else {
         if (MOVE_REGS) asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(MMA_REGS));
         if (warp < MMA_WARP + MMA_WARPS && lane == 0)
-            mma_role(p, bars, tmem_base, b_descriptor(smem_u32(smem + SMEM_B_OFF)), warp - MMA_WARP);
+            mma_role<CF>(p, bars, tmem_base, b_descriptor(smem_u32(smem + SMEM_B_OFF)), warp - MMA_WARP);
         else if (VEC == VEC_TMA && warp == TMA_WARP && lane == 0)
             tma_role(p, bars, smem + SMEM_RING_OFF, reinterpret_cast<uint32_t *>(smem + SMEM_META_OFF));
     }
@@ -749,7 +859,7 @@ static bool make_pixel_tensor_map(KParams &p)
 }
 
 template <int LAYOUT>
-static cudaError_t launch_tc(const KParams &p, unsigned grid, bool tma, cudaStream_t s)
+static cudaError_t launch_tc(const KParams &p, unsigned grid, bool tma, bool rgb_fused, cudaStream_t s)
 {
 #define SDCT_TC_GO(C, V)                                                                                             \
     do {                                                                                                             \
@@ -766,6 +876,7 @@ static cudaError_t launch_tc(const KParams &p, unsigned grid, bool tma, cudaStre
         if (tma) SDCT_TC_GO(1, tc::VEC_TMA);
         if (p.pixel_vec >= 2) SDCT_TC_GO(1, 2); else if (p.pixel_vec >= 1) SDCT_TC_GO(1, 1); else SDCT_TC_GO(1, 0);
     } else {
+        if (rgb_fused) SDCT_TC_GO(3, tc::VEC_RGB);
         if (p.pixel_vec >= 1) SDCT_TC_GO(3, 1); else SDCT_TC_GO(3, 0);
     }
 #undef SDCT_TC_GO
@@ -793,13 +904,20 @@ extern "C" cudaError_t sdct_k_launch_tc(int op, int layout, const KParams *pp, c
     p.div_chunks = make_fastdiv(p.chunks);
     p.div_bpr = make_fastdiv(p.bpr);
     const unsigned sms = p.sm_count ? p.sm_count : 148u;
-    const unsigned grid = (unsigned)(tiles < sms ? tiles : sms);
+    // interleaved RGB with 16-byte-aligned rows and an even number (>= 128: a tile spans at most two block rows) of
+    // blocks per row: the three components of a
+    // pixel tile are produced from one copy of its pixels; p.tiles then counts pixel tiles
+    const uint64_t strides = p.pitch | (p.eyes == 2 ? p.eye_stride : 0) | (p.frames > 1 ? p.pixel_frame_stride : 0);
+    const bool rgb_fused = p.comps == 3 && tc::PRODUCER_WGS == 1 && !(((uintptr_t)p.pixels | strides) & 15) && !(p.bpr & 1) && p.bpr >= (uint32_t)tc::TILE &&
+                           !(((unsigned long long)p.rows * p.bpr) & 1) && !getenv("SDCT_TC_NO_RGB_FUSE");
+    if (rgb_fused) p.tiles = (uint32_t)(tiles / 3);
+    const unsigned grid = (unsigned)(p.tiles < sms ? p.tiles : sms);
     // measured: the TMA pixel path wins for layouts A and B; layout C (staging image + flush) is faster on the cp.async ring
     const bool tma = layout != SDCT_K_LAYOUT_C && make_pixel_tensor_map(p);
     switch (layout) {
-    case SDCT_K_LAYOUT_A: return launch_tc<SDCT_K_LAYOUT_A>(p, grid, tma, s);
-    case SDCT_K_LAYOUT_B: return launch_tc<SDCT_K_LAYOUT_B>(p, grid, tma, s);
-    case SDCT_K_LAYOUT_C: return launch_tc<SDCT_K_LAYOUT_C>(p, grid, tma, s);
+    case SDCT_K_LAYOUT_A: return launch_tc<SDCT_K_LAYOUT_A>(p, grid, tma, rgb_fused, s);
+    case SDCT_K_LAYOUT_B: return launch_tc<SDCT_K_LAYOUT_B>(p, grid, tma, rgb_fused, s);
+    case SDCT_K_LAYOUT_C: return launch_tc<SDCT_K_LAYOUT_C>(p, grid, tma, rgb_fused, s);
     default: return cudaErrorInvalidValue;
     }
 }

@@ -519,3 +519,30 @@ def test_tensor_core_levels_stay_within_one_of_the_reference_arithmetic(ctx, ora
         d = np.abs(got.astype(int) - exact.astype(int))
         assert d.max() <= 1
         assert np.mean(d != 0) <= 1e-3, np.mean(d != 0)
+
+
+@pytest.mark.parametrize("layout", LAYOUTS)
+def test_tensor_core_fused_rgb_components(ctx, oracle, layout):
+    """Interleaved RGB with 16-byte-aligned rows: one copy of a pixel tile feeds the three components' tiles
+    (sdct_tc.cu, VEC_RGB).  Tiles that run on into the next block row, a ragged tail, several frames, a CTA
+    walking several pixel tiles, and the unaligned fallback must all give the per-plane oracle bytes."""
+    lut = ol.lut(16)
+    for (f, h, w) in ((2, 40, 1088), (1, 1080 - 1080 % 8, 1920)):
+        rgb = np.stack([make_image("rand", h, w, seed=60 + k, comps=3) for k in range(f)])
+        job = sd.dense_job(layout, w, h, frames=f, components=3, flags=sd.TENSOR)
+        got = ctx.forward(dev(rgb), lut, job).cpu().numpy().reshape(f, 3, -1)
+        for k in range(f):
+            for c in range(3):
+                want = oracle.forward(layout, rgb[k], lut, mode=ol.MODE_TENSOR, comp=c)
+                assert np.array_equal(got[k, c], want), (f, h, w, k, c, np.count_nonzero(got[k, c] != want))
+    # rows that are only 8-byte aligned (pitch = 3 * 1080 + 8): register-prefetch path, same bytes
+    h, w = 24, 1088
+    rgb = make_image("smooth", h, w, seed=70, comps=3)
+    pitch = 3 * w + 8
+    buf = np.zeros((h, pitch), dtype=np.uint8)
+    buf[:, :3 * w] = rgb.reshape(h, 3 * w)
+    job = sd.dense_job(layout, w, h, components=3, flags=sd.TENSOR)
+    job.pitch = pitch
+    got = ctx.forward(dev(buf), lut, job).cpu().numpy().reshape(3, -1)
+    for c in range(3):
+        assert np.array_equal(got[c], oracle.forward(layout, rgb, lut, mode=ol.MODE_TENSOR, comp=c))
