@@ -249,6 +249,31 @@ SDCT_DEV void flush_coefs(const uint8_t *sm, const KParams &p, const Tile &b)
     }
 }
 
+// Layouts A and B, 16-byte-aligned output: the bytes a warp stages are whole 16-byte chunks of the output that
+// no other warp touches (B: its 64 blocks = 8 groups of 512 bytes; A: blocks 32w.. and 128 + 32w.., 64 bytes
+// each), so the warp flushes its own part after a __syncwarp() and the CTA needs no barrier at all.
+template <int LAYOUT, bool COMPL>
+SDCT_DEV void flush_coefs_warp(const uint8_t *sm, const KParams &p, const Tile &b)
+{
+    const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint64_t n_first = (uint64_t)p.row0 * p.bpr + b.n0;
+    const uint32_t m32 = COMPL ? 0xffffffffu : 0u;
+    uint4 *dst = reinterpret_cast<uint4 *>(b.coef + n_first * 64);
+    const uint32_t chunks16 = b.count * 4;
+#pragma unroll
+    for (uint32_t j = 0; j < 8; j++) {
+        uint32_t k, off;
+        if (LAYOUT == SDCT_K_LAYOUT_B) {
+            k = 256u * warp + 32u * j + lane;
+            off = (k >> 5) * B_GROUP_PITCH + (k & 31) * 16;
+        } else {
+            k = (j >> 2) * 512u + 128u * warp + 32u * (j & 3) + lane;
+            off = (k >> 2) * A_SLOT + (k & 3) * 16;
+        }
+        if (k < chunks16) dst[k] = xor4(*reinterpret_cast<const uint4 *>(sm + off), m32);
+    }
+}
+
 // Persistent CTAs: tile = blockIdx.x, + gridDim.x, ...  The pixels of tile k+1 are prefetched with
 // cp.async while tile k is transformed; the output staging image is double-buffered so that one
 // barrier per tile suffices (the image written in iteration k is flushed before barrier k+1, and
@@ -287,8 +312,13 @@ __global__ void __launch_bounds__(SDCT_TB, 3) forward_kernel(const __grid_consta
         forward_pair<LAYOUT, MODE, X3>(wp, wq, p.tab, v);
         uint8_t *sm = smem + (it & 1) * STAGE_BYTES;
         stage_levels<LAYOUT>(sm, v);
-        __syncthreads();
-        flush_coefs<LAYOUT, complemented<LAYOUT, MODE>()>(sm, p, t);
+        if (LAYOUT != SDCT_K_LAYOUT_C && p.coef_aligned16) {
+            __syncwarp();
+            flush_coefs_warp<LAYOUT, complemented<LAYOUT, MODE>()>(sm, p, t);
+        } else {
+            __syncthreads();
+            flush_coefs<LAYOUT, complemented<LAYOUT, MODE>()>(sm, p, t);
+        }
         if (!more) break;
         t = tn;
     }
