@@ -362,6 +362,28 @@ SDCT_DEV void fetch_coefs(uint8_t *sm, const KParams &p, const Tile &b)
     }
 }
 
+// the warp's own 16-byte chunks of a tile's coefficient image (layouts A, B), asynchronously
+template <int LAYOUT>
+SDCT_DEV void prefetch_coefs_warp(uint8_t *sm, const KParams &p, const Tile &b)
+{
+    const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint64_t n_first = (uint64_t)p.row0 * p.bpr + b.n0;
+    const uint8_t *src = b.coef + n_first * 64;
+    const uint32_t chunks16 = b.count * 4;
+#pragma unroll
+    for (uint32_t j = 0; j < 8; j++) {
+        uint32_t k, off;
+        if (LAYOUT == SDCT_K_LAYOUT_B) {
+            k = 256u * warp + 32u * j + lane;
+            off = (k >> 5) * B_GROUP_PITCH + (k & 31) * 16;
+        } else {
+            k = (j >> 2) * 512u + 128u * warp + 32u * (j & 3) + lane;
+            off = (k >> 2) * A_SLOT + (k & 3) * 16;
+        }
+        if (k < chunks16) cp_async16(sm + off, src + 16ull * k);
+    }
+}
+
 // shared-memory image -> the pair's levels as floats, natural index b[u*8+v]
 template <int LAYOUT>
 SDCT_DEV void unstage_levels(const uint8_t *sm, F2 b[64])
@@ -454,6 +476,33 @@ __global__ void __launch_bounds__(SDCT_TB, 3) inverse_kernel(const __grid_consta
     extern __shared__ __align__(16) uint8_t smem[];
     TileWalk w;
     w.init(p, 0, 1);
+    if (LAYOUT != SDCT_K_LAYOUT_C && p.coef_aligned16) {
+        // layouts A and B, 16-byte-aligned coefficients: the 16-byte chunks a warp's blocks need are whole
+        // chunks of the input that no other warp reads (see flush_coefs_warp), so each warp prefetches its own
+        // part of the NEXT tile with cp.async while it transforms the current one - no CTA barrier
+        if (w.tile >= p.tiles) return;
+        Tile t = tile_at<COMPS, CB>(p, w);
+        prefetch_coefs_warp<LAYOUT>(smem, p, t);
+        cp_async_commit();
+        w.next(p);
+        for (uint32_t it = 0;; it++, w.next(p)) {
+            const bool more = w.tile < p.tiles;
+            Tile tn = t;
+            if (more) tn = tile_at<COMPS, CB>(p, w);
+            __syncwarp();   // every lane has read the image the next copies overwrite
+            if (more) prefetch_coefs_warp<LAYOUT>(smem + ((it + 1) & 1) * STAGE_BYTES, p, tn);
+            cp_async_commit();
+            cp_async_wait<1>();
+            __syncwarp();
+            F2 v[64];
+            unstage_levels<LAYOUT>(smem + (it & 1) * STAGE_BYTES, v);
+            inverse_pair<LAYOUT>(p.tab, p.off, v);
+            store_pair<COMPS, VEC>(locate<LAYOUT>(p, t), p.pixels, const_cast<uint8_t *>(p.pixels), p.pitch, v);
+            if (!more) break;
+            t = tn;
+        }
+        return;
+    }
     for (uint32_t it = 0; w.tile < p.tiles; it++, w.next(p)) {
         const Tile t = tile_at<COMPS, CB>(p, w);
         uint8_t *sm = smem + (it & 1) * STAGE_BYTES;
