@@ -258,6 +258,16 @@ SDCT_DEV void flush_coefs_warp(const uint8_t *sm, const KParams &p, const Tile &
     const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const uint64_t n_first = (uint64_t)p.row0 * p.bpr + b.n0;
     const uint32_t m32 = COMPL ? 0xffffffffu : 0u;
+    if (LAYOUT == SDCT_K_LAYOUT_C) {   // the warp's 64 blocks = 64 bytes of each of the 64 plane rows (counts are multiples of 16)
+#pragma unroll
+        for (uint32_t j = 0; j < 8; j++) {
+            const uint32_t k = 32u * j + lane, i = k >> 2, c = 64u * warp + 16u * (k & 3);
+            if (c < b.count)
+                *reinterpret_cast<uint4 *>(b.coef + (uint64_t)i * p.coef_plane_stride + n_first + c) =
+                    xor4(*reinterpret_cast<const uint4 *>(sm + i * C_PITCH + c), m32);
+        }
+        return;
+    }
     uint4 *dst = reinterpret_cast<uint4 *>(b.coef + n_first * 64);
     const uint32_t chunks16 = b.count * 4;
 #pragma unroll
@@ -272,6 +282,13 @@ SDCT_DEV void flush_coefs_warp(const uint8_t *sm, const KParams &p, const Tile &
         }
         if (k < chunks16) dst[k] = xor4(*reinterpret_cast<const uint4 *>(sm + off), m32);
     }
+}
+
+// can every warp move its own part of the coefficient image?  (uniform per launch)
+template <int LAYOUT>
+SDCT_DEV bool warp_local_coefs(const KParams &p)
+{
+    return p.coef_aligned16 && (LAYOUT != SDCT_K_LAYOUT_C || ((p.rows * p.bpr) & 15) == 0);
 }
 
 // Persistent CTAs: tile = blockIdx.x, + gridDim.x, ...  The pixels of tile k+1 are prefetched with
@@ -312,7 +329,7 @@ __global__ void __launch_bounds__(SDCT_TB, 3) forward_kernel(const __grid_consta
         forward_pair<LAYOUT, MODE, X3>(wp, wq, p.tab, v);
         uint8_t *sm = smem + (it & 1) * STAGE_BYTES;
         stage_levels<LAYOUT>(sm, v);
-        if (LAYOUT != SDCT_K_LAYOUT_C && p.coef_aligned16) {
+        if (warp_local_coefs<LAYOUT>(p)) {
             __syncwarp();
             flush_coefs_warp<LAYOUT, complemented<LAYOUT, MODE>()>(sm, p, t);
         } else {
@@ -368,6 +385,14 @@ SDCT_DEV void prefetch_coefs_warp(uint8_t *sm, const KParams &p, const Tile &b)
 {
     const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const uint64_t n_first = (uint64_t)p.row0 * p.bpr + b.n0;
+    if (LAYOUT == SDCT_K_LAYOUT_C) {
+#pragma unroll
+        for (uint32_t j = 0; j < 8; j++) {
+            const uint32_t k = 32u * j + lane, i = k >> 2, c = 64u * warp + 16u * (k & 3);
+            if (c < b.count) cp_async16(sm + i * C_PITCH + c, b.coef + (uint64_t)i * p.coef_plane_stride + n_first + c);
+        }
+        return;
+    }
     const uint8_t *src = b.coef + n_first * 64;
     const uint32_t chunks16 = b.count * 4;
 #pragma unroll
@@ -476,8 +501,8 @@ __global__ void __launch_bounds__(SDCT_TB, 3) inverse_kernel(const __grid_consta
     extern __shared__ __align__(16) uint8_t smem[];
     TileWalk w;
     w.init(p, 0, 1);
-    if (LAYOUT != SDCT_K_LAYOUT_C && p.coef_aligned16) {
-        // layouts A and B, 16-byte-aligned coefficients: the 16-byte chunks a warp's blocks need are whole
+    if (warp_local_coefs<LAYOUT>(p)) {
+        // 16-byte-aligned coefficients: the 16-byte chunks a warp's blocks need are whole
         // chunks of the input that no other warp reads (see flush_coefs_warp), so each warp prefetches its own
         // part of the NEXT tile with cp.async while it transforms the current one - no CTA barrier
         if (w.tile >= p.tiles) return;
