@@ -397,6 +397,77 @@ void sdct_oracle_inverse(int layout, const uint8_t *coef, size_t plane_stride, s
             }
 }
 
+/* Inverse, mode TENSOR (this repo; simd_dct_b200/csrc/sdct_tc.cu, inverse_tc_kernel).  PARITY UNPINNED like every
+ * inverse here (the reference has none).  The dequantiser scale is folded into the matrix:
+ *   E[p][i]   = W[p][i] * tab[i]            (double; W = unnormalised inverse basis, tab = SDCT_O_TAB_INVERSE as float,
+ *                                            i = the layout's own coefficient index, p = y*8+x)
+ *   S         = the largest integer with 2^S * max|E| < 2^20 - 512
+ *   full      = llrint(2^S * E), hi = (full + 512) >> 10, lo = full - 1024 * hi
+ *   per pixel : D1 = sum q_i * hi, D0 = sum q_i * lo (exact integers, |.| < 2^24: the tensor core's fp32
+ *               accumulation is exact), t = fma(D1, 1024, D0), y = fma(t, 2^-S, off[p]) with
+ *               off[p] = (float)(-127 * sum_i E[p][i]), pixel = clamp(rne(y), 0, 255). */
+static int inverse_tensor_matrix(int layout, const float tab[64], int32_t full[64 * 64], float off[64])
+{
+    static double E[64 * 64];
+    double emax = 0.0;
+    const double N = 0.35355339059327376220042218105242;
+    for (int y = 0; y < 8; y++)
+        for (int x = 0; x < 8; x++)
+            for (int u = 0; u < 8; u++)
+                for (int v = 0; v < 8; v++) {
+                    const int i = layout == SDCT_O_LAYOUT_A ? v * 8 + u : u * 8 + v;
+                    const double w = (dct_entry(u, y) / N) * (dct_entry(v, x) / N);
+                    const double e = w * (double)tab[i];
+                    E[(y * 8 + x) * 64 + i] = e;
+                    if (fabs(e) > emax) emax = fabs(e);
+                }
+    int S = 0;
+    if (emax > 0.0) {
+        S = (int)floor(log2((1048576.0 - 512.0) / emax));
+        while (ldexp(emax, S) >= 1048576.0 - 512.0) S--;
+        while (ldexp(emax, S + 1) < 1048576.0 - 512.0) S++;
+    }
+    for (int p = 0; p < 64; p++) {
+        double sum = 0.0;
+        for (int i = 0; i < 64; i++) {
+            full[p * 64 + i] = (int32_t)llrint(ldexp(E[p * 64 + i], S));
+            sum += E[p * 64 + i];
+        }
+        off[p] = (float)(-127.0 * sum);
+    }
+    return S;
+}
+
+void sdct_oracle_inverse_tensor(int layout, const uint8_t *coef, size_t plane_stride, size_t width, size_t height,
+                                int eyes, size_t eye_stride, const float lut[64], uint8_t *out, size_t pitch, size_t xstep)
+{
+    float tab[64], off[64];
+    static int32_t full[64 * 64];
+    sdct_oracle_tables(lut, layout, tab, SDCT_O_TAB_INVERSE);
+    const int S = inverse_tensor_matrix(layout, tab, full, off);
+    const float unscale = ldexpf(1.f, -S);
+    if (layout != SDCT_O_LAYOUT_C) eyes = 1;
+    for (size_t band = 0; band < height / 8; band++)
+        for (int eye = 0; eye < eyes; eye++)
+            for (size_t bx = 0; bx < width / 8; bx++) {
+                int32_t q[64];
+                for (int i = 0; i < 64; i++)
+                    q[i] = *coef_addr(layout, (uint8_t *)coef, plane_stride, width, eyes, band, eye, bx, i);
+                uint8_t *dst = out + (size_t)eye * eye_stride + band * 8 * pitch + bx * 8 * xstep;
+                for (int p = 0; p < 64; p++) {
+                    int32_t d1 = 0, d0 = 0;
+                    for (int i = 0; i < 64; i++) {
+                        const int32_t f = full[p * 64 + i];
+                        const int32_t hi = (f + 512) >> 10, lo = f - hi * 1024;
+                        d1 += q[i] * hi;
+                        d0 += q[i] * lo;
+                    }
+                    const float t = fmaf((float)d1, 1024.f, (float)d0);
+                    dst[(p >> 3) * pitch + (size_t)(p & 7) * xstep] = pixel_u8(fmaf(t, unscale, off[p]));
+                }
+            }
+}
+
 /* component reorder: interleaved rows (ncomp bytes per pixel) <-> ncomp planar planes */
 void sdct_oracle_deinterleave(const uint8_t *in, size_t pitch, size_t width, size_t height, int ncomp, uint8_t *out)
 {

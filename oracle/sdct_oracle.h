@@ -73,6 +73,9 @@ void sdct_oracle_forward(int layout, int mode, int quirks, const uint8_t *in, si
 /* inverse (PARITY UNPINNED, see header): coefficient layouts as above -> pixels */
 void sdct_oracle_inverse(int layout, const uint8_t *coef, size_t plane_stride, size_t width, size_t height,
                          int eyes, size_t eye_stride, const float lut[64], uint8_t *out, size_t pitch, size_t xstep);
+/* inverse, mode TENSOR (exact-integer matrix form with the dequantiser folded in; parity unpinned) */
+void sdct_oracle_inverse_tensor(int layout, const uint8_t *coef, size_t plane_stride, size_t width, size_t height,
+                         int eyes, size_t eye_stride, const float lut[64], uint8_t *out, size_t pitch, size_t xstep);
 
 /* component reorder: interleaved (width*ncomp bytes per row) <-> ncomp planar planes ---- */
 void sdct_oracle_deinterleave(const uint8_t *in, size_t pitch, size_t width, size_t height,

@@ -111,9 +111,10 @@ int run_device(sdct_context *ctx, int op, const sdct_job *j, const uint8_t *pixe
     KParams p;
     memset(&p, 0, sizeof(p));
     const bool tensor = (j->flags & SDCT_TENSOR) != 0;
-    if (tensor && op != SDCT_K_OP_FORWARD) return fail(SDCT_NOT_SUPPORTED, "SDCT_TENSOR is implemented for the forward transform only");
+    if (tensor && op == SDCT_K_OP_ROUNDTRIP) return fail(SDCT_NOT_SUPPORTED, "SDCT_TENSOR is implemented for the forward and the inverse transform, not for the fused round trip");
     if (tensor && (j->flags & (SDCT_FAST | SDCT_QUIRK_AVX_X3))) return fail(SDCT_INVALID_PARAMETER, "SDCT_TENSOR excludes SDCT_FAST and SDCT_QUIRK_AVX_X3");
-    rc = tensor ? build_tc_tables(j, lut, p.tab) : build_tables(j, lut, op, p.tab, p.tab2, p.off);
+    const bool tensor_inv = tensor && op == SDCT_K_OP_INVERSE;
+    rc = (tensor && !tensor_inv) ? build_tc_tables(j, lut, p.tab) : build_tables(j, lut, op, p.tab, p.tab2, p.off);
     if (rc) return rc;
     p.pixels = pixels; p.coefs = coefs; p.pixels_out = pixels_out;
     p.pitch = j->pitch; p.eye_stride = j->eye_stride; p.pixel_frame_stride = j->pixel_frame_stride;
@@ -139,7 +140,37 @@ int run_device(sdct_context *ctx, int op, const sdct_job *j, const uint8_t *pixe
     CU_TRY(cudaSetDevice(ctx->device));
     const int mode = (j->flags & SDCT_FAST) ? SDCT_K_FAST : SDCT_K_EXACT;
     const int x3 = (j->flags & SDCT_QUIRK_AVX_X3) ? 1 : 0;
-    if (tensor) {
+    if (tensor_inv) {
+        // the tensor-core inverse moves whole 16-byte pieces on both sides; other geometries have no kernel (the fp32
+        // inverse is a different arithmetic definition, so it is not substituted silently)
+        if (g.comps != 1 || p.pixel_vec != 2 || !p.coef_aligned16 || (j->layout == SDCT_LAYOUT_C && (blocks & 15)))
+            return fail(SDCT_NOT_SUPPORTED, "SDCT_TENSOR inverse needs one component, 16-byte-aligned pixel rows and coefficients, "
+                                            "an even number of blocks per row (layout C: a multiple of 16 blocks)");
+        cudaStream_t st = stream ? stream : ctx->stream;
+        sdct_context::InvOperand *op_entry = nullptr;
+        {
+            std::lock_guard<std::mutex> lock(ctx->inv_mu);
+            for (auto &e : ctx->inv_cache)
+                if (e.d && e.layout == j->layout && memcmp(e.lut, lut, sizeof(e.lut)) == 0) op_entry = &e;
+            if (!op_entry) {
+                op_entry = &ctx->inv_cache[ctx->inv_next++ % 4];
+                static thread_local uint16_t operand[128 * 64];
+                float scale[64];
+                for (int i = 0; i < 64; i++) scale[i] = p.tab[i].x;
+                op_entry->S = sdct_tc_inverse_operand(j->layout, scale, operand, op_entry->off_cols);
+                if (!op_entry->d) CU_TRY(cudaMalloc(&op_entry->d, sizeof(operand)));
+                // pageable source: the copy is staged before the call returns, and it is ordered before the launch below
+                CU_TRY(cudaMemcpyAsync(op_entry->d, operand, sizeof(operand), cudaMemcpyHostToDevice, st));
+                op_entry->layout = j->layout;
+                memcpy(op_entry->lut, lut, sizeof(op_entry->lut));
+            }
+            p.tc_matrix = op_entry->d;
+            for (int c = 0; c < 64; c++) p.tab[c] = make_float2(op_entry->off_cols[c], op_entry->off_cols[c]);
+            const float unscale = std::ldexp(1.f, -op_entry->S);
+            p.tab2[0] = make_float2(unscale, unscale);
+        }
+        CU_TRY(sdct_k_launch_tc(op, j->layout, &p, st));
+    } else if (tensor) {
         p.tc_matrix = ctx->d_tc_matrix[j->layout == SDCT_LAYOUT_A ? 0 : 1];
         CU_TRY(sdct_k_launch_tc(op, j->layout, &p, stream ? stream : ctx->stream));
     } else {
@@ -225,6 +256,7 @@ void sdct_destroy(sdct_context *c)
     }
     if (c->stream) { cudaStreamSynchronize(c->stream); cudaStreamDestroy(c->stream); }
     cudaFree(c->d_tc_matrix[0]); cudaFree(c->d_tc_matrix[1]);
+    for (auto &e : c->inv_cache) cudaFree(e.d);
     delete c;
 }
 

@@ -38,6 +38,11 @@ struct sdct_context {
     std::atomic<uint64_t> launches{0};
     std::mutex host_mu;  // the host pipeline owns the slots
     void *d_tc_matrix[2] = {nullptr, nullptr};  // tensor-core B operand: [0] layout-A column order, [1] natural order
+    // tensor-core inverse operands depend on the LUT: a small cache keyed by (layout, LUT)
+    struct InvOperand { void *d = nullptr; int layout = -1; float lut[64]; float off_cols[64]; int S = 0; };
+    InvOperand inv_cache[4];
+    unsigned inv_next = 0;
+    std::mutex inv_mu;
 };
 
 struct Geometry {
@@ -49,3 +54,6 @@ int sdct_validate(const sdct_job *j, Geometry *g);
 void sdct_tc_integer_matrix(int32_t K[64 * 64]);
 // the 16 KiB B operand for `layout`: fp16 digits of K in the UMMA canonical K-major layout
 void sdct_tc_operand(int layout, uint16_t out[128 * 64]);
+// the LUT-dependent 16 KiB B operand of the tensor-core inverse; returns the scaling exponent S, fills the
+// per-column offsets -127 * sum_i E[p][i]
+int sdct_tc_inverse_operand(int layout, const float tab[64], uint16_t out[128 * 64], float off_cols[64]);

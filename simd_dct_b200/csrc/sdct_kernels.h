@@ -57,5 +57,12 @@ static inline int sdct_tc_column_position(int layout, int j)
 {
     return layout == SDCT_K_LAYOUT_A ? 16 * ((j & 7) >> 1) + 2 * (j >> 3) + (j & 1) : j;
 }
+// tensor-core inverse: D column j -> pixel y*8+x of the block.  A thread receives columns 8k + 2q + e; chunk k / 4
+// is then the pixel row 2q + k/4 and (k % 4, e) its eight pixels, so a thread stores whole 8-byte pixel rows.
+static inline int sdct_tc_inverse_column_pixel(int j)
+{
+    const int k = j >> 3, q = (j & 7) >> 1, e = j & 1;
+    return (2 * q + (k >> 2)) * 8 + 2 * (k & 3) + e;
+}
 // the 8-point kernels on n raw 8-float vectors (device memory, in place); see dct8_selftest_kernel
 extern "C" cudaError_t sdct_k_selftest(float *d_data, uint32_t n, int kind, cudaStream_t s);

@@ -182,15 +182,27 @@ SDCT_DEV void mma_f16_ts(uint32_t d_tmem, uint32_t a_tmem, uint64_t b_desc, uint
         : "memory");
 }
 
-// shared-memory matrix descriptor: K-major, no swizzle (cute::UMMA::SmemDescriptor, version 1)
-SDCT_DEV uint64_t b_descriptor(uint32_t smem_addr)
+// shared-memory matrix descriptor, no swizzle (cute::UMMA::SmemDescriptor, version 1): 8 x 16-byte core matrices,
+// lbo = bytes between core matrices along K, sbo = bytes between core matrices along M / N (either major-ness)
+SDCT_DEV uint64_t smem_descriptor(uint32_t smem_addr, uint32_t lbo, uint32_t sbo)
 {
     uint64_t d = 0;
     d |= (uint64_t)((smem_addr >> 4) & 0x3fff);
-    d |= (uint64_t)((B_LBO >> 4) & 0x3fff) << 16;
-    d |= (uint64_t)((B_SBO >> 4) & 0x3fff) << 32;
+    d |= (uint64_t)((lbo >> 4) & 0x3fff) << 16;
+    d |= (uint64_t)((sbo >> 4) & 0x3fff) << 32;
     d |= (uint64_t)1 << 46;   // descriptor version (Blackwell)
     return d;                 // base offset 0, layout type 0 = no swizzle
+}
+SDCT_DEV uint64_t b_descriptor(uint32_t smem_addr) { return smem_descriptor(smem_addr, B_LBO, B_SBO); }
+
+// D[tmem] (+)= A[smem] * B[smem]^T, kind::f16, fp32 accumulate
+SDCT_DEV void mma_f16_ss(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t accumulate)
+{
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
+        : "memory");
 }
 
 // instruction descriptor (cute::UMMA::InstrDescriptor): D = F32, A = B = F16, both K-major, M = 128, N = 128
@@ -817,6 +829,227 @@ __global__ void __launch_bounds__(THREADS, 1) forward_tc_kernel(const __grid_con
     if (warp == 0) tmem_dealloc(tmem_base);
 }
 
+
+// =====================================================================================================
+// Inverse (levels -> pixels) on the tensor cores: X = E * q with the dequantiser folded into the matrix
+// (oracle/sdct_oracle.c: sdct_oracle_inverse_tensor; host side: sdct_tc_inverse_operand).  Same role
+// structure, barriers and TMEM D stages as the forward kernel; what differs:
+//   * the A operand (128 blocks x 64 levels, fp16 subnormals) lives in SHARED memory, because the natural
+//     order of the coefficient bytes decides its major-ness: layout A (64 contiguous bytes per block) is
+//     K-major, layouts B and C (8 / 128 consecutive BLOCKS per coefficient) are MN-major - the 8-byte run
+//     "coefficient i of 8 blocks" zero-extended to fp16 is exactly one 16-byte row of a UMMA core matrix, so
+//     the producer is a straight 2x expansion of 16-byte pieces, no gather and no transpose anywhere;
+//   * D column j is pixel sdct_tc_inverse_column_pixel(j): a chunk hands a thread one whole 8-byte pixel row
+//     of its two blocks (8 blocks apart), stored as 8-byte vectors (a warp's store covers 64 contiguous bytes of a row).
+constexpr int INV_A_STAGE_BYTES = TILE * 64 * 2;          // 16 KiB
+constexpr int INV_A_LBO = 128, INV_A_SBO = 1024;          // core matrices: 8 along K contiguous, then the next 8 blocks
+constexpr int INV_RING = 6, INV_RAW_BYTES = TILE * 64;    // raw coefficient bytes of a tile: 8 KiB
+constexpr int SMEM_INV_A_OFF = B_BYTES, SMEM_INV_RING_OFF = SMEM_INV_A_OFF + A_STAGES * INV_A_STAGE_BYTES;
+static_assert(SMEM_INV_RING_OFF + INV_RING * INV_RAW_BYTES <= SMEM_BAR_OFF, "inverse shared-memory plan");
+
+template <int LAYOUT>
+SDCT_DEV void inv_producer_role(const KParams &p, uint64_t *bars, uint8_t *a_stages, uint8_t *ring, uint32_t L)
+{
+    // this thread's four 16-byte pieces of a tile's raw bytes, and where their two expanded halves go
+    uint32_t raw_off[4], dst_off[4];
+#pragma unroll
+    for (int m = 0; m < 4; m++) {
+        const uint32_t c = L + 128u * m;   // piece index 0..511
+        if (LAYOUT == SDCT_K_LAYOUT_C) {
+            const uint32_t i = c >> 3, jj = c & 7;        // plane i, blocks 16 jj .. 16 jj + 15
+            raw_off[m] = i * 128u + 16u * jj;
+            dst_off[m] = (2u * jj) * INV_A_SBO + i * 16u;  // second half: the next 8 blocks, + SBO
+        } else if (LAYOUT == SDCT_K_LAYOUT_B) {
+            raw_off[m] = 16u * c;                         // group c / 32, coefficients 2 (c % 32), + 1: 8 blocks each
+            dst_off[m] = 32u * c;                         // second half: the next coefficient, + 16
+        } else {
+            raw_off[m] = 16u * c;                         // block c / 4, levels 16 (c % 4) .. + 15
+            dst_off[m] = (c >> 5) * INV_A_SBO + ((c >> 2) & 7u) * 16u + (2u * (c & 3u)) * INV_A_LBO;   // second half: + LBO
+        }
+    }
+    constexpr uint32_t second = LAYOUT == SDCT_K_LAYOUT_C ? INV_A_SBO : (LAYOUT == SDCT_K_LAYOUT_B ? 16 : INV_A_LBO);
+    TileWalk wi;
+    wi.init(p, 0, 1);
+    auto issue = [&](uint32_t j) {
+        if (wi.tile < p.tiles) {
+            const Tile t = tile_at<1, TILE>(p, wi);
+            const uint64_t n_first = (uint64_t)p.row0 * p.bpr + t.n0;
+            uint8_t *slot = ring + (j % INV_RING) * INV_RAW_BYTES;
+#pragma unroll
+            for (int m = 0; m < 4; m++) {
+                if (LAYOUT == SDCT_K_LAYOUT_C) {
+                    const uint32_t c = L + 128u * m, i = c >> 3, b0 = 16u * (c & 7);
+                    if (b0 < t.count) cp_async16(slot + raw_off[m], t.coef + (uint64_t)i * p.coef_plane_stride + n_first + b0);
+                } else {
+                    if (raw_off[m] < t.count * 64u) cp_async16(slot + raw_off[m], t.coef + n_first * 64 + raw_off[m]);
+                }
+            }
+        }
+        wi.next(p);
+        cp_async_commit();
+    };
+    for (uint32_t j = 0; j < INV_RING; j++) issue(j);
+    uint32_t tile = blockIdx.x;
+    for (uint32_t k = 0;; k++, tile += gridDim.x) {
+        if (tile >= p.tiles) return;
+        cp_async_wait<INV_RING - 1>();   // this thread's pieces of tile k have landed (it expands only its own)
+        const uint8_t *slot = ring + (k % INV_RING) * INV_RAW_BYTES;
+        const uint32_t sa = k % A_STAGES, ua = k / A_STAGES;
+        uint4 raw[4];
+#pragma unroll
+        for (int m = 0; m < 4; m++) raw[m] = *reinterpret_cast<const uint4 *>(slot + raw_off[m]);
+        mbar_wait(bars + BAR_A_EMPTY + sa, (ua & 1) ^ 1);   // the MMAs of tile k - 4 have read this A stage
+        uint8_t *a = a_stages + sa * INV_A_STAGE_BYTES;
+#pragma unroll
+        for (int m = 0; m < 4; m++) {
+            const uint32_t w[4] = {raw[m].x, raw[m].y, raw[m].z, raw[m].w};
+            uint32_t h[8];
+#pragma unroll
+            for (int i = 0; i < 4; i++) {
+                h[2 * i] = __byte_perm(w[i], 0u, 0x4140);
+                h[2 * i + 1] = __byte_perm(w[i], 0u, 0x4342);
+            }
+            *reinterpret_cast<uint4 *>(a + dst_off[m]) = make_uint4(h[0], h[1], h[2], h[3]);
+            *reinterpret_cast<uint4 *>(a + dst_off[m] + second) = make_uint4(h[4], h[5], h[6], h[7]);
+        }
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic stores -> the tensor core's async-proxy reads
+        mbar_arrive(bars + BAR_A_FULL + sa);
+        issue(k + INV_RING);
+    }
+}
+
+template <int LAYOUT>
+SDCT_DEV void inv_mma_role(const KParams &p, uint64_t *bars, uint32_t tmem_base, uint32_t a_stages_addr, uint64_t bdesc, uint32_t m)
+{
+    // layout A: K-major A operand; layouts B, C: MN-major (instruction descriptor bit 15)
+    constexpr uint32_t idesc = IDESC | (LAYOUT == SDCT_K_LAYOUT_A ? 0u : (1u << 15));
+    const uint64_t bd[4] = {bdesc, bdesc + (uint64_t)((2 * B_LBO) >> 4), bdesc + (uint64_t)((4 * B_LBO) >> 4), bdesc + (uint64_t)((6 * B_LBO) >> 4)};
+    for (uint32_t k = m;; k += MMA_WARPS) {
+        if (blockIdx.x + k * gridDim.x >= p.tiles) break;
+        const uint32_t sa = k % A_STAGES, ua = k / A_STAGES, sd = k % D_STAGES;
+        mbar_wait(bars + BAR_A_FULL + sa, ua & 1);
+        if (k >= D_STAGES)
+            mbar_wait(bars + BAR_D_EMPTY + ((k + 1) & 1) * D_STAGES + sd, ((k - D_STAGES) / (2 * D_STAGES)) & 1);
+        fence_after();
+        const uint64_t ad = smem_descriptor(a_stages_addr + sa * INV_A_STAGE_BYTES, INV_A_LBO, INV_A_SBO);
+        const uint32_t tD = tmem_base + TMEM_D_OFF + sd * D_COLS;
+#pragma unroll
+        for (int ks = 0; ks < 4; ks++)   // K = 16 levels per instruction: two core matrices along K
+            mma_f16_ss(tD, ad + (uint64_t)((2 * ks * INV_A_LBO) >> 4), bd[ks], idesc, ks);
+        mma_commit(bars + BAR_A_EMPTY + sa);
+        mma_commit(bars + BAR_D_FULL + (k & 1) * D_STAGES + sd);
+    }
+}
+
+
+template <int LAYOUT>
+SDCT_DEV void inv_consumer_role(const KParams &p, uint64_t *bars, uint32_t tmem_base, uint32_t c, uint32_t L, uint32_t lane_field)
+{
+    const uint32_t lane = L & 31, g = lane >> 2, q = lane & 3;
+    // this thread's 16 pixel offsets -127 * sum E (columns 8k + 2q + e), and the common 2^(24 - S)
+    F2 off[8];
+#pragma unroll
+    for (int k = 0; k < 8; k++) off[k] = make_float2(p.tab[8 * k + 2 * q].x, p.tab[8 * k + 2 * q + 1].x);
+    const F2 unscale = splat(p.tab2[0].x);
+    // TMEM lane = block of the tile (the A rows are in natural order here): a 16x256b load hands this thread lanes
+    // g and g + 8 of a 16-lane half, i.e. blocks P = sp0 + 16 half and Q = P + 8
+    const uint32_t sp0 = (L >> 5) * 32u + g;
+    TileWalk wk;
+    wk.init(p, c, CONSUMER_WGS);
+    for (uint32_t k = c;; k += CONSUMER_WGS, wk.next(p)) {
+        if (wk.tile >= p.tiles) break;
+        const uint32_t sd = k % D_STAGES, ud = k / (2 * D_STAGES);
+        uint64_t *d_full = bars + BAR_D_FULL + c * D_STAGES + sd, *d_empty = bars + BAR_D_EMPTY + c * D_STAGES + sd;
+        const Tile cur = tile_at<1, TILE>(p, wk);
+        uint8_t *px[2][2];   // [half][P, Q]: pixel row 2q of the block
+#pragma unroll
+        for (int half = 0; half < 2; half++)
+#pragma unroll
+            for (int e = 0; e < 2; e++)
+                px[half][e] = const_cast<uint8_t *>(block_pixels<1>(p, cur, sp0 + 16 * half + 8 * e)) + (uint64_t)(2 * q) * p.pitch;
+        mbar_wait(d_full, ud & 1);
+        fence_after();
+        float hiA[16], loA[16], hiB[16], loB[16];
+        const uint32_t td = tmem_base + TMEM_D_OFF + sd * D_COLS + lane_field;
+        tmem_ld_16x256b_x4(td, hiA);
+        tmem_ld_16x256b_x4(td + 64, loA);
+#define SDCT_TC_INV_CHUNK(C, HI, LO, NHI, NLO)                                                                        \
+        {                                                                                                             \
+            constexpr int half = (C) >> 1, kk = (C) & 1;                                                              \
+            tmem_wait_ld(HI, LO);                                                                                     \
+            if ((C) < 3) {                                                                                            \
+                const uint32_t tn = td + ((uint32_t)(16 * (((C) + 1) >> 1)) << 16) + 32 * (((C) + 1) & 1);            \
+                tmem_ld_16x256b_x4(tn, NHI);                                                                          \
+                tmem_ld_16x256b_x4(tn + 64, NLO);                                                                     \
+            } else {                                                                                                  \
+                fence_before();                                                                                       \
+                mbar_arrive(d_empty);                                                                                 \
+            }                                                                                                         \
+            F2 bp[4], bq[4];   /* pixels x = 2 k2, 2 k2 + 1 of row 2q + kk, blocks P and Q: bit patterns */           \
+            _Pragma("unroll") for (int k2 = 0; k2 < 4; k2++) {                                                        \
+                const F2 tp = fma2(make_float2(HI[4 * k2], HI[4 * k2 + 1]), splat(1024.f), make_float2(LO[4 * k2], LO[4 * k2 + 1]));         \
+                const F2 tq = fma2(make_float2(HI[4 * k2 + 2], HI[4 * k2 + 3]), splat(1024.f), make_float2(LO[4 * k2 + 2], LO[4 * k2 + 3])); \
+                bp[k2] = mulk(fma2(tp, unscale, off[4 * kk + k2]), SDCT_DENORM_MIN);                                  \
+                bq[k2] = mulk(fma2(tq, unscale, off[4 * kk + k2]), SDCT_DENORM_MIN);                                  \
+            }                                                                                                         \
+            if (sp0 + 16 * half < cur.count)                                                                          \
+                *reinterpret_cast<uint2 *>(px[half][0] + (uint64_t)kk * p.pitch) =                                    \
+                    make_uint2(pack4_sat(bp[0].x, bp[0].y, bp[1].x, bp[1].y), pack4_sat(bp[2].x, bp[2].y, bp[3].x, bp[3].y)); \
+            if (sp0 + 16 * half + 8 < cur.count)                                                                      \
+                *reinterpret_cast<uint2 *>(px[half][1] + (uint64_t)kk * p.pitch) =                                    \
+                    make_uint2(pack4_sat(bq[0].x, bq[0].y, bq[1].x, bq[1].y), pack4_sat(bq[2].x, bq[2].y, bq[3].x, bq[3].y)); \
+        }
+        SDCT_TC_INV_CHUNK(0, hiA, loA, hiB, loB)
+        SDCT_TC_INV_CHUNK(1, hiB, loB, hiA, loA)
+        SDCT_TC_INV_CHUNK(2, hiA, loA, hiB, loB)
+        SDCT_TC_INV_CHUNK(3, hiB, loB, hiA, loA)
+#undef SDCT_TC_INV_CHUNK
+    }
+}
+
+template <int LAYOUT>
+__global__ void __launch_bounds__(THREADS, 1) inverse_tc_kernel(const __grid_constant__ KParams p)
+{
+    extern __shared__ __align__(128) uint8_t smem[];
+    const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    uint64_t *bars = reinterpret_cast<uint64_t *>(smem + SMEM_BAR_OFF);
+    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(smem + SMEM_BAR_OFF + NUM_BARS * 8);
+    {
+        const uint4 *src = reinterpret_cast<const uint4 *>(p.tc_matrix);
+        uint4 *dst = reinterpret_cast<uint4 *>(smem + SMEM_B_OFF);
+        for (int i = threadIdx.x; i < B_BYTES / 16; i += THREADS) dst[i] = __ldg(src + i);
+    }
+    if (threadIdx.x == 0) {
+        for (int i = 0; i < A_STAGES; i++) {
+            mbar_init(bars + BAR_A_FULL + i, 128);
+            mbar_init(bars + BAR_A_EMPTY + i, 1);
+        }
+        for (int i = 0; i < 2 * D_STAGES; i++) {
+            mbar_init(bars + BAR_D_FULL + i, 1);
+            mbar_init(bars + BAR_D_EMPTY + i, 128);
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 0) tmem_alloc(tmem_slot);
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    fence_before();
+    __syncthreads();
+    fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+    const uint32_t lane_field = ((warp & 3u) * 32u) << 16;
+    static_assert(PRODUCER_WGS == 1, "the inverse kernel has one producer warpgroup");
+    if (warp < CONSUMER_WARP) {
+        inv_producer_role<LAYOUT>(p, bars, smem + SMEM_INV_A_OFF, smem + SMEM_INV_RING_OFF, threadIdx.x);
+    } else if (warp < MMA_WARP) {
+        const uint32_t c = (warp - CONSUMER_WARP) >> 2;
+        inv_consumer_role<LAYOUT>(p, bars, tmem_base, c, threadIdx.x & 127, lane_field);
+    } else if (warp < MMA_WARP + MMA_WARPS && lane == 0) {
+        inv_mma_role<LAYOUT>(p, bars, tmem_base, smem_u32(smem + SMEM_INV_A_OFF), b_descriptor(smem_u32(smem + SMEM_B_OFF)), warp - MMA_WARP);
+    }
+    fence_before();
+    __syncthreads();
+    if (warp == 0) tmem_dealloc(tmem_base);
+}
 }  // namespace tc
 }  // namespace sdct
 
@@ -888,9 +1121,22 @@ extern "C" int sdct_k_tc_trace(unsigned long long *host)
     return (int)cudaMemcpyFromSymbol(host, tc::g_trace, sizeof(tc::g_trace));
 }
 
+template <int LAYOUT>
+static cudaError_t launch_tc_inverse(const KParams &p, unsigned grid, cudaStream_t s)
+{
+    static bool attr_done = false;
+    if (!attr_done) {
+        cudaError_t e = cudaFuncSetAttribute(tc::inverse_tc_kernel<LAYOUT>, cudaFuncAttributeMaxDynamicSharedMemorySize, tc::SMEM_BYTES);
+        if (e != cudaSuccess) return e;
+        attr_done = true;
+    }
+    tc::inverse_tc_kernel<LAYOUT><<<grid, tc::THREADS, tc::SMEM_BYTES, s>>>(p);
+    return cudaGetLastError();
+}
+
 extern "C" cudaError_t sdct_k_launch_tc(int op, int layout, const KParams *pp, cudaStream_t s)
 {
-    if (op != SDCT_K_OP_FORWARD) return cudaErrorNotSupported;
+    if (op != SDCT_K_OP_FORWARD && op != SDCT_K_OP_INVERSE) return cudaErrorNotSupported;
     KParams p = *pp;
     p.layout = (uint32_t)layout;
     const unsigned long long blocks = (unsigned long long)p.rows * p.bpr;
@@ -900,6 +1146,20 @@ extern "C" cudaError_t sdct_k_launch_tc(int op, int layout, const KParams *pp, c
     if (tiles > 0xffff0000ull) return cudaErrorInvalidConfiguration;   // a TileWalk may step past the end without wrapping
     p.tiles = (uint32_t)tiles;
     { const char *e = getenv("SDCT_TC_ABLATE"); p.tc_ablate = e ? (uint32_t)atoi(e) : 0u; }
+    if (op == SDCT_K_OP_INVERSE) {
+        // single component, aligned geometry (checked by the caller); p.tab = column offsets, p.tab2[0] = 2^-S
+        p.tab2[0].x = p.tab2[0].y = ldexpf(p.tab2[0].x, tc::A_SCALE_LOG2);   // the A operand carries 2^-24 (bytes_to_half)
+        p.div_chunks = make_fastdiv(p.chunks);
+        p.div_bpr = make_fastdiv(p.bpr);
+        const unsigned sms_i = p.sm_count ? p.sm_count : 148u;
+        const unsigned grid_i = (unsigned)(tiles < sms_i ? tiles : sms_i);
+        switch (layout) {
+        case SDCT_K_LAYOUT_A: return launch_tc_inverse<SDCT_K_LAYOUT_A>(p, grid_i, s);
+        case SDCT_K_LAYOUT_B: return launch_tc_inverse<SDCT_K_LAYOUT_B>(p, grid_i, s);
+        case SDCT_K_LAYOUT_C: return launch_tc_inverse<SDCT_K_LAYOUT_C>(p, grid_i, s);
+        default: return cudaErrorInvalidValue;
+        }
+    }
     for (int c = 0; c < 64; c++) p.tab[c].x = p.tab[c].y = ldexpf(p.tab[c].x, tc::A_SCALE_LOG2);   // see bytes_to_half
     p.div_chunks = make_fastdiv(p.chunks);
     p.div_bpr = make_fastdiv(p.bpr);

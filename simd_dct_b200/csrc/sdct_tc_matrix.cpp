@@ -72,3 +72,50 @@ void sdct_tc_operand(int layout, uint16_t out[128 * 64])
         }
     }
 }
+
+// ---- inverse (sdct_tc.cu: inverse_tc_kernel) ---------------------------------------------------------------------
+// The dequantiser scale is folded into the matrix, so the operand depends on the LUT: E[p][i] = W[p][i] * tab[i]
+// (W = unnormalised inverse basis = 8 * C[u][y] * C[v][x], tab = the inverse scale table indexed by the layout's own
+// coefficient index i), scaled by the largest 2^S that keeps |round(2^S E)| < 2^20 - 512, split into two fp16 digits.
+// Row n of the operand = digit n / 64 of D column j = n % 64 = pixel sdct_tc_inverse_column_pixel(j).
+// oracle/sdct_oracle.c (inverse_tensor_matrix) restates this independently.
+int sdct_tc_inverse_operand(int layout, const float tab[64], uint16_t out[128 * 64], float off_cols[64])
+{
+    static thread_local double E[64 * 64];
+    double emax = 0.0;
+    for (int y = 0; y < 8; y++)
+        for (int x = 0; x < 8; x++)
+            for (int u = 0; u < 8; u++)
+                for (int v = 0; v < 8; v++) {
+                    const int i = layout == SDCT_K_LAYOUT_A ? v * 8 + u : u * 8 + v;
+                    const double w = (dct_entry(u, y) / kN) * (dct_entry(v, x) / kN);
+                    const double e = w * (double)tab[i];
+                    E[(y * 8 + x) * 64 + i] = e;
+                    if (std::fabs(e) > emax) emax = std::fabs(e);
+                }
+    int S = 0;
+    const double lim = 1048576.0 - 512.0;
+    if (emax > 0.0) {
+        S = (int)std::floor(std::log2(lim / emax));
+        while (std::ldexp(emax, S) >= lim) S--;
+        while (std::ldexp(emax, S + 1) < lim) S++;
+    }
+    memset(out, 0, 128 * 64 * sizeof(uint16_t));
+    for (int j = 0; j < 64; j++) {
+        const int px = sdct_tc_inverse_column_pixel(j);
+        double sum = 0.0;
+        for (int k = 0; k < 64; k++) {
+            const double e = E[px * 64 + k];
+            sum += e;
+            const int32_t full = (int32_t)std::llrint(std::ldexp(e, S));
+            const int32_t hi = (full + 512) >> 10, lo = full - hi * 1024;
+            for (int digit = 0; digit < 2; digit++) {
+                const int n = digit * 64 + j;
+                const size_t off = (size_t)(k >> 3) * (128 * 16) + (size_t)(n >> 3) * 128 + (size_t)(n & 7) * 16 + (size_t)(k & 7) * 2;
+                out[off / 2] = half_bits_of_int(digit == 0 ? hi : lo);
+            }
+        }
+        off_cols[j] = (float)(-127.0 * sum);
+    }
+    return S;
+}

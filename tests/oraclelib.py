@@ -59,6 +59,8 @@ class Oracle:
         L.sdct_oracle_forward.restype = None
         L.sdct_oracle_inverse.argtypes = [C.c_int, _u8p, _sz, _sz, _sz, C.c_int, _sz, _f32p, _u8p, _sz, _sz]
         L.sdct_oracle_inverse.restype = None
+        L.sdct_oracle_inverse_tensor.argtypes = L.sdct_oracle_inverse.argtypes
+        L.sdct_oracle_inverse_tensor.restype = None
         L.sdct_oracle_tables.argtypes = [_f32p, C.c_int, _f32p, C.c_int]
         L.sdct_oracle_tables.restype = None
         for n in ("dct8_scalar", "dct8_fast", "idct8"):
@@ -91,11 +93,11 @@ class Oracle:
                                      _pf(lut_), _p8(out), eyes * h * w // 64)
         return out
 
-    def inverse(self, layout, coef, w, h, lut_, eyes=1):
+    def inverse(self, layout, coef, w, h, lut_, eyes=1, tensor=False):
         coef = np.ascontiguousarray(coef)
         out = np.zeros((eyes * h, w), dtype=np.uint8)
-        self.lib.sdct_oracle_inverse(layout, _p8(coef), eyes * h * w // 64, w, h, eyes, h * w, _pf(lut_),
-                                     _p8(out), w, 1)
+        fn = self.lib.sdct_oracle_inverse_tensor if tensor else self.lib.sdct_oracle_inverse
+        fn(layout, _p8(coef), eyes * h * w // 64, w, h, eyes, h * w, _pf(lut_), _p8(out), w, 1)
         return out
 
     def tensor_matrix(self):

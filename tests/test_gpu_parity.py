@@ -546,3 +546,35 @@ def test_tensor_core_fused_rgb_components(ctx, oracle, layout):
     got = ctx.forward(dev(buf), lut, job).cpu().numpy().reshape(3, -1)
     for c in range(3):
         assert np.array_equal(got[c], oracle.forward(layout, rgb, lut, mode=ol.MODE_TENSOR, comp=c))
+
+
+@pytest.mark.parametrize("layout", LAYOUTS)
+def test_tensor_core_inverse_is_bit_exact_to_its_cpu_restatement(ctx, oracle, layout):
+    """SDCT_TENSOR inverse (sdct_tc.cu, inverse_tc_kernel): dequantiser folded into an exact-integer matrix,
+    A operand in shared memory (K-major for layout A, MN-major for B and C).  Byte-identical to
+    oracle.inverse(tensor=True); within one level of the fp32 inverse; unsupported geometries are refused."""
+    for (h, w, kind, seed) in ((512, 512, "smooth", 1), (48, 1088, "rand", 2), (8 * 1080, 1920, "smooth", 3)):
+        img = make_image(kind, h, w, seed=seed)
+        lut = rt_lut(layout)
+        coef = oracle.forward(layout, img, lut)
+        job = sd.dense_job(layout, w, h, flags=sd.TENSOR)
+        got = ctx.inverse(dev(coef), lut, job).cpu().numpy().reshape(h, w)
+        want = oracle.inverse(layout, coef, w, h, lut, tensor=True)
+        assert np.array_equal(got, want), (h, w, np.count_nonzero(got != want))
+        if h <= 512:
+            fp32 = oracle.inverse(layout, coef, w, h, lut)
+            d = np.abs(got.astype(int) - fp32.astype(int))
+            assert d.max() <= 1 and np.mean(d != 0) < 5e-3, (int(d.max()), float(np.mean(d != 0)))
+    # a second LUT on the same context (the LUT-dependent operand is rebuilt), several frames
+    f, h, w = 3, 64, 256
+    imgs = np.stack([make_image("smooth", h, w, seed=20 + k) for k in range(f)])
+    lut = (rt_lut(layout) * np.float32(1.5)).astype(np.float32)
+    coefs = np.stack([oracle.forward(layout, imgs[k], lut) for k in range(f)])
+    job = sd.dense_job(layout, w, h, frames=f, flags=sd.TENSOR)
+    got = ctx.inverse(dev(coefs), lut, job).cpu().numpy().reshape(f, h, w)
+    for k in range(f):
+        assert np.array_equal(got[k], oracle.inverse(layout, coefs[k], w, h, lut, tensor=True))
+    # interleaved RGB has no tensor-core inverse: refused, not silently replaced by the fp32 arithmetic
+    job = sd.dense_job(layout, 64, 64, components=3, flags=sd.TENSOR)
+    with pytest.raises(Exception):
+        ctx.inverse(torch.zeros(3 * 64 * 64, dtype=torch.uint8, device="cuda"), lut, job)
