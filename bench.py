@@ -385,6 +385,7 @@ def main():
             ctx.forward(d_in, lut, j, out=d_out)
             d_back = torch.empty_like(d_in)
             add(f"inverse_{lname}", lambda j=j, d_back=d_back: ctx.inverse(d_out, lut, j, out=d_back))
+            add(f"inverse_{lname}_tensor", lambda jt=jt, d_back=d_back: ctx.inverse(d_out, lut, jt, out=d_back))
             add(f"roundtrip_fused_{lname}_exact", lambda j=j, d_back=d_back: ctx.roundtrip(d_in, lut, j, out=d_back))
 
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,

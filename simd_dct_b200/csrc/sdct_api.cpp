@@ -143,7 +143,7 @@ int run_device(sdct_context *ctx, int op, const sdct_job *j, const uint8_t *pixe
     if (tensor_inv) {
         // the tensor-core inverse moves whole 16-byte pieces on both sides; other geometries have no kernel (the fp32
         // inverse is a different arithmetic definition, so it is not substituted silently)
-        if (g.comps != 1 || p.pixel_vec != 2 || !p.coef_aligned16 || (j->layout == SDCT_LAYOUT_C && (blocks & 15)))
+        if (g.comps != 1 || p.pixel_vec != 2 || !p.coef_aligned16 || (j->layout == SDCT_LAYOUT_C && (blocks & 15)) || (j->pitch >> 32))
             return fail(SDCT_NOT_SUPPORTED, "SDCT_TENSOR inverse needs one component, 16-byte-aligned pixel rows and coefficients, "
                                             "an even number of blocks per row (layout C: a multiple of 16 blocks)");
         cudaStream_t st = stream ? stream : ctx->stream;

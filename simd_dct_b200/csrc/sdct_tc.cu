@@ -843,61 +843,84 @@ __global__ void __launch_bounds__(THREADS, 1) forward_tc_kernel(const __grid_con
 //     of its two blocks (8 blocks apart), stored as 8-byte vectors (a warp's store covers 64 contiguous bytes of a row).
 constexpr int INV_A_STAGE_BYTES = TILE * 64 * 2;          // 16 KiB
 constexpr int INV_A_LBO = 128, INV_A_SBO = 1024;          // core matrices: 8 along K contiguous, then the next 8 blocks
-constexpr int INV_RING = 6, INV_RAW_BYTES = TILE * 64;    // raw coefficient bytes of a tile: 8 KiB
+constexpr int INV_RING = 6, INV_RAW_MAX = 128 * 80;       // raw coefficient bytes of a tile, padded rows: at most 10 KiB
 constexpr int SMEM_INV_A_OFF = B_BYTES, SMEM_INV_RING_OFF = SMEM_INV_A_OFF + A_STAGES * INV_A_STAGE_BYTES;
-static_assert(SMEM_INV_RING_OFF + INV_RING * INV_RAW_BYTES <= SMEM_BAR_OFF, "inverse shared-memory plan");
+static_assert(SMEM_INV_RING_OFF + INV_RING * INV_RAW_MAX <= SMEM_BAR_OFF, "inverse shared-memory plan");
+
+// raw ring slot: the tile's coefficient bytes with a row pitch that makes the expansion's 16-byte reads
+// conflict-free (A: 128 block rows of 64 B + 16; C: 64 plane rows of 128 B + 16; B: the 8 KiB image as it is)
+template <int LAYOUT> __host__ __device__ constexpr int inv_raw_pitch() { return LAYOUT == SDCT_K_LAYOUT_A ? 80 : (LAYOUT == SDCT_K_LAYOUT_C ? 144 : 0); }
+template <int LAYOUT> __host__ __device__ constexpr int inv_raw_bytes() { return LAYOUT == SDCT_K_LAYOUT_A ? 128 * 80 : (LAYOUT == SDCT_K_LAYOUT_C ? 64 * 144 : TILE * 64); }
 
 template <int LAYOUT>
 SDCT_DEV void inv_producer_role(const KParams &p, uint64_t *bars, uint8_t *a_stages, uint8_t *ring, uint32_t L)
 {
-    // this thread's four 16-byte pieces of a tile's raw bytes, and where their two expanded halves go
-    uint32_t raw_off[4], dst_off[4];
+    // Two piece-to-thread mappings.  COPY: piece c = L + 128 m in global order (coalesced cp.async).  EXPAND: the
+    // piece whose two expanded 16-byte halves this thread stores, chosen so that a quarter-warp's stores fall on
+    // 32 distinct banks.  Layout B expands the pieces it copied (no barrier); A and C read pieces other threads
+    // copied (one warpgroup barrier per tile, which also frees the slot read before).
+    constexpr bool OWN = LAYOUT == SDCT_K_LAYOUT_B;
+    constexpr int RAW = inv_raw_bytes<LAYOUT>(), PITCH = inv_raw_pitch<LAYOUT>();
+    uint32_t copy_dst[4], rd_off[4], dst_off[4];
 #pragma unroll
     for (int m = 0; m < 4; m++) {
-        const uint32_t c = L + 128u * m;   // piece index 0..511
+        const uint32_t c = L + 128u * m;   // 0..511
         if (LAYOUT == SDCT_K_LAYOUT_C) {
-            const uint32_t i = c >> 3, jj = c & 7;        // plane i, blocks 16 jj .. 16 jj + 15
-            raw_off[m] = i * 128u + 16u * jj;
-            dst_off[m] = (2u * jj) * INV_A_SBO + i * 16u;  // second half: the next 8 blocks, + SBO
+            copy_dst[m] = (c >> 3) * PITCH + 16u * (c & 7);          // plane c / 8, blocks 16 (c % 8) ..
+            const uint32_t i = c & 63, jj = c >> 6;                   // expand: plane i, blocks 16 jj .. 16 jj + 15
+            rd_off[m] = i * PITCH + 16u * jj;
+            dst_off[m] = (2u * jj) * INV_A_SBO + i * 16u;             // second half: the next 8 blocks, + SBO
         } else if (LAYOUT == SDCT_K_LAYOUT_B) {
-            raw_off[m] = 16u * c;                         // group c / 32, coefficients 2 (c % 32), + 1: 8 blocks each
-            dst_off[m] = 32u * c;                         // second half: the next coefficient, + 16
+            copy_dst[m] = 16u * c;                                    // group c / 32, coefficients 2 (c % 32), + 1: 8 blocks each
+            rd_off[m] = 16u * c;
+            dst_off[m] = 32u * c;                                     // second half: the next coefficient, + 16
         } else {
-            raw_off[m] = 16u * c;                         // block c / 4, levels 16 (c % 4) .. + 15
-            dst_off[m] = (c >> 5) * INV_A_SBO + ((c >> 2) & 7u) * 16u + (2u * (c & 3u)) * INV_A_LBO;   // second half: + LBO
+            copy_dst[m] = (c >> 2) * PITCH + 16u * (c & 3);          // block c / 4, levels 16 (c % 4) ..
+            const uint32_t blk = c & 127, ch = c >> 7;                // expand: block blk, levels 16 ch .. 16 ch + 15
+            rd_off[m] = blk * PITCH + 16u * ch;
+            dst_off[m] = (blk >> 3) * INV_A_SBO + (blk & 7u) * 16u + (2u * ch) * INV_A_LBO;   // second half: + LBO
         }
     }
     constexpr uint32_t second = LAYOUT == SDCT_K_LAYOUT_C ? INV_A_SBO : (LAYOUT == SDCT_K_LAYOUT_B ? 16 : INV_A_LBO);
+    // layout B: lanes 4..7 of every 8 store the second half first, so that the eight 16-byte stores of a phase
+    // cover 128 contiguous bytes' worth of banks
+    const uint32_t swap = OWN ? (L >> 2) & 1u : 0u;
+    constexpr int AHEAD = OWN ? INV_RING : INV_RING - 1;   // tiles whose copies are in flight
     TileWalk wi;
     wi.init(p, 0, 1);
     auto issue = [&](uint32_t j) {
         if (wi.tile < p.tiles) {
             const Tile t = tile_at<1, TILE>(p, wi);
             const uint64_t n_first = (uint64_t)p.row0 * p.bpr + t.n0;
-            uint8_t *slot = ring + (j % INV_RING) * INV_RAW_BYTES;
+            uint8_t *slot = ring + (j % INV_RING) * RAW;
 #pragma unroll
             for (int m = 0; m < 4; m++) {
+                const uint32_t c = L + 128u * m;
                 if (LAYOUT == SDCT_K_LAYOUT_C) {
-                    const uint32_t c = L + 128u * m, i = c >> 3, b0 = 16u * (c & 7);
-                    if (b0 < t.count) cp_async16(slot + raw_off[m], t.coef + (uint64_t)i * p.coef_plane_stride + n_first + b0);
+                    const uint32_t b0 = 16u * (c & 7);
+                    if (b0 < t.count) cp_async16(slot + copy_dst[m], t.coef + (uint64_t)(c >> 3) * p.coef_plane_stride + n_first + b0);
                 } else {
-                    if (raw_off[m] < t.count * 64u) cp_async16(slot + raw_off[m], t.coef + n_first * 64 + raw_off[m]);
+                    if (16u * c < t.count * 64u) cp_async16(slot + copy_dst[m], t.coef + n_first * 64 + 16u * c);
                 }
             }
         }
         wi.next(p);
         cp_async_commit();
     };
-    for (uint32_t j = 0; j < INV_RING; j++) issue(j);
+    for (uint32_t j = 0; j < AHEAD; j++) issue(j);
     uint32_t tile = blockIdx.x;
     for (uint32_t k = 0;; k++, tile += gridDim.x) {
         if (tile >= p.tiles) return;
-        cp_async_wait<INV_RING - 1>();   // this thread's pieces of tile k have landed (it expands only its own)
-        const uint8_t *slot = ring + (k % INV_RING) * INV_RAW_BYTES;
+        cp_async_wait<AHEAD - 1>();   // this thread's pieces of tile k have landed
+        if (!OWN) {
+            named_barrier(3);         // ... and everybody's; everybody has read tile k - 1
+            issue(k + AHEAD);         // into the slot of tile k - 1
+        }
+        const uint8_t *slot = ring + (k % INV_RING) * RAW;
         const uint32_t sa = k % A_STAGES, ua = k / A_STAGES;
         uint4 raw[4];
 #pragma unroll
-        for (int m = 0; m < 4; m++) raw[m] = *reinterpret_cast<const uint4 *>(slot + raw_off[m]);
+        for (int m = 0; m < 4; m++) raw[m] = *reinterpret_cast<const uint4 *>(slot + rd_off[m]);
         mbar_wait(bars + BAR_A_EMPTY + sa, (ua & 1) ^ 1);   // the MMAs of tile k - 4 have read this A stage
         uint8_t *a = a_stages + sa * INV_A_STAGE_BYTES;
 #pragma unroll
@@ -909,12 +932,18 @@ SDCT_DEV void inv_producer_role(const KParams &p, uint64_t *bars, uint8_t *a_sta
                 h[2 * i] = __byte_perm(w[i], 0u, 0x4140);
                 h[2 * i + 1] = __byte_perm(w[i], 0u, 0x4342);
             }
-            *reinterpret_cast<uint4 *>(a + dst_off[m]) = make_uint4(h[0], h[1], h[2], h[3]);
-            *reinterpret_cast<uint4 *>(a + dst_off[m] + second) = make_uint4(h[4], h[5], h[6], h[7]);
+            const uint4 lo = make_uint4(h[0], h[1], h[2], h[3]), hi = make_uint4(h[4], h[5], h[6], h[7]);
+            if (OWN) {
+                *reinterpret_cast<uint4 *>(a + dst_off[m] + (swap ? second : 0u)) = swap ? hi : lo;
+                *reinterpret_cast<uint4 *>(a + dst_off[m] + (swap ? 0u : second)) = swap ? lo : hi;
+            } else {
+                *reinterpret_cast<uint4 *>(a + dst_off[m]) = lo;
+                *reinterpret_cast<uint4 *>(a + dst_off[m] + second) = hi;
+            }
         }
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic stores -> the tensor core's async-proxy reads
         mbar_arrive(bars + BAR_A_FULL + sa);
-        issue(k + INV_RING);
+        if (OWN) issue(k + AHEAD);
     }
 }
 
@@ -961,12 +990,21 @@ SDCT_DEV void inv_consumer_role(const KParams &p, uint64_t *bars, uint32_t tmem_
         const uint32_t sd = k % D_STAGES, ud = k / (2 * D_STAGES);
         uint64_t *d_full = bars + BAR_D_FULL + c * D_STAGES + sd, *d_empty = bars + BAR_D_EMPTY + c * D_STAGES + sd;
         const Tile cur = tile_at<1, TILE>(p, wk);
-        uint8_t *px[2][2];   // [half][P, Q]: pixel row 2q of the block
+        uint8_t *px[2][2];   // [half][P, Q]: pixel row 2q of the block (one 32 x 32 -> 64-bit multiply each; pitch < 2^32)
+        const uint32_t pitch32 = (uint32_t)p.pitch;
+        const bool full = cur.count == TILE;
 #pragma unroll
         for (int half = 0; half < 2; half++)
 #pragma unroll
-            for (int e = 0; e < 2; e++)
-                px[half][e] = const_cast<uint8_t *>(block_pixels<1>(p, cur, sp0 + 16 * half + 8 * e)) + (uint64_t)(2 * q) * p.pitch;
+            for (int e = 0; e < 2; e++) {
+                const uint32_t slot = sp0 + 16 * half + 8 * e;
+                const uint32_t nl = cur.n0 + (slot < cur.count ? slot : 0u);   // keep addresses in range
+                const uint32_t r = fastdiv(nl, p.div_bpr), bx = nl - r * p.bpr, row = r + p.row0;
+                const uint32_t band = p.eyes == 2 ? row >> 1 : row;
+                uint8_t *b = const_cast<uint8_t *>(cur.pix) + ((uint64_t)(band * 8 + 2 * q) * pitch32 + bx * 8);
+                if (p.eyes == 2 && (row & 1)) b += p.eye_stride;
+                px[half][e] = b;
+            }
         mbar_wait(d_full, ud & 1);
         fence_after();
         float hiA[16], loA[16], hiB[16], loB[16];
@@ -992,11 +1030,11 @@ SDCT_DEV void inv_consumer_role(const KParams &p, uint64_t *bars, uint32_t tmem_
                 bp[k2] = mulk(fma2(tp, unscale, off[4 * kk + k2]), SDCT_DENORM_MIN);                                  \
                 bq[k2] = mulk(fma2(tq, unscale, off[4 * kk + k2]), SDCT_DENORM_MIN);                                  \
             }                                                                                                         \
-            if (sp0 + 16 * half < cur.count)                                                                          \
-                *reinterpret_cast<uint2 *>(px[half][0] + (uint64_t)kk * p.pitch) =                                    \
+            if (full || sp0 + 16 * half < cur.count)                                                                  \
+                *reinterpret_cast<uint2 *>(px[half][0] + (kk ? pitch32 : 0u)) =                                       \
                     make_uint2(pack4_sat(bp[0].x, bp[0].y, bp[1].x, bp[1].y), pack4_sat(bp[2].x, bp[2].y, bp[3].x, bp[3].y)); \
-            if (sp0 + 16 * half + 8 < cur.count)                                                                      \
-                *reinterpret_cast<uint2 *>(px[half][1] + (uint64_t)kk * p.pitch) =                                    \
+            if (full || sp0 + 16 * half + 8 < cur.count)                                                              \
+                *reinterpret_cast<uint2 *>(px[half][1] + (kk ? pitch32 : 0u)) =                                       \
                     make_uint2(pack4_sat(bq[0].x, bq[0].y, bq[1].x, bq[1].y), pack4_sat(bq[2].x, bq[2].y, bq[3].x, bq[3].y)); \
         }
         SDCT_TC_INV_CHUNK(0, hiA, loA, hiB, loB)
