@@ -933,7 +933,9 @@ SDCT_DEV void inv_producer_role(const KParams &p, uint64_t *bars, uint8_t *a_sta
                 h[2 * i + 1] = __byte_perm(w[i], 0u, 0x4342);
             }
             const uint4 lo = make_uint4(h[0], h[1], h[2], h[3]), hi = make_uint4(h[4], h[5], h[6], h[7]);
-            if (OWN) {
+            if (ablate_bits(p) & 2) {
+                if (lo.x == 0x12345678u && hi.y == 0x9abcdef0u) a[0] = 1;
+            } else if (OWN) {
                 *reinterpret_cast<uint4 *>(a + dst_off[m] + (swap ? second : 0u)) = swap ? hi : lo;
                 *reinterpret_cast<uint4 *>(a + dst_off[m] + (swap ? 0u : second)) = swap ? lo : hi;
             } else {
@@ -964,7 +966,7 @@ SDCT_DEV void inv_mma_role(const KParams &p, uint64_t *bars, uint32_t tmem_base,
         const uint32_t tD = tmem_base + TMEM_D_OFF + sd * D_COLS;
 #pragma unroll
         for (int ks = 0; ks < 4; ks++)   // K = 16 levels per instruction: two core matrices along K
-            mma_f16_ss(tD, ad + (uint64_t)((2 * ks * INV_A_LBO) >> 4), bd[ks], idesc, ks);
+            if (!(ablate_bits(p) & 1)) mma_f16_ss(tD, ad + (uint64_t)((2 * ks * INV_A_LBO) >> 4), bd[ks], idesc, ks);
         mma_commit(bars + BAR_A_EMPTY + sa);
         mma_commit(bars + BAR_D_FULL + (k & 1) * D_STAGES + sd);
     }
@@ -990,23 +992,27 @@ SDCT_DEV void inv_consumer_role(const KParams &p, uint64_t *bars, uint32_t tmem_
         const uint32_t sd = k % D_STAGES, ud = k / (2 * D_STAGES);
         uint64_t *d_full = bars + BAR_D_FULL + c * D_STAGES + sd, *d_empty = bars + BAR_D_EMPTY + c * D_STAGES + sd;
         const Tile cur = tile_at<1, TILE>(p, wk);
-        uint8_t *px[2][2];   // [half][P, Q]: pixel row 2q of the block (one 32 x 32 -> 64-bit multiply each; pitch < 2^32)
+        // pixel row 2q of this thread's four blocks (slots sp0, +8, +16, +24): one division for the first, the others
+        // step 8 blocks along the block row and wrap; 32 x 32 -> 64-bit address products (pitch < 2^32)
+        uint8_t *px[2][2];   // [half][P, Q]
         const uint32_t pitch32 = (uint32_t)p.pitch;
         const bool full = cur.count == TILE;
+        {
+            const uint32_t nl = cur.n0 + (sp0 < cur.count ? sp0 : 0u);
+            uint32_t r = fastdiv(nl, p.div_bpr), bx = nl - r * p.bpr;
 #pragma unroll
-        for (int half = 0; half < 2; half++)
-#pragma unroll
-            for (int e = 0; e < 2; e++) {
-                const uint32_t slot = sp0 + 16 * half + 8 * e;
-                const uint32_t nl = cur.n0 + (slot < cur.count ? slot : 0u);   // keep addresses in range
-                const uint32_t r = fastdiv(nl, p.div_bpr), bx = nl - r * p.bpr, row = r + p.row0;
-                const uint32_t band = p.eyes == 2 ? row >> 1 : row;
+            for (int i = 0; i < 4; i++) {
+                const uint32_t row = r + p.row0, band = p.eyes == 2 ? row >> 1 : row;
                 uint8_t *b = const_cast<uint8_t *>(cur.pix) + ((uint64_t)(band * 8 + 2 * q) * pitch32 + bx * 8);
                 if (p.eyes == 2 && (row & 1)) b += p.eye_stride;
-                px[half][e] = b;
+                px[i >> 1][i & 1] = b;
+                bx += 8;
+                while (bx >= p.bpr) { bx -= p.bpr; r++; }   // (a slot past the tile's end may point past the window: never stored)
             }
+        }
         mbar_wait(d_full, ud & 1);
         fence_after();
+        if (ablate_bits(p) & 4) { fence_before(); mbar_arrive(d_empty); continue; }
         float hiA[16], loA[16], hiB[16], loB[16];
         const uint32_t td = tmem_base + TMEM_D_OFF + sd * D_COLS + lane_field;
         tmem_ld_16x256b_x4(td, hiA);
@@ -1030,12 +1036,16 @@ SDCT_DEV void inv_consumer_role(const KParams &p, uint64_t *bars, uint32_t tmem_
                 bp[k2] = mulk(fma2(tp, unscale, off[4 * kk + k2]), SDCT_DENORM_MIN);                                  \
                 bq[k2] = mulk(fma2(tq, unscale, off[4 * kk + k2]), SDCT_DENORM_MIN);                                  \
             }                                                                                                         \
-            if (full || sp0 + 16 * half < cur.count)                                                                  \
-                *reinterpret_cast<uint2 *>(px[half][0] + (kk ? pitch32 : 0u)) =                                       \
-                    make_uint2(pack4_sat(bp[0].x, bp[0].y, bp[1].x, bp[1].y), pack4_sat(bp[2].x, bp[2].y, bp[3].x, bp[3].y)); \
-            if (full || sp0 + 16 * half + 8 < cur.count)                                                              \
-                *reinterpret_cast<uint2 *>(px[half][1] + (kk ? pitch32 : 0u)) =                                       \
-                    make_uint2(pack4_sat(bq[0].x, bq[0].y, bq[1].x, bq[1].y), pack4_sat(bq[2].x, bq[2].y, bq[3].x, bq[3].y)); \
+            const uint2 vp = make_uint2(pack4_sat(bp[0].x, bp[0].y, bp[1].x, bp[1].y), pack4_sat(bp[2].x, bp[2].y, bp[3].x, bp[3].y)); \
+            const uint2 vq = make_uint2(pack4_sat(bq[0].x, bq[0].y, bq[1].x, bq[1].y), pack4_sat(bq[2].x, bq[2].y, bq[3].x, bq[3].y)); \
+            uint2 *dp = reinterpret_cast<uint2 *>(px[half][0] + (kk ? pitch32 : 0u));                                 \
+            uint2 *dq = reinterpret_cast<uint2 *>(px[half][1] + (kk ? pitch32 : 0u));                                 \
+            if (ablate_bits(p) & 8) { if (vp.x == 0x12345678u && vq.y == 0x9abcdef0u) *dp = vp; }                     \
+            else if (full) { *dp = vp; *dq = vq; }                                                                    \
+            else {                                                                                                    \
+                if (sp0 + 16 * half < cur.count) *dp = vp;                                                            \
+                if (sp0 + 16 * half + 8 < cur.count) *dq = vq;                                                        \
+            }                                                                                                         \
         }
         SDCT_TC_INV_CHUNK(0, hiA, loA, hiB, loB)
         SDCT_TC_INV_CHUNK(1, hiB, loB, hiA, loA)

@@ -132,3 +132,22 @@ def test_tensor_mode_stays_within_one_lsb_of_exact(oracle, layout):
             d = np.abs(t.astype(int) - e.astype(int))
             assert d.max() <= 1
             assert np.mean(d != 0) <= 2e-3, np.mean(d != 0)
+
+
+@pytest.mark.parametrize("layout", [0, 1, 2])
+def test_tensor_inverse_definition_stays_within_one_level_of_the_fp32_inverse(oracle, layout):
+    """oracle.inverse(tensor=True) (dequantiser folded into an exact-integer matrix, two fp16 digits) against the
+    fp32 inverse definition: same pixels except for rare one-level rounding differences, for small and large LUTs;
+    both are this repo's definitions (the reference has no inverse)."""
+    import oraclelib as ol
+    from conftest import make_image
+    img = make_image("smooth", 64, 128, seed=5)
+    for scale in (4, 32):
+        t = ol.lut(scale).copy()
+        t[0] = 20.0
+        lut = (t * np.float32(255)).astype(np.float32) if layout == 1 else t
+        coef = oracle.forward(layout, img, lut)
+        a = oracle.inverse(layout, coef, 128, 64, lut).astype(int)
+        b = oracle.inverse(layout, coef, 128, 64, lut, tensor=True).astype(int)
+        d = np.abs(a - b)
+        assert d.max() <= 1 and np.mean(d != 0) < 5e-3, (int(d.max()), float(np.mean(d != 0)))
