@@ -18,6 +18,9 @@
  *       pinned only relative to mode EXACT (<= 1 LSB on a measured fraction of bytes).
  *   forward, mode TENSOR : this repo's integer-matrix form of the true DCT (exact integer sums, one
  *       fma + one multiply + round); no reference counterpart, pinned relative to mode EXACT.
+ *   inverse, mode TENSOR : this repo's integer-matrix form of the inverse with the dequantiser folded into the
+ *       matrix (sdct_oracle_inverse_tensor); PARITY UNPINNED like every inverse, pinned relative to the fp32
+ *       inverse definition (<= 1 level on a measured fraction of pixels).
  *   interleaved 3-component input : extension, defined by composition (deinterleave, then
  *       the pinned single-plane forward per component).
  *
