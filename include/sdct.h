@@ -44,7 +44,9 @@ enum {
     SDCT_FAST = 1,          /* FMA-contracted arithmetic defined in oracle/sdct_oracle.c (<= 1 LSB from SDCT_EXACT) */
     SDCT_QUIRK_AVX_X3 = 2,  /* layout B: reproduce the reference's X3 sign (src/simd_dct.cpp:2181); see DESIGN.md */
     SDCT_TENSOR = 4         /* tensor-core (tcgen05) integer form of the true DCT, defined in oracle/sdct_oracle.c mode TENSOR
-                               (<= 1 LSB from SDCT_EXACT); forward only for now */
+                               (<= 1 LSB from SDCT_EXACT).  Forward: every geometry.  Inverse: one component, 16-byte-aligned
+                               pixel rows and coefficients, an even number of blocks per row (SDCT_NOT_SUPPORTED otherwise).
+                               No fused round trip; excludes SDCT_FAST and SDCT_QUIRK_AVX_X3 */
 };
 
 typedef struct sdct_context sdct_context;
