@@ -366,7 +366,7 @@ def main():
     # secondary measurements (same batch; informative, not the headline)
     variants = {}
     if not args.no_variants:
-        vs = max(3, args.steps // 4)
+        vs = max(10, args.steps // 2)
 
         def add(name, fn, bytes_per_block=BYTES_PER_BLOCK, nblocks=blocks_per_rank):
             ms, _, _ = timed(fn, vs, 3)
