@@ -841,16 +841,57 @@ __global__ void __launch_bounds__(THREADS, 1) forward_tc_kernel(const __grid_con
 //     the producer is a straight 2x expansion of 16-byte pieces, no gather and no transpose anywhere;
 //   * D column j is pixel sdct_tc_inverse_column_pixel(j): a chunk hands a thread one whole 8-byte pixel row
 //     of its two blocks (8 blocks apart), stored as 8-byte vectors (a warp's store covers 64 contiguous bytes of a row).
-constexpr int INV_A_STAGE_BYTES = TILE * 64 * 2;          // 16 KiB
-constexpr int INV_A_LBO = 128, INV_A_SBO = 1024;          // core matrices: 8 along K contiguous, then the next 8 blocks
-constexpr int INV_RING = 6, INV_RAW_MAX = 128 * 80;       // raw coefficient bytes of a tile, padded rows: at most 10 KiB
+// A stage: core matrices (8 x 16 bytes) at LBO along K and SBO along the blocks.  Layouts B, C: the dense 128 / 1024.
+// Layout A: LBO = 144, so that the expansion stores of the four 16-level chunks of a block (2 LBO apart) fall on
+// different banks.
+template <int LAYOUT> __host__ __device__ constexpr uint32_t inv_lbo() { return LAYOUT == SDCT_K_LAYOUT_A ? 144u : 128u; }
+template <int LAYOUT> __host__ __device__ constexpr uint32_t inv_sbo() { return 8u * inv_lbo<LAYOUT>(); }
+constexpr int INV_A_STAGE_BYTES = 16 * 8 * 144;           // 18 KiB (layout A's padded form)
+// layouts A and B: a tile's raw bytes are one contiguous piece -> ONE bulk copy (cp.async.bulk) by the TMA thread.
+// Layout C's 64 plane segments of 128 bytes as 64 small bulk copies measured 256 us against 74 us for the producer's
+// own cp.async copies (the copy engine is per-operation bound at that size), so C keeps the latter.
+template <int LAYOUT> __host__ __device__ constexpr bool inv_bulk() { return LAYOUT != SDCT_K_LAYOUT_C; }
+constexpr int INV_RING = 6, INV_RAW_MAX = 64 * 144;       // raw coefficient bytes of a tile (layout C: padded plane rows): at most 9 KiB
 constexpr int SMEM_INV_A_OFF = B_BYTES, SMEM_INV_RING_OFF = SMEM_INV_A_OFF + A_STAGES * INV_A_STAGE_BYTES;
 static_assert(SMEM_INV_RING_OFF + INV_RING * INV_RAW_MAX <= SMEM_BAR_OFF, "inverse shared-memory plan");
 
 // raw ring slot: the tile's coefficient bytes with a row pitch that makes the expansion's 16-byte reads
 // conflict-free (A: 128 block rows of 64 B + 16; C: 64 plane rows of 128 B + 16; B: the 8 KiB image as it is)
-template <int LAYOUT> __host__ __device__ constexpr int inv_raw_pitch() { return LAYOUT == SDCT_K_LAYOUT_A ? 80 : (LAYOUT == SDCT_K_LAYOUT_C ? 144 : 0); }
-template <int LAYOUT> __host__ __device__ constexpr int inv_raw_bytes() { return LAYOUT == SDCT_K_LAYOUT_A ? 128 * 80 : (LAYOUT == SDCT_K_LAYOUT_C ? 64 * 144 : TILE * 64); }
+template <int LAYOUT> __host__ __device__ constexpr int inv_raw_pitch() { return LAYOUT == SDCT_K_LAYOUT_C ? 144 : 0; }
+template <int LAYOUT> __host__ __device__ constexpr int inv_raw_bytes() { return LAYOUT == SDCT_K_LAYOUT_C ? 64 * 144 : TILE * 64; }
+
+SDCT_DEV void bulk_copy_g2s(void *smem_dst, const void *gmem, uint32_t bytes, uint64_t *bar)
+{
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(smem_u32(smem_dst)), "l"(gmem), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+
+// the TMA warp lands each tile's raw coefficient bytes in the ring: lane 0 announces the byte count, then layouts A, B:
+// one copy of count * 64 contiguous bytes; layout C: lane l copies the tile's segments of planes l and l + 32
+template <int LAYOUT>
+SDCT_DEV void inv_bulk_role(const KParams &p, uint64_t *bars, uint8_t *ring, uint32_t lane)
+{
+    TileWalk w;
+    w.init(p, 0, 1);
+    for (uint32_t k = 0; w.tile < p.tiles; k++, w.next(p)) {
+        const uint32_t rs = k % INV_RING, ru = k / INV_RING;
+        const Tile t = tile_at<1, TILE>(p, w);
+        const uint64_t n_first = (uint64_t)p.row0 * p.bpr + t.n0;
+        uint64_t *full = bars + BAR_RING_FULL + rs;
+        uint8_t *slot = ring + rs * inv_raw_bytes<LAYOUT>();
+        if (lane == 0) {
+            mbar_wait(bars + BAR_RING_EMPTY + rs, (ru & 1) ^ 1);
+            mbar_expect_tx(full, t.count * 64u);
+            if (LAYOUT != SDCT_K_LAYOUT_C) bulk_copy_g2s(slot, t.coef + n_first * 64, t.count * 64u, full);
+        }
+        if (LAYOUT == SDCT_K_LAYOUT_C) {
+            __syncwarp();   // the slot is free and the byte count registered before any lane's copy can complete
+#pragma unroll
+            for (uint32_t i = lane; i < 64; i += 32)
+                bulk_copy_g2s(slot + i * inv_raw_pitch<LAYOUT>(), t.coef + (uint64_t)i * p.coef_plane_stride + n_first, t.count, full);
+        }
+    }
+}
 
 template <int LAYOUT>
 SDCT_DEV void inv_producer_role(const KParams &p, uint64_t *bars, uint8_t *a_stages, uint8_t *ring, uint32_t L)
@@ -859,8 +900,9 @@ SDCT_DEV void inv_producer_role(const KParams &p, uint64_t *bars, uint8_t *a_sta
     // piece whose two expanded 16-byte halves this thread stores, chosen so that a quarter-warp's stores fall on
     // 32 distinct banks.  Layout B expands the pieces it copied (no barrier); A and C read pieces other threads
     // copied (one warpgroup barrier per tile, which also frees the slot read before).
-    constexpr bool OWN = LAYOUT == SDCT_K_LAYOUT_B;
+    constexpr bool OWN = LAYOUT == SDCT_K_LAYOUT_B, BULK = inv_bulk<LAYOUT>();
     constexpr int RAW = inv_raw_bytes<LAYOUT>(), PITCH = inv_raw_pitch<LAYOUT>();
+    constexpr uint32_t INV_A_LBO = inv_lbo<LAYOUT>(), INV_A_SBO = inv_sbo<LAYOUT>();
     uint32_t copy_dst[4], rd_off[4], dst_off[4];
 #pragma unroll
     for (int m = 0; m < 4; m++) {
@@ -875,16 +917,16 @@ SDCT_DEV void inv_producer_role(const KParams &p, uint64_t *bars, uint8_t *a_sta
             rd_off[m] = 16u * c;
             dst_off[m] = 32u * c;                                     // second half: the next coefficient, + 16
         } else {
-            copy_dst[m] = (c >> 2) * PITCH + 16u * (c & 3);          // block c / 4, levels 16 (c % 4) ..
-            const uint32_t blk = c & 127, ch = c >> 7;                // expand: block blk, levels 16 ch .. 16 ch + 15
-            rd_off[m] = blk * PITCH + 16u * ch;
+            copy_dst[m] = 16u * c;
+            const uint32_t blk = c >> 2, ch = c & 3;                  // block c / 4, levels 16 (c % 4) .. + 15
+            rd_off[m] = 16u * c;
             dst_off[m] = (blk >> 3) * INV_A_SBO + (blk & 7u) * 16u + (2u * ch) * INV_A_LBO;   // second half: + LBO
         }
     }
     constexpr uint32_t second = LAYOUT == SDCT_K_LAYOUT_C ? INV_A_SBO : (LAYOUT == SDCT_K_LAYOUT_B ? 16 : INV_A_LBO);
     // layout B: lanes 4..7 of every 8 store the second half first, so that the eight 16-byte stores of a phase
     // cover 128 contiguous bytes' worth of banks
-    const uint32_t swap = OWN ? (L >> 2) & 1u : 0u;
+    const uint32_t swap = OWN ? (L >> 2) & 1u : 0u;   // (OWN: the natural piece order, whoever copied the pieces)
     constexpr int AHEAD = OWN ? INV_RING : INV_RING - 1;   // tiles whose copies are in flight
     TileWalk wi;
     wi.init(p, 0, 1);
@@ -907,14 +949,19 @@ SDCT_DEV void inv_producer_role(const KParams &p, uint64_t *bars, uint8_t *a_sta
         wi.next(p);
         cp_async_commit();
     };
-    for (uint32_t j = 0; j < AHEAD; j++) issue(j);
+    if (!BULK)
+        for (uint32_t j = 0; j < AHEAD; j++) issue(j);
     uint32_t tile = blockIdx.x;
     for (uint32_t k = 0;; k++, tile += gridDim.x) {
         if (tile >= p.tiles) return;
-        cp_async_wait<AHEAD - 1>();   // this thread's pieces of tile k have landed
-        if (!OWN) {
-            named_barrier(3);         // ... and everybody's; everybody has read tile k - 1
-            issue(k + AHEAD);         // into the slot of tile k - 1
+        if (BULK) {
+            mbar_wait(bars + BAR_RING_FULL + k % INV_RING, (k / INV_RING) & 1);   // the TMA thread's bulk copy has landed
+        } else {
+            cp_async_wait<AHEAD - 1>();   // this thread's pieces of tile k have landed
+            if (!OWN) {
+                named_barrier(3);         // ... and everybody's; everybody has read tile k - 1
+                issue(k + AHEAD);         // into the slot of tile k - 1
+            }
         }
         const uint8_t *slot = ring + (k % INV_RING) * RAW;
         const uint32_t sa = k % A_STAGES, ua = k / A_STAGES;
@@ -945,7 +992,12 @@ SDCT_DEV void inv_producer_role(const KParams &p, uint64_t *bars, uint8_t *a_sta
         }
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic stores -> the tensor core's async-proxy reads
         mbar_arrive(bars + BAR_A_FULL + sa);
-        if (OWN) issue(k + AHEAD);
+        if (BULK) {
+            __syncwarp();
+            if ((L & 31) == 0) mbar_arrive(bars + BAR_RING_EMPTY + k % INV_RING);   // this warp has read the slot
+        } else if (OWN) {
+            issue(k + AHEAD);
+        }
     }
 }
 
@@ -962,6 +1014,7 @@ SDCT_DEV void inv_mma_role(const KParams &p, uint64_t *bars, uint32_t tmem_base,
         if (k >= D_STAGES)
             mbar_wait(bars + BAR_D_EMPTY + ((k + 1) & 1) * D_STAGES + sd, ((k - D_STAGES) / (2 * D_STAGES)) & 1);
         fence_after();
+        constexpr uint32_t INV_A_LBO = inv_lbo<LAYOUT>(), INV_A_SBO = inv_sbo<LAYOUT>();
         const uint64_t ad = smem_descriptor(a_stages_addr + sa * INV_A_STAGE_BYTES, INV_A_LBO, INV_A_SBO);
         const uint32_t tD = tmem_base + TMEM_D_OFF + sd * D_COLS;
 #pragma unroll
@@ -1076,6 +1129,10 @@ __global__ void __launch_bounds__(THREADS, 1) inverse_tc_kernel(const __grid_con
             mbar_init(bars + BAR_D_FULL + i, 1);
             mbar_init(bars + BAR_D_EMPTY + i, 128);
         }
+        for (int i = 0; i < INV_RING; i++) {
+            mbar_init(bars + BAR_RING_FULL + i, 1);
+            mbar_init(bars + BAR_RING_EMPTY + i, 4);
+        }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 0) tmem_alloc(tmem_slot);
@@ -1085,7 +1142,7 @@ __global__ void __launch_bounds__(THREADS, 1) inverse_tc_kernel(const __grid_con
     fence_after();
     const uint32_t tmem_base = *tmem_slot;
     const uint32_t lane_field = ((warp & 3u) * 32u) << 16;
-    static_assert(PRODUCER_WGS == 1, "the inverse kernel has one producer warpgroup");
+    static_assert(PRODUCER_WGS == 1 && INV_RING <= TMA_RING, "the inverse kernel has one producer warpgroup and reuses the ring barriers");
     if (warp < CONSUMER_WARP) {
         inv_producer_role<LAYOUT>(p, bars, smem + SMEM_INV_A_OFF, smem + SMEM_INV_RING_OFF, threadIdx.x);
     } else if (warp < MMA_WARP) {
@@ -1093,6 +1150,8 @@ __global__ void __launch_bounds__(THREADS, 1) inverse_tc_kernel(const __grid_con
         inv_consumer_role<LAYOUT>(p, bars, tmem_base, c, threadIdx.x & 127, lane_field);
     } else if (warp < MMA_WARP + MMA_WARPS && lane == 0) {
         inv_mma_role<LAYOUT>(p, bars, tmem_base, smem_u32(smem + SMEM_INV_A_OFF), b_descriptor(smem_u32(smem + SMEM_B_OFF)), warp - MMA_WARP);
+    } else if (inv_bulk<LAYOUT>() && warp == TMA_WARP && (lane == 0 || LAYOUT == SDCT_K_LAYOUT_C)) {
+        inv_bulk_role<LAYOUT>(p, bars, smem + SMEM_INV_RING_OFF, lane);
     }
     fence_before();
     __syncthreads();
