@@ -47,6 +47,9 @@ struct KParams {
     // tensor-core kernels, TMA pixel path: CUtensorMap over the pixels as u32[frame][eye][row][W / 4]
     // (filled in by sdct_k_launch_tc; must stay 64-byte aligned inside the kernel parameter block)
     alignas(64) unsigned char tc_tensor_map[128];
+    // layout C coefficients as u8[frame][component][plane 0..63][block], box 128 blocks x 64 planes, 128-byte swizzle:
+    // the tensor-core inverse loads its tiles through it, the tensor-core forward stores them
+    alignas(64) unsigned char tc_coef_map[128];
 };
 
 extern "C" cudaError_t sdct_k_launch(int op, int layout, int mode, int x3, const KParams *p, cudaStream_t s);

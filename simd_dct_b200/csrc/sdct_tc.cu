@@ -172,6 +172,15 @@ SDCT_DEV void tma_load_box(void *smem_dst, const void *tensor_map, uint64_t *bar
                  : "memory");
 }
 
+// shared memory -> one box of a 4-D tensor (bulk async-group completion; clipped at the tensor's bounds)
+SDCT_DEV void tma_store_box(const void *tensor_map, const void *smem_src, int32_t x, int32_t y, int32_t z, int32_t w)
+{
+    asm volatile("cp.async.bulk.tensor.4d.global.shared::cta.bulk_group [%0, {%2, %3, %4, %5}], [%1];"
+                 ::"l"(tensor_map), "r"(smem_u32(smem_src)), "r"(x), "r"(y), "r"(z), "r"(w) : "memory");
+    asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+}
+SDCT_DEV void tma_store_wait_read() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+
 // D[tmem] (+)= A[tmem] * B[smem]^T, kind::f16, fp32 accumulate
 SDCT_DEV void mma_f16_ts(uint32_t d_tmem, uint32_t a_tmem, uint64_t b_desc, uint32_t idesc, uint32_t accumulate)
 {
@@ -667,7 +676,10 @@ SDCT_DEV void mma_role(const KParams &p, uint64_t *bars, uint32_t tmem_base, uin
     }
 }
 
-template <int LAYOUT, int COMPS, int CF>
+// CS (layout C): the staging image is the 64 x 128-byte box of the coefficient tensor map in the 128-byte swizzle
+// (16-byte piece j of plane i at piece j ^ (i % 8): a warp's byte-pair stores to four planes fall on disjoint banks
+// without padding), and ONE tensor-map store per tile replaces the warpgroup's flush.
+template <int LAYOUT, int COMPS, int CF, bool CS>
 SDCT_DEV void consumer_role(const KParams &p, uint64_t *bars, uint32_t tmem_base, uint8_t *img_base, uint32_t c, uint32_t L, uint32_t lane_field)
 {
     const uint32_t lane = L & 31, g = lane >> 2, q = lane & 3;
@@ -738,7 +750,8 @@ SDCT_DEV void consumer_role(const KParams &p, uint64_t *bars, uint32_t tmem_base
                         const uint32_t pq = pack_sat(__float_as_uint(e ? bq[k2].y : bq[k2].x), __float_as_uint(e ? bp[k2].y : bp[k2].x), 0u); \
                         uint8_t *d = LAYOUT == SDCT_K_LAYOUT_B                                                         \
                                          ? ((DIRECT) ? gdst + (sp >> 3) * 512 : img + (sp >> 3) * IMG_B_PITCH) + i * 8 + (sp & 7) \
-                                         : img + i * IMG_C_PITCH + sp;                                                \
+                                         : (CS ? img + i * 128u + ((((sp >> 4) ^ i) & 7u) << 4) + (sp & 15u)           \
+                                               : img + i * IMG_C_PITCH + sp);                                         \
                         *reinterpret_cast<uint16_t *>(d) = (uint16_t)pq;                                              \
                     }                                                                                                 \
                 }                                                                                                     \
@@ -762,19 +775,29 @@ SDCT_DEV void consumer_role(const KParams &p, uint64_t *bars, uint32_t tmem_base
         SDCT_TC_CHUNK(2, hiA, loA, hiB, loB, false)
         SDCT_TC_CHUNK(3, hiB, loB, hiA, loA, false)
 #undef SDCT_TC_CHUNK
-        if (LAYOUT != SDCT_K_LAYOUT_A) {
+        if (CS) {
+            // the store of this warpgroup's tile before last has read the other image (it is written next)
+            if (L == 0) tma_store_wait_read();
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic stores -> the copy engine's reads
+            named_barrier(1 + c);
+            stamp(tr, 2, k, 3);
+            if (L == 0)
+                tma_store_box(p.tc_coef_map, img, (int32_t)n_first, 0, (int32_t)cur.comp,
+                              (int32_t)((CF == 1 && COMPS != 1) ? wk.fc / COMPS : wk.fc));
+        } else if (LAYOUT != SDCT_K_LAYOUT_A) {
             named_barrier(1 + c);
             stamp(tr, 2, k, 3);
             flush_image<LAYOUT>(p, cur, n_first, img, L);
         }
         stamp(tr, 2, k, 4);
     }
+    if (CS && L == 0) tma_store_wait_read();   // the images must outlive the copy engine's reads
 }
 
-template <int LAYOUT, int COMPS, int VEC>
+template <int LAYOUT, int COMPS, int VEC, bool CS>
 __global__ void __launch_bounds__(THREADS, 1) forward_tc_kernel(const __grid_constant__ KParams p)
 {
-    extern __shared__ __align__(128) uint8_t smem[];
+    extern __shared__ __align__(1024) uint8_t smem[];
     constexpr int CF = (COMPS == 3 && VEC == VEC_RGB) ? 3 : 1;
     const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     uint64_t *bars = reinterpret_cast<uint64_t *>(smem + SMEM_BAR_OFF);
@@ -816,7 +839,7 @@ __global__ void __launch_bounds__(THREADS, 1) forward_tc_kernel(const __grid_con
     } else if (warp < MMA_WARP) {
         if (MOVE_REGS) asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(CONSUMER_REGS));
         const uint32_t c = (warp - CONSUMER_WARP) >> 2;
-        consumer_role<LAYOUT, COMPS, CF>(p, bars, tmem_base, smem + SMEM_IMG_OFF + c * 2 * IMG_BYTES, c, threadIdx.x & 127, lane_field);
+        consumer_role<LAYOUT, COMPS, CF, CS>(p, bars, tmem_base, smem + SMEM_IMG_OFF + c * 2 * IMG_BYTES, c, threadIdx.x & 127, lane_field);
     } else {
         if (MOVE_REGS) asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(MMA_REGS));
         if (warp < MMA_WARP + MMA_WARPS && lane == 0)
@@ -848,17 +871,22 @@ template <int LAYOUT> __host__ __device__ constexpr uint32_t inv_lbo() { return 
 template <int LAYOUT> __host__ __device__ constexpr uint32_t inv_sbo() { return 8u * inv_lbo<LAYOUT>(); }
 constexpr int INV_A_STAGE_BYTES = 16 * 8 * 144;           // 18 KiB (layout A's padded form)
 // layouts A and B: a tile's raw bytes are one contiguous piece -> ONE bulk copy (cp.async.bulk) by the TMA thread.
-// Layout C's 64 plane segments of 128 bytes as 64 small bulk copies measured 256 us against 74 us for the producer's
-// own cp.async copies (the copy engine is per-operation bound at that size), so C keeps the latter.
-template <int LAYOUT> __host__ __device__ constexpr bool inv_bulk() { return LAYOUT != SDCT_K_LAYOUT_C; }
+// Layout C's 64 plane segments of 128 bytes: ONE tensor-map box (64 planes x 128 blocks, 128-byte swizzle) when the
+// geometry fits a tensor map (CT), else the producer's own cp.async copies.  (64 small bulk copies measured 256 us
+// against 74 us for cp.async: the copy engine is per-operation bound at that size.)
+template <int LAYOUT, bool CT> __host__ __device__ constexpr bool inv_bulk() { return LAYOUT != SDCT_K_LAYOUT_C || CT; }
 constexpr int INV_RING = 6, INV_RAW_MAX = 64 * 144;       // raw coefficient bytes of a tile (layout C: padded plane rows): at most 9 KiB
 constexpr int SMEM_INV_A_OFF = B_BYTES, SMEM_INV_RING_OFF = SMEM_INV_A_OFF + A_STAGES * INV_A_STAGE_BYTES;
 static_assert(SMEM_INV_RING_OFF + INV_RING * INV_RAW_MAX <= SMEM_BAR_OFF, "inverse shared-memory plan");
 
 // raw ring slot: the tile's coefficient bytes with a row pitch that makes the expansion's 16-byte reads
 // conflict-free (A: 128 block rows of 64 B + 16; C: 64 plane rows of 128 B + 16; B: the 8 KiB image as it is)
-template <int LAYOUT> __host__ __device__ constexpr int inv_raw_pitch() { return LAYOUT == SDCT_K_LAYOUT_C ? 144 : 0; }
-template <int LAYOUT> __host__ __device__ constexpr int inv_raw_bytes() { return LAYOUT == SDCT_K_LAYOUT_C ? 64 * 144 : TILE * 64; }
+// (the tensor-map form of layout C has pitch 128 and the hardware's 128-byte swizzle instead: 16-byte piece j of plane i
+// sits at piece j ^ (i % 8))
+template <int LAYOUT, bool CT> __host__ __device__ constexpr int inv_raw_pitch() { return LAYOUT == SDCT_K_LAYOUT_C ? (CT ? 128 : 144) : 0; }
+template <int LAYOUT, bool CT> __host__ __device__ constexpr int inv_raw_bytes() { return LAYOUT == SDCT_K_LAYOUT_C ? 64 * inv_raw_pitch<LAYOUT, CT>() : TILE * 64; }
+
+
 
 SDCT_DEV void bulk_copy_g2s(void *smem_dst, const void *gmem, uint32_t bytes, uint64_t *bar)
 {
@@ -866,10 +894,10 @@ SDCT_DEV void bulk_copy_g2s(void *smem_dst, const void *gmem, uint32_t bytes, ui
                  ::"r"(smem_u32(smem_dst)), "l"(gmem), "r"(bytes), "r"(smem_u32(bar)) : "memory");
 }
 
-// the TMA warp lands each tile's raw coefficient bytes in the ring: lane 0 announces the byte count, then layouts A, B:
-// one copy of count * 64 contiguous bytes; layout C: lane l copies the tile's segments of planes l and l + 32
+// the TMA thread lands each tile's raw coefficient bytes in the ring: layouts A, B: one copy of count * 64 contiguous
+// bytes; layout C: one box of the coefficient tensor (blocks past the end of a plane read as zero and are never stored)
 template <int LAYOUT>
-SDCT_DEV void inv_bulk_role(const KParams &p, uint64_t *bars, uint8_t *ring, uint32_t lane)
+SDCT_DEV void inv_bulk_role(const KParams &p, uint64_t *bars, uint8_t *ring)
 {
     TileWalk w;
     w.init(p, 0, 1);
@@ -878,30 +906,27 @@ SDCT_DEV void inv_bulk_role(const KParams &p, uint64_t *bars, uint8_t *ring, uin
         const Tile t = tile_at<1, TILE>(p, w);
         const uint64_t n_first = (uint64_t)p.row0 * p.bpr + t.n0;
         uint64_t *full = bars + BAR_RING_FULL + rs;
-        uint8_t *slot = ring + rs * inv_raw_bytes<LAYOUT>();
-        if (lane == 0) {
-            mbar_wait(bars + BAR_RING_EMPTY + rs, (ru & 1) ^ 1);
-            mbar_expect_tx(full, t.count * 64u);
-            if (LAYOUT != SDCT_K_LAYOUT_C) bulk_copy_g2s(slot, t.coef + n_first * 64, t.count * 64u, full);
-        }
+        uint8_t *slot = ring + rs * (TILE * 64);
+        mbar_wait(bars + BAR_RING_EMPTY + rs, (ru & 1) ^ 1);
         if (LAYOUT == SDCT_K_LAYOUT_C) {
-            __syncwarp();   // the slot is free and the byte count registered before any lane's copy can complete
-#pragma unroll
-            for (uint32_t i = lane; i < 64; i += 32)
-                bulk_copy_g2s(slot + i * inv_raw_pitch<LAYOUT>(), t.coef + (uint64_t)i * p.coef_plane_stride + n_first, t.count, full);
+            mbar_expect_tx(full, TILE * 64u);
+            tma_load_box(slot, p.tc_coef_map, full, (int32_t)n_first, 0, 0, (int32_t)w.fc);
+        } else {
+            mbar_expect_tx(full, t.count * 64u);
+            bulk_copy_g2s(slot, t.coef + n_first * 64, t.count * 64u, full);
         }
     }
 }
 
-template <int LAYOUT>
+template <int LAYOUT, bool CT>
 SDCT_DEV void inv_producer_role(const KParams &p, uint64_t *bars, uint8_t *a_stages, uint8_t *ring, uint32_t L)
 {
     // Two piece-to-thread mappings.  COPY: piece c = L + 128 m in global order (coalesced cp.async).  EXPAND: the
     // piece whose two expanded 16-byte halves this thread stores, chosen so that a quarter-warp's stores fall on
     // 32 distinct banks.  Layout B expands the pieces it copied (no barrier); A and C read pieces other threads
     // copied (one warpgroup barrier per tile, which also frees the slot read before).
-    constexpr bool OWN = LAYOUT == SDCT_K_LAYOUT_B, BULK = inv_bulk<LAYOUT>();
-    constexpr int RAW = inv_raw_bytes<LAYOUT>(), PITCH = inv_raw_pitch<LAYOUT>();
+    constexpr bool OWN = LAYOUT == SDCT_K_LAYOUT_B, BULK = inv_bulk<LAYOUT, CT>();
+    constexpr int RAW = inv_raw_bytes<LAYOUT, CT>(), PITCH = inv_raw_pitch<LAYOUT, CT>();
     constexpr uint32_t INV_A_LBO = inv_lbo<LAYOUT>(), INV_A_SBO = inv_sbo<LAYOUT>();
     uint32_t copy_dst[4], rd_off[4], dst_off[4];
 #pragma unroll
@@ -910,7 +935,7 @@ SDCT_DEV void inv_producer_role(const KParams &p, uint64_t *bars, uint8_t *a_sta
         if (LAYOUT == SDCT_K_LAYOUT_C) {
             copy_dst[m] = (c >> 3) * PITCH + 16u * (c & 7);          // plane c / 8, blocks 16 (c % 8) ..
             const uint32_t i = c & 63, jj = c >> 6;                   // expand: plane i, blocks 16 jj .. 16 jj + 15
-            rd_off[m] = i * PITCH + 16u * jj;
+            rd_off[m] = i * PITCH + 16u * (CT ? jj ^ (i & 7u) : jj);
             dst_off[m] = (2u * jj) * INV_A_SBO + i * 16u;             // second half: the next 8 blocks, + SBO
         } else if (LAYOUT == SDCT_K_LAYOUT_B) {
             copy_dst[m] = 16u * c;                                    // group c / 32, coefficients 2 (c % 32), + 1: 8 blocks each
@@ -1108,10 +1133,11 @@ SDCT_DEV void inv_consumer_role(const KParams &p, uint64_t *bars, uint32_t tmem_
     }
 }
 
-template <int LAYOUT>
+template <int LAYOUT, bool CT>
 __global__ void __launch_bounds__(THREADS, 1) inverse_tc_kernel(const __grid_constant__ KParams p)
 {
-    extern __shared__ __align__(128) uint8_t smem[];
+    extern __shared__ __align__(1024) uint8_t smem[];   // the swizzled ring slots of layout C need 1024-byte alignment
+    static_assert(SMEM_INV_RING_OFF % 1024 == 0, "ring slot alignment");
     const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     uint64_t *bars = reinterpret_cast<uint64_t *>(smem + SMEM_BAR_OFF);
     uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(smem + SMEM_BAR_OFF + NUM_BARS * 8);
@@ -1144,14 +1170,14 @@ __global__ void __launch_bounds__(THREADS, 1) inverse_tc_kernel(const __grid_con
     const uint32_t lane_field = ((warp & 3u) * 32u) << 16;
     static_assert(PRODUCER_WGS == 1 && INV_RING <= TMA_RING, "the inverse kernel has one producer warpgroup and reuses the ring barriers");
     if (warp < CONSUMER_WARP) {
-        inv_producer_role<LAYOUT>(p, bars, smem + SMEM_INV_A_OFF, smem + SMEM_INV_RING_OFF, threadIdx.x);
+        inv_producer_role<LAYOUT, CT>(p, bars, smem + SMEM_INV_A_OFF, smem + SMEM_INV_RING_OFF, threadIdx.x);
     } else if (warp < MMA_WARP) {
         const uint32_t c = (warp - CONSUMER_WARP) >> 2;
         inv_consumer_role<LAYOUT>(p, bars, tmem_base, c, threadIdx.x & 127, lane_field);
     } else if (warp < MMA_WARP + MMA_WARPS && lane == 0) {
         inv_mma_role<LAYOUT>(p, bars, tmem_base, smem_u32(smem + SMEM_INV_A_OFF), b_descriptor(smem_u32(smem + SMEM_B_OFF)), warp - MMA_WARP);
-    } else if (inv_bulk<LAYOUT>() && warp == TMA_WARP && (lane == 0 || LAYOUT == SDCT_K_LAYOUT_C)) {
-        inv_bulk_role<LAYOUT>(p, bars, smem + SMEM_INV_RING_OFF, lane);
+    } else if (inv_bulk<LAYOUT, CT>() && warp == TMA_WARP && lane == 0) {
+        inv_bulk_role<LAYOUT>(p, bars, smem + SMEM_INV_RING_OFF);
     }
     fence_before();
     __syncthreads();
@@ -1165,20 +1191,26 @@ using namespace sdct;
 // The pixels as a 4-D tensor of u32 [frame][eye][pixel row][W / 4] for the TMA path; box = 256 x 8 x 1 x 1 =
 // the 8 rows x 1024 bytes of 128 consecutive blocks of one block row.  Returns false when the geometry does
 // not fit a tensor map (the cp.async path is used instead).
-static bool make_pixel_tensor_map(KParams &p)
+typedef CUresult (*TensorMapEncodeFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *,
+                                      const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                      CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static TensorMapEncodeFn tensor_map_encoder()
 {
-    typedef CUresult (*EncodeFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *,
-                                 const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle,
-                                 CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
-    static EncodeFn encode = nullptr;
+    static TensorMapEncodeFn encode = nullptr;
     static bool looked = false;
     if (!looked) {
         looked = true;
         void *fn = nullptr;
         cudaDriverEntryPointQueryResult q;
         if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &q) == cudaSuccess && q == cudaDriverEntryPointSuccess)
-            encode = reinterpret_cast<EncodeFn>(fn);
+            encode = reinterpret_cast<TensorMapEncodeFn>(fn);
     }
+    return encode;
+}
+
+static bool make_pixel_tensor_map(KParams &p)
+{
+    TensorMapEncodeFn encode = tensor_map_encoder();
     if (!encode || tc::PRODUCER_WGS != 1 || getenv("SDCT_TC_NO_TMA")) return false;
     if (p.comps != 1 || p.pixel_vec < 2 || p.bpr < (uint32_t)tc::TILE || (p.eyes != 1 && p.eyes != 2)) return false;
     const uint64_t band_rows = ((uint64_t)p.row0 + p.rows + p.eyes - 1) / p.eyes * 8;   // pixel rows of one eye that the window reaches
@@ -1198,18 +1230,18 @@ static bool make_pixel_tensor_map(KParams &p)
     return true;
 }
 
-template <int LAYOUT>
+template <int LAYOUT, bool CS>
 static cudaError_t launch_tc(const KParams &p, unsigned grid, bool tma, bool rgb_fused, cudaStream_t s)
 {
 #define SDCT_TC_GO(C, V)                                                                                             \
     do {                                                                                                             \
         static bool attr_done = false;                                                                               \
         if (!attr_done) {                                                                                            \
-            cudaError_t e = cudaFuncSetAttribute(tc::forward_tc_kernel<LAYOUT, C, V>, cudaFuncAttributeMaxDynamicSharedMemorySize, tc::SMEM_BYTES); \
+            cudaError_t e = cudaFuncSetAttribute(tc::forward_tc_kernel<LAYOUT, C, V, CS>, cudaFuncAttributeMaxDynamicSharedMemorySize, tc::SMEM_BYTES); \
             if (e != cudaSuccess) return e;                                                                          \
             attr_done = true;                                                                                        \
         }                                                                                                            \
-        tc::forward_tc_kernel<LAYOUT, C, V><<<grid, tc::THREADS, tc::SMEM_BYTES, s>>>(p);                            \
+        tc::forward_tc_kernel<LAYOUT, C, V, CS><<<grid, tc::THREADS, tc::SMEM_BYTES, s>>>(p);                        \
         return cudaGetLastError();                                                                                   \
     } while (0)
     if (p.comps == 1) {
@@ -1228,17 +1260,42 @@ extern "C" int sdct_k_tc_trace(unsigned long long *host)
     return (int)cudaMemcpyFromSymbol(host, tc::g_trace, sizeof(tc::g_trace));
 }
 
-template <int LAYOUT>
+template <int LAYOUT, bool CT>
 static cudaError_t launch_tc_inverse(const KParams &p, unsigned grid, cudaStream_t s)
 {
     static bool attr_done = false;
     if (!attr_done) {
-        cudaError_t e = cudaFuncSetAttribute(tc::inverse_tc_kernel<LAYOUT>, cudaFuncAttributeMaxDynamicSharedMemorySize, tc::SMEM_BYTES);
+        cudaError_t e = cudaFuncSetAttribute(tc::inverse_tc_kernel<LAYOUT, CT>, cudaFuncAttributeMaxDynamicSharedMemorySize, tc::SMEM_BYTES);
         if (e != cudaSuccess) return e;
         attr_done = true;
     }
-    tc::inverse_tc_kernel<LAYOUT><<<grid, tc::THREADS, tc::SMEM_BYTES, s>>>(p);
+    tc::inverse_tc_kernel<LAYOUT, CT><<<grid, tc::THREADS, tc::SMEM_BYTES, s>>>(p);
     return cudaGetLastError();
+}
+
+// Layout C's coefficients as a 4-D u8 tensor [frame][component][plane 0..63][block]; box = 128 blocks x 64 planes with
+// the 128-byte swizzle (inverse: tile loads; forward: tile stores).  Returns false when the geometry does not fit a
+// tensor map (the thread-copy paths are used instead).
+static bool make_coef_tensor_map(KParams &p)
+{
+    TensorMapEncodeFn encode = tensor_map_encoder();
+    if (!encode || getenv("SDCT_TC_NO_TMA")) return false;
+    const uint64_t plane_len = ((uint64_t)p.row0 + p.rows) * p.bpr;   // blocks of a plane that the window reaches
+    const uint64_t cstride = p.comps > 1 ? p.coef_comp_stride : p.coef_plane_stride * 64;
+    const uint64_t fstride = p.frames > 1 ? p.coef_frame_stride : cstride * p.comps;
+    if (plane_len == 0 || plane_len >= (1ull << 31) || p.frames >= (1u << 31) || ((uintptr_t)p.coefs & 15)) return false;
+    const cuuint64_t dims[4] = {plane_len, 64, p.comps, p.frames};
+    const cuuint64_t strides[3] = {p.coef_plane_stride, cstride, fstride};
+    for (int i = 0; i < 3; i++)
+        if (strides[i] == 0 || (strides[i] & 15) || strides[i] >= (1ull << 40)) return false;
+    const cuuint32_t box[4] = {128, 64, 1, 1}, estr[4] = {1, 1, 1, 1};
+    CUtensorMap map;
+    if (encode(&map, CU_TENSOR_MAP_DATA_TYPE_UINT8, 4, const_cast<uint8_t *>(p.coefs), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+               CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
+        return false;
+    static_assert(sizeof(map) == sizeof(p.tc_coef_map), "CUtensorMap size");
+    memcpy(p.tc_coef_map, &map, sizeof(map));
+    return true;
 }
 
 extern "C" cudaError_t sdct_k_launch_tc(int op, int layout, const KParams *pp, cudaStream_t s)
@@ -1261,9 +1318,11 @@ extern "C" cudaError_t sdct_k_launch_tc(int op, int layout, const KParams *pp, c
         const unsigned sms_i = p.sm_count ? p.sm_count : 148u;
         const unsigned grid_i = (unsigned)(tiles < sms_i ? tiles : sms_i);
         switch (layout) {
-        case SDCT_K_LAYOUT_A: return launch_tc_inverse<SDCT_K_LAYOUT_A>(p, grid_i, s);
-        case SDCT_K_LAYOUT_B: return launch_tc_inverse<SDCT_K_LAYOUT_B>(p, grid_i, s);
-        case SDCT_K_LAYOUT_C: return launch_tc_inverse<SDCT_K_LAYOUT_C>(p, grid_i, s);
+        case SDCT_K_LAYOUT_A: return launch_tc_inverse<SDCT_K_LAYOUT_A, false>(p, grid_i, s);
+        case SDCT_K_LAYOUT_B: return launch_tc_inverse<SDCT_K_LAYOUT_B, false>(p, grid_i, s);
+        case SDCT_K_LAYOUT_C:
+            if (make_coef_tensor_map(p)) return launch_tc_inverse<SDCT_K_LAYOUT_C, true>(p, grid_i, s);
+            return launch_tc_inverse<SDCT_K_LAYOUT_C, false>(p, grid_i, s);
         default: return cudaErrorInvalidValue;
         }
     }
@@ -1279,12 +1338,17 @@ extern "C" cudaError_t sdct_k_launch_tc(int op, int layout, const KParams *pp, c
                            !(((unsigned long long)p.rows * p.bpr) & 1) && !getenv("SDCT_TC_NO_RGB_FUSE");
     if (rgb_fused) p.tiles = (uint32_t)(tiles / 3);
     const unsigned grid = (unsigned)(p.tiles < sms ? p.tiles : sms);
-    // measured: the TMA pixel path wins for layouts A and B; layout C (staging image + flush) is faster on the cp.async ring
-    const bool tma = layout != SDCT_K_LAYOUT_C && make_pixel_tensor_map(p);
+    // layout C: one tensor-map store per tile when the coefficient planes fit a tensor map.  Measured (64 x 1080p):
+    // thread flush + cp.async pixel ring 59.7 us, tensor-map store alone 59.7, tensor-map store + TMA pixel path 54.6
+    // (the TMA pixel path WITHOUT the store was slower than the cp.async ring), so the two go together.
+    const bool c_store = layout == SDCT_K_LAYOUT_C && !getenv("SDCT_TC_NO_TMA_STORE") && make_coef_tensor_map(p);
+    const bool tma = (layout != SDCT_K_LAYOUT_C || c_store) && make_pixel_tensor_map(p);
     switch (layout) {
-    case SDCT_K_LAYOUT_A: return launch_tc<SDCT_K_LAYOUT_A>(p, grid, tma, rgb_fused, s);
-    case SDCT_K_LAYOUT_B: return launch_tc<SDCT_K_LAYOUT_B>(p, grid, tma, rgb_fused, s);
-    case SDCT_K_LAYOUT_C: return launch_tc<SDCT_K_LAYOUT_C>(p, grid, tma, rgb_fused, s);
+    case SDCT_K_LAYOUT_A: return launch_tc<SDCT_K_LAYOUT_A, false>(p, grid, tma, rgb_fused, s);
+    case SDCT_K_LAYOUT_B: return launch_tc<SDCT_K_LAYOUT_B, false>(p, grid, tma, rgb_fused, s);
+    case SDCT_K_LAYOUT_C:
+        if (c_store) return launch_tc<SDCT_K_LAYOUT_C, true>(p, grid, tma, rgb_fused, s);
+        return launch_tc<SDCT_K_LAYOUT_C, false>(p, grid, tma, rgb_fused, s);
     default: return cudaErrorInvalidValue;
     }
 }

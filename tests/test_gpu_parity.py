@@ -467,10 +467,10 @@ def test_tensor_core_forward_is_bit_exact_to_its_cpu_restatement(ctx, oracle, la
 
 
 @pytest.mark.parametrize("layout", LAYOUTS)
-def test_tensor_core_wide_images_tma_pixel_path(ctx, oracle, layout):
-    """Images at least 128 blocks wide with 16-byte-aligned rows take the TMA pixel path of sdct_tc.cu (layouts
-    A, B; bulk tensor copies of 8 rows x 1024 bytes, a second box where a tile runs on into the next block
-    row) and, for layout B, the direct byte-pair stores: batch of frames with a ragged tail tile, band
+def test_tensor_core_wide_images_tma_pixel_path(ctx, oracle, layout, monkeypatch):
+    """Images at least 128 blocks wide with 16-byte-aligned rows take the TMA pixel path of sdct_tc.cu (bulk
+    tensor copies of 8 rows x 1024 bytes, a second box where a tile runs on into the next block row); layout B
+    the direct byte-pair stores, layout C one tensor-map store per tile (clipped at the window's end): batch of frames with a ragged tail tile, band
     window whose first block is not a multiple of 8, padded pitch, two eyes."""
     f, h, w = 3, 40, 1088            # 136 blocks per row (layout B needs width % 64 == 0): every tile straddles block rows; 680 = 5 * 128 + 40 blocks per frame
     imgs = np.stack([make_image("rand", h, w, seed=40 + s) for s in range(f)])
@@ -478,6 +478,12 @@ def test_tensor_core_wide_images_tma_pixel_path(ctx, oracle, layout):
     job = sd.dense_job(layout, w, h, frames=f, flags=sd.TENSOR)
     got = ctx.forward(dev(imgs), lut, job).cpu().numpy().reshape(f, -1)
     want = [oracle.forward(layout, imgs[k], lut, mode=ol.MODE_TENSOR) for k in range(f)]
+    for k in range(f):
+        assert np.array_equal(got[k], want[k]), (k, np.count_nonzero(got[k] != want[k]))
+    # the same through the thread-copy paths (what a geometry that fits no tensor map gets)
+    monkeypatch.setenv("SDCT_TC_NO_TMA", "1")
+    got = ctx.forward(dev(imgs), lut, job).cpu().numpy().reshape(f, -1)
+    monkeypatch.delenv("SDCT_TC_NO_TMA")
     for k in range(f):
         assert np.array_equal(got[k], want[k]), (k, np.count_nonzero(got[k] != want[k]))
     # band window: bands 1..3 of frame 0 only, the rest of the output untouched
@@ -549,7 +555,7 @@ def test_tensor_core_fused_rgb_components(ctx, oracle, layout):
 
 
 @pytest.mark.parametrize("layout", LAYOUTS)
-def test_tensor_core_inverse_is_bit_exact_to_its_cpu_restatement(ctx, oracle, layout):
+def test_tensor_core_inverse_is_bit_exact_to_its_cpu_restatement(ctx, oracle, layout, monkeypatch):
     """SDCT_TENSOR inverse (sdct_tc.cu, inverse_tc_kernel): dequantiser folded into an exact-integer matrix,
     A operand in shared memory (K-major for layout A, MN-major for B and C).  Byte-identical to
     oracle.inverse(tensor=True); within one level of the fp32 inverse; unsupported geometries are refused."""
@@ -572,6 +578,12 @@ def test_tensor_core_inverse_is_bit_exact_to_its_cpu_restatement(ctx, oracle, la
     coefs = np.stack([oracle.forward(layout, imgs[k], lut) for k in range(f)])
     job = sd.dense_job(layout, w, h, frames=f, flags=sd.TENSOR)
     got = ctx.inverse(dev(coefs), lut, job).cpu().numpy().reshape(f, h, w)
+    for k in range(f):
+        assert np.array_equal(got[k], oracle.inverse(layout, coefs[k], w, h, lut, tensor=True))
+    # the same with the tensor-map / bulk-copy paths switched off (the fallback for geometries no tensor map describes)
+    monkeypatch.setenv("SDCT_TC_NO_TMA", "1")
+    got = ctx.inverse(dev(coefs), lut, job).cpu().numpy().reshape(f, h, w)
+    monkeypatch.delenv("SDCT_TC_NO_TMA")
     for k in range(f):
         assert np.array_equal(got[k], oracle.inverse(layout, coefs[k], w, h, lut, tensor=True))
     # interleaved RGB has no tensor-core inverse: refused, not silently replaced by the fp32 arithmetic
