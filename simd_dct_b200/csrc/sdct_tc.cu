@@ -270,6 +270,14 @@ SDCT_DEV void tmem_wait_ld(float (&a)[16], float (&b)[16])
                  : "memory");
 }
 
+SDCT_DEV void tmem_wait_ld4(float (&a)[16], float (&b)[16], float (&c)[16], float (&d)[16])
+{
+#define SDCT_R16(x) "+f"(x[0]), "+f"(x[1]), "+f"(x[2]), "+f"(x[3]), "+f"(x[4]), "+f"(x[5]), "+f"(x[6]), "+f"(x[7]), "+f"(x[8]), "+f"(x[9]), \
+                    "+f"(x[10]), "+f"(x[11]), "+f"(x[12]), "+f"(x[13]), "+f"(x[14]), "+f"(x[15])
+    asm volatile("tcgen05.wait::ld.sync.aligned;" : SDCT_R16(a), SDCT_R16(b), SDCT_R16(c), SDCT_R16(d) : : "memory");
+#undef SDCT_R16
+}
+
 // ---- block <-> thread mapping -----------------------------------------------------------------------
 // TMEM lane L (= thread index inside the warpgroup) holds block slot(L) of the tile, chosen so that
 // the two lanes one 16x256b load hands to a thread (g, g + 8) are adjacent blocks.
@@ -979,6 +987,8 @@ SDCT_DEV void inv_producer_role(const KParams &p, uint64_t *bars, uint8_t *a_sta
     uint32_t tile = blockIdx.x;
     for (uint32_t k = 0;; k++, tile += gridDim.x) {
         if (tile >= p.tiles) return;
+        const bool tr = (ablate_bits(p) & 32) && blockIdx.x == 0 && L == 0;
+        stamp(tr, 0, k, 0);
         if (BULK) {
             mbar_wait(bars + BAR_RING_FULL + k % INV_RING, (k / INV_RING) & 1);   // the TMA thread's bulk copy has landed
         } else {
@@ -993,7 +1003,9 @@ SDCT_DEV void inv_producer_role(const KParams &p, uint64_t *bars, uint8_t *a_sta
         uint4 raw[4];
 #pragma unroll
         for (int m = 0; m < 4; m++) raw[m] = *reinterpret_cast<const uint4 *>(slot + rd_off[m]);
+        stamp(tr, 0, k, 1);
         mbar_wait(bars + BAR_A_EMPTY + sa, (ua & 1) ^ 1);   // the MMAs of tile k - 4 have read this A stage
+        stamp(tr, 0, k, 2);
         uint8_t *a = a_stages + sa * INV_A_STAGE_BYTES;
 #pragma unroll
         for (int m = 0; m < 4; m++) {
@@ -1017,6 +1029,7 @@ SDCT_DEV void inv_producer_role(const KParams &p, uint64_t *bars, uint8_t *a_sta
         }
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic stores -> the tensor core's async-proxy reads
         mbar_arrive(bars + BAR_A_FULL + sa);
+        stamp(tr, 0, k, 3);
         if (BULK) {
             __syncwarp();
             if ((L & 31) == 0) mbar_arrive(bars + BAR_RING_EMPTY + k % INV_RING);   // this warp has read the slot
@@ -1035,10 +1048,14 @@ SDCT_DEV void inv_mma_role(const KParams &p, uint64_t *bars, uint32_t tmem_base,
     for (uint32_t k = m;; k += MMA_WARPS) {
         if (blockIdx.x + k * gridDim.x >= p.tiles) break;
         const uint32_t sa = k % A_STAGES, ua = k / A_STAGES, sd = k % D_STAGES;
+        const bool tr = (ablate_bits(p) & 32) && blockIdx.x == 0;
+        stamp(tr, 1, k, 0);
         mbar_wait(bars + BAR_A_FULL + sa, ua & 1);
+        stamp(tr, 1, k, 1);
         if (k >= D_STAGES)
             mbar_wait(bars + BAR_D_EMPTY + ((k + 1) & 1) * D_STAGES + sd, ((k - D_STAGES) / (2 * D_STAGES)) & 1);
         fence_after();
+        stamp(tr, 1, k, 2);
         constexpr uint32_t INV_A_LBO = inv_lbo<LAYOUT>(), INV_A_SBO = inv_sbo<LAYOUT>();
         const uint64_t ad = smem_descriptor(a_stages_addr + sa * INV_A_STAGE_BYTES, INV_A_LBO, INV_A_SBO);
         const uint32_t tD = tmem_base + TMEM_D_OFF + sd * D_COLS;
@@ -1047,9 +1064,9 @@ SDCT_DEV void inv_mma_role(const KParams &p, uint64_t *bars, uint32_t tmem_base,
             if (!(ablate_bits(p) & 1)) mma_f16_ss(tD, ad + (uint64_t)((2 * ks * INV_A_LBO) >> 4), bd[ks], idesc, ks);
         mma_commit(bars + BAR_A_EMPTY + sa);
         mma_commit(bars + BAR_D_FULL + (k & 1) * D_STAGES + sd);
+        stamp(tr, 1, k, 3);
     }
 }
-
 
 template <int LAYOUT>
 SDCT_DEV void inv_consumer_role(const KParams &p, uint64_t *bars, uint32_t tmem_base, uint32_t c, uint32_t L, uint32_t lane_field)
@@ -1063,50 +1080,77 @@ SDCT_DEV void inv_consumer_role(const KParams &p, uint64_t *bars, uint32_t tmem_
     // TMEM lane = block of the tile (the A rows are in natural order here): a 16x256b load hands this thread lanes
     // g and g + 8 of a 16-lane half, i.e. blocks P = sp0 + 16 half and Q = P + 8
     const uint32_t sp0 = (L >> 5) * 32u + g;
+    // where a tile's pixels go: pixel row 2q of this thread's four blocks (slots sp0, +8, +16, +24).  One division
+    // for the first; the others step 8 blocks (64 bytes) along the block row and wrap into the next one - at most
+    // once per step when a row has at least 8 blocks, which is the branch-free path (a wrap adds a precomputed
+    // byte step: mono 8 pitch - 8 bpr; two eyes: eye_stride - 8 bpr from the even row, 8 pitch - eye_stride - 8 bpr
+    // from the odd one).  32 x 32 -> 64-bit address products (pitch < 2^32).
+    struct Dst { uint8_t *px[2][2]; uint32_t count; };   // [half][P, Q]
+    const uint32_t pitch32 = (uint32_t)p.pitch;
+    const bool stereo = p.eyes == 2, wide = p.bpr >= 8;
+    const int64_t row_bytes = (int64_t)p.bpr * 8;
+    const int64_t wrap_even = (stereo ? (int64_t)p.eye_stride : (int64_t)p.pitch * 8) - row_bytes;
+    const int64_t wrap_odd = (stereo ? (int64_t)p.pitch * 8 - (int64_t)p.eye_stride : (int64_t)p.pitch * 8) - row_bytes;
+    const uint64_t q_rows = (uint64_t)(2 * q) * pitch32;
+    auto locate_tile = [&](const TileWalk &w, Dst &d) {
+        const Tile t = tile_at<1, TILE>(p, w);
+        d.count = t.count;
+        const uint32_t nl = t.n0 + (sp0 < t.count ? sp0 : 0u);
+        uint32_t r = fastdiv(nl, p.div_bpr), bx = nl - r * p.bpr;
+        if (wide) {
+            uint32_t row = r + p.row0;
+            uint8_t *b = const_cast<uint8_t *>(t.pix) + q_rows + ((uint64_t)((stereo ? row >> 1 : row) * 8) * pitch32 + bx * 8);
+            if (stereo && (row & 1)) b += p.eye_stride;
+#pragma unroll
+            for (int i = 0; i < 4; i++) {
+                d.px[i >> 1][i & 1] = b;
+                bx += 8;
+                b += 64;
+                if (bx >= p.bpr) { bx -= p.bpr; b += (row & 1) ? wrap_odd : wrap_even; row++; }
+            }
+            return;
+        }
+#pragma unroll
+        for (int i = 0; i < 4; i++) {
+            const uint32_t row = r + p.row0, band = stereo ? row >> 1 : row;
+            uint8_t *b = const_cast<uint8_t *>(t.pix) + ((uint64_t)(band * 8 + 2 * q) * pitch32 + bx * 8);
+            if (stereo && (row & 1)) b += p.eye_stride;
+            d.px[i >> 1][i & 1] = b;
+            bx += 8;
+            while (bx >= p.bpr) { bx -= p.bpr; r++; }   // (a slot past the tile's end may point past the window: never stored)
+        }
+    };
     TileWalk wk;
     wk.init(p, c, CONSUMER_WGS);
-    for (uint32_t k = c;; k += CONSUMER_WGS, wk.next(p)) {
+    Dst cur;
+    if (wk.tile < p.tiles) locate_tile(wk, cur);
+    for (uint32_t k = c;; k += CONSUMER_WGS) {
         if (wk.tile >= p.tiles) break;
         const uint32_t sd = k % D_STAGES, ud = k / (2 * D_STAGES);
         uint64_t *d_full = bars + BAR_D_FULL + c * D_STAGES + sd, *d_empty = bars + BAR_D_EMPTY + c * D_STAGES + sd;
-        const Tile cur = tile_at<1, TILE>(p, wk);
-        // pixel row 2q of this thread's four blocks (slots sp0, +8, +16, +24): one division for the first, the others
-        // step 8 blocks along the block row and wrap; 32 x 32 -> 64-bit address products (pitch < 2^32)
-        uint8_t *px[2][2];   // [half][P, Q]
-        const uint32_t pitch32 = (uint32_t)p.pitch;
         const bool full = cur.count == TILE;
-        {
-            const uint32_t nl = cur.n0 + (sp0 < cur.count ? sp0 : 0u);
-            uint32_t r = fastdiv(nl, p.div_bpr), bx = nl - r * p.bpr;
-#pragma unroll
-            for (int i = 0; i < 4; i++) {
-                const uint32_t row = r + p.row0, band = p.eyes == 2 ? row >> 1 : row;
-                uint8_t *b = const_cast<uint8_t *>(cur.pix) + ((uint64_t)(band * 8 + 2 * q) * pitch32 + bx * 8);
-                if (p.eyes == 2 && (row & 1)) b += p.eye_stride;
-                px[i >> 1][i & 1] = b;
-                bx += 8;
-                while (bx >= p.bpr) { bx -= p.bpr; r++; }   // (a slot past the tile's end may point past the window: never stored)
-            }
-        }
+        const bool tr = (ablate_bits(p) & 32) && blockIdx.x == 0 && L == 0;
+        stamp(tr, 2, k, 0);
         mbar_wait(d_full, ud & 1);
         fence_after();
-        if (ablate_bits(p) & 4) { fence_before(); mbar_arrive(d_empty); continue; }
+        stamp(tr, 2, k, 1);
+        wk.next(p);
+        if (ablate_bits(p) & 4) { fence_before(); mbar_arrive(d_empty); if (wk.tile < p.tiles) locate_tile(wk, cur); continue; }
+        // Four chunks of 32 columns (pixel rows 2q, 2q + 1 of two 16-block halves).  Chunks 0 and 1 are loaded
+        // together; chunk 2 is requested as soon as chunk 0's registers are free, chunk 3 after chunk 1's: two
+        // load waits per tile instead of four, the second hidden behind chunk 1's arithmetic.  The next tile's
+        // addresses are computed while the first loads are in flight.
         float hiA[16], loA[16], hiB[16], loB[16];
         const uint32_t td = tmem_base + TMEM_D_OFF + sd * D_COLS + lane_field;
         tmem_ld_16x256b_x4(td, hiA);
         tmem_ld_16x256b_x4(td + 64, loA);
-#define SDCT_TC_INV_CHUNK(C, HI, LO, NHI, NLO)                                                                        \
+        tmem_ld_16x256b_x4(td + 32, hiB);
+        tmem_ld_16x256b_x4(td + 96, loB);
+        Dst nxt = cur;
+        if (wk.tile < p.tiles) locate_tile(wk, nxt);
+#define SDCT_TC_INV_CHUNK(C, HI, LO)                                                                                  \
         {                                                                                                             \
             constexpr int half = (C) >> 1, kk = (C) & 1;                                                              \
-            tmem_wait_ld(HI, LO);                                                                                     \
-            if ((C) < 3) {                                                                                            \
-                const uint32_t tn = td + ((uint32_t)(16 * (((C) + 1) >> 1)) << 16) + 32 * (((C) + 1) & 1);            \
-                tmem_ld_16x256b_x4(tn, NHI);                                                                          \
-                tmem_ld_16x256b_x4(tn + 64, NLO);                                                                     \
-            } else {                                                                                                  \
-                fence_before();                                                                                       \
-                mbar_arrive(d_empty);                                                                                 \
-            }                                                                                                         \
             F2 bp[4], bq[4];   /* pixels x = 2 k2, 2 k2 + 1 of row 2q + kk, blocks P and Q: bit patterns */           \
             _Pragma("unroll") for (int k2 = 0; k2 < 4; k2++) {                                                        \
                 const F2 tp = fma2(make_float2(HI[4 * k2], HI[4 * k2 + 1]), splat(1024.f), make_float2(LO[4 * k2], LO[4 * k2 + 1]));         \
@@ -1116,8 +1160,8 @@ SDCT_DEV void inv_consumer_role(const KParams &p, uint64_t *bars, uint32_t tmem_
             }                                                                                                         \
             const uint2 vp = make_uint2(pack4_sat(bp[0].x, bp[0].y, bp[1].x, bp[1].y), pack4_sat(bp[2].x, bp[2].y, bp[3].x, bp[3].y)); \
             const uint2 vq = make_uint2(pack4_sat(bq[0].x, bq[0].y, bq[1].x, bq[1].y), pack4_sat(bq[2].x, bq[2].y, bq[3].x, bq[3].y)); \
-            uint2 *dp = reinterpret_cast<uint2 *>(px[half][0] + (kk ? pitch32 : 0u));                                 \
-            uint2 *dq = reinterpret_cast<uint2 *>(px[half][1] + (kk ? pitch32 : 0u));                                 \
+            uint2 *dp = reinterpret_cast<uint2 *>(cur.px[half][0] + (kk ? pitch32 : 0u));                             \
+            uint2 *dq = reinterpret_cast<uint2 *>(cur.px[half][1] + (kk ? pitch32 : 0u));                             \
             if (ablate_bits(p) & 8) { if (vp.x == 0x12345678u && vq.y == 0x9abcdef0u) *dp = vp; }                     \
             else if (full) { *dp = vp; *dq = vq; }                                                                    \
             else {                                                                                                    \
@@ -1125,11 +1169,23 @@ SDCT_DEV void inv_consumer_role(const KParams &p, uint64_t *bars, uint32_t tmem_
                 if (sp0 + 16 * half + 8 < cur.count) *dq = vq;                                                        \
             }                                                                                                         \
         }
-        SDCT_TC_INV_CHUNK(0, hiA, loA, hiB, loB)
-        SDCT_TC_INV_CHUNK(1, hiB, loB, hiA, loA)
-        SDCT_TC_INV_CHUNK(2, hiA, loA, hiB, loB)
-        SDCT_TC_INV_CHUNK(3, hiB, loB, hiA, loA)
+        const uint32_t td2 = td + (16u << 16);   // lanes 16..31 of the warp's quarter: the second half
+        tmem_wait_ld4(hiA, loA, hiB, loB);
+        SDCT_TC_INV_CHUNK(0, hiA, loA)
+        tmem_ld_16x256b_x4(td2, hiA);
+        tmem_ld_16x256b_x4(td2 + 64, loA);
+        SDCT_TC_INV_CHUNK(1, hiB, loB)
+        tmem_ld_16x256b_x4(td2 + 32, hiB);
+        tmem_ld_16x256b_x4(td2 + 96, loB);
+        tmem_wait_ld4(hiA, loA, hiB, loB);
+        fence_before();
+        mbar_arrive(d_empty);   // every load of this thread has landed: hand the D stage back to the MMA warp
+        stamp(tr, 2, k, 2);
+        SDCT_TC_INV_CHUNK(2, hiA, loA)
+        SDCT_TC_INV_CHUNK(3, hiB, loB)
 #undef SDCT_TC_INV_CHUNK
+        stamp(tr, 2, k, 3);
+        cur = nxt;
     }
 }
 

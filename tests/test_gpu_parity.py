@@ -580,6 +580,16 @@ def test_tensor_core_inverse_is_bit_exact_to_its_cpu_restatement(ctx, oracle, la
     got = ctx.inverse(dev(coefs), lut, job).cpu().numpy().reshape(f, h, w)
     for k in range(f):
         assert np.array_equal(got[k], oracle.inverse(layout, coefs[k], w, h, lut, tensor=True))
+    # narrow images (fewer than 8 blocks per row: the generic address walk) and, for layout C, two eyes with a tile
+    # that runs across block rows of both
+    for (h2, w2, eyes) in ((128, 32, 1), (64, 1088, 2)):
+        if (layout == sd.LAYOUT_B and w2 % 64) or (eyes == 2 and layout != sd.LAYOUT_C):
+            continue
+        img = make_image("rand", h2 * eyes, w2, seed=7 + eyes)
+        coef = oracle.forward(layout, img, rt_lut(layout), eyes=eyes)
+        job2 = sd.dense_job(layout, w2, h2, eyes=eyes, flags=sd.TENSOR)
+        got = ctx.inverse(dev(coef), rt_lut(layout), job2).cpu().numpy().reshape(h2 * eyes, w2)
+        assert np.array_equal(got, oracle.inverse(layout, coef, w2, h2, rt_lut(layout), eyes=eyes, tensor=True)), (h2, w2, eyes)
     # the same with the tensor-map / bulk-copy paths switched off (the fallback for geometries no tensor map describes)
     monkeypatch.setenv("SDCT_TC_NO_TMA", "1")
     got = ctx.inverse(dev(coefs), lut, job).cpu().numpy().reshape(f, h, w)
