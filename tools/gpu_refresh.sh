@@ -13,4 +13,6 @@ PY
 timeout 300 python bench.py --impl reference --steps 5 --warmup 3 > gpurun_out/bench_ref.json 2>> gpurun_out/bench.err; echo "ref rc=$?"
 bash tools/gpu_ncu.sh fwd_C_tensor forward_tc_kernel --reps 4 fwd_C_tensor
 bash tools/gpu_ncu.sh inv_C_tensor inverse_tc_kernel --reps 4 inv_C_tensor
+bash tools/gpu_ncu.sh inv_A_tensor inverse_tc_kernel --reps 4 inv_A_tensor
+bash tools/gpu_ncu.sh inv_B_tensor inverse_tc_kernel --reps 4 inv_B_tensor
 timeout 300 python tools/prof_run.py --frames 16 --w 3840 --h 2160 --reps 10 rgb_B_exact rgb_B_fast rgb_B_tensor rgb_A_tensor rgb_C_tensor fwd_B_tensor fwd_A_tensor fwd_C_tensor fwd_B_exact inv_A inv_B inv_C inv_A_tensor inv_B_tensor inv_C_tensor > gpurun_out/time_4k.txt 2>&1; cat gpurun_out/time_4k.txt
