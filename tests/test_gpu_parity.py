@@ -590,7 +590,8 @@ def test_tensor_core_inverse_is_bit_exact_to_its_cpu_restatement(ctx, oracle, la
         job2 = sd.dense_job(layout, w2, h2, eyes=eyes, flags=sd.TENSOR)
         got = ctx.inverse(dev(coef), rt_lut(layout), job2).cpu().numpy().reshape(h2 * eyes, w2)
         assert np.array_equal(got, oracle.inverse(layout, coef, w2, h2, rt_lut(layout), eyes=eyes, tensor=True)), (h2, w2, eyes)
-    # the same with the tensor-map / bulk-copy paths switched off (the fallback for geometries no tensor map describes)
+    # the same with the tensor-map path of layout C switched off (the thread-copy fallback for geometries no tensor
+    # map describes; layouts A and B always use the 1-D bulk copy, which needs no map)
     monkeypatch.setenv("SDCT_TC_NO_TMA", "1")
     got = ctx.inverse(dev(coefs), lut, job).cpu().numpy().reshape(f, h, w)
     monkeypatch.delenv("SDCT_TC_NO_TMA")
