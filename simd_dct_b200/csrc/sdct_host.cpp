@@ -119,20 +119,45 @@ int host_run(sdct_context *ctx, int op, const sdct_job *job, const uint8_t *h_pi
     const uint64_t frame_bytes = band_bytes * (g.band_end - g.band_begin);
     const char *env = getenv("SDCT_HOST_CHUNK_MB");
     const uint64_t target = (env && atoi(env) > 0 ? (uint64_t)atoi(env) : 16) << 20;
+    // The first chunk's upload and the last chunk's download overlap with nothing, so the chunk sizes ramp:
+    // per/8, per/4, per/2, per, ..., per, per/2, per/4, per/8 units (frames or bands) when the job is long enough.
+    auto ramp = [](uint64_t total, uint64_t per) {
+        std::vector<uint64_t> sizes;
+        const uint64_t edge[3] = {std::max<uint64_t>(1, per / 8), std::max<uint64_t>(1, per / 4), std::max<uint64_t>(1, per / 2)};
+        const uint64_t edges = edge[0] + edge[1] + edge[2];
+        if (getenv("SDCT_HOST_NO_RAMP") || total < 2 * edges + per) {
+            for (uint64_t u = 0; u < total; u += per) sizes.push_back(std::min(per, total - u));
+            return sizes;
+        }
+        for (int i = 0; i < 3; i++) sizes.push_back(edge[i]);
+        for (uint64_t left = total - 2 * edges; left > 0;) {
+            const uint64_t n = std::min(per, left);
+            sizes.push_back(n);
+            left -= n;
+        }
+        for (int i = 2; i >= 0; i--) sizes.push_back(edge[i]);
+        return sizes;
+    };
     std::vector<Chunk> chunks;
     if (job->frames > 1 && frame_bytes <= 2 * target) {
         const uint64_t per = std::max<uint64_t>(1, target / std::max<uint64_t>(frame_bytes, 1));
-        for (uint64_t f = 0; f < job->frames; f += per) {
-            Chunk c; c.f0 = f; c.f1 = std::min(job->frames, f + per); c.b0 = g.band_begin; c.b1 = g.band_end;
+        uint64_t f = 0;
+        for (uint64_t n : ramp(job->frames, per)) {
+            Chunk c; c.f0 = f; c.f1 = f + n; c.b0 = g.band_begin; c.b1 = g.band_end;
             chunks.push_back(std::move(c));
+            f += n;
         }
     } else {
-        const uint32_t per = (uint32_t)std::max<uint64_t>(1, target / std::max<uint64_t>(band_bytes, 1));
-        for (uint64_t f = 0; f < job->frames; f++)
-            for (uint32_t b = g.band_begin; b < g.band_end; b += per) {
-                Chunk c; c.f0 = f; c.f1 = f + 1; c.b0 = b; c.b1 = std::min(g.band_end, b + per);
+        const uint64_t per = std::max<uint64_t>(1, target / std::max<uint64_t>(band_bytes, 1));
+        const std::vector<uint64_t> sizes = ramp(g.band_end - g.band_begin, per);
+        for (uint64_t f = 0; f < job->frames; f++) {
+            uint32_t bnd = g.band_begin;
+            for (uint64_t n : sizes) {
+                Chunk c; c.f0 = f; c.f1 = f + 1; c.b0 = bnd; c.b1 = bnd + (uint32_t)n;
                 chunks.push_back(std::move(c));
+                bnd += (uint32_t)n;
             }
+        }
     }
 
     const bool fwd = op == SDCT_K_OP_FORWARD;
