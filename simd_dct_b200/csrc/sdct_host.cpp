@@ -164,16 +164,19 @@ int host_run(sdct_context *ctx, int op, const sdct_job *job, const uint8_t *h_pi
     const uint8_t *h_in = fwd ? h_pixels : h_coefs;
     uint8_t *h_out = fwd ? h_coefs : const_cast<uint8_t *>(h_pixels);
     const bool in_pinned = is_pinned(h_in), out_pinned = is_pinned(h_out);
+    // pipeline depth: chunks in flight ($SDCT_HOST_SLOTS for experiments)
+    const char *senv = getenv("SDCT_HOST_SLOTS");
+    const int depth = senv && atoi(senv) >= 1 && atoi(senv) <= kSlots ? atoi(senv) : 4;
     Pending pending[kSlots];
 
     for (size_t ci = 0; ci < chunks.size(); ci++) {
         Chunk &c = chunks[ci];
         chunk_spans(*job, g, c);
-        Slot &s = ctx->slots[ci % kSlots];
-        Pending &pd = pending[ci % kSlots];
+        Slot &s = ctx->slots[ci % depth];
+        Pending &pd = pending[ci % depth];
         rc = drain(s, pd);
         if (rc) return rc;
-        if (ci >= (size_t)kSlots) CU_TRY(cudaEventSynchronize(s.done));  // slot buffers free again
+        if (ci >= (size_t)depth) CU_TRY(cudaEventSynchronize(s.done));  // slot buffers free again
 
         const uint64_t plo = c.pix.front().off, phi = c.pix.back().off + c.pix.back().len;
         const uint64_t clo = c.coef.front().off, chi = c.coef.back().off + c.coef.back().len;

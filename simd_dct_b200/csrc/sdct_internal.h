@@ -19,7 +19,7 @@ int sdct_fail(int code, const char *fmt, ...);
                         __FILE__, __LINE__);                                                      \
     } while (0)
 
-constexpr int kSlots = 4;  // pipeline depth of the host path
+constexpr int kSlots = 8;  // slots of the host path; the pipeline depth in use is host_depth() <= kSlots
 
 struct Slot {
     cudaStream_t stream = nullptr;
