@@ -130,37 +130,42 @@ class ClockSampler:
 
 
 # ---- CPU reference arm --------------------------------------------------------------------------
-def cpu_reference_runner(w, h):
+def cpu_reference_runner(w, h, layout="B"):
     """returns (kind, isa, fn(frames_u8[F,H,W], lut, out[F,H*W], threads)) timing the reference's own
     CPU implementation of the path (oracle/_ref, the unmodified reference built with its own
-    flags) or, if that did not travel, the oracle port."""
-    import ctypes as C
+    flags) or, if that did not travel, the oracle port.  layout B: the AVX-512VL / AVX2 path
+    (src/simd_dct.cpp:1869 / :2064); layout A: the default dispatch (SSE4.1, :1540); layout C: the SSE4.1
+    stereo path (:896), a frame passed as two eyes of H/2 rows."""
     import oraclelib as ol
     from concurrent.futures import ThreadPoolExecutor
 
+    isa = None
     if ol.have_reference("fast"):
         ref = ol.Reference("fast")
         flags = ol.cpu_flags()
-        isa = "avx512vl" if {"avx512vl", "avx512f"} <= flags else ("avx2" if "avx2" in flags else None)
+        if layout == "B":
+            isa = "avx512vl" if {"avx512vl", "avx512f"} <= flags else ("avx2" if "avx2" in flags else None)
+        else:
+            isa = "sse41" if "sse4_1" in flags else "scalar"
         if isa:
             ref.set_isa(isa)
-            fn = ref.fn["B"]
+            fn = ref.fn[layout]
             kind = "reference"
 
             def one(src, dst, lut):
-                # full H-row plane through the reference: sizeY = 2H (only rows < sizeY/2 are visited)
-                fn(src.ctypes.data_as(ol._u8p), dst.ctypes.data_as(ol._u8p), lut.ctypes.data_as(ol._f32p), w, 2 * h, 0, 2 * h)
-        else:
-            isa = None
-    else:
-        isa = None
+                # layouts A, B: a full H-row plane = sizeY 2H (only rows < sizeY/2 are visited); layout C: sizeY = H
+                sy = h - h % 16 if layout == "C" else 2 * h   # (two eyes of whole bands: sizeY % 16 == 0)
+                fn(src.ctypes.data_as(ol._u8p), dst.ctypes.data_as(ol._u8p), lut.ctypes.data_as(ol._f32p), w, sy, 0, sy)
     if isa is None:
         o = ol.Oracle()
         kind, isa = "port", "scalar-c"
+        lay = {"A": ol.LAYOUT_A, "B": ol.LAYOUT_B, "C": ol.LAYOUT_C}[layout]
+        eyes = 2 if layout == "C" else 1
 
         def one(src, dst, lut):
-            o.lib.sdct_oracle_forward(ol.LAYOUT_B, ol.MODE_EXACT, ol.QUIRK_AVX_X3, src.ctypes.data_as(ol._u8p), w, 1, w, h, 1, 0,
-                                      lut.ctypes.data_as(ol._f32p), dst.ctypes.data_as(ol._u8p), 0)
+            he = (h - h % 16) // 2 if eyes == 2 else h
+            o.lib.sdct_oracle_forward(lay, ol.MODE_EXACT, ol.QUIRK_AVX_X3, src.ctypes.data_as(ol._u8p), w, 1, w, he, eyes,
+                                      he * w, lut.ctypes.data_as(ol._f32p), dst.ctypes.data_as(ol._u8p), eyes * he * w // 64)
 
     def run(frames, lut, out, threads):
         n = frames.shape[0]
@@ -168,6 +173,9 @@ def cpu_reference_runner(w, h):
         def work(t):
             for f in range(t, n, threads):
                 one(frames[f], out[f], lut)
+        if threads == 1:
+            work(0)
+            return
         with ThreadPoolExecutor(threads) as ex:
             list(ex.map(work, range(threads)))
     return kind, isa, run
@@ -180,19 +188,46 @@ def host_threads():
         return os.cpu_count() or 1
 
 
-def time_cpu(w, h, frames_np, lut, reps):
-    kind, isa, run = cpu_reference_runner(w, h)
-    threads = host_threads()
-    out = np.empty((frames_np.shape[0], h * w), dtype=np.uint8)
+def time_cpu(w, h, frames_np, lut, reps, layout="B", threads=None, budget_s=8.0):
+    """best of `reps` passes over `frames_np` (bounded by budget_s) -> blocks/s"""
+    kind, isa, run = cpu_reference_runner(w, h, layout)
+    threads = threads or host_threads()
+    out = np.empty((frames_np.shape[0], h * w + 4096), dtype=np.uint8)   # + slack: the SSE layout-A stores overrun (SURVEY A.5)
     run(frames_np, lut, out, threads)  # warm
     best = float("inf")
+    t_start = time.perf_counter()
+    done = 0
     for _ in range(reps):
         t0 = time.perf_counter()
         run(frames_np, lut, out, threads)
         best = min(best, time.perf_counter() - t0)
-    blocks = frames_np.shape[0] * (h // 8) * (w // 8)
-    return {"value": blocks / best, "unit": UNIT, "cores": threads, "kind": kind,
-            "sample": f"{frames_np.shape[0]} frames {w}x{h}, layout B, {isa}, best of {reps}, {threads} threads"}, out
+        done += 1
+        if time.perf_counter() - t_start > budget_s:
+            break
+    hh = h - h % 16 if layout == "C" else h
+    blocks = frames_np.shape[0] * (hh // 8) * (w // 8)
+    return {"value": blocks / best, "unit": UNIT, "cores": threads, "kind": kind, "gbps": blocks / best * BYTES_PER_BLOCK / 1e9,
+            "sample": f"{frames_np.shape[0]} frames {w}x{h}, layout {layout}, {isa}, best of {done}, {threads} thread(s)"}, out[:, :h * w]
+
+
+def strict_reference_bytes(frames_np, lut, w, h):
+    """the bytes the reference writes for these frames: the STRICT build of the unmodified reference, AVX2 path
+    (the parity target of layout B; AVX-512VL under -ffast-math differs from it in ~1e-5 of the bytes, SURVEY 4);
+    the oracle port when the host has no AVX2 or oracle/_ref did not travel.  -> (bytes[F, H*W], source)"""
+    import oraclelib as ol
+    out = np.empty((frames_np.shape[0], h * w), dtype=np.uint8)
+    if ol.have_reference("strict") and "avx2" in ol.cpu_flags():
+        ref = ol.Reference("strict")
+        ref.set_isa("avx2")
+        for f in range(frames_np.shape[0]):
+            rc, o = ref.call("B", frames_np[f], lut, w, 2 * h, 0, 2 * h)
+            assert rc == 0
+            out[f] = o[:h * w]
+        return out, "reference (strict build, avx2 path)"
+    o = ol.Oracle()
+    for f in range(frames_np.shape[0]):
+        out[f] = o.forward(ol.LAYOUT_B, frames_np[f], lut, quirks=ol.QUIRK_AVX_X3)
+    return out, "oracle port (reference not runnable on this host)"
 
 
 def main():
@@ -324,6 +359,7 @@ def main():
         sampler.start()
     t_heat = time.perf_counter()
     ms_step, launches, (w0, w1) = timed(lambda: ctx.forward(d_in, lut, job, out=d_out), args.steps, args.warmup, preheat_s=args.preheat)
+    headline_out = d_out.clone()   # the bytes the timed launches wrote (d_out is reused by the variants below)
     clocks = None
     if rank == 0:
         # the same kernel runs back to back from t_heat + warm-up to w1: the clock samples of that
@@ -346,70 +382,255 @@ def main():
                 "traffic": traffic, "peak_source": peak_src, "kernel": "sdct::forward_kernel<layout B, exact, X3>",
                 "algorithmic_bytes_per_launch": blocks_per_rank * BYTES_PER_BLOCK}
 
-    # e2e: HOST buffers through the reference-facing call (the simd_dct.h symbol exported by
-    # libsdct.so), H2D + kernel + D2H inside the timed region.  The batch is handed over the way a
-    # caller of the reference would hand it over: the F frames stacked into one plane of F*H rows
-    # (blocks are independent, so the bytes equal the per-frame results), sizeY = 2*F*H because the
-    # reference visits only rows below sizeY/2 (src/simd_dct.cpp:2243).
+    def rate(ms, nblocks, bytes_per_block=BYTES_PER_BLOCK, ranks=world):
+        gbps = nblocks * bytes_per_block / (ms * 1e-3) / 1e9
+        return {"us_per_launch": ms * 1e3, "blocks_per_s": ranks * nblocks / (ms * 1e-3), "gbps_per_gpu": gbps, "frac_of_hbm_peak": gbps / peak}
+
+    # ---- parity of the timed bytes, checked in this run (rank 0; the first PF frames of the batch) ----------------------
+    # EXACT: against the bytes of the unmodified reference (strict build, AVX2 path).  FAST / TENSOR are this repo's own
+    # arithmetic: their distance from the EXACT bytes with the same X3 setting is reported as a rate, the
+    # bound is <= 1 level.
+    parity = None
+    if rank == 0:
+        PF = min(2, F)
+        want, src = strict_reference_bytes(frames_np[:PF], lut, W, H)
+        got = headline_out.view(F, -1)[:PF].cpu().numpy()
+        parity = {"frames_checked": PF, "against": src, "exact_bytes_identical": bool(np.array_equal(got, want)),
+                  "exact_bytes_differing": int(np.count_nonzero(got != want))}
+        truth = ctx.forward(d_in[:PF], lut, sd.dense_job(sd.LAYOUT_B, W, H, frames=PF, flags=sd.EXACT)).cpu().numpy().astype(np.int16)
+        for name, fl in (("fast", sd.FAST), ("tensor", sd.TENSOR)):
+            lv = ctx.forward(d_in[:PF], lut, sd.dense_job(sd.LAYOUT_B, W, H, frames=PF, flags=fl)).cpu().numpy().astype(np.int16)
+            d = np.abs(lv - truth)
+            parity[name + "_mismatch_rate"] = float(np.mean(d != 0))
+            parity[name + "_max_abs"] = int(d.max())
+        parity["note"] = ("fast/tensor rates are vs EXACT without the X3 quirk (the true DCT) on this workload: uniform random pixels under "
+                          "the default LUT, where layout B's quantiser scale reaches 2 684 per unit coefficient")
+
+    # ---- e2e: HOST buffers through the reference-facing call (the simd_dct.h symbol exported by libsdct.so), H2D +
+    # kernel + D2H inside the timed region.  The batch is handed over the way a caller of the reference would hand it
+    # over: the F frames stacked into one plane of F*H rows (blocks are independent, so the bytes equal the per-frame
+    # results), sizeY = 2*F*H because the reference visits only rows below sizeY/2 (src/simd_dct.cpp:2243).
     e2e = None
     if not args.no_e2e:
         h_in = torch.from_numpy(frames_np).pin_memory()
         h_out = torch.empty(F * H * W, dtype=torch.uint8).pin_memory()
         e2e_steps = max(3, min(args.steps, 10))
+        nbytes = F * H * W
 
-        def e2e_step():
-            rc = sd.simdDCT_EncodeQuantize32ReorderBuffer(h_in, h_out, lut, W, 2 * F * H, 0, 2 * F * H)
-            assert rc == sd.sdr_Success, sd.last_error()
-        for _ in range(3):
-            e2e_step()
-        barrier()
-        t0 = time.perf_counter()
-        for _ in range(e2e_steps):
-            e2e_step()
-        dt = max_over_ranks((time.perf_counter() - t0) / e2e_steps)
-        barrier()
-        e2e = {"value": world * blocks_per_rank / dt, "unit": UNIT, "h2d_bytes_per_step": F * H * W,
-               "d2h_bytes_per_step": F * H * W, "ms_per_step": dt * 1e3, "steps": e2e_steps,
-               "gbps_each_way": F * H * W / dt / 1e9,
+        def wall(fn, steps, warm=3):
+            for _ in range(warm):
+                fn()
+            barrier()
+            t0 = time.perf_counter()
+            for _ in range(steps):
+                fn()
+            dt = max_over_ranks((time.perf_counter() - t0) / steps)
+            barrier()
+            return dt
+
+        def shim_step(fn, sy):
+            def step():
+                rc = fn(h_in, h_out, lut, W, sy, 0, sy)
+                assert rc == sd.sdr_Success, sd.last_error()
+            return step
+        dt = wall(shim_step(sd.simdDCT_EncodeQuantize32ReorderBuffer, 2 * F * H), e2e_steps)
+        assert torch.equal(h_out.cuda(), headline_out), "host pipeline and device path disagree"
+        # the platform's ceiling for this traffic: the same bytes as raw concurrent pinned copies (all ranks at once)
+        s_up, s_dn = torch.cuda.Stream(), torch.cuda.Stream()
+        d_a, d_b = torch.empty_like(d_in), torch.empty_like(d_out)
+
+        def raw_copies():
+            with torch.cuda.stream(s_up):
+                d_a.copy_(h_in, non_blocking=True)
+            with torch.cuda.stream(s_dn):
+                h_out.copy_(d_b, non_blocking=True)
+            s_up.synchronize()
+            s_dn.synchronize()
+        dt_raw = wall(raw_copies, e2e_steps)
+        del d_a, d_b
+        e2e = {"value": world * blocks_per_rank / dt, "unit": UNIT, "h2d_bytes_per_step": nbytes,
+               "d2h_bytes_per_step": nbytes, "ms_per_step": dt * 1e3, "steps": e2e_steps,
+               "gbps_each_way": nbytes / dt / 1e9,
+               "copy_ceiling": {"ms_per_step": dt_raw * 1e3, "gbps_each_way_per_gpu": nbytes / dt_raw / 1e9, "aggregate_gbps_each_way": world * nbytes / dt_raw / 1e9,
+                                "how": "the step's bytes as one pinned H2D and one pinned D2H copy on two streams, all ranks concurrently, wall clock, max over ranks"},
+               "frac_of_copy_ceiling": dt_raw / dt,
                "api": "simdDCT_EncodeQuantize32ReorderBuffer (simd_dct.h shim of libsdct.so) on pinned host buffers; "
                       "synchronous call = chunked H2D / kernel / D2H pipeline, wall clock"}
-        assert torch.equal(h_out.cuda(), d_out), "host pipeline and device path disagree"
+        if not args.no_variants:
+            # the other two entry points on the same bytes (layout C: the batch as two eyes of F*H/2 rows)
+            other = {}
+            dta = wall(shim_step(sd.simdDCT_EncodeQuantizeBuffer, 2 * F * H), max(3, e2e_steps // 2), warm=2)
+            other["layout_A"] = {"ms_per_step": dta * 1e3, "blocks_per_s": world * blocks_per_rank / dta, "gbps_each_way": nbytes / dta / 1e9}
+            if (F * H) % 16 == 0:
+                dtc = wall(shim_step(sd.simdDCT_EncodeQuantizeReorderStereoBuffer, F * H), max(3, e2e_steps // 2), warm=2)
+                other["layout_C"] = {"ms_per_step": dtc * 1e3, "blocks_per_s": world * blocks_per_rank / dtc, "gbps_each_way": nbytes / dtc / 1e9}
+            # pageable caller memory (what an unmodified caller's malloc'd buffers are): staged through pinned memory
+            p_in, p_out = frames_np, np.empty(F * H * W, dtype=np.uint8)
 
-    # secondary measurements (same batch; informative, not the headline)
+            def pageable():
+                assert sd.simdDCT_EncodeQuantize32ReorderBuffer(p_in, p_out, lut, W, 2 * F * H, 0, 2 * F * H) == sd.sdr_Success
+            dtp = wall(pageable, 3, warm=1)
+            other["layout_B_pageable"] = {"ms_per_step": dtp * 1e3, "blocks_per_s": world * blocks_per_rank / dtp, "gbps_each_way": nbytes / dtp / 1e9}
+            e2e["other_entry_points"] = other
+            # one process driving every visible GPU through ONE host call (rank 0, the other ranks idle at the barrier)
+            ndev = torch.cuda.device_count()
+            if ndev > 1:
+                if rank == 0:
+                    ctxs = [sd.Context(d) for d in range(ndev)]
+                    mj = sd.dense_job(sd.LAYOUT_B, W, H, frames=F, flags=flags)
+
+                    def multi():
+                        sd.forward_host_multi(ctxs, h_in, lut, mj, out=h_out)
+                    for _ in range(2):
+                        multi()
+                    t0 = time.perf_counter()
+                    for _ in range(5):
+                        multi()
+                    dtm = (time.perf_counter() - t0) / 5
+                    e2e["single_process_all_gpus"] = {"gpus": ndev, "ms_per_step": dtm * 1e3, "blocks_per_s": blocks_per_rank / dtm,
+                                                      "gbps_each_way": nbytes / dtm / 1e9,
+                                                      "api": "sdct_forward_host_multi: one call, frames sharded over all devices, one host thread each"}
+                    assert torch.equal(h_out.cuda(), headline_out)
+                    for c in ctxs:
+                        c.close()
+                barrier()
+        del h_in, h_out
+
+    # ---- secondary measurements, keyed by BASELINE.json config (informative; `value` stays configs[1] EXACT) --------------
     variants = {}
     if not args.no_variants:
         vs = max(10, args.steps // 2)
 
-        def add(name, fn, bytes_per_block=BYTES_PER_BLOCK, nblocks=blocks_per_rank):
-            ms, _, _ = timed(fn, vs, 3)
-            variants[name] = {"blocks_per_s": world * nblocks / (ms * 1e-3), "ms_per_step": ms,
-                              "gbps_per_gpu": nblocks * bytes_per_block / (ms * 1e-3) / 1e9,
-                              "frac_of_hbm_peak": nblocks * bytes_per_block / (ms * 1e-3) / 1e9 / peak}
-        for lname, layout in (("A", sd.LAYOUT_A), ("B", sd.LAYOUT_B), ("C", sd.LAYOUT_C)):
-            fl = sd.EXACT | (sd.QUIRK_AVX_X3 if layout == sd.LAYOUT_B else 0)
-            j = sd.dense_job(layout, W, H, frames=F, flags=fl)
-            if layout != sd.LAYOUT_B:
-                add(f"forward_{lname}_exact", lambda j=j: ctx.forward(d_in, lut, j, out=d_out))
+        def tm(fn, steps=vs):
+            ms, _, _ = timed(fn, steps, 3)
+            return ms
+        L = (("A", sd.LAYOUT_A), ("B", sd.LAYOUT_B), ("C", sd.LAYOUT_C))
+
+        def exact_flags(layout):
+            return sd.EXACT | (sd.QUIRK_AVX_X3 if layout == sd.LAYOUT_B else 0)
+
+        # configs[1]: the headline batch, every layout / arithmetic / direction
+        c1 = {}
+        d_back = torch.empty_like(d_in)
+        for lname, layout in L:
+            j = sd.dense_job(layout, W, H, frames=F, flags=exact_flags(layout))
             jf = sd.dense_job(layout, W, H, frames=F, flags=sd.FAST)
-            add(f"forward_{lname}_fast", lambda jf=jf: ctx.forward(d_in, lut, jf, out=d_out))
             jt = sd.dense_job(layout, W, H, frames=F, flags=sd.TENSOR)   # tcgen05 form (own exact-integer definition, not the reference's fp32 rounding)
-            add(f"forward_{lname}_tensor", lambda jt=jt: ctx.forward(d_in, lut, jt, out=d_out))
+            c1[f"forward_{lname}_exact"] = rate(tm(lambda: ctx.forward(d_in, lut, j, out=d_out)), blocks_per_rank)
+            c1[f"forward_{lname}_fast"] = rate(tm(lambda: ctx.forward(d_in, lut, jf, out=d_out)), blocks_per_rank)
+            c1[f"forward_{lname}_tensor"] = rate(tm(lambda: ctx.forward(d_in, lut, jt, out=d_out)), blocks_per_rank)
             ctx.forward(d_in, lut, j, out=d_out)
-            d_back = torch.empty_like(d_in)
-            add(f"inverse_{lname}", lambda j=j, d_back=d_back: ctx.inverse(d_out, lut, j, out=d_back))
-            add(f"inverse_{lname}_tensor", lambda jt=jt, d_back=d_back: ctx.inverse(d_out, lut, jt, out=d_back))
-            add(f"roundtrip_fused_{lname}_exact", lambda j=j, d_back=d_back: ctx.roundtrip(d_in, lut, j, out=d_back))
+            c1[f"inverse_{lname}"] = rate(tm(lambda: ctx.inverse(d_out, lut, j, out=d_back)), blocks_per_rank)
+            c1[f"inverse_{lname}_tensor"] = rate(tm(lambda: ctx.inverse(d_out, lut, jt, out=d_back)), blocks_per_rank)
+            c1[f"roundtrip_fused_{lname}_exact"] = rate(tm(lambda: ctx.roundtrip(d_in, lut, j, out=d_back)), blocks_per_rank)
+            try:
+                c1[f"roundtrip_fused_{lname}_tensor"] = rate(tm(lambda: ctx.roundtrip(d_in, lut, jt, out=d_back)), blocks_per_rank)
+            except sd.SdctError as e:
+                c1[f"roundtrip_fused_{lname}_tensor"] = {"unsupported": str(e)}
+        variants["configs[1] 64x1080p luma, per GPU (weak)"] = c1
+        del d_back
+
+        # configs[2]: 256 frames 3840x2160x3 interleaved RGB -> 3 planar coefficient sets, per GPU (weak scaling)
+        F2, H2, W2 = 256, 2160, 3840
+        nb2 = F2 * 3 * (H2 // 8) * (W2 // 8)
+        gen = torch.Generator(device="cuda").manual_seed(99 + rank)
+        rgb = torch.randint(0, 256, (F2, H2, W2, 3), dtype=torch.uint8, device="cuda", generator=gen)
+        coef2 = torch.empty(F2 * H2 * W2 * 3, dtype=torch.uint8, device="cuda")
+        c2 = {}
+        for lname, layout in L[1:]:
+            for mname, fl in (("exact", exact_flags(layout)), ("tensor", sd.TENSOR)):
+                j = sd.dense_job(layout, W2, H2, frames=F2, components=3, flags=fl)
+                c2[f"forward_rgb_{lname}_{mname}"] = rate(tm(lambda: ctx.forward(rgb, lut, j, out=coef2), steps=5), nb2)
+        variants["configs[2] 256x4K interleaved RGB -> planar + forward, per GPU (weak)"] = c2
+        # ... and the decode of those coefficient sets back to interleaved pixels (fp32; TENSOR where supported)
+        back2 = torch.empty_like(rgb)
+        for lname, layout in L[1:]:
+            for mname, fl in (("fp32", exact_flags(layout)), ("tensor", sd.TENSOR)):
+                j = sd.dense_job(layout, W2, H2, frames=F2, components=3, flags=fl)
+                try:
+                    c2[f"inverse_rgb_{lname}_{mname}"] = rate(tm(lambda: ctx.inverse(coef2, lut, j, out=back2), steps=5), nb2)
+                except sd.SdctError as e:
+                    c2[f"inverse_rgb_{lname}_{mname}"] = {"unsupported": str(e)}
+        del rgb, coef2, back2
+
+        # configs[3]: inverse-only decode of 4K coefficient planes, 64 frames in total sharded by frame over the ranks
+        # (strong scaling: the job is fixed, every rank decodes its contiguous frame range; no collective)
+        from simd_dct_b200 import sharding
+        F3 = 64
+        c3 = {}
+        for lname, layout in L:
+            whole = sd.dense_job(layout, W2, H2, frames=F3, flags=exact_flags(layout))
+            sub, _, _ = sharding.shard_frames(whole, rank, world)
+            mine = int(sub.frames)
+            px = torch.randint(0, 256, (max(mine, 1), H2, W2), dtype=torch.uint8, device="cuda", generator=gen)
+            cf = ctx.forward(px, lut, sub) if mine else torch.empty(0, dtype=torch.uint8, device="cuda")
+            for mname, fl in (("fp32", exact_flags(layout)), ("tensor", sd.TENSOR)):
+                jj = sd.dense_job(layout, W2, H2, frames=mine, flags=fl)
+                ms = tm(lambda: ctx.inverse(cf, lut, jj, out=px) if mine else None)
+                r = rate(ms, F3 * (H2 // 8) * (W2 // 8) / world, ranks=world)
+                r["frames_this_rank"] = mine
+                c3[f"inverse_{lname}_{mname}"] = r
+            del px, cf
+        variants[f"configs[3] inverse-only, 64x4K planes sharded by frame over {world} GPU(s) (strong)"] = c3
+
+        # configs[4]: 32768x32768x3 interleaved image, forward + inverse round trip, band ranges sharded over the ranks
+        # (strong scaling; every rank holds only its own band range: 4096 / world bands)
+        W5 = H5 = 32768
+        bands = H5 // 8
+        b0, b1 = sd.shard_range(bands, rank, world)
+        rows = (b1 - b0) * 8
+        nb5 = 3 * (b1 - b0) * (W5 // 8)
+        img = torch.randint(0, 256, (max(rows, 8), W5, 3), dtype=torch.uint8, device="cuda", generator=gen)
+        out5 = torch.empty_like(img)
+        c5 = {}
+        lut5 = ol.lut(255.0 * 4)   # a LUT under which layout B's round trip is meaningful (the default one saturates)
+        tot5 = 3 * bands * (W5 // 8)
+        for lname, layout in L[1:2]:
+            je = sd.dense_job(layout, W5, rows, components=3, flags=sd.EXACT)
+            jt = sd.dense_job(layout, W5, rows, components=3, flags=sd.TENSOR)
+            r = rate(tm(lambda: ctx.roundtrip(img, lut5, je, out=out5), steps=5), tot5 / world, ranks=world)
+            c5[f"roundtrip_fused_{lname}_exact"] = r
+            try:
+                c5[f"roundtrip_fused_{lname}_tensor"] = rate(tm(lambda: ctx.roundtrip(img, lut5, jt, out=out5), steps=5), tot5 / world, ranks=world)
+            except sd.SdctError as e:
+                c5[f"roundtrip_fused_{lname}_tensor"] = {"unsupported": str(e)}
+            cf5 = torch.empty(rows * W5 * 3, dtype=torch.uint8, device="cuda")
+
+            def two(j):
+                ctx.forward(img, lut5, j, out=cf5)
+                ctx.inverse(cf5, lut5, j, out=out5)
+            c5[f"forward_then_inverse_{lname}_exact (256 B/block)"] = rate(tm(lambda: two(je), steps=5), tot5 / world, 2 * BYTES_PER_BLOCK, ranks=world)
+            try:
+                c5[f"forward_then_inverse_{lname}_tensor (256 B/block)"] = rate(tm(lambda: two(jt), steps=5), tot5 / world, 2 * BYTES_PER_BLOCK, ranks=world)
+            except sd.SdctError as e:
+                c5[f"forward_then_inverse_{lname}_tensor (256 B/block)"] = {"unsupported": str(e)}
+            del cf5
+        c5["bands_this_rank"] = b1 - b0
+        del img, out5
+        variants[f"configs[4] 32768x32768x3 round trip, bands sharded over {world} GPU(s) (strong)"] = c5
 
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
             "data": "synthetic", "config": config, "gbps": value * BYTES_PER_BLOCK / 1e9, "roofline": roofline,
-            "e2e": e2e, "gpu_launches": launches, "clocks": clocks, "variants": variants}
-    if rank == 0 and world == 1:
-        cpu, cpu_out = time_cpu(W, H, frames_np, lut, reps=3)
+            "e2e": e2e, "gpu_launches": launches, "clocks": clocks, "parity": parity, "variants": variants}
+    if variants:
+        c1 = variants["configs[1] 64x1080p luma, per GPU (weak)"]
+        pick = lambda k: {kk: c1[k][kk] for kk in ("us_per_launch", "gbps_per_gpu", "frac_of_hbm_peak")} if "us_per_launch" in c1.get(k, {}) else None  # noqa: E731
+        line["roofline_inverse"] = {"kernel": "inverse_kernel<B> (fp32) / inverse_tc_kernel<B> (tensor)", "fp32": pick("inverse_B"), "tensor": pick("inverse_B_tensor"),
+                                    "note": "parity unpinned: the reference has no inverse"}
+        line["roofline_roundtrip"] = {"kernel": "roundtrip_kernel<B> (fp32, fused) / roundtrip_tc_kernel<B>", "fp32": pick("roundtrip_fused_B_exact"),
+                                      "tensor": pick("roundtrip_fused_B_tensor"), "algorithmic_bytes_per_block": BYTES_PER_BLOCK}
+    if rank == 0:
+        # the reference's CPU implementation beside it, on this box's host cores (bounded samples; the other ranks wait)
+        n_cpu = F if world == 1 else min(F, 16)
+        cpu, _ = time_cpu(W, H, frames_np[:n_cpu], lut, reps=3)
+        cpu["single_thread"], _ = time_cpu(W, H, frames_np[:4], lut, reps=5, threads=1, budget_s=4.0)   # the reference's own method: best of N, one thread (src/main.cpp:510-530)
+        if world == 1:
+            cpu["layout_A"], _ = time_cpu(W, H, frames_np[:16], lut, reps=2, layout="A", budget_s=5.0)
+            cpu["layout_C"], _ = time_cpu(W, H, frames_np[:16], lut, reps=2, layout="C", budget_s=5.0)
+            cpu["layout_C_single_thread"], _ = time_cpu(W, H, frames_np[:2], lut, reps=3, layout="C", threads=1, budget_s=4.0)
         line["cpu_baseline"] = cpu
-        # the timed GPU output is the reference's output (when the reference itself is the baseline)
-        if cpu["kind"] == "reference" and "avx2" in cpu["sample"]:
-            line["cpu_baseline"]["bytes_identical_to_gpu"] = bool(np.array_equal(cpu_out.reshape(-1), d_out.cpu().numpy()))
+    barrier()
     if rank == 0:
         print(json.dumps(line), flush=True)
     if dist is not None:

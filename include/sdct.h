@@ -84,7 +84,8 @@ void sdct_job_dense(sdct_job *job, int layout, int flags, int components, int ey
                     uint64_t width, uint64_t height, uint64_t frames);
 
 /* context = one device + its streams, staging buffers and launch counters
- * (replaces the caller-side _DetectCPUFeatures() contract, src/simd_platform.h:131) */
+ * (replaces the caller-side _DetectCPUFeatures() contract, src/simd_platform.h:131).  The $SDCT_* environment
+ * switches (SDCT_HOST_CHUNK_MB, SDCT_HOST_SLOTS, SDCT_HOST_NO_RAMP, SDCT_TC_NO_TMA, ...) are read here, once. */
 int sdct_create(int device, sdct_context **out);
 void sdct_destroy(sdct_context *ctx);
 const char *sdct_last_error(void);
@@ -107,11 +108,21 @@ int sdct_inverse_device(sdct_context *ctx, const sdct_job *job, const void *d_co
 int sdct_roundtrip_device(sdct_context *ctx, const sdct_job *job, const void *d_pixels_in, const float *lut,
                           void *d_pixels_out, void *stream);
 
-/* host-buffer operations: pinned staging + chunked H2D -> kernel -> D2H pipeline on 3 streams */
+/* host-buffer operations: chunked H2D -> kernel -> D2H pipeline ($SDCT_HOST_SLOTS chunks in flight, default 4, each a
+ * dense 16-byte-aligned sub-job on the device); pinned caller memory is DMA'd directly, pageable memory goes through
+ * pinned staging.  Only the bytes of the job's window are written - row padding and unprocessed bands stay untouched.
+ * Thread-safe: concurrent calls on one context (e.g. disjoint band windows of one image, the reference's threading
+ * model, src/simd_dct.cpp:1073-1087) run on separate pipelines and overlap. */
 int sdct_forward_host(sdct_context *ctx, const sdct_job *job, const void *h_pixels, const float *lut,
                       void *h_coefs);
 int sdct_inverse_host(sdct_context *ctx, const sdct_job *job, const void *h_coefs, const float *lut,
                       void *h_pixels);
+/* the same over several devices in ONE call: contiguous frame ranges (frames >= n_ctx) or band ranges of the job's
+ * window go to the contexts' devices, one host thread and pipeline each; no inter-device exchange */
+int sdct_forward_host_multi(sdct_context *const *ctxs, int n_ctx, const sdct_job *job, const void *h_pixels,
+                            const float *lut, void *h_coefs);
+int sdct_inverse_host_multi(sdct_context *const *ctxs, int n_ctx, const sdct_job *job, const void *h_coefs,
+                            const float *lut, void *h_pixels);
 
 /* test hook: runs one of the device 8-point kernels on n vectors of 8 floats (host memory, in place)
  * so that tests can compare the GPU arithmetic bit for bit with the CPU restatement.
@@ -135,8 +146,9 @@ void sdct_host_free(void *p);
  * The reference's call semantics on HOST buffers, used by the simd_dct.h shim:
  * sizeY is the stereo (double) height, only rows below sizeY/2 are visited, [startY, endY] is
  * the inclusive window of src/simd_dct.cpp:268-282 / :375-387 / :2243-2255, return value is
- * the reference's simdDctResult.  They run on a lazily created process-wide context
- * (device = $SDCT_DEVICE or 0).
+ * the reference's simdDctResult.  They run on lazily created process-wide contexts: device $SDCT_DEVICE (default 0),
+ * or - $SDCT_DEVICES = "all" | "0,1,..." - the call's bands sharded over several devices (sdct_forward_host_multi).
+ * Calls from several threads overlap (see sdct_forward_host).
  */
 int sdct_ref_encode_quantize_buffer(const uint8_t *from, uint8_t *to, const float *lut,
                                     size_t size_x, size_t size_y, size_t start_y, size_t end_y);        /* src/simd_dct.h:29 */
@@ -147,6 +159,8 @@ int sdct_ref_encode_quantize32_reorder_buffer(const uint8_t *from, uint8_t *to, 
 /* flags applied by the three functions above (default SDCT_EXACT | SDCT_QUIRK_AVX_X3 = reference bytes) */
 void sdct_ref_set_flags(int flags);
 int sdct_ref_get_flags(void);
+/* number of devices the three functions above shard a call over (creates the process-wide contexts; 0 on failure) */
+int sdct_ref_device_count(void);
 
 /* contiguous shard [begin, end) of `total` units for `rank` of `world` (frames or bands; no collective) */
 void sdct_shard_range(uint64_t total, int rank, int world, uint64_t *begin, uint64_t *end);

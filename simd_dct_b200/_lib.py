@@ -6,7 +6,8 @@ import ctypes as C
 import os
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libsdct.so")
+# $SDCT_LIB: an experiment build of the same library (tools/build_variants.py); never a different implementation
+LIB_PATH = os.environ.get("SDCT_LIB") or os.path.join(HERE, "libsdct.so")
 
 OK, INVALID_PARAMETER, NOT_SUPPORTED, CUDA_ERROR, NO_DEVICE = range(5)
 LAYOUT_A, LAYOUT_B, LAYOUT_C = 0, 1, 2
@@ -39,6 +40,8 @@ SYMBOLS = {
     "sdct_roundtrip_device": (C.c_int, [_vp, _JP, _vp, _fp, _vp, _vp]),
     "sdct_forward_host": (C.c_int, [_vp, _JP, _vp, _fp, _vp]),
     "sdct_inverse_host": (C.c_int, [_vp, _JP, _vp, _fp, _vp]),
+    "sdct_forward_host_multi": (C.c_int, [C.POINTER(_vp), C.c_int, _JP, _vp, _fp, _vp]),
+    "sdct_inverse_host_multi": (C.c_int, [C.POINTER(_vp), C.c_int, _JP, _vp, _fp, _vp]),
     "sdct_selftest_dct8": (C.c_int, [_vp, C.c_int, _fp, _sz]),
     "sdct_tensor_matrix": (None, [C.POINTER(C.c_int32)]),
     "sdct_synchronize": (C.c_int, [_vp]),
@@ -49,6 +52,7 @@ SYMBOLS = {
     "sdct_ref_encode_quantize32_reorder_buffer": (C.c_int, [_vp, _vp, _fp, _sz, _sz, _sz, _sz]),
     "sdct_ref_set_flags": (None, [C.c_int]),
     "sdct_ref_get_flags": (C.c_int, []),
+    "sdct_ref_device_count": (C.c_int, []),
     "sdct_shard_range": (None, [C.c_uint64, C.c_int, C.c_int, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]),
 }
 # the reference's C++-linkage entry points (include/simd_dct.h), Itanium-mangled

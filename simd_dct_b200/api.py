@@ -185,3 +185,25 @@ class Context:
         check(self._lib.sdct_inverse_host(self._h, C.byref(job), C.c_void_p(_host_ptr(coefs)), _fp(lut),
                                           C.c_void_p(_host_ptr(out))))
         return out
+
+
+def _ctx_array(ctxs):
+    arr = (C.c_void_p * len(ctxs))(*[c._h for c in ctxs])
+    return arr, len(ctxs)
+
+
+def forward_host_multi(ctxs, pixels, lut, job: Job, out=None):
+    """one host-buffer call sharded over several Contexts (= devices): frame ranges or band ranges, no collective"""
+    if out is None:
+        out = np.empty(int(job.frames * job.coef_frame_stride), dtype=np.uint8)
+    arr, n = _ctx_array(ctxs)
+    check(_lib.load().sdct_forward_host_multi(arr, n, C.byref(job), C.c_void_p(_host_ptr(pixels)), _fp(lut), C.c_void_p(_host_ptr(out))))
+    return out
+
+
+def inverse_host_multi(ctxs, coefs, lut, job: Job, out=None):
+    if out is None:
+        out = np.empty(int(job.frames * job.pixel_frame_stride), dtype=np.uint8)
+    arr, n = _ctx_array(ctxs)
+    check(_lib.load().sdct_inverse_host_multi(arr, n, C.byref(job), C.c_void_p(_host_ptr(coefs)), _fp(lut), C.c_void_p(_host_ptr(out))))
+    return out

@@ -31,11 +31,13 @@ def _stale() -> bool:
     return any(os.path.getmtime(os.path.join(CSRC, f)) > t for f in SOURCES + HEADERS)
 
 
-def build(force: bool = False, verbose: bool = False) -> str:
-    if not force and not _stale():
+def build(force: bool = False, verbose: bool = False, defs=None, out: str = LIB, only_kernels: bool = False) -> str:
+    """defs / out: experiment builds (tools/build_variants.py) - extra -D switches, written to another .so that
+    $SDCT_LIB selects at load time; the product build is the default call."""
+    if defs is None and out == LIB and not force and not _stale():
         return LIB
     nvcc = _nvcc()
-    objdir = os.path.join(HERE, "build")
+    objdir = os.path.join(HERE, "build" if out == LIB else os.path.join("build", os.path.splitext(os.path.basename(out))[0]))
     os.makedirs(objdir, exist_ok=True)
     objs = []
     procs = []
@@ -46,22 +48,23 @@ def build(force: bool = False, verbose: bool = False) -> str:
         cmd = [nvcc] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ([] if part is None else ["-DSDCT_PART=%d" % part])
         if os.environ.get("SDCT_NVCC_DEFS"):         # experiments: extra -D switches
             cmd += ["-D" + d for d in os.environ["SDCT_NVCC_DEFS"].split(",")]
+        cmd += ["-D" + d for d in (defs or [])]
         if os.environ.get("SDCT_TC_TRACE") == "1":   # profiling build: role stamps + ablation switches in sdct_tc.cu
             cmd.append("-DSDCT_TC_TRACE=1")
         cmd += ["-c", os.path.join(CSRC, src), "-o", obj]
         procs.append((cmd, subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)))
         objs.append(obj)
     for cmd, p in procs:
-        out, _ = p.communicate()
-        if verbose and out:
-            print(out)
+        log, _ = p.communicate()
+        if verbose and log:
+            print(log)
         if p.returncode != 0:
-            raise RuntimeError("nvcc failed: %s\n%s" % (" ".join(cmd), out))
-    cmd = [nvcc, "-shared", "-o", LIB] + objs
+            raise RuntimeError("nvcc failed: %s\n%s" % (" ".join(cmd), log))
+    cmd = [nvcc, "-shared", "-o", out] + objs
     r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
     if r.returncode != 0:
         raise RuntimeError("link failed: %s\n%s" % (" ".join(cmd), r.stdout))
-    return LIB
+    return out
 
 
 if __name__ == "__main__":

@@ -99,6 +99,24 @@ int build_tables(const sdct_job *j, const float *lut, int op, float2 tab[64], fl
 
 bool aligned(const void *p, uint64_t a) { return (reinterpret_cast<uintptr_t>(p) & (a - 1)) == 0; }
 
+// the $SDCT_* switches of a context, read once (sdct_create)
+void read_env(SdctEnv *e)
+{
+    auto num = [](const char *name, long lo, long hi, long dflt) {
+        const char *v = getenv(name);
+        if (!v) return dflt;
+        const long n = atol(v);
+        return n >= lo && n <= hi ? n : dflt;
+    };
+    e->host_chunk_bytes = (uint64_t)num("SDCT_HOST_CHUNK_MB", 1, 4096, 16) << 20;
+    e->host_slots = (int)num("SDCT_HOST_SLOTS", 1, kSlots, 4);
+    e->host_no_ramp = getenv("SDCT_HOST_NO_RAMP") != nullptr;
+    e->tc.no_tma = getenv("SDCT_TC_NO_TMA") != nullptr;
+    e->tc.no_rgb_fuse = getenv("SDCT_TC_NO_RGB_FUSE") != nullptr;
+    e->tc.no_tma_store = getenv("SDCT_TC_NO_TMA_STORE") != nullptr;
+    e->tc.ablate = (uint32_t)num("SDCT_TC_ABLATE", 0, 0x7fffffff, 0);
+}
+
 int run_device(sdct_context *ctx, int op, const sdct_job *j, const uint8_t *pixels, uint8_t *coefs,
                uint8_t *pixels_out, const float *lut, cudaStream_t stream)
 {
@@ -147,32 +165,48 @@ int run_device(sdct_context *ctx, int op, const sdct_job *j, const uint8_t *pixe
             return fail(SDCT_NOT_SUPPORTED, "SDCT_TENSOR inverse needs one component, 16-byte-aligned pixel rows and coefficients, "
                                             "an even number of blocks per row (layout C: a multiple of 16 blocks)");
         cudaStream_t st = stream ? stream : ctx->stream;
-        sdct_context::InvOperand *op_entry = nullptr;
         {
+            // The LUT-dependent operand.  A miss uploads it SYNCHRONOUSLY (the key becomes visible only after the
+            // copy has completed, so a hit on any stream may launch without an event); before an entry's device
+            // buffer is overwritten the device is synchronised (kernels in flight on other streams may read it).
             std::lock_guard<std::mutex> lock(ctx->inv_mu);
+            sdct_context::InvOperand *op_entry = nullptr;
             for (auto &e : ctx->inv_cache)
                 if (e.d && e.layout == j->layout && memcmp(e.lut, lut, sizeof(e.lut)) == 0) op_entry = &e;
             if (!op_entry) {
-                op_entry = &ctx->inv_cache[ctx->inv_next++ % 4];
-                static thread_local uint16_t operand[128 * 64];
-                float scale[64];
+                sdct_context::InvOperand *victim = &ctx->inv_cache[0];
+                for (auto &e : ctx->inv_cache) {
+                    if (e.layout < 0) { victim = &e; break; }
+                    if (e.used < victim->used) victim = &e;
+                }
+                std::vector<uint16_t> operand(128 * 64);
+                float scale[64], off_cols[64];
                 for (int i = 0; i < 64; i++) scale[i] = p.tab[i].x;
-                op_entry->S = sdct_tc_inverse_operand(j->layout, scale, operand, op_entry->off_cols);
-                if (!op_entry->d) CU_TRY(cudaMalloc(&op_entry->d, sizeof(operand)));
-                // pageable source: the copy is staged before the call returns, and it is ordered before the launch below
-                CU_TRY(cudaMemcpyAsync(op_entry->d, operand, sizeof(operand), cudaMemcpyHostToDevice, st));
-                op_entry->layout = j->layout;
-                memcpy(op_entry->lut, lut, sizeof(op_entry->lut));
+                const int S = sdct_tc_inverse_operand(j->layout, scale, operand.data(), off_cols);
+                if (victim->layout >= 0) CU_TRY(cudaDeviceSynchronize());
+                victim->layout = -1;   // invalid while its buffer is rewritten
+                if (!victim->d) CU_TRY(cudaMalloc(&victim->d, operand.size() * sizeof(uint16_t)));
+                CU_TRY(cudaMemcpy(victim->d, operand.data(), operand.size() * sizeof(uint16_t), cudaMemcpyHostToDevice));
+                victim->S = S;
+                memcpy(victim->off_cols, off_cols, sizeof(off_cols));
+                memcpy(victim->lut, lut, sizeof(victim->lut));
+                victim->layout = j->layout;
+                op_entry = victim;
             }
+            op_entry->used = ++ctx->inv_clock;
             p.tc_matrix = op_entry->d;
             for (int c = 0; c < 64; c++) p.tab[c] = make_float2(op_entry->off_cols[c], op_entry->off_cols[c]);
             const float unscale = std::ldexp(1.f, -op_entry->S);
             p.tab2[0] = make_float2(unscale, unscale);
         }
-        CU_TRY(sdct_k_launch_tc(op, j->layout, &p, st));
+        {
+            std::lock_guard<std::mutex> lock(ctx->tc_maps_mu);
+            CU_TRY(sdct_k_launch_tc(op, j->layout, &p, &ctx->env.tc, &ctx->tc_maps, st));
+        }
     } else if (tensor) {
         p.tc_matrix = ctx->d_tc_matrix[j->layout == SDCT_LAYOUT_A ? 0 : 1];
-        CU_TRY(sdct_k_launch_tc(op, j->layout, &p, stream ? stream : ctx->stream));
+        std::lock_guard<std::mutex> lock(ctx->tc_maps_mu);
+        CU_TRY(sdct_k_launch_tc(op, j->layout, &p, &ctx->env.tc, &ctx->tc_maps, stream ? stream : ctx->stream));
     } else {
         CU_TRY(sdct_k_launch(op, j->layout, mode, x3, &p, stream ? stream : ctx->stream));
     }
@@ -223,24 +257,21 @@ int sdct_create(int device, sdct_context **out)
     CU_TRY(cudaGetDeviceProperties(&prop, device));
     if (prop.major != 10) return fail(SDCT_NO_DEVICE, "device %d is sm_%d%d; kernels are built for sm_100a only", device, prop.major, prop.minor);
     CU_TRY(cudaSetDevice(device));
-    sdct_context *c = new sdct_context();
+    std::unique_ptr<sdct_context, void (*)(sdct_context *)> c(new sdct_context(), sdct_destroy);   // released on every early return
     c->device = device;
     c->sm_count = prop.multiProcessorCount;
+    read_env(&c->env);
     CU_TRY(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
-    for (Slot &s : c->slots) {
-        CU_TRY(cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking));
-        CU_TRY(cudaEventCreateWithFlags(&s.done, cudaEventDisableTiming));
-    }
     {   // tensor-core B operands (16 KiB each)
-        static uint16_t op[128 * 64];
+        std::vector<uint16_t> op(128 * 64);
         const int layouts[2] = {SDCT_K_LAYOUT_A, SDCT_K_LAYOUT_B};
         for (int i = 0; i < 2; i++) {
-            sdct_tc_operand(layouts[i], op);
-            CU_TRY(cudaMalloc(&c->d_tc_matrix[i], sizeof(op)));
-            CU_TRY(cudaMemcpy(c->d_tc_matrix[i], op, sizeof(op), cudaMemcpyHostToDevice));
+            sdct_tc_operand(layouts[i], op.data());
+            CU_TRY(cudaMalloc(&c->d_tc_matrix[i], op.size() * sizeof(uint16_t)));
+            CU_TRY(cudaMemcpy(c->d_tc_matrix[i], op.data(), op.size() * sizeof(uint16_t), cudaMemcpyHostToDevice));
         }
     }
-    *out = c;
+    *out = c.release();
     return SDCT_OK;
 }
 
@@ -248,12 +279,8 @@ void sdct_destroy(sdct_context *c)
 {
     if (!c) return;
     cudaSetDevice(c->device);
-    for (Slot &s : c->slots) {
-        if (s.stream) { cudaStreamSynchronize(s.stream); cudaStreamDestroy(s.stream); }
-        if (s.done) cudaEventDestroy(s.done);
-        cudaFree(s.d_pix); cudaFree(s.d_coef);
-        cudaFreeHost(s.h_in); cudaFreeHost(s.h_out);
-    }
+    for (auto &p : c->pipes) sdct_destroy_pipeline(p.get());
+    c->pipes.clear();
     if (c->stream) { cudaStreamSynchronize(c->stream); cudaStreamDestroy(c->stream); }
     cudaFree(c->d_tc_matrix[0]); cudaFree(c->d_tc_matrix[1]);
     for (auto &e : c->inv_cache) cudaFree(e.d);
@@ -268,7 +295,10 @@ int sdct_synchronize(sdct_context *c)
     if (!c) return fail(SDCT_INVALID_PARAMETER, "context is null");
     CU_TRY(cudaSetDevice(c->device));
     CU_TRY(cudaStreamSynchronize(c->stream));
-    for (Slot &s : c->slots) CU_TRY(cudaStreamSynchronize(s.stream));
+    std::lock_guard<std::mutex> lock(c->pipes_mu);
+    for (auto &p : c->pipes)
+        for (Slot &s : p->slots)
+            if (s.stream) CU_TRY(cudaStreamSynchronize(s.stream));
     return SDCT_OK;
 }
 

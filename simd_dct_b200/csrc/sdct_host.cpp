@@ -1,62 +1,102 @@
 // sdct_host.cpp - host-buffer entry points: the chunked H2D -> kernel -> D2H pipeline behind
-// sdct_forward_host / sdct_inverse_host, and the reference-call wrappers that the simd_dct.h
-// shim binds (src/simd_dct.h:29-31).  Copies and kernels of different chunks overlap on
-// kSlots streams; pageable caller memory goes through pinned staging, pinned memory
-// (sdct_host_alloc / cudaHostRegister) is DMA'd directly.
+// sdct_forward_host / sdct_inverse_host (one device) and sdct_*_host_multi (several devices, one
+// call), and the reference-call wrappers that the simd_dct.h shim binds (src/simd_dct.h:29-31).
+//
+// A job is cut into chunks (frame ranges of a batch, band ranges of a large frame).  Every chunk is a
+// DENSE SUB-JOB on the device: its window of the caller's image is copied into a compact,
+// 16-byte-aligned device layout (row pitch rounded up to 16, only the window's rows, only the
+// window's coefficient bytes), so the kernels always run their aligned vector / TMA paths whatever
+// the caller's pitch and alignment, a small window over large frames costs no device memory, and
+// bytes outside the window - row padding included - are never written back.  Copies are linear
+// where source and destination are contiguous and 2-D (cudaMemcpy2DAsync: pixel rows with a padded
+// pitch; the 64 plane segments of a layout-C window) otherwise.  Copies and kernels of different
+// chunks overlap on the slots' streams; pageable caller memory goes through pinned staging that
+// has the device layout (one linear transfer per chunk), pinned memory is DMA'd directly.
+//
+// Concurrency: a call owns one Pipeline of the context's pool for its duration, so caller threads
+// with disjoint windows (the reference's threading model, src/simd_dct.cpp:1073-1087) overlap; the
+// multi-device form runs one such pipeline per device on its own host thread.
 #include "sdct_internal.h"
 
 #include <algorithm>
 #include <cstdlib>
 #include <cstring>
+#include <string>
+#include <thread>
 #include <vector>
 
 namespace {
 
-struct Span { uint64_t off, len; };
+struct Copy {   // width x rows bytes between host (h_off, h_pitch) and device (d_off, d_pitch); rows == 1: linear
+    uint64_t h_off, d_off, width, rows, h_pitch, d_pitch;
+};
 
-void merge_spans(std::vector<Span> &v)
+void normalise(std::vector<Copy> &v)
 {
-    std::sort(v.begin(), v.end(), [](const Span &a, const Span &b) { return a.off < b.off; });
+    for (Copy &c : v)
+        if (c.rows > 1 && c.h_pitch == c.width && c.d_pitch == c.width) { c.width *= c.rows; c.rows = 1; }
+    std::sort(v.begin(), v.end(), [](const Copy &a, const Copy &b) { return a.h_off < b.h_off; });
     size_t o = 0;
     for (size_t i = 0; i < v.size(); i++) {
-        if (v[i].len == 0) continue;
-        if (o && v[o - 1].off + v[o - 1].len >= v[i].off) {
-            v[o - 1].len = std::max(v[o - 1].off + v[o - 1].len, v[i].off + v[i].len) - v[o - 1].off;
-        } else {
+        if (v[i].width == 0 || v[i].rows == 0) continue;
+        if (o && v[o - 1].rows == 1 && v[i].rows == 1 && v[o - 1].h_off + v[o - 1].width == v[i].h_off &&
+            v[o - 1].d_off + v[o - 1].width == v[i].d_off)
+            v[o - 1].width += v[i].width;
+        else
             v[o++] = v[i];
-        }
     }
     v.resize(o);
 }
 
+uint64_t align16(uint64_t x) { return (x + 15) & ~(uint64_t)15; }
+
 struct Chunk {
     uint64_t f0, f1;      // frames
     uint32_t b0, b1;      // bands
-    std::vector<Span> pix, coef;
 };
 
-void chunk_spans(const sdct_job &j, const Geometry &g, Chunk &c)
+struct Plan {             // a chunk as a dense sub-job on the device + its copies
+    sdct_job dev;
+    std::vector<Copy> pix, coef;
+    uint64_t pix_bytes = 0, coef_bytes = 0;
+};
+
+Plan plan_chunk(const sdct_job &j, const Geometry &g, const Chunk &c)
 {
-    const uint64_t row_bytes = j.width * (uint64_t)g.comps;
-    const uint64_t nb = (uint64_t)(c.b1 - c.b0);
-    for (uint64_t f = c.f0; f < c.f1; f++) {
+    Plan p;
+    const uint64_t nb = c.b1 - c.b0, frames = c.f1 - c.f0;
+    const uint64_t row_bytes = j.width * (uint64_t)g.comps, dpitch = align16(row_bytes);
+    const uint64_t n = nb * g.eyes * g.bpr;            // blocks of one coefficient set in the window
+    sdct_job &d = p.dev;
+    d = j;
+    d.eyes = (int32_t)g.eyes;
+    d.height = nb * 8;
+    d.pitch = dpitch;
+    d.eye_stride = dpitch * nb * 8;
+    d.frames = frames;
+    d.pixel_frame_stride = d.eye_stride * g.eyes;
+    d.band_begin = 0; d.band_end = nb;
+    d.coef_plane_stride = j.layout == SDCT_LAYOUT_C ? align16(n) : n;
+    d.coef_comp_stride = j.layout == SDCT_LAYOUT_C ? 64 * d.coef_plane_stride : n * 64;
+    d.coef_frame_stride = d.coef_comp_stride * g.comps;
+    p.pix_bytes = d.pixel_frame_stride * frames;
+    p.coef_bytes = d.coef_frame_stride * frames;
+    const uint64_t n0 = (uint64_t)c.b0 * g.eyes * g.bpr;
+    for (uint64_t f = 0; f < frames; f++) {
         for (uint32_t e = 0; e < g.eyes; e++)
-            c.pix.push_back({f * j.pixel_frame_stride + e * j.eye_stride + (uint64_t)c.b0 * 8 * j.pitch,
-                             nb ? (nb * 8 - 1) * j.pitch + row_bytes : 0});
-        const uint64_t n0 = (uint64_t)c.b0 * g.eyes * g.bpr, n1 = (uint64_t)c.b1 * g.eyes * g.bpr;
+            p.pix.push_back({(c.f0 + f) * j.pixel_frame_stride + e * j.eye_stride + (uint64_t)c.b0 * 8 * j.pitch,
+                             f * d.pixel_frame_stride + e * d.eye_stride, row_bytes, nb * 8, j.pitch, dpitch});
         for (uint32_t k = 0; k < g.comps; k++) {
-            const uint64_t base = f * j.coef_frame_stride + k * j.coef_comp_stride;
-            if (j.layout == SDCT_LAYOUT_C)
-                for (int i = 0; i < 64; i++) c.coef.push_back({base + i * j.coef_plane_stride + n0, n1 - n0});
-            else
-                c.coef.push_back({base + n0 * 64, (n1 - n0) * 64});
+            const uint64_t hb = (c.f0 + f) * j.coef_frame_stride + k * j.coef_comp_stride;
+            const uint64_t db = f * d.coef_frame_stride + k * d.coef_comp_stride;
+            if (j.layout == SDCT_LAYOUT_C) p.coef.push_back({hb + n0, db, n, 64, j.coef_plane_stride, d.coef_plane_stride});
+            else p.coef.push_back({hb + n0 * 64, db, n * 64, 1, 0, 0});
         }
     }
-    merge_spans(c.pix);
-    merge_spans(c.coef);
+    normalise(p.pix);
+    normalise(p.coef);
+    return p;
 }
-
-uint64_t span_bytes(const std::vector<Span> &v) { uint64_t s = 0; for (const Span &x : v) s += x.len; return s; }
 
 bool is_pinned(const void *p)
 {
@@ -85,9 +125,35 @@ int grow_pinned(uint8_t **p, size_t *cap, size_t need)
     return SDCT_OK;
 }
 
+// host <-> device copies of one chunk side, straight between the caller's (pinned) memory and the device buffer
+int copy_direct(const std::vector<Copy> &v, uint8_t *host, uint8_t *dev, bool to_device, cudaStream_t st)
+{
+    for (const Copy &c : v) {
+        uint8_t *h = host + c.h_off, *d = dev + c.d_off;
+        if (c.rows == 1) {
+            CU_TRY(to_device ? cudaMemcpyAsync(d, h, c.width, cudaMemcpyHostToDevice, st)
+                             : cudaMemcpyAsync(h, d, c.width, cudaMemcpyDeviceToHost, st));
+        } else {
+            CU_TRY(to_device ? cudaMemcpy2DAsync(d, c.d_pitch, h, c.h_pitch, c.width, c.rows, cudaMemcpyHostToDevice, st)
+                             : cudaMemcpy2DAsync(h, c.h_pitch, d, c.d_pitch, c.width, c.rows, cudaMemcpyDeviceToHost, st));
+        }
+    }
+    return SDCT_OK;
+}
+
+// pageable caller memory <-> pinned staging that has the device layout
+void stage_rows(const std::vector<Copy> &v, uint8_t *host, uint8_t *stage, bool to_stage)
+{
+    for (const Copy &c : v)
+        for (uint64_t r = 0; r < c.rows; r++) {
+            uint8_t *h = host + c.h_off + r * c.h_pitch, *s = stage + c.d_off + r * c.d_pitch;
+            if (to_stage) memcpy(s, h, c.width); else memcpy(h, s, c.width);
+        }
+}
+
 struct Pending {  // a staged D2H that still has to be scattered into pageable caller memory
     bool active = false;
-    std::vector<Span> spans;
+    std::vector<Copy> copies;
     uint8_t *dst = nullptr;
 };
 
@@ -95,14 +161,110 @@ int drain(Slot &s, Pending &p)
 {
     if (!p.active) return SDCT_OK;
     CU_TRY(cudaEventSynchronize(s.done));
-    uint64_t o = 0;
-    for (const Span &x : p.spans) { memcpy(p.dst + x.off, s.h_out + o, x.len); o += x.len; }
+    stage_rows(p.copies, p.dst, s.h_out, false);
     p.active = false;
     return SDCT_OK;
 }
 
-int host_run(sdct_context *ctx, int op, const sdct_job *job, const uint8_t *h_pixels, uint8_t *h_coefs,
-             const float *lut)
+// chunk sizes in units (frames or bands).  The first chunk's upload and the last chunk's download overlap with
+// nothing, so the sizes ramp: per/8, per/4, per/2, per, ..., per, per/2, per/4, per/8 when the job is long enough.
+std::vector<uint64_t> ramp(uint64_t total, uint64_t per, bool no_ramp)
+{
+    std::vector<uint64_t> sizes;
+    const uint64_t edge[3] = {std::max<uint64_t>(1, per / 8), std::max<uint64_t>(1, per / 4), std::max<uint64_t>(1, per / 2)};
+    const uint64_t edges = edge[0] + edge[1] + edge[2];
+    if (no_ramp || total < 2 * edges + per) {
+        for (uint64_t u = 0; u < total; u += per) sizes.push_back(std::min(per, total - u));
+        return sizes;
+    }
+    for (int i = 0; i < 3; i++) sizes.push_back(edge[i]);
+    for (uint64_t left = total - 2 * edges; left > 0;) {
+        const uint64_t n = std::min(per, left);
+        sizes.push_back(n);
+        left -= n;
+    }
+    for (int i = 2; i >= 0; i--) sizes.push_back(edge[i]);
+    return sizes;
+}
+
+int run_chunks(sdct_context *ctx, Pipeline *pipe, int op, const sdct_job *job, const Geometry &g, const uint8_t *h_pixels,
+               uint8_t *h_coefs, const float *lut)
+{
+    CU_TRY(cudaSetDevice(ctx->device));
+    int rc;
+    // ---- chunking: by frames for batches, by band ranges inside a frame otherwise ----------
+    const uint64_t band_bytes = (uint64_t)g.eyes * 8 * job->width * g.comps;
+    const uint64_t frame_bytes = band_bytes * (g.band_end - g.band_begin);
+    const uint64_t target = ctx->env.host_chunk_bytes;
+    std::vector<Chunk> chunks;
+    if (job->frames > 1 && frame_bytes <= 2 * target) {
+        const uint64_t per = std::max<uint64_t>(1, target / std::max<uint64_t>(frame_bytes, 1));
+        uint64_t f = 0;
+        for (uint64_t n : ramp(job->frames, per, ctx->env.host_no_ramp)) {
+            chunks.push_back({f, f + n, g.band_begin, g.band_end});
+            f += n;
+        }
+    } else {
+        const uint64_t per = std::max<uint64_t>(1, target / std::max<uint64_t>(band_bytes, 1));
+        const std::vector<uint64_t> sizes = ramp(g.band_end - g.band_begin, per, ctx->env.host_no_ramp);
+        for (uint64_t f = 0; f < job->frames; f++) {
+            uint32_t bnd = g.band_begin;
+            for (uint64_t n : sizes) {
+                chunks.push_back({f, f + 1, bnd, bnd + (uint32_t)n});
+                bnd += (uint32_t)n;
+            }
+        }
+    }
+
+    const bool fwd = op == SDCT_K_OP_FORWARD;
+    uint8_t *h_in = const_cast<uint8_t *>(fwd ? h_pixels : h_coefs);
+    uint8_t *h_out = fwd ? h_coefs : const_cast<uint8_t *>(h_pixels);
+    const bool in_pinned = is_pinned(h_in), out_pinned = is_pinned(h_out);
+    const int depth = ctx->env.host_slots;
+    Pending pending[kSlots];
+
+    for (size_t ci = 0; ci < chunks.size(); ci++) {
+        const Plan plan = plan_chunk(*job, g, chunks[ci]);
+        Slot &s = pipe->slots[ci % depth];
+        Pending &pd = pending[ci % depth];
+        if ((rc = drain(s, pd))) return rc;
+        if (ci >= (size_t)depth) CU_TRY(cudaEventSynchronize(s.done));  // slot buffers free again
+        if ((rc = grow_device(&s.d_pix, &s.d_pix_cap, plan.pix_bytes))) return rc;
+        if ((rc = grow_device(&s.d_coef, &s.d_coef_cap, plan.coef_bytes))) return rc;
+        const std::vector<Copy> &cin = fwd ? plan.pix : plan.coef, &cout = fwd ? plan.coef : plan.pix;
+        uint8_t *d_in = fwd ? s.d_pix : s.d_coef, *d_out = fwd ? s.d_coef : s.d_pix;
+        const uint64_t in_bytes = fwd ? plan.pix_bytes : plan.coef_bytes, out_bytes = fwd ? plan.coef_bytes : plan.pix_bytes;
+
+        // H2D
+        if (in_pinned) {
+            if ((rc = copy_direct(cin, h_in, d_in, true, s.stream))) return rc;
+        } else {
+            if ((rc = grow_pinned(&s.h_in, &s.h_in_cap, in_bytes))) return rc;
+            stage_rows(cin, h_in, s.h_in, true);
+            CU_TRY(cudaMemcpyAsync(d_in, s.h_in, in_bytes, cudaMemcpyHostToDevice, s.stream));
+        }
+        // kernel: the chunk as a dense job on the slot's buffers
+        rc = fwd ? sdct_forward_device(ctx, &plan.dev, s.d_pix, lut, s.d_coef, s.stream)
+                 : sdct_inverse_device(ctx, &plan.dev, s.d_coef, lut, s.d_pix, s.stream);
+        if (rc) return rc;
+        // D2H
+        if (out_pinned) {
+            if ((rc = copy_direct(cout, h_out, d_out, false, s.stream))) return rc;
+        } else {
+            if ((rc = grow_pinned(&s.h_out, &s.h_out_cap, out_bytes))) return rc;
+            CU_TRY(cudaMemcpyAsync(s.h_out, d_out, out_bytes, cudaMemcpyDeviceToHost, s.stream));
+            pd.active = true; pd.copies = cout; pd.dst = h_out;
+        }
+        CU_TRY(cudaEventRecord(s.done, s.stream));
+    }
+    for (int i = 0; i < kSlots; i++) {
+        if ((rc = drain(pipe->slots[i], pending[i]))) return rc;
+        if (pipe->slots[i].stream) CU_TRY(cudaStreamSynchronize(pipe->slots[i].stream));
+    }
+    return SDCT_OK;
+}
+
+int host_run(sdct_context *ctx, int op, const sdct_job *job, const uint8_t *h_pixels, uint8_t *h_coefs, const float *lut)
 {
     if (!ctx) return fail(SDCT_INVALID_PARAMETER, "context is null");
     Geometry g;
@@ -111,141 +273,107 @@ int host_run(sdct_context *ctx, int op, const sdct_job *job, const uint8_t *h_pi
     if (!h_pixels || !h_coefs) return fail(SDCT_INVALID_PARAMETER, "null buffer");
     if (!lut) return fail(SDCT_INVALID_PARAMETER, "quantisation LUT is null");
     if (job->frames == 0 || g.band_end == g.band_begin) return SDCT_OK;
-    std::lock_guard<std::mutex> lock(ctx->host_mu);
-    CU_TRY(cudaSetDevice(ctx->device));
-
-    // ---- chunking: by frames for batches, by band ranges inside a frame otherwise ----------
-    const uint64_t band_bytes = (uint64_t)g.eyes * 8 * job->width * g.comps;
-    const uint64_t frame_bytes = band_bytes * (g.band_end - g.band_begin);
-    const char *env = getenv("SDCT_HOST_CHUNK_MB");
-    const uint64_t target = (env && atoi(env) > 0 ? (uint64_t)atoi(env) : 16) << 20;
-    // The first chunk's upload and the last chunk's download overlap with nothing, so the chunk sizes ramp:
-    // per/8, per/4, per/2, per, ..., per, per/2, per/4, per/8 units (frames or bands) when the job is long enough.
-    auto ramp = [](uint64_t total, uint64_t per) {
-        std::vector<uint64_t> sizes;
-        const uint64_t edge[3] = {std::max<uint64_t>(1, per / 8), std::max<uint64_t>(1, per / 4), std::max<uint64_t>(1, per / 2)};
-        const uint64_t edges = edge[0] + edge[1] + edge[2];
-        if (getenv("SDCT_HOST_NO_RAMP") || total < 2 * edges + per) {
-            for (uint64_t u = 0; u < total; u += per) sizes.push_back(std::min(per, total - u));
-            return sizes;
-        }
-        for (int i = 0; i < 3; i++) sizes.push_back(edge[i]);
-        for (uint64_t left = total - 2 * edges; left > 0;) {
-            const uint64_t n = std::min(per, left);
-            sizes.push_back(n);
-            left -= n;
-        }
-        for (int i = 2; i >= 0; i--) sizes.push_back(edge[i]);
-        return sizes;
-    };
-    std::vector<Chunk> chunks;
-    if (job->frames > 1 && frame_bytes <= 2 * target) {
-        const uint64_t per = std::max<uint64_t>(1, target / std::max<uint64_t>(frame_bytes, 1));
-        uint64_t f = 0;
-        for (uint64_t n : ramp(job->frames, per)) {
-            Chunk c; c.f0 = f; c.f1 = f + n; c.b0 = g.band_begin; c.b1 = g.band_end;
-            chunks.push_back(std::move(c));
-            f += n;
-        }
-    } else {
-        const uint64_t per = std::max<uint64_t>(1, target / std::max<uint64_t>(band_bytes, 1));
-        const std::vector<uint64_t> sizes = ramp(g.band_end - g.band_begin, per);
-        for (uint64_t f = 0; f < job->frames; f++) {
-            uint32_t bnd = g.band_begin;
-            for (uint64_t n : sizes) {
-                Chunk c; c.f0 = f; c.f1 = f + 1; c.b0 = bnd; c.b1 = bnd + (uint32_t)n;
-                chunks.push_back(std::move(c));
-                bnd += (uint32_t)n;
-            }
-        }
+    Pipeline *pipe = sdct_acquire_pipeline(ctx);
+    if (!pipe) return SDCT_CUDA_ERROR;   // message set by sdct_acquire_pipeline
+    rc = run_chunks(ctx, pipe, op, job, g, h_pixels, h_coefs, lut);
+    if (rc) {   // leave no work of a failed call in flight on the pipeline's streams
+        for (Slot &s : pipe->slots)
+            if (s.stream) cudaStreamSynchronize(s.stream);
+        cudaGetLastError();
     }
+    sdct_release_pipeline(ctx, pipe);
+    return rc;
+}
 
-    const bool fwd = op == SDCT_K_OP_FORWARD;
-    const uint8_t *h_in = fwd ? h_pixels : h_coefs;
-    uint8_t *h_out = fwd ? h_coefs : const_cast<uint8_t *>(h_pixels);
-    const bool in_pinned = is_pinned(h_in), out_pinned = is_pinned(h_out);
-    // pipeline depth: chunks in flight ($SDCT_HOST_SLOTS for experiments)
-    const char *senv = getenv("SDCT_HOST_SLOTS");
-    const int depth = senv && atoi(senv) >= 1 && atoi(senv) <= kSlots ? atoi(senv) : 4;
-    Pending pending[kSlots];
-
-    for (size_t ci = 0; ci < chunks.size(); ci++) {
-        Chunk &c = chunks[ci];
-        chunk_spans(*job, g, c);
-        Slot &s = ctx->slots[ci % depth];
-        Pending &pd = pending[ci % depth];
-        rc = drain(s, pd);
-        if (rc) return rc;
-        if (ci >= (size_t)depth) CU_TRY(cudaEventSynchronize(s.done));  // slot buffers free again
-
-        const uint64_t plo = c.pix.front().off, phi = c.pix.back().off + c.pix.back().len;
-        const uint64_t clo = c.coef.front().off, chi = c.coef.back().off + c.coef.back().len;
-        // keep the vector-path alignment of the caller's layout: round the window start down
-        const uint64_t plo_a = plo & ~(uint64_t)15, clo_a = clo & ~(uint64_t)15;
-        if ((rc = grow_device(&s.d_pix, &s.d_pix_cap, phi - plo_a))) return rc;
-        if ((rc = grow_device(&s.d_coef, &s.d_coef_cap, chi - clo_a))) return rc;
-        const std::vector<Span> &sin = fwd ? c.pix : c.coef, &sout = fwd ? c.coef : c.pix;
-        uint8_t *d_in = fwd ? s.d_pix : s.d_coef, *d_out = fwd ? s.d_coef : s.d_pix;
-        const uint64_t in_lo = fwd ? plo_a : clo_a, out_lo = fwd ? clo_a : plo_a;
-
-        // H2D
-        if (in_pinned) {
-            for (const Span &x : sin)
-                CU_TRY(cudaMemcpyAsync(d_in + (x.off - in_lo), h_in + x.off, x.len, cudaMemcpyHostToDevice, s.stream));
-        } else {
-            if ((rc = grow_pinned(&s.h_in, &s.h_in_cap, span_bytes(sin)))) return rc;
-            uint64_t o = 0;
-            for (const Span &x : sin) {
-                memcpy(s.h_in + o, h_in + x.off, x.len);
-                CU_TRY(cudaMemcpyAsync(d_in + (x.off - in_lo), s.h_in + o, x.len, cudaMemcpyHostToDevice, s.stream));
-                o += x.len;
+// one call over several devices: contiguous frame ranges (batches) or band ranges (one large frame) per device,
+// each on its own host thread and pipeline; no inter-device exchange (blocks are independent)
+int host_run_multi(sdct_context *const *ctxs, int n, int op, const sdct_job *job, const uint8_t *h_pixels, uint8_t *h_coefs,
+                   const float *lut)
+{
+    if (!ctxs || n < 1) return fail(SDCT_INVALID_PARAMETER, "no contexts");
+    for (int i = 0; i < n; i++)
+        if (!ctxs[i]) return fail(SDCT_INVALID_PARAMETER, "context %d is null", i);
+    if (n == 1) return host_run(ctxs[0], op, job, h_pixels, h_coefs, lut);
+    Geometry g;
+    int rc = sdct_validate(job, &g);
+    if (rc) return rc;
+    if (!h_pixels || !h_coefs) return fail(SDCT_INVALID_PARAMETER, "null buffer");
+    if (!lut) return fail(SDCT_INVALID_PARAMETER, "quantisation LUT is null");
+    const bool by_frames = job->frames >= (uint64_t)n;
+    const uint64_t total = by_frames ? job->frames : (uint64_t)(g.band_end - g.band_begin);
+    std::vector<int> rcs(n, SDCT_OK);
+    std::vector<std::string> msgs(n);
+    std::vector<std::thread> threads;
+    for (int i = 0; i < n; i++) {
+        uint64_t b, e;
+        sdct_shard_range(total, i, n, &b, &e);
+        if (e == b) continue;
+        threads.emplace_back([=, &rcs, &msgs]() {
+            sdct_job sub = *job;
+            const uint8_t *px = h_pixels;
+            uint8_t *cf = h_coefs;
+            if (by_frames) {
+                sub.frames = e - b;
+                px += b * job->pixel_frame_stride;
+                cf += b * job->coef_frame_stride;
+            } else {   // base pointers stay those of the whole image: a band's output position does not depend on the window
+                sub.band_begin = g.band_begin + b;
+                sub.band_end = g.band_begin + e;
             }
-        }
-        // kernel on this chunk's window of the caller's layout
-        sdct_job sub = *job;
-        sub.frames = c.f1 - c.f0;
-        sub.band_begin = c.b0; sub.band_end = c.b1;
-        const uint8_t *kp = s.d_pix - plo_a + c.f0 * job->pixel_frame_stride;
-        uint8_t *kc = s.d_coef - clo_a + c.f0 * job->coef_frame_stride;
-        rc = fwd ? sdct_forward_device(ctx, &sub, kp, lut, kc, s.stream)
-                 : sdct_inverse_device(ctx, &sub, kc, lut, const_cast<uint8_t *>(kp), s.stream);
-        if (rc) return rc;
-        // D2H
-        if (out_pinned) {
-            for (const Span &x : sout)
-                CU_TRY(cudaMemcpyAsync(h_out + x.off, d_out + (x.off - out_lo), x.len, cudaMemcpyDeviceToHost, s.stream));
-        } else {
-            if ((rc = grow_pinned(&s.h_out, &s.h_out_cap, span_bytes(sout)))) return rc;
-            uint64_t o = 0;
-            for (const Span &x : sout) {
-                CU_TRY(cudaMemcpyAsync(s.h_out + o, d_out + (x.off - out_lo), x.len, cudaMemcpyDeviceToHost, s.stream));
-                o += x.len;
-            }
-            pd.active = true; pd.spans = sout; pd.dst = h_out;
-        }
-        CU_TRY(cudaEventRecord(s.done, s.stream));
+            rcs[i] = host_run(ctxs[i], op, &sub, px, cf, lut);
+            if (rcs[i]) msgs[i] = sdct_last_error();
+        });
     }
-    for (int i = 0; i < kSlots; i++) {
-        if ((rc = drain(ctx->slots[i], pending[i]))) return rc;
-        CU_TRY(cudaStreamSynchronize(ctx->slots[i].stream));
-    }
+    for (std::thread &t : threads) t.join();
+    for (int i = 0; i < n; i++)
+        if (rcs[i]) return fail(rcs[i], "device %d: %s", ctxs[i]->device, msgs[i].c_str());
     return SDCT_OK;
 }
 
-// ---- process-wide context for the reference-style calls -----------------------------------
+// ---- process-wide contexts for the reference-style calls -----------------------------------
+// $SDCT_DEVICES = "all" or a comma-separated list: the call is sharded over those devices (one process, no
+// collective); otherwise the single device $SDCT_DEVICE (default 0).
 std::mutex g_mu;
-sdct_context *g_ctx = nullptr;
+std::vector<sdct_context *> g_ctxs;
 std::atomic<int> g_ref_flags{SDCT_EXACT | SDCT_QUIRK_AVX_X3};
 
-int global_context(sdct_context **out)
+int global_contexts(std::vector<sdct_context *> *out)
 {
     std::lock_guard<std::mutex> lock(g_mu);
-    if (!g_ctx) {
-        const char *env = getenv("SDCT_DEVICE");
-        int rc = sdct_create(env ? atoi(env) : 0, &g_ctx);
-        if (rc) return rc;
+    if (g_ctxs.empty()) {
+        std::vector<int> devs;
+        const char *list = getenv("SDCT_DEVICES");
+        if (list && *list) {
+            if (!strcmp(list, "all")) {
+                const int n = sdct_device_count();
+                for (int i = 0; i < n; i++) devs.push_back(i);
+            } else {
+                for (const char *p = list; *p;) {
+                    char *end;
+                    const long d = strtol(p, &end, 10);
+                    if (end == p) break;
+                    devs.push_back((int)d);
+                    p = *end == ',' ? end + 1 : end;
+                }
+            }
+        }
+        if (devs.empty()) {
+            const char *env = getenv("SDCT_DEVICE");
+            devs.push_back(env ? atoi(env) : 0);
+        }
+        std::vector<sdct_context *> made;
+        for (int d : devs) {
+            sdct_context *c = nullptr;
+            const int rc = sdct_create(d, &c);
+            if (rc) {
+                for (sdct_context *m : made) sdct_destroy(m);
+                return rc;
+            }
+            made.push_back(c);
+        }
+        g_ctxs = made;
     }
-    *out = g_ctx;
+    *out = g_ctxs;
     return SDCT_OK;
 }
 
@@ -267,8 +395,8 @@ int ref_call(int layout, const uint8_t *from, uint8_t *to, const float *lut, siz
     const size_t b0 = (start_y + step - 1) / step;
     const size_t b1 = std::min(bands, end_y / step + 1);
     if (b0 >= b1) return SDCT_OK;
-    sdct_context *ctx;
-    int rc = global_context(&ctx);
+    std::vector<sdct_context *> ctxs;
+    int rc = global_contexts(&ctxs);
     if (rc) return rc;
     sdct_job j;
     const int eyes = layout == SDCT_LAYOUT_C ? 2 : 1;
@@ -278,10 +406,53 @@ int ref_call(int layout, const uint8_t *from, uint8_t *to, const float *lut, siz
         j.coef_plane_stride = sx * sy / 64;           // :257
     }
     j.band_begin = b0; j.band_end = b1;
-    return host_run(ctx, SDCT_K_OP_FORWARD, &j, from, to, lut);
+    return host_run_multi(ctxs.data(), (int)ctxs.size(), SDCT_K_OP_FORWARD, &j, from, to, lut);
 }
 
 }  // namespace
+
+// ---- pipeline pool ----------------------------------------------------------------------------
+Pipeline *sdct_acquire_pipeline(sdct_context *ctx)
+{
+    {
+        std::lock_guard<std::mutex> lock(ctx->pipes_mu);
+        for (auto &p : ctx->pipes)
+            if (!p->busy) { p->busy = true; return p.get(); }
+    }
+    if (cudaSetDevice(ctx->device) != cudaSuccess) { fail(SDCT_CUDA_ERROR, "cudaSetDevice(%d) failed", ctx->device); return nullptr; }
+    std::unique_ptr<Pipeline> p(new Pipeline());
+    p->busy = true;
+    for (Slot &s : p->slots) {
+        cudaError_t e = cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking);
+        if (e == cudaSuccess) e = cudaEventCreateWithFlags(&s.done, cudaEventDisableTiming);
+        if (e != cudaSuccess) {
+            fail(SDCT_CUDA_ERROR, "creating a host pipeline failed: %s", cudaGetErrorString(e));
+            sdct_destroy_pipeline(p.get());
+            return nullptr;
+        }
+    }
+    std::lock_guard<std::mutex> lock(ctx->pipes_mu);
+    ctx->pipes.push_back(std::move(p));
+    return ctx->pipes.back().get();
+}
+
+void sdct_release_pipeline(sdct_context *ctx, Pipeline *p)
+{
+    std::lock_guard<std::mutex> lock(ctx->pipes_mu);
+    p->busy = false;
+}
+
+void sdct_destroy_pipeline(Pipeline *p)
+{
+    for (Slot &s : p->slots) {
+        if (s.stream) { cudaStreamSynchronize(s.stream); cudaStreamDestroy(s.stream); s.stream = nullptr; }
+        if (s.done) { cudaEventDestroy(s.done); s.done = nullptr; }
+        cudaFree(s.d_pix); cudaFree(s.d_coef);
+        cudaFreeHost(s.h_in); cudaFreeHost(s.h_out);
+        s.d_pix = s.d_coef = s.h_in = s.h_out = nullptr;
+        s.d_pix_cap = s.d_coef_cap = s.h_in_cap = s.h_out_cap = 0;
+    }
+}
 
 extern "C" {
 
@@ -293,6 +464,16 @@ int sdct_forward_host(sdct_context *c, const sdct_job *j, const void *h_pixels, 
 int sdct_inverse_host(sdct_context *c, const sdct_job *j, const void *h_coefs, const float *lut, void *h_pixels)
 {
     return host_run(c, SDCT_K_OP_INVERSE, j, (const uint8_t *)h_pixels, (uint8_t *)const_cast<void *>(h_coefs), lut);
+}
+
+int sdct_forward_host_multi(sdct_context *const *ctxs, int n, const sdct_job *j, const void *h_pixels, const float *lut, void *h_coefs)
+{
+    return host_run_multi(ctxs, n, SDCT_K_OP_FORWARD, j, (const uint8_t *)h_pixels, (uint8_t *)h_coefs, lut);
+}
+
+int sdct_inverse_host_multi(sdct_context *const *ctxs, int n, const sdct_job *j, const void *h_coefs, const float *lut, void *h_pixels)
+{
+    return host_run_multi(ctxs, n, SDCT_K_OP_INVERSE, j, (const uint8_t *)h_pixels, (uint8_t *)const_cast<void *>(h_coefs), lut);
 }
 
 int sdct_ref_encode_quantize_buffer(const uint8_t *from, uint8_t *to, const float *lut, size_t sx, size_t sy,
@@ -315,5 +496,10 @@ int sdct_ref_encode_quantize32_reorder_buffer(const uint8_t *from, uint8_t *to, 
 
 void sdct_ref_set_flags(int flags) { g_ref_flags.store(flags); }
 int sdct_ref_get_flags(void) { return g_ref_flags.load(); }
+int sdct_ref_device_count(void)
+{
+    std::vector<sdct_context *> ctxs;
+    return global_contexts(&ctxs) == SDCT_OK ? (int)ctxs.size() : 0;
+}
 
 }  // extern "C"

@@ -6,7 +6,9 @@
 #include <atomic>
 #include <cstdarg>
 #include <cstdio>
+#include <memory>
 #include <mutex>
+#include <vector>
 
 int sdct_fail(int code, const char *fmt, ...);
 #define fail sdct_fail
@@ -19,36 +21,60 @@ int sdct_fail(int code, const char *fmt, ...);
                         __FILE__, __LINE__);                                                      \
     } while (0)
 
-constexpr int kSlots = 8;  // slots of the host path; the pipeline depth in use is host_depth() <= kSlots
+constexpr int kSlots = 8;  // slots of one host pipeline; the depth in use is SdctEnv::host_slots <= kSlots
 
+// one in-flight chunk of the host path: its stream, the device buffers of the chunk's dense sub-job and the
+// pinned staging buffers used when the caller's memory is pageable
 struct Slot {
     cudaStream_t stream = nullptr;
     cudaEvent_t done = nullptr;
     uint8_t *d_pix = nullptr, *d_coef = nullptr;
     size_t d_pix_cap = 0, d_coef_cap = 0;
-    uint8_t *h_in = nullptr, *h_out = nullptr;  // pinned staging for pageable callers
+    uint8_t *h_in = nullptr, *h_out = nullptr;
     size_t h_in_cap = 0, h_out_cap = 0;
+};
+
+// A host-buffer call owns one Pipeline from the context's pool for its duration, so that N caller threads
+// (the reference's concurrency model: disjoint startY/endY windows, src/simd_dct.cpp:1073-1087) overlap.
+struct Pipeline {
+    Slot slots[kSlots];
+    bool busy = false;
+};
+
+// $SDCT_* switches, read ONCE per context in sdct_create (no getenv on any launch path)
+struct SdctEnv {
+    uint64_t host_chunk_bytes = 16ull << 20;
+    int host_slots = 4;
+    bool host_no_ramp = false;
+    SdctTcOptions tc;
 };
 
 struct sdct_context {
     int device = 0;
     int sm_count = 0;
     cudaStream_t stream = nullptr;
-    Slot slots[kSlots];
+    SdctEnv env;
     std::atomic<uint64_t> launches{0};
-    std::mutex host_mu;  // the host pipeline owns the slots
+    std::mutex pipes_mu;   // guards the pool only; a call runs on its own pipeline without the lock
+    std::vector<std::unique_ptr<Pipeline>> pipes;
     void *d_tc_matrix[2] = {nullptr, nullptr};  // tensor-core B operand: [0] layout-A column order, [1] natural order
-    // tensor-core inverse operands depend on the LUT: a small cache keyed by (layout, LUT)
-    struct InvOperand { void *d = nullptr; int layout = -1; float lut[64]; float off_cols[64]; int S = 0; };
-    InvOperand inv_cache[4];
-    unsigned inv_next = 0;
+    // tensor-core inverse operands depend on the LUT: a small cache keyed by (layout, LUT).  An entry is uploaded
+    // synchronously before its key becomes visible and is only overwritten after a device synchronise.
+    struct InvOperand { void *d = nullptr; int layout = -1; float lut[64]; float off_cols[64]; int S = 0; uint64_t used = 0; };
+    InvOperand inv_cache[8];
+    uint64_t inv_clock = 0;
     std::mutex inv_mu;
+    SdctTcMapCache tc_maps;   // encoded CUtensorMaps keyed by (pointer, geometry); guarded by its own mutex
+    std::mutex tc_maps_mu;
 };
 
 struct Geometry {
     uint32_t bpr, bands_total, band_begin, band_end, eyes, comps;
 };
 int sdct_validate(const sdct_job *j, Geometry *g);
+Pipeline *sdct_acquire_pipeline(sdct_context *ctx);
+void sdct_release_pipeline(sdct_context *ctx, Pipeline *p);
+void sdct_destroy_pipeline(Pipeline *p);
 
 // tensor-core form: K[c][p] = round(2^22 * C[u][y] * C[v][x]), c = u*8+v, p = y*8+x (sdct_tc_matrix.cpp)
 void sdct_tc_integer_matrix(int32_t K[64 * 64]);

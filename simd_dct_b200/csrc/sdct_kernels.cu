@@ -14,11 +14,16 @@
 #include "sdct_math.cuh"
 #include "sdct_io.cuh"
 
+#include <atomic>
+
 // This file is compiled once per SDCT_PART (simd_dct_b200/build.py) so that the template
 // instantiations build in parallel: part 0 = dispatcher + self-test kernel, parts 1..8 = one
 // (operation, layout / mode) family each.
 #ifndef SDCT_CONV_MAGIC
 #define SDCT_CONV_MAGIC 0
+#endif
+#ifndef SDCT_CONV_FOLD
+#define SDCT_CONV_FOLD 1
 #endif
 #ifndef SDCT_PART
 #error "compile with -DSDCT_PART=<0..8>"
@@ -128,21 +133,35 @@ SDCT_DEV constexpr bool complemented() { return MODE == SDCT_K_FAST || LAYOUT ==
 template <int LAYOUT, int MODE, bool X3>
 SDCT_DEV void forward_pair(const uint32_t wp[16], const uint32_t wq[16], const float2 *tab, F2 b[64])
 {
+    // FAST (every layout) and EXACT layout B transform the raw pixel values, rows first: the conversion is folded
+    // into the first butterfly stage of the row pass (stage1_pixels, sdct_math.cuh) - no I2F, no extra FMA-pipe op
+    constexpr bool FOLD = SDCT_CONV_FOLD && (MODE == SDCT_K_FAST || LAYOUT == SDCT_K_LAYOUT_B);
+    if (FOLD) {
 #pragma unroll
-    for (int i = 0; i < 64; i++) {
+        for (int r = 0; r < 8; r++) {
+            const Stage1 a = stage1_pixels(wp[2 * r], wp[2 * r + 1], wq[2 * r], wq[2 * r + 1]);
+            if (MODE == SDCT_K_FAST) dct8_fast_tail<1>(a, b + 8 * r);
+            else dct8_paired_tail<1, X3>(a, b + 8 * r);
+        }
+    } else {
+#pragma unroll
+        for (int i = 0; i < 64; i++) {
 #if SDCT_CONV_MAGIC
-        // 2^23 + byte assembled by PRMT (ALU pipe), minus 2^23 (exact) on the FMA pipe: no XU conversion
-        const uint32_t sel = 0x7540u | (uint32_t)(i & 3);
-        const F2 m = make_float2(__uint_as_float(__byte_perm(wp[i >> 2], 0x4B000000u, sel)), __uint_as_float(__byte_perm(wq[i >> 2], 0x4B000000u, sel)));
-        const F2 x = sub2(m, splat(8388608.f));
+            // 2^23 + byte assembled by PRMT (ALU pipe), minus 2^23 (exact) on the FMA pipe: no XU conversion
+            const uint32_t sel = 0x7540u | (uint32_t)(i & 3);
+            const F2 m = make_float2(__uint_as_float(__byte_perm(wp[i >> 2], 0x4B000000u, sel)), __uint_as_float(__byte_perm(wq[i >> 2], 0x4B000000u, sel)));
+            const F2 x = sub2(m, splat(8388608.f));
 #else
-        const F2 x = make_float2(byte_to_float(wp[i >> 2], i & 3), byte_to_float(wq[i >> 2], i & 3));
+            const F2 x = make_float2(byte_to_float(wp[i >> 2], i & 3), byte_to_float(wq[i >> 2], i & 3));
 #endif
-        b[i] = (MODE == SDCT_K_EXACT && LAYOUT != SDCT_K_LAYOUT_B) ? div255(x) : x;
+            b[i] = (MODE == SDCT_K_EXACT && LAYOUT != SDCT_K_LAYOUT_B) ? div255(x) : x;
+        }
     }
     if (MODE == SDCT_K_FAST) {
+        if (!FOLD) {
 #pragma unroll
-        for (int r = 0; r < 8; r++) dct8_fast<1>(b + 8 * r);
+            for (int r = 0; r < 8; r++) dct8_fast<1>(b + 8 * r);
+        }
 #pragma unroll
         for (int c = 0; c < 8; c++) dct8_fast<8>(b + c);
     } else if (LAYOUT == SDCT_K_LAYOUT_A) {  // rows, then columns (:343-358)
@@ -156,8 +175,10 @@ SDCT_DEV void forward_pair(const uint32_t wp[16], const uint32_t wq[16], const f
 #pragma unroll
         for (int r = 0; r < 8; r++) dct8_scalar<1, true>(b + 8 * r);
     } else {                                 // layout B: rows, then columns (:2158-2215)
+        if (!FOLD) {
 #pragma unroll
-        for (int r = 0; r < 8; r++) dct8_paired<1, false, X3>(b + 8 * r);
+            for (int r = 0; r < 8; r++) dct8_paired<1, false, X3>(b + 8 * r);
+        }
 #pragma unroll
         for (int c = 0; c < 8; c++) dct8_paired<8, true, X3>(b + c);
     }
@@ -626,6 +647,15 @@ __global__ void dct8_selftest_kernel(float *data, uint32_t n, int kind)
 // ---- launchers ------------------------------------------------------------------------------------
 using namespace sdct;
 
+// cudaFuncSetAttribute belongs to the current device's context, not to the process: one flag bit per device
+static inline bool attr_pending(std::atomic<uint64_t> &done, uint64_t *bit)
+{
+    int dev = 0;
+    cudaGetDevice(&dev);
+    *bit = 1ull << (dev & 63);
+    return !(done.load(std::memory_order_acquire) & *bit);
+}
+
 typedef cudaError_t (*part_fn)(int op, int x3, const KParams &p, unsigned grid, cudaStream_t s);
 #define SDCT_DECL(name) cudaError_t name(int op, int x3, const KParams &p, unsigned grid, cudaStream_t s)
 SDCT_DECL(sdct_part_exact_a); SDCT_DECL(sdct_part_exact_b); SDCT_DECL(sdct_part_exact_c);
@@ -639,11 +669,12 @@ static cudaError_t launch_fwd2(int op, const KParams &p, unsigned grid, cudaStre
     do {                                                                                              \
         const size_t smem = (op == SDCT_K_OP_FORWARD ? 2 * STAGE_BYTES : 0) +                         \
                             (prefetchable<C, V>() ? 2 * IN_STAGE_BYTES : 0);                          \
-        static bool attr_done = false;                                                                \
-        if (!attr_done) {                                                                             \
+        static std::atomic<uint64_t> attr_done{0};                                                    \
+        uint64_t bit;                                                                                 \
+        if (attr_pending(attr_done, &bit)) {                                                          \
             cudaError_t e = cudaFuncSetAttribute(K<LAYOUT, MODE, X3, C, V>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
             if (e != cudaSuccess) return e;                                                           \
-            attr_done = true;                                                                         \
+            attr_done.fetch_or(bit, std::memory_order_release);                                       \
         }                                                                                             \
         K<LAYOUT, MODE, X3, C, V><<<grid, SDCT_TB, smem, s>>>(p);                                     \
         return cudaGetLastError();                                                                    \
@@ -670,11 +701,12 @@ static cudaError_t launch_inv2(const KParams &p, unsigned grid, cudaStream_t s)
     const size_t smem = 2 * STAGE_BYTES;
 #define SDCT_INV(C, V)                                                                                                   \
     do {                                                                                                                 \
-        static bool attr_done = false;                                                                                   \
-        if (!attr_done) {                                                                                                \
+        static std::atomic<uint64_t> attr_done{0};                                                                       \
+        uint64_t bit;                                                                                                    \
+        if (attr_pending(attr_done, &bit)) {                                                                             \
             cudaError_t e = cudaFuncSetAttribute(inverse_kernel<LAYOUT, C, V>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
             if (e != cudaSuccess) return e;                                                                              \
-            attr_done = true;                                                                                            \
+            attr_done.fetch_or(bit, std::memory_order_release);                                                          \
         }                                                                                                                \
         inverse_kernel<LAYOUT, C, V><<<grid, SDCT_TB, smem, s>>>(p);                                                     \
         return cudaGetLastError();                                                                                       \

@@ -53,8 +53,26 @@ struct KParams {
 };
 
 extern "C" cudaError_t sdct_k_launch(int op, int layout, int mode, int x3, const KParams *p, cudaStream_t s);
-// tensor-core form (sdct_tc.cu); p->tab holds the folded scales in D-column order
-extern "C" cudaError_t sdct_k_launch_tc(int op, int layout, const KParams *p, cudaStream_t s);
+
+// switches of the tensor-core launcher (the context reads $SDCT_TC_* once, in sdct_create)
+struct SdctTcOptions {
+    bool no_tma = false;         // $SDCT_TC_NO_TMA: thread-copy paths instead of tensor maps
+    bool no_rgb_fuse = false;    // $SDCT_TC_NO_RGB_FUSE
+    bool no_tma_store = false;   // $SDCT_TC_NO_TMA_STORE
+    uint32_t ablate = 0;         // $SDCT_TC_ABLATE (profiling builds only)
+};
+// encoded CUtensorMaps, keyed by (base pointer, dimensions, strides): cuTensorMapEncodeTiled runs once per
+// distinct buffer geometry instead of once or twice per launch
+struct SdctTcMapCache {
+    struct Entry { const void *base; uint64_t dims[4], strides[3]; uint32_t kind; bool ok; uint64_t used; unsigned char map[128]; };
+    static constexpr int N = 16;
+    Entry e[N];
+    int n = 0;
+    uint64_t clock = 0, hits = 0, misses = 0;
+};
+// tensor-core form (sdct_tc.cu); p->tab holds the folded scales in D-column order.  `maps` may be null (no caching);
+// the caller serialises access to it.
+extern "C" cudaError_t sdct_k_launch_tc(int op, int layout, const KParams *p, const SdctTcOptions *opt, SdctTcMapCache *maps, cudaStream_t s);
 // D column j of the tensor-core kernels -> coefficient position in the layout's own index order
 static inline int sdct_tc_column_position(int layout, int j)
 {

@@ -105,37 +105,80 @@ SDCT_DEV void dct8_scalar(F2 *v)
     v[7 * S] = mulx<true>(sadd<true>(sadd<true>(sadd<true>(mulx<true>(d07, SDCT_KF), mulx<true>(d61, SDCT_KD)), mulx<true>(d25, SDCT_KC)), mulx<true>(d43, SDCT_KA)), SDCT_KN);
 }
 
-// ---- 8-point forward, reference AVX2 lane order (:2160-2183); X3 = true keeps :2181's sign -----
-template <int S, bool PROD_IN, bool X3>
-SDCT_DEV void dct8_paired(F2 *v)
+// first butterfly stage of every forward graph (:148-155 / :2160-2167): exact whenever the inputs are integers
+struct Stage1 { F2 s07, s16, s25, s34, d07, d61, d25, d43; };
+
+template <int S, bool PROD_IN, bool FP>
+SDCT_DEV Stage1 stage1_of(const F2 *v)
 {
-    const F2 s07 = add_in<PROD_IN, false>(v[0], v[7 * S]), s16 = add_in<PROD_IN, false>(v[S], v[6 * S]);
-    const F2 s25 = add_in<PROD_IN, false>(v[2 * S], v[5 * S]), s34 = add_in<PROD_IN, false>(v[3 * S], v[4 * S]);
-    const F2 d07 = sub_in<PROD_IN, false>(v[0], v[7 * S]), d61 = sub_in<PROD_IN, false>(v[6 * S], v[S]);
-    const F2 d25 = sub_in<PROD_IN, false>(v[2 * S], v[5 * S]), d43 = sub_in<PROD_IN, false>(v[4 * S], v[3 * S]);
+    Stage1 a;
+    a.s07 = add_in<PROD_IN, FP>(v[0], v[7 * S]); a.s16 = add_in<PROD_IN, FP>(v[S], v[6 * S]);
+    a.s25 = add_in<PROD_IN, FP>(v[2 * S], v[5 * S]); a.s34 = add_in<PROD_IN, FP>(v[3 * S], v[4 * S]);
+    a.d07 = sub_in<PROD_IN, FP>(v[0], v[7 * S]); a.d61 = sub_in<PROD_IN, FP>(v[6 * S], v[S]);
+    a.d25 = sub_in<PROD_IN, FP>(v[2 * S], v[5 * S]); a.d43 = sub_in<PROD_IN, FP>(v[4 * S], v[3 * S]);
+    return a;
+}
+
+// The same stage straight from the pixel bytes of one row of the blocks P and Q (words p0 = x0..x3, p1 = x4..x7),
+// with the u8 -> f32 conversion folded into it: PRMT builds the float 2^23 + x from a byte (ALU pipe), an integer
+// subtract turns its bits into those of x - 2^23 (bits = 0xCB000000 - 2x), and
+//     (2^23 + a) + (b - 2^23) = a + b,      (2^23 + a) - (2^23 + b) = a - b
+// are exact fp32 operations with exactly representable results - the sums and differences the reference computes
+// from (float)x (:2107-2151, :2160-2167), bit for bit, with no conversion instruction (XU pipe: 1 I2F per 8 clk per
+// scheduler) and no extra FMA-pipe operation.
+SDCT_DEV F2 magic_plus(uint32_t wp, uint32_t wq, int k)
+{
+    const uint32_t sel = 0x7540u | (uint32_t)k;
+    return make_float2(__uint_as_float(__byte_perm(wp, 0x4B000000u, sel)), __uint_as_float(__byte_perm(wq, 0x4B000000u, sel)));
+}
+SDCT_DEV F2 magic_minus(F2 m)   // bits of (x - 2^23) from the bits of (2^23 + x)
+{
+    const uint32_t a = __float_as_uint(m.x), b = __float_as_uint(m.y);
+    return make_float2(__uint_as_float((0x61000000u - a) - a), __uint_as_float((0x61000000u - b) - b));
+}
+SDCT_DEV Stage1 stage1_pixels(uint32_t p0, uint32_t p1, uint32_t q0, uint32_t q1)
+{
+    const F2 m0 = magic_plus(p0, q0, 0), m1 = magic_plus(p0, q0, 1), m2 = magic_plus(p0, q0, 2), m3 = magic_plus(p0, q0, 3);
+    const F2 m4 = magic_plus(p1, q1, 0), m5 = magic_plus(p1, q1, 1), m6 = magic_plus(p1, q1, 2), m7 = magic_plus(p1, q1, 3);
+    Stage1 a;
+    a.s07 = add2(m0, magic_minus(m7)); a.s16 = add2(m1, magic_minus(m6));
+    a.s25 = add2(m2, magic_minus(m5)); a.s34 = add2(m3, magic_minus(m4));
+    a.d07 = sub2(m0, m7); a.d61 = sub2(m6, m1); a.d25 = sub2(m2, m5); a.d43 = sub2(m4, m3);
+    return a;
+}
+
+// ---- 8-point forward, reference AVX2 lane order (:2160-2183); X3 = true keeps :2181's sign -----
+// how the AVX-order graph keeps its products out of FFMA2 contraction (see mulx): measured per build
+#ifndef SDCT_PAIRED_FP
+#define SDCT_PAIRED_FP 0
+#endif
+constexpr bool PFP = SDCT_PAIRED_FP;
+template <int S, bool X3>
+SDCT_DEV void dct8_paired_tail(const Stage1 &a, F2 *v)
+{
+    const F2 s07 = a.s07, s16 = a.s16, s25 = a.s25, s34 = a.s34, d07 = a.d07, d61 = a.d61, d25 = a.d25, d43 = a.d43;
     const F2 pp = add2(s07, s34), pm = sub2(s07, s34), qq = add2(s16, s25), qm = sub2(s16, s25);
 
-    v[0] = mulx<false>(add2(pp, qq), SDCT_KN);
-    v[4 * S] = mulx<false>(sub2(pp, qq), SDCT_KN);
-    v[2 * S] = mulx<false>(sadd<false>(mulx<false>(pm, SDCT_KB), mulx<false>(qm, SDCT_KE)), SDCT_KN);
-    v[6 * S] = mulx<false>(ssub<false>(mulx<false>(pm, SDCT_KE), mulx<false>(qm, SDCT_KB)), SDCT_KN);
+    v[0] = mulx<PFP>(add2(pp, qq), SDCT_KN);
+    v[4 * S] = mulx<PFP>(sub2(pp, qq), SDCT_KN);
+    v[2 * S] = mulx<PFP>(sadd<PFP>(mulx<PFP>(pm, SDCT_KB), mulx<PFP>(qm, SDCT_KE)), SDCT_KN);
+    v[6 * S] = mulx<PFP>(ssub<PFP>(mulx<PFP>(pm, SDCT_KE), mulx<PFP>(qm, SDCT_KB)), SDCT_KN);
     // odd outputs, pairwise: (t0 op t1) op (t2 op t3); the outer add sees two sums -> packed
-    v[S] = mulx<false>(add2(ssub<false>(mulx<false>(d07, SDCT_KA), mulx<false>(d61, SDCT_KC)), ssub<false>(mulx<false>(d25, SDCT_KD), mulx<false>(d43, SDCT_KF))), SDCT_KN);
-    const F2 x3r = X3 ? sadd<false>(mulx<false>(d25, SDCT_KA), mulx<false>(d43, SDCT_KD)) : ssub<false>(mulx<false>(d25, SDCT_KA), mulx<false>(d43, SDCT_KD));
-    v[3 * S] = mulx<false>(sub2(sadd<false>(mulx<false>(d07, SDCT_KC), mulx<false>(d61, SDCT_KF)), x3r), SDCT_KN);
-    v[5 * S] = mulx<false>(add2(sadd<false>(mulx<false>(d07, SDCT_KD), mulx<false>(d61, SDCT_KA)), ssub<false>(mulx<false>(d25, SDCT_KF), mulx<false>(d43, SDCT_KC))), SDCT_KN);
-    v[7 * S] = mulx<false>(add2(sadd<false>(mulx<false>(d07, SDCT_KF), mulx<false>(d61, SDCT_KD)), sadd<false>(mulx<false>(d25, SDCT_KC), mulx<false>(d43, SDCT_KA))), SDCT_KN);
+    v[S] = mulx<PFP>(add2(ssub<PFP>(mulx<PFP>(d07, SDCT_KA), mulx<PFP>(d61, SDCT_KC)), ssub<PFP>(mulx<PFP>(d25, SDCT_KD), mulx<PFP>(d43, SDCT_KF))), SDCT_KN);
+    const F2 x3r = X3 ? sadd<PFP>(mulx<PFP>(d25, SDCT_KA), mulx<PFP>(d43, SDCT_KD)) : ssub<PFP>(mulx<PFP>(d25, SDCT_KA), mulx<PFP>(d43, SDCT_KD));
+    v[3 * S] = mulx<PFP>(sub2(sadd<PFP>(mulx<PFP>(d07, SDCT_KC), mulx<PFP>(d61, SDCT_KF)), x3r), SDCT_KN);
+    v[5 * S] = mulx<PFP>(add2(sadd<PFP>(mulx<PFP>(d07, SDCT_KD), mulx<PFP>(d61, SDCT_KA)), ssub<PFP>(mulx<PFP>(d25, SDCT_KF), mulx<PFP>(d43, SDCT_KC))), SDCT_KN);
+    v[7 * S] = mulx<PFP>(add2(sadd<PFP>(mulx<PFP>(d07, SDCT_KF), mulx<PFP>(d61, SDCT_KD)), sadd<PFP>(mulx<PFP>(d25, SDCT_KC), mulx<PFP>(d43, SDCT_KA))), SDCT_KN);
 }
+template <int S, bool PROD_IN, bool X3>
+SDCT_DEV void dct8_paired(F2 *v) { dct8_paired_tail<S, X3>(stage1_of<S, PROD_IN, PFP>(v), v); }
 
 // ---- 8-point forward, FAST (oracle/sdct_oracle.c: sdct_oracle_dct8_fast), unnormalised ---------
 // explicit FMAs; no multiply feeds a plain add, so there is nothing left for ptxas to contract
 template <int S>
-SDCT_DEV void dct8_fast(F2 *v)
+SDCT_DEV void dct8_fast_tail(const Stage1 &a, F2 *v)
 {
-    const F2 s07 = add2(v[0], v[7 * S]), s16 = add2(v[S], v[6 * S]);
-    const F2 s25 = add2(v[2 * S], v[5 * S]), s34 = add2(v[3 * S], v[4 * S]);
-    const F2 d07 = sub2(v[0], v[7 * S]), d61 = sub2(v[6 * S], v[S]);
-    const F2 d25 = sub2(v[2 * S], v[5 * S]), d43 = sub2(v[4 * S], v[3 * S]);
+    const F2 s07 = a.s07, s16 = a.s16, s25 = a.s25, s34 = a.s34, d07 = a.d07, d61 = a.d61, d25 = a.d25, d43 = a.d43;
     const F2 pp = add2(s07, s34), pm = sub2(s07, s34), qq = add2(s16, s25), qm = sub2(s16, s25);
 
     v[0] = add2(pp, qq);
@@ -147,6 +190,8 @@ SDCT_DEV void dct8_fast(F2 *v)
     v[5 * S] = fmak(-SDCT_KC, d43, fmak(SDCT_KF, d25, fmak(SDCT_KA, d61, mulk(d07, SDCT_KD))));
     v[7 * S] = fmak(SDCT_KA, d43, fmak(SDCT_KC, d25, fmak(SDCT_KD, d61, mulk(d07, SDCT_KF))));
 }
+template <int S>
+SDCT_DEV void dct8_fast(F2 *v) { dct8_fast_tail<S>(stage1_of<S, false, true>(v), v); }
 
 // ---- 8-point inverse (oracle/sdct_oracle.c: sdct_oracle_idct8), unnormalised -------------------
 template <int S>

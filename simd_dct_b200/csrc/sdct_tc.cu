@@ -30,6 +30,7 @@
 // TMEM: 3 stages x (128 D columns + 32 A columns) = 480 of 512 columns.
 #include "sdct_io.cuh"
 
+#include <atomic>
 #include <cmath>
 #include <cstdlib>
 #include <cstring>
@@ -1264,10 +1265,46 @@ static TensorMapEncodeFn tensor_map_encoder()
     return encode;
 }
 
-static bool make_pixel_tensor_map(KParams &p)
+// encode (or fetch from the context's cache) a 4-D tiled tensor map; false when the driver refuses the geometry
+static bool encode_cached(SdctTcMapCache *cache, uint32_t kind, CUtensorMapDataType type, const void *base, const cuuint64_t dims[4],
+                          const cuuint64_t strides[3], const cuuint32_t box[4], CUtensorMapSwizzle swizzle, unsigned char out[128])
 {
+    if (cache) {
+        for (int i = 0; i < cache->n; i++) {
+            SdctTcMapCache::Entry &e = cache->e[i];
+            if (e.base == base && e.kind == kind && !memcmp(e.dims, dims, sizeof(e.dims)) && !memcmp(e.strides, strides, sizeof(e.strides))) {
+                e.used = ++cache->clock;
+                cache->hits++;
+                if (e.ok) memcpy(out, e.map, 128);
+                return e.ok;
+            }
+        }
+    }
     TensorMapEncodeFn encode = tensor_map_encoder();
-    if (!encode || tc::PRODUCER_WGS != 1 || getenv("SDCT_TC_NO_TMA")) return false;
+    const cuuint32_t estr[4] = {1, 1, 1, 1};
+    CUtensorMap map;
+    const bool ok = encode && encode(&map, type, 4, const_cast<void *>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, swizzle,
+                                     CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+    static_assert(sizeof(map) == 128, "CUtensorMap size");
+    if (ok) memcpy(out, &map, 128);
+    if (cache) {
+        int slot = 0;
+        if (cache->n < SdctTcMapCache::N) slot = cache->n++;
+        else
+            for (int i = 1; i < SdctTcMapCache::N; i++)
+                if (cache->e[i].used < cache->e[slot].used) slot = i;
+        SdctTcMapCache::Entry &e = cache->e[slot];
+        e.base = base; e.kind = kind; e.ok = ok; e.used = ++cache->clock;
+        memcpy(e.dims, dims, sizeof(e.dims)); memcpy(e.strides, strides, sizeof(e.strides));
+        if (ok) memcpy(e.map, &map, 128);
+        cache->misses++;
+    }
+    return ok;
+}
+
+static bool make_pixel_tensor_map(KParams &p, const SdctTcOptions &opt, SdctTcMapCache *cache)
+{
+    if (tc::PRODUCER_WGS != 1 || opt.no_tma) return false;
     if (p.comps != 1 || p.pixel_vec < 2 || p.bpr < (uint32_t)tc::TILE || (p.eyes != 1 && p.eyes != 2)) return false;
     const uint64_t band_rows = ((uint64_t)p.row0 + p.rows + p.eyes - 1) / p.eyes * 8;   // pixel rows of one eye that the window reaches
     const uint64_t plane = p.pitch * band_rows;
@@ -1276,14 +1313,18 @@ static bool make_pixel_tensor_map(KParams &p)
     for (int i = 0; i < 3; i++)
         if (strides[i] == 0 || (strides[i] & 15) || strides[i] >= (1ull << 40)) return false;
     if (((uintptr_t)p.pixels & 15) || band_rows >= (1ull << 31) || p.frames >= (1u << 31)) return false;
-    const cuuint32_t box[4] = {256, 8, 1, 1}, estr[4] = {1, 1, 1, 1};
-    CUtensorMap map;
-    if (encode(&map, CU_TENSOR_MAP_DATA_TYPE_UINT32, 4, const_cast<uint8_t *>(p.pixels), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-               CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
-        return false;
-    static_assert(sizeof(map) == sizeof(p.tc_tensor_map), "CUtensorMap size");
-    memcpy(p.tc_tensor_map, &map, sizeof(map));
-    return true;
+    const cuuint32_t box[4] = {256, 8, 1, 1};
+    static_assert(sizeof(p.tc_tensor_map) == 128, "CUtensorMap size");
+    return encode_cached(cache, 0, CU_TENSOR_MAP_DATA_TYPE_UINT32, p.pixels, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_NONE, p.tc_tensor_map);
+}
+
+// cudaFuncSetAttribute belongs to the current device's context, not to the process: one flag bit per device
+static bool attr_pending(std::atomic<uint64_t> &done, uint64_t *bit)
+{
+    int dev = 0;
+    cudaGetDevice(&dev);
+    *bit = 1ull << (dev & 63);
+    return !(done.load(std::memory_order_acquire) & *bit);
 }
 
 template <int LAYOUT, bool CS>
@@ -1291,11 +1332,12 @@ static cudaError_t launch_tc(const KParams &p, unsigned grid, bool tma, bool rgb
 {
 #define SDCT_TC_GO(C, V)                                                                                             \
     do {                                                                                                             \
-        static bool attr_done = false;                                                                               \
-        if (!attr_done) {                                                                                            \
+        static std::atomic<uint64_t> attr_done{0};                                                                   \
+        uint64_t bit;                                                                                                \
+        if (attr_pending(attr_done, &bit)) {                                                                         \
             cudaError_t e = cudaFuncSetAttribute(tc::forward_tc_kernel<LAYOUT, C, V, CS>, cudaFuncAttributeMaxDynamicSharedMemorySize, tc::SMEM_BYTES); \
             if (e != cudaSuccess) return e;                                                                          \
-            attr_done = true;                                                                                        \
+            attr_done.fetch_or(bit, std::memory_order_release);                                                      \
         }                                                                                                            \
         tc::forward_tc_kernel<LAYOUT, C, V, CS><<<grid, tc::THREADS, tc::SMEM_BYTES, s>>>(p);                        \
         return cudaGetLastError();                                                                                   \
@@ -1319,11 +1361,12 @@ extern "C" int sdct_k_tc_trace(unsigned long long *host)
 template <int LAYOUT, bool CT>
 static cudaError_t launch_tc_inverse(const KParams &p, unsigned grid, cudaStream_t s)
 {
-    static bool attr_done = false;
-    if (!attr_done) {
+    static std::atomic<uint64_t> attr_done{0};
+    uint64_t bit;
+    if (attr_pending(attr_done, &bit)) {
         cudaError_t e = cudaFuncSetAttribute(tc::inverse_tc_kernel<LAYOUT, CT>, cudaFuncAttributeMaxDynamicSharedMemorySize, tc::SMEM_BYTES);
         if (e != cudaSuccess) return e;
-        attr_done = true;
+        attr_done.fetch_or(bit, std::memory_order_release);
     }
     tc::inverse_tc_kernel<LAYOUT, CT><<<grid, tc::THREADS, tc::SMEM_BYTES, s>>>(p);
     return cudaGetLastError();
@@ -1332,10 +1375,9 @@ static cudaError_t launch_tc_inverse(const KParams &p, unsigned grid, cudaStream
 // Layout C's coefficients as a 4-D u8 tensor [frame][component][plane 0..63][block]; box = 128 blocks x 64 planes with
 // the 128-byte swizzle (inverse: tile loads; forward: tile stores).  Returns false when the geometry does not fit a
 // tensor map (the thread-copy paths are used instead).
-static bool make_coef_tensor_map(KParams &p)
+static bool make_coef_tensor_map(KParams &p, const SdctTcOptions &opt, SdctTcMapCache *cache)
 {
-    TensorMapEncodeFn encode = tensor_map_encoder();
-    if (!encode || getenv("SDCT_TC_NO_TMA")) return false;
+    if (opt.no_tma) return false;
     const uint64_t plane_len = ((uint64_t)p.row0 + p.rows) * p.bpr;   // blocks of a plane that the window reaches
     const uint64_t cstride = p.comps > 1 ? p.coef_comp_stride : p.coef_plane_stride * 64;
     const uint64_t fstride = p.frames > 1 ? p.coef_frame_stride : cstride * p.comps;
@@ -1344,18 +1386,14 @@ static bool make_coef_tensor_map(KParams &p)
     const cuuint64_t strides[3] = {p.coef_plane_stride, cstride, fstride};
     for (int i = 0; i < 3; i++)
         if (strides[i] == 0 || (strides[i] & 15) || strides[i] >= (1ull << 40)) return false;
-    const cuuint32_t box[4] = {128, 64, 1, 1}, estr[4] = {1, 1, 1, 1};
-    CUtensorMap map;
-    if (encode(&map, CU_TENSOR_MAP_DATA_TYPE_UINT8, 4, const_cast<uint8_t *>(p.coefs), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-               CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
-        return false;
-    static_assert(sizeof(map) == sizeof(p.tc_coef_map), "CUtensorMap size");
-    memcpy(p.tc_coef_map, &map, sizeof(map));
-    return true;
+    const cuuint32_t box[4] = {128, 64, 1, 1};
+    static_assert(sizeof(p.tc_coef_map) == 128, "CUtensorMap size");
+    return encode_cached(cache, 1, CU_TENSOR_MAP_DATA_TYPE_UINT8, p.coefs, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B, p.tc_coef_map);
 }
 
-extern "C" cudaError_t sdct_k_launch_tc(int op, int layout, const KParams *pp, cudaStream_t s)
+extern "C" cudaError_t sdct_k_launch_tc(int op, int layout, const KParams *pp, const SdctTcOptions *popt, SdctTcMapCache *maps, cudaStream_t s)
 {
+    const SdctTcOptions opt = popt ? *popt : SdctTcOptions();
     if (op != SDCT_K_OP_FORWARD && op != SDCT_K_OP_INVERSE) return cudaErrorNotSupported;
     KParams p = *pp;
     p.layout = (uint32_t)layout;
@@ -1365,7 +1403,7 @@ extern "C" cudaError_t sdct_k_launch_tc(int op, int layout, const KParams *pp, c
     if (tiles == 0) return cudaSuccess;
     if (tiles > 0xffff0000ull) return cudaErrorInvalidConfiguration;   // a TileWalk may step past the end without wrapping
     p.tiles = (uint32_t)tiles;
-    { const char *e = getenv("SDCT_TC_ABLATE"); p.tc_ablate = e ? (uint32_t)atoi(e) : 0u; }
+    p.tc_ablate = opt.ablate;
     if (op == SDCT_K_OP_INVERSE) {
         // single component, aligned geometry (checked by the caller); p.tab = column offsets, p.tab2[0] = 2^-S
         p.tab2[0].x = p.tab2[0].y = ldexpf(p.tab2[0].x, tc::A_SCALE_LOG2);   // the A operand carries 2^-24 (bytes_to_half)
@@ -1377,7 +1415,7 @@ extern "C" cudaError_t sdct_k_launch_tc(int op, int layout, const KParams *pp, c
         case SDCT_K_LAYOUT_A: return launch_tc_inverse<SDCT_K_LAYOUT_A, false>(p, grid_i, s);
         case SDCT_K_LAYOUT_B: return launch_tc_inverse<SDCT_K_LAYOUT_B, false>(p, grid_i, s);
         case SDCT_K_LAYOUT_C:
-            if (make_coef_tensor_map(p)) return launch_tc_inverse<SDCT_K_LAYOUT_C, true>(p, grid_i, s);
+            if (make_coef_tensor_map(p, opt, maps)) return launch_tc_inverse<SDCT_K_LAYOUT_C, true>(p, grid_i, s);
             return launch_tc_inverse<SDCT_K_LAYOUT_C, false>(p, grid_i, s);
         default: return cudaErrorInvalidValue;
         }
@@ -1391,14 +1429,14 @@ extern "C" cudaError_t sdct_k_launch_tc(int op, int layout, const KParams *pp, c
     // pixel tile are produced from one copy of its pixels; p.tiles then counts pixel tiles
     const uint64_t strides = p.pitch | (p.eyes == 2 ? p.eye_stride : 0) | (p.frames > 1 ? p.pixel_frame_stride : 0);
     const bool rgb_fused = p.comps == 3 && tc::PRODUCER_WGS == 1 && !(((uintptr_t)p.pixels | strides) & 15) && !(p.bpr & 1) && p.bpr >= (uint32_t)tc::TILE &&
-                           !(((unsigned long long)p.rows * p.bpr) & 1) && !getenv("SDCT_TC_NO_RGB_FUSE");
+                           !(((unsigned long long)p.rows * p.bpr) & 1) && !opt.no_rgb_fuse;
     if (rgb_fused) p.tiles = (uint32_t)(tiles / 3);
     const unsigned grid = (unsigned)(p.tiles < sms ? p.tiles : sms);
     // layout C: one tensor-map store per tile when the coefficient planes fit a tensor map.  Measured (64 x 1080p):
     // thread flush + cp.async pixel ring 59.7 us, tensor-map store alone 59.7, tensor-map store + TMA pixel path 54.6
     // (the TMA pixel path WITHOUT the store was slower than the cp.async ring), so the two go together.
-    const bool c_store = layout == SDCT_K_LAYOUT_C && !getenv("SDCT_TC_NO_TMA_STORE") && make_coef_tensor_map(p);
-    const bool tma = (layout != SDCT_K_LAYOUT_C || c_store) && make_pixel_tensor_map(p);
+    const bool c_store = layout == SDCT_K_LAYOUT_C && !opt.no_tma_store && make_coef_tensor_map(p, opt, maps);
+    const bool tma = (layout != SDCT_K_LAYOUT_C || c_store) && make_pixel_tensor_map(p, opt, maps);
     switch (layout) {
     case SDCT_K_LAYOUT_A: return launch_tc<SDCT_K_LAYOUT_A, false>(p, grid, tma, rgb_fused, s);
     case SDCT_K_LAYOUT_B: return launch_tc<SDCT_K_LAYOUT_B, false>(p, grid, tma, rgb_fused, s);

@@ -9,6 +9,7 @@
 
 #include <cmath>
 #include <cstring>
+#include <vector>
 
 namespace {
 
@@ -53,7 +54,8 @@ void sdct_tc_integer_matrix(int32_t K[64 * 64])
 
 void sdct_tc_operand(int layout, uint16_t out[128 * 64])
 {
-    static int32_t K[64 * 64];
+    std::vector<int32_t> Kv(64 * 64);   // (no static scratch: contexts may be created concurrently)
+    int32_t *K = Kv.data();
     sdct_tc_integer_matrix(K);
     memset(out, 0, 128 * 64 * sizeof(uint16_t));
     for (int n = 0; n < 128; n++) {
@@ -81,7 +83,8 @@ void sdct_tc_operand(int layout, uint16_t out[128 * 64])
 // oracle/sdct_oracle.c (inverse_tensor_matrix) restates this independently.
 int sdct_tc_inverse_operand(int layout, const float tab[64], uint16_t out[128 * 64], float off_cols[64])
 {
-    static thread_local double E[64 * 64];
+    std::vector<double> Ev(64 * 64);
+    double *E = Ev.data();
     double emax = 0.0;
     for (int y = 0; y < 8; y++)
         for (int x = 0; x < 8; x++)

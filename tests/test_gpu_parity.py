@@ -270,8 +270,9 @@ def test_reference_entry_points_host_buffers(oracle, name, layout):
 
 
 @pytest.mark.parametrize("layout", LAYOUTS)
-def test_host_pipeline_matches_device_path(ctx, oracle, layout, monkeypatch):
-    monkeypatch.setenv("SDCT_HOST_CHUNK_MB", "1")
+def test_host_pipeline_matches_device_path(oracle, layout, monkeypatch):
+    monkeypatch.setenv("SDCT_HOST_CHUNK_MB", "1")   # the $SDCT_* switches are read once, in sdct_create
+    ctx = sd.Context(0)
     lut = ol.lut(12)
     for (f, h, w, eyes) in ((9, 256, 512, 1), (1, 1080 - 1080 % 8, 1920, 1), (2, 128, 256, 2)):
         if eyes == 2 and layout != sd.LAYOUT_C:
@@ -481,9 +482,12 @@ def test_tensor_core_wide_images_tma_pixel_path(ctx, oracle, layout, monkeypatch
     for k in range(f):
         assert np.array_equal(got[k], want[k]), (k, np.count_nonzero(got[k] != want[k]))
     # the same through the thread-copy paths (what a geometry that fits no tensor map gets)
-    monkeypatch.setenv("SDCT_TC_NO_TMA", "1")
-    got = ctx.forward(dev(imgs), lut, job).cpu().numpy().reshape(f, -1)
+    monkeypatch.setenv("SDCT_TC_NO_TMA", "1")   # read once, in sdct_create
+    ctx_no_tma = sd.Context(0)
     monkeypatch.delenv("SDCT_TC_NO_TMA")
+    got = ctx_no_tma.forward(dev(imgs), lut, job).cpu().numpy().reshape(f, -1)
+    torch.cuda.synchronize()
+    ctx_no_tma.close()
     for k in range(f):
         assert np.array_equal(got[k], want[k]), (k, np.count_nonzero(got[k] != want[k]))
     # band window: bands 1..3 of frame 0 only, the rest of the output untouched
@@ -592,9 +596,12 @@ def test_tensor_core_inverse_is_bit_exact_to_its_cpu_restatement(ctx, oracle, la
         assert np.array_equal(got, oracle.inverse(layout, coef, w2, h2, rt_lut(layout), eyes=eyes, tensor=True)), (h2, w2, eyes)
     # the same with the tensor-map path of layout C switched off (the thread-copy fallback for geometries no tensor
     # map describes; layouts A and B always use the 1-D bulk copy, which needs no map)
-    monkeypatch.setenv("SDCT_TC_NO_TMA", "1")
-    got = ctx.inverse(dev(coefs), lut, job).cpu().numpy().reshape(f, h, w)
+    monkeypatch.setenv("SDCT_TC_NO_TMA", "1")   # read once, in sdct_create
+    ctx_no_tma = sd.Context(0)
     monkeypatch.delenv("SDCT_TC_NO_TMA")
+    got = ctx_no_tma.inverse(dev(coefs), lut, job).cpu().numpy().reshape(f, h, w)
+    torch.cuda.synchronize()
+    ctx_no_tma.close()
     for k in range(f):
         assert np.array_equal(got[k], oracle.inverse(layout, coefs[k], w, h, lut, tensor=True))
     # interleaved RGB has no tensor-core inverse: refused, not silently replaced by the fp32 arithmetic
