@@ -270,38 +270,62 @@ SDCT_DEV void flush_coefs(const uint8_t *sm, const KParams &p, const Tile &b)
     }
 }
 
-// Layouts A and B, 16-byte-aligned output: the bytes a warp stages are whole 16-byte chunks of the output that
-// no other warp touches (B: its 64 blocks = 8 groups of 512 bytes; A: blocks 32w.. and 128 + 32w.., 64 bytes
-// each), so the warp flushes its own part after a __syncwarp() and the CTA needs no barrier at all.
+// 16-byte-aligned output: the bytes a warp stages are whole 16-byte chunks of the output that no other warp touches
+// (B: its 64 blocks = 8 groups of 512 bytes; A: blocks 32w.. and TB + 32w.., 64 bytes each; C: 64 bytes of each of the
+// 64 plane rows - block counts are multiples of 16 there), so the warp flushes its own part after a __syncwarp() and
+// the CTA needs no barrier at all.  The flush is ONE basic block: eight unconditional 16-byte shared-memory loads
+// (thread-constant base + immediate offsets), then eight PREDICATED 16-byte stores - no branch around a chunk, so the
+// loads are all in flight together and ptxas can sink the stores into the arithmetic that follows (the caller
+// flushes tile k - 1 at the start of tile k's row pass, when most data registers are still free).
+SDCT_DEV void st_global_v4_if(void *ptr, uint4 v, bool pred)
+{
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.u32 p, %5, 0;\n\t@p st.global.v4.u32 [%0], {%1, %2, %3, %4};\n\t}"
+                 ::"l"(ptr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w), "r"((uint32_t)pred) : "memory");
+}
+
+struct FlushJob {       // the tile whose staged image is still to be written (count == 0: none)
+    uint8_t *coef;      // start of the coefficient set
+    uint64_t n_first;   // first block of the tile in the set's block sequence
+    uint32_t count;
+};
+
 template <int LAYOUT, bool COMPL>
-SDCT_DEV void flush_coefs_warp(const uint8_t *sm, const KParams &p, const Tile &b)
+SDCT_DEV void flush_coefs_warp(const uint8_t *sm, const KParams &p, const FlushJob &f)
 {
     const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const uint64_t n_first = (uint64_t)p.row0 * p.bpr + b.n0;
     const uint32_t m32 = COMPL ? 0xffffffffu : 0u;
-    if (LAYOUT == SDCT_K_LAYOUT_C) {   // the warp's 64 blocks = 64 bytes of each of the 64 plane rows (counts are multiples of 16)
+    uint4 v[8];
+    if (LAYOUT == SDCT_K_LAYOUT_C) {   // chunk j: plane row 8j + lane/4, bytes 64 warp + 16 (lane % 4) ..
+        const uint32_t c = 64u * warp + 16u * (lane & 3);
+        const uint8_t *src = sm + (lane >> 2) * C_PITCH + c;
 #pragma unroll
-        for (uint32_t j = 0; j < 8; j++) {
-            const uint32_t k = 32u * j + lane, i = k >> 2, c = 64u * warp + 16u * (k & 3);
-            if (c < b.count)
-                *reinterpret_cast<uint4 *>(b.coef + (uint64_t)i * p.coef_plane_stride + n_first + c) =
-                    xor4(*reinterpret_cast<const uint4 *>(sm + i * C_PITCH + c), m32);
-        }
+        for (int j = 0; j < 8; j++) v[j] = *reinterpret_cast<const uint4 *>(src + j * 8 * C_PITCH);
+        uint8_t *dst = f.coef + (uint64_t)(lane >> 2) * p.coef_plane_stride + f.n_first + c;
+        const uint64_t step = 8 * p.coef_plane_stride;
+#pragma unroll
+        for (int j = 0; j < 8; j++, dst += step) st_global_v4_if(dst, xor4(v[j], m32), c < f.count);
         return;
     }
-    uint4 *dst = reinterpret_cast<uint4 *>(b.coef + n_first * 64);
-    const uint32_t chunks16 = b.count * 4;
+    const uint32_t chunks16 = f.count * 4;
+    if (LAYOUT == SDCT_K_LAYOUT_B) {   // chunk k = 256 warp + 32 j + lane: group 8 warp + j, piece lane
+        const uint8_t *src = sm + 8u * warp * B_GROUP_PITCH + lane * 16u;
 #pragma unroll
-    for (uint32_t j = 0; j < 8; j++) {
-        uint32_t k, off;
-        if (LAYOUT == SDCT_K_LAYOUT_B) {
-            k = 256u * warp + 32u * j + lane;
-            off = (k >> 5) * B_GROUP_PITCH + (k & 31) * 16;
-        } else {
-            k = (j >> 2) * 512u + 128u * warp + 32u * (j & 3) + lane;
-            off = (k >> 2) * A_SLOT + (k & 3) * 16;
+        for (int j = 0; j < 8; j++) v[j] = *reinterpret_cast<const uint4 *>(src + j * B_GROUP_PITCH);
+        const uint32_t k0 = 256u * warp + lane;
+        uint8_t *dst = f.coef + f.n_first * 64 + 16ull * k0;
+#pragma unroll
+        for (int j = 0; j < 8; j++) st_global_v4_if(dst + j * 512, xor4(v[j], m32), k0 + 32u * j < chunks16);
+    } else {                           // chunk k = (j / 4) 4 TB + 128 warp + 32 (j % 4) + lane: block k / 4, piece k % 4
+        const uint8_t *src = sm + (32u * warp + (lane >> 2)) * A_SLOT + (lane & 3) * 16u;
+#pragma unroll
+        for (int j = 0; j < 8; j++) v[j] = *reinterpret_cast<const uint4 *>(src + ((j >> 2) * TB + 8 * (j & 3)) * A_SLOT);
+        const uint32_t k0 = 128u * warp + lane;
+        uint8_t *dst = f.coef + f.n_first * 64 + 16ull * k0;
+#pragma unroll
+        for (int j = 0; j < 8; j++) {
+            const uint32_t dk = (j >> 2) * 4u * TB + 32u * (j & 3);
+            st_global_v4_if(dst + 16ull * dk, xor4(v[j], m32), k0 + dk < chunks16);
         }
-        if (k < chunks16) dst[k] = xor4(*reinterpret_cast<const uint4 *>(sm + off), m32);
     }
 }
 
@@ -318,11 +342,13 @@ SDCT_DEV bool warp_local_coefs(const KParams &p)
 // written again only after it).
 template <int COMPS, int VEC> __host__ __device__ constexpr bool prefetchable() { return COMPS == 1 && VEC >= 1; }
 
-template <int LAYOUT, int MODE, bool X3, int COMPS, int VEC>
-__global__ void __launch_bounds__(SDCT_TB, 3) forward_kernel(const __grid_constant__ KParams p)
+// WL (warp-local coefficients, uniform per launch) is a template parameter so that the deferred flush and the row pass
+// it hides behind are one basic block.
+template <int LAYOUT, int MODE, bool X3, int COMPS, int VEC, bool WL>
+SDCT_DEV void forward_tiles(const KParams &p, uint8_t *smem)
 {
-    extern __shared__ __align__(16) uint8_t smem[];
     constexpr bool PF = prefetchable<COMPS, VEC>();
+    constexpr bool COMPL = complemented<LAYOUT, MODE>();
     uint8_t *stage_in = smem + 2 * STAGE_BYTES;
     TileWalk w;   // the tile after the current one (the one whose pixels are prefetched)
     w.init(p, 0, 1);
@@ -333,6 +359,7 @@ __global__ void __launch_bounds__(SDCT_TB, 3) forward_kernel(const __grid_consta
         cp_async_commit();
     }
     w.next(p);
+    FlushJob pending = {nullptr, 0, 0};   // WL: the previous tile's image, flushed inside this tile's row pass
     for (uint32_t it = 0;; it++, w.next(p)) {
         const bool more = w.tile < p.tiles;
         Tile tn = t;
@@ -346,20 +373,30 @@ __global__ void __launch_bounds__(SDCT_TB, 3) forward_kernel(const __grid_consta
         } else {
             load_pair<COMPS, VEC>(locate<LAYOUT>(p, t), p.pitch, wp, wq);
         }
+        if (WL) flush_coefs_warp<LAYOUT, COMPL>(smem + ((it + 1) & 1) * STAGE_BYTES, p, pending);
         F2 v[64];
         forward_pair<LAYOUT, MODE, X3>(wp, wq, p.tab, v);
         uint8_t *sm = smem + (it & 1) * STAGE_BYTES;
         stage_levels<LAYOUT>(sm, v);
-        if (warp_local_coefs<LAYOUT>(p)) {
+        if (WL) {
             __syncwarp();
-            flush_coefs_warp<LAYOUT, complemented<LAYOUT, MODE>()>(sm, p, t);
+            pending.coef = t.coef; pending.n_first = (uint64_t)p.row0 * p.bpr + t.n0; pending.count = t.count;
+            if (!more) { flush_coefs_warp<LAYOUT, COMPL>(sm, p, pending); break; }
         } else {
             __syncthreads();
-            flush_coefs<LAYOUT, complemented<LAYOUT, MODE>()>(sm, p, t);
+            flush_coefs<LAYOUT, COMPL>(sm, p, t);
+            if (!more) break;
         }
-        if (!more) break;
         t = tn;
     }
+}
+
+template <int LAYOUT, int MODE, bool X3, int COMPS, int VEC>
+__global__ void __launch_bounds__(SDCT_TB, 3) forward_kernel(const __grid_constant__ KParams p)
+{
+    extern __shared__ __align__(16) uint8_t smem[];
+    if (warp_local_coefs<LAYOUT>(p)) forward_tiles<LAYOUT, MODE, X3, COMPS, VEC, true>(p, smem);
+    else forward_tiles<LAYOUT, MODE, X3, COMPS, VEC, false>(p, smem);
 }
 
 // ---- inverse ---------------------------------------------------------------------------------------
