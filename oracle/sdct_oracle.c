@@ -428,12 +428,13 @@ static int inverse_tensor_matrix(int layout, const float tab[64], int32_t full[6
         while (ldexp(emax, S + 1) < 1048576.0 - 512.0) S++;
     }
     for (int p = 0; p < 64; p++) {
-        double sum = 0.0;
+        /* the level offset -127 goes through the ROUNDED matrix too, so that the all-127 block decodes to exactly 0 */
+        int64_t sum = 0;
         for (int i = 0; i < 64; i++) {
             full[p * 64 + i] = (int32_t)llrint(ldexp(E[p * 64 + i], S));
-            sum += E[p * 64 + i];
+            sum += full[p * 64 + i];
         }
-        off[p] = (float)(-127.0 * sum);
+        off[p] = (float)(-127.0 * ldexp((double)sum, -S));
     }
     return S;
 }

@@ -55,8 +55,8 @@ struct TileWalk {
     }
 };
 
-template <int COMPS, int CB>
-SDCT_DEV Tile tile_at(const KParams &p, const TileWalk &w)
+template <int COMPS, int CB, class Walk = TileWalk>
+SDCT_DEV Tile tile_at(const KParams &p, const Walk &w)
 {
     Tile t;
     uint32_t frame = w.fc;

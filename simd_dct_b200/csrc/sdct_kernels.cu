@@ -391,10 +391,202 @@ SDCT_DEV void forward_tiles(const KParams &p, uint8_t *smem)
     }
 }
 
+
+// ---- dynamic schedule: warps draw 64-block tiles from a ticket counter ---------------------------------------------
+// With a static tile list the CTAs of an SM do not finish together: the warp schedulers favour some warps, those run
+// ahead, and the rest of the launch runs with one or two warps per scheduler, which cannot keep the FMA pipe fed (ncu:
+// 2.3 of 3 warps active on average).  Here every WARP is its own worker (the aligned paths need no CTA barrier: a warp
+// stages and flushes whole 16-byte chunks of its own 64 blocks): first tile = its index in the grid, then tickets from
+// p.sched[0], drawn one iteration ahead of use so that the atomic's latency hides behind a tile's arithmetic.  The
+// last warp to finish (p.sched[1]) resets both counters for the next launch on the stream.
+constexpr int WB = 64;                        // blocks per warp tile
+constexpr int W_STAGE = WB * A_SLOT;          // A: 64 slots of 80 B; B: 8 groups of 528 B; C: 64 plane rows of 64 B
+constexpr int WC_PITCH = WB;
+constexpr int W_IN = 8 * 32 * 16;             // prefetched pixels of a warp tile
+constexpr int W_SMEM = 2 * W_STAGE + 2 * W_IN;
+static_assert((TB / 32) * W_SMEM <= 2 * STAGE_BYTES + 2 * IN_STAGE_BYTES, "the warp-tile form fits the CTA-tile form's shared memory");
+
+struct WTile { uint32_t fc, chunk; };
+SDCT_DEV WTile wtile_of(const KParams &p, uint32_t wt)
+{
+    WTile w;
+    w.fc = fastdiv(wt, p.div_wchunks);
+    w.chunk = wt - w.fc * p.wchunks;
+    return w;
+}
+
+template <int LAYOUT>
+SDCT_DEV BlockPos locate_w(const KParams &p, const Tile &t, uint32_t lane)
+{
+    BlockPos b;
+    b.comp = t.comp;
+#pragma unroll
+    for (int k = 0; k < 2; k++) {
+        const uint32_t slot = (LAYOUT == SDCT_K_LAYOUT_A) ? lane + k * 32 : 2 * lane + k;
+        b.valid[k] = slot < t.count;
+        const uint32_t nl = t.n0 + (b.valid[k] ? slot : 0);
+        const uint32_t r = fastdiv(nl, p.div_bpr);
+        const uint32_t bx = nl - r * p.bpr;
+        const uint32_t row = r + p.row0;
+        const uint32_t band = p.eyes == 2 ? row >> 1 : row, eye = p.eyes == 2 ? row & 1 : 0;
+        b.px[k] = t.pix + (uint64_t)eye * p.eye_stride + (uint64_t)band * 8 * p.pitch + (uint64_t)bx * 8 * p.comps;
+    }
+    return b;
+}
+
+template <int VEC>
+SDCT_DEV void prefetch_pair_w(uint8_t *stage, uint32_t lane, const BlockPos &b, uint64_t pitch)
+{
+    uint8_t *slot = stage + lane * 16;
+#pragma unroll
+    for (int r = 0; r < 8; r++) {
+        if (VEC == 2) {
+            cp_async16(slot + r * 512, b.px[0] + r * pitch);
+        } else {
+            cp_async8(slot + r * 512, b.px[0] + r * pitch);
+            cp_async8(slot + r * 512 + 8, b.px[1] + r * pitch);
+        }
+    }
+}
+
+SDCT_DEV void read_prefetched_w(const uint8_t *stage, uint32_t lane, uint32_t wp[16], uint32_t wq[16])
+{
+    const uint8_t *slot = stage + lane * 16;
+#pragma unroll
+    for (int r = 0; r < 8; r++) {
+        const uint4 v = *reinterpret_cast<const uint4 *>(slot + r * 512);
+        wp[2 * r] = v.x; wp[2 * r + 1] = v.y; wq[2 * r] = v.z; wq[2 * r + 1] = v.w;
+    }
+}
+
+template <int LAYOUT>
+SDCT_DEV void stage_levels_w(uint8_t *sm, uint32_t lane, const F2 b[64])
+{
+    if (LAYOUT == SDCT_K_LAYOUT_B) {
+        uint16_t *d = reinterpret_cast<uint16_t *>(sm + (lane >> 2) * B_GROUP_PITCH + 2 * (lane & 3));
+#pragma unroll
+        for (int i = 0; i < 64; i++) d[i * 4] = (uint16_t)pack_pq(b[i]);
+    } else if (LAYOUT == SDCT_K_LAYOUT_C) {
+        uint16_t *d = reinterpret_cast<uint16_t *>(sm + 2 * lane);
+#pragma unroll
+        for (int i = 0; i < 64; i++) d[i * (WC_PITCH / 2)] = (uint16_t)pack_pq(b[i]);
+    } else {
+#pragma unroll
+        for (int k = 0; k < 2; k++) {
+            uint4 *d = reinterpret_cast<uint4 *>(sm + (lane + k * 32) * A_SLOT);
+#pragma unroll
+            for (int j = 0; j < 4; j++) {
+                uint32_t w[4];
+#pragma unroll
+                for (int q = 0; q < 4; q++) {
+                    const int v = 2 * j + (q >> 1), u0 = 4 * (q & 1);
+#define SDCT_L(u) (k ? b[(u) * 8 + v].y : b[(u) * 8 + v].x)
+                    w[q] = pack4_sat(SDCT_L(u0), SDCT_L(u0 + 1), SDCT_L(u0 + 2), SDCT_L(u0 + 3));
+#undef SDCT_L
+                }
+                d[j] = make_uint4(w[0], w[1], w[2], w[3]);
+            }
+        }
+    }
+}
+
+// the warp's staged image -> global memory: eight unconditional 16-byte loads, eight predicated 16-byte stores
+template <int LAYOUT, bool COMPL>
+SDCT_DEV void flush_w(const uint8_t *sm, uint32_t lane, const KParams &p, const FlushJob &f)
+{
+    const uint32_t m32 = COMPL ? 0xffffffffu : 0u;
+    uint4 v[8];
+    if (LAYOUT == SDCT_K_LAYOUT_C) {          // chunk j: plane row 8j + lane / 4, bytes 16 (lane % 4) ..
+        const uint32_t c = 16u * (lane & 3);
+        const uint8_t *src = sm + (lane >> 2) * WC_PITCH + c;
+#pragma unroll
+        for (int j = 0; j < 8; j++) v[j] = *reinterpret_cast<const uint4 *>(src + j * 8 * WC_PITCH);
+        uint8_t *dst = f.coef + (uint64_t)(lane >> 2) * p.coef_plane_stride + f.n_first + c;
+        const uint64_t step = 8 * p.coef_plane_stride;
+#pragma unroll
+        for (int j = 0; j < 8; j++, dst += step) st_global_v4_if(dst, xor4(v[j], m32), c < f.count);
+    } else if (LAYOUT == SDCT_K_LAYOUT_B) {   // chunk j: group j, piece lane
+        const uint8_t *src = sm + lane * 16u;
+#pragma unroll
+        for (int j = 0; j < 8; j++) v[j] = *reinterpret_cast<const uint4 *>(src + j * B_GROUP_PITCH);
+        uint8_t *dst = f.coef + f.n_first * 64 + 16ull * lane;
+#pragma unroll
+        for (int j = 0; j < 8; j++) st_global_v4_if(dst + j * 512, xor4(v[j], m32), 8u * j < f.count);
+    } else {                                   // chunk j: block 8j + lane % 8, piece lane / 8 (conflict-free reads)
+        const uint32_t s0 = lane & 7, piece = lane >> 3;
+        const uint8_t *src = sm + s0 * A_SLOT + piece * 16u;
+#pragma unroll
+        for (int j = 0; j < 8; j++) v[j] = *reinterpret_cast<const uint4 *>(src + j * 8 * A_SLOT);
+        uint8_t *dst = f.coef + (f.n_first + s0) * 64 + 16ull * piece;
+#pragma unroll
+        for (int j = 0; j < 8; j++) st_global_v4_if(dst + j * 512, xor4(v[j], m32), 8u * j + s0 < f.count);
+    }
+}
+
+template <int LAYOUT, int MODE, bool X3, int VEC>
+SDCT_DEV void forward_warp_tiles(const KParams &p, uint8_t *smem)
+{
+    constexpr bool COMPL = complemented<LAYOUT, MODE>();
+    const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    uint8_t *out_stage = smem + warp * W_SMEM, *in_stage = out_stage + 2 * W_STAGE;
+    const uint32_t workers = gridDim.x * (TB / 32);
+    uint32_t cur = blockIdx.x * (TB / 32) + warp;
+    auto draw = [&]() -> uint32_t {            // the ticket is consumed (broadcast) one iteration later
+        uint32_t v = 0;
+        // (atom.inc, not atomicAdd / atom.add: ptxas turns a warp-uniform add into its warp-aggregation pattern, whose broadcast shuffle waits for
+        // the atomic's result on the spot)
+        if (lane == 0) asm volatile("atom.global.inc.u32 %0, [%1], 0x7fffffff;" : "=r"(v) : "l"(p.sched) : "memory");
+        return v;
+    };
+    auto take = [&](uint32_t v) -> uint32_t { return workers + __shfl_sync(0xffffffffu, v, 0); };
+    if (cur < p.wtiles) {
+        Tile t = tile_at<1, WB>(p, wtile_of(p, cur));
+        prefetch_pair_w<VEC>(in_stage, lane, locate_w<LAYOUT>(p, t, lane), p.pitch);
+        cp_async_commit();
+        uint32_t nxt = take(draw());
+        uint32_t ticket = nxt < p.wtiles ? draw() : 0u;
+        FlushJob pending = {nullptr, 0, 0};
+        for (uint32_t it = 0;; it++) {
+            const bool more = nxt < p.wtiles;
+            Tile tn = t;
+            if (more) {
+                tn = tile_at<1, WB>(p, wtile_of(p, nxt));
+                prefetch_pair_w<VEC>(in_stage + ((it + 1) & 1) * W_IN, lane, locate_w<LAYOUT>(p, tn, lane), p.pitch);
+            }
+            cp_async_commit();
+            cp_async_wait<1>();
+            uint32_t wp[16], wq[16];
+            read_prefetched_w(in_stage + (it & 1) * W_IN, lane, wp, wq);
+            flush_w<LAYOUT, COMPL>(out_stage + ((it + 1) & 1) * W_STAGE, lane, p, pending);
+            F2 v[64];
+            forward_pair<LAYOUT, MODE, X3>(wp, wq, p.tab, v);
+            uint8_t *sm = out_stage + (it & 1) * W_STAGE;
+            stage_levels_w<LAYOUT>(sm, lane, v);
+            __syncwarp();
+            pending.coef = t.coef; pending.n_first = (uint64_t)p.row0 * p.bpr + t.n0; pending.count = t.count;
+            if (!more) { flush_w<LAYOUT, COMPL>(sm, lane, p, pending); break; }
+            t = tn;
+            nxt = take(ticket);                       // drawn a whole tile ago
+            if (nxt < p.wtiles) ticket = draw();
+        }
+    }
+    if (lane == 0) {
+        __threadfence();
+        if (atomicAdd(p.sched + 1, 1u) == workers - 1) {   // every other warp has drawn its last ticket
+            p.sched[0] = 0;
+            p.sched[1] = 0;
+        }
+    }
+}
+
 template <int LAYOUT, int MODE, bool X3, int COMPS, int VEC>
 __global__ void __launch_bounds__(SDCT_TB, 3) forward_kernel(const __grid_constant__ KParams p)
 {
     extern __shared__ __align__(16) uint8_t smem[];
+    if (prefetchable<COMPS, VEC>() && COMPS == 1 && p.sched != nullptr && warp_local_coefs<LAYOUT>(p)) {
+        forward_warp_tiles<LAYOUT, MODE, X3, (VEC ? VEC : 1)>(p, smem);
+        return;
+    }
     if (warp_local_coefs<LAYOUT>(p)) forward_tiles<LAYOUT, MODE, X3, COMPS, VEC, true>(p, smem);
     else forward_tiles<LAYOUT, MODE, X3, COMPS, VEC, false>(p, smem);
 }
@@ -795,6 +987,14 @@ extern "C" cudaError_t sdct_k_launch(int op, int layout, int mode, int x3, const
     p.tiles = (uint32_t)tiles;
     p.div_chunks = make_fastdiv(p.chunks);
     p.div_bpr = make_fastdiv(p.bpr);
+    {   // the dynamic schedule's 64-block warp tiles (forward, aligned single-plane geometry; decided in the kernel)
+        const unsigned long long blocks = (unsigned long long)p.rows * p.bpr;
+        p.wchunks = (uint32_t)((blocks + 63) / 64);
+        const unsigned long long wt = (unsigned long long)p.wchunks * p.comps * p.frames;
+        if (op != SDCT_K_OP_FORWARD || p.comps != 1 || wt > 0x7fff0000ull) p.sched = nullptr;
+        p.wtiles = (uint32_t)wt;
+        p.div_wchunks = make_fastdiv(p.wchunks);
+    }
     // persistent CTAs: three per SM (168 registers/thread), each walking tiles blockIdx.x, +grid, ...
     const unsigned resident = 3u * (p.sm_count ? p.sm_count : 148u);
     const unsigned grid = (unsigned)(tiles < resident ? tiles : resident);

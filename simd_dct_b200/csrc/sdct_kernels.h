@@ -42,6 +42,11 @@ struct KParams {
     float2 tab2[64];          // roundtrip: dequantiser scale
     float2 off[64];           // inverse / roundtrip: -127 * dequantiser scale
     KFastDiv div_chunks, div_bpr;  // tensor-core kernels
+    // fp32 forward kernels, dynamic schedule: warps draw 64-block tiles from a ticket counter (sched[0]; sched[1] counts
+    // the warps that have finished - the last one resets both).  null: static schedule of 256-block CTA tiles.
+    uint32_t *sched;
+    uint32_t wchunks, wtiles;      // 64-block tiles per (frame, component) / in total
+    KFastDiv div_wchunks;
     uint32_t tc_ablate;       // profiling only ($SDCT_TC_ABLATE): bit0 no MMA, 1 no A write, 2 no epilogue, 3 no stores, 4 no loads
     const void *tc_matrix;    // tensor-core kernels: the 16 KiB B operand (fp16 digits of 2^22 C(x)C, UMMA canonical layout)
     // tensor-core kernels, TMA pixel path: CUtensorMap over the pixels as u32[frame][eye][row][W / 4]

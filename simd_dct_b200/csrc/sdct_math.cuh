@@ -68,47 +68,65 @@ SDCT_DEV F2 splat(float k) { return make_float2(k, k); }
 SDCT_DEV F2 mulk(F2 a, float k) { return mul2(a, splat(k)); }
 SDCT_DEV F2 fmak(float k, F2 a, F2 c) { return fma2(a, splat(k), c); }   // k*a + c
 // EXACT graphs, two ways to keep ptxas from contracting a packed product into the add that consumes it:
-//   FP = true : the product is issued as fma(a, k, -0.0), which is fl(a * k) bit for bit (x + -0.0 == x for
+//   FP = 1    : the product is issued as fma(a, k, -0.0), which is fl(a * k) bit for bit (x + -0.0 == x for
 //               every x, signed zeros included) and cannot be fused any further, so the add stays a packed
 //               FADD2.  The -0.0 comes from constant memory: ptxas must not know its value, or it would
 //               simplify the FMA back into the multiply it is allowed to fuse.  (scalar-order graph: -12 %)
-//   FP = false: packed multiply, the add as two scalar FADDs on the halves.  (AVX-order graph: measured
-//               3 % faster than FP = true, its outer adds see two sums and are packed anyway)
+//   FP = 0    : packed multiply, the add as two scalar FADDs on the halves.  (AVX-order graph: measured
+//               3 % faster than FP = 1, its outer adds see two sums and are packed anyway)
+//   FP = 2    : packed multiply; the add is issued as fma(b, 1.0, a) (a - b: fma(b, -1.0, a)) - fl(b * 1 + a) is
+//               fl(a + b) bit for bit, b's multiply cannot be contracted into an FMA that already has a multiplier,
+//               and the +-1.0 pairs live in constant memory, so ptxas neither knows their value nor spends a
+//               register on them (FFMA2 r, c[], r runs at the full packed rate).  No scalar instruction is left:
+//               half the issue slots of FP = false for these adds, and no packed/scalar switching on the FMA pipe
+//               (profiles/r01_probe2_issue_rates.txt: alternating FADD2 / FADD reaches 102 of 127 lanes/clk/SM).
 static __constant__ float c_neg_zero = -0.0f;
-template <bool FP> SDCT_DEV F2 mulx(F2 a, float k) { return FP ? fma2(a, splat(k), splat(c_neg_zero)) : mulk(a, k); }
-template <bool FP> SDCT_DEV F2 sadd(F2 a, F2 b) { return FP ? add2(a, b) : make_float2(__fadd_rn(a.x, b.x), __fadd_rn(a.y, b.y)); }
-template <bool FP> SDCT_DEV F2 ssub(F2 a, F2 b) { return FP ? sub2(a, b) : make_float2(__fsub_rn(a.x, b.x), __fsub_rn(a.y, b.y)); }
+static __constant__ float2 c_one2 = {1.0f, 1.0f}, c_neg_one2 = {-1.0f, -1.0f};
+template <int FP> SDCT_DEV F2 mulx(F2 a, float k) { return FP == 1 ? fma2(a, splat(k), splat(c_neg_zero)) : mulk(a, k); }
+template <int FP> SDCT_DEV F2 sadd(F2 a, F2 b)
+{
+    return FP == 1 ? add2(a, b) : FP == 2 ? fma2(b, c_one2, a) : make_float2(__fadd_rn(a.x, b.x), __fadd_rn(a.y, b.y));
+}
+template <int FP> SDCT_DEV F2 ssub(F2 a, F2 b)
+{
+    return FP == 1 ? sub2(a, b) : FP == 2 ? fma2(b, c_neg_one2, a) : make_float2(__fsub_rn(a.x, b.x), __fsub_rn(a.y, b.y));
+}
 
 // first butterfly stage: packed when the inputs are not products (converted pixels), scalar when
 // they are (the second pass reads the first pass's K_N * (...) results)
-template <bool PROD_IN, bool FP> SDCT_DEV F2 add_in(F2 a, F2 b) { return PROD_IN ? sadd<FP>(a, b) : add2(a, b); }
-template <bool PROD_IN, bool FP> SDCT_DEV F2 sub_in(F2 a, F2 b) { return PROD_IN ? ssub<FP>(a, b) : sub2(a, b); }
+template <bool PROD_IN, int FP> SDCT_DEV F2 add_in(F2 a, F2 b) { return PROD_IN ? sadd<FP>(a, b) : add2(a, b); }
+template <bool PROD_IN, int FP> SDCT_DEV F2 sub_in(F2 a, F2 b) { return PROD_IN ? ssub<FP>(a, b) : sub2(a, b); }
 
 // ---- 8-point forward, reference scalar order (:148-171); v[0], v[S], ... v[7S] ----------------
+// how the scalar-order graph keeps its products out of FFMA2 contraction (see mulx): measured per build
+#ifndef SDCT_SCALAR_FP
+#define SDCT_SCALAR_FP 1
+#endif
+constexpr int SFP = SDCT_SCALAR_FP;
 template <int S, bool PROD_IN>
 SDCT_DEV void dct8_scalar(F2 *v)
 {
-    const F2 s07 = add_in<PROD_IN, true>(v[0], v[7 * S]), s16 = add_in<PROD_IN, true>(v[S], v[6 * S]);
-    const F2 s25 = add_in<PROD_IN, true>(v[2 * S], v[5 * S]), s34 = add_in<PROD_IN, true>(v[3 * S], v[4 * S]);
-    const F2 d07 = sub_in<PROD_IN, true>(v[0], v[7 * S]), d61 = sub_in<PROD_IN, true>(v[6 * S], v[S]);
-    const F2 d25 = sub_in<PROD_IN, true>(v[2 * S], v[5 * S]), d43 = sub_in<PROD_IN, true>(v[4 * S], v[3 * S]);
+    const F2 s07 = add_in<PROD_IN, SFP>(v[0], v[7 * S]), s16 = add_in<PROD_IN, SFP>(v[S], v[6 * S]);
+    const F2 s25 = add_in<PROD_IN, SFP>(v[2 * S], v[5 * S]), s34 = add_in<PROD_IN, SFP>(v[3 * S], v[4 * S]);
+    const F2 d07 = sub_in<PROD_IN, SFP>(v[0], v[7 * S]), d61 = sub_in<PROD_IN, SFP>(v[6 * S], v[S]);
+    const F2 d25 = sub_in<PROD_IN, SFP>(v[2 * S], v[5 * S]), d43 = sub_in<PROD_IN, SFP>(v[4 * S], v[3 * S]);
     const F2 pp = add2(s07, s34), pm = sub2(s07, s34), qq = add2(s16, s25), qm = sub2(s16, s25);
 
-    v[0] = mulx<true>(add2(pp, qq), SDCT_KN);
-    v[2 * S] = mulx<true>(sadd<true>(mulx<true>(pm, SDCT_KB), mulx<true>(qm, SDCT_KE)), SDCT_KN);
-    v[4 * S] = mulx<true>(sub2(pp, qq), SDCT_KN);
-    v[6 * S] = mulx<true>(ssub<true>(mulx<true>(pm, SDCT_KE), mulx<true>(qm, SDCT_KB)), SDCT_KN);
+    v[0] = mulx<SFP>(add2(pp, qq), SDCT_KN);
+    v[2 * S] = mulx<SFP>(sadd<SFP>(mulx<SFP>(pm, SDCT_KB), mulx<SFP>(qm, SDCT_KE)), SDCT_KN);
+    v[4 * S] = mulx<SFP>(sub2(pp, qq), SDCT_KN);
+    v[6 * S] = mulx<SFP>(ssub<SFP>(mulx<SFP>(pm, SDCT_KE), mulx<SFP>(qm, SDCT_KB)), SDCT_KN);
     // odd outputs, left to right: ((t0 op t1) op t2) op t3 - every add has a product operand
-    v[S] = mulx<true>(ssub<true>(sadd<true>(ssub<true>(mulx<true>(d07, SDCT_KA), mulx<true>(d61, SDCT_KC)), mulx<true>(d25, SDCT_KD)), mulx<true>(d43, SDCT_KF)), SDCT_KN);
-    v[3 * S] = mulx<true>(sadd<true>(ssub<true>(sadd<true>(mulx<true>(d07, SDCT_KC), mulx<true>(d61, SDCT_KF)), mulx<true>(d25, SDCT_KA)), mulx<true>(d43, SDCT_KD)), SDCT_KN);
-    v[5 * S] = mulx<true>(ssub<true>(sadd<true>(sadd<true>(mulx<true>(d07, SDCT_KD), mulx<true>(d61, SDCT_KA)), mulx<true>(d25, SDCT_KF)), mulx<true>(d43, SDCT_KC)), SDCT_KN);
-    v[7 * S] = mulx<true>(sadd<true>(sadd<true>(sadd<true>(mulx<true>(d07, SDCT_KF), mulx<true>(d61, SDCT_KD)), mulx<true>(d25, SDCT_KC)), mulx<true>(d43, SDCT_KA)), SDCT_KN);
+    v[S] = mulx<SFP>(ssub<SFP>(sadd<SFP>(ssub<SFP>(mulx<SFP>(d07, SDCT_KA), mulx<SFP>(d61, SDCT_KC)), mulx<SFP>(d25, SDCT_KD)), mulx<SFP>(d43, SDCT_KF)), SDCT_KN);
+    v[3 * S] = mulx<SFP>(sadd<SFP>(ssub<SFP>(sadd<SFP>(mulx<SFP>(d07, SDCT_KC), mulx<SFP>(d61, SDCT_KF)), mulx<SFP>(d25, SDCT_KA)), mulx<SFP>(d43, SDCT_KD)), SDCT_KN);
+    v[5 * S] = mulx<SFP>(ssub<SFP>(sadd<SFP>(sadd<SFP>(mulx<SFP>(d07, SDCT_KD), mulx<SFP>(d61, SDCT_KA)), mulx<SFP>(d25, SDCT_KF)), mulx<SFP>(d43, SDCT_KC)), SDCT_KN);
+    v[7 * S] = mulx<SFP>(sadd<SFP>(sadd<SFP>(sadd<SFP>(mulx<SFP>(d07, SDCT_KF), mulx<SFP>(d61, SDCT_KD)), mulx<SFP>(d25, SDCT_KC)), mulx<SFP>(d43, SDCT_KA)), SDCT_KN);
 }
 
 // first butterfly stage of every forward graph (:148-155 / :2160-2167): exact whenever the inputs are integers
 struct Stage1 { F2 s07, s16, s25, s34, d07, d61, d25, d43; };
 
-template <int S, bool PROD_IN, bool FP>
+template <int S, bool PROD_IN, int FP>
 SDCT_DEV Stage1 stage1_of(const F2 *v)
 {
     Stage1 a;
@@ -150,9 +168,9 @@ SDCT_DEV Stage1 stage1_pixels(uint32_t p0, uint32_t p1, uint32_t q0, uint32_t q1
 // ---- 8-point forward, reference AVX2 lane order (:2160-2183); X3 = true keeps :2181's sign -----
 // how the AVX-order graph keeps its products out of FFMA2 contraction (see mulx): measured per build
 #ifndef SDCT_PAIRED_FP
-#define SDCT_PAIRED_FP 0
+#define SDCT_PAIRED_FP 2
 #endif
-constexpr bool PFP = SDCT_PAIRED_FP;
+constexpr int PFP = SDCT_PAIRED_FP;
 template <int S, bool X3>
 SDCT_DEV void dct8_paired_tail(const Stage1 &a, F2 *v)
 {
@@ -191,7 +209,7 @@ SDCT_DEV void dct8_fast_tail(const Stage1 &a, F2 *v)
     v[7 * S] = fmak(SDCT_KA, d43, fmak(SDCT_KC, d25, fmak(SDCT_KD, d61, mulk(d07, SDCT_KF))));
 }
 template <int S>
-SDCT_DEV void dct8_fast(F2 *v) { dct8_fast_tail<S>(stage1_of<S, false, true>(v), v); }
+SDCT_DEV void dct8_fast(F2 *v) { dct8_fast_tail<S>(stage1_of<S, false, 1>(v), v); }
 
 // ---- 8-point inverse (oracle/sdct_oracle.c: sdct_oracle_idct8), unnormalised -------------------
 template <int S>

@@ -106,11 +106,11 @@ int sdct_tc_inverse_operand(int layout, const float tab[64], uint16_t out[128 * 
     memset(out, 0, 128 * 64 * sizeof(uint16_t));
     for (int j = 0; j < 64; j++) {
         const int px = sdct_tc_inverse_column_pixel(j);
-        double sum = 0.0;
+        int64_t sum = 0;   // of the rounded entries: the level offset -127 must go through the same matrix as the levels
         for (int k = 0; k < 64; k++) {
             const double e = E[px * 64 + k];
-            sum += e;
             const int32_t full = (int32_t)std::llrint(std::ldexp(e, S));
+            sum += full;
             const int32_t hi = (full + 512) >> 10, lo = full - hi * 1024;
             for (int digit = 0; digit < 2; digit++) {
                 const int n = digit * 64 + j;
@@ -118,7 +118,7 @@ int sdct_tc_inverse_operand(int layout, const float tab[64], uint16_t out[128 * 
                 out[off / 2] = half_bits_of_int(digit == 0 ? hi : lo);
             }
         }
-        off_cols[j] = (float)(-127.0 * sum);
+        off_cols[j] = (float)(-127.0 * std::ldexp((double)sum, -S));
     }
     return S;
 }

@@ -3,8 +3,8 @@
 mkdir -p gpurun_out
 nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm,power.draw --format=csv > gpurun_out/smi.txt 2>&1
 nproc > gpurun_out/nproc.txt; lscpu | grep -E "Model name|^CPU\(s\)|NUMA" >> gpurun_out/nproc.txt
-timeout 1200 python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.txt 2>&1; echo "pytest rc=$?"; tail -5 gpurun_out/pytest_gpu.txt
-for v in "" i2f fold_fp; do
+timeout 1200 python -m pytest tests -m gpu -q > gpurun_out/pytest_gpu.txt 2>&1; echo "pytest rc=$?"; tail -5 gpurun_out/pytest_gpu.txt
+for v in "" $VARIANTS; do
   if [ -n "$v" ]; then export SDCT_LIB=$PWD/simd_dct_b200/variants/libsdct_$v.so; else unset SDCT_LIB; fi
   echo "== variant '${v:-default}'"
   timeout 300 python tools/prof_run.py --reps 30 fwd_B_exact fwd_A_exact fwd_C_exact fwd_A_fast fwd_B_fast fwd_C_fast rt_B_exact 2>&1 | tail -8
