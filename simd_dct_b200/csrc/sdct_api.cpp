@@ -111,23 +111,10 @@ void read_env(SdctEnv *e)
     e->host_chunk_bytes = (uint64_t)num("SDCT_HOST_CHUNK_MB", 1, 4096, 16) << 20;
     e->host_slots = (int)num("SDCT_HOST_SLOTS", 1, kSlots, 4);
     e->host_no_ramp = getenv("SDCT_HOST_NO_RAMP") != nullptr;
-    e->static_schedule = getenv("SDCT_STATIC_SCHEDULE") != nullptr;
     e->tc.no_tma = getenv("SDCT_TC_NO_TMA") != nullptr;
     e->tc.no_rgb_fuse = getenv("SDCT_TC_NO_RGB_FUSE") != nullptr;
     e->tc.no_tma_store = getenv("SDCT_TC_NO_TMA_STORE") != nullptr;
     e->tc.ablate = (uint32_t)num("SDCT_TC_ABLATE", 0, 0x7fffffff, 0);
-}
-
-// the {ticket, done} counters of the launch's stream (null when more streams were seen than there are slots: static schedule)
-uint32_t *sched_for(sdct_context *ctx, cudaStream_t st)
-{
-    if (!ctx->d_sched) return nullptr;
-    std::lock_guard<std::mutex> lock(ctx->sched_mu);
-    for (int i = 0; i < ctx->sched_used; i++)
-        if (ctx->sched_streams[i] == st) return ctx->d_sched + 2 * i;
-    if (ctx->sched_used == sdct_context::kSchedSlots) return nullptr;
-    ctx->sched_streams[ctx->sched_used] = st;
-    return ctx->d_sched + 2 * ctx->sched_used++;
 }
 
 int run_device(sdct_context *ctx, int op, const sdct_job *j, const uint8_t *pixels, uint8_t *coefs,
@@ -162,6 +149,7 @@ int run_device(sdct_context *ctx, int op, const sdct_job *j, const uint8_t *pixe
         return aligned(pixels, a) && (pstr & (a - 1)) == 0 && (op != SDCT_K_OP_ROUNDTRIP || aligned(pixels_out, a));
     };
     p.pixel_vec = (pix_aligned(16) && g.comps == 1 && (g.bpr & 1) == 0) ? 2 : (pix_aligned(8) ? 1 : 0);
+    p.pixel_aligned16 = pix_aligned(16);
     const uint64_t cstr = j->coef_frame_stride | j->coef_comp_stride;
     p.coef_aligned16 = coefs && aligned(coefs, 16) && (cstr & 15) == 0;
     p.coef_aligned4 = coefs && aligned(coefs, 4) && ((cstr | j->coef_plane_stride) & 3) == 0;
@@ -221,9 +209,7 @@ int run_device(sdct_context *ctx, int op, const sdct_job *j, const uint8_t *pixe
         std::lock_guard<std::mutex> lock(ctx->tc_maps_mu);
         CU_TRY(sdct_k_launch_tc(op, j->layout, &p, &ctx->env.tc, &ctx->tc_maps, stream ? stream : ctx->stream));
     } else {
-        cudaStream_t st = stream ? stream : ctx->stream;
-        p.sched = ctx->env.static_schedule ? nullptr : sched_for(ctx, st);
-        CU_TRY(sdct_k_launch(op, j->layout, mode, x3, &p, st));
+        CU_TRY(sdct_k_launch(op, j->layout, mode, x3, &p, stream ? stream : ctx->stream));
     }
     ctx->launches.fetch_add(1, std::memory_order_relaxed);
     return SDCT_OK;
@@ -277,8 +263,6 @@ int sdct_create(int device, sdct_context **out)
     c->sm_count = prop.multiProcessorCount;
     read_env(&c->env);
     CU_TRY(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
-    CU_TRY(cudaMalloc((void **)&c->d_sched, 2 * sdct_context::kSchedSlots * sizeof(uint32_t)));
-    CU_TRY(cudaMemset(c->d_sched, 0, 2 * sdct_context::kSchedSlots * sizeof(uint32_t)));
     {   // tensor-core B operands (16 KiB each)
         std::vector<uint16_t> op(128 * 64);
         const int layouts[2] = {SDCT_K_LAYOUT_A, SDCT_K_LAYOUT_B};
@@ -300,7 +284,6 @@ void sdct_destroy(sdct_context *c)
     c->pipes.clear();
     if (c->stream) { cudaStreamSynchronize(c->stream); cudaStreamDestroy(c->stream); }
     cudaFree(c->d_tc_matrix[0]); cudaFree(c->d_tc_matrix[1]);
-    cudaFree(c->d_sched);
     for (auto &e : c->inv_cache) cudaFree(e.d);
     delete c;
 }

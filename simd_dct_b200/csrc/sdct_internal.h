@@ -46,7 +46,6 @@ struct SdctEnv {
     uint64_t host_chunk_bytes = 16ull << 20;
     int host_slots = 4;
     bool host_no_ramp = false;
-    bool static_schedule = false;   // $SDCT_STATIC_SCHEDULE: fp32 kernels walk a static tile schedule (no ticket counter)
     SdctTcOptions tc;
 };
 
@@ -65,13 +64,6 @@ struct sdct_context {
     InvOperand inv_cache[8];
     uint64_t inv_clock = 0;
     std::mutex inv_mu;
-    // dynamic tile schedule of the fp32 kernels: one self-resetting {ticket, done} counter pair per stream seen (kernels
-    // on one stream run in order, so they can share a pair; kernels on different streams may overlap and must not)
-    uint32_t *d_sched = nullptr;
-    static constexpr int kSchedSlots = 64;
-    cudaStream_t sched_streams[kSchedSlots] = {};
-    int sched_used = 0;
-    std::mutex sched_mu;
     SdctTcMapCache tc_maps;   // encoded CUtensorMaps keyed by (pointer, geometry); guarded by its own mutex
     std::mutex tc_maps_mu;
 };

@@ -392,201 +392,11 @@ SDCT_DEV void forward_tiles(const KParams &p, uint8_t *smem)
 }
 
 
-// ---- dynamic schedule: warps draw 64-block tiles from a ticket counter ---------------------------------------------
-// With a static tile list the CTAs of an SM do not finish together: the warp schedulers favour some warps, those run
-// ahead, and the rest of the launch runs with one or two warps per scheduler, which cannot keep the FMA pipe fed (ncu:
-// 2.3 of 3 warps active on average).  Here every WARP is its own worker (the aligned paths need no CTA barrier: a warp
-// stages and flushes whole 16-byte chunks of its own 64 blocks): first tile = its index in the grid, then tickets from
-// p.sched[0], drawn one iteration ahead of use so that the atomic's latency hides behind a tile's arithmetic.  The
-// last warp to finish (p.sched[1]) resets both counters for the next launch on the stream.
-constexpr int WB = 64;                        // blocks per warp tile
-constexpr int W_STAGE = WB * A_SLOT;          // A: 64 slots of 80 B; B: 8 groups of 528 B; C: 64 plane rows of 64 B
-constexpr int WC_PITCH = WB;
-constexpr int W_IN = 8 * 32 * 16;             // prefetched pixels of a warp tile
-constexpr int W_SMEM = 2 * W_STAGE + 2 * W_IN;
-static_assert((TB / 32) * W_SMEM <= 2 * STAGE_BYTES + 2 * IN_STAGE_BYTES, "the warp-tile form fits the CTA-tile form's shared memory");
-
-struct WTile { uint32_t fc, chunk; };
-SDCT_DEV WTile wtile_of(const KParams &p, uint32_t wt)
-{
-    WTile w;
-    w.fc = fastdiv(wt, p.div_wchunks);
-    w.chunk = wt - w.fc * p.wchunks;
-    return w;
-}
-
-template <int LAYOUT>
-SDCT_DEV BlockPos locate_w(const KParams &p, const Tile &t, uint32_t lane)
-{
-    BlockPos b;
-    b.comp = t.comp;
-#pragma unroll
-    for (int k = 0; k < 2; k++) {
-        const uint32_t slot = (LAYOUT == SDCT_K_LAYOUT_A) ? lane + k * 32 : 2 * lane + k;
-        b.valid[k] = slot < t.count;
-        const uint32_t nl = t.n0 + (b.valid[k] ? slot : 0);
-        const uint32_t r = fastdiv(nl, p.div_bpr);
-        const uint32_t bx = nl - r * p.bpr;
-        const uint32_t row = r + p.row0;
-        const uint32_t band = p.eyes == 2 ? row >> 1 : row, eye = p.eyes == 2 ? row & 1 : 0;
-        b.px[k] = t.pix + (uint64_t)eye * p.eye_stride + (uint64_t)band * 8 * p.pitch + (uint64_t)bx * 8 * p.comps;
-    }
-    return b;
-}
-
-template <int VEC>
-SDCT_DEV void prefetch_pair_w(uint8_t *stage, uint32_t lane, const BlockPos &b, uint64_t pitch)
-{
-    uint8_t *slot = stage + lane * 16;
-#pragma unroll
-    for (int r = 0; r < 8; r++) {
-        if (VEC == 2) {
-            cp_async16(slot + r * 512, b.px[0] + r * pitch);
-        } else {
-            cp_async8(slot + r * 512, b.px[0] + r * pitch);
-            cp_async8(slot + r * 512 + 8, b.px[1] + r * pitch);
-        }
-    }
-}
-
-SDCT_DEV void read_prefetched_w(const uint8_t *stage, uint32_t lane, uint32_t wp[16], uint32_t wq[16])
-{
-    const uint8_t *slot = stage + lane * 16;
-#pragma unroll
-    for (int r = 0; r < 8; r++) {
-        const uint4 v = *reinterpret_cast<const uint4 *>(slot + r * 512);
-        wp[2 * r] = v.x; wp[2 * r + 1] = v.y; wq[2 * r] = v.z; wq[2 * r + 1] = v.w;
-    }
-}
-
-template <int LAYOUT>
-SDCT_DEV void stage_levels_w(uint8_t *sm, uint32_t lane, const F2 b[64])
-{
-    if (LAYOUT == SDCT_K_LAYOUT_B) {
-        uint16_t *d = reinterpret_cast<uint16_t *>(sm + (lane >> 2) * B_GROUP_PITCH + 2 * (lane & 3));
-#pragma unroll
-        for (int i = 0; i < 64; i++) d[i * 4] = (uint16_t)pack_pq(b[i]);
-    } else if (LAYOUT == SDCT_K_LAYOUT_C) {
-        uint16_t *d = reinterpret_cast<uint16_t *>(sm + 2 * lane);
-#pragma unroll
-        for (int i = 0; i < 64; i++) d[i * (WC_PITCH / 2)] = (uint16_t)pack_pq(b[i]);
-    } else {
-#pragma unroll
-        for (int k = 0; k < 2; k++) {
-            uint4 *d = reinterpret_cast<uint4 *>(sm + (lane + k * 32) * A_SLOT);
-#pragma unroll
-            for (int j = 0; j < 4; j++) {
-                uint32_t w[4];
-#pragma unroll
-                for (int q = 0; q < 4; q++) {
-                    const int v = 2 * j + (q >> 1), u0 = 4 * (q & 1);
-#define SDCT_L(u) (k ? b[(u) * 8 + v].y : b[(u) * 8 + v].x)
-                    w[q] = pack4_sat(SDCT_L(u0), SDCT_L(u0 + 1), SDCT_L(u0 + 2), SDCT_L(u0 + 3));
-#undef SDCT_L
-                }
-                d[j] = make_uint4(w[0], w[1], w[2], w[3]);
-            }
-        }
-    }
-}
-
-// the warp's staged image -> global memory: eight unconditional 16-byte loads, eight predicated 16-byte stores
-template <int LAYOUT, bool COMPL>
-SDCT_DEV void flush_w(const uint8_t *sm, uint32_t lane, const KParams &p, const FlushJob &f)
-{
-    const uint32_t m32 = COMPL ? 0xffffffffu : 0u;
-    uint4 v[8];
-    if (LAYOUT == SDCT_K_LAYOUT_C) {          // chunk j: plane row 8j + lane / 4, bytes 16 (lane % 4) ..
-        const uint32_t c = 16u * (lane & 3);
-        const uint8_t *src = sm + (lane >> 2) * WC_PITCH + c;
-#pragma unroll
-        for (int j = 0; j < 8; j++) v[j] = *reinterpret_cast<const uint4 *>(src + j * 8 * WC_PITCH);
-        uint8_t *dst = f.coef + (uint64_t)(lane >> 2) * p.coef_plane_stride + f.n_first + c;
-        const uint64_t step = 8 * p.coef_plane_stride;
-#pragma unroll
-        for (int j = 0; j < 8; j++, dst += step) st_global_v4_if(dst, xor4(v[j], m32), c < f.count);
-    } else if (LAYOUT == SDCT_K_LAYOUT_B) {   // chunk j: group j, piece lane
-        const uint8_t *src = sm + lane * 16u;
-#pragma unroll
-        for (int j = 0; j < 8; j++) v[j] = *reinterpret_cast<const uint4 *>(src + j * B_GROUP_PITCH);
-        uint8_t *dst = f.coef + f.n_first * 64 + 16ull * lane;
-#pragma unroll
-        for (int j = 0; j < 8; j++) st_global_v4_if(dst + j * 512, xor4(v[j], m32), 8u * j < f.count);
-    } else {                                   // chunk j: block 8j + lane % 8, piece lane / 8 (conflict-free reads)
-        const uint32_t s0 = lane & 7, piece = lane >> 3;
-        const uint8_t *src = sm + s0 * A_SLOT + piece * 16u;
-#pragma unroll
-        for (int j = 0; j < 8; j++) v[j] = *reinterpret_cast<const uint4 *>(src + j * 8 * A_SLOT);
-        uint8_t *dst = f.coef + (f.n_first + s0) * 64 + 16ull * piece;
-#pragma unroll
-        for (int j = 0; j < 8; j++) st_global_v4_if(dst + j * 512, xor4(v[j], m32), 8u * j + s0 < f.count);
-    }
-}
-
-template <int LAYOUT, int MODE, bool X3, int VEC>
-SDCT_DEV void forward_warp_tiles(const KParams &p, uint8_t *smem)
-{
-    constexpr bool COMPL = complemented<LAYOUT, MODE>();
-    const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    uint8_t *out_stage = smem + warp * W_SMEM, *in_stage = out_stage + 2 * W_STAGE;
-    const uint32_t workers = gridDim.x * (TB / 32);
-    uint32_t cur = blockIdx.x * (TB / 32) + warp;
-    auto draw = [&]() -> uint32_t {            // the ticket is consumed (broadcast) one iteration later
-        uint32_t v = 0;
-        // (atom.inc, not atomicAdd / atom.add: ptxas turns a warp-uniform add into its warp-aggregation pattern, whose broadcast shuffle waits for
-        // the atomic's result on the spot)
-        if (lane == 0) asm volatile("atom.global.inc.u32 %0, [%1], 0x7fffffff;" : "=r"(v) : "l"(p.sched) : "memory");
-        return v;
-    };
-    auto take = [&](uint32_t v) -> uint32_t { return workers + __shfl_sync(0xffffffffu, v, 0); };
-    if (cur < p.wtiles) {
-        Tile t = tile_at<1, WB>(p, wtile_of(p, cur));
-        prefetch_pair_w<VEC>(in_stage, lane, locate_w<LAYOUT>(p, t, lane), p.pitch);
-        cp_async_commit();
-        uint32_t nxt = take(draw());
-        uint32_t ticket = nxt < p.wtiles ? draw() : 0u;
-        FlushJob pending = {nullptr, 0, 0};
-        for (uint32_t it = 0;; it++) {
-            const bool more = nxt < p.wtiles;
-            Tile tn = t;
-            if (more) {
-                tn = tile_at<1, WB>(p, wtile_of(p, nxt));
-                prefetch_pair_w<VEC>(in_stage + ((it + 1) & 1) * W_IN, lane, locate_w<LAYOUT>(p, tn, lane), p.pitch);
-            }
-            cp_async_commit();
-            cp_async_wait<1>();
-            uint32_t wp[16], wq[16];
-            read_prefetched_w(in_stage + (it & 1) * W_IN, lane, wp, wq);
-            flush_w<LAYOUT, COMPL>(out_stage + ((it + 1) & 1) * W_STAGE, lane, p, pending);
-            F2 v[64];
-            forward_pair<LAYOUT, MODE, X3>(wp, wq, p.tab, v);
-            uint8_t *sm = out_stage + (it & 1) * W_STAGE;
-            stage_levels_w<LAYOUT>(sm, lane, v);
-            __syncwarp();
-            pending.coef = t.coef; pending.n_first = (uint64_t)p.row0 * p.bpr + t.n0; pending.count = t.count;
-            if (!more) { flush_w<LAYOUT, COMPL>(sm, lane, p, pending); break; }
-            t = tn;
-            nxt = take(ticket);                       // drawn a whole tile ago
-            if (nxt < p.wtiles) ticket = draw();
-        }
-    }
-    if (lane == 0) {
-        __threadfence();
-        if (atomicAdd(p.sched + 1, 1u) == workers - 1) {   // every other warp has drawn its last ticket
-            p.sched[0] = 0;
-            p.sched[1] = 0;
-        }
-    }
-}
 
 template <int LAYOUT, int MODE, bool X3, int COMPS, int VEC>
 __global__ void __launch_bounds__(SDCT_TB, 3) forward_kernel(const __grid_constant__ KParams p)
 {
     extern __shared__ __align__(16) uint8_t smem[];
-    if (prefetchable<COMPS, VEC>() && COMPS == 1 && p.sched != nullptr && warp_local_coefs<LAYOUT>(p)) {
-        forward_warp_tiles<LAYOUT, MODE, X3, (VEC ? VEC : 1)>(p, smem);
-        return;
-    }
     if (warp_local_coefs<LAYOUT>(p)) forward_tiles<LAYOUT, MODE, X3, COMPS, VEC, true>(p, smem);
     else forward_tiles<LAYOUT, MODE, X3, COMPS, VEC, false>(p, smem);
 }
@@ -835,6 +645,124 @@ __global__ void __launch_bounds__(SDCT_TB, 3) roundtrip_kernel(const __grid_cons
     }
 }
 
+
+// ---- interleaved 3-component pixels on the OUTPUT side (inverse, round trip) ---------------------------------------
+// A CTA decodes the three components of the same 256 blocks one after the other, stages their pixel rows planar in
+// shared memory ([component][pixel row][block slot][8 bytes]) and then writes interleaved rows: a thread takes the 16
+// pixels of two adjacent blocks of one row (three 16-byte reads), interleaves them with 24 PRMTs into 48 contiguous
+// bytes and stores three 16-byte vectors, so that every output byte crosses HBM once, in full sectors.  Needs 16-byte
+// aligned pixel rows and an even number of blocks per row (a slot pair never straddles a block-row wrap); other
+// geometries keep the byte-store path of store_block.
+constexpr int PIX_IMG = CB * 64;   // 16 KiB per component
+
+template <int LAYOUT>
+SDCT_DEV void stage_pixels(uint8_t *img, const F2 v[64])
+{
+    const uint32_t t = threadIdx.x;
+#pragma unroll
+    for (int r = 0; r < 8; r++) {
+        const uint32_t p0 = pack4_sat(v[8 * r].x, v[8 * r + 1].x, v[8 * r + 2].x, v[8 * r + 3].x), p1 = pack4_sat(v[8 * r + 4].x, v[8 * r + 5].x, v[8 * r + 6].x, v[8 * r + 7].x);
+        const uint32_t q0 = pack4_sat(v[8 * r].y, v[8 * r + 1].y, v[8 * r + 2].y, v[8 * r + 3].y), q1 = pack4_sat(v[8 * r + 4].y, v[8 * r + 5].y, v[8 * r + 6].y, v[8 * r + 7].y);
+        if (LAYOUT == SDCT_K_LAYOUT_A) {   // slots t, t + 128
+            *reinterpret_cast<uint2 *>(img + r * (CB * 8) + t * 8) = make_uint2(p0, p1);
+            *reinterpret_cast<uint2 *>(img + r * (CB * 8) + (t + TB) * 8) = make_uint2(q0, q1);
+        } else {                           // slots 2t, 2t + 1
+            *reinterpret_cast<uint4 *>(img + r * (CB * 8) + t * 16) = make_uint4(p0, p1, q0, q1);
+        }
+    }
+}
+
+// planar images of the three components -> interleaved pixel rows of the tile's blocks in `out_frame`
+SDCT_DEV void flush_rgb(const uint8_t *img3, const KParams &p, const Tile &t, uint8_t *out_frame)
+{
+    const uint32_t k = threadIdx.x, slot = 2 * k;
+    if (slot >= t.count) return;
+    const uint32_t nl = t.n0 + slot;
+    const uint32_t r0 = fastdiv(nl, p.div_bpr), bx = nl - r0 * p.bpr, row = r0 + p.row0;
+    const uint32_t band = p.eyes == 2 ? row >> 1 : row, eye = p.eyes == 2 ? row & 1 : 0;
+    uint8_t *dst = out_frame + (uint64_t)eye * p.eye_stride + (uint64_t)band * 8 * p.pitch + (uint64_t)bx * 24;
+#pragma unroll 2
+    for (int r = 0; r < 8; r++, dst += p.pitch) {
+        const uint4 R = *reinterpret_cast<const uint4 *>(img3 + r * (CB * 8) + k * 16);
+        const uint4 G = *reinterpret_cast<const uint4 *>(img3 + PIX_IMG + r * (CB * 8) + k * 16);
+        const uint4 B = *reinterpret_cast<const uint4 *>(img3 + 2 * PIX_IMG + r * (CB * 8) + k * 16);
+        const uint32_t rr[4] = {R.x, R.y, R.z, R.w}, gg[4] = {G.x, G.y, G.z, G.w}, bb[4] = {B.x, B.y, B.z, B.w};
+        uint32_t o[12];
+#pragma unroll
+        for (int q = 0; q < 4; q++) {   // four pixels (R, G, B words q) -> 12 bytes
+            o[3 * q] = __byte_perm(__byte_perm(rr[q], gg[q], 0x1040), bb[q], 0x3410);       // R0 G0 B0 R1
+            o[3 * q + 1] = __byte_perm(__byte_perm(gg[q], rr[q], 0x2601), bb[q], 0x3250);   // G1 B1 R2 G2
+            o[3 * q + 2] = __byte_perm(__byte_perm(bb[q], rr[q], 0x3072), gg[q], 0x3710);   // B2 R3 G3 B3
+        }
+        uint4 *d = reinterpret_cast<uint4 *>(dst);
+        d[0] = make_uint4(o[0], o[1], o[2], o[3]);
+        d[1] = make_uint4(o[4], o[5], o[6], o[7]);
+        d[2] = make_uint4(o[8], o[9], o[10], o[11]);
+    }
+}
+
+// can the output side take the staged interleave?  (uniform per launch; the launcher decides)
+static inline bool rgb_out_fusable(const KParams &p) { return p.comps == 3 && p.pixel_aligned16 && (p.bpr & 1) == 0; }
+
+// p.tiles counts PIXEL tiles here (chunks * frames); the three components are an inner loop
+template <int LAYOUT>
+__global__ void __launch_bounds__(SDCT_TB, 2) inverse_rgb_kernel(const __grid_constant__ KParams p)
+{
+    extern __shared__ __align__(16) uint8_t smem[];
+    uint8_t *pix = smem + 2 * STAGE_BYTES;
+    TileWalk w;
+    w.init(p, 0, 1);
+    for (uint32_t it = 0; w.tile < p.tiles; w.next(p)) {
+        const Tile t = tile_at<1, CB>(p, w);
+#pragma unroll 1
+        for (uint32_t c = 0; c < 3; c++, it++) {
+            Tile tc = t;
+            tc.coef += (uint64_t)c * p.coef_comp_stride;
+            uint8_t *sm = smem + (it & 1) * STAGE_BYTES;
+            fetch_coefs<LAYOUT>(sm, p, tc);
+            __syncthreads();
+            F2 v[64];
+            unstage_levels<LAYOUT>(sm, v);
+            inverse_pair<LAYOUT>(p.tab, p.off, v);
+            stage_pixels<LAYOUT>(pix + c * PIX_IMG, v);
+        }
+        __syncthreads();
+        flush_rgb(pix, p, t, const_cast<uint8_t *>(t.pix));
+        __syncthreads();
+    }
+}
+
+template <int LAYOUT, int MODE, bool X3>
+__global__ void __launch_bounds__(SDCT_TB, 3) roundtrip_rgb_kernel(const __grid_constant__ KParams p)
+{
+    extern __shared__ __align__(16) uint8_t pix[];
+    TileWalk w;
+    w.init(p, 0, 1);
+    for (; w.tile < p.tiles; w.next(p)) {
+        const Tile t = tile_at<1, CB>(p, w);
+        BlockPos b = locate<LAYOUT>(p, t);
+#pragma unroll 1
+        for (uint32_t c = 0; c < 3; c++) {
+            b.comp = c;
+            uint32_t wp[16], wq[16];
+            load_pair<3, 1>(b, p.pitch, wp, wq);
+            F2 v[64];
+            forward_pair<LAYOUT, MODE, X3>(wp, wq, p.tab, v);
+#pragma unroll
+            for (int i = 0; i < 64; i++) {
+                uint32_t h = pack_pq(v[i]);
+                if (complemented<LAYOUT, MODE>()) h = ~h;
+                v[i] = make_float2(byte_to_float(h, 0), byte_to_float(h, 1));
+            }
+            inverse_pair<LAYOUT>(p.tab2, p.off, v);
+            stage_pixels<LAYOUT>(pix + c * PIX_IMG, v);
+        }
+        __syncthreads();
+        flush_rgb(pix, p, t, p.pixels_out + (t.pix - p.pixels));
+        __syncthreads();
+    }
+}
+
 #if SDCT_PART == 0
 // ---- self-test: the 8-point kernels on raw floats (bitwise oracle comparison in tests/) ----------
 // data: n vectors of 8 floats, transformed in place.  kind: 0 scalar, 1 paired, 2 paired+X3,
@@ -918,6 +846,20 @@ static cudaError_t launch_fwd2(int op, const KParams &p, unsigned grid, cudaStre
             if (p.pixel_vec >= 1) SDCT_GO(K, 3, 1); else SDCT_GO(K, 3, 0);                             \
         }                                                                                              \
     } while (0)
+    if (op == SDCT_K_OP_ROUNDTRIP && rgb_out_fusable(p)) {   // staged interleave on the output side; tiles = pixel tiles
+        KParams q = p;
+        q.tiles = p.tiles / 3;
+        const unsigned resident3 = 3u * (p.sm_count ? p.sm_count : 148u);
+        static std::atomic<uint64_t> attr_done{0};
+        uint64_t bit;
+        if (attr_pending(attr_done, &bit)) {
+            cudaError_t e = cudaFuncSetAttribute(roundtrip_rgb_kernel<LAYOUT, MODE, X3>, cudaFuncAttributeMaxDynamicSharedMemorySize, 3 * PIX_IMG);
+            if (e != cudaSuccess) return e;
+            attr_done.fetch_or(bit, std::memory_order_release);
+        }
+        roundtrip_rgb_kernel<LAYOUT, MODE, X3><<<(q.tiles < resident3 ? q.tiles : resident3), SDCT_TB, 3 * PIX_IMG, s>>>(q);
+        return cudaGetLastError();
+    }
     if (op == SDCT_K_OP_FORWARD) SDCT_PICK(forward_kernel);
     else SDCT_PICK(roundtrip_kernel);
 #undef SDCT_PICK
@@ -940,6 +882,21 @@ static cudaError_t launch_inv2(const KParams &p, unsigned grid, cudaStream_t s)
         inverse_kernel<LAYOUT, C, V><<<grid, SDCT_TB, smem, s>>>(p);                                                     \
         return cudaGetLastError();                                                                                       \
     } while (0)
+    if (rgb_out_fusable(p)) {   // staged interleave on the output side; tiles = pixel tiles
+        KParams q = p;
+        q.tiles = p.tiles / 3;
+        const unsigned resident2 = 2u * (p.sm_count ? p.sm_count : 148u);
+        const size_t smem_rgb = 2 * STAGE_BYTES + 3 * PIX_IMG;
+        static std::atomic<uint64_t> attr_done{0};
+        uint64_t bit;
+        if (attr_pending(attr_done, &bit)) {
+            cudaError_t e = cudaFuncSetAttribute(inverse_rgb_kernel<LAYOUT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_rgb);
+            if (e != cudaSuccess) return e;
+            attr_done.fetch_or(bit, std::memory_order_release);
+        }
+        inverse_rgb_kernel<LAYOUT><<<(q.tiles < resident2 ? q.tiles : resident2), SDCT_TB, smem_rgb, s>>>(q);
+        return cudaGetLastError();
+    }
     if (p.comps == 1) {
         if (p.pixel_vec == 2 && LAYOUT != SDCT_K_LAYOUT_A) SDCT_INV(1, 2);
         else if (p.pixel_vec >= 1) SDCT_INV(1, 1);
@@ -987,14 +944,6 @@ extern "C" cudaError_t sdct_k_launch(int op, int layout, int mode, int x3, const
     p.tiles = (uint32_t)tiles;
     p.div_chunks = make_fastdiv(p.chunks);
     p.div_bpr = make_fastdiv(p.bpr);
-    {   // the dynamic schedule's 64-block warp tiles (forward, aligned single-plane geometry; decided in the kernel)
-        const unsigned long long blocks = (unsigned long long)p.rows * p.bpr;
-        p.wchunks = (uint32_t)((blocks + 63) / 64);
-        const unsigned long long wt = (unsigned long long)p.wchunks * p.comps * p.frames;
-        if (op != SDCT_K_OP_FORWARD || p.comps != 1 || wt > 0x7fff0000ull) p.sched = nullptr;
-        p.wtiles = (uint32_t)wt;
-        p.div_wchunks = make_fastdiv(p.wchunks);
-    }
     // persistent CTAs: three per SM (168 registers/thread), each walking tiles blockIdx.x, +grid, ...
     const unsigned resident = 3u * (p.sm_count ? p.sm_count : 148u);
     const unsigned grid = (unsigned)(tiles < resident ? tiles : resident);

@@ -37,16 +37,12 @@ struct KParams {
     uint32_t sm_count;        // SMs of the device (persistent grid size)
     uint32_t pixel_vec;       // 0 = byte access, 1 = 8-byte rows, 2 = 16-byte rows for an adjacent block pair
     uint32_t coef_aligned16, coef_aligned4;
+    uint32_t pixel_aligned16; // pixel base pointers and strides are multiples of 16 (whatever the component count)
     // scale tables, each value duplicated for the two packed lanes (P, Q)
     float2 tab[64];           // forward: quantiser scale; inverse: dequantiser scale
     float2 tab2[64];          // roundtrip: dequantiser scale
     float2 off[64];           // inverse / roundtrip: -127 * dequantiser scale
     KFastDiv div_chunks, div_bpr;  // tensor-core kernels
-    // fp32 forward kernels, dynamic schedule: warps draw 64-block tiles from a ticket counter (sched[0]; sched[1] counts
-    // the warps that have finished - the last one resets both).  null: static schedule of 256-block CTA tiles.
-    uint32_t *sched;
-    uint32_t wchunks, wtiles;      // 64-block tiles per (frame, component) / in total
-    KFastDiv div_wchunks;
     uint32_t tc_ablate;       // profiling only ($SDCT_TC_ABLATE): bit0 no MMA, 1 no A write, 2 no epilogue, 3 no stores, 4 no loads
     const void *tc_matrix;    // tensor-core kernels: the 16 KiB B operand (fp16 digits of 2^22 C(x)C, UMMA canonical layout)
     // tensor-core kernels, TMA pixel path: CUtensorMap over the pixels as u32[frame][eye][row][W / 4]

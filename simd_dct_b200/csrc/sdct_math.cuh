@@ -100,7 +100,7 @@ template <bool PROD_IN, int FP> SDCT_DEV F2 sub_in(F2 a, F2 b) { return PROD_IN 
 // ---- 8-point forward, reference scalar order (:148-171); v[0], v[S], ... v[7S] ----------------
 // how the scalar-order graph keeps its products out of FFMA2 contraction (see mulx): measured per build
 #ifndef SDCT_SCALAR_FP
-#define SDCT_SCALAR_FP 1
+#define SDCT_SCALAR_FP 2
 #endif
 constexpr int SFP = SDCT_SCALAR_FP;
 template <int S, bool PROD_IN>
@@ -171,42 +171,57 @@ SDCT_DEV Stage1 stage1_pixels(uint32_t p0, uint32_t p1, uint32_t q0, uint32_t q1
 #define SDCT_PAIRED_FP 2
 #endif
 constexpr int PFP = SDCT_PAIRED_FP;
+// even outputs X0, X2, X4, X6 from the four sums, odd outputs X1, X3, X5, X7 from the four differences: the two halves
+// share nothing
+SDCT_DEV void paired_even(F2 s07, F2 s16, F2 s25, F2 s34, F2 &x0, F2 &x2, F2 &x4, F2 &x6)
+{
+    const F2 pp = add2(s07, s34), pm = sub2(s07, s34), qq = add2(s16, s25), qm = sub2(s16, s25);
+    x0 = mulx<PFP>(add2(pp, qq), SDCT_KN);
+    x4 = mulx<PFP>(sub2(pp, qq), SDCT_KN);
+    x2 = mulx<PFP>(sadd<PFP>(mulx<PFP>(pm, SDCT_KB), mulx<PFP>(qm, SDCT_KE)), SDCT_KN);
+    x6 = mulx<PFP>(ssub<PFP>(mulx<PFP>(pm, SDCT_KE), mulx<PFP>(qm, SDCT_KB)), SDCT_KN);
+}
+template <bool X3>
+SDCT_DEV void paired_odd(F2 d07, F2 d61, F2 d25, F2 d43, F2 &x1, F2 &x3, F2 &x5, F2 &x7)
+{
+    // pairwise: (t0 op t1) op (t2 op t3); the outer add sees two sums -> packed
+    x1 = mulx<PFP>(add2(ssub<PFP>(mulx<PFP>(d07, SDCT_KA), mulx<PFP>(d61, SDCT_KC)), ssub<PFP>(mulx<PFP>(d25, SDCT_KD), mulx<PFP>(d43, SDCT_KF))), SDCT_KN);
+    const F2 x3r = X3 ? sadd<PFP>(mulx<PFP>(d25, SDCT_KA), mulx<PFP>(d43, SDCT_KD)) : ssub<PFP>(mulx<PFP>(d25, SDCT_KA), mulx<PFP>(d43, SDCT_KD));
+    x3 = mulx<PFP>(sub2(sadd<PFP>(mulx<PFP>(d07, SDCT_KC), mulx<PFP>(d61, SDCT_KF)), x3r), SDCT_KN);
+    x5 = mulx<PFP>(add2(sadd<PFP>(mulx<PFP>(d07, SDCT_KD), mulx<PFP>(d61, SDCT_KA)), ssub<PFP>(mulx<PFP>(d25, SDCT_KF), mulx<PFP>(d43, SDCT_KC))), SDCT_KN);
+    x7 = mulx<PFP>(add2(sadd<PFP>(mulx<PFP>(d07, SDCT_KF), mulx<PFP>(d61, SDCT_KD)), sadd<PFP>(mulx<PFP>(d25, SDCT_KC), mulx<PFP>(d43, SDCT_KA))), SDCT_KN);
+}
 template <int S, bool X3>
 SDCT_DEV void dct8_paired_tail(const Stage1 &a, F2 *v)
 {
-    const F2 s07 = a.s07, s16 = a.s16, s25 = a.s25, s34 = a.s34, d07 = a.d07, d61 = a.d61, d25 = a.d25, d43 = a.d43;
-    const F2 pp = add2(s07, s34), pm = sub2(s07, s34), qq = add2(s16, s25), qm = sub2(s16, s25);
-
-    v[0] = mulx<PFP>(add2(pp, qq), SDCT_KN);
-    v[4 * S] = mulx<PFP>(sub2(pp, qq), SDCT_KN);
-    v[2 * S] = mulx<PFP>(sadd<PFP>(mulx<PFP>(pm, SDCT_KB), mulx<PFP>(qm, SDCT_KE)), SDCT_KN);
-    v[6 * S] = mulx<PFP>(ssub<PFP>(mulx<PFP>(pm, SDCT_KE), mulx<PFP>(qm, SDCT_KB)), SDCT_KN);
-    // odd outputs, pairwise: (t0 op t1) op (t2 op t3); the outer add sees two sums -> packed
-    v[S] = mulx<PFP>(add2(ssub<PFP>(mulx<PFP>(d07, SDCT_KA), mulx<PFP>(d61, SDCT_KC)), ssub<PFP>(mulx<PFP>(d25, SDCT_KD), mulx<PFP>(d43, SDCT_KF))), SDCT_KN);
-    const F2 x3r = X3 ? sadd<PFP>(mulx<PFP>(d25, SDCT_KA), mulx<PFP>(d43, SDCT_KD)) : ssub<PFP>(mulx<PFP>(d25, SDCT_KA), mulx<PFP>(d43, SDCT_KD));
-    v[3 * S] = mulx<PFP>(sub2(sadd<PFP>(mulx<PFP>(d07, SDCT_KC), mulx<PFP>(d61, SDCT_KF)), x3r), SDCT_KN);
-    v[5 * S] = mulx<PFP>(add2(sadd<PFP>(mulx<PFP>(d07, SDCT_KD), mulx<PFP>(d61, SDCT_KA)), ssub<PFP>(mulx<PFP>(d25, SDCT_KF), mulx<PFP>(d43, SDCT_KC))), SDCT_KN);
-    v[7 * S] = mulx<PFP>(add2(sadd<PFP>(mulx<PFP>(d07, SDCT_KF), mulx<PFP>(d61, SDCT_KD)), sadd<PFP>(mulx<PFP>(d25, SDCT_KC), mulx<PFP>(d43, SDCT_KA))), SDCT_KN);
+    paired_even(a.s07, a.s16, a.s25, a.s34, v[0], v[2 * S], v[4 * S], v[6 * S]);
+    paired_odd<X3>(a.d07, a.d61, a.d25, a.d43, v[S], v[3 * S], v[5 * S], v[7 * S]);
 }
 template <int S, bool PROD_IN, bool X3>
 SDCT_DEV void dct8_paired(F2 *v) { dct8_paired_tail<S, X3>(stage1_of<S, PROD_IN, PFP>(v), v); }
 
 // ---- 8-point forward, FAST (oracle/sdct_oracle.c: sdct_oracle_dct8_fast), unnormalised ---------
 // explicit FMAs; no multiply feeds a plain add, so there is nothing left for ptxas to contract
+SDCT_DEV void fast_even(F2 s07, F2 s16, F2 s25, F2 s34, F2 &x0, F2 &x2, F2 &x4, F2 &x6)
+{
+    const F2 pp = add2(s07, s34), pm = sub2(s07, s34), qq = add2(s16, s25), qm = sub2(s16, s25);
+    x0 = add2(pp, qq);
+    x4 = sub2(pp, qq);
+    x2 = fmak(SDCT_KB, pm, mulk(qm, SDCT_KE));
+    x6 = fmak(SDCT_KE, pm, mulk(qm, -SDCT_KB));
+}
+SDCT_DEV void fast_odd(F2 d07, F2 d61, F2 d25, F2 d43, F2 &x1, F2 &x3, F2 &x5, F2 &x7)
+{
+    x1 = fmak(-SDCT_KF, d43, fmak(SDCT_KD, d25, fmak(-SDCT_KC, d61, mulk(d07, SDCT_KA))));
+    x3 = fmak(SDCT_KD, d43, fmak(-SDCT_KA, d25, fmak(SDCT_KF, d61, mulk(d07, SDCT_KC))));
+    x5 = fmak(-SDCT_KC, d43, fmak(SDCT_KF, d25, fmak(SDCT_KA, d61, mulk(d07, SDCT_KD))));
+    x7 = fmak(SDCT_KA, d43, fmak(SDCT_KC, d25, fmak(SDCT_KD, d61, mulk(d07, SDCT_KF))));
+}
 template <int S>
 SDCT_DEV void dct8_fast_tail(const Stage1 &a, F2 *v)
 {
-    const F2 s07 = a.s07, s16 = a.s16, s25 = a.s25, s34 = a.s34, d07 = a.d07, d61 = a.d61, d25 = a.d25, d43 = a.d43;
-    const F2 pp = add2(s07, s34), pm = sub2(s07, s34), qq = add2(s16, s25), qm = sub2(s16, s25);
-
-    v[0] = add2(pp, qq);
-    v[4 * S] = sub2(pp, qq);
-    v[2 * S] = fmak(SDCT_KB, pm, mulk(qm, SDCT_KE));
-    v[6 * S] = fmak(SDCT_KE, pm, mulk(qm, -SDCT_KB));
-    v[S] = fmak(-SDCT_KF, d43, fmak(SDCT_KD, d25, fmak(-SDCT_KC, d61, mulk(d07, SDCT_KA))));
-    v[3 * S] = fmak(SDCT_KD, d43, fmak(-SDCT_KA, d25, fmak(SDCT_KF, d61, mulk(d07, SDCT_KC))));
-    v[5 * S] = fmak(-SDCT_KC, d43, fmak(SDCT_KF, d25, fmak(SDCT_KA, d61, mulk(d07, SDCT_KD))));
-    v[7 * S] = fmak(SDCT_KA, d43, fmak(SDCT_KC, d25, fmak(SDCT_KD, d61, mulk(d07, SDCT_KF))));
+    fast_even(a.s07, a.s16, a.s25, a.s34, v[0], v[2 * S], v[4 * S], v[6 * S]);
+    fast_odd(a.d07, a.d61, a.d25, a.d43, v[S], v[3 * S], v[5 * S], v[7 * S]);
 }
 template <int S>
 SDCT_DEV void dct8_fast(F2 *v) { dct8_fast_tail<S>(stage1_of<S, false, 1>(v), v); }

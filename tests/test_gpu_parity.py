@@ -188,6 +188,32 @@ def test_inverse_and_fused_roundtrip(ctx, oracle, layout):
                 assert 10 * np.log10(255 ** 2 / mse) > 30
 
 
+@pytest.mark.parametrize("layout", LAYOUTS)
+@pytest.mark.parametrize("w,window", [(512, None), (2112, (3, 9)), (72, None), (1032, (1, 5))])
+def test_interleaved_rgb_inverse_and_roundtrip(ctx, oracle, layout, w, window):
+    """the component reorder on the OUTPUT side: three planar coefficient sets -> interleaved pixels.  An even number
+    of blocks per row takes the staged interleave (three components per CTA, 16-byte stores; w = 2112 makes tiles
+    wrap block rows), an odd one (w = 72, 1032) the byte-store path; band windows leave the other rows untouched."""
+    if layout == sd.LAYOUT_B and w % 64:
+        pytest.skip("layout B needs width % 64 == 0")
+    h = 96
+    img = make_image("smooth", h, w, seed=21, comps=3)
+    lut = rt_lut(layout)
+    b0, b1 = window if window else (0, h // 8)
+    job = sd.dense_job(layout, w, h, components=3, flags=sd.EXACT, band_begin=b0, band_end=b1 if window else 0)
+    planes = oracle.deinterleave(img)
+    coef = np.concatenate([oracle.forward(layout, planes[k], lut) for k in range(3)])
+    want = np.full((h, w, 3), 0x5a, dtype=np.uint8)
+    for k in range(3):
+        want[b0 * 8:b1 * 8, :, k] = oracle.inverse(layout, coef[k * h * w:(k + 1) * h * w], w, h, lut)[b0 * 8:b1 * 8]
+    out = torch.full((h, w, 3), 0x5a, dtype=torch.uint8, device="cuda")
+    ctx.inverse(dev(coef), lut, job, out=out)
+    assert np.array_equal(out.cpu().numpy(), want)
+    out.fill_(0x5a)
+    ctx.roundtrip(dev(img), lut, job, out=out)
+    assert np.array_equal(out.cpu().numpy(), want)
+
+
 def test_roundtrip_error_no_worse_than_float64_inverse(ctx, oracle):
     """SURVEY 8c acceptance test for the (unpinned) inverse: GPU fwd->inv error must not exceed
     the error of oracle-forward -> float64 textbook inverse on the same input."""

@@ -1,7 +1,8 @@
 #!/usr/bin/env python
 """Runs selected kernels a few times on the bench workload (for ncu / compute-sanitizer).
 usage: prof_run.py [--frames 64] [--w 1920] [--h 1080] [--reps 4] name [name ...]
-names: fwd_{A,B,C}_{exact,fast,tensor}, inv_{A,B,C}, rt_{A,B,C}_{exact,fast}, rgb_{B,C}_{exact,fast}"""
+names: fwd_{A,B,C}_{exact,fast,tensor}, inv_{A,B,C}[_tensor], rt_{A,B,C}_{exact,fast,tensor}, rgb_{A,B,C}_{exact,fast,tensor} (interleaved RGB
+forward), irgb_* (inverse to interleaved RGB), rtrgb_* (round trip)"""
 import argparse
 import os
 import sys
@@ -29,7 +30,7 @@ for name in a.names:
     parts = name.split("_")
     op, lay = parts[0], L[parts[1]]
     mode = parts[2] if len(parts) > 2 else "exact"
-    comps = 3 if op == "rgb" else 1
+    comps = 3 if op in ("rgb", "irgb", "rtrgb") else 1
     flags = sd.TENSOR if mode == "tensor" else sd.FAST if mode == "fast" else (sd.EXACT | (sd.QUIRK_AVX_X3 if lay == sd.LAYOUT_B else 0))
     job = sd.dense_job(lay, a.w, a.h, frames=a.frames, components=comps, flags=flags)
     shape = (a.frames, a.h, a.w) if comps == 1 else (a.frames, a.h, a.w, 3)
@@ -43,7 +44,7 @@ for name in a.names:
             e0.record()
         if op in ("fwd", "rgb"):
             ctx.forward(pix, lut, job, out=coef)
-        elif op == "inv":
+        elif op in ("inv", "irgb"):
             ctx.inverse(coef, lut, job, out=back)
         else:
             ctx.roundtrip(pix, lut, job, out=back)
