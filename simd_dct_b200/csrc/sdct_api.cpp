@@ -129,7 +129,26 @@ int run_device(sdct_context *ctx, int op, const sdct_job *j, const uint8_t *pixe
     KParams p;
     memset(&p, 0, sizeof(p));
     const bool tensor = (j->flags & SDCT_TENSOR) != 0;
-    if (tensor && op == SDCT_K_OP_ROUNDTRIP) return fail(SDCT_NOT_SUPPORTED, "SDCT_TENSOR is implemented for the forward and the inverse transform, not for the fused round trip");
+    if (tensor && op == SDCT_K_OP_ROUNDTRIP) {
+        // no fused tensor-core round-trip kernel: the forward and the inverse kernel back to back on the caller's stream,
+        // the coefficients in a stream-ordered scratch allocation with dense 16-byte-aligned strides
+        if (!ctx) return fail(SDCT_INVALID_PARAMETER, "context is null");
+        if (!pixels || !pixels_out) return fail(SDCT_INVALID_PARAMETER, "null buffer");
+        sdct_job cj = *j;
+        cj.coef_comp_stride = j->width * j->height * (uint64_t)g.eyes;
+        cj.coef_plane_stride = cj.coef_comp_stride / 64;
+        cj.coef_frame_stride = cj.coef_comp_stride * g.comps;
+        const size_t bytes = (size_t)(j->frames * cj.coef_frame_stride);
+        if (bytes == 0) return SDCT_OK;
+        CU_TRY(cudaSetDevice(ctx->device));
+        cudaStream_t st = stream ? stream : ctx->stream;
+        void *scratch = nullptr;
+        CU_TRY(cudaMallocAsync(&scratch, bytes, st));
+        rc = run_device(ctx, SDCT_K_OP_FORWARD, &cj, pixels, (uint8_t *)scratch, nullptr, lut, st);
+        if (rc == SDCT_OK) rc = run_device(ctx, SDCT_K_OP_INVERSE, &cj, pixels_out, (uint8_t *)scratch, nullptr, lut, st);
+        cudaFreeAsync(scratch, st);
+        return rc;
+    }
     if (tensor && (j->flags & (SDCT_FAST | SDCT_QUIRK_AVX_X3))) return fail(SDCT_INVALID_PARAMETER, "SDCT_TENSOR excludes SDCT_FAST and SDCT_QUIRK_AVX_X3");
     const bool tensor_inv = tensor && op == SDCT_K_OP_INVERSE;
     rc = (tensor && !tensor_inv) ? build_tc_tables(j, lut, p.tab) : build_tables(j, lut, op, p.tab, p.tab2, p.off);
@@ -162,8 +181,9 @@ int run_device(sdct_context *ctx, int op, const sdct_job *j, const uint8_t *pixe
     if (tensor_inv) {
         // the tensor-core inverse moves whole 16-byte pieces on both sides; other geometries have no kernel (the fp32
         // inverse is a different arithmetic definition, so it is not substituted silently)
-        if (g.comps != 1 || p.pixel_vec != 2 || !p.coef_aligned16 || (j->layout == SDCT_LAYOUT_C && (blocks & 15)) || (j->pitch >> 32))
-            return fail(SDCT_NOT_SUPPORTED, "SDCT_TENSOR inverse needs one component, 16-byte-aligned pixel rows and coefficients, "
+        const bool pix_ok = g.comps == 1 ? p.pixel_vec == 2 : (p.pixel_aligned16 && (g.bpr & 1) == 0);
+        if (!pix_ok || !p.coef_aligned16 || (j->layout == SDCT_LAYOUT_C && (blocks & 15)) || (j->pitch >> 32))
+            return fail(SDCT_NOT_SUPPORTED, "SDCT_TENSOR inverse needs 16-byte-aligned pixel rows and coefficients and "
                                             "an even number of blocks per row (layout C: a multiple of 16 blocks)");
         cudaStream_t st = stream ? stream : ctx->stream;
         {
@@ -202,7 +222,9 @@ int run_device(sdct_context *ctx, int op, const sdct_job *j, const uint8_t *pixe
         }
         {
             std::lock_guard<std::mutex> lock(ctx->tc_maps_mu);
-            CU_TRY(sdct_k_launch_tc(op, j->layout, &p, &ctx->env.tc, &ctx->tc_maps, st));
+            const cudaError_t e = sdct_k_launch_tc(op, j->layout, &p, &ctx->env.tc, &ctx->tc_maps, st);
+            if (e == cudaErrorNotSupported) return fail(SDCT_NOT_SUPPORTED, "SDCT_TENSOR inverse: this geometry does not fit a tensor map");
+            CU_TRY(e);
         }
     } else if (tensor) {
         p.tc_matrix = ctx->d_tc_matrix[j->layout == SDCT_LAYOUT_A ? 0 : 1];

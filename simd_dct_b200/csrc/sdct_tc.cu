@@ -897,6 +897,14 @@ template <int LAYOUT, bool CT> __host__ __device__ constexpr int inv_raw_bytes()
 
 
 
+// three-component output: the consumers stage a pixel tile's rows planar, [component][pixel row][block slot][8 bytes]
+// (row pitch + 16: the 8-byte stores of a warp's four pixel rows fall on different banks), two images (pixel tile j uses
+// image j % 2), placed behind the barriers
+constexpr int PIX_PITCH = TILE * 8 + 16, PIX_COMP = 8 * PIX_PITCH, PIX_IMG3 = 3 * PIX_COMP;
+constexpr int SMEM_INV_PIX_OFF = (SMEM_USED + 15) & ~15;
+constexpr int SMEM_INV_RGB_BYTES = SMEM_INV_PIX_OFF + 2 * PIX_IMG3;
+static_assert(SMEM_INV_RGB_BYTES <= 227 * 1024, "shared memory of the three-component inverse");
+
 SDCT_DEV void bulk_copy_g2s(void *smem_dst, const void *gmem, uint32_t bytes, uint64_t *bar)
 {
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
@@ -905,31 +913,39 @@ SDCT_DEV void bulk_copy_g2s(void *smem_dst, const void *gmem, uint32_t bytes, ui
 
 // the TMA thread lands each tile's raw coefficient bytes in the ring: layouts A, B: one copy of count * 64 contiguous
 // bytes; layout C: one box of the coefficient tensor (blocks past the end of a plane read as zero and are never stored)
-template <int LAYOUT>
+// CF = 3: interleaved 3-component pixels on the output side; p.tiles counts PIXEL tiles and the CTA's tile k is component
+// k % 3 of its pixel tile k / 3 (the three coefficient sets of a frame lie coef_comp_stride apart)
+template <int LAYOUT, int CF>
 SDCT_DEV void inv_bulk_role(const KParams &p, uint64_t *bars, uint8_t *ring)
 {
     TileWalk w;
     w.init(p, 0, 1);
-    for (uint32_t k = 0; w.tile < p.tiles; k++, w.next(p)) {
+    uint32_t comp = 0;
+    for (uint32_t k = 0; w.tile < p.tiles; k++) {
         const uint32_t rs = k % INV_RING, ru = k / INV_RING;
-        const Tile t = tile_at<1, TILE>(p, w);
+        Tile t = tile_at<1, TILE>(p, w);
+        t.coef += (uint64_t)comp * p.coef_comp_stride;
+        const uint32_t this_comp = comp, frame = w.fc;
+        if (++comp == (uint32_t)CF) { comp = 0; w.next(p); }
         const uint64_t n_first = (uint64_t)p.row0 * p.bpr + t.n0;
         uint64_t *full = bars + BAR_RING_FULL + rs;
         uint8_t *slot = ring + rs * (TILE * 64);
         mbar_wait(bars + BAR_RING_EMPTY + rs, (ru & 1) ^ 1);
         if (LAYOUT == SDCT_K_LAYOUT_C) {
             mbar_expect_tx(full, TILE * 64u);
-            tma_load_box(slot, p.tc_coef_map, full, (int32_t)n_first, 0, 0, (int32_t)w.fc);
+            tma_load_box(slot, p.tc_coef_map, full, (int32_t)n_first, 0, (int32_t)this_comp, (int32_t)frame);
         } else {
+            (void)this_comp; (void)frame;
             mbar_expect_tx(full, t.count * 64u);
             bulk_copy_g2s(slot, t.coef + n_first * 64, t.count * 64u, full);
         }
     }
 }
 
-template <int LAYOUT, bool CT>
+template <int LAYOUT, bool CT, int CF>
 SDCT_DEV void inv_producer_role(const KParams &p, uint64_t *bars, uint8_t *a_stages, uint8_t *ring, uint32_t L)
 {
+    static_assert(CF == 1 || inv_bulk<LAYOUT, CT>(), "the three-component form takes its tiles from the bulk-copy ring");
     // Two piece-to-thread mappings.  COPY: piece c = L + 128 m in global order (coalesced cp.async).  EXPAND: the
     // piece whose two expanded 16-byte halves this thread stores, chosen so that a quarter-warp's stores fall on
     // 32 distinct banks.  Layout B expands the pieces it copied (no barrier); A and C read pieces other threads
@@ -985,9 +1001,8 @@ SDCT_DEV void inv_producer_role(const KParams &p, uint64_t *bars, uint8_t *a_sta
     };
     if (!BULK)
         for (uint32_t j = 0; j < AHEAD; j++) issue(j);
-    uint32_t tile = blockIdx.x;
-    for (uint32_t k = 0;; k++, tile += gridDim.x) {
-        if (tile >= p.tiles) return;
+    for (uint32_t k = 0;; k++) {
+        if (blockIdx.x + (k / CF) * gridDim.x >= p.tiles) return;
         const bool tr = (ablate_bits(p) & 32) && blockIdx.x == 0 && L == 0;
         stamp(tr, 0, k, 0);
         if (BULK) {
@@ -1040,14 +1055,14 @@ SDCT_DEV void inv_producer_role(const KParams &p, uint64_t *bars, uint8_t *a_sta
     }
 }
 
-template <int LAYOUT>
+template <int LAYOUT, int CF>
 SDCT_DEV void inv_mma_role(const KParams &p, uint64_t *bars, uint32_t tmem_base, uint32_t a_stages_addr, uint64_t bdesc, uint32_t m)
 {
     // layout A: K-major A operand; layouts B, C: MN-major (instruction descriptor bit 15)
     constexpr uint32_t idesc = IDESC | (LAYOUT == SDCT_K_LAYOUT_A ? 0u : (1u << 15));
     const uint64_t bd[4] = {bdesc, bdesc + (uint64_t)((2 * B_LBO) >> 4), bdesc + (uint64_t)((4 * B_LBO) >> 4), bdesc + (uint64_t)((6 * B_LBO) >> 4)};
     for (uint32_t k = m;; k += MMA_WARPS) {
-        if (blockIdx.x + k * gridDim.x >= p.tiles) break;
+        if (blockIdx.x + (k / CF) * gridDim.x >= p.tiles) break;
         const uint32_t sa = k % A_STAGES, ua = k / A_STAGES, sd = k % D_STAGES;
         const bool tr = (ablate_bits(p) & 32) && blockIdx.x == 0;
         stamp(tr, 1, k, 0);
@@ -1069,8 +1084,38 @@ SDCT_DEV void inv_mma_role(const KParams &p, uint64_t *bars, uint32_t tmem_base,
     }
 }
 
-template <int LAYOUT>
-SDCT_DEV void inv_consumer_role(const KParams &p, uint64_t *bars, uint32_t tmem_base, uint32_t c, uint32_t L, uint32_t lane_field)
+// planar pixel images of a pixel tile's three components -> interleaved rows in global memory (both consumer
+// warpgroups, T = 0..255): a thread takes the 16 pixels of an adjacent block pair of one row, three 16-byte reads,
+// 24 PRMTs, three 16-byte stores (see flush_rgb in sdct_kernels.cu)
+SDCT_DEV void tc_flush_rgb(const uint8_t *img3, const KParams &p, const Tile &t, uint32_t T)
+{
+    const uint32_t u = T & 63u, slot = 2u * u;
+    if (slot >= t.count) return;
+    const uint32_t nl = t.n0 + slot;
+    const uint32_t r0 = fastdiv(nl, p.div_bpr), bx = nl - r0 * p.bpr, row = r0 + p.row0;
+    const uint32_t band = p.eyes == 2 ? row >> 1 : row, eye = p.eyes == 2 ? row & 1 : 0;
+    uint8_t *dst = const_cast<uint8_t *>(t.pix) + (uint64_t)eye * p.eye_stride + (uint64_t)(band * 8 + (T >> 6)) * p.pitch + (uint64_t)bx * 24;
+    const uint8_t *src = img3 + (T >> 6) * PIX_PITCH + u * 16u;
+#pragma unroll
+    for (int i = 0; i < 2; i++, dst += 4 * p.pitch, src += 4 * PIX_PITCH) {
+        const uint4 R = *reinterpret_cast<const uint4 *>(src), G = *reinterpret_cast<const uint4 *>(src + PIX_COMP), B = *reinterpret_cast<const uint4 *>(src + 2 * PIX_COMP);
+        const uint32_t rr[4] = {R.x, R.y, R.z, R.w}, gg[4] = {G.x, G.y, G.z, G.w}, bb[4] = {B.x, B.y, B.z, B.w};
+        uint32_t o[12];
+#pragma unroll
+        for (int q = 0; q < 4; q++) {
+            o[3 * q] = __byte_perm(__byte_perm(rr[q], gg[q], 0x1040), bb[q], 0x3410);       // R0 G0 B0 R1
+            o[3 * q + 1] = __byte_perm(__byte_perm(gg[q], rr[q], 0x2601), bb[q], 0x3250);   // G1 B1 R2 G2
+            o[3 * q + 2] = __byte_perm(__byte_perm(bb[q], rr[q], 0x3072), gg[q], 0x3710);   // B2 R3 G3 B3
+        }
+        uint4 *d = reinterpret_cast<uint4 *>(dst);
+        d[0] = make_uint4(o[0], o[1], o[2], o[3]);
+        d[1] = make_uint4(o[4], o[5], o[6], o[7]);
+        d[2] = make_uint4(o[8], o[9], o[10], o[11]);
+    }
+}
+
+template <int LAYOUT, int CF>
+SDCT_DEV void inv_consumer_role(const KParams &p, uint64_t *bars, uint32_t tmem_base, uint32_t c, uint32_t L, uint32_t lane_field, uint8_t *pix_images)
 {
     const uint32_t lane = L & 31, g = lane >> 2, q = lane & 3;
     // this thread's 16 pixel offsets -127 * sum E (columns 8k + 2q + e), and the common 2^(24 - S)
@@ -1121,22 +1166,39 @@ SDCT_DEV void inv_consumer_role(const KParams &p, uint64_t *bars, uint32_t tmem_
             while (bx >= p.bpr) { bx -= p.bpr; r++; }   // (a slot past the tile's end may point past the window: never stored)
         }
     };
+    // CF == 1: wk walks this warpgroup's tiles.  CF == 3: wk walks the CTA's pixel tiles; tile k = component k % 3 of pixel
+    // tile k / 3, whose pixel rows go to the shared-memory image (k / 3) % 2 instead of global memory.
+    static_assert(CF == 1 || (CF == 3 && CONSUMER_WGS == 2), "fused components");
     TileWalk wk;
-    wk.init(p, c, CONSUMER_WGS);
-    Dst cur;
-    if (wk.tile < p.tiles) locate_tile(wk, cur);
+    if (CF == 1) wk.init(p, c, CONSUMER_WGS); else wk.init(p, 0, 1);
+    uint32_t comp = CF == 1 ? 0u : c;
+    Dst cur = {};
+    if (CF == 1 && wk.tile < p.tiles) locate_tile(wk, cur);
     for (uint32_t k = c;; k += CONSUMER_WGS) {
         if (wk.tile >= p.tiles) break;
         const uint32_t sd = k % D_STAGES, ud = k / (2 * D_STAGES);
         uint64_t *d_full = bars + BAR_D_FULL + c * D_STAGES + sd, *d_empty = bars + BAR_D_EMPTY + c * D_STAGES + sd;
-        const bool full = cur.count == TILE;
+        Tile ptile;             // CF == 3: the pixel tile of this tile
+        uint8_t *img = nullptr; //          and this component's image
+        bool last_own = false;  //          this warpgroup's last component of the pixel tile
+        if (CF != 1) {
+            ptile = tile_at<1, TILE>(p, wk);
+            img = pix_images + ((k / CF) & 1u) * PIX_IMG3 + comp * PIX_COMP;
+            last_own = comp + CONSUMER_WGS >= (uint32_t)CF;
+        }
+        const bool full = CF == 1 && cur.count == TILE;
         const bool tr = (ablate_bits(p) & 32) && blockIdx.x == 0 && L == 0;
         stamp(tr, 2, k, 0);
         mbar_wait(d_full, ud & 1);
         fence_after();
         stamp(tr, 2, k, 1);
-        wk.next(p);
-        if (ablate_bits(p) & 4) { fence_before(); mbar_arrive(d_empty); if (wk.tile < p.tiles) locate_tile(wk, cur); continue; }
+        if (CF == 1) {
+            wk.next(p);
+        } else {
+            comp += CONSUMER_WGS;
+            if (comp >= (uint32_t)CF) { comp -= CF; wk.next(p); }
+        }
+        if (CF == 1 && (ablate_bits(p) & 4)) { fence_before(); mbar_arrive(d_empty); if (wk.tile < p.tiles) locate_tile(wk, cur); continue; }
         // Four chunks of 32 columns (pixel rows 2q, 2q + 1 of two 16-block halves).  Chunks 0 and 1 are loaded
         // together; chunk 2 is requested as soon as chunk 0's registers are free, chunk 3 after chunk 1's: two
         // load waits per tile instead of four, the second hidden behind chunk 1's arithmetic.  The next tile's
@@ -1148,7 +1210,7 @@ SDCT_DEV void inv_consumer_role(const KParams &p, uint64_t *bars, uint32_t tmem_
         tmem_ld_16x256b_x4(td + 32, hiB);
         tmem_ld_16x256b_x4(td + 96, loB);
         Dst nxt = cur;
-        if (wk.tile < p.tiles) locate_tile(wk, nxt);
+        if (CF == 1 && wk.tile < p.tiles) locate_tile(wk, nxt);
 #define SDCT_TC_INV_CHUNK(C, HI, LO)                                                                                  \
         {                                                                                                             \
             constexpr int half = (C) >> 1, kk = (C) & 1;                                                              \
@@ -1161,9 +1223,15 @@ SDCT_DEV void inv_consumer_role(const KParams &p, uint64_t *bars, uint32_t tmem_
             }                                                                                                         \
             const uint2 vp = make_uint2(pack4_sat(bp[0].x, bp[0].y, bp[1].x, bp[1].y), pack4_sat(bp[2].x, bp[2].y, bp[3].x, bp[3].y)); \
             const uint2 vq = make_uint2(pack4_sat(bq[0].x, bq[0].y, bq[1].x, bq[1].y), pack4_sat(bq[2].x, bq[2].y, bq[3].x, bq[3].y)); \
+            if (CF != 1) {   /* pixel row 2q + kk of slots sp0 + 16 half (P) and + 8 (Q) of this component's image */   \
+                uint8_t *d = img + (2 * q + kk) * PIX_PITCH + (sp0 + 16 * half) * 8u;                                 \
+                *reinterpret_cast<uint2 *>(d) = vp;                                                                   \
+                *reinterpret_cast<uint2 *>(d + 64) = vq;                                                              \
+            }                                                                                                         \
             uint2 *dp = reinterpret_cast<uint2 *>(cur.px[half][0] + (kk ? pitch32 : 0u));                             \
             uint2 *dq = reinterpret_cast<uint2 *>(cur.px[half][1] + (kk ? pitch32 : 0u));                             \
-            if (ablate_bits(p) & 8) { if (vp.x == 0x12345678u && vq.y == 0x9abcdef0u) *dp = vp; }                     \
+            if (CF != 1) { }                                                                                          \
+            else if (ablate_bits(p) & 8) { if (vp.x == 0x12345678u && vq.y == 0x9abcdef0u) *dp = vp; }                \
             else if (full) { *dp = vp; *dq = vq; }                                                                    \
             else {                                                                                                    \
                 if (sp0 + 16 * half < cur.count) *dp = vp;                                                            \
@@ -1187,10 +1255,17 @@ SDCT_DEV void inv_consumer_role(const KParams &p, uint64_t *bars, uint32_t tmem_
 #undef SDCT_TC_INV_CHUNK
         stamp(tr, 2, k, 3);
         cur = nxt;
+        if (CF != 1 && last_own) {
+            // both warpgroups have staged their components of the pixel tile: write it out interleaved.  (Image j % 2
+            // is written again by pixel tile j + 2, after the barrier of pixel tile j + 1, which every thread reaches
+            // only after this flush.)
+            asm volatile("bar.sync 4, 256;" ::: "memory");
+            tc_flush_rgb(pix_images + ((k / CF) & 1u) * PIX_IMG3, p, ptile, c * 128u + L);
+        }
     }
 }
 
-template <int LAYOUT, bool CT>
+template <int LAYOUT, bool CT, int CF>
 __global__ void __launch_bounds__(THREADS, 1) inverse_tc_kernel(const __grid_constant__ KParams p)
 {
     extern __shared__ __align__(1024) uint8_t smem[];   // the swizzled ring slots of layout C need 1024-byte alignment
@@ -1227,14 +1302,14 @@ __global__ void __launch_bounds__(THREADS, 1) inverse_tc_kernel(const __grid_con
     const uint32_t lane_field = ((warp & 3u) * 32u) << 16;
     static_assert(PRODUCER_WGS == 1 && INV_RING <= TMA_RING, "the inverse kernel has one producer warpgroup and reuses the ring barriers");
     if (warp < CONSUMER_WARP) {
-        inv_producer_role<LAYOUT, CT>(p, bars, smem + SMEM_INV_A_OFF, smem + SMEM_INV_RING_OFF, threadIdx.x);
+        inv_producer_role<LAYOUT, CT, CF>(p, bars, smem + SMEM_INV_A_OFF, smem + SMEM_INV_RING_OFF, threadIdx.x);
     } else if (warp < MMA_WARP) {
         const uint32_t c = (warp - CONSUMER_WARP) >> 2;
-        inv_consumer_role<LAYOUT>(p, bars, tmem_base, c, threadIdx.x & 127, lane_field);
+        inv_consumer_role<LAYOUT, CF>(p, bars, tmem_base, c, threadIdx.x & 127, lane_field, smem + SMEM_INV_PIX_OFF);
     } else if (warp < MMA_WARP + MMA_WARPS && lane == 0) {
-        inv_mma_role<LAYOUT>(p, bars, tmem_base, smem_u32(smem + SMEM_INV_A_OFF), b_descriptor(smem_u32(smem + SMEM_B_OFF)), warp - MMA_WARP);
+        inv_mma_role<LAYOUT, CF>(p, bars, tmem_base, smem_u32(smem + SMEM_INV_A_OFF), b_descriptor(smem_u32(smem + SMEM_B_OFF)), warp - MMA_WARP);
     } else if (inv_bulk<LAYOUT, CT>() && warp == TMA_WARP && lane == 0) {
-        inv_bulk_role<LAYOUT>(p, bars, smem + SMEM_INV_RING_OFF);
+        inv_bulk_role<LAYOUT, CF>(p, bars, smem + SMEM_INV_RING_OFF);
     }
     fence_before();
     __syncthreads();
@@ -1358,17 +1433,18 @@ extern "C" int sdct_k_tc_trace(unsigned long long *host)
     return (int)cudaMemcpyFromSymbol(host, tc::g_trace, sizeof(tc::g_trace));
 }
 
-template <int LAYOUT, bool CT>
+template <int LAYOUT, bool CT, int CF = 1>
 static cudaError_t launch_tc_inverse(const KParams &p, unsigned grid, cudaStream_t s)
 {
+    constexpr int smem = CF == 1 ? tc::SMEM_BYTES : tc::SMEM_INV_RGB_BYTES;
     static std::atomic<uint64_t> attr_done{0};
     uint64_t bit;
     if (attr_pending(attr_done, &bit)) {
-        cudaError_t e = cudaFuncSetAttribute(tc::inverse_tc_kernel<LAYOUT, CT>, cudaFuncAttributeMaxDynamicSharedMemorySize, tc::SMEM_BYTES);
+        cudaError_t e = cudaFuncSetAttribute(tc::inverse_tc_kernel<LAYOUT, CT, CF>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
         if (e != cudaSuccess) return e;
         attr_done.fetch_or(bit, std::memory_order_release);
     }
-    tc::inverse_tc_kernel<LAYOUT, CT><<<grid, tc::THREADS, tc::SMEM_BYTES, s>>>(p);
+    tc::inverse_tc_kernel<LAYOUT, CT, CF><<<grid, tc::THREADS, smem, s>>>(p);
     return cudaGetLastError();
 }
 
@@ -1410,6 +1486,20 @@ extern "C" cudaError_t sdct_k_launch_tc(int op, int layout, const KParams *pp, c
         p.div_chunks = make_fastdiv(p.chunks);
         p.div_bpr = make_fastdiv(p.bpr);
         const unsigned sms_i = p.sm_count ? p.sm_count : 148u;
+        if (p.comps == 3) {
+            // interleaved pixels on the output side: tiles = pixel tiles, three components each (the caller has checked
+            // the alignment and the even block count per row); layout C needs its tensor map
+            p.tiles = (uint32_t)(tiles / 3);
+            const unsigned grid3 = p.tiles < sms_i ? p.tiles : sms_i;
+            switch (layout) {
+            case SDCT_K_LAYOUT_A: return launch_tc_inverse<SDCT_K_LAYOUT_A, false, 3>(p, grid3, s);
+            case SDCT_K_LAYOUT_B: return launch_tc_inverse<SDCT_K_LAYOUT_B, false, 3>(p, grid3, s);
+            case SDCT_K_LAYOUT_C:
+                if (make_coef_tensor_map(p, opt, maps)) return launch_tc_inverse<SDCT_K_LAYOUT_C, true, 3>(p, grid3, s);
+                return cudaErrorNotSupported;
+            default: return cudaErrorInvalidValue;
+            }
+        }
         const unsigned grid_i = (unsigned)(tiles < sms_i ? tiles : sms_i);
         switch (layout) {
         case SDCT_K_LAYOUT_A: return launch_tc_inverse<SDCT_K_LAYOUT_A, false>(p, grid_i, s);

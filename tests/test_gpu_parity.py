@@ -630,7 +630,40 @@ def test_tensor_core_inverse_is_bit_exact_to_its_cpu_restatement(ctx, oracle, la
     ctx_no_tma.close()
     for k in range(f):
         assert np.array_equal(got[k], oracle.inverse(layout, coefs[k], w, h, lut, tensor=True))
-    # interleaved RGB has no tensor-core inverse: refused, not silently replaced by the fp32 arithmetic
-    job = sd.dense_job(layout, 64, 64, components=3, flags=sd.TENSOR)
-    with pytest.raises(Exception):
-        ctx.inverse(torch.zeros(3 * 64 * 64, dtype=torch.uint8, device="cuda"), lut, job)
+    # a geometry the tensor-core inverse has no path for (an odd number of blocks per row of interleaved pixels) is refused,
+    # not silently replaced by the fp32 arithmetic
+    if layout != sd.LAYOUT_B:
+        job = sd.dense_job(layout, 72, 64, components=3, flags=sd.TENSOR)
+        with pytest.raises(sd.SdctError):
+            ctx.inverse(torch.zeros(3 * 72 * 64, dtype=torch.uint8, device="cuda"), lut, job)
+
+
+@pytest.mark.parametrize("layout", LAYOUTS)
+@pytest.mark.parametrize("w,h,window", [(512, 96, None), (2112, 96, (4, 10)), (3840, 64, None)])
+def test_tensor_core_rgb_inverse_and_roundtrip(ctx, oracle, layout, w, h, window):
+    """SDCT_TENSOR on the output side of interleaved RGB (three components per pixel tile staged planar, written
+    interleaved) and the SDCT_TENSOR round trip (forward + inverse kernels back to back): byte-identical to the CPU
+    restatement inverse_tensor(forward_tensor(x)) per component; bytes outside the band window untouched."""
+    img = make_image("smooth", h, w, seed=31, comps=3)
+    lut = rt_lut(layout)
+    b0, b1 = window if window else (0, h // 8)
+    job = sd.dense_job(layout, w, h, components=3, flags=sd.TENSOR, band_begin=b0, band_end=b1 if window else 0)
+    planes = oracle.deinterleave(img)
+    coef = np.concatenate([oracle.forward(layout, planes[k], lut, mode=ol.MODE_TENSOR) for k in range(3)])
+    want = np.full((h, w, 3), 0x5a, dtype=np.uint8)
+    for k in range(3):
+        want[b0 * 8:b1 * 8, :, k] = oracle.inverse(layout, coef[k * h * w:(k + 1) * h * w], w, h, lut, tensor=True)[b0 * 8:b1 * 8]
+    out = torch.full((h, w, 3), 0x5a, dtype=torch.uint8, device="cuda")
+    ctx.inverse(dev(coef), lut, job, out=out)
+    assert np.array_equal(out.cpu().numpy(), want)
+    out.fill_(0x5a)
+    n0 = ctx.kernel_launches
+    ctx.roundtrip(dev(img), lut, job, out=out)
+    assert ctx.kernel_launches - n0 == 2
+    assert np.array_equal(out.cpu().numpy(), want)
+    # single plane too
+    luma = np.ascontiguousarray(img[:, :, 1])
+    j1 = sd.dense_job(layout, w, h, flags=sd.TENSOR)
+    c1 = oracle.forward(layout, luma, lut, mode=ol.MODE_TENSOR)
+    rt = ctx.roundtrip(dev(luma), lut, j1).cpu().numpy().reshape(h, w)
+    assert np.array_equal(rt, oracle.inverse(layout, c1, w, h, lut, tensor=True))
