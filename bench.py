@@ -434,7 +434,7 @@ def main():
                 assert rc == sd.sdr_Success, sd.last_error()
             return step
         dt = wall(shim_step(sd.simdDCT_EncodeQuantize32ReorderBuffer, 2 * F * H), e2e_steps)
-        assert torch.equal(h_out.cuda(), headline_out), "host pipeline and device path disagree"
+        assert torch.equal(h_out.to(headline_out.device), headline_out), "host pipeline and device path disagree"
         # the platform's ceiling for this traffic: the same bytes as raw concurrent pinned copies (all ranks at once)
         s_up, s_dn = torch.cuda.Stream(), torch.cuda.Stream()
         d_a, d_b = torch.empty_like(d_in), torch.empty_like(d_out)
@@ -490,9 +490,11 @@ def main():
                     e2e["single_process_all_gpus"] = {"gpus": ndev, "ms_per_step": dtm * 1e3, "blocks_per_s": blocks_per_rank / dtm,
                                                       "gbps_each_way": nbytes / dtm / 1e9,
                                                       "api": "sdct_forward_host_multi: one call, frames sharded over all devices, one host thread each"}
-                    assert torch.equal(h_out.cuda(), headline_out)
+                    torch.cuda.set_device(local_rank)
+                    assert torch.equal(h_out.to(headline_out.device), headline_out)
                     for c in ctxs:
                         c.close()
+                    torch.cuda.set_device(local_rank)
                 barrier()
         del h_in, h_out
 

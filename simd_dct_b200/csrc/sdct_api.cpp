@@ -140,10 +140,11 @@ int run_device(sdct_context *ctx, int op, const sdct_job *j, const uint8_t *pixe
         cj.coef_frame_stride = cj.coef_comp_stride * g.comps;
         const size_t bytes = (size_t)(j->frames * cj.coef_frame_stride);
         if (bytes == 0) return SDCT_OK;
-        CU_TRY(cudaSetDevice(ctx->device));
+        DeviceScope dev(ctx->device);
+        CU_TRY(dev.err);
         cudaStream_t st = stream ? stream : ctx->stream;
         void *scratch = nullptr;
-        CU_TRY(cudaMallocAsync(&scratch, bytes, st));
+        CU_TRY(cudaMallocFromPoolAsync(&scratch, bytes, ctx->scratch_pool, st));
         rc = run_device(ctx, SDCT_K_OP_FORWARD, &cj, pixels, (uint8_t *)scratch, nullptr, lut, st);
         if (rc == SDCT_OK) rc = run_device(ctx, SDCT_K_OP_INVERSE, &cj, pixels_out, (uint8_t *)scratch, nullptr, lut, st);
         cudaFreeAsync(scratch, st);
@@ -175,7 +176,8 @@ int run_device(sdct_context *ctx, int op, const sdct_job *j, const uint8_t *pixe
     if (j->layout == SDCT_LAYOUT_C)  // 16-byte plane segments: every plane and the window start must be aligned too
         p.coef_aligned16 = p.coef_aligned16 && (j->coef_plane_stride & 15) == 0 && (((uint64_t)p.row0 * p.bpr) & 15) == 0;
     if (blocks == 0 || j->frames == 0) return SDCT_OK;
-    CU_TRY(cudaSetDevice(ctx->device));
+    DeviceScope dev(ctx->device);
+    CU_TRY(dev.err);
     const int mode = (j->flags & SDCT_FAST) ? SDCT_K_FAST : SDCT_K_EXACT;
     const int x3 = (j->flags & SDCT_QUIRK_AVX_X3) ? 1 : 0;
     if (tensor_inv) {
@@ -279,12 +281,23 @@ int sdct_create(int device, sdct_context **out)
     cudaDeviceProp prop;
     CU_TRY(cudaGetDeviceProperties(&prop, device));
     if (prop.major != 10) return fail(SDCT_NO_DEVICE, "device %d is sm_%d%d; kernels are built for sm_100a only", device, prop.major, prop.minor);
-    CU_TRY(cudaSetDevice(device));
+    DeviceScope dev(device);
+    CU_TRY(dev.err);
     std::unique_ptr<sdct_context, void (*)(sdct_context *)> c(new sdct_context(), sdct_destroy);   // released on every early return
     c->device = device;
     c->sm_count = prop.multiProcessorCount;
     read_env(&c->env);
     CU_TRY(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+    {
+        cudaMemPoolProps props = {};
+        props.allocType = cudaMemAllocationTypePinned;
+        props.handleTypes = cudaMemHandleTypeNone;
+        props.location.type = cudaMemLocationTypeDevice;
+        props.location.id = device;
+        CU_TRY(cudaMemPoolCreate(&c->scratch_pool, &props));
+        uint64_t keep = ~0ull;
+        CU_TRY(cudaMemPoolSetAttribute(c->scratch_pool, cudaMemPoolAttrReleaseThreshold, &keep));
+    }
     {   // tensor-core B operands (16 KiB each)
         std::vector<uint16_t> op(128 * 64);
         const int layouts[2] = {SDCT_K_LAYOUT_A, SDCT_K_LAYOUT_B};
@@ -301,10 +314,11 @@ int sdct_create(int device, sdct_context **out)
 void sdct_destroy(sdct_context *c)
 {
     if (!c) return;
-    cudaSetDevice(c->device);
+    DeviceScope dev(c->device);
     for (auto &p : c->pipes) sdct_destroy_pipeline(p.get());
     c->pipes.clear();
     if (c->stream) { cudaStreamSynchronize(c->stream); cudaStreamDestroy(c->stream); }
+    if (c->scratch_pool) cudaMemPoolDestroy(c->scratch_pool);
     cudaFree(c->d_tc_matrix[0]); cudaFree(c->d_tc_matrix[1]);
     for (auto &e : c->inv_cache) cudaFree(e.d);
     delete c;
@@ -316,7 +330,8 @@ uint64_t sdct_kernel_launches(const sdct_context *c) { return c ? c->launches.lo
 int sdct_synchronize(sdct_context *c)
 {
     if (!c) return fail(SDCT_INVALID_PARAMETER, "context is null");
-    CU_TRY(cudaSetDevice(c->device));
+    DeviceScope dev(c->device);
+    CU_TRY(dev.err);
     CU_TRY(cudaStreamSynchronize(c->stream));
     std::lock_guard<std::mutex> lock(c->pipes_mu);
     for (auto &p : c->pipes)
@@ -347,7 +362,8 @@ int sdct_selftest_dct8(sdct_context *c, int kind, float *h_data, size_t n)
     if (!c || !h_data) return fail(SDCT_INVALID_PARAMETER, "null argument");
     if (n == 0) return SDCT_OK;
     if (n > 0x7fffffffu / 8) return fail(SDCT_NOT_SUPPORTED, "too many vectors");
-    CU_TRY(cudaSetDevice(c->device));
+    DeviceScope dev(c->device);
+    CU_TRY(dev.err);
     float *d = nullptr;
     CU_TRY(cudaMalloc((void **)&d, n * 8 * sizeof(float)));
     cudaError_t e = cudaMemcpyAsync(d, h_data, n * 8 * sizeof(float), cudaMemcpyHostToDevice, c->stream);

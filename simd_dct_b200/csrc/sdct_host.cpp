@@ -190,7 +190,8 @@ std::vector<uint64_t> ramp(uint64_t total, uint64_t per, bool no_ramp)
 int run_chunks(sdct_context *ctx, Pipeline *pipe, int op, const sdct_job *job, const Geometry &g, const uint8_t *h_pixels,
                uint8_t *h_coefs, const float *lut)
 {
-    CU_TRY(cudaSetDevice(ctx->device));
+    DeviceScope dev(ctx->device);
+    CU_TRY(dev.err);
     int rc;
     // ---- chunking: by frames for batches, by band ranges inside a frame otherwise ----------
     const uint64_t band_bytes = (uint64_t)g.eyes * 8 * job->width * g.comps;
@@ -419,7 +420,8 @@ Pipeline *sdct_acquire_pipeline(sdct_context *ctx)
         for (auto &p : ctx->pipes)
             if (!p->busy) { p->busy = true; return p.get(); }
     }
-    if (cudaSetDevice(ctx->device) != cudaSuccess) { fail(SDCT_CUDA_ERROR, "cudaSetDevice(%d) failed", ctx->device); return nullptr; }
+    DeviceScope dev(ctx->device);
+    if (dev.err != cudaSuccess) { fail(SDCT_CUDA_ERROR, "cudaSetDevice(%d) failed", ctx->device); return nullptr; }
     std::unique_ptr<Pipeline> p(new Pipeline());
     p->busy = true;
     for (Slot &s : p->slots) {

@@ -21,6 +21,24 @@ int sdct_fail(int code, const char *fmt, ...);
                         __FILE__, __LINE__);                                                      \
     } while (0)
 
+// makes `device` current for a scope and restores the caller's current device afterwards: the library never changes
+// the calling thread's current device behind its back (a caller that drives several contexts keeps its own)
+struct DeviceScope {
+    int prev = -1, dev;
+    cudaError_t err;
+    explicit DeviceScope(int device) : dev(device)
+    {
+        err = cudaGetDevice(&prev);
+        if (err == cudaSuccess && prev != dev) err = cudaSetDevice(dev);
+    }
+    ~DeviceScope()
+    {
+        if (prev >= 0 && prev != dev) cudaSetDevice(prev);
+    }
+    DeviceScope(const DeviceScope &) = delete;
+    DeviceScope &operator=(const DeviceScope &) = delete;
+};
+
 constexpr int kSlots = 8;  // slots of one host pipeline; the depth in use is SdctEnv::host_slots <= kSlots
 
 // one in-flight chunk of the host path: its stream, the device buffers of the chunk's dense sub-job and the
@@ -64,6 +82,9 @@ struct sdct_context {
     InvOperand inv_cache[8];
     uint64_t inv_clock = 0;
     std::mutex inv_mu;
+    // stream-ordered scratch memory (SDCT_TENSOR round trip: the coefficients between the two kernels): an own pool that
+    // keeps its memory (the default pool hands freed memory back to the driver at every synchronisation point)
+    cudaMemPool_t scratch_pool = nullptr;
     SdctTcMapCache tc_maps;   // encoded CUtensorMaps keyed by (pointer, geometry); guarded by its own mutex
     std::mutex tc_maps_mu;
 };

@@ -177,3 +177,22 @@ def test_two_devices_in_one_process():
         c.close()
     for a, b in zip(*outs):
         assert np.array_equal(a, b)
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs")
+def test_library_leaves_the_callers_current_device_alone():
+    """contexts on other devices (creation, launches, host-buffer calls, destruction) must not change the calling
+    thread's current device - bench.py at N > 1 once compared tensors on the wrong device because of that"""
+    torch.cuda.set_device(0)
+    lut = ol.lut(8)
+    img = make_image("rand", 64, 128, seed=51)
+    c = sd.Context(1)
+    assert torch.cuda.current_device() == 0
+    job = sd.dense_job(sd.LAYOUT_B, 128, 64, flags=flags_for(sd.LAYOUT_B))
+    x = torch.from_numpy(img).cuda(1)
+    c.forward(x, lut, job)
+    c.forward_host(img, lut, job)
+    c.synchronize()
+    assert torch.cuda.current_device() == 0
+    c.close()
+    assert torch.cuda.current_device() == 0
