@@ -360,6 +360,40 @@ def test_reference_cli_linked_against_libsdct(tmp_path, mode, simd):
     assert np.array_equal(outs[0][:n], outs[1][:n])
 
 
+@pytest.mark.skipif(not os.path.exists(os.path.join(CLI_DIR, "simd_dct_cli_cpu")), reason="oracle/_ref CLIs not built")
+@pytest.mark.parametrize("mode,simd", [("enc-quant", "none"), ("enc-quant32", "avx2"), ("enc-quant-stereo", "none")])
+def test_python_cli_dump_equals_the_reference_cli(tmp_path, mode, simd):
+    """SURVEY 8f f2: `python -m simd_dct_b200.cli` follows the reference CLI's workflow (src/main.cpp:84-102, :508-606);
+    its --to dump equals the all-CPU reference binary's, and --inverse dumps pixels close to the input."""
+    import sys
+    if simd == "avx2" and "avx2" not in ol.cpu_flags():
+        pytest.skip("host CPU has no AVX2: the reference cannot produce layout B here")
+    img = make_image("smooth", 512, 768, seed=6)
+    raw = tmp_path / "img.raw"
+    raw.write_bytes(img.tobytes())
+    ref_dump, my_dump, inv_dump = tmp_path / "ref.bin", tmp_path / "mine.bin", tmp_path / "inv.bin"
+    common = [str(raw), "768", "512", "--runs", "2", "--quality", "8", "--mode", mode]
+    r = subprocess.run([os.path.join(CLI_DIR, "simd_dct_cli_cpu")] + common + ["--max-simd", simd, "--to", str(ref_dump)], capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0, r.stdout + r.stderr
+    root = os.path.dirname(os.path.dirname(CLI_DIR))
+    r = subprocess.run([sys.executable, "-m", "simd_dct_b200.cli"] + common + ["--to", str(my_dump), "--resident"], capture_output=True, text=True, timeout=300, cwd=root)
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert "MiB/s" in r.stdout and "blocks/s" in r.stdout and "kernel only" in r.stdout
+    a, b = np.frombuffer(ref_dump.read_bytes(), dtype=np.uint8), np.frombuffer(my_dump.read_bytes(), dtype=np.uint8)
+    n = 768 * 512 if mode == "enc-quant-stereo" else 768 * 256
+    assert a.size == b.size == 768 * 512 and np.array_equal(a[:n], b[:n])
+    # decode: a quality under which the round trip is meaningful (the reference applies no level shift, so the DC entry
+    # .17 * quality must reach 8 / 0.5 / 0.95 for DC not to saturate; the unnormalised layout B needs 255 times that)
+    q = "25500" if mode == "enc-quant32" else "100"
+    r = subprocess.run([sys.executable, "-m", "simd_dct_b200.cli", str(raw), "768", "512", "--runs", "1", "--quality", q, "--mode", mode,
+                        "--no-quirk", "--inverse", "--to", str(inv_dump)], capture_output=True, text=True, timeout=300, cwd=root)
+    assert r.returncode == 0, r.stdout + r.stderr
+    back = np.frombuffer(inv_dump.read_bytes(), dtype=np.uint8).reshape(512, 768)
+    rows = 512 if mode == "enc-quant-stereo" else 256
+    err = np.abs(back[:rows].astype(int) - img[:rows].astype(int))
+    assert err.mean() < 6, float(err.mean())
+
+
 def test_config3_4k_interleaved_rgb(ctx, oracle):
     """BASELINE config 3 shape (3840x2160x3 interleaved RGB -> 3 planar coefficient sets), 3 frames:
     oracle parity on sampled bands of frame 1 (oracle = de-interleave + reference single-plane
