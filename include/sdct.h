@@ -108,6 +108,15 @@ int sdct_inverse_device(sdct_context *ctx, const sdct_job *job, const void *d_co
 int sdct_roundtrip_device(sdct_context *ctx, const sdct_job *job, const void *d_pixels_in, const float *lut,
                           void *d_pixels_out, void *stream);
 
+/* The step after the path (layout C only: each of its 64 planes is one homogeneous stream, src/simd_dct.cpp:1061-1069):
+ * per coefficient plane of every (frame, component) set, over the job's band window, how many levels are zero (byte 127,
+ * the quantiser's bias), in how many runs they come (in block order), the sum of |level - 127| and the bitwise OR of all |level - 127| (its
+ * top set bit = the magnitude bit width) - what an entropy coder needs to choose a code per plane.  d_stats: frames * components * 64 records, device memory. */
+typedef struct sdct_plane_stat {
+    uint64_t zeros, zero_runs, sum_abs, or_abs;
+} sdct_plane_stat;
+int sdct_plane_stats_device(sdct_context *ctx, const sdct_job *job, const void *d_coefs, sdct_plane_stat *d_stats, void *stream);
+
 /* host-buffer operations: chunked H2D -> kernel -> D2H pipeline ($SDCT_HOST_SLOTS chunks in flight, default 4, each a
  * dense 16-byte-aligned sub-job on the device); pinned caller memory is DMA'd directly, pageable memory goes through
  * pinned staging.  Only the bytes of the job's window are written - row padding and unprocessed bands stay untouched.

@@ -469,6 +469,22 @@ void sdct_oracle_inverse_tensor(int layout, const uint8_t *coef, size_t plane_st
             }
 }
 
+/* per-plane statistics of a layout-C coefficient plane (this repo's definition, include/sdct.h sdct_plane_stat; the
+ * reference stops at the quantised planes, src/simd_dct.cpp:1061-1069): zero levels (byte 127), zero runs, sum and
+ * bitwise OR of |level - 127| over bytes [0, n) */
+void sdct_oracle_plane_stats(const uint8_t *plane, size_t n, uint64_t out[4])
+{
+    uint64_t zeros = 0, runs = 0, sum = 0, mx = 0;
+    for (size_t k = 0; k < n; k++) {
+        const uint64_t a = plane[k] >= 127 ? (uint64_t)(plane[k] - 127) : (uint64_t)(127 - plane[k]);
+        zeros += a == 0;
+        runs += a == 0 && (k == 0 || plane[k - 1] != 127);
+        sum += a;
+        mx |= a;
+    }
+    out[0] = zeros; out[1] = runs; out[2] = sum; out[3] = mx;
+}
+
 /* component reorder: interleaved rows (ncomp bytes per pixel) <-> ncomp planar planes */
 void sdct_oracle_deinterleave(const uint8_t *in, size_t pitch, size_t width, size_t height, int ncomp, uint8_t *out)
 {

@@ -42,6 +42,7 @@ SYMBOLS = {
     "sdct_inverse_host": (C.c_int, [_vp, _JP, _vp, _fp, _vp]),
     "sdct_forward_host_multi": (C.c_int, [C.POINTER(_vp), C.c_int, _JP, _vp, _fp, _vp]),
     "sdct_inverse_host_multi": (C.c_int, [C.POINTER(_vp), C.c_int, _JP, _vp, _fp, _vp]),
+    "sdct_plane_stats_device": (C.c_int, [_vp, _JP, _vp, _vp, _vp]),
     "sdct_selftest_dct8": (C.c_int, [_vp, C.c_int, _fp, _sz]),
     "sdct_tensor_matrix": (None, [C.POINTER(C.c_int32)]),
     "sdct_synchronize": (C.c_int, [_vp]),

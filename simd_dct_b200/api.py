@@ -171,6 +171,14 @@ class Context:
                                               C.c_void_p(out.data_ptr()), self._stream()))
         return out
 
+    def plane_stats(self, coefs, job: Job):
+        """layout C: per coefficient plane {zero levels, zero runs, sum |level - 127|, OR of |level - 127|} over the job's
+        band window -> int64 tensor [frames, components, 64, 4] on the device (sdct_plane_stats_device)"""
+        import torch
+        out = torch.empty((int(job.frames), int(job.components), 64, 4), dtype=torch.int64, device=coefs.device)
+        check(self._lib.sdct_plane_stats_device(self._h, C.byref(job), C.c_void_p(coefs.data_ptr()), C.c_void_p(out.data_ptr()), self._stream()))
+        return out
+
     # host buffers (numpy arrays or CPU torch tensors, pinned or pageable); synchronous
     def forward_host(self, pixels, lut, job: Job, out=None):
         if out is None:

@@ -355,6 +355,29 @@ int sdct_roundtrip_device(sdct_context *c, const sdct_job *j, const void *d_in, 
     return run_device(c, SDCT_K_OP_ROUNDTRIP, j, (const uint8_t *)d_in, nullptr, (uint8_t *)d_out, lut, (cudaStream_t)stream);
 }
 
+int sdct_plane_stats_device(sdct_context *c, const sdct_job *j, const void *d_coefs, sdct_plane_stat *d_stats, void *stream)
+{
+    Geometry g;
+    int rc = sdct_validate(j, &g);
+    if (rc) return rc;
+    if (!c) return fail(SDCT_INVALID_PARAMETER, "context is null");
+    if (!d_coefs || !d_stats) return fail(SDCT_INVALID_PARAMETER, "null buffer");
+    if (j->layout != SDCT_LAYOUT_C) return fail(SDCT_NOT_SUPPORTED, "plane statistics are defined for layout C (64 coefficient planes)");
+    KParams p;
+    memset(&p, 0, sizeof(p));
+    p.coefs = (uint8_t *)const_cast<void *>(d_coefs);
+    p.coef_frame_stride = j->coef_frame_stride; p.coef_comp_stride = j->coef_comp_stride; p.coef_plane_stride = j->coef_plane_stride;
+    p.bpr = g.bpr; p.comps = g.comps; p.frames = (uint32_t)j->frames; p.sm_count = (uint32_t)c->sm_count;
+    p.row0 = g.band_begin * g.eyes; p.rows = (g.band_end - g.band_begin) * g.eyes;
+    const uint64_t cstr = j->coef_frame_stride | j->coef_comp_stride | j->coef_plane_stride;
+    p.coef_aligned16 = aligned(d_coefs, 16) && (cstr & 15) == 0 && (((uint64_t)p.row0 * p.bpr) & 15) == 0;
+    DeviceScope dev(c->device);
+    CU_TRY(dev.err);
+    CU_TRY(sdct_k_plane_stats(&p, d_stats, stream ? (cudaStream_t)stream : c->stream));
+    c->launches.fetch_add(1, std::memory_order_relaxed);
+    return SDCT_OK;
+}
+
 void sdct_tensor_matrix(int32_t *k4096) { if (k4096) sdct_tc_integer_matrix(k4096); }
 
 int sdct_selftest_dct8(sdct_context *c, int kind, float *h_data, size_t n)

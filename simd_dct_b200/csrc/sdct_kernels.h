@@ -86,5 +86,8 @@ static inline int sdct_tc_inverse_column_pixel(int j)
     const int k = j >> 3, q = (j & 7) >> 1, e = j & 1;
     return (2 * q + (k >> 2)) * 8 + 2 * (k & 3) + e;
 }
+// per-plane statistics of layout-C coefficient sets (sdct_stats.cu): d_stats = frames * comps * 64 records of four
+// 64-bit counters {zero levels, zero runs, sum |level - 127|, OR |level - 127|} over the job's band window
+extern "C" cudaError_t sdct_k_plane_stats(const KParams *p, void *d_stats, cudaStream_t s);
 // the 8-point kernels on n raw 8-float vectors (device memory, in place); see dct8_selftest_kernel
 extern "C" cudaError_t sdct_k_selftest(float *d_data, uint32_t n, int kind, cudaStream_t s);

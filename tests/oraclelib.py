@@ -68,6 +68,8 @@ class Oracle:
             getattr(L, "sdct_oracle_" + n).restype = None
         L.sdct_oracle_dct8_paired.argtypes = [_f32p, C.c_int]
         L.sdct_oracle_dct8_paired.restype = None
+        L.sdct_oracle_plane_stats.argtypes = [_u8p, _sz, C.POINTER(C.c_uint64)]
+        L.sdct_oracle_plane_stats.restype = None
         L.sdct_oracle_deinterleave.argtypes = [_u8p, _sz, _sz, _sz, C.c_int, _u8p]
         L.sdct_oracle_interleave.argtypes = [_u8p, _sz, _sz, C.c_int, _u8p, _sz]
         sig = [_u8p, _u8p, _f32p, _sz, _sz, _sz, _sz]
@@ -129,6 +131,13 @@ class Oracle:
             else:
                 fn(ptr)
         return vs
+
+    def plane_stats(self, plane):
+        """{zeros, zero_runs, sum_abs, or_abs} of one coefficient plane (bytes in block order)"""
+        plane = np.ascontiguousarray(plane, dtype=np.uint8)
+        out = np.zeros(4, dtype=np.uint64)
+        self.lib.sdct_oracle_plane_stats(_p8(plane), plane.size, out.ctypes.data_as(C.POINTER(C.c_uint64)))
+        return out
 
     def deinterleave(self, img):
         h, w, nc = img.shape
