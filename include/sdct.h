@@ -43,6 +43,10 @@ enum {
     SDCT_EXACT = 0,         /* the reference's fp32 operation order; byte-identical to its CPU output */
     SDCT_FAST = 1,          /* FMA-contracted arithmetic defined in oracle/sdct_oracle.c (<= 1 LSB from SDCT_EXACT) */
     SDCT_QUIRK_AVX_X3 = 2,  /* layout B: reproduce the reference's X3 sign (src/simd_dct.cpp:2181); see DESIGN.md */
+    SDCT_COLOR_YCBCR = 8,   /* interleaved 3-component pixels: RGB -> YCbCr (JFIF / BT.601 full range, 8-bit fixed point, exact integer
+                               arithmetic defined in oracle/sdct_oracle.c) fused into the forward load, YCbCr -> RGB into the inverse
+                               store; the coefficient sets of a frame are then Y, Cb, Cr.  Combines with every arithmetic mode.
+                               The inverse side needs 16-byte-aligned pixel rows and an even number of blocks per row. */
     SDCT_TENSOR = 4         /* tensor-core (tcgen05) integer form of the true DCT, defined in oracle/sdct_oracle.c mode TENSOR
                                (<= 1 LSB from SDCT_EXACT).  Forward: every geometry.  Inverse: one component, 16-byte-aligned
                                pixel rows and coefficients, an even number of blocks per row (SDCT_NOT_SUPPORTED otherwise).

@@ -469,6 +469,34 @@ void sdct_oracle_inverse_tensor(int layout, const uint8_t *coef, size_t plane_st
             }
 }
 
+/* colour front-end (this repo's definition; include/sdct.h SDCT_COLOR_YCBCR): JFIF / BT.601 full-range
+ * RGB <-> YCbCr in 8-bit fixed point.  in: interleaved rows (3 bytes per pixel), out: three planar planes Y, Cb, Cr. */
+static int floor_shift8(int v) { return v >= 0 ? v >> 8 : -((-v + 255) >> 8); }
+static uint8_t clamp_u8(int v) { return (uint8_t)(v < 0 ? 0 : (v > 255 ? 255 : v)); }
+
+void sdct_oracle_rgb_to_ycc(const uint8_t *in, size_t pitch, size_t width, size_t height, uint8_t *out)
+{
+    for (size_t y = 0; y < height; y++)
+        for (size_t x = 0; x < width; x++) {
+            const int r = in[y * pitch + 3 * x], g = in[y * pitch + 3 * x + 1], b = in[y * pitch + 3 * x + 2];
+            out[(0 * height + y) * width + x] = (uint8_t)((77 * r + 150 * g + 29 * b + 128) >> 8);
+            out[(1 * height + y) * width + x] = (uint8_t)((-43 * r - 85 * g + 128 * b + 127 + 32768) >> 8);
+            out[(2 * height + y) * width + x] = (uint8_t)((128 * r - 107 * g - 21 * b + 127 + 32768) >> 8);
+        }
+}
+
+void sdct_oracle_ycc_to_rgb(const uint8_t *planes, size_t width, size_t height, uint8_t *out, size_t pitch)
+{
+    for (size_t y = 0; y < height; y++)
+        for (size_t x = 0; x < width; x++) {
+            const int yy = planes[(0 * height + y) * width + x], cb = planes[(1 * height + y) * width + x] - 128,
+                      cr = planes[(2 * height + y) * width + x] - 128;
+            out[y * pitch + 3 * x] = clamp_u8(floor_shift8(256 * yy + 359 * cr + 128));
+            out[y * pitch + 3 * x + 1] = clamp_u8(floor_shift8(256 * yy - 88 * cb - 183 * cr + 128));
+            out[y * pitch + 3 * x + 2] = clamp_u8(floor_shift8(256 * yy + 454 * cb + 128));
+        }
+}
+
 /* per-plane statistics of a layout-C coefficient plane (this repo's definition, include/sdct.h sdct_plane_stat; the
  * reference stops at the quantised planes, src/simd_dct.cpp:1061-1069): zero levels (byte 127), zero runs, sum and
  * bitwise OR of |level - 127| over bytes [0, n) */

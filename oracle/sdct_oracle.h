@@ -81,6 +81,9 @@ void sdct_oracle_inverse_tensor(int layout, const uint8_t *coef, size_t plane_st
                          int eyes, size_t eye_stride, const float lut[64], uint8_t *out, size_t pitch, size_t xstep);
 
 /* component reorder: interleaved (width*ncomp bytes per row) <-> ncomp planar planes ---- */
+/* this repo: interleaved RGB rows -> planar Y, Cb, Cr planes and back (8-bit fixed point, exact) */
+void sdct_oracle_rgb_to_ycc(const uint8_t *in, size_t pitch, size_t width, size_t height, uint8_t *out);
+void sdct_oracle_ycc_to_rgb(const uint8_t *planes, size_t width, size_t height, uint8_t *out, size_t pitch);
 void sdct_oracle_plane_stats(const uint8_t *plane, size_t n, uint64_t out[4]);   /* this repo */
 void sdct_oracle_deinterleave(const uint8_t *in, size_t pitch, size_t width, size_t height,
                               int ncomp, uint8_t *out /* ncomp planes of width*height */);

@@ -16,7 +16,7 @@ from typing import Optional
 import numpy as np
 
 from . import _lib
-from ._lib import EXACT, FAST, LAYOUT_A, LAYOUT_B, LAYOUT_C, QUIRK_AVX_X3, TENSOR, Job, SdctError, check  # noqa: F401
+from ._lib import COLOR_YCBCR, EXACT, FAST, LAYOUT_A, LAYOUT_B, LAYOUT_C, QUIRK_AVX_X3, TENSOR, Job, SdctError, check  # noqa: F401
 
 sdr_Success, sdr_InvalidParameter, sdr_NotSupported = 0, 1, 2
 

@@ -170,6 +170,12 @@ int run_device(sdct_context *ctx, int op, const sdct_job *j, const uint8_t *pixe
     };
     p.pixel_vec = (pix_aligned(16) && g.comps == 1 && (g.bpr & 1) == 0) ? 2 : (pix_aligned(8) ? 1 : 0);
     p.pixel_aligned16 = pix_aligned(16);
+    if (j->flags & SDCT_COLOR_YCBCR) {
+        if (g.comps != 3) return fail(SDCT_INVALID_PARAMETER, "SDCT_COLOR_YCBCR needs components = 3 (interleaved RGB)");
+        if (op != SDCT_K_OP_FORWARD && !(p.pixel_aligned16 && (g.bpr & 1) == 0))
+            return fail(SDCT_NOT_SUPPORTED, "SDCT_COLOR_YCBCR on the output side needs 16-byte-aligned pixel rows and an even number of blocks per row");
+        p.color = 1;
+    }
     const uint64_t cstr = j->coef_frame_stride | j->coef_comp_stride;
     p.coef_aligned16 = coefs && aligned(coefs, 16) && (cstr & 15) == 0;
     p.coef_aligned4 = coefs && aligned(coefs, 4) && ((cstr | j->coef_plane_stride) & 3) == 0;

@@ -69,10 +69,76 @@ SDCT_DEV Tile tile_at(const KParams &p, const Walk &w)
     return t;
 }
 
+// ---- colour front-end (flag SDCT_COLOR_YCBCR) -------------------------------------------------------------
+// JFIF / BT.601 full-range RGB <-> YCbCr in 8-bit fixed point, exact integer arithmetic (restated in oracle/sdct_oracle.c):
+//   Y  = (77 R + 150 G + 29 B + 128) >> 8
+//   Cb = (-43 R - 85 G + 128 B + 127 + 32768) >> 8        Cr = (128 R - 107 G - 21 B + 127 + 32768) >> 8
+//   R = clamp((256 Y + 359 (Cr - 128) + 128) >> 8)         B = clamp((256 Y + 454 (Cb - 128) + 128) >> 8)
+//   G = clamp((256 Y - 88 (Cb - 128) - 183 (Cr - 128) + 128) >> 8)
+// Forward: one DP4A per pixel and component on the pixel's bytes gathered into one word [R, G, B, .]; the coefficient
+// 128 does not fit a signed byte, so the chroma forms take the complemented byte: 128 B = -128 (255 - B) + 128 * 255.
+// Every sum lies in [0, 65535]; the result is byte 1 of the sum.
+SDCT_DEV uint32_t dp4a_u8_s8(uint32_t a, uint32_t b, uint32_t c)
+{
+    uint32_t d;
+    asm("dp4a.u32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+    return d;
+}
+// the 16-bit sum whose byte 1 is component k (0 Y, 1 Cb, 2 Cr) of the pixel gathered in g = [R, G, B, .]
+SDCT_DEV uint32_t ycc_sum(uint32_t g, uint32_t k)
+{
+    const uint32_t coef = k == 0 ? 0x001d964du : (k == 1 ? 0x0080abd5u : 0x00eb9580u);   // [77, 150, 29] / [-43, -85, -128] / [-128, -107, -21]
+    const uint32_t flip = k == 0 ? 0u : (k == 1 ? 0x00ff0000u : 0x000000ffu);
+    const uint32_t bias = k == 0 ? 128u : 65535u;                                          // 128 * 255 + 127 + 32768
+    if (k == 0) return __dp4a(g, coef, bias);            // (150 needs the unsigned form; byte 3 meets a zero coefficient)
+    return dp4a_u8_s8(g ^ flip, coef, bias);
+}
+// interleaved pixel x of a 24-byte row held in six words -> [R, G, B, .]
+template <int X>
+SDCT_DEV uint32_t gather_rgb(const uint32_t (&s)[6])
+{
+    constexpr int b0 = 3 * X, w0 = b0 >> 2, o = b0 & 3;
+    if (o == 0) return s[w0];
+    constexpr int w1 = w0 + 1 < 6 ? w0 + 1 : 5;
+    return __byte_perm(s[w0], s[w1], (uint32_t)(o | ((o + 1) << 4) | ((o + 2) << 8) | ((o + 3 > 7 ? 7 : o + 3) << 12)));
+}
+// component k of the eight pixels of a row -> two words of four bytes
+SDCT_DEV void ycc_row(const uint32_t (&s)[6], uint32_t k, uint32_t &lo, uint32_t &hi)
+{
+    const uint32_t v0 = ycc_sum(gather_rgb<0>(s), k), v1 = ycc_sum(gather_rgb<1>(s), k), v2 = ycc_sum(gather_rgb<2>(s), k), v3 = ycc_sum(gather_rgb<3>(s), k);
+    const uint32_t v4 = ycc_sum(gather_rgb<4>(s), k), v5 = ycc_sum(gather_rgb<5>(s), k), v6 = ycc_sum(gather_rgb<6>(s), k), v7 = ycc_sum(gather_rgb<7>(s), k);
+    lo = __byte_perm(__byte_perm(v0, v1, 0x0051), __byte_perm(v2, v3, 0x0051), 0x5410);
+    hi = __byte_perm(__byte_perm(v4, v5, 0x0051), __byte_perm(v6, v7, 0x0051), 0x5410);
+}
+// the inverse for one pixel: levels (y, cb, cr) as integers -> the three sums whose >> 8, clamped, are R, G, B
+SDCT_DEV void ycc_to_rgb_sums(int y, int cb, int cr, int &r, int &g, int &b)
+{
+    const int y8 = (y << 8) + 128;
+    r = (y8 + 359 * cr - 359 * 128) >> 8;
+    g = (y8 - 88 * cb - 183 * cr + (88 + 183) * 128) >> 8;
+    b = (y8 + 454 * cb - 454 * 128) >> 8;
+}
+
+// four pixels' Y, Cb, Cr bytes (one word each) -> the 12 interleaved RGB bytes; the saturating pack does the clamp
+SDCT_DEV void ycc_words_to_rgb(uint32_t yw, uint32_t cbw, uint32_t crw, uint32_t *o)
+{
+    int r[4], g[4], b[4];
+#pragma unroll
+    for (int i = 0; i < 4; i++)
+        ycc_to_rgb_sums((int)((yw >> (8 * i)) & 0xffu), (int)((cbw >> (8 * i)) & 0xffu), (int)((crw >> (8 * i)) & 0xffu), r[i], g[i], b[i]);
+    // cvt.pack.sat.u8.s32.b32 d, a, b, c: d = c << 16 | sat(a) << 8 | sat(b)
+#define SDCT_PK(b0, b1, b2, b3) pack_sat((uint32_t)(b1), (uint32_t)(b0), pack_sat((uint32_t)(b3), (uint32_t)(b2), 0u))
+    o[0] = SDCT_PK(r[0], g[0], b[0], r[1]);
+    o[1] = SDCT_PK(g[1], b[1], r[2], g[2]);
+    o[2] = SDCT_PK(b[2], r[3], g[3], b[3]);
+#undef SDCT_PK
+}
+
 // ---- pixel block -> 16 words (row r = words 2r, 2r+1), component extraction fused ----------------
 // VEC: 0 = byte loads, 1 = 8-byte loads, 2 = one 16-byte load per row for the adjacent pair (P, Q)
+// color (interleaved pixels only): component `comp` of the pixels converted to YCbCr instead of the raw component
 template <int COMPS, int VEC>
-SDCT_DEV void load_block(const uint8_t *px, uint64_t pitch, uint32_t comp, uint32_t w[16])
+SDCT_DEV void load_block(const uint8_t *px, uint64_t pitch, uint32_t comp, uint32_t w[16], uint32_t color = 0)
 {
     if (COMPS == 1) {
 #pragma unroll
@@ -109,6 +175,10 @@ SDCT_DEV void load_block(const uint8_t *px, uint64_t pitch, uint32_t comp, uint3
 #pragma unroll
                     for (int c = 0; c < 4; c++) s[k] |= (uint32_t)__ldg(px + r * pitch + 4 * k + c) << (8 * c);
                 }
+            }
+            if (color) {
+                ycc_row(s, comp, w[2 * r], w[2 * r + 1]);
+                continue;
             }
             w[2 * r] = __byte_perm(__byte_perm(s[0], s[1], selT), s[2], selU);
             w[2 * r + 1] = __byte_perm(__byte_perm(s[3], s[4], selT), s[5], selU);

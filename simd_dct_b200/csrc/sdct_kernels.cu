@@ -47,6 +47,7 @@ struct BlockPos {
     const uint8_t *px[2];   // top-left pixel (component 0)
     bool valid[2];
     uint32_t comp;
+    uint32_t color;         // interleaved pixels: convert to YCbCr on load
 };
 
 template <int LAYOUT>
@@ -54,6 +55,7 @@ SDCT_DEV BlockPos locate(const KParams &p, const Tile &t)
 {
     BlockPos b;
     b.comp = t.comp;
+    b.color = p.color;
 #pragma unroll
     for (int k = 0; k < 2; k++) {
         const uint32_t slot = (LAYOUT == SDCT_K_LAYOUT_A) ? threadIdx.x + k * TB : 2 * threadIdx.x + k;
@@ -116,8 +118,8 @@ SDCT_DEV void load_pair(const BlockPos &b, uint64_t pitch, uint32_t wp[16], uint
             wp[2 * r] = v.x; wp[2 * r + 1] = v.y; wq[2 * r] = v.z; wq[2 * r + 1] = v.w;
         }
     } else {
-        load_block<COMPS, (VEC ? 1 : 0)>(b.px[0], pitch, b.comp, wp);
-        load_block<COMPS, (VEC ? 1 : 0)>(b.px[1], pitch, b.comp, wq);
+        load_block<COMPS, (VEC ? 1 : 0)>(b.px[0], pitch, b.comp, wp, b.color);
+        load_block<COMPS, (VEC ? 1 : 0)>(b.px[1], pitch, b.comp, wq, b.color);
     }
 }
 
@@ -690,6 +692,7 @@ SDCT_DEV void flush_rgb(const uint8_t *img3, const KParams &p, const Tile &t, ui
         uint32_t o[12];
 #pragma unroll
         for (int q = 0; q < 4; q++) {   // four pixels (R, G, B words q) -> 12 bytes
+            if (p.color) { ycc_words_to_rgb(rr[q], gg[q], bb[q], o + 3 * q); continue; }
             o[3 * q] = __byte_perm(__byte_perm(rr[q], gg[q], 0x1040), bb[q], 0x3410);       // R0 G0 B0 R1
             o[3 * q + 1] = __byte_perm(__byte_perm(gg[q], rr[q], 0x2601), bb[q], 0x3250);   // G1 B1 R2 G2
             o[3 * q + 2] = __byte_perm(__byte_perm(bb[q], rr[q], 0x3072), gg[q], 0x3710);   // B2 R3 G3 B3

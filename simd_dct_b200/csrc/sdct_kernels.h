@@ -37,6 +37,7 @@ struct KParams {
     uint32_t sm_count;        // SMs of the device (persistent grid size)
     uint32_t pixel_vec;       // 0 = byte access, 1 = 8-byte rows, 2 = 16-byte rows for an adjacent block pair
     uint32_t coef_aligned16, coef_aligned4;
+    uint32_t color;           // interleaved pixels: 1 = RGB <-> YCbCr fused into the load / the store (SDCT_COLOR_YCBCR)
     uint32_t pixel_aligned16; // pixel base pointers and strides are multiples of 16 (whatever the component count)
     // scale tables, each value duplicated for the two packed lanes (P, Q)
     float2 tab[64];           // forward: quantiser scale; inverse: dequantiser scale

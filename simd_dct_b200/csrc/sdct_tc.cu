@@ -440,6 +440,16 @@ SDCT_DEV void rgb_row_to_half(const uint32_t (&s)[6], uint32_t *h)
     }
 }
 
+// the same with the colour front-end: component k of the row's eight pixels converted to YCbCr (sdct_io.cuh) -> 4 fp16-pair
+// words; a sum's byte 1 is the result and its bytes 2, 3 are zero, so one PRMT builds a pair
+SDCT_DEV void ycc_row_to_half(const uint32_t (&s)[6], uint32_t k, uint32_t *h)
+{
+    h[0] = __byte_perm(ycc_sum(gather_rgb<0>(s), k), ycc_sum(gather_rgb<1>(s), k), 0x7531);
+    h[1] = __byte_perm(ycc_sum(gather_rgb<2>(s), k), ycc_sum(gather_rgb<3>(s), k), 0x7531);
+    h[2] = __byte_perm(ycc_sum(gather_rgb<4>(s), k), ycc_sum(gather_rgb<5>(s), k), 0x7531);
+    h[3] = __byte_perm(ycc_sum(gather_rgb<6>(s), k), ycc_sum(gather_rgb<7>(s), k), 0x7531);
+}
+
 // base address of block row r (relative to the window's first row) of a tile's frame
 SDCT_DEV const uint8_t *block_row_base(const KParams &p, const Tile &t, uint32_t r)
 {
@@ -511,7 +521,8 @@ SDCT_DEV void producer_role(const KParams &p, uint64_t *bars, uint32_t tmem_base
                 uint32_t h[32];
 #pragma unroll
                 for (int r = 0; r < 8; r++) {
-                    if (c == 0) rgb_row_to_half<0>(s[r], h + 4 * r);
+                    if (p.color) ycc_row_to_half(s[r], c, h + 4 * r);   // colour front-end: component c of YCbCr
+                    else if (c == 0) rgb_row_to_half<0>(s[r], h + 4 * r);
                     else if (c == 1) rgb_row_to_half<1>(s[r], h + 4 * r);
                     else rgb_row_to_half<2>(s[r], h + 4 * r);
                 }
@@ -604,7 +615,7 @@ SDCT_DEV void producer_role(const KParams &p, uint64_t *bars, uint32_t tmem_base
         for (int j = 0; j < PF; j++) {
             if (wl.tile < p.tiles) {
                 const Tile t = tile_at<COMPS, TILE>(p, wl);
-                load_block<COMPS, VEC>(block_pixels<COMPS>(p, t, my_slot), p.pitch, t.comp, w[j]);
+                load_block<COMPS, VEC>(block_pixels<COMPS>(p, t, my_slot), p.pitch, t.comp, w[j], p.color);
             }
             wl.next(p);
         }
@@ -618,7 +629,7 @@ SDCT_DEV void producer_role(const KParams &p, uint64_t *bars, uint32_t tmem_base
                 for (int i = 0; i < 16; i++) cur[i] = w[j][i];
                 if (wl.tile < p.tiles) {
                     const Tile tn = tile_at<COMPS, TILE>(p, wl);
-                    load_block<COMPS, VEC>(block_pixels<COMPS>(p, tn, my_slot), p.pitch, tn.comp, w[j]);
+                    load_block<COMPS, VEC>(block_pixels<COMPS>(p, tn, my_slot), p.pitch, tn.comp, w[j], p.color);
                 }
                 wl.next(p);
                 publish_a(p, bars, tmem_base, lane_field, k, cur);
@@ -1103,6 +1114,7 @@ SDCT_DEV void tc_flush_rgb(const uint8_t *img3, const KParams &p, const Tile &t,
         uint32_t o[12];
 #pragma unroll
         for (int q = 0; q < 4; q++) {
+            if (p.color) { ycc_words_to_rgb(rr[q], gg[q], bb[q], o + 3 * q); continue; }
             o[3 * q] = __byte_perm(__byte_perm(rr[q], gg[q], 0x1040), bb[q], 0x3410);       // R0 G0 B0 R1
             o[3 * q + 1] = __byte_perm(__byte_perm(gg[q], rr[q], 0x2601), bb[q], 0x3250);   // G1 B1 R2 G2
             o[3 * q + 2] = __byte_perm(__byte_perm(bb[q], rr[q], 0x3072), gg[q], 0x3710);   // B2 R3 G3 B3

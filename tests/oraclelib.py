@@ -68,6 +68,8 @@ class Oracle:
             getattr(L, "sdct_oracle_" + n).restype = None
         L.sdct_oracle_dct8_paired.argtypes = [_f32p, C.c_int]
         L.sdct_oracle_dct8_paired.restype = None
+        L.sdct_oracle_rgb_to_ycc.argtypes = [_u8p, _sz, _sz, _sz, _u8p]
+        L.sdct_oracle_ycc_to_rgb.argtypes = [_u8p, _sz, _sz, _u8p, _sz]
         L.sdct_oracle_plane_stats.argtypes = [_u8p, _sz, C.POINTER(C.c_uint64)]
         L.sdct_oracle_plane_stats.restype = None
         L.sdct_oracle_deinterleave.argtypes = [_u8p, _sz, _sz, _sz, C.c_int, _u8p]
@@ -131,6 +133,21 @@ class Oracle:
             else:
                 fn(ptr)
         return vs
+
+    def rgb_to_ycc(self, img):
+        """(H, W, 3) interleaved RGB -> (3, H, W) planar Y, Cb, Cr (the colour front-end's definition)"""
+        img = np.ascontiguousarray(img, dtype=np.uint8)
+        h, w, _ = img.shape
+        out = np.empty((3, h, w), dtype=np.uint8)
+        self.lib.sdct_oracle_rgb_to_ycc(_p8(img), 3 * w, w, h, _p8(out))
+        return out
+
+    def ycc_to_rgb(self, planes):
+        planes = np.ascontiguousarray(planes, dtype=np.uint8)
+        _, h, w = planes.shape
+        out = np.empty((h, w, 3), dtype=np.uint8)
+        self.lib.sdct_oracle_ycc_to_rgb(_p8(planes), w, h, _p8(out), 3 * w)
+        return out
 
     def plane_stats(self, plane):
         """{zeros, zero_runs, sum_abs, or_abs} of one coefficient plane (bytes in block order)"""

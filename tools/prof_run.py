@@ -32,6 +32,8 @@ for name in a.names:
     mode = parts[2] if len(parts) > 2 else "exact"
     comps = 3 if op in ("rgb", "irgb", "rtrgb") else 1
     flags = sd.TENSOR if mode == "tensor" else sd.FAST if mode == "fast" else (sd.EXACT | (sd.QUIRK_AVX_X3 if lay == sd.LAYOUT_B else 0))
+    if len(parts) > 3 and parts[3] == "ycc":   # colour front-end (interleaved pixels)
+        flags |= sd.COLOR_YCBCR
     job = sd.dense_job(lay, a.w, a.h, frames=a.frames, components=comps, flags=flags)
     shape = (a.frames, a.h, a.w) if comps == 1 else (a.frames, a.h, a.w, 3)
     pix = torch.from_numpy(rng.integers(0, 256, shape, dtype=np.uint8)).cuda()
