@@ -158,12 +158,7 @@ SDCT_DEV void load_block(const uint8_t *px, uint64_t pitch, uint32_t comp, uint3
         }
     } else {
         // 8 interleaved pixels = 24 bytes; component k sits at bytes k, k+3, ..., k+21.
-        // Two PRMTs per output word; the selectors repeat every 12 bytes (= 3 words).
-        const uint32_t selT = comp == 0 ? 0x0630u : (comp == 1 ? 0x0741u : 0x0052u);
-        const uint32_t selU = comp == 0 ? 0x5210u : (comp == 1 ? 0x6210u : 0x7410u);
-#pragma unroll
-        for (int r = 0; r < 8; r++) {
-            uint32_t s[6];
+        auto row_words = [&](int r, uint32_t (&s)[6]) {
             if (VEC) {
                 const uint2 *q = reinterpret_cast<const uint2 *>(px + r * pitch);
                 const uint2 a = __ldg(q), b = __ldg(q + 1), c = __ldg(q + 2);
@@ -176,10 +171,23 @@ SDCT_DEV void load_block(const uint8_t *px, uint64_t pitch, uint32_t comp, uint3
                     for (int c = 0; c < 4; c++) s[k] |= (uint32_t)__ldg(px + r * pitch + 4 * k + c) << (8 * c);
                 }
             }
-            if (color) {
+        };
+        if (color) {   // (uniform; its own loop, so that the plain path below keeps its schedule and registers)
+#pragma unroll
+            for (int r = 0; r < 8; r++) {
+                uint32_t s[6];
+                row_words(r, s);
                 ycc_row(s, comp, w[2 * r], w[2 * r + 1]);
-                continue;
             }
+            return;
+        }
+        // Two PRMTs per output word; the selectors repeat every 12 bytes (= 3 words).
+        const uint32_t selT = comp == 0 ? 0x0630u : (comp == 1 ? 0x0741u : 0x0052u);
+        const uint32_t selU = comp == 0 ? 0x5210u : (comp == 1 ? 0x6210u : 0x7410u);
+#pragma unroll
+        for (int r = 0; r < 8; r++) {
+            uint32_t s[6];
+            row_words(r, s);
             w[2 * r] = __byte_perm(__byte_perm(s[0], s[1], selT), s[2], selU);
             w[2 * r + 1] = __byte_perm(__byte_perm(s[3], s[4], selT), s[5], selU);
         }

@@ -43,12 +43,21 @@ namespace tc {
 #define SDCT_TC_PRODUCER_WGS 1
 #endif
 constexpr int PRODUCER_WGS = SDCT_TC_PRODUCER_WGS;
-constexpr int CONSUMER_WGS = 2;
+#ifndef SDCT_TC_CONSUMER_WGS
+#define SDCT_TC_CONSUMER_WGS 2
+#endif
+// tile k is stored by consumer warpgroup k % CONSUMER_WGS.  Three warpgroups (640 threads, registers moved with setmaxnreg:
+// producer 72 / consumers 120 / MMA 40) were measured SLOWER than two on every kernel (forward 50-55 -> 55-64 us, inverse
+// 54-58 -> 87 us at 64 x 1080p): with three D stages each warpgroup then owns exactly one, so the chain "consumer
+// releases the stage -> MMA -> commit -> consumer wakes" is exposed once per tile.  Kept as a compile-time experiment.
+constexpr int CONSUMER_WGS = SDCT_TC_CONSUMER_WGS;
+static_assert(CONSUMER_WGS == 2 || CONSUMER_WGS == 3, "consumer warpgroups");
 constexpr int MMA_WARPS = 2;                // each issues the MMAs of every MMA_WARPS-th tile (one elected thread)
 constexpr int THREADS = 128 * (PRODUCER_WGS + CONSUMER_WGS + 1);   // producer WGs, consumer WGs, the MMA warpgroup (two MMA warps, the TMA warp)
 // setmaxnreg moves registers inside the CTA's own allocation only (THREADS * LAUNCH_REGS <= 65536): what the
 // consumer warpgroups acquire, the producer warpgroups must have released
-constexpr int LAUNCH_REGS = PRODUCER_WGS == 2 ? 96 : 128, PRODUCER_REGS = 80, CONSUMER_REGS = 128, MMA_REGS = 56;
+constexpr int LAUNCH_REGS = 65536 / THREADS / 8 * 8;   // what __launch_bounds__(THREADS, 1) gives every thread
+constexpr int PRODUCER_REGS = CONSUMER_WGS == 3 ? 72 : 80, CONSUMER_REGS = CONSUMER_WGS == 3 ? 120 : 128, MMA_REGS = CONSUMER_WGS == 3 ? 40 : 56;
 constexpr bool MOVE_REGS = LAUNCH_REGS < CONSUMER_REGS;
 static_assert(THREADS * LAUNCH_REGS <= 65536, "register file");
 static_assert(!MOVE_REGS || PRODUCER_WGS * (LAUNCH_REGS - PRODUCER_REGS) + (LAUNCH_REGS - MMA_REGS) >= CONSUMER_WGS * (CONSUMER_REGS - LAUNCH_REGS), "setmaxnreg balance");
@@ -94,11 +103,19 @@ constexpr int SMEM_BAR_OFF = SMEM_RING_OFF + PRODUCER_WGS * RING * RING_TILE_BYT
 //   a_empty[k % 4]          MMA commit -> producer warpgroup k % 2
 //   d_full[k % 2][k % 3]    MMA commit -> consumer warpgroup k % 2
 //   d_empty[k % 2][k % 3]   consumer k % 2 -> the MMA warp of tile k + 3   (128 arrivals)
-constexpr int BAR_A_FULL = 0, BAR_A_EMPTY = A_STAGES, BAR_D_FULL = 2 * A_STAGES, BAR_D_EMPTY = 2 * A_STAGES + 2 * D_STAGES;
+constexpr int BAR_A_FULL = 0, BAR_A_EMPTY = A_STAGES, BAR_D_FULL = 2 * A_STAGES, BAR_D_EMPTY = BAR_D_FULL + CONSUMER_WGS * D_STAGES;
+// tile k's D barriers: index k % D_PERIOD.  Six of each, so that a barrier belongs to ONE MMA warp (tiles of one parity)
+// and ONE consumer warpgroup (D_PERIOD is a multiple of MMA_WARPS, CONSUMER_WGS and D_STAGES): with a period of 3 the
+// two MMA warps would alternate on a barrier, each seeing every other phase, and a parity wait cannot tell phase u from
+// phase u - 2 (that build passed the small tests and hung on 16 200 tiles).
+constexpr int D_PERIOD = 6;
+static_assert(D_PERIOD % MMA_WARPS == 0 && D_PERIOD % CONSUMER_WGS == 0 && D_PERIOD % D_STAGES == 0 && D_PERIOD <= CONSUMER_WGS * D_STAGES, "D barrier period");
+__host__ __device__ constexpr uint32_t d_bar(uint32_t k) { return k % D_PERIOD; }
+constexpr int BAR_PRODUCER = 8, BAR_FLUSH = 9;    // named barriers (ids 1 .. CONSUMER_WGS: the consumer warpgroups' own)
 //   ring_full[j % 6]        TMA (complete_tx) -> producer warpgroup; ring_empty[j % 6]: its four warps -> TMA thread
 constexpr int TMA_RING = 6;                       // slots of two 8 KiB boxes: 8 rows x 1024 bytes of this / of the next block row
 constexpr int TMA_BOX_BYTES = 8 * TILE * 8, TMA_SLOT_BYTES = 2 * TMA_BOX_BYTES;
-constexpr int BAR_RING_FULL = 2 * A_STAGES + 4 * D_STAGES, BAR_RING_EMPTY = BAR_RING_FULL + TMA_RING;
+constexpr int BAR_RING_FULL = BAR_D_EMPTY + CONSUMER_WGS * D_STAGES, BAR_RING_EMPTY = BAR_RING_FULL + TMA_RING;
 constexpr int NUM_BARS = BAR_RING_EMPTY + TMA_RING;
 static_assert(TMA_RING * TMA_SLOT_BYTES <= PRODUCER_WGS * RING * RING_TILE_BYTES, "the TMA ring lives in the cp.async ring's space");
 static_assert(RGB_RING * 8 * RGB_ROW_BYTES <= PRODUCER_WGS * RING * RING_TILE_BYTES, "... and so does the RGB ring");
@@ -504,7 +521,7 @@ SDCT_DEV void producer_role(const KParams &p, uint64_t *bars, uint32_t tmem_base
         for (uint32_t j = 0;; j++, tile += gridDim.x) {
             if (tile >= p.tiles) return;
             cp_async_wait<RGB_RING - 2>();   // this thread's pieces of pixel tile j have landed
-            named_barrier(3);                // ... and everybody's; everybody has read pixel tile j - 1
+            named_barrier(BAR_PRODUCER);     // ... and everybody's; everybody has read pixel tile j - 1
             issue(j + RGB_RING - 1);         // into the slot of pixel tile j - 1
             const uint8_t *src = ring + (j % RGB_RING) * (8 * RGB_ROW_BYTES) + my_slot * 24u;
             uint32_t s[8][6];
@@ -516,13 +533,23 @@ SDCT_DEV void producer_role(const KParams &p, uint64_t *bars, uint32_t tmem_base
                     s[r][2 * e] = v.x; s[r][2 * e + 1] = v.y;
                 }
             }
+            if (p.color) {   // colour front-end: components of YCbCr (uniform; its own loop, the plain path keeps its schedule)
+#pragma unroll
+                for (int c = 0; c < 3; c++) {
+                    uint32_t h[32];
+#pragma unroll
+                    for (int r = 0; r < 8; r++) ycc_row_to_half(s[r], (uint32_t)c, h + 4 * r);
+                    store_a_halves(p, bars, tmem_base, lane_field, 3 * j + c, h);
+                    signal_a_rows(p, bars, 3 * j + c);
+                }
+                continue;
+            }
 #pragma unroll
             for (int c = 0; c < 3; c++) {
                 uint32_t h[32];
 #pragma unroll
                 for (int r = 0; r < 8; r++) {
-                    if (p.color) ycc_row_to_half(s[r], c, h + 4 * r);   // colour front-end: component c of YCbCr
-                    else if (c == 0) rgb_row_to_half<0>(s[r], h + 4 * r);
+                    if (c == 0) rgb_row_to_half<0>(s[r], h + 4 * r);
                     else if (c == 1) rgb_row_to_half<1>(s[r], h + 4 * r);
                     else rgb_row_to_half<2>(s[r], h + 4 * r);
                 }
@@ -680,7 +707,7 @@ SDCT_DEV void mma_role(const KParams &p, uint64_t *bars, uint32_t tmem_base, uin
         mbar_wait(bars + BAR_A_FULL + sa, ua & 1);
         stamp(tr, 1, k, 1);
         if (k >= D_STAGES)   // tile k - 3 (other parity: the other consumer warpgroup) has left the D stage
-            mbar_wait(bars + BAR_D_EMPTY + ((k + 1) & 1) * D_STAGES + sd, ((k - D_STAGES) / (2 * D_STAGES)) & 1);
+            mbar_wait(bars + BAR_D_EMPTY + d_bar(k - D_STAGES), ((k - D_STAGES) / D_PERIOD) & 1);
         fence_after();
         stamp(tr, 1, k, 2);
         const uint32_t tA = tmem_base + TMEM_A_OFF + sa * A_COLS, tD = tmem_base + TMEM_D_OFF + sd * D_COLS;
@@ -691,7 +718,7 @@ SDCT_DEV void mma_role(const KParams &p, uint64_t *bars, uint32_t tmem_base, uin
         }
         stamp(tr, 1, k, 3);
         mma_commit(bars + BAR_A_EMPTY + sa);
-        mma_commit(bars + BAR_D_FULL + (k & 1) * D_STAGES + sd);
+        mma_commit(bars + BAR_D_FULL + d_bar(k));
         stamp(tr, 1, k, 4);
     }
 }
@@ -711,7 +738,7 @@ SDCT_DEV void consumer_role(const KParams &p, uint64_t *bars, uint32_t tmem_base
     const uint32_t sp0 = (L >> 5) * 32u + 2u * g;
     const uint32_t abl = ablate_bits(p);
     // CF == 1: wk walks this warpgroup's tiles.  CF == 3: wk walks the CTA's pixel tiles, comp = k % 3.
-    static_assert(CF == 1 || (CF == 3 && CONSUMER_WGS == 2), "fused components");
+    static_assert(CF == 1 || CF == 3, "fused components");
     TileWalk wk;
     if (CF == 1) wk.init(p, c, CONSUMER_WGS); else wk.init(p, 0, 1);
     uint32_t comp = CF == 1 ? 0u : c;
@@ -722,8 +749,8 @@ SDCT_DEV void consumer_role(const KParams &p, uint64_t *bars, uint32_t tmem_base
     };
     for (uint32_t k = c;; k += CONSUMER_WGS, advance()) {
         if (wk.tile >= p.tiles) break;
-        const uint32_t sd = k % D_STAGES, ud = k / (2 * D_STAGES);
-        uint64_t *d_full = bars + BAR_D_FULL + c * D_STAGES + sd, *d_empty = bars + BAR_D_EMPTY + c * D_STAGES + sd;
+        const uint32_t sd = k % D_STAGES, ud = k / D_PERIOD;
+        uint64_t *d_full = bars + BAR_D_FULL + d_bar(k), *d_empty = bars + BAR_D_EMPTY + d_bar(k);
         Tile cur = tile_at<(CF == 1 ? COMPS : 1), TILE>(p, wk);
         if (CF != 1) { cur.comp = comp; cur.coef += (uint64_t)comp * p.coef_comp_stride; }
         const uint64_t n_first = (uint64_t)p.row0 * p.bpr + cur.n0;
@@ -834,7 +861,7 @@ __global__ void __launch_bounds__(THREADS, 1) forward_tc_kernel(const __grid_con
             mbar_init(bars + BAR_A_FULL + i, 128);
             mbar_init(bars + BAR_A_EMPTY + i, 1);
         }
-        for (int i = 0; i < 2 * D_STAGES; i++) {
+        for (int i = 0; i < CONSUMER_WGS * D_STAGES; i++) {
             mbar_init(bars + BAR_D_FULL + i, 1);
             mbar_init(bars + BAR_D_EMPTY + i, 128);
         }
@@ -1021,7 +1048,7 @@ SDCT_DEV void inv_producer_role(const KParams &p, uint64_t *bars, uint8_t *a_sta
         } else {
             cp_async_wait<AHEAD - 1>();   // this thread's pieces of tile k have landed
             if (!OWN) {
-                named_barrier(3);         // ... and everybody's; everybody has read tile k - 1
+                named_barrier(BAR_PRODUCER);   // ... and everybody's; everybody has read tile k - 1
                 issue(k + AHEAD);         // into the slot of tile k - 1
             }
         }
@@ -1080,7 +1107,7 @@ SDCT_DEV void inv_mma_role(const KParams &p, uint64_t *bars, uint32_t tmem_base,
         mbar_wait(bars + BAR_A_FULL + sa, ua & 1);
         stamp(tr, 1, k, 1);
         if (k >= D_STAGES)
-            mbar_wait(bars + BAR_D_EMPTY + ((k + 1) & 1) * D_STAGES + sd, ((k - D_STAGES) / (2 * D_STAGES)) & 1);
+            mbar_wait(bars + BAR_D_EMPTY + d_bar(k - D_STAGES), ((k - D_STAGES) / D_PERIOD) & 1);
         fence_after();
         stamp(tr, 1, k, 2);
         constexpr uint32_t INV_A_LBO = inv_lbo<LAYOUT>(), INV_A_SBO = inv_sbo<LAYOUT>();
@@ -1090,7 +1117,7 @@ SDCT_DEV void inv_mma_role(const KParams &p, uint64_t *bars, uint32_t tmem_base,
         for (int ks = 0; ks < 4; ks++)   // K = 16 levels per instruction: two core matrices along K
             if (!(ablate_bits(p) & 1)) mma_f16_ss(tD, ad + (uint64_t)((2 * ks * INV_A_LBO) >> 4), bd[ks], idesc, ks);
         mma_commit(bars + BAR_A_EMPTY + sa);
-        mma_commit(bars + BAR_D_FULL + (k & 1) * D_STAGES + sd);
+        mma_commit(bars + BAR_D_FULL + d_bar(k));
         stamp(tr, 1, k, 3);
     }
 }
@@ -1100,15 +1127,15 @@ SDCT_DEV void inv_mma_role(const KParams &p, uint64_t *bars, uint32_t tmem_base,
 // 24 PRMTs, three 16-byte stores (see flush_rgb in sdct_kernels.cu)
 SDCT_DEV void tc_flush_rgb(const uint8_t *img3, const KParams &p, const Tile &t, uint32_t T)
 {
-    const uint32_t u = T & 63u, slot = 2u * u;
-    if (slot >= t.count) return;
-    const uint32_t nl = t.n0 + slot;
-    const uint32_t r0 = fastdiv(nl, p.div_bpr), bx = nl - r0 * p.bpr, row = r0 + p.row0;
-    const uint32_t band = p.eyes == 2 ? row >> 1 : row, eye = p.eyes == 2 ? row & 1 : 0;
-    uint8_t *dst = const_cast<uint8_t *>(t.pix) + (uint64_t)eye * p.eye_stride + (uint64_t)(band * 8 + (T >> 6)) * p.pitch + (uint64_t)bx * 24;
-    const uint8_t *src = img3 + (T >> 6) * PIX_PITCH + u * 16u;
-#pragma unroll
-    for (int i = 0; i < 2; i++, dst += 4 * p.pitch, src += 4 * PIX_PITCH) {
+    // 8 pixel rows x 64 block pairs = 512 units of 48 bytes over the consumer threads
+    for (uint32_t unit = T; unit < 8u * (TILE / 2); unit += CONSUMER_WGS * 128u) {
+        const uint32_t u = unit & 63u, r = unit >> 6, slot = 2u * u;
+        if (slot >= t.count) continue;
+        const uint32_t nl = t.n0 + slot;
+        const uint32_t r0 = fastdiv(nl, p.div_bpr), bx = nl - r0 * p.bpr, row = r0 + p.row0;
+        const uint32_t band = p.eyes == 2 ? row >> 1 : row, eye = p.eyes == 2 ? row & 1 : 0;
+        uint8_t *dst = const_cast<uint8_t *>(t.pix) + (uint64_t)eye * p.eye_stride + (uint64_t)(band * 8 + r) * p.pitch + (uint64_t)bx * 24;
+        const uint8_t *src = img3 + r * PIX_PITCH + u * 16u;
         const uint4 R = *reinterpret_cast<const uint4 *>(src), G = *reinterpret_cast<const uint4 *>(src + PIX_COMP), B = *reinterpret_cast<const uint4 *>(src + 2 * PIX_COMP);
         const uint32_t rr[4] = {R.x, R.y, R.z, R.w}, gg[4] = {G.x, G.y, G.z, G.w}, bb[4] = {B.x, B.y, B.z, B.w};
         uint32_t o[12];
@@ -1180,7 +1207,7 @@ SDCT_DEV void inv_consumer_role(const KParams &p, uint64_t *bars, uint32_t tmem_
     };
     // CF == 1: wk walks this warpgroup's tiles.  CF == 3: wk walks the CTA's pixel tiles; tile k = component k % 3 of pixel
     // tile k / 3, whose pixel rows go to the shared-memory image (k / 3) % 2 instead of global memory.
-    static_assert(CF == 1 || (CF == 3 && CONSUMER_WGS == 2), "fused components");
+    static_assert(CF == 1 || CF == 3, "fused components");
     TileWalk wk;
     if (CF == 1) wk.init(p, c, CONSUMER_WGS); else wk.init(p, 0, 1);
     uint32_t comp = CF == 1 ? 0u : c;
@@ -1188,8 +1215,8 @@ SDCT_DEV void inv_consumer_role(const KParams &p, uint64_t *bars, uint32_t tmem_
     if (CF == 1 && wk.tile < p.tiles) locate_tile(wk, cur);
     for (uint32_t k = c;; k += CONSUMER_WGS) {
         if (wk.tile >= p.tiles) break;
-        const uint32_t sd = k % D_STAGES, ud = k / (2 * D_STAGES);
-        uint64_t *d_full = bars + BAR_D_FULL + c * D_STAGES + sd, *d_empty = bars + BAR_D_EMPTY + c * D_STAGES + sd;
+        const uint32_t sd = k % D_STAGES, ud = k / D_PERIOD;
+        uint64_t *d_full = bars + BAR_D_FULL + d_bar(k), *d_empty = bars + BAR_D_EMPTY + d_bar(k);
         Tile ptile;             // CF == 3: the pixel tile of this tile
         uint8_t *img = nullptr; //          and this component's image
         bool last_own = false;  //          this warpgroup's last component of the pixel tile
@@ -1271,7 +1298,7 @@ SDCT_DEV void inv_consumer_role(const KParams &p, uint64_t *bars, uint32_t tmem_
             // both warpgroups have staged their components of the pixel tile: write it out interleaved.  (Image j % 2
             // is written again by pixel tile j + 2, after the barrier of pixel tile j + 1, which every thread reaches
             // only after this flush.)
-            asm volatile("bar.sync 4, 256;" ::: "memory");
+            asm volatile("bar.sync %0, %1;" ::"n"(BAR_FLUSH), "n"(CONSUMER_WGS * 128) : "memory");
             tc_flush_rgb(pix_images + ((k / CF) & 1u) * PIX_IMG3, p, ptile, c * 128u + L);
         }
     }
@@ -1295,7 +1322,7 @@ __global__ void __launch_bounds__(THREADS, 1) inverse_tc_kernel(const __grid_con
             mbar_init(bars + BAR_A_FULL + i, 128);
             mbar_init(bars + BAR_A_EMPTY + i, 1);
         }
-        for (int i = 0; i < 2 * D_STAGES; i++) {
+        for (int i = 0; i < CONSUMER_WGS * D_STAGES; i++) {
             mbar_init(bars + BAR_D_FULL + i, 1);
             mbar_init(bars + BAR_D_EMPTY + i, 128);
         }
@@ -1314,14 +1341,18 @@ __global__ void __launch_bounds__(THREADS, 1) inverse_tc_kernel(const __grid_con
     const uint32_t lane_field = ((warp & 3u) * 32u) << 16;
     static_assert(PRODUCER_WGS == 1 && INV_RING <= TMA_RING, "the inverse kernel has one producer warpgroup and reuses the ring barriers");
     if (warp < CONSUMER_WARP) {
+        if (MOVE_REGS) asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(PRODUCER_REGS));
         inv_producer_role<LAYOUT, CT, CF>(p, bars, smem + SMEM_INV_A_OFF, smem + SMEM_INV_RING_OFF, threadIdx.x);
     } else if (warp < MMA_WARP) {
+        if (MOVE_REGS) asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(CONSUMER_REGS));
         const uint32_t c = (warp - CONSUMER_WARP) >> 2;
         inv_consumer_role<LAYOUT, CF>(p, bars, tmem_base, c, threadIdx.x & 127, lane_field, smem + SMEM_INV_PIX_OFF);
-    } else if (warp < MMA_WARP + MMA_WARPS && lane == 0) {
-        inv_mma_role<LAYOUT, CF>(p, bars, tmem_base, smem_u32(smem + SMEM_INV_A_OFF), b_descriptor(smem_u32(smem + SMEM_B_OFF)), warp - MMA_WARP);
-    } else if (inv_bulk<LAYOUT, CT>() && warp == TMA_WARP && lane == 0) {
-        inv_bulk_role<LAYOUT, CF>(p, bars, smem + SMEM_INV_RING_OFF);
+    } else {
+        if (MOVE_REGS) asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(MMA_REGS));
+        if (warp < MMA_WARP + MMA_WARPS && lane == 0)
+            inv_mma_role<LAYOUT, CF>(p, bars, tmem_base, smem_u32(smem + SMEM_INV_A_OFF), b_descriptor(smem_u32(smem + SMEM_B_OFF)), warp - MMA_WARP);
+        else if (inv_bulk<LAYOUT, CT>() && warp == TMA_WARP && lane == 0)
+            inv_bulk_role<LAYOUT, CF>(p, bars, smem + SMEM_INV_RING_OFF);
     }
     fence_before();
     __syncthreads();

@@ -491,6 +491,35 @@ def test_config5_gigapixel_band_sharded_roundtrip(ctx, oracle):
     assert torch.equal(fused, back)
 
 
+@pytest.mark.timeout(300, method="thread")
+@pytest.mark.parametrize("layout", LAYOUTS)
+def test_tensor_core_kernels_full_bench_batch(ctx, layout):
+    """the bench workload (64 x 1080p: 16 200 tiles, about 110 per CTA) through the tensor-core kernels: the whole batch
+    equals its eight 8-frame shards, forward and inverse.  (A build whose mbarrier phases were ambiguous passed every small
+    test and hung here: many tiles per CTA are part of the contract.)"""
+    f, h, w = 64, 1080, 1920
+    g = torch.Generator(device="cuda").manual_seed(77)
+    x = torch.randint(0, 256, (f, h, w), dtype=torch.uint8, device="cuda", generator=g)
+    lut = rt_lut(layout)
+    job = sd.dense_job(layout, w, h, frames=f, flags=sd.TENSOR)
+    sub = sd.dense_job(layout, w, h, frames=8, flags=sd.TENSOR)
+    coef = ctx.forward(x, lut, job)
+    torch.cuda.synchronize()
+    parts = torch.cat([ctx.forward(x[i:i + 8], lut, sub) for i in range(0, f, 8)])
+    assert torch.equal(coef, parts)
+    back = ctx.inverse(coef, lut, job)
+    torch.cuda.synchronize()
+    parts = torch.cat([ctx.inverse(coef.view(f, -1)[i:i + 8].contiguous(), lut, sub) for i in range(0, f, 8)])
+    assert torch.equal(back.view(-1), parts.view(-1))
+    rgb = torch.randint(0, 256, (4, 2160, 3840, 3), dtype=torch.uint8, device="cuda", generator=g)
+    j3 = sd.dense_job(layout, 3840, 2160, frames=4, components=3, flags=sd.TENSOR)
+    one = sd.dense_job(layout, 3840, 2160, frames=1, components=3, flags=sd.TENSOR)
+    c3 = ctx.forward(rgb, lut, j3)
+    assert torch.equal(c3, torch.cat([ctx.forward(rgb[i], lut, one) for i in range(4)]))
+    b3 = ctx.inverse(c3, lut, j3)
+    assert torch.equal(b3.view(-1), torch.cat([ctx.inverse(c3.view(4, -1)[i].contiguous(), lut, one).view(-1) for i in range(4)]))
+
+
 @pytest.mark.parametrize("layout", LAYOUTS)
 def test_tensor_core_forward_is_bit_exact_to_its_cpu_restatement(ctx, oracle, layout):
     """SDCT_TENSOR (tcgen05.mma + TMEM, sdct_tc.cu): integer-exact matrix form of the true DCT.
