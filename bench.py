@@ -539,10 +539,15 @@ def main():
         rgb = torch.randint(0, 256, (F2, H2, W2, 3), dtype=torch.uint8, device="cuda", generator=gen)
         coef2 = torch.empty(F2 * H2 * W2 * 3, dtype=torch.uint8, device="cuda")
         c2 = {}
-        for lname, layout in L[1:]:
+        for lname, layout in L:
             for mname, fl in (("exact", exact_flags(layout)), ("tensor", sd.TENSOR)):
+                if lname == "A" and mname == "exact":
+                    continue
                 j = sd.dense_job(layout, W2, H2, frames=F2, components=3, flags=fl)
                 c2[f"forward_rgb_{lname}_{mname}"] = rate(tm(lambda: ctx.forward(rgb, lut, j, out=coef2), steps=5), nb2)
+        # the colour front-end: RGB -> YCbCr fused into the same load
+        jy = sd.dense_job(sd.LAYOUT_B, W2, H2, frames=F2, components=3, flags=sd.TENSOR | sd.COLOR_YCBCR)
+        c2["forward_rgb_to_ycbcr_B_tensor"] = rate(tm(lambda: ctx.forward(rgb, lut, jy, out=coef2), steps=5), nb2)
         variants["configs[2] 256x4K interleaved RGB -> planar + forward, per GPU (weak)"] = c2
         # ... and the decode of those coefficient sets back to interleaved pixels (fp32; TENSOR where supported)
         back2 = torch.empty_like(rgb)
@@ -553,6 +558,10 @@ def main():
                     c2[f"inverse_rgb_{lname}_{mname}"] = rate(tm(lambda: ctx.inverse(coef2, lut, j, out=back2), steps=5), nb2)
                 except sd.SdctError as e:
                     c2[f"inverse_rgb_{lname}_{mname}"] = {"unsupported": str(e)}
+        # the step after the path: per-plane statistics of the layout-C sets, one streaming read (64 B / block)
+        jc = sd.dense_job(sd.LAYOUT_C, W2, H2, frames=F2, components=3, flags=sd.TENSOR)
+        ctx.forward(rgb, lut, jc, out=coef2)
+        c2["plane_stats_C (64 B read per block)"] = rate(tm(lambda: ctx.plane_stats(coef2, jc), steps=5), nb2, 64)
         del rgb, coef2, back2
 
         # configs[3]: inverse-only decode of 4K coefficient planes, 64 frames in total sharded by frame over the ranks

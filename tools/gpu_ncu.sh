@@ -5,3 +5,6 @@ mkdir -p gpurun_out
 python tools/prof_run.py "$@" > gpurun_out/${out}_plain.log 2>&1 &&
 ncu --set full --clock-control none --import-source on -k regex:$rx -s 2 -c 2 -f -o gpurun_out/$out python tools/prof_run.py "$@" > gpurun_out/${out}_ncu.log 2>&1
 echo "ncu rc=$?"; cat gpurun_out/${out}_plain.log; tail -3 gpurun_out/${out}_ncu.log
+# the summary csv travels back (gpurun_out/ is capped at 64 MiB); the report itself only with KEEP_REP=1
+python tools/ncu_summary.py gpurun_out/$out.ncu-rep gpurun_out/${out}_ncu.csv 2>/dev/null
+[ -n "$KEEP_REP" ] || rm -f gpurun_out/$out.ncu-rep
