@@ -629,7 +629,7 @@ def main():
         pick = lambda k: {kk: c1[k][kk] for kk in ("us_per_launch", "gbps_per_gpu", "frac_of_hbm_peak")} if "us_per_launch" in c1.get(k, {}) else None  # noqa: E731
         line["roofline_inverse"] = {"kernel": "inverse_kernel<B> (fp32) / inverse_tc_kernel<B> (tensor)", "fp32": pick("inverse_B"), "tensor": pick("inverse_B_tensor"),
                                     "note": "parity unpinned: the reference has no inverse"}
-        line["roofline_roundtrip"] = {"kernel": "roundtrip_kernel<B> (fp32, fused) / roundtrip_tc_kernel<B>", "fp32": pick("roundtrip_fused_B_exact"),
+        line["roofline_roundtrip"] = {"kernel": "roundtrip_kernel<B> (fp32, fused) / roundtrip_tc_kernel<B> (tensor cores, fused: levels stay in shared / tensor memory)", "fp32": pick("roundtrip_fused_B_exact"),
                                       "tensor": pick("roundtrip_fused_B_tensor"), "algorithmic_bytes_per_block": BYTES_PER_BLOCK}
     if rank == 0:
         # the reference's CPU implementation beside it, on this box's host cores (bounded samples; the other ranks wait)

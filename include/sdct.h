@@ -49,8 +49,8 @@ enum {
                                The inverse side needs 16-byte-aligned pixel rows and an even number of blocks per row. */
     SDCT_TENSOR = 4         /* tensor-core (tcgen05) integer form of the true DCT, defined in oracle/sdct_oracle.c mode TENSOR.
                                Forward: every geometry.  Inverse: one or three components, 16-byte-aligned pixel rows and
-                               coefficients, an even number of blocks per row (SDCT_NOT_SUPPORTED otherwise).  Round trip: the two
-                               kernels back to back.  Excludes SDCT_FAST and SDCT_QUIRK_AVX_X3.
+                               coefficients, an even number of blocks per row (SDCT_NOT_SUPPORTED otherwise).  Round trip: one fused kernel
+                               for single planes with rows of >= 128 blocks, the two kernels back to back otherwise (same bytes).  Excludes SDCT_FAST and SDCT_QUIRK_AVX_X3.
                                Distance from SDCT_EXACT (measured on every workload of tests/test_gpu_mismatch_rates.py, recorded in
                                profiles/r02_mismatch_rates.json): SDCT_FAST and SDCT_TENSOR levels differ by at most 1 in at most
                                3e-4 of the bytes (asserted bound 1e-3); the SDCT_TENSOR inverse differs from the fp32 inverse by

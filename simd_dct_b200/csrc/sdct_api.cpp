@@ -114,7 +114,44 @@ void read_env(SdctEnv *e)
     e->tc.no_tma = getenv("SDCT_TC_NO_TMA") != nullptr;
     e->tc.no_rgb_fuse = getenv("SDCT_TC_NO_RGB_FUSE") != nullptr;
     e->tc.no_tma_store = getenv("SDCT_TC_NO_TMA_STORE") != nullptr;
+    e->tc.no_rt_fuse = getenv("SDCT_TC_NO_RT_FUSE") != nullptr;
     e->tc.ablate = (uint32_t)num("SDCT_TC_ABLATE", 0, 0x7fffffff, 0);
+}
+
+// The LUT-dependent operand of the tensor-core inverse (cached per (layout, LUT)).  A miss uploads it SYNCHRONOUSLY (the
+// key becomes visible only after the copy has completed, so a hit on any stream may launch without an event); before an
+// entry's device buffer is overwritten the device is synchronised (kernels in flight on other streams may read it).
+struct InvOperandRef { void *d; int S; float off_cols[64]; };
+int inverse_operand(sdct_context *ctx, int layout, const float *lut, const float scale[64], InvOperandRef *out)
+{
+    std::lock_guard<std::mutex> lock(ctx->inv_mu);
+    sdct_context::InvOperand *op_entry = nullptr;
+    for (auto &e : ctx->inv_cache)
+        if (e.d && e.layout == layout && memcmp(e.lut, lut, sizeof(e.lut)) == 0) op_entry = &e;
+    if (!op_entry) {
+        sdct_context::InvOperand *victim = &ctx->inv_cache[0];
+        for (auto &e : ctx->inv_cache) {
+            if (e.layout < 0) { victim = &e; break; }
+            if (e.used < victim->used) victim = &e;
+        }
+        std::vector<uint16_t> operand(128 * 64);
+        float off_cols[64];
+        const int S = sdct_tc_inverse_operand(layout, scale, operand.data(), off_cols);
+        if (victim->layout >= 0) CU_TRY(cudaDeviceSynchronize());
+        victim->layout = -1;   // invalid while its buffer is rewritten
+        if (!victim->d) CU_TRY(cudaMalloc(&victim->d, operand.size() * sizeof(uint16_t)));
+        CU_TRY(cudaMemcpy(victim->d, operand.data(), operand.size() * sizeof(uint16_t), cudaMemcpyHostToDevice));
+        victim->S = S;
+        memcpy(victim->off_cols, off_cols, sizeof(off_cols));
+        memcpy(victim->lut, lut, sizeof(victim->lut));
+        victim->layout = layout;
+        op_entry = victim;
+    }
+    op_entry->used = ++ctx->inv_clock;
+    out->d = op_entry->d;
+    out->S = op_entry->S;
+    memcpy(out->off_cols, op_entry->off_cols, sizeof(out->off_cols));
+    return SDCT_OK;
 }
 
 int run_device(sdct_context *ctx, int op, const sdct_job *j, const uint8_t *pixels, uint8_t *coefs,
@@ -130,8 +167,8 @@ int run_device(sdct_context *ctx, int op, const sdct_job *j, const uint8_t *pixe
     memset(&p, 0, sizeof(p));
     const bool tensor = (j->flags & SDCT_TENSOR) != 0;
     if (tensor && op == SDCT_K_OP_ROUNDTRIP) {
-        // no fused tensor-core round-trip kernel: the forward and the inverse kernel back to back on the caller's stream,
-        // the coefficients in a stream-ordered scratch allocation with dense 16-byte-aligned strides
+        // single planes with a TMA pixel path: the fused kernel below; everything else: the forward and the inverse kernel back to
+        // back on the caller's stream, the coefficients in a stream-ordered scratch allocation with dense 16-byte-aligned strides
         if (!ctx) return fail(SDCT_INVALID_PARAMETER, "context is null");
         if (!pixels || !pixels_out) return fail(SDCT_INVALID_PARAMETER, "null buffer");
         sdct_job cj = *j;
@@ -143,6 +180,51 @@ int run_device(sdct_context *ctx, int op, const sdct_job *j, const uint8_t *pixe
         DeviceScope dev(ctx->device);
         CU_TRY(dev.err);
         cudaStream_t st = stream ? stream : ctx->stream;
+        if (g.comps == 1 && !(j->flags & (SDCT_FAST | SDCT_QUIRK_AVX_X3 | SDCT_COLOR_YCBCR)) && lut) {
+            // single planes: ONE kernel that keeps the levels in tensor memory between the two products (sdct_tc.cu:
+            // roundtrip_tc_kernel) where the geometry has a TMA pixel path; same bytes as the two kernels
+            KParams q;
+            memset(&q, 0, sizeof(q));
+            float2 inv_tab[64], unused[64];
+            if ((rc = build_tables(j, lut, SDCT_K_OP_INVERSE, inv_tab, unused, unused))) return rc;
+            const bool lb = j->layout == SDCT_LAYOUT_B;
+            bool ok = true;
+            for (int c = 0; c < 64 && ok; c++) {   // forward scales in POSITIONAL column order (D1's columns are E's K index)
+                const float d = lut[c] * 0.95f;
+                const float f = std::ldexp(lb ? 255.0f / d : 1.f / d, -22);
+                ok = std::isfinite(f) && std::fabs(f) * 17179869184.f < 2147483648.f;
+                q.tab[c] = make_float2(f, f);
+            }
+            InvOperandRef ref;
+            float scale[64];
+            for (int i = 0; i < 64; i++) scale[i] = inv_tab[i].x;
+            if (ok && inverse_operand(ctx, j->layout, lut, scale, &ref) == SDCT_OK) {
+                for (int c = 0; c < 64; c++) q.off[c] = make_float2(ref.off_cols[c], ref.off_cols[c]);
+                const float unscale = std::ldexp(1.f, -ref.S);
+                q.tab2[0] = make_float2(unscale, unscale);
+                q.tc_matrix = ctx->d_tc_matrix[j->layout == SDCT_LAYOUT_A ? 2 : 1];
+                q.tc_matrix2 = ref.d;
+                q.pixels = pixels; q.pixels_out = pixels_out;
+                q.pitch = j->pitch; q.eye_stride = j->eye_stride; q.pixel_frame_stride = j->pixel_frame_stride;
+                q.bpr = g.bpr; q.eyes = g.eyes; q.comps = 1; q.frames = (uint32_t)j->frames;
+                q.sm_count = (uint32_t)ctx->sm_count;
+                q.row0 = g.band_begin * g.eyes;
+                q.rows = (g.band_end - g.band_begin) * g.eyes;
+                const uint64_t pstr = j->pitch | j->eye_stride | j->pixel_frame_stride;
+                q.pixel_vec = (aligned(pixels, 16) && aligned(pixels_out, 16) && (pstr & 15) == 0 && (g.bpr & 1) == 0 && !(j->pitch >> 32)) ? 2 : 0;
+                cudaError_t e;
+                {
+                    std::lock_guard<std::mutex> lock(ctx->tc_maps_mu);
+                    e = sdct_k_launch_tc_roundtrip(j->layout, &q, &ctx->env.tc, &ctx->tc_maps, st);
+                }
+                if (e == cudaSuccess) {
+                    ctx->launches.fetch_add(1, std::memory_order_relaxed);
+                    return SDCT_OK;
+                }
+                if (e != cudaErrorNotSupported) CU_TRY(e);
+                cudaGetLastError();
+            }
+        }
         void *scratch = nullptr;
         CU_TRY(cudaMallocFromPoolAsync(&scratch, bytes, ctx->scratch_pool, st));
         rc = run_device(ctx, SDCT_K_OP_FORWARD, &cj, pixels, (uint8_t *)scratch, nullptr, lut, st);
@@ -195,37 +277,13 @@ int run_device(sdct_context *ctx, int op, const sdct_job *j, const uint8_t *pixe
                                             "an even number of blocks per row (layout C: a multiple of 16 blocks)");
         cudaStream_t st = stream ? stream : ctx->stream;
         {
-            // The LUT-dependent operand.  A miss uploads it SYNCHRONOUSLY (the key becomes visible only after the
-            // copy has completed, so a hit on any stream may launch without an event); before an entry's device
-            // buffer is overwritten the device is synchronised (kernels in flight on other streams may read it).
-            std::lock_guard<std::mutex> lock(ctx->inv_mu);
-            sdct_context::InvOperand *op_entry = nullptr;
-            for (auto &e : ctx->inv_cache)
-                if (e.d && e.layout == j->layout && memcmp(e.lut, lut, sizeof(e.lut)) == 0) op_entry = &e;
-            if (!op_entry) {
-                sdct_context::InvOperand *victim = &ctx->inv_cache[0];
-                for (auto &e : ctx->inv_cache) {
-                    if (e.layout < 0) { victim = &e; break; }
-                    if (e.used < victim->used) victim = &e;
-                }
-                std::vector<uint16_t> operand(128 * 64);
-                float scale[64], off_cols[64];
-                for (int i = 0; i < 64; i++) scale[i] = p.tab[i].x;
-                const int S = sdct_tc_inverse_operand(j->layout, scale, operand.data(), off_cols);
-                if (victim->layout >= 0) CU_TRY(cudaDeviceSynchronize());
-                victim->layout = -1;   // invalid while its buffer is rewritten
-                if (!victim->d) CU_TRY(cudaMalloc(&victim->d, operand.size() * sizeof(uint16_t)));
-                CU_TRY(cudaMemcpy(victim->d, operand.data(), operand.size() * sizeof(uint16_t), cudaMemcpyHostToDevice));
-                victim->S = S;
-                memcpy(victim->off_cols, off_cols, sizeof(off_cols));
-                memcpy(victim->lut, lut, sizeof(victim->lut));
-                victim->layout = j->layout;
-                op_entry = victim;
-            }
-            op_entry->used = ++ctx->inv_clock;
-            p.tc_matrix = op_entry->d;
-            for (int c = 0; c < 64; c++) p.tab[c] = make_float2(op_entry->off_cols[c], op_entry->off_cols[c]);
-            const float unscale = std::ldexp(1.f, -op_entry->S);
+            InvOperandRef ref;
+            float scale[64];
+            for (int i = 0; i < 64; i++) scale[i] = p.tab[i].x;
+            if ((rc = inverse_operand(ctx, j->layout, lut, scale, &ref))) return rc;
+            p.tc_matrix = ref.d;
+            for (int c = 0; c < 64; c++) p.tab[c] = make_float2(ref.off_cols[c], ref.off_cols[c]);
+            const float unscale = std::ldexp(1.f, -ref.S);
             p.tab2[0] = make_float2(unscale, unscale);
         }
         {
@@ -306,9 +364,9 @@ int sdct_create(int device, sdct_context **out)
     }
     {   // tensor-core B operands (16 KiB each)
         std::vector<uint16_t> op(128 * 64);
-        const int layouts[2] = {SDCT_K_LAYOUT_A, SDCT_K_LAYOUT_B};
-        for (int i = 0; i < 2; i++) {
-            sdct_tc_operand(layouts[i], op.data());
+        const int layouts[3] = {SDCT_K_LAYOUT_A, SDCT_K_LAYOUT_B, SDCT_K_LAYOUT_A};
+        for (int i = 0; i < 3; i++) {   // [2]: layout A in positional column order (the fused round trip)
+            sdct_tc_operand(layouts[i], op.data(), i == 2);
             CU_TRY(cudaMalloc(&c->d_tc_matrix[i], op.size() * sizeof(uint16_t)));
             CU_TRY(cudaMemcpy(c->d_tc_matrix[i], op.data(), op.size() * sizeof(uint16_t), cudaMemcpyHostToDevice));
         }
@@ -325,7 +383,7 @@ void sdct_destroy(sdct_context *c)
     c->pipes.clear();
     if (c->stream) { cudaStreamSynchronize(c->stream); cudaStreamDestroy(c->stream); }
     if (c->scratch_pool) cudaMemPoolDestroy(c->scratch_pool);
-    cudaFree(c->d_tc_matrix[0]); cudaFree(c->d_tc_matrix[1]);
+    cudaFree(c->d_tc_matrix[0]); cudaFree(c->d_tc_matrix[1]); cudaFree(c->d_tc_matrix[2]);
     for (auto &e : c->inv_cache) cudaFree(e.d);
     delete c;
 }

@@ -75,7 +75,7 @@ struct sdct_context {
     std::atomic<uint64_t> launches{0};
     std::mutex pipes_mu;   // guards the pool only; a call runs on its own pipeline without the lock
     std::vector<std::unique_ptr<Pipeline>> pipes;
-    void *d_tc_matrix[2] = {nullptr, nullptr};  // tensor-core B operand: [0] layout-A column order, [1] natural order
+    void *d_tc_matrix[3] = {nullptr, nullptr, nullptr};  // tensor-core B operand: [0] layout-A column order, [1] natural order, [2] layout A positional
     // tensor-core inverse operands depend on the LUT: a small cache keyed by (layout, LUT).  An entry is uploaded
     // synchronously before its key becomes visible and is only overwritten after a device synchronise.
     struct InvOperand { void *d = nullptr; int layout = -1; float lut[64]; float off_cols[64]; int S = 0; uint64_t used = 0; };
@@ -100,7 +100,7 @@ void sdct_destroy_pipeline(Pipeline *p);
 // tensor-core form: K[c][p] = round(2^22 * C[u][y] * C[v][x]), c = u*8+v, p = y*8+x (sdct_tc_matrix.cpp)
 void sdct_tc_integer_matrix(int32_t K[64 * 64]);
 // the 16 KiB B operand for `layout`: fp16 digits of K in the UMMA canonical K-major layout
-void sdct_tc_operand(int layout, uint16_t out[128 * 64]);
+void sdct_tc_operand(int layout, uint16_t out[128 * 64], bool positional = false);   // positional: column c = coefficient position c
 // the LUT-dependent 16 KiB B operand of the tensor-core inverse; returns the scaling exponent S, fills the
 // per-column offsets -127 * sum_i E[p][i]
 int sdct_tc_inverse_operand(int layout, const float tab[64], uint16_t out[128 * 64], float off_cols[64]);

@@ -46,6 +46,7 @@ struct KParams {
     KFastDiv div_chunks, div_bpr;  // tensor-core kernels
     uint32_t tc_ablate;       // profiling only ($SDCT_TC_ABLATE): bit0 no MMA, 1 no A write, 2 no epilogue, 3 no stores, 4 no loads
     const void *tc_matrix;    // tensor-core kernels: the 16 KiB B operand (fp16 digits of 2^22 C(x)C, UMMA canonical layout)
+    const void *tc_matrix2;   // fused tensor-core round trip: the dequantising inverse operand E (tc_matrix = the forward operand)
     // tensor-core kernels, TMA pixel path: CUtensorMap over the pixels as u32[frame][eye][row][W / 4]
     // (filled in by sdct_k_launch_tc; must stay 64-byte aligned inside the kernel parameter block)
     alignas(64) unsigned char tc_tensor_map[128];
@@ -61,6 +62,7 @@ struct SdctTcOptions {
     bool no_tma = false;         // $SDCT_TC_NO_TMA: thread-copy paths instead of tensor maps
     bool no_rgb_fuse = false;    // $SDCT_TC_NO_RGB_FUSE
     bool no_tma_store = false;   // $SDCT_TC_NO_TMA_STORE
+    bool no_rt_fuse = false;     // $SDCT_TC_NO_RT_FUSE: SDCT_TENSOR round trip always as two kernels
     uint32_t ablate = 0;         // $SDCT_TC_ABLATE (profiling builds only)
 };
 // encoded CUtensorMaps, keyed by (base pointer, dimensions, strides): cuTensorMapEncodeTiled runs once per
@@ -75,6 +77,10 @@ struct SdctTcMapCache {
 // tensor-core form (sdct_tc.cu); p->tab holds the folded scales in D-column order.  `maps` may be null (no caching);
 // the caller serialises access to it.
 extern "C" cudaError_t sdct_k_launch_tc(int op, int layout, const KParams *p, const SdctTcOptions *opt, SdctTcMapCache *maps, cudaStream_t s);
+// fused tensor-core round trip (single planes with the TMA pixel path): p->tab = forward scales in POSITIONAL column order,
+// p->off = the inverse's pixel offsets, p->tab2[0] = its 2^-S, p->tc_matrix / tc_matrix2 = forward (positional order) /
+// inverse operand.  cudaErrorNotSupported when the geometry has no TMA path (the caller then runs the two kernels).
+extern "C" cudaError_t sdct_k_launch_tc_roundtrip(int layout, const KParams *p, const SdctTcOptions *opt, SdctTcMapCache *maps, cudaStream_t s);
 // D column j of the tensor-core kernels -> coefficient position in the layout's own index order
 static inline int sdct_tc_column_position(int layout, int j)
 {

@@ -111,6 +111,17 @@ constexpr int BAR_A_FULL = 0, BAR_A_EMPTY = A_STAGES, BAR_D_FULL = 2 * A_STAGES,
 constexpr int D_PERIOD = 6;
 static_assert(D_PERIOD % MMA_WARPS == 0 && D_PERIOD % CONSUMER_WGS == 0 && D_PERIOD % D_STAGES == 0 && D_PERIOD <= CONSUMER_WGS * D_STAGES, "D barrier period");
 __host__ __device__ constexpr uint32_t d_bar(uint32_t k) { return k % D_PERIOD; }
+// fused round trip (roundtrip_tc_kernel): its own barrier and TMEM plan.  TMEM holds the accumulators only, both
+// double-buffered: D2 (pixels) 2 x 128 columns, D1 (coefficients) 2 x 128; the A operands (pixels / levels as fp16) live in
+// shared memory as K-major core matrices (the inverse kernel's layout-A form: LBO 144, conflict-free 16-byte row stores).
+// (A first build kept A1 / A2 in TMEM and D1 single-buffered: the chain MMA1 -> middle warpgroup's loads -> MMA1 then set
+// the pace, 108 us per 64 x 1080p - no faster than the two kernels.)
+constexpr int RT_BAR_A1_FULL = 0, RT_BAR_A1_EMPTY = 2, RT_BAR_D1_FULL = 4, RT_BAR_D1_EMPTY = 6, RT_BAR_A2_FULL = 8, RT_BAR_A2_EMPTY = 10,
+              RT_BAR_D2_FULL = 12, RT_BAR_D2_EMPTY = 14;   // two of each (the TMA ring keeps BAR_RING_FULL / BAR_RING_EMPTY)
+static_assert(RT_BAR_D2_EMPTY + 2 <= 2 * A_STAGES + 2 * CONSUMER_WGS * D_STAGES, "round-trip barriers fit below the ring barriers");
+constexpr int RT_TMEM_D2 = 0, RT_TMEM_D1 = 256;
+constexpr uint32_t RT_A_LBO = 144, RT_A_SBO = 8 * RT_A_LBO;
+constexpr int RT_A_STAGE_BYTES = 16 * 8 * 144;   // 128 block rows x 64 fp16, padded
 constexpr int BAR_PRODUCER = 8, BAR_FLUSH = 9;    // named barriers (ids 1 .. CONSUMER_WGS: the consumer warpgroups' own)
 //   ring_full[j % 6]        TMA (complete_tx) -> producer warpgroup; ring_empty[j % 6]: its four warps -> TMA thread
 constexpr int TMA_RING = 6;                       // slots of two 8 KiB boxes: 8 rows x 1024 bytes of this / of the next block row
@@ -123,6 +134,9 @@ constexpr int SMEM_META_OFF = SMEM_BAR_OFF + NUM_BARS * 8 + 16;   // TMA ring: b
 constexpr int SMEM_USED = SMEM_META_OFF + TMA_RING * 4;
 // more than half of the SM's shared memory: exactly one CTA per SM (it allocates all of TMEM)
 constexpr int SMEM_BYTES = SMEM_USED > 120 * 1024 ? SMEM_USED : 120 * 1024;
+// fused round trip: A1[2] and A2[2] behind everything else
+constexpr int SMEM_RT_A_OFF = (SMEM_USED + 127) & ~127, SMEM_RT_BYTES = SMEM_RT_A_OFF + 4 * RT_A_STAGE_BYTES;
+static_assert(SMEM_RT_BYTES <= 227 * 1024, "shared memory of the fused round trip");
 
 // profiling builds only (-DSDCT_TC_TRACE=1; $SDCT_TC_ABLATE then selects ablations, bit 5 = clock64 stamps of
 // CTA 0's roles, 8 per tile and role).  In the product build the stamps and ablation tests compile to nothing.
@@ -1153,14 +1167,17 @@ SDCT_DEV void tc_flush_rgb(const uint8_t *img3, const KParams &p, const Tile &t,
     }
 }
 
-template <int LAYOUT, int CF>
+// RT: the fused round-trip kernel's pixel epilogue (roundtrip_tc_kernel below): D2 stage = warpgroup, its own barriers,
+// pixel offsets in p.off, output into p.pixels_out
+template <int LAYOUT, int CF, bool RT = false>
 SDCT_DEV void inv_consumer_role(const KParams &p, uint64_t *bars, uint32_t tmem_base, uint32_t c, uint32_t L, uint32_t lane_field, uint8_t *pix_images)
 {
+    static_assert(!RT || CF == 1, "the fused round trip handles single planes");
     const uint32_t lane = L & 31, g = lane >> 2, q = lane & 3;
     // this thread's 16 pixel offsets -127 * sum E (columns 8k + 2q + e), and the common 2^(24 - S)
     F2 off[8];
 #pragma unroll
-    for (int k = 0; k < 8; k++) off[k] = make_float2(p.tab[8 * k + 2 * q].x, p.tab[8 * k + 2 * q + 1].x);
+    for (int k = 0; k < 8; k++) off[k] = RT ? make_float2(p.off[8 * k + 2 * q].x, p.off[8 * k + 2 * q + 1].x) : make_float2(p.tab[8 * k + 2 * q].x, p.tab[8 * k + 2 * q + 1].x);
     const F2 unscale = splat(p.tab2[0].x);
     // TMEM lane = block of the tile (the A rows are in natural order here): a 16x256b load hands this thread lanes
     // g and g + 8 of a 16-lane half, i.e. blocks P = sp0 + 16 half and Q = P + 8
@@ -1184,7 +1201,7 @@ SDCT_DEV void inv_consumer_role(const KParams &p, uint64_t *bars, uint32_t tmem_
         uint32_t r = fastdiv(nl, p.div_bpr), bx = nl - r * p.bpr;
         if (wide) {
             uint32_t row = r + p.row0;
-            uint8_t *b = const_cast<uint8_t *>(t.pix) + q_rows + ((uint64_t)((stereo ? row >> 1 : row) * 8) * pitch32 + bx * 8);
+            uint8_t *b = (RT ? p.pixels_out + (t.pix - p.pixels) : const_cast<uint8_t *>(t.pix)) + q_rows + ((uint64_t)((stereo ? row >> 1 : row) * 8) * pitch32 + bx * 8);
             if (stereo && (row & 1)) b += p.eye_stride;
 #pragma unroll
             for (int i = 0; i < 4; i++) {
@@ -1198,7 +1215,7 @@ SDCT_DEV void inv_consumer_role(const KParams &p, uint64_t *bars, uint32_t tmem_
 #pragma unroll
         for (int i = 0; i < 4; i++) {
             const uint32_t row = r + p.row0, band = stereo ? row >> 1 : row;
-            uint8_t *b = const_cast<uint8_t *>(t.pix) + ((uint64_t)(band * 8 + 2 * q) * pitch32 + bx * 8);
+            uint8_t *b = (RT ? p.pixels_out + (t.pix - p.pixels) : const_cast<uint8_t *>(t.pix)) + ((uint64_t)(band * 8 + 2 * q) * pitch32 + bx * 8);
             if (stereo && (row & 1)) b += p.eye_stride;
             d.px[i >> 1][i & 1] = b;
             bx += 8;
@@ -1215,8 +1232,8 @@ SDCT_DEV void inv_consumer_role(const KParams &p, uint64_t *bars, uint32_t tmem_
     if (CF == 1 && wk.tile < p.tiles) locate_tile(wk, cur);
     for (uint32_t k = c;; k += CONSUMER_WGS) {
         if (wk.tile >= p.tiles) break;
-        const uint32_t sd = k % D_STAGES, ud = k / D_PERIOD;
-        uint64_t *d_full = bars + BAR_D_FULL + d_bar(k), *d_empty = bars + BAR_D_EMPTY + d_bar(k);
+        const uint32_t sd = RT ? c : k % D_STAGES, ud = RT ? k / 2 : k / D_PERIOD;
+        uint64_t *d_full = bars + (RT ? RT_BAR_D2_FULL + c : BAR_D_FULL + d_bar(k)), *d_empty = bars + (RT ? RT_BAR_D2_EMPTY + c : BAR_D_EMPTY + d_bar(k));
         Tile ptile;             // CF == 3: the pixel tile of this tile
         uint8_t *img = nullptr; //          and this component's image
         bool last_own = false;  //          this warpgroup's last component of the pixel tile
@@ -1243,7 +1260,7 @@ SDCT_DEV void inv_consumer_role(const KParams &p, uint64_t *bars, uint32_t tmem_
         // load waits per tile instead of four, the second hidden behind chunk 1's arithmetic.  The next tile's
         // addresses are computed while the first loads are in flight.
         float hiA[16], loA[16], hiB[16], loB[16];
-        const uint32_t td = tmem_base + TMEM_D_OFF + sd * D_COLS + lane_field;
+        const uint32_t td = tmem_base + (RT ? RT_TMEM_D2 : TMEM_D_OFF) + sd * D_COLS + lane_field;
         tmem_ld_16x256b_x4(td, hiA);
         tmem_ld_16x256b_x4(td + 64, loA);
         tmem_ld_16x256b_x4(td + 32, hiB);
@@ -1353,6 +1370,225 @@ __global__ void __launch_bounds__(THREADS, 1) inverse_tc_kernel(const __grid_con
             inv_mma_role<LAYOUT, CF>(p, bars, tmem_base, smem_u32(smem + SMEM_INV_A_OFF), b_descriptor(smem_u32(smem + SMEM_B_OFF)), warp - MMA_WARP);
         else if (inv_bulk<LAYOUT, CT>() && warp == TMA_WARP && lane == 0)
             inv_bulk_role<LAYOUT, CF>(p, bars, smem + SMEM_INV_RING_OFF);
+    }
+    fence_before();
+    __syncthreads();
+    if (warp == 0) tmem_dealloc(tmem_base);
+}
+
+// =====================================================================================================
+// Fused round trip on the tensor cores (single planes, TMA pixel path): pixels -> D1 = X K^T (coefficients, exact
+// integers) -> quantise in registers -> the levels, again exact fp16 subnormals, into a second A operand in TMEM ->
+// D2 = L E^T (the dequantising inverse operand) -> pixels.  The coefficients never leave the SM: 128 B of HBM traffic per
+// block.  Bytes = inverse_tensor(forward_tensor(x)) of the CPU restatement (the same two products and roundings as the
+// forward and the inverse kernel).  Five warpgroups:
+//   0, 1   front     warpgroup k % 2: TMA ring slot -> fp16 -> A1[k % 2] in shared memory (row = block, natural order), and
+//                    D1[k % 2] -> tcgen05.ld.32x32b (thread = block: its 64 coefficients, both digits) -> quantise with the
+//                    per-column scales from the constant bank -> saturating pack -> A2[k % 2] in shared memory
+//   2, 3   consumers the inverse kernel's pixel epilogue on D2[k % 2] (inv_consumer_role<..., RT>)
+//   4      two MMA threads (SS-form products; one issues every MMA1, the other every MMA2) and the TMA thread
+constexpr int RT_THREADS = 128 * 5;
+constexpr int RT_LAUNCH_REGS = 65536 / RT_THREADS / 8 * 8, RT_CONSUMER_REGS = 120, RT_MMA_REGS = 40;
+static_assert(RT_LAUNCH_REGS == 96 && (RT_LAUNCH_REGS - RT_MMA_REGS) >= 2 * (RT_CONSUMER_REGS - RT_LAUNCH_REGS), "setmaxnreg balance");
+
+SDCT_DEV void tmem_ld_32x32b_x16(uint32_t taddr, float (&r)[16])
+{
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+        : "=f"(r[0]), "=f"(r[1]), "=f"(r[2]), "=f"(r[3]), "=f"(r[4]), "=f"(r[5]), "=f"(r[6]), "=f"(r[7]), "=f"(r[8]), "=f"(r[9]), "=f"(r[10]),
+          "=f"(r[11]), "=f"(r[12]), "=f"(r[13]), "=f"(r[14]), "=f"(r[15])
+        : "r"(taddr)
+        : "memory");
+}
+
+// 64 fp16 of block row m -> the K-major core-matrix image of an A stage: chunk c (8 fp16 = 4 words) of row m at
+// (m / 8) SBO + (m % 8) 16 + c LBO; a quarter-warp's eight rows are 128 contiguous bytes per chunk
+SDCT_DEV uint8_t *rt_a_row(uint8_t *stage, uint32_t m) { return stage + (m >> 3) * RT_A_SBO + (m & 7u) * 16u; }
+
+// 16 coefficients (columns C0 .. C0 + 15 of D1: both digits) of this thread's block -> 8 words of fp16-subnormal level
+// pairs = chunks C0 / 8 and C0 / 8 + 1 of its A2 row
+template <int C0>
+SDCT_DEV void rt_quantise16(const KParams &p, const float (&hi)[16], const float (&lo)[16], uint8_t *row)
+{
+    uint32_t w[8];
+#pragma unroll
+    for (int i = 0; i < 8; i++) {
+        const F2 t = fma2(make_float2(hi[2 * i], hi[2 * i + 1]), splat(1024.f), make_float2(lo[2 * i], lo[2 * i + 1]));
+        const F2 bits = quant_rne_bias(t, make_float2(p.tab[C0 + 2 * i].x, p.tab[C0 + 2 * i + 1].x));
+        // saturate to bytes, then zero-extend each to 16 bits: low half = column C0 + 2i, high half = the next one
+        w[i] = __byte_perm(pack_sat(__float_as_uint(bits.y), __float_as_uint(bits.x), 0u), 0u, 0x4140);
+    }
+    *reinterpret_cast<uint4 *>(row + (C0 / 8) * RT_A_LBO) = make_uint4(w[0], w[1], w[2], w[3]);
+    *reinterpret_cast<uint4 *>(row + (C0 / 8 + 1) * RT_A_LBO) = make_uint4(w[4], w[5], w[6], w[7]);
+}
+
+// front warpgroup wg (0, 1) owns the tiles of its parity end to end on the input side: it turns the TMA ring slot into
+// A1[wg] (the forward producer's work) and, two of its tiles later, D1[wg] into A2[wg] (quantisation).  Two warpgroups
+// because the quantising half is a latency chain (wait, TMEM load, arithmetic, store) of about 2 000 clocks per tile for
+// one warp per scheduler - a single middle warpgroup set the kernel's pace (108-133 us per 64 x 1080p).
+SDCT_DEV void rt_front_role(const KParams &p, uint64_t *bars, uint32_t tmem_base, uint8_t *a1, uint8_t *a2, const uint8_t *ring, const uint32_t *meta,
+                            uint32_t wg, uint32_t L, uint32_t lane_field)
+{
+    auto live = [&](uint32_t k) { return blockIdx.x + k * gridDim.x < p.tiles; };
+    uint8_t *a1_row = rt_a_row(a1 + wg * RT_A_STAGE_BYTES, L), *a2_row = rt_a_row(a2 + wg * RT_A_STAGE_BYTES, L);
+    const bool tr = (ablate_bits(p) & 32) && blockIdx.x == 0 && L == 0 && wg == 0;
+    auto produce = [&](uint32_t k) {
+        const uint32_t rs = k % TMA_RING, ru = k / TMA_RING, ua = k >> 1;
+        stamp(tr, 0, k, 0);
+        mbar_wait(bars + BAR_RING_FULL + rs, ru & 1);
+        stamp(tr, 0, k, 1);
+        const uint32_t split = meta[rs];
+        const uint8_t *src = ring + rs * TMA_SLOT_BYTES + (L < split ? L * 8 : TMA_BOX_BYTES + (L - split) * 8);
+        uint32_t w[16];
+#pragma unroll
+        for (int r = 0; r < 8; r++) {
+            const uint2 v = *reinterpret_cast<const uint2 *>(src + r * (TILE * 8));
+            w[2 * r] = v.x; w[2 * r + 1] = v.y;
+        }
+        uint32_t h[32];
+        bytes_to_half(w, h);
+        mbar_wait(bars + RT_BAR_A1_EMPTY + wg, (ua & 1) ^ 1);   // MMA1 of tile k - 2 has read A1[wg]
+        stamp(tr, 0, k, 2);
+#pragma unroll
+        for (int c = 0; c < 8; c++) *reinterpret_cast<uint4 *>(a1_row + c * RT_A_LBO) = make_uint4(h[4 * c], h[4 * c + 1], h[4 * c + 2], h[4 * c + 3]);
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic stores -> the tensor core's async-proxy reads
+        mbar_arrive(bars + RT_BAR_A1_FULL + wg);
+        stamp(tr, 0, k, 3);
+        __syncwarp();
+        if ((L & 31) == 0) mbar_arrive(bars + BAR_RING_EMPTY + rs);
+    };
+    auto quantise = [&](uint32_t k) {
+        const uint32_t ua = k >> 1;
+        stamp(tr, 0, k, 4);
+        mbar_wait(bars + RT_BAR_A2_EMPTY + wg, (ua & 1) ^ 1);   // MMA2 of tile k - 2 has read A2[wg]
+        mbar_wait(bars + RT_BAR_D1_FULL + wg, ua & 1);
+        fence_after();
+        stamp(tr, 0, k, 5);
+        const uint32_t td = tmem_base + RT_TMEM_D1 + wg * D_COLS + lane_field;
+        float hiA[16], loA[16], hiB[16], loB[16];
+        tmem_ld_32x32b_x16(td, hiA);
+        tmem_ld_32x32b_x16(td + 64, loA);
+        tmem_ld_32x32b_x16(td + 16, hiB);
+        tmem_ld_32x32b_x16(td + 80, loB);
+        tmem_wait_ld4(hiA, loA, hiB, loB);
+        rt_quantise16<0>(p, hiA, loA, a2_row);
+        tmem_ld_32x32b_x16(td + 32, hiA);
+        tmem_ld_32x32b_x16(td + 96, loA);
+        rt_quantise16<16>(p, hiB, loB, a2_row);
+        tmem_ld_32x32b_x16(td + 48, hiB);
+        tmem_ld_32x32b_x16(td + 112, loB);
+        tmem_wait_ld4(hiA, loA, hiB, loB);
+        fence_before();
+        mbar_arrive(bars + RT_BAR_D1_EMPTY + wg);   // every load of this thread has landed: MMA1 of tile k + 2 may overwrite D1[wg]
+        stamp(tr, 0, k, 6);
+        rt_quantise16<32>(p, hiA, loA, a2_row);
+        rt_quantise16<48>(p, hiB, loB, a2_row);
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        mbar_arrive(bars + RT_BAR_A2_FULL + wg);
+        stamp(tr, 0, k, 7);
+    };
+    if (!live(wg)) return;
+    produce(wg);
+    for (uint32_t k = wg; live(k); k += 2) {
+        if (live(k + 2)) produce(k + 2);
+        quantise(k);
+    }
+}
+
+SDCT_DEV void rt_mma_role(const KParams &p, uint64_t *bars, uint32_t tmem_base, uint32_t a1_addr, uint32_t a2_addr, uint64_t kdesc, uint64_t edesc, uint32_t which)
+{
+    const uint64_t kd[4] = {kdesc, kdesc + (uint64_t)((2 * B_LBO) >> 4), kdesc + (uint64_t)((4 * B_LBO) >> 4), kdesc + (uint64_t)((6 * B_LBO) >> 4)};
+    const uint64_t ed[4] = {edesc, edesc + (uint64_t)((2 * B_LBO) >> 4), edesc + (uint64_t)((4 * B_LBO) >> 4), edesc + (uint64_t)((6 * B_LBO) >> 4)};
+    auto live = [&](uint32_t k) { return blockIdx.x + k * gridDim.x < p.tiles; };
+    const bool trm = (ablate_bits(p) & 32) && blockIdx.x == 0;
+    auto mma1 = [&](uint32_t k) {
+        const uint32_t sa = k & 1;
+        stamp(trm, 1, k, 0);
+        mbar_wait(bars + RT_BAR_A1_FULL + sa, (k >> 1) & 1);
+        stamp(trm, 1, k, 1);
+        if (k >= 2) mbar_wait(bars + RT_BAR_D1_EMPTY + sa, ((k - 2) >> 1) & 1);   // the middle warpgroup has read tile k - 2's coefficients
+        fence_after();
+        stamp(trm, 1, k, 2);
+        const uint64_t ad = smem_descriptor(a1_addr + sa * RT_A_STAGE_BYTES, RT_A_LBO, RT_A_SBO);
+#pragma unroll
+        for (int ks = 0; ks < 4; ks++) mma_f16_ss(tmem_base + RT_TMEM_D1 + sa * D_COLS, ad + (uint64_t)((2 * ks * RT_A_LBO) >> 4), kd[ks], IDESC, ks);
+        mma_commit(bars + RT_BAR_A1_EMPTY + sa);
+        mma_commit(bars + RT_BAR_D1_FULL + sa);
+        stamp(trm, 1, k, 3);
+#if SDCT_TC_TRACE
+        if (trm && (p.tc_ablate & 64)) { mbar_wait(bars + RT_BAR_D1_FULL + sa, (k >> 1) & 1); stamp(trm, 1, k, 0); }   // experiment: the product's own latency
+#endif
+    };
+    auto mma2 = [&](uint32_t k) {
+        const uint32_t sa = k & 1;
+        stamp(trm, 1, k, 4);
+        mbar_wait(bars + RT_BAR_A2_FULL + sa, (k >> 1) & 1);
+        stamp(trm, 1, k, 5);
+        if (k >= 2) mbar_wait(bars + RT_BAR_D2_EMPTY + sa, ((k - 2) >> 1) & 1);   // consumer warpgroup k % 2 has read tile k - 2's pixels
+        fence_after();
+        stamp(trm, 1, k, 6);
+        const uint64_t ad = smem_descriptor(a2_addr + sa * RT_A_STAGE_BYTES, RT_A_LBO, RT_A_SBO);
+#pragma unroll
+        for (int ks = 0; ks < 4; ks++) mma_f16_ss(tmem_base + RT_TMEM_D2 + sa * D_COLS, ad + (uint64_t)((2 * ks * RT_A_LBO) >> 4), ed[ks], IDESC, ks);
+        mma_commit(bars + RT_BAR_A2_EMPTY + sa);
+        mma_commit(bars + RT_BAR_D2_FULL + sa);
+        stamp(trm, 1, k, 7);
+    };
+    // two issuing threads, one per product, so that a wait of one product never holds up the other (with ONE thread in
+    // program order the whole kernel became a single latency chain); every barrier still has one in-order waiter
+    if (which == 0) { for (uint32_t k = 0; live(k); k++) mma1(k); }
+    else { for (uint32_t k = 0; live(k); k++) mma2(k); }
+}
+
+template <int LAYOUT>
+__global__ void __launch_bounds__(RT_THREADS, 1) roundtrip_tc_kernel(const __grid_constant__ KParams p)
+{
+    extern __shared__ __align__(1024) uint8_t smem[];
+    const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    uint64_t *bars = reinterpret_cast<uint64_t *>(smem + SMEM_BAR_OFF);
+    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(smem + SMEM_BAR_OFF + NUM_BARS * 8);
+    {   // both B operands: K (forward) at SMEM_B_OFF, E (dequantising inverse) behind it
+        const uint4 *k_src = reinterpret_cast<const uint4 *>(p.tc_matrix), *e_src = reinterpret_cast<const uint4 *>(p.tc_matrix2);
+        uint4 *dst = reinterpret_cast<uint4 *>(smem + SMEM_B_OFF);
+        for (int i = threadIdx.x; i < B_BYTES / 16; i += RT_THREADS) {
+            dst[i] = __ldg(k_src + i);
+            dst[i + B_BYTES / 16] = __ldg(e_src + i);
+        }
+    }
+    if (threadIdx.x == 0) {
+        for (int i = 0; i < 2; i++) {
+            mbar_init(bars + RT_BAR_A1_FULL + i, 128); mbar_init(bars + RT_BAR_A1_EMPTY + i, 1);
+            mbar_init(bars + RT_BAR_A2_FULL + i, 128); mbar_init(bars + RT_BAR_A2_EMPTY + i, 1);
+            mbar_init(bars + RT_BAR_D2_FULL + i, 1); mbar_init(bars + RT_BAR_D2_EMPTY + i, 128);
+            mbar_init(bars + RT_BAR_D1_FULL + i, 1); mbar_init(bars + RT_BAR_D1_EMPTY + i, 128);
+        }
+        for (int i = 0; i < TMA_RING; i++) {
+            mbar_init(bars + BAR_RING_FULL + i, 1);
+            mbar_init(bars + BAR_RING_EMPTY + i, 4);
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 0) tmem_alloc(tmem_slot);
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    fence_before();
+    __syncthreads();
+    fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+    const uint32_t lane_field = ((warp & 3u) * 32u) << 16;
+    static_assert(SMEM_IMG_OFF == SMEM_B_OFF + B_BYTES && SMEM_RING_OFF >= SMEM_IMG_OFF + B_BYTES, "the second operand lives where the forward kernel keeps its staging images");
+    if (warp < 8) {   // (the two front warpgroups keep the launch allocation of 96 registers)
+        rt_front_role(p, bars, tmem_base, smem + SMEM_RT_A_OFF, smem + SMEM_RT_A_OFF + 2 * RT_A_STAGE_BYTES, smem + SMEM_RING_OFF,
+                      reinterpret_cast<const uint32_t *>(smem + SMEM_META_OFF), warp >> 2, threadIdx.x & 127, lane_field);
+    } else if (warp < 16) {
+        asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(RT_CONSUMER_REGS));
+        inv_consumer_role<LAYOUT, 1, true>(p, bars, tmem_base, (warp - 8) >> 2, threadIdx.x & 127, lane_field, nullptr);
+    } else {
+        asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(RT_MMA_REGS));
+        if (warp < 18 && lane == 0)
+            rt_mma_role(p, bars, tmem_base, smem_u32(smem + SMEM_RT_A_OFF), smem_u32(smem + SMEM_RT_A_OFF + 2 * RT_A_STAGE_BYTES),
+                        b_descriptor(smem_u32(smem + SMEM_B_OFF)), b_descriptor(smem_u32(smem + SMEM_B_OFF + B_BYTES)), warp - 16);
+        else if (warp == 18 && lane == 0)
+            tma_role(p, bars, smem + SMEM_RING_OFF, reinterpret_cast<uint32_t *>(smem + SMEM_META_OFF));
     }
     fence_before();
     __syncthreads();
@@ -1508,6 +1744,47 @@ static bool make_coef_tensor_map(KParams &p, const SdctTcOptions &opt, SdctTcMap
     const cuuint32_t box[4] = {128, 64, 1, 1};
     static_assert(sizeof(p.tc_coef_map) == 128, "CUtensorMap size");
     return encode_cached(cache, 1, CU_TENSOR_MAP_DATA_TYPE_UINT8, p.coefs, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B, p.tc_coef_map);
+}
+
+template <int LAYOUT>
+static cudaError_t launch_tc_roundtrip(const KParams &p, unsigned grid, cudaStream_t s)
+{
+    static std::atomic<uint64_t> attr_done{0};
+    uint64_t bit;
+    if (attr_pending(attr_done, &bit)) {
+        cudaError_t e = cudaFuncSetAttribute(tc::roundtrip_tc_kernel<LAYOUT>, cudaFuncAttributeMaxDynamicSharedMemorySize, tc::SMEM_RT_BYTES);
+        if (e != cudaSuccess) return e;
+        attr_done.fetch_or(bit, std::memory_order_release);
+    }
+    tc::roundtrip_tc_kernel<LAYOUT><<<grid, tc::RT_THREADS, tc::SMEM_RT_BYTES, s>>>(p);
+    return cudaGetLastError();
+}
+
+extern "C" cudaError_t sdct_k_launch_tc_roundtrip(int layout, const KParams *pp, const SdctTcOptions *popt, SdctTcMapCache *maps, cudaStream_t s)
+{
+    const SdctTcOptions opt = popt ? *popt : SdctTcOptions();
+    KParams p = *pp;
+    p.layout = (uint32_t)layout;
+    const unsigned long long blocks = (unsigned long long)p.rows * p.bpr;
+    p.chunks = (uint32_t)((blocks + SDCT_TC_TILE - 1) / SDCT_TC_TILE);
+    const unsigned long long tiles = (unsigned long long)p.chunks * p.frames;
+    if (tiles == 0) return cudaSuccess;
+    if (p.comps != 1 || tiles > 0xffff0000ull || opt.no_rt_fuse) return cudaErrorNotSupported;
+    p.tiles = (uint32_t)tiles;
+    p.tc_ablate = opt.ablate & (32u | 64u);   // profiling builds: role stamps (+ bit 6: MMA1 latency probe) only
+    for (int c = 0; c < 64; c++) p.tab[c].x = p.tab[c].y = ldexpf(p.tab[c].x, tc::A_SCALE_LOG2);   // A1 carries 2^-24 (bytes_to_half)
+    p.tab2[0].x = p.tab2[0].y = ldexpf(p.tab2[0].x, tc::A_SCALE_LOG2);                              // ... and so does A2
+    p.div_chunks = make_fastdiv(p.chunks);
+    p.div_bpr = make_fastdiv(p.bpr);
+    if (!make_pixel_tensor_map(p, opt, maps)) return cudaErrorNotSupported;   // needs 16-byte-aligned rows, >= 128 blocks per row
+    const unsigned sms = p.sm_count ? p.sm_count : 148u;
+    const unsigned grid = (unsigned)(tiles < sms ? tiles : sms);
+    switch (layout) {
+    case SDCT_K_LAYOUT_A: return launch_tc_roundtrip<SDCT_K_LAYOUT_A>(p, grid, s);
+    case SDCT_K_LAYOUT_B: return launch_tc_roundtrip<SDCT_K_LAYOUT_B>(p, grid, s);
+    case SDCT_K_LAYOUT_C: return launch_tc_roundtrip<SDCT_K_LAYOUT_C>(p, grid, s);
+    default: return cudaErrorInvalidValue;
+    }
 }
 
 extern "C" cudaError_t sdct_k_launch_tc(int op, int layout, const KParams *pp, const SdctTcOptions *popt, SdctTcMapCache *maps, cudaStream_t s)

@@ -52,7 +52,7 @@ void sdct_tc_integer_matrix(int32_t K[64 * 64])
                     K[(u * 8 + v) * 64 + y * 8 + x] = (int32_t)std::llrint(std::ldexp(dct_entry(u, y) * dct_entry(v, x), 22));
 }
 
-void sdct_tc_operand(int layout, uint16_t out[128 * 64])
+void sdct_tc_operand(int layout, uint16_t out[128 * 64], bool positional)
 {
     std::vector<int32_t> Kv(64 * 64);   // (no static scratch: contexts may be created concurrently)
     int32_t *K = Kv.data();
@@ -60,7 +60,7 @@ void sdct_tc_operand(int layout, uint16_t out[128 * 64])
     memset(out, 0, 128 * 64 * sizeof(uint16_t));
     for (int n = 0; n < 128; n++) {
         const int digit = n >> 6, j = n & 63;                  // rows 0..63: K1 (hi), 64..127: K0 (lo)
-        const int pos = sdct_tc_column_position(layout, j);
+        const int pos = positional ? j : sdct_tc_column_position(layout, j);
         // layout A stores (and quantises) coefficient (u, v) at position v*8+u; B and C at u*8+v
         const int u = layout == SDCT_K_LAYOUT_A ? pos & 7 : pos >> 3, v = layout == SDCT_K_LAYOUT_A ? pos >> 3 : pos & 7;
         for (int k = 0; k < 64; k++) {

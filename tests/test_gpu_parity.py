@@ -493,6 +493,43 @@ def test_config5_gigapixel_band_sharded_roundtrip(ctx, oracle):
 
 @pytest.mark.timeout(300, method="thread")
 @pytest.mark.parametrize("layout", LAYOUTS)
+def test_tensor_core_fused_roundtrip(ctx, oracle, layout, monkeypatch):
+    """the ONE-kernel tensor-core round trip (single planes, TMA pixel path: rows of at least 128 blocks): the levels stay
+    in tensor memory between the two products.  Bytes = inverse_tensor(forward_tensor(x)) of the restatement = the two
+    kernels back to back; band windows leave the other rows alone; the bench batch (16 200 tiles) under a hard timeout."""
+    lut = rt_lut(layout)
+    cases = [(64, 1088, 1, None), (96, 2112, 1, (4, 10))] + ([(64, 1088, 2, None)] if layout == sd.LAYOUT_C else [])
+    for (h, w, eyes, window) in cases:
+        img = make_image("smooth", h * eyes, w, seed=81)
+        b0, b1 = window if window else (0, h // 8)
+        job = sd.dense_job(layout, w, h, eyes=eyes, flags=sd.TENSOR, band_begin=b0, band_end=b1 if window else 0)
+        coef = oracle.forward(layout, img, lut, mode=ol.MODE_TENSOR, eyes=eyes)
+        want = np.full((eyes, h, w), 0x5a, dtype=np.uint8)
+        want[:, b0 * 8:b1 * 8] = oracle.inverse(layout, coef, w, h, lut, eyes=eyes, tensor=True).reshape(eyes, h, w)[:, b0 * 8:b1 * 8]
+        out = torch.full((eyes * h, w), 0x5a, dtype=torch.uint8, device="cuda")
+        n0 = ctx.kernel_launches
+        ctx.roundtrip(dev(img), lut, job, out=out)
+        assert ctx.kernel_launches - n0 == 1, "the fused kernel was not taken"
+        assert np.array_equal(out.cpu().numpy().reshape(eyes, h, w), want), (h, w, eyes, window)
+    f, h, w = 64, 1080, 1920
+    g = torch.Generator(device="cuda").manual_seed(78)
+    x = torch.randint(0, 256, (f, h, w), dtype=torch.uint8, device="cuda", generator=g)
+    job = sd.dense_job(layout, w, h, frames=f, flags=sd.TENSOR)
+    fused = ctx.roundtrip(x, lut, job)
+    torch.cuda.synchronize()
+    monkeypatch.setenv("SDCT_TC_NO_RT_FUSE", "1")   # read once, in sdct_create
+    two = sd.Context(0)
+    monkeypatch.delenv("SDCT_TC_NO_RT_FUSE")
+    n0 = two.kernel_launches
+    unfused = two.roundtrip(x, lut, job)
+    torch.cuda.synchronize()
+    assert two.kernel_launches - n0 == 2
+    two.close()
+    assert torch.equal(fused, unfused)
+
+
+@pytest.mark.timeout(300, method="thread")
+@pytest.mark.parametrize("layout", LAYOUTS)
 def test_tensor_core_kernels_full_bench_batch(ctx, layout):
     """the bench workload (64 x 1080p: 16 200 tiles, about 110 per CTA) through the tensor-core kernels: the whole batch
     equals its eight 8-frame shards, forward and inverse.  (A build whose mbarrier phases were ambiguous passed every small

@@ -7,6 +7,7 @@ sys.path.insert(0, ROOT)
 abl = int(sys.argv[1]) if len(sys.argv) > 1 else 0
 layout_name = sys.argv[2] if len(sys.argv) > 2 else "A"
 inverse = len(sys.argv) > 3 and sys.argv[3] == "inverse"
+roundtrip = len(sys.argv) > 3 and sys.argv[3] == "roundtrip"
 os.environ["SDCT_TC_ABLATE"] = str(abl | 32)
 import simd_dct_b200 as sd
 from simd_dct_b200 import _lib
@@ -16,7 +17,9 @@ job = sd.dense_job(L, 1920, 1080, frames=64, flags=sd.TENSOR)
 pix = torch.randint(0, 256, (64, 1080, 1920), dtype=torch.uint8, device="cuda")
 out = torch.empty(64 * 1080 * 1920, dtype=torch.uint8, device="cuda")
 for _ in range(3):
-    if inverse:
+    if roundtrip:
+        ctx.roundtrip(pix, sd.quality_lut(1), job, out=out.view(64, 1080, 1920))
+    elif inverse:
         ctx.inverse(out, sd.quality_lut(1), job, out=pix.view(-1))
     else:
         ctx.forward(pix, sd.quality_lut(1), job, out=out)
@@ -26,7 +29,7 @@ assert _lib.load().sdct_k_tc_trace(tr.ctypes.data_as(C.c_void_p)) == 0
 tr = tr.reshape(3, 256, 8).astype(np.int64)
 t0 = tr[0, 0, 0]
 names = ["producer", "mma", "consumer0"]
-print(f"ablate={abl} layout={layout_name} {'inverse' if inverse else 'forward'}; cycles relative to producer tile 0")
+print(f"ablate={abl} layout={layout_name} {'roundtrip' if roundtrip else 'inverse' if inverse else 'forward'}; cycles relative to producer tile 0")
 for role in range(3):
     print(names[role])
     ks = range(12, 30) if role < 2 else range(12, 30, 2)
