@@ -122,12 +122,12 @@ void read_env(SdctEnv *e)
 // key becomes visible only after the copy has completed, so a hit on any stream may launch without an event); before an
 // entry's device buffer is overwritten the device is synchronised (kernels in flight on other streams may read it).
 struct InvOperandRef { void *d; int S; float off_cols[64]; };
-int inverse_operand(sdct_context *ctx, int layout, const float *lut, const float scale[64], InvOperandRef *out)
+int inverse_operand(sdct_context *ctx, int layout, const float *lut, const float scale[64], InvOperandRef *out, bool rows = false)
 {
     std::lock_guard<std::mutex> lock(ctx->inv_mu);
     sdct_context::InvOperand *op_entry = nullptr;
     for (auto &e : ctx->inv_cache)
-        if (e.d && e.layout == layout && memcmp(e.lut, lut, sizeof(e.lut)) == 0) op_entry = &e;
+        if (e.d && e.layout == layout && e.rows == rows && memcmp(e.lut, lut, sizeof(e.lut)) == 0) op_entry = &e;
     if (!op_entry) {
         sdct_context::InvOperand *victim = &ctx->inv_cache[0];
         for (auto &e : ctx->inv_cache) {
@@ -136,7 +136,7 @@ int inverse_operand(sdct_context *ctx, int layout, const float *lut, const float
         }
         std::vector<uint16_t> operand(128 * 64);
         float off_cols[64];
-        const int S = sdct_tc_inverse_operand(layout, scale, operand.data(), off_cols);
+        const int S = sdct_tc_inverse_operand(layout, scale, operand.data(), off_cols, rows);
         if (victim->layout >= 0) CU_TRY(cudaDeviceSynchronize());
         victim->layout = -1;   // invalid while its buffer is rewritten
         if (!victim->d) CU_TRY(cudaMalloc(&victim->d, operand.size() * sizeof(uint16_t)));
@@ -144,6 +144,7 @@ int inverse_operand(sdct_context *ctx, int layout, const float *lut, const float
         victim->S = S;
         memcpy(victim->off_cols, off_cols, sizeof(off_cols));
         memcpy(victim->lut, lut, sizeof(victim->lut));
+        victim->rows = rows;
         victim->layout = layout;
         op_entry = victim;
     }
@@ -198,7 +199,7 @@ int run_device(sdct_context *ctx, int op, const sdct_job *j, const uint8_t *pixe
             InvOperandRef ref;
             float scale[64];
             for (int i = 0; i < 64; i++) scale[i] = inv_tab[i].x;
-            if (ok && inverse_operand(ctx, j->layout, lut, scale, &ref) == SDCT_OK) {
+            if (ok && inverse_operand(ctx, j->layout, lut, scale, &ref, /*rows*/ true) == SDCT_OK) {
                 for (int c = 0; c < 64; c++) q.off[c] = make_float2(ref.off_cols[c], ref.off_cols[c]);
                 const float unscale = std::ldexp(1.f, -ref.S);
                 q.tab2[0] = make_float2(unscale, unscale);

@@ -78,7 +78,7 @@ struct sdct_context {
     void *d_tc_matrix[3] = {nullptr, nullptr, nullptr};  // tensor-core B operand: [0] layout-A column order, [1] natural order, [2] layout A positional
     // tensor-core inverse operands depend on the LUT: a small cache keyed by (layout, LUT).  An entry is uploaded
     // synchronously before its key becomes visible and is only overwritten after a device synchronise.
-    struct InvOperand { void *d = nullptr; int layout = -1; float lut[64]; float off_cols[64]; int S = 0; uint64_t used = 0; };
+    struct InvOperand { void *d = nullptr; int layout = -1; bool rows = false; float lut[64]; float off_cols[64]; int S = 0; uint64_t used = 0; };
     InvOperand inv_cache[8];
     uint64_t inv_clock = 0;
     std::mutex inv_mu;
@@ -103,4 +103,4 @@ void sdct_tc_integer_matrix(int32_t K[64 * 64]);
 void sdct_tc_operand(int layout, uint16_t out[128 * 64], bool positional = false);   // positional: column c = coefficient position c
 // the LUT-dependent 16 KiB B operand of the tensor-core inverse; returns the scaling exponent S, fills the
 // per-column offsets -127 * sum_i E[p][i]
-int sdct_tc_inverse_operand(int layout, const float tab[64], uint16_t out[128 * 64], float off_cols[64]);
+int sdct_tc_inverse_operand(int layout, const float tab[64], uint16_t out[128 * 64], float off_cols[64], bool rows = false);

@@ -86,10 +86,16 @@ static inline int sdct_tc_column_position(int layout, int j)
 {
     return layout == SDCT_K_LAYOUT_A ? 16 * ((j & 7) >> 1) + 2 * (j >> 3) + (j & 1) : j;
 }
-// tensor-core inverse: D column j -> pixel y*8+x of the block.  A thread receives columns 8k + 2q + e; chunk k / 4
-// is then the pixel row 2q + k/4 and (k % 4, e) its eight pixels, so a thread stores whole 8-byte pixel rows.
-static inline int sdct_tc_inverse_column_pixel(int j)
+// tensor-core inverse: D column j -> pixel y*8+x of the block, two forms of the pixel epilogue:
+//   rows = true  (the fused round trip): column j IS pixel j.  A consumer thread reads its own TMEM lane
+//     (tcgen05.ld.32x32b: thread = block), i.e. whole pixel rows of one block; a warp's store of a row covers 256 contiguous bytes.
+//   rows = false (the inverse kernel): a thread receives columns 8k + 2q + e of two lanes (16x256b loads); chunk k / 4 is then
+//     the pixel row 2q + k/4 and (k % 4, e) its eight pixels.
+// (measured both ways on both kernels, 64 x 1080p: inverse 58 us chunk form / 61-63 us row form, RGB inverse 205 / 245 us;
+//  fused round trip 94 us chunk form / 83 us row form)
+static inline int sdct_tc_inverse_column_pixel(int j, bool rows = false)
 {
+    if (rows) return j;
     const int k = j >> 3, q = (j & 7) >> 1, e = j & 1;
     return (2 * q + (k >> 2)) * 8 + 2 * (k & 3) + e;
 }

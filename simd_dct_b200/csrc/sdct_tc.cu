@@ -1167,10 +1167,121 @@ SDCT_DEV void tc_flush_rgb(const uint8_t *img3, const KParams &p, const Tile &t,
     }
 }
 
+SDCT_DEV void tmem_ld_32x32b_x16(uint32_t taddr, float (&r)[16]);
+
+// The pixel epilogue, row form (the fused round trip): D column j is pixel j of the block, TMEM lane = block, and a thread
+// reads ITS lane - 16 columns (two pixel rows, both digits) per step, the next step's loads in flight while this step is
+// turned into bytes: t = fma(hi, 1024, lo), x = fma(t, 2^-S, offset), rne by the denormal multiply, saturating pack, one
+// 8-byte store per pixel row.  A warp's 32 lanes are 32 consecutive blocks, so its store of one pixel row covers 256
+// contiguous bytes (the 16x256b form of round 1 covered four rows of 64 bytes and needed four block addresses per thread
+// and tile: ~130 dependent integer instructions, a third of its time).  One address per thread and tile here.
+// RT: the fused round-trip kernel's pixel epilogue (D2 stage = warpgroup, its own barriers, offsets in p.off, output into
+// p.pixels_out).  CF == 3: component k % 3 of pixel tile k / 3, rows staged planar in shared memory (see tc_flush_rgb).
+template <int LAYOUT, int CF, bool RT = false>
+SDCT_DEV void inv_consumer_rows(const KParams &p, uint64_t *bars, uint32_t tmem_base, uint32_t c, uint32_t L, uint32_t lane_field, uint8_t *pix_images)
+{
+    static_assert(!RT || CF == 1, "the fused round trip handles single planes");
+    const F2 unscale = p.tab2[0];   // (.x == .y: one 64-bit constant-bank operand)
+    const float2 *offs = RT ? p.off : p.tab;
+    const uint32_t pitch32 = (uint32_t)p.pitch;
+    const bool stereo = p.eyes == 2;
+    // where this thread's block (slot L of the tile) goes: one division per tile
+    auto locate = [&](const Tile &t) -> uint8_t * {
+        const uint32_t nl = t.n0 + (L < t.count ? L : 0u);
+        const uint32_t r = fastdiv(nl, p.div_bpr), bx = nl - r * p.bpr, row = r + p.row0;
+        uint8_t *b = (RT ? p.pixels_out + (t.pix - p.pixels) : const_cast<uint8_t *>(t.pix)) + ((uint64_t)((stereo ? row >> 1 : row) * 8) * pitch32 + bx * 8);
+        if (stereo && (row & 1)) b += p.eye_stride;
+        return b;
+    };
+    TileWalk wk;
+    if (CF == 1) wk.init(p, c, CONSUMER_WGS); else wk.init(p, 0, 1);
+    uint32_t comp = CF == 1 ? 0u : c;
+    uint8_t *dst = nullptr;
+    uint32_t count = 0;
+    if (CF == 1 && wk.tile < p.tiles) {
+        const Tile t = tile_at<1, TILE>(p, wk);
+        dst = locate(t);
+        count = t.count;
+    }
+    for (uint32_t k = c;; k += CONSUMER_WGS) {
+        if (wk.tile >= p.tiles) break;
+        const uint32_t sd = RT ? c : k % D_STAGES, ud = RT ? k / 2 : k / D_PERIOD;
+        uint64_t *d_full = bars + (RT ? RT_BAR_D2_FULL + c : BAR_D_FULL + d_bar(k)), *d_empty = bars + (RT ? RT_BAR_D2_EMPTY + c : BAR_D_EMPTY + d_bar(k));
+        Tile ptile;             // CF == 3: the pixel tile of this tile
+        uint8_t *img = nullptr; //          and this thread's row 0 in this component's image
+        bool last_own = false;  //          this warpgroup's last component of the pixel tile
+        if (CF != 1) {
+            ptile = tile_at<1, TILE>(p, wk);
+            img = pix_images + ((k / CF) & 1u) * PIX_IMG3 + comp * PIX_COMP + L * 8u;
+            last_own = comp + CONSUMER_WGS >= (uint32_t)CF;
+        }
+        const bool tr = (ablate_bits(p) & 32) && blockIdx.x == 0 && L == 0;
+        stamp(tr, 2, k, 0);
+        mbar_wait(d_full, ud & 1);
+        fence_after();
+        stamp(tr, 2, k, 1);
+        if (CF == 1) {
+            wk.next(p);
+        } else {
+            comp += CONSUMER_WGS;
+            if (comp >= (uint32_t)CF) { comp -= CF; wk.next(p); }
+        }
+        const uint32_t td = tmem_base + (RT ? RT_TMEM_D2 : TMEM_D_OFF) + sd * D_COLS + lane_field;
+        float hiA[16], loA[16], hiB[16], loB[16];
+        tmem_ld_32x32b_x16(td, hiA);
+        tmem_ld_32x32b_x16(td + 64, loA);
+        tmem_ld_32x32b_x16(td + 16, hiB);
+        tmem_ld_32x32b_x16(td + 80, loB);
+        const bool valid = CF != 1 || L < count;
+#define SDCT_TC_ROWS_STEP(S, HI, LO)                                                                                  \
+        {                                                                                                             \
+            _Pragma("unroll") for (int rr = 0; rr < 2; rr++) {   /* pixel row 2 S + rr: columns 16 S + 8 rr .. + 7 */ \
+                F2 b4[4];                                                                                             \
+                _Pragma("unroll") for (int i = 0; i < 4; i++) {                                                       \
+                    const int j = 16 * (S) + 8 * rr + 2 * i;                                                          \
+                    const F2 t = fma2(make_float2(HI[8 * rr + 2 * i], HI[8 * rr + 2 * i + 1]), splat(1024.f), make_float2(LO[8 * rr + 2 * i], LO[8 * rr + 2 * i + 1])); \
+                    /* RT: the offsets are packed in pairs, (p.off[j / 2].x, .y) = columns j, j + 1: one 64-bit constant operand */ \
+                    b4[i] = mulk(fma2(t, unscale, RT ? offs[j / 2] : make_float2(offs[j].x, offs[j + 1].x)), SDCT_DENORM_MIN); \
+                }                                                                                                     \
+                const uint2 v = make_uint2(pack4_sat(b4[0].x, b4[0].y, b4[1].x, b4[1].y), pack4_sat(b4[2].x, b4[2].y, b4[3].x, b4[3].y)); \
+                if (CF != 1) *reinterpret_cast<uint2 *>(img + (2 * (S) + rr) * PIX_PITCH) = v;                          \
+                else if (valid) *reinterpret_cast<uint2 *>(dst + (uint64_t)(2 * (S) + rr) * pitch32) = v;              \
+            }                                                                                                         \
+        }
+        stamp(tr, 2, k, 4);
+        tmem_wait_ld4(hiA, loA, hiB, loB);
+        stamp(tr, 2, k, 5);
+        SDCT_TC_ROWS_STEP(0, hiA, loA)
+        tmem_ld_32x32b_x16(td + 32, hiA);
+        tmem_ld_32x32b_x16(td + 96, loA);
+        SDCT_TC_ROWS_STEP(1, hiB, loB)
+        tmem_ld_32x32b_x16(td + 48, hiB);
+        tmem_ld_32x32b_x16(td + 112, loB);
+        stamp(tr, 2, k, 6);
+        tmem_wait_ld4(hiA, loA, hiB, loB);
+        fence_before();
+        mbar_arrive(d_empty);   // every load of this thread has landed: hand the D stage back to the MMA warp
+        stamp(tr, 2, k, 2);
+        SDCT_TC_ROWS_STEP(2, hiA, loA)
+        SDCT_TC_ROWS_STEP(3, hiB, loB)
+#undef SDCT_TC_ROWS_STEP
+        stamp(tr, 2, k, 3);
+        if (CF == 1 && wk.tile < p.tiles) {
+            const Tile t = tile_at<1, TILE>(p, wk);
+            dst = locate(t);
+            count = t.count;
+        }
+        if (CF != 1 && last_own) {
+            asm volatile("bar.sync %0, %1;" ::"n"(BAR_FLUSH), "n"(CONSUMER_WGS * 128) : "memory");
+            tc_flush_rgb(pix_images + ((k / CF) & 1u) * PIX_IMG3, p, ptile, c * 128u + L);
+        }
+    }
+}
+
 // RT: the fused round-trip kernel's pixel epilogue (roundtrip_tc_kernel below): D2 stage = warpgroup, its own barriers,
 // pixel offsets in p.off, output into p.pixels_out
 template <int LAYOUT, int CF, bool RT = false>
-SDCT_DEV void inv_consumer_role(const KParams &p, uint64_t *bars, uint32_t tmem_base, uint32_t c, uint32_t L, uint32_t lane_field, uint8_t *pix_images)
+SDCT_DEV void inv_consumer_chunks(const KParams &p, uint64_t *bars, uint32_t tmem_base, uint32_t c, uint32_t L, uint32_t lane_field, uint8_t *pix_images)
 {
     static_assert(!RT || CF == 1, "the fused round trip handles single planes");
     const uint32_t lane = L & 31, g = lane >> 2, q = lane & 3;
@@ -1178,7 +1289,7 @@ SDCT_DEV void inv_consumer_role(const KParams &p, uint64_t *bars, uint32_t tmem_
     F2 off[8];
 #pragma unroll
     for (int k = 0; k < 8; k++) off[k] = RT ? make_float2(p.off[8 * k + 2 * q].x, p.off[8 * k + 2 * q + 1].x) : make_float2(p.tab[8 * k + 2 * q].x, p.tab[8 * k + 2 * q + 1].x);
-    const F2 unscale = splat(p.tab2[0].x);
+    const F2 unscale = p.tab2[0];   // (.x == .y: one 64-bit constant-bank operand)
     // TMEM lane = block of the tile (the A rows are in natural order here): a 16x256b load hands this thread lanes
     // g and g + 8 of a 16-lane half, i.e. blocks P = sp0 + 16 half and Q = P + 8
     const uint32_t sp0 = (L >> 5) * 32u + g;
@@ -1257,16 +1368,13 @@ SDCT_DEV void inv_consumer_role(const KParams &p, uint64_t *bars, uint32_t tmem_
         if (CF == 1 && (ablate_bits(p) & 4)) { fence_before(); mbar_arrive(d_empty); if (wk.tile < p.tiles) locate_tile(wk, cur); continue; }
         // Four chunks of 32 columns (pixel rows 2q, 2q + 1 of two 16-block halves).  Chunks 0 and 1 are loaded
         // together; chunk 2 is requested as soon as chunk 0's registers are free, chunk 3 after chunk 1's: two
-        // load waits per tile instead of four, the second hidden behind chunk 1's arithmetic.  The next tile's
-        // addresses are computed while the first loads are in flight.
+        // load waits per tile instead of four, the second hidden behind chunk 1's arithmetic.
         float hiA[16], loA[16], hiB[16], loB[16];
         const uint32_t td = tmem_base + (RT ? RT_TMEM_D2 : TMEM_D_OFF) + sd * D_COLS + lane_field;
         tmem_ld_16x256b_x4(td, hiA);
         tmem_ld_16x256b_x4(td + 64, loA);
         tmem_ld_16x256b_x4(td + 32, hiB);
         tmem_ld_16x256b_x4(td + 96, loB);
-        Dst nxt = cur;
-        if (CF == 1 && wk.tile < p.tiles) locate_tile(wk, nxt);
 #define SDCT_TC_INV_CHUNK(C, HI, LO)                                                                                  \
         {                                                                                                             \
             constexpr int half = (C) >> 1, kk = (C) & 1;                                                              \
@@ -1295,17 +1403,24 @@ SDCT_DEV void inv_consumer_role(const KParams &p, uint64_t *bars, uint32_t tmem_
             }                                                                                                         \
         }
         const uint32_t td2 = td + (16u << 16);   // lanes 16..31 of the warp's quarter: the second half
+        stamp(tr, 2, k, 4);
         tmem_wait_ld4(hiA, loA, hiB, loB);
+        stamp(tr, 2, k, 5);
         SDCT_TC_INV_CHUNK(0, hiA, loA)
         tmem_ld_16x256b_x4(td2, hiA);
         tmem_ld_16x256b_x4(td2 + 64, loA);
         SDCT_TC_INV_CHUNK(1, hiB, loB)
         tmem_ld_16x256b_x4(td2 + 32, hiB);
         tmem_ld_16x256b_x4(td2 + 96, loB);
+        stamp(tr, 2, k, 6);
         tmem_wait_ld4(hiA, loA, hiB, loB);
         fence_before();
         mbar_arrive(d_empty);   // every load of this thread has landed: hand the D stage back to the MMA warp
         stamp(tr, 2, k, 2);
+        // the next tile's addresses: a chain of ~130 dependent integer instructions (540-920 clocks when it stood between
+        // "D full" and the first chunk, role stamps of round 2); here it has the arithmetic of two chunks to interleave with
+        Dst nxt = cur;
+        if (CF == 1 && wk.tile < p.tiles) locate_tile(wk, nxt);
         SDCT_TC_INV_CHUNK(2, hiA, loA)
         SDCT_TC_INV_CHUNK(3, hiB, loB)
 #undef SDCT_TC_INV_CHUNK
@@ -1319,6 +1434,14 @@ SDCT_DEV void inv_consumer_role(const KParams &p, uint64_t *bars, uint32_t tmem_
             tc_flush_rgb(pix_images + ((k / CF) & 1u) * PIX_IMG3, p, ptile, c * 128u + L);
         }
     }
+}
+
+template <int LAYOUT, int CF, bool RT = false>
+SDCT_DEV void inv_consumer_role(const KParams &p, uint64_t *bars, uint32_t tmem_base, uint32_t c, uint32_t L, uint32_t lane_field, uint8_t *pix_images)
+{
+    // the row form wins in the fused round trip, the chunk form in the inverse kernel (sdct_kernels.h: sdct_tc_inverse_column_pixel)
+    if (RT) inv_consumer_rows<LAYOUT, CF, RT>(p, bars, tmem_base, c, L, lane_field, pix_images);
+    else inv_consumer_chunks<LAYOUT, CF, RT>(p, bars, tmem_base, c, L, lane_field, pix_images);
 }
 
 template <int LAYOUT, bool CT, int CF>
@@ -1414,7 +1537,7 @@ SDCT_DEV void rt_quantise16(const KParams &p, const float (&hi)[16], const float
 #pragma unroll
     for (int i = 0; i < 8; i++) {
         const F2 t = fma2(make_float2(hi[2 * i], hi[2 * i + 1]), splat(1024.f), make_float2(lo[2 * i], lo[2 * i + 1]));
-        const F2 bits = quant_rne_bias(t, make_float2(p.tab[C0 + 2 * i].x, p.tab[C0 + 2 * i + 1].x));
+        const F2 bits = quant_rne_bias(t, p.tab[(C0 + 2 * i) / 2]);   // scales packed in pairs: (p.tab[j / 2].x, .y) = columns j, j + 1
         // saturate to bytes, then zero-extend each to 16 bits: low half = column C0 + 2i, high half = the next one
         w[i] = __byte_perm(pack_sat(__float_as_uint(bits.y), __float_as_uint(bits.x), 0u), 0u, 0x4140);
     }
@@ -1772,8 +1895,13 @@ extern "C" cudaError_t sdct_k_launch_tc_roundtrip(int layout, const KParams *pp,
     if (p.comps != 1 || tiles > 0xffff0000ull || opt.no_rt_fuse) return cudaErrorNotSupported;
     p.tiles = (uint32_t)tiles;
     p.tc_ablate = opt.ablate & (32u | 64u);   // profiling builds: role stamps (+ bit 6: MMA1 latency probe) only
-    for (int c = 0; c < 64; c++) p.tab[c].x = p.tab[c].y = ldexpf(p.tab[c].x, tc::A_SCALE_LOG2);   // A1 carries 2^-24 (bytes_to_half)
-    p.tab2[0].x = p.tab2[0].y = ldexpf(p.tab2[0].x, tc::A_SCALE_LOG2);                              // ... and so does A2
+    // p.tab / p.off arrive with one value per column (.x); the kernel wants them packed in pairs so that a packed instruction
+    // takes both lanes' constants as one 64-bit constant-bank operand: (tab[i].x, tab[i].y) = columns 2i, 2i + 1
+    for (int i = 0; i < 32; i++) {
+        p.tab[i] = make_float2(ldexpf(pp->tab[2 * i].x, tc::A_SCALE_LOG2), ldexpf(pp->tab[2 * i + 1].x, tc::A_SCALE_LOG2));   // A1 carries 2^-24 (bytes_to_half)
+        p.off[i] = make_float2(pp->off[2 * i].x, pp->off[2 * i + 1].x);
+    }
+    p.tab2[0].x = p.tab2[0].y = ldexpf(p.tab2[0].x, tc::A_SCALE_LOG2);   // ... and so does A2
     p.div_chunks = make_fastdiv(p.chunks);
     p.div_bpr = make_fastdiv(p.bpr);
     if (!make_pixel_tensor_map(p, opt, maps)) return cudaErrorNotSupported;   // needs 16-byte-aligned rows, >= 128 blocks per row

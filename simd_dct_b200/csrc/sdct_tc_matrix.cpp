@@ -79,9 +79,9 @@ void sdct_tc_operand(int layout, uint16_t out[128 * 64], bool positional)
 // The dequantiser scale is folded into the matrix, so the operand depends on the LUT: E[p][i] = W[p][i] * tab[i]
 // (W = unnormalised inverse basis = 8 * C[u][y] * C[v][x], tab = the inverse scale table indexed by the layout's own
 // coefficient index i), scaled by the largest 2^S that keeps |round(2^S E)| < 2^20 - 512, split into two fp16 digits.
-// Row n of the operand = digit n / 64 of D column j = n % 64 = pixel sdct_tc_inverse_column_pixel(j).
+// Row n of the operand = digit n / 64 of D column j = n % 64 = pixel sdct_tc_inverse_column_pixel(j, rows).
 // oracle/sdct_oracle.c (inverse_tensor_matrix) restates this independently.
-int sdct_tc_inverse_operand(int layout, const float tab[64], uint16_t out[128 * 64], float off_cols[64])
+int sdct_tc_inverse_operand(int layout, const float tab[64], uint16_t out[128 * 64], float off_cols[64], bool rows)
 {
     std::vector<double> Ev(64 * 64);
     double *E = Ev.data();
@@ -105,7 +105,7 @@ int sdct_tc_inverse_operand(int layout, const float tab[64], uint16_t out[128 * 
     }
     memset(out, 0, 128 * 64 * sizeof(uint16_t));
     for (int j = 0; j < 64; j++) {
-        const int px = sdct_tc_inverse_column_pixel(j);
+        const int px = sdct_tc_inverse_column_pixel(j, rows);
         int64_t sum = 0;   // of the rounded entries: the level offset -127 must go through the same matrix as the levels
         for (int k = 0; k < 64; k++) {
             const double e = E[px * 64 + k];
