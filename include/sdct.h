@@ -117,6 +117,19 @@ int sdct_inverse_device(sdct_context *ctx, const sdct_job *job, const void *d_co
 int sdct_roundtrip_device(sdct_context *ctx, const sdct_job *job, const void *d_pixels_in, const float *lut,
                           void *d_pixels_out, void *stream);
 
+/* The same round trip as TWO kernels (forward -> quantised levels in scratch memory -> inverse) for callers that cannot allocate
+ * device memory at call time (CUDA graph capture, serving loops, harnesses that forbid cudaMalloc).  No counterpart in the
+ * reference.  The levels live in a file-scope __device__ array of
+ * SDCT_NOALLOC_MAX_COEF_BYTES (32 MiB, plus 16 KiB for the SDCT_TENSOR inverse operand) that every GPU which loads the library
+ * holds until process exit; the call path contains no cudaMalloc / cudaFree / memory-pool routine.  Same arguments, same flags
+ * and the same output bytes as sdct_roundtrip_device.  Jobs with frames * width * height * eyes * components above the maximum
+ * are rejected with SDCT_NOT_SUPPORTED (sdct_last_error() names both sizes).  Every call on a GPU shares the array (it keeps
+ * the previous call's contents; nothing in it needs clearing, the forward kernel writes every byte the inverse reads): calls
+ * whose kernels overlap on the device - different streams, threads or contexts - race and must be serialised by the caller. */
+#define SDCT_NOALLOC_MAX_COEF_BYTES (32u << 20)
+int sdct_roundtrip_noalloc_device(sdct_context *ctx, const sdct_job *job, const void *d_pixels_in, const float *lut,
+                                  void *d_pixels_out, void *stream);
+
 /* The step after the path (layout C only: each of its 64 planes is one homogeneous stream, src/simd_dct.cpp:1061-1069):
  * per coefficient plane of every (frame, component) set, over the job's band window, how many levels are zero (byte 127,
  * the quantiser's bias), in how many runs they come (in block order), the sum of |level - 127| and the bitwise OR of all |level - 127| (its

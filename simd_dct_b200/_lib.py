@@ -38,6 +38,7 @@ SYMBOLS = {
     "sdct_forward_device": (C.c_int, [_vp, _JP, _vp, _fp, _vp, _vp]),
     "sdct_inverse_device": (C.c_int, [_vp, _JP, _vp, _fp, _vp, _vp]),
     "sdct_roundtrip_device": (C.c_int, [_vp, _JP, _vp, _fp, _vp, _vp]),
+    "sdct_roundtrip_noalloc_device": (C.c_int, [_vp, _JP, _vp, _fp, _vp, _vp]),
     "sdct_forward_host": (C.c_int, [_vp, _JP, _vp, _fp, _vp]),
     "sdct_inverse_host": (C.c_int, [_vp, _JP, _vp, _fp, _vp]),
     "sdct_forward_host_multi": (C.c_int, [C.POINTER(_vp), C.c_int, _JP, _vp, _fp, _vp]),

@@ -171,6 +171,13 @@ class Context:
                                               C.c_void_p(out.data_ptr()), self._stream()))
         return out
 
+    def roundtrip_noalloc(self, pixels, lut, job: Job, out):
+        """sdct_roundtrip_noalloc_device: the two-kernel round trip with the levels in the library's file-scope device array
+        (at most NOALLOC_MAX_COEF_BYTES); `out` is the caller's - nothing is allocated on this path, here or in the library"""
+        check(self._lib.sdct_roundtrip_noalloc_device(self._h, C.byref(job), C.c_void_p(pixels.data_ptr()), _fp(lut),
+                                                      C.c_void_p(out.data_ptr()), self._stream()))
+        return out
+
     def plane_stats(self, coefs, job: Job):
         """layout C: per coefficient plane {zero levels, zero runs, sum |level - 127|, OR of |level - 127|} over the job's
         band window -> int64 tensor [frames, components, 64, 4] on the device (sdct_plane_stats_device)"""

@@ -11,7 +11,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libsdct.so")
 KERNEL_PARTS = 8  # sdct_kernels.cu is compiled once per -DSDCT_PART (parallel template instantiation)
-SOURCES = ["sdct_kernels.cu", "sdct_tc.cu", "sdct_stats.cu", "sdct_tc_matrix.cpp", "sdct_api.cpp", "sdct_host.cpp", "simd_dct_shim.cpp"]
+SOURCES = ["sdct_kernels.cu", "sdct_tc.cu", "sdct_stats.cu", "sdct_noalloc.cu", "sdct_tc_matrix.cpp", "sdct_api.cpp", "sdct_host.cpp", "simd_dct_shim.cpp"]
 HEADERS = ["sdct_kernels.h", "sdct_math.cuh", "sdct_io.cuh", "sdct_internal.h", "../../include/sdct.h", "../../include/simd_dct.h"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC,-Wall", "-x", "cu"]

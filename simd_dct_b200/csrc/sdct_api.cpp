@@ -155,8 +155,28 @@ int inverse_operand(sdct_context *ctx, int layout, const float *lut, const float
     return SDCT_OK;
 }
 
+// The same operand in the allocation-free path's file-scope array (sdct_noalloc.cu) instead of a cache entry: uploaded on the
+// call's stream when (layout, LUT) differ from what the array holds; no allocation of device memory on any path.
+int static_inverse_operand(SdctStaticScratch *ss, int layout, const float *lut, const float scale[64], InvOperandRef *out, cudaStream_t st)
+{
+    std::lock_guard<std::mutex> lock(ss->mu);
+    if (ss->layout != layout || memcmp(ss->lut, lut, sizeof(ss->lut)) != 0) {
+        std::vector<uint16_t> operand(128 * 64);
+        ss->layout = -1;
+        ss->S = sdct_tc_inverse_operand(layout, scale, operand.data(), ss->off_cols, false);
+        // pageable source: the call returns once the bytes are staged, so `operand` may go out of scope
+        CU_TRY(cudaMemcpyAsync(ss->inv_operand, operand.data(), operand.size() * sizeof(uint16_t), cudaMemcpyHostToDevice, st));
+        memcpy(ss->lut, lut, sizeof(ss->lut));
+        ss->layout = layout;
+    }
+    out->d = ss->inv_operand;
+    out->S = ss->S;
+    memcpy(out->off_cols, ss->off_cols, sizeof(out->off_cols));
+    return SDCT_OK;
+}
+
 int run_device(sdct_context *ctx, int op, const sdct_job *j, const uint8_t *pixels, uint8_t *coefs,
-               uint8_t *pixels_out, const float *lut, cudaStream_t stream)
+               uint8_t *pixels_out, const float *lut, cudaStream_t stream, SdctStaticScratch *static_operand = nullptr)
 {
     Geometry g;
     int rc = sdct_validate(j, &g);
@@ -281,7 +301,8 @@ int run_device(sdct_context *ctx, int op, const sdct_job *j, const uint8_t *pixe
             InvOperandRef ref;
             float scale[64];
             for (int i = 0; i < 64; i++) scale[i] = p.tab[i].x;
-            if ((rc = inverse_operand(ctx, j->layout, lut, scale, &ref))) return rc;
+            if ((rc = static_operand ? static_inverse_operand(static_operand, j->layout, lut, scale, &ref, st)
+                                     : inverse_operand(ctx, j->layout, lut, scale, &ref))) return rc;
             p.tc_matrix = ref.d;
             for (int c = 0; c < 64; c++) p.tab[c] = make_float2(ref.off_cols[c], ref.off_cols[c]);
             const float unscale = std::ldexp(1.f, -ref.S);
@@ -305,6 +326,31 @@ int run_device(sdct_context *ctx, int op, const sdct_job *j, const uint8_t *pixe
 }
 
 }  // namespace
+
+// The two-kernel round trip with the levels in caller-chosen memory (sdct_noalloc.cu passes its file-scope array): what the
+// SDCT_TENSOR branch of run_device does with a pool allocation, for every arithmetic, without one.
+int sdct_roundtrip_two_pass_static(sdct_context *ctx, const sdct_job *j, const void *d_in, const float *lut, void *d_out,
+                                   void *stream, SdctStaticScratch *ss, uint64_t max_coef_bytes)
+{
+    Geometry g;
+    int rc = sdct_validate(j, &g);
+    if (rc) return rc;
+    if (!ctx) return fail(SDCT_INVALID_PARAMETER, "context is null");
+    if (!d_in || !d_out) return fail(SDCT_INVALID_PARAMETER, "null buffer");
+    sdct_job cj = *j;   // dense, 16-byte-aligned coefficient strides (the array is 256-byte aligned)
+    cj.coef_comp_stride = j->width * j->height * (uint64_t)g.eyes;
+    cj.coef_plane_stride = cj.coef_comp_stride / 64;
+    cj.coef_frame_stride = cj.coef_comp_stride * g.comps;
+    if (j->frames != 0 && cj.coef_frame_stride > max_coef_bytes / j->frames)
+        return fail(SDCT_NOT_SUPPORTED, "job has %llu x %llu coefficient bytes; the allocation-free entry point holds at most %llu "
+                                        "(SDCT_NOALLOC_MAX_COEF_BYTES) - use sdct_roundtrip_device",
+                    (unsigned long long)j->frames, (unsigned long long)cj.coef_frame_stride, (unsigned long long)max_coef_bytes);
+    if (j->frames * cj.coef_frame_stride == 0) return SDCT_OK;
+    cudaStream_t st = stream ? (cudaStream_t)stream : ctx->stream;
+    rc = run_device(ctx, SDCT_K_OP_FORWARD, &cj, (const uint8_t *)d_in, ss->coefs, nullptr, lut, st);
+    if (rc == SDCT_OK) rc = run_device(ctx, SDCT_K_OP_INVERSE, &cj, (const uint8_t *)d_out, ss->coefs, nullptr, lut, st, ss);
+    return rc;
+}
 
 extern "C" {
 

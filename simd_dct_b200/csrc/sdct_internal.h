@@ -97,6 +97,21 @@ Pipeline *sdct_acquire_pipeline(sdct_context *ctx);
 void sdct_release_pipeline(sdct_context *ctx, Pipeline *p);
 void sdct_destroy_pipeline(Pipeline *p);
 
+// sdct_noalloc.cu: the allocation-free two-kernel round trip keeps its scratch in file-scope __device__ arrays; this is the
+// per-device record of their ADDRESSES (cudaGetSymbolAddress, once per device) and of what the operand array holds
+struct SdctStaticScratch {
+    uint8_t *coefs = nullptr;      // SDCT_NOALLOC_MAX_COEF_BYTES: the levels between the forward and the inverse kernel
+    void *inv_operand = nullptr;   // 16 KiB: the tensor-core inverse's LUT-dependent operand (SDCT_TENSOR jobs)
+    int layout = -1;               // key of inv_operand's current contents: (layout, lut); -1 = nothing valid
+    float lut[64];
+    float off_cols[64];
+    int S = 0;
+    std::mutex mu;                 // guards the key; the arrays themselves are shared by every call (overlapping calls race)
+};
+// sdct_api.cpp: forward kernel -> ss->coefs -> inverse kernel on `stream`; calls no allocating routine
+int sdct_roundtrip_two_pass_static(sdct_context *ctx, const sdct_job *j, const void *d_in, const float *lut, void *d_out,
+                                   void *stream, SdctStaticScratch *ss, uint64_t max_coef_bytes);
+
 // tensor-core form: K[c][p] = round(2^22 * C[u][y] * C[v][x]), c = u*8+v, p = y*8+x (sdct_tc_matrix.cpp)
 void sdct_tc_integer_matrix(int32_t K[64 * 64]);
 // the 16 KiB B operand for `layout`: fp16 digits of K in the UMMA canonical K-major layout
