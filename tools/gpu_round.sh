@@ -15,7 +15,7 @@ timeout 300 python bench.py --steps 3 --warmup 3 --no-variants --no-e2e > gpurun
 timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/launches.csv python bench.py --steps 3 --warmup 3 --no-variants --no-e2e > gpurun_out/ncu.log 2>&1
 echo "ncu launches rc=$?"
 for spec in "fwd_B_exact forward_kernel" "fwd_A_exact forward_kernel" "rt_B_exact roundtrip_kernel" "inv_B_exact inverse_kernel" "fwd_B_tensor forward_tc_kernel" \
-            "fwd_A_tensor forward_tc_kernel" "fwd_C_tensor forward_tc_kernel" "inv_B_tensor inverse_tc_kernel" "inv_A_tensor inverse_tc_kernel" "inv_C_tensor inverse_tc_kernel" $EXTRA_NCU; do
+            "fwd_A_tensor forward_tc_kernel" "fwd_C_tensor forward_tc_kernel" "inv_B_tensor inverse_tc_kernel" "inv_A_tensor inverse_tc_kernel" "inv_C_tensor inverse_tc_kernel" "rt_B_tensor roundtrip_tc_kernel" $EXTRA_NCU; do
   set -- $spec
   timeout 300 bash tools/gpu_ncu.sh $1 $2 --reps 4 $1 2>&1 | tail -2
 done
