@@ -111,6 +111,7 @@ void read_env(SdctEnv *e)
     e->host_chunk_bytes = (uint64_t)num("SDCT_HOST_CHUNK_MB", 1, 4096, 16) << 20;
     e->host_slots = (int)num("SDCT_HOST_SLOTS", 1, kSlots, 4);
     e->host_no_ramp = getenv("SDCT_HOST_NO_RAMP") != nullptr;
+    e->host_trace = getenv("SDCT_HOST_TRACE") != nullptr;
     e->tc.no_tma = getenv("SDCT_TC_NO_TMA") != nullptr;
     e->tc.no_rgb_fuse = getenv("SDCT_TC_NO_RGB_FUSE") != nullptr;
     e->tc.no_tma_store = getenv("SDCT_TC_NO_TMA_STORE") != nullptr;

@@ -18,6 +18,8 @@
 // multi-device form runs one such pipeline per device on its own host thread.
 #include "sdct_internal.h"
 
+#include <chrono>
+
 #include <algorithm>
 #include <cstdlib>
 #include <cstring>
@@ -223,6 +225,18 @@ int run_chunks(sdct_context *ctx, Pipeline *pipe, int op, const sdct_job *job, c
     const bool in_pinned = is_pinned(h_in), out_pinned = is_pinned(h_out);
     const int depth = ctx->env.host_slots;
     Pending pending[kSlots];
+    // $SDCT_HOST_TRACE (profiling only): four events per chunk and the host's submit times, printed after the call
+    const bool trace = ctx->env.host_trace;
+    std::vector<cudaEvent_t> tev;
+    std::vector<double> t_submit;
+    const auto t_begin = std::chrono::steady_clock::now();
+    auto stamp = [&](cudaStream_t st) {
+        if (!trace) return;
+        cudaEvent_t e;
+        cudaEventCreate(&e);
+        cudaEventRecord(e, st);
+        tev.push_back(e);
+    };
 
     for (size_t ci = 0; ci < chunks.size(); ci++) {
         const Plan plan = plan_chunk(*job, g, chunks[ci]);
@@ -230,6 +244,8 @@ int run_chunks(sdct_context *ctx, Pipeline *pipe, int op, const sdct_job *job, c
         Pending &pd = pending[ci % depth];
         if ((rc = drain(s, pd))) return rc;
         if (ci >= (size_t)depth) CU_TRY(cudaEventSynchronize(s.done));  // slot buffers free again
+        if (trace) t_submit.push_back(std::chrono::duration<double, std::micro>(std::chrono::steady_clock::now() - t_begin).count());
+        stamp(s.stream);
         if ((rc = grow_device(&s.d_pix, &s.d_pix_cap, plan.pix_bytes))) return rc;
         if ((rc = grow_device(&s.d_coef, &s.d_coef_cap, plan.coef_bytes))) return rc;
         const std::vector<Copy> &cin = fwd ? plan.pix : plan.coef, &cout = fwd ? plan.coef : plan.pix;
@@ -244,10 +260,12 @@ int run_chunks(sdct_context *ctx, Pipeline *pipe, int op, const sdct_job *job, c
             stage_rows(cin, h_in, s.h_in, true);
             CU_TRY(cudaMemcpyAsync(d_in, s.h_in, in_bytes, cudaMemcpyHostToDevice, s.stream));
         }
+        stamp(s.stream);
         // kernel: the chunk as a dense job on the slot's buffers
         rc = fwd ? sdct_forward_device(ctx, &plan.dev, s.d_pix, lut, s.d_coef, s.stream)
                  : sdct_inverse_device(ctx, &plan.dev, s.d_coef, lut, s.d_pix, s.stream);
         if (rc) return rc;
+        stamp(s.stream);
         // D2H
         if (out_pinned) {
             if ((rc = copy_direct(cout, h_out, d_out, false, s.stream))) return rc;
@@ -256,11 +274,24 @@ int run_chunks(sdct_context *ctx, Pipeline *pipe, int op, const sdct_job *job, c
             CU_TRY(cudaMemcpyAsync(s.h_out, d_out, out_bytes, cudaMemcpyDeviceToHost, s.stream));
             pd.active = true; pd.copies = cout; pd.dst = h_out;
         }
+        stamp(s.stream);
         CU_TRY(cudaEventRecord(s.done, s.stream));
     }
     for (int i = 0; i < kSlots; i++) {
         if ((rc = drain(pipe->slots[i], pending[i]))) return rc;
         if (pipe->slots[i].stream) CU_TRY(cudaStreamSynchronize(pipe->slots[i].stream));
+    }
+    if (trace) {
+        const double t_end = std::chrono::duration<double, std::micro>(std::chrono::steady_clock::now() - t_begin).count();
+        fprintf(stderr, "sdct host trace: %zu chunks, %d slots, call %.0f us (times in us: host submit | device h2d begin, h2d end, kernel end, d2h end; device clock starts at chunk 0's h2d begin)\n",
+                chunks.size(), depth, t_end);
+        for (size_t ci = 0; ci < chunks.size(); ci++) {
+            float t[4];
+            for (int k = 0; k < 4; k++) cudaEventElapsedTime(&t[k], tev[0], tev[4 * ci + k]);
+            fprintf(stderr, "  chunk %2zu frames %llu-%llu bands %u-%u | %8.0f | %8.0f %8.0f %8.0f %8.0f\n", ci, (unsigned long long)chunks[ci].f0,
+                    (unsigned long long)chunks[ci].f1, chunks[ci].b0, chunks[ci].b1, t_submit[ci], t[0] * 1e3, t[1] * 1e3, t[2] * 1e3, t[3] * 1e3);
+        }
+        for (cudaEvent_t e : tev) cudaEventDestroy(e);
     }
     return SDCT_OK;
 }

@@ -64,6 +64,7 @@ struct SdctEnv {
     uint64_t host_chunk_bytes = 16ull << 20;
     int host_slots = 4;
     bool host_no_ramp = false;
+    bool host_trace = false;   // $SDCT_HOST_TRACE: per-chunk timeline of a host call on stderr (profiling)
     SdctTcOptions tc;
 };
 

@@ -266,8 +266,10 @@ SDCT_DEV F2 div255(F2 x) { return fma2(x, splat(SDCT_R255_HI), mulk(x, SDCT_R255
 #define SDCT_128_DENORM __int_as_float(0x00000080)        /*  128 * 2^-149 */
 
 // reference AVX2 path (:2224): max(min(127 + cvtps_epi32(c*q), 255), 0), cvtps = nearest even.
-// bits = 128 - rne(fl(c*q)) (complemented level before saturation).  Exact for |c*q| < 2^23;
-// sdct_api.cpp rejects tables that could exceed that.
+// bits = 128 - rne(fl(c*q)) (complemented level before saturation) while |c*q| < 2^23 (the result is a denormal whose
+// bit pattern IS the integer); beyond that the pattern is a normal float's, same sign and larger magnitude, which the
+// saturating pack clamps to the same byte.  From 2^31 the reference's cvtps_epi32 returns INT_MIN (:2224): sdct_api.cpp
+// (build_tables) rejects tables under which |c*q| could get there.
 SDCT_DEV F2 quant_rne_c(F2 c, F2 q) { return fma2(mul2(c, q), splat(SDCT_NEG_DENORM_MIN), splat(SDCT_128_DENORM)); }
 
 // reference scalar path (:245 / :362): (u8)roundf(clamp(c*rq + 127/255, 0, 1) * 255).

@@ -18,16 +18,24 @@
 //     t = fma(D1, 1024, D0), one multiply by the folded quantiser scale, the denormal-FMA
 //     rounding + saturating pack of sdct_math.cuh, then the layout's store path.
 //
-// One CTA per SM, warp-specialised (416 threads), every role in its own loop over the CTA's tiles and
-// coupled only through mbarriers, so that no role ever waits for the whole load -> MMA -> store chain:
-//   warps 0-3   PRODUCER   pixels (cp.async into a 12-tile shared-memory ring, ~96 KiB of loads in flight
-//                          per SM) -> fp16 -> tcgen05.st into the stage's A columns; arrive on a_full[stage]
-//   warps 12-13 MMA        one thread each, alternate tiles: wait a_full / d_empty, 4 x tcgen05.mma,
-//                          tcgen05.commit onto d_full[stage] (which also tells the producer A is free)
-//   warps 4-11  CONSUMERS  two warpgroups taking alternate tiles: wait d_full, tcgen05.ld, quantise,
-//                          store (layout A: straight from registers; B, C: through a double-buffered
-//                          shared-memory image), arrive on d_empty[stage]
-// TMEM: 3 stages x (128 D columns + 32 A columns) = 480 of 512 columns.
+// forward_tc_kernel: one CTA per SM, warp-specialised (128 * (1 + CONSUMER_WGS + 1) = 512 threads), every role in its own loop
+// over the CTA's tiles and coupled only through mbarriers, so that no role ever waits for the whole load -> MMA -> store chain:
+//   warpgroup 0     PRODUCER   pixels (TMA boxes or cp.async into a shared-memory ring) -> fp16 -> tcgen05.st into the
+//                              stage's A columns; arrive on a_full[stage]
+//   warpgroups 1-2  CONSUMERS  alternate tiles: wait d_full, tcgen05.ld, quantise, store (layout A: straight from
+//                              registers; B, C: through a double-buffered shared-memory image), arrive on d_empty
+//   warpgroup 3     MMA + TMA  two MMA warps, one thread each, alternate tiles: wait a_full / d_empty, 4 x tcgen05.mma,
+//                              tcgen05.commit onto d_full (which also tells the producer A is free); one TMA thread
+// TMEM: 3 D stages x 128 columns + 4 A stages x 32 columns = 512 columns.  Every mbarrier has exactly ONE waiter that sees
+// every phase in order (a parity wait cannot tell phase u from u - 2): the D barriers are indexed k % D_PERIOD (6).
+//
+// inverse_tc_kernel: the same roles the other way round - the producer turns raw coefficient bytes (one bulk copy / one 4-D
+// tensor-map box per tile) into the A operand, B is the LUT-dependent dequantising operand (sdct_tc_matrix.cpp), the consumers
+// write pixels (chunk form, inv_consumer_chunks; CF = 3: through a planar image that tc_flush_rgb interleaves).
+//
+// roundtrip_tc_kernel: both products in one kernel, five warpgroups (2 front, 2 consumers, MMA1 / MMA2 / TMA threads), A1 / A2 in
+// shared memory, D1 / D2 double-buffered in TMEM (4 x 128 columns), the levels never leave the SM; row-form pixel epilogue
+// (inv_consumer_rows).  DESIGN.md section 4b has the measurements behind each of these choices.
 #include "sdct_io.cuh"
 
 #include <atomic>

@@ -3,12 +3,12 @@
 mkdir -p gpurun_out
 N=${N:-8}
 rm -f gpurun_out/copy_ceiling.json
-for g in 1 2 4 $N; do
+[ -n "$SKIP_PROBE" ] || for g in 1 2 4 $N; do
   [ $g -le $N ] || continue
   echo "== probe gpus=$g"; timeout 300 python tools/pcie_probe.py --gpus $g --out gpurun_out/copy_ceiling.json 2>&1 | tail -3
 done
-echo "== probe gpus=$N affinity"; timeout 300 python tools/pcie_probe.py --gpus $N --affinity --out gpurun_out/copy_ceiling.json 2>&1 | tail -3
-echo "== probe gpus=$N chunk 16 MB"; timeout 300 python tools/pcie_probe.py --gpus $N --chunk-mb 16 --out gpurun_out/copy_ceiling.json 2>&1 | tail -3
+[ -n "$SKIP_PROBE" ] || { echo "== probe gpus=$N affinity"; timeout 300 python tools/pcie_probe.py --gpus $N --affinity --out gpurun_out/copy_ceiling.json 2>&1 | tail -3
+echo "== probe gpus=$N chunk 16 MB"; timeout 300 python tools/pcie_probe.py --gpus $N --chunk-mb 16 --out gpurun_out/copy_ceiling.json 2>&1 | tail -3; }
 nvidia-smi topo -m > gpurun_out/topo.txt 2>&1
 for g in 2 4 $N; do
   [ $g -le $N ] || continue
