@@ -94,7 +94,7 @@ void sdct_job_dense(sdct_job *job, int layout, int flags, int components, int ey
 
 /* context = one device + its streams, staging buffers and launch counters
  * (replaces the caller-side _DetectCPUFeatures() contract, src/simd_platform.h:131).  The $SDCT_* environment
- * switches (SDCT_HOST_CHUNK_MB, SDCT_HOST_SLOTS, SDCT_HOST_NO_RAMP, SDCT_TC_NO_TMA, ...) are read here, once. */
+ * switches (SDCT_HOST_CHUNK_MB, SDCT_HOST_SLOTS, SDCT_HOST_NO_RAMP, SDCT_HOST_ENGINE_STREAMS, SDCT_TC_NO_TMA, ...) are read here, once. */
 int sdct_create(int device, sdct_context **out);
 void sdct_destroy(sdct_context *ctx);
 const char *sdct_last_error(void);
@@ -140,8 +140,9 @@ typedef struct sdct_plane_stat {
 int sdct_plane_stats_device(sdct_context *ctx, const sdct_job *job, const void *d_coefs, sdct_plane_stat *d_stats, void *stream);
 
 /* host-buffer operations: chunked H2D -> kernel -> D2H pipeline ($SDCT_HOST_SLOTS chunks in flight, default 4, each a
- * dense 16-byte-aligned sub-job on the device); pinned caller memory is DMA'd directly, pageable memory goes through
- * pinned staging.  Only the bytes of the job's window are written - row padding and unprocessed bands stay untouched.
+ * dense 16-byte-aligned sub-job on the device); pinned caller memory is DMA'd directly (one stream per engine: uploads,
+ * kernels and downloads each in their own queue, ordered by events; $SDCT_HOST_ENGINE_STREAMS=0 selects one stream per
+ * slot), pageable memory goes through pinned staging.  Only the bytes of the job's window are written - row padding and unprocessed bands stay untouched.
  * Thread-safe: concurrent calls on one context (e.g. disjoint band windows of one image, the reference's threading
  * model, src/simd_dct.cpp:1073-1087) run on separate pipelines and overlap. */
 int sdct_forward_host(sdct_context *ctx, const sdct_job *job, const void *h_pixels, const float *lut,

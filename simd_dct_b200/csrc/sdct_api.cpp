@@ -112,6 +112,7 @@ void read_env(SdctEnv *e)
     e->host_slots = (int)num("SDCT_HOST_SLOTS", 1, kSlots, 4);
     e->host_no_ramp = getenv("SDCT_HOST_NO_RAMP") != nullptr;
     e->host_trace = getenv("SDCT_HOST_TRACE") != nullptr;
+    e->host_engine_streams = num("SDCT_HOST_ENGINE_STREAMS", 0, 1, 1) != 0;
     e->tc.no_tma = getenv("SDCT_TC_NO_TMA") != nullptr;
     e->tc.no_rgb_fuse = getenv("SDCT_TC_NO_RGB_FUSE") != nullptr;
     e->tc.no_tma_store = getenv("SDCT_TC_NO_TMA_STORE") != nullptr;

@@ -45,7 +45,8 @@ constexpr int kSlots = 8;  // slots of one host pipeline; the depth in use is Sd
 // pinned staging buffers used when the caller's memory is pageable
 struct Slot {
     cudaStream_t stream = nullptr;
-    cudaEvent_t done = nullptr;
+    cudaEvent_t done = nullptr;                    // the slot's chunk has left the device (its download is complete)
+    cudaEvent_t ev_in = nullptr, ev_k = nullptr;   // engine-stream mode: upload complete, kernel complete
     uint8_t *d_pix = nullptr, *d_coef = nullptr;
     size_t d_pix_cap = 0, d_coef_cap = 0;
     uint8_t *h_in = nullptr, *h_out = nullptr;
@@ -64,6 +65,7 @@ struct SdctEnv {
     uint64_t host_chunk_bytes = 16ull << 20;
     int host_slots = 4;
     bool host_no_ramp = false;
+    bool host_engine_streams = true;    // $SDCT_HOST_ENGINE_STREAMS=0: one stream per slot instead of one per engine (sdct_host.cpp)
     bool host_trace = false;   // $SDCT_HOST_TRACE: per-chunk timeline of a host call on stderr (profiling)
     SdctTcOptions tc;
 };

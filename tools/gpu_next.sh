@@ -1,11 +1,9 @@
 #!/bin/bash
-# round-2 follow-up pass (one GPU): role stamps of the three tensor-core kernels (trace build), host pipeline timeline + knob sweep
 mkdir -p gpurun_out
-T=$PWD/simd_dct_b200/variants/libsdct_trace.so
-if [ -f $T ]; then
-  for spec in "B roundtrip" "B inverse" "B" "C"; do
-    SDCT_LIB=$T timeout 120 python tools/tc_trace.py 0 $spec
-  done > gpurun_out/tc_traces.txt 2>&1
-  tail -30 gpurun_out/tc_traces.txt
-fi
-bash tools/gpu_e2e.sh
+for v in "" deep ring8; do
+  lib=$PWD/simd_dct_b200/libsdct.so; [ -n "$v" ] && lib=$PWD/simd_dct_b200/variants/libsdct_$v.so
+  echo "== ${v:-product}"
+  SDCT_LIB=$lib timeout 300 python tools/prof_run.py --reps 20 fwd_A_tensor fwd_B_tensor fwd_C_tensor inv_A_tensor inv_B_tensor inv_C_tensor rt_B_tensor 2>&1 | tail -7
+  SDCT_LIB=$lib timeout 300 python tools/prof_run.py --frames 16 --w 3840 --h 2160 --reps 10 rgb_A_tensor rgb_B_tensor rgb_C_tensor rgb_B_tensor_ycc 2>&1 | tail -4
+done | tee gpurun_out/deep.txt
+SDCT_LIB=$PWD/simd_dct_b200/variants/libsdct_deep.so timeout 900 python -m pytest tests/test_gpu_parity.py tests/test_gpu_mismatch_rates.py tests/test_color.py -x -q -m gpu -k "tensor or color or mismatch" 2>&1 | tail -4
