@@ -97,13 +97,30 @@ constexpr int IMG_B_PITCH = 576;            // 512 B group + 64 B pad: the two g
 constexpr int IMG_C_PITCH = TILE + 16;      // plane row of 128 bytes + pad
 constexpr int IMG_BYTES = 64 * IMG_C_PITCH > 16 * IMG_B_PITCH ? 64 * IMG_C_PITCH : 16 * IMG_B_PITCH;
 
-constexpr int SMEM_B_OFF = 0;
-constexpr int SMEM_IMG_OFF = B_BYTES;
+// Shared-memory plan: the barriers (+ TMEM base address, TMA ring meta words) in the first KiB, then the B operand; what
+// follows is each kernel's own (forward: staging images, pixel ring; inverse: A stages, coefficient ring, RGB pixel images;
+// fused round trip: second operand, pixel ring, A1 / A2 stages), so that one kernel's ring depth costs the others nothing.
+constexpr int SMEM_BAR_OFF = 0, SMEM_BAR_REGION = 1024;
+constexpr int SMEM_B_OFF = SMEM_BAR_REGION;
+constexpr int SMEM_IMG_OFF = SMEM_B_OFF + B_BYTES;
 // pixel ring of the producer: cp.async lands the raw bytes of RING tiles ahead (8 rows x 128 threads x 8 B each)
 constexpr int RING = 12 / PRODUCER_WGS;      // tiles in flight per producer warpgroup
 constexpr int RING_TILE_BYTES = 8 * TILE * 8;
 constexpr int SMEM_RING_OFF = SMEM_IMG_OFF + CONSUMER_WGS * 2 * IMG_BYTES;
-constexpr int SMEM_BAR_OFF = SMEM_RING_OFF + PRODUCER_WGS * RING * RING_TILE_BYTES;
+// copy-engine ring depths = tiles in flight per SM.  Forward (TMA boxes of pixels, 16 KiB of shared memory per slot) and
+// inverse (one bulk copy / box of 8-9 KiB per slot): 8 - measured against 6 on 64 x 1080p: forward A 50.1 -> 48.2 us, inverse A
+// 58.6 -> 56.2 us, layouts B / C (consumer-bound) unchanged; 10: no further gain.  The fused round trip and the three-component
+// inverse keep 6 (their A stages / pixel images need the space).
+#ifndef SDCT_TC_TMA_RING
+#define SDCT_TC_TMA_RING 8
+#endif
+#ifndef SDCT_TC_INV_RING
+#define SDCT_TC_INV_RING 8
+#endif
+constexpr int TMA_RING = SDCT_TC_TMA_RING, RT_RING = 6;
+template <int CF> __host__ __device__ constexpr int inv_ring() { return CF == 1 ? SDCT_TC_INV_RING : 6; }
+constexpr int cmax(int a, int b) { return a > b ? a : b; }
+constexpr int RING_BARS = cmax(cmax(TMA_RING, RT_RING), cmax(inv_ring<1>(), inv_ring<3>()));
 // barriers (8 B each), then the TMEM base address.  mbarrier waits tell phases apart by parity only, so every
 // barrier has ONE waiting agent that visits its phases in order (a waiter that skipped a phase could mistake
 // "phase u - 2 complete" for "phase u complete"):
@@ -132,18 +149,20 @@ constexpr uint32_t RT_A_LBO = 144, RT_A_SBO = 8 * RT_A_LBO;
 constexpr int RT_A_STAGE_BYTES = 16 * 8 * 144;   // 128 block rows x 64 fp16, padded
 constexpr int BAR_PRODUCER = 8, BAR_FLUSH = 9;    // named barriers (ids 1 .. CONSUMER_WGS: the consumer warpgroups' own)
 //   ring_full[j % 6]        TMA (complete_tx) -> producer warpgroup; ring_empty[j % 6]: its four warps -> TMA thread
-constexpr int TMA_RING = 6;                       // slots of two 8 KiB boxes: 8 rows x 1024 bytes of this / of the next block row
+// TMA ring slots hold two 8 KiB boxes: 8 rows x 1024 bytes of this / of the next block row
 constexpr int TMA_BOX_BYTES = 8 * TILE * 8, TMA_SLOT_BYTES = 2 * TMA_BOX_BYTES;
-constexpr int BAR_RING_FULL = BAR_D_EMPTY + CONSUMER_WGS * D_STAGES, BAR_RING_EMPTY = BAR_RING_FULL + TMA_RING;
-constexpr int NUM_BARS = BAR_RING_EMPTY + TMA_RING;
-static_assert(TMA_RING * TMA_SLOT_BYTES <= PRODUCER_WGS * RING * RING_TILE_BYTES, "the TMA ring lives in the cp.async ring's space");
-static_assert(RGB_RING * 8 * RGB_ROW_BYTES <= PRODUCER_WGS * RING * RING_TILE_BYTES, "... and so does the RGB ring");
+constexpr int BAR_RING_FULL = BAR_D_EMPTY + CONSUMER_WGS * D_STAGES, BAR_RING_EMPTY = BAR_RING_FULL + RING_BARS;
+constexpr int NUM_BARS = BAR_RING_EMPTY + RING_BARS;
 constexpr int SMEM_META_OFF = SMEM_BAR_OFF + NUM_BARS * 8 + 16;   // TMA ring: blocks of the tile that lie in the first box
-constexpr int SMEM_USED = SMEM_META_OFF + TMA_RING * 4;
+static_assert(SMEM_META_OFF + RING_BARS * 4 <= SMEM_BAR_REGION, "barrier region");
+// forward kernel: the cp.async ring, the TMA ring and the RGB ring share one region
+constexpr int FWD_RING_REGION = cmax(cmax(PRODUCER_WGS * RING * RING_TILE_BYTES, TMA_RING * TMA_SLOT_BYTES), RGB_RING * 8 * RGB_ROW_BYTES);
+constexpr int SMEM_USED = SMEM_RING_OFF + FWD_RING_REGION;
 // more than half of the SM's shared memory: exactly one CTA per SM (it allocates all of TMEM)
-constexpr int SMEM_BYTES = SMEM_USED > 120 * 1024 ? SMEM_USED : 120 * 1024;
+constexpr int SMEM_BYTES = SMEM_USED > 120 * 1024 ? SMEM_USED : 120 * 1024;   // (the one-component inverse fits inside, asserted below)
+static_assert(SMEM_BYTES <= 227 * 1024, "shared memory of the forward kernel");
 // fused round trip: A1[2] and A2[2] behind everything else
-constexpr int SMEM_RT_A_OFF = (SMEM_USED + 127) & ~127, SMEM_RT_BYTES = SMEM_RT_A_OFF + 4 * RT_A_STAGE_BYTES;
+constexpr int SMEM_RT_A_OFF = (SMEM_RING_OFF + RT_RING * TMA_SLOT_BYTES + 127) & ~127, SMEM_RT_BYTES = SMEM_RT_A_OFF + 4 * RT_A_STAGE_BYTES;
 static_assert(SMEM_RT_BYTES <= 227 * 1024, "shared memory of the fused round trip");
 
 // profiling builds only (-DSDCT_TC_TRACE=1; $SDCT_TC_ABLATE then selects ablations, bit 5 = clock64 stamps of
@@ -588,7 +607,7 @@ SDCT_DEV void producer_role(const KParams &p, uint64_t *bars, uint32_t tmem_base
         uint32_t tile = blockIdx.x;
         for (uint32_t k = 0;; k++, tile += gridDim.x) {
             if (tile >= p.tiles) return;
-            const uint32_t rs = k % TMA_RING, ru = k / TMA_RING;
+            const uint32_t rs = k % TMA_RING, ru = k / TMA_RING;   // (forward kernel: TMA_RING slots)
             mbar_wait(bars + BAR_RING_FULL + rs, ru & 1);
             const uint32_t split = meta[rs];
             const uint8_t *src = ring + rs * TMA_SLOT_BYTES + (my_slot < split ? my_slot * 8 : TMA_BOX_BYTES + (my_slot - split) * 8);
@@ -687,7 +706,8 @@ SDCT_DEV void producer_role(const KParams &p, uint64_t *bars, uint32_t tmem_base
     }
 }
 
-// one thread: the bulk tensor copies of the CTA's tiles, TMA_RING tiles ahead of the producer warpgroup
+// one thread: the bulk tensor copies of the CTA's tiles, RINGN tiles ahead of the producer warpgroup
+template <int RINGN>
 SDCT_DEV void tma_role(const KParams &p, uint64_t *bars, uint8_t *ring, uint32_t *meta)
 {
     const void *map = p.tc_tensor_map;
@@ -695,7 +715,7 @@ SDCT_DEV void tma_role(const KParams &p, uint64_t *bars, uint8_t *ring, uint32_t
     w.init(p, 0, 1);
     const uint32_t blocks = p.rows * p.bpr;
     for (uint32_t k = 0; w.tile < p.tiles; k++, w.next(p)) {
-        const uint32_t rs = k % TMA_RING, ru = k / TMA_RING;
+        const uint32_t rs = k % RINGN, ru = k / RINGN;
         const uint32_t n0 = w.chunk * TILE, count = min((uint32_t)TILE, blocks - n0);
         const uint32_t r = fastdiv(n0, p.div_bpr), bx0 = n0 - r * p.bpr;
         const uint32_t split = min((uint32_t)TILE, p.bpr - bx0);
@@ -914,7 +934,7 @@ __global__ void __launch_bounds__(THREADS, 1) forward_tc_kernel(const __grid_con
         if (warp < MMA_WARP + MMA_WARPS && lane == 0)
             mma_role<CF>(p, bars, tmem_base, b_descriptor(smem_u32(smem + SMEM_B_OFF)), warp - MMA_WARP);
         else if (VEC == VEC_TMA && warp == TMA_WARP && lane == 0)
-            tma_role(p, bars, smem + SMEM_RING_OFF, reinterpret_cast<uint32_t *>(smem + SMEM_META_OFF));
+            tma_role<TMA_RING>(p, bars, smem + SMEM_RING_OFF, reinterpret_cast<uint32_t *>(smem + SMEM_META_OFF));
     }
     fence_before();
     __syncthreads();
@@ -944,9 +964,9 @@ constexpr int INV_A_STAGE_BYTES = 16 * 8 * 144;           // 18 KiB (layout A's 
 // geometry fits a tensor map (CT), else the producer's own cp.async copies.  (64 small bulk copies measured 256 us
 // against 74 us for cp.async: the copy engine is per-operation bound at that size.)
 template <int LAYOUT, bool CT> __host__ __device__ constexpr bool inv_bulk() { return LAYOUT != SDCT_K_LAYOUT_C || CT; }
-constexpr int INV_RING = 6, INV_RAW_MAX = 64 * 144;       // raw coefficient bytes of a tile (layout C: padded plane rows): at most 9 KiB
-constexpr int SMEM_INV_A_OFF = B_BYTES, SMEM_INV_RING_OFF = SMEM_INV_A_OFF + A_STAGES * INV_A_STAGE_BYTES;
-static_assert(SMEM_INV_RING_OFF + INV_RING * INV_RAW_MAX <= SMEM_BAR_OFF, "inverse shared-memory plan");
+constexpr int INV_RAW_MAX = 64 * 144;       // raw coefficient bytes of a tile (layout C: padded plane rows): at most 9 KiB
+constexpr int SMEM_INV_A_OFF = SMEM_B_OFF + B_BYTES, SMEM_INV_RING_OFF = SMEM_INV_A_OFF + A_STAGES * INV_A_STAGE_BYTES;
+static_assert(SMEM_INV_RING_OFF + inv_ring<1>() * INV_RAW_MAX <= SMEM_BYTES, "inverse shared-memory plan");
 
 // raw ring slot: the tile's coefficient bytes with a row pitch that makes the expansion's 16-byte reads
 // conflict-free (A: 128 block rows of 64 B + 16; C: 64 plane rows of 128 B + 16; B: the 8 KiB image as it is)
@@ -961,7 +981,7 @@ template <int LAYOUT, bool CT> __host__ __device__ constexpr int inv_raw_bytes()
 // (row pitch + 16: the 8-byte stores of a warp's four pixel rows fall on different banks), two images (pixel tile j uses
 // image j % 2), placed behind the barriers
 constexpr int PIX_PITCH = TILE * 8 + 16, PIX_COMP = 8 * PIX_PITCH, PIX_IMG3 = 3 * PIX_COMP;
-constexpr int SMEM_INV_PIX_OFF = (SMEM_USED + 15) & ~15;
+constexpr int SMEM_INV_PIX_OFF = (SMEM_INV_RING_OFF + inv_ring<3>() * INV_RAW_MAX + 15) & ~15;
 constexpr int SMEM_INV_RGB_BYTES = SMEM_INV_PIX_OFF + 2 * PIX_IMG3;
 static_assert(SMEM_INV_RGB_BYTES <= 227 * 1024, "shared memory of the three-component inverse");
 
@@ -982,7 +1002,7 @@ SDCT_DEV void inv_bulk_role(const KParams &p, uint64_t *bars, uint8_t *ring)
     w.init(p, 0, 1);
     uint32_t comp = 0;
     for (uint32_t k = 0; w.tile < p.tiles; k++) {
-        const uint32_t rs = k % INV_RING, ru = k / INV_RING;
+        const uint32_t rs = k % inv_ring<CF>(), ru = k / inv_ring<CF>();
         Tile t = tile_at<1, TILE>(p, w);
         t.coef += (uint64_t)comp * p.coef_comp_stride;
         const uint32_t this_comp = comp, frame = w.fc;
@@ -1037,14 +1057,14 @@ SDCT_DEV void inv_producer_role(const KParams &p, uint64_t *bars, uint8_t *a_sta
     // layout B: lanes 4..7 of every 8 store the second half first, so that the eight 16-byte stores of a phase
     // cover 128 contiguous bytes' worth of banks
     const uint32_t swap = OWN ? (L >> 2) & 1u : 0u;   // (OWN: the natural piece order, whoever copied the pieces)
-    constexpr int AHEAD = OWN ? INV_RING : INV_RING - 1;   // tiles whose copies are in flight
+    constexpr int AHEAD = OWN ? inv_ring<CF>() : inv_ring<CF>() - 1;   // tiles whose copies are in flight
     TileWalk wi;
     wi.init(p, 0, 1);
     auto issue = [&](uint32_t j) {
         if (wi.tile < p.tiles) {
             const Tile t = tile_at<1, TILE>(p, wi);
             const uint64_t n_first = (uint64_t)p.row0 * p.bpr + t.n0;
-            uint8_t *slot = ring + (j % INV_RING) * RAW;
+            uint8_t *slot = ring + (j % inv_ring<CF>()) * RAW;
 #pragma unroll
             for (int m = 0; m < 4; m++) {
                 const uint32_t c = L + 128u * m;
@@ -1066,7 +1086,7 @@ SDCT_DEV void inv_producer_role(const KParams &p, uint64_t *bars, uint8_t *a_sta
         const bool tr = (ablate_bits(p) & 32) && blockIdx.x == 0 && L == 0;
         stamp(tr, 0, k, 0);
         if (BULK) {
-            mbar_wait(bars + BAR_RING_FULL + k % INV_RING, (k / INV_RING) & 1);   // the TMA thread's bulk copy has landed
+            mbar_wait(bars + BAR_RING_FULL + k % inv_ring<CF>(), (k / inv_ring<CF>()) & 1);   // the TMA thread's bulk copy has landed
         } else {
             cp_async_wait<AHEAD - 1>();   // this thread's pieces of tile k have landed
             if (!OWN) {
@@ -1074,7 +1094,7 @@ SDCT_DEV void inv_producer_role(const KParams &p, uint64_t *bars, uint8_t *a_sta
                 issue(k + AHEAD);         // into the slot of tile k - 1
             }
         }
-        const uint8_t *slot = ring + (k % INV_RING) * RAW;
+        const uint8_t *slot = ring + (k % inv_ring<CF>()) * RAW;
         const uint32_t sa = k % A_STAGES, ua = k / A_STAGES;
         uint4 raw[4];
 #pragma unroll
@@ -1108,7 +1128,7 @@ SDCT_DEV void inv_producer_role(const KParams &p, uint64_t *bars, uint8_t *a_sta
         stamp(tr, 0, k, 3);
         if (BULK) {
             __syncwarp();
-            if ((L & 31) == 0) mbar_arrive(bars + BAR_RING_EMPTY + k % INV_RING);   // this warp has read the slot
+            if ((L & 31) == 0) mbar_arrive(bars + BAR_RING_EMPTY + k % inv_ring<CF>());   // this warp has read the slot
         } else if (OWN) {
             issue(k + AHEAD);
         }
@@ -1474,7 +1494,7 @@ __global__ void __launch_bounds__(THREADS, 1) inverse_tc_kernel(const __grid_con
             mbar_init(bars + BAR_D_FULL + i, 1);
             mbar_init(bars + BAR_D_EMPTY + i, 128);
         }
-        for (int i = 0; i < INV_RING; i++) {
+        for (int i = 0; i < inv_ring<CF>(); i++) {
             mbar_init(bars + BAR_RING_FULL + i, 1);
             mbar_init(bars + BAR_RING_EMPTY + i, 4);
         }
@@ -1487,7 +1507,7 @@ __global__ void __launch_bounds__(THREADS, 1) inverse_tc_kernel(const __grid_con
     fence_after();
     const uint32_t tmem_base = *tmem_slot;
     const uint32_t lane_field = ((warp & 3u) * 32u) << 16;
-    static_assert(PRODUCER_WGS == 1 && INV_RING <= TMA_RING, "the inverse kernel has one producer warpgroup and reuses the ring barriers");
+    static_assert(PRODUCER_WGS == 1 && inv_ring<CF>() <= RING_BARS, "the inverse kernel has one producer warpgroup and reuses the ring barriers");
     if (warp < CONSUMER_WARP) {
         if (MOVE_REGS) asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(PRODUCER_REGS));
         inv_producer_role<LAYOUT, CT, CF>(p, bars, smem + SMEM_INV_A_OFF, smem + SMEM_INV_RING_OFF, threadIdx.x);
@@ -1564,7 +1584,7 @@ SDCT_DEV void rt_front_role(const KParams &p, uint64_t *bars, uint32_t tmem_base
     uint8_t *a1_row = rt_a_row(a1 + wg * RT_A_STAGE_BYTES, L), *a2_row = rt_a_row(a2 + wg * RT_A_STAGE_BYTES, L);
     const bool tr = (ablate_bits(p) & 32) && blockIdx.x == 0 && L == 0 && wg == 0;
     auto produce = [&](uint32_t k) {
-        const uint32_t rs = k % TMA_RING, ru = k / TMA_RING, ua = k >> 1;
+        const uint32_t rs = k % RT_RING, ru = k / RT_RING, ua = k >> 1;
         stamp(tr, 0, k, 0);
         mbar_wait(bars + BAR_RING_FULL + rs, ru & 1);
         stamp(tr, 0, k, 1);
@@ -1693,7 +1713,7 @@ __global__ void __launch_bounds__(RT_THREADS, 1) roundtrip_tc_kernel(const __gri
             mbar_init(bars + RT_BAR_D2_FULL + i, 1); mbar_init(bars + RT_BAR_D2_EMPTY + i, 128);
             mbar_init(bars + RT_BAR_D1_FULL + i, 1); mbar_init(bars + RT_BAR_D1_EMPTY + i, 128);
         }
-        for (int i = 0; i < TMA_RING; i++) {
+        for (int i = 0; i < RT_RING; i++) {
             mbar_init(bars + BAR_RING_FULL + i, 1);
             mbar_init(bars + BAR_RING_EMPTY + i, 4);
         }
@@ -1719,7 +1739,7 @@ __global__ void __launch_bounds__(RT_THREADS, 1) roundtrip_tc_kernel(const __gri
             rt_mma_role(p, bars, tmem_base, smem_u32(smem + SMEM_RT_A_OFF), smem_u32(smem + SMEM_RT_A_OFF + 2 * RT_A_STAGE_BYTES),
                         b_descriptor(smem_u32(smem + SMEM_B_OFF)), b_descriptor(smem_u32(smem + SMEM_B_OFF + B_BYTES)), warp - 16);
         else if (warp == 18 && lane == 0)
-            tma_role(p, bars, smem + SMEM_RING_OFF, reinterpret_cast<uint32_t *>(smem + SMEM_META_OFF));
+            tma_role<RT_RING>(p, bars, smem + SMEM_RING_OFF, reinterpret_cast<uint32_t *>(smem + SMEM_META_OFF));
     }
     fence_before();
     __syncthreads();
