@@ -778,6 +778,16 @@ SDCT_DEV void consumer_role(const KParams &p, uint64_t *bars, uint32_t tmem_base
     for (int k = 0; k < 8; k++) scale[k] = make_float2(p.tab[8 * k + 2 * q].x, p.tab[8 * k + 2 * q + 1].x);
     // blocks P, Q of this thread: slots sp0 (+1) in the first 16-lane half, sp0 + 16 (+1) in the second
     const uint32_t sp0 = (L >> 5) * 32u + 2u * g;
+    // this thread's part of the staging-image addresses (the rest are immediates, see the chunk macro):
+    //   layout B image: group (sp >> 3) at IMG_B_PITCH, byte i * 8 + (sp & 7);   layout C image: plane row i at IMG_C_PITCH, byte sp;
+    //   layout C, tensor-map store (CS): plane row i of 128 bytes, 16-byte piece (sp >> 4) ^ (i & 7) (the 128-byte swizzle), byte sp & 15
+    const uint32_t off_b = (sp0 >> 3) * IMG_B_PITCH + (sp0 & 7u) + q * 16u;
+    const uint32_t off_c = 2u * q * IMG_C_PITCH + sp0;
+    uint32_t off_cs[2][2];
+#pragma unroll
+    for (int half = 0; half < 2; half++)
+#pragma unroll
+        for (int e = 0; e < 2; e++) off_cs[half][e] = (e + 2u * q) * 128u + (((((sp0 >> 4) + half) ^ (e + 2u * q)) & 7u) << 4) + (sp0 & 15u);
     const uint32_t abl = ablate_bits(p);
     // CF == 1: wk walks this warpgroup's tiles.  CF == 3: wk walks the CTA's pixel tiles, comp = k % 3.
     static_assert(CF == 1 || CF == 3, "fused components");
@@ -833,14 +843,15 @@ SDCT_DEV void consumer_role(const KParams &p, uint64_t *bars, uint32_t tmem_base
                 wq[2 * kk + 1] = pack4_sat(bq[2].x, bq[2].y, bq[3].x, bq[3].y);                                       \
                 if (kk == 1) store_a(p, cur, n_first, sp, q, wp, wq);                                                 \
             } else {                                                                                                  \
+                /* coefficient i = 8 m + e + 2 q (m = 4 kk + k2) of blocks sp, sp + 1 (sp = sp0 + 16 half): everything but the      */ \
+                /* thread's own offset is a compile-time constant, so every store is [register + immediate]                      */ \
                 _Pragma("unroll") for (int k2 = 0; k2 < 4; k2++) {                                                    \
                     _Pragma("unroll") for (int e = 0; e < 2; e++) {                                                   \
-                        const uint32_t i = 8 * (4 * kk + k2) + e + 2 * q;                                             \
+                        const int m = 4 * kk + k2;                                                                    \
                         const uint32_t pq = pack_sat(__float_as_uint(e ? bq[k2].y : bq[k2].x), __float_as_uint(e ? bp[k2].y : bp[k2].x), 0u); \
                         uint8_t *d = LAYOUT == SDCT_K_LAYOUT_B                                                         \
-                                         ? ((DIRECT) ? gdst + (sp >> 3) * 512 : img + (sp >> 3) * IMG_B_PITCH) + i * 8 + (sp & 7) \
-                                         : (CS ? img + i * 128u + ((((sp >> 4) ^ i) & 7u) << 4) + (sp & 15u)           \
-                                               : img + i * IMG_C_PITCH + sp);                                         \
+                                         ? ((DIRECT) ? bdir + (half * 1024 + (8 * m + e) * 8) : img + off_b + (half * 2 * IMG_B_PITCH + (8 * m + e) * 8)) \
+                                         : (CS ? img + off_cs[half][e] + m * 1024 : img + off_c + ((8 * m + e) * IMG_C_PITCH + 16 * half)); \
                         *reinterpret_cast<uint16_t *>(d) = (uint16_t)pq;                                              \
                     }                                                                                                 \
                 }                                                                                                     \
@@ -851,6 +862,7 @@ SDCT_DEV void consumer_role(const KParams &p, uint64_t *bars, uint32_t tmem_base
         // image, no warpgroup barrier, no flush
         // (layout C keeps the staging image: its byte pairs would scatter over 64 planes, measured 7 % slower)
         uint8_t *gdst = cur.coef + n_first * 64;
+        uint8_t *bdir = gdst + ((sp0 >> 3) * 512u + (sp0 & 7u) + q * 16u);
         const bool direct = DIRECT_B && LAYOUT == SDCT_K_LAYOUT_B && cur.count == TILE && p.coef_aligned4 && !(abl & 8);
         if (direct) {
             SDCT_TC_CHUNK(0, hiA, loA, hiB, loB, true)
