@@ -74,7 +74,10 @@ constexpr int MMA_WARP = 4 * (PRODUCER_WGS + CONSUMER_WGS);
 constexpr int TMA_WARP = MMA_WARP + MMA_WARPS;   // one thread: bulk tensor copies of the pixel tiles (VEC == VEC_TMA)
 constexpr int VEC_TMA = 3;
 constexpr int VEC_RGB = 4;                   // interleaved RGB, 16-byte-aligned rows: one pixel tile feeds the three components' tiles
-constexpr int RGB_RING = 4, RGB_ROW_BYTES = 24 * SDCT_TC_TILE;   // ring slots of 8 rows x 3072 bytes
+#ifndef SDCT_TC_RGB_RING
+#define SDCT_TC_RGB_RING 4
+#endif
+constexpr int RGB_RING = SDCT_TC_RGB_RING, RGB_ROW_BYTES = 24 * SDCT_TC_TILE;   // ring slots of 8 rows x 3072 bytes
 #ifndef SDCT_TC_DIRECT_B
 #define SDCT_TC_DIRECT_B 1
 #endif
@@ -109,16 +112,19 @@ constexpr int RING_TILE_BYTES = 8 * TILE * 8;
 constexpr int SMEM_RING_OFF = SMEM_IMG_OFF + CONSUMER_WGS * 2 * IMG_BYTES;
 // copy-engine ring depths = tiles in flight per SM.  Forward (TMA boxes of pixels, 16 KiB of shared memory per slot) and
 // inverse (one bulk copy / box of 8-9 KiB per slot): 8 - measured against 6 on 64 x 1080p: forward A 50.1 -> 48.2 us, inverse A
-// 58.6 -> 56.2 us, layouts B / C (consumer-bound) unchanged; 10: no further gain.  The fused round trip and the three-component
-// inverse keep 6 (their A stages / pixel images need the space).
+// 58.6 -> 56.2 us, layouts B / C (consumer-bound) unchanged; 10: no further gain.  The fused round trip has room for 7
+// (its ring starts right behind its second operand; the A1 / A2 stages take the rest).
 #ifndef SDCT_TC_TMA_RING
 #define SDCT_TC_TMA_RING 8
 #endif
 #ifndef SDCT_TC_INV_RING
 #define SDCT_TC_INV_RING 8
 #endif
-constexpr int TMA_RING = SDCT_TC_TMA_RING, RT_RING = 6;
-template <int CF> __host__ __device__ constexpr int inv_ring() { return CF == 1 ? SDCT_TC_INV_RING : 6; }
+#ifndef SDCT_TC_RT_RING
+#define SDCT_TC_RT_RING 7
+#endif
+constexpr int TMA_RING = SDCT_TC_TMA_RING, RT_RING = SDCT_TC_RT_RING;
+template <int CF> __host__ __device__ constexpr int inv_ring() { return SDCT_TC_INV_RING; }
 constexpr int cmax(int a, int b) { return a > b ? a : b; }
 constexpr int RING_BARS = cmax(cmax(TMA_RING, RT_RING), cmax(inv_ring<1>(), inv_ring<3>()));
 // barriers (8 B each), then the TMEM base address.  mbarrier waits tell phases apart by parity only, so every
@@ -162,7 +168,8 @@ constexpr int SMEM_USED = SMEM_RING_OFF + FWD_RING_REGION;
 constexpr int SMEM_BYTES = SMEM_USED > 120 * 1024 ? SMEM_USED : 120 * 1024;   // (the one-component inverse fits inside, asserted below)
 static_assert(SMEM_BYTES <= 227 * 1024, "shared memory of the forward kernel");
 // fused round trip: A1[2] and A2[2] behind everything else
-constexpr int SMEM_RT_A_OFF = (SMEM_RING_OFF + RT_RING * TMA_SLOT_BYTES + 127) & ~127, SMEM_RT_BYTES = SMEM_RT_A_OFF + 4 * RT_A_STAGE_BYTES;
+constexpr int SMEM_RT_RING_OFF = SMEM_IMG_OFF + B_BYTES;   // (the forward kernel's staging images are not needed here)
+constexpr int SMEM_RT_A_OFF = (SMEM_RT_RING_OFF + RT_RING * TMA_SLOT_BYTES + 127) & ~127, SMEM_RT_BYTES = SMEM_RT_A_OFF + 4 * RT_A_STAGE_BYTES;
 static_assert(SMEM_RT_BYTES <= 227 * 1024, "shared memory of the fused round trip");
 
 // profiling builds only (-DSDCT_TC_TRACE=1; $SDCT_TC_ABLATE then selects ablations, bit 5 = clock64 stamps of
@@ -1738,9 +1745,9 @@ __global__ void __launch_bounds__(RT_THREADS, 1) roundtrip_tc_kernel(const __gri
     fence_after();
     const uint32_t tmem_base = *tmem_slot;
     const uint32_t lane_field = ((warp & 3u) * 32u) << 16;
-    static_assert(SMEM_IMG_OFF == SMEM_B_OFF + B_BYTES && SMEM_RING_OFF >= SMEM_IMG_OFF + B_BYTES, "the second operand lives where the forward kernel keeps its staging images");
+    static_assert(SMEM_IMG_OFF == SMEM_B_OFF + B_BYTES && SMEM_RT_RING_OFF == SMEM_IMG_OFF + B_BYTES && SMEM_RT_RING_OFF % 1024 == 0, "second operand behind the first, the pixel ring behind both");
     if (warp < 8) {   // (the two front warpgroups keep the launch allocation of 96 registers)
-        rt_front_role(p, bars, tmem_base, smem + SMEM_RT_A_OFF, smem + SMEM_RT_A_OFF + 2 * RT_A_STAGE_BYTES, smem + SMEM_RING_OFF,
+        rt_front_role(p, bars, tmem_base, smem + SMEM_RT_A_OFF, smem + SMEM_RT_A_OFF + 2 * RT_A_STAGE_BYTES, smem + SMEM_RT_RING_OFF,
                       reinterpret_cast<const uint32_t *>(smem + SMEM_META_OFF), warp >> 2, threadIdx.x & 127, lane_field);
     } else if (warp < 16) {
         asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(RT_CONSUMER_REGS));
@@ -1751,7 +1758,7 @@ __global__ void __launch_bounds__(RT_THREADS, 1) roundtrip_tc_kernel(const __gri
             rt_mma_role(p, bars, tmem_base, smem_u32(smem + SMEM_RT_A_OFF), smem_u32(smem + SMEM_RT_A_OFF + 2 * RT_A_STAGE_BYTES),
                         b_descriptor(smem_u32(smem + SMEM_B_OFF)), b_descriptor(smem_u32(smem + SMEM_B_OFF + B_BYTES)), warp - 16);
         else if (warp == 18 && lane == 0)
-            tma_role<RT_RING>(p, bars, smem + SMEM_RING_OFF, reinterpret_cast<uint32_t *>(smem + SMEM_META_OFF));
+            tma_role<RT_RING>(p, bars, smem + SMEM_RT_RING_OFF, reinterpret_cast<uint32_t *>(smem + SMEM_META_OFF));
     }
     fence_before();
     __syncthreads();
