@@ -4,13 +4,16 @@ the dominant stall reason of each, and totals per stall reason.   tools/ncu_hot.
 import csv, sys
 rows = list(csv.reader(open(sys.argv[1])))
 top = int(sys.argv[2]) if len(sys.argv) > 2 else 40
+# a report with several launches has one section per launch ("Kernel Name" row, header row, instructions): take the first
+starts = [i for i, r in enumerate(rows) if r and r[0] == "Kernel Name"]
+rows = rows[starts[0]:(starts[1] if len(starts) > 1 else len(rows))]
 hdr = rows[1]
 col = {h: i for i, h in enumerate(hdr)}
 stalls = [h for h in hdr if h.startswith("stall_") and "Not Issued" not in h]
 data = []
 tot = {s: 0 for s in stalls}
 for k, r in enumerate(rows[2:]):
-    if len(r) < len(hdr):
+    if len(r) < len(hdr) or not r[col["# Samples"]].strip().isdigit():
         continue
     n = int(r[col["# Samples"]] or 0)
     per = {s: int(r[col[s]] or 0) for s in stalls}
