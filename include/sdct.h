@@ -43,6 +43,9 @@ enum {
     SDCT_EXACT = 0,         /* the reference's fp32 operation order; byte-identical to its CPU output */
     SDCT_FAST = 1,          /* FMA-contracted arithmetic defined in oracle/sdct_oracle.c (<= 1 LSB from SDCT_EXACT) */
     SDCT_QUIRK_AVX_X3 = 2,  /* layout B: reproduce the reference's X3 sign (src/simd_dct.cpp:2181); see DESIGN.md */
+    SDCT_QUIRK_SSE = 16,    /* layout C: the bytes of the reference's SSE4.1 / SSSE3 / SSE2 stereo encoders (src/simd_dct.cpp:896-1103,
+                               what its dispatcher runs on every x86-64 CPU, :78-83) instead of its scalar path's: x * (1.f / 255),
+                               inplace_dct8_sse41 with its X1 sign (:788), cvtps_epi32(c * q + 127.f).  Forward and round trip, width % 16 == 0 */
     SDCT_COLOR_YCBCR = 8,   /* interleaved 3-component pixels: RGB -> YCbCr (JFIF / BT.601 full range, 8-bit fixed point, exact integer
                                arithmetic defined in oracle/sdct_oracle.c) fused into the forward load, YCbCr -> RGB into the inverse
                                store; the coefficient sets of a frame are then Y, Cb, Cr.  Combines with every arithmetic mode.

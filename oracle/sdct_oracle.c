@@ -66,6 +66,26 @@ void sdct_oracle_dct8_paired(float v[8], int quirk_x3)
     v[7] = K_N * ((K_F * d07 + K_D * d61) + (K_C * d25 + K_A * d43));
 }
 
+/* :672-892 (SSE4.1) == :434-654 (SSE2) lane arithmetic, one row of two adjacent blocks per call.  The sums, differences,
+ * even outputs and the pairwise summation of the odd outputs are those of the AVX2 form above (the sign flips the SSE code
+ * applies by XOR, :717-721, and its negative factors -C_c, -C_a, -C_b are exact negations, so a + (-b) = a - b bit for
+ * bit); what differs is the defect: X1 adds C_f * x43m where the DCT subtracts it (:762 "xf14 = (C_f * x34m)", :788). */
+void sdct_oracle_dct8_sse(float v[8])
+{
+    const float s07 = v[0] + v[7], s16 = v[1] + v[6], s25 = v[2] + v[5], s34 = v[3] + v[4];
+    const float d07 = v[0] - v[7], d61 = v[6] - v[1], d25 = v[2] - v[5], d43 = v[4] - v[3];
+    const float pp = s07 + s34, pm = s07 - s34, qq = s16 + s25, qm = s16 - s25;
+
+    v[0] = K_N * (pp + qq);
+    v[4] = K_N * (pp - qq);
+    v[2] = K_N * (K_B * pm + K_E * qm);
+    v[6] = K_N * (K_E * pm - K_B * qm);
+    v[1] = K_N * ((K_A * d07 - K_C * d61) + (K_D * d25 + K_F * d43));   /* the defect */
+    v[3] = K_N * ((K_C * d07 + K_F * d61) - (K_A * d25 - K_D * d43));
+    v[5] = K_N * ((K_D * d07 + K_A * d61) + (K_F * d25 - K_C * d43));
+    v[7] = K_N * ((K_F * d07 + K_D * d61) + (K_C * d25 + K_A * d43));
+}
+
 /* ---------------------------------------------------------------------------------------
  * This repo's own arithmetic definitions (no reference counterpart): the FMA-contracted
  * "fast" forward and the inverse.  Both are *defined* here and the CUDA kernels reproduce
@@ -207,6 +227,32 @@ static void block_fwd_c(const uint8_t *px, size_t pitch, const float rq[64], uin
     transpose8(b);
     for (int r = 0; r < 8; r++) sdct_oracle_dct8_scalar(b + r * 8);
     for (int i = 0; i < 64; i++) o[i] = quant_scalar(b[i], rq[i]);
+}
+
+/* layout C as the reference's SSE4.1 / SSSE3 / SSE2 stereo encoders compute it (:896-1103; quirk SDCT_O_QUIRK_SSE):
+ * x * (1.f / 255) instead of x / 255.f (:955-962), the transposes and passes of the scalar form with inplace_dct8_sse41
+ * (:964-1007), and the quantiser min(255, max(0, cvtps_epi32(c * (255 / (lut * .95)) + 127.f))) (:1018-1024): product and
+ * sum are rounded separately, the conversion rounds to nearest even, out-of-range and NaN convert to INT_MIN and clamp to 0 */
+static uint8_t quant_sse(float c, float q)
+{
+    const float p = c * q;
+    const float y = p + 127.0f;
+    if (!(y >= -2147483648.f && y < 2147483648.f)) return 0;
+    const long r = lrintf(y);
+    return (uint8_t)(r > 255 ? 255 : (r < 0 ? 0 : r));
+}
+
+static void block_fwd_c_sse(const uint8_t *px, size_t pitch, const float q[64], uint8_t o[64])
+{
+    const float inv255 = 1.f / (float)0xFF;
+    float b[64];
+    for (int r = 0; r < 8; r++)
+        for (int c = 0; c < 8; c++) b[r * 8 + c] = inv255 * (float)px[r * pitch + c];
+    transpose8(b);
+    for (int r = 0; r < 8; r++) sdct_oracle_dct8_sse(b + r * 8);
+    transpose8(b);
+    for (int r = 0; r < 8; r++) sdct_oracle_dct8_sse(b + r * 8);
+    for (int i = 0; i < 64; i++) o[i] = quant_sse(b[i], q[i]);
 }
 
 /* layout B, :2107-2228 : (float)x, horizontal pass, vertical pass, natural order */
@@ -355,15 +401,17 @@ static void forward_band(int layout, int mode, int quirks, const uint8_t *in, si
             else if (mode == SDCT_O_MODE_FAST) block_fwd_fast(tile, 8, tab, layout == SDCT_O_LAYOUT_A, o);
             else if (layout == SDCT_O_LAYOUT_A) block_fwd_a(tile, 8, tab, o);
             else if (layout == SDCT_O_LAYOUT_B) block_fwd_b(tile, 8, tab, quirks, o);
+            else if (quirks & SDCT_O_QUIRK_SSE) block_fwd_c_sse(tile, 8, tab, o);
             else block_fwd_c(tile, 8, tab, o);
             for (int i = 0; i < 64; i++) *coef_addr(layout, out, plane_stride, width, eyes, band, eye, bx, i) = o[i];
         }
 }
 
-static void forward_table(int layout, int mode, const float lut[64], float tab[64])
+static void forward_table(int layout, int mode, int quirks, const float lut[64], float tab[64])
 {
     const int which = mode == SDCT_O_MODE_TENSOR ? SDCT_O_TAB_TENSOR : mode == SDCT_O_MODE_FAST ? SDCT_O_TAB_FAST
-                    : layout == SDCT_O_LAYOUT_B ? SDCT_O_TAB_AVX : SDCT_O_TAB_SCALAR;
+                    : (layout == SDCT_O_LAYOUT_B || (layout == SDCT_O_LAYOUT_C && (quirks & SDCT_O_QUIRK_SSE))) ? SDCT_O_TAB_AVX
+                    : SDCT_O_TAB_SCALAR;   /* (the SSE encoders build the AVX path's 255 / (lut * .95), :908-923) */
     sdct_oracle_tables(lut, layout, tab, which);
 }
 
@@ -372,7 +420,7 @@ void sdct_oracle_forward(int layout, int mode, int quirks, const uint8_t *in, si
                          uint8_t *out, size_t plane_stride)
 {
     float tab[64];
-    forward_table(layout, mode, lut, tab);
+    forward_table(layout, mode, quirks, lut, tab);
     if (layout != SDCT_O_LAYOUT_C) eyes = 1;
     for (size_t band = 0; band < height / 8; band++)
         forward_band(layout, mode, quirks, in, pitch, xstep, width, band, eyes, eye_stride, tab, out, plane_stride);
@@ -542,7 +590,7 @@ int sdct_oracle_ref_encode_quantize_buffer(const uint8_t *from, uint8_t *to, con
     float tab[64];
     if (!from || !to) return 1;                               /* :97 */
     if ((size_x & 7) || (size_y & 7)) return 2;               /* :98 */
-    forward_table(SDCT_O_LAYOUT_A, SDCT_O_MODE_EXACT, lut, tab);
+    forward_table(SDCT_O_LAYOUT_A, SDCT_O_MODE_EXACT, 0, lut, tab);
     for (size_t y = 0; y < size_y / 2; y += 8) {
         if (y < start_y) continue;                            /* :377 - compares y, not 2y */
         if (y > end_y) break;                                 /* :384 */
@@ -558,7 +606,7 @@ int sdct_oracle_ref_encode_quantize32_reorder_buffer(const uint8_t *from, uint8_
     float tab[64];
     if (!from || !to) return 1;                               /* :117 */
     if ((size_x & 63) || (size_y & 7)) return 2;              /* :118 */
-    forward_table(SDCT_O_LAYOUT_B, SDCT_O_MODE_EXACT, lut, tab);
+    forward_table(SDCT_O_LAYOUT_B, SDCT_O_MODE_EXACT, quirks, lut, tab);
     for (size_t y = 0; y < size_y / 2; y += 8) {
         if (y * 2 < start_y) continue;                        /* :2245 */
         if (y * 2 > end_y) break;                             /* :2252 */
@@ -567,18 +615,28 @@ int sdct_oracle_ref_encode_quantize32_reorder_buffer(const uint8_t *from, uint8_
     return 0;
 }
 
-int sdct_oracle_ref_encode_quantize_reorder_stereo_buffer(const uint8_t *from, uint8_t *to, const float *lut,
-                                                          size_t size_x, size_t size_y, size_t start_y, size_t end_y)
+/* quirks = SDCT_O_QUIRK_SSE: the bytes of the SSE4.1 / SSSE3 / SSE2 variants the dispatcher picks on every x86-64 CPU
+ * (:78-83); they step through a row 16 pixels at a time (:945), so size_x must be a multiple of 16 here */
+int sdct_oracle_ref_encode_quantize_reorder_stereo_buffer_q(const uint8_t *from, uint8_t *to, const float *lut,
+                                                            size_t size_x, size_t size_y, size_t start_y, size_t end_y,
+                                                            int quirks)
 {
     float tab[64];
     if (!from || !to) return 1;                               /* :75 */
     if ((size_x & 7) || (size_y & 7)) return 2;               /* :76 */
-    forward_table(SDCT_O_LAYOUT_C, SDCT_O_MODE_EXACT, lut, tab);
+    if ((quirks & SDCT_O_QUIRK_SSE) && (size_x & 15)) return 2;
+    forward_table(SDCT_O_LAYOUT_C, SDCT_O_MODE_EXACT, quirks, lut, tab);
     for (size_t y = 0; y < size_y / 2; y += 8) {
-        if (y * 2 < start_y) continue;                        /* :270 */
-        if (y * 2 > end_y) break;                             /* :280 */
-        forward_band(SDCT_O_LAYOUT_C, SDCT_O_MODE_EXACT, 0, from, size_x, 1, size_x, y / 8, 2,
+        if (y * 2 < start_y) continue;                        /* :270, :1070 */
+        if (y * 2 > end_y) break;                             /* :280, :1080 */
+        forward_band(SDCT_O_LAYOUT_C, SDCT_O_MODE_EXACT, quirks, from, size_x, 1, size_x, y / 8, 2,
                      size_x * size_y / 2, tab, to, size_x * size_y / 64);
     }
     return 0;
+}
+
+int sdct_oracle_ref_encode_quantize_reorder_stereo_buffer(const uint8_t *from, uint8_t *to, const float *lut,
+                                                          size_t size_x, size_t size_y, size_t start_y, size_t end_y)
+{
+    return sdct_oracle_ref_encode_quantize_reorder_stereo_buffer_q(from, to, lut, size_x, size_y, start_y, end_y, 0);
 }

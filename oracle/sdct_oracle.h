@@ -43,12 +43,13 @@ extern "C" {
 
 enum { SDCT_O_LAYOUT_A = 0, SDCT_O_LAYOUT_B = 1, SDCT_O_LAYOUT_C = 2 };
 enum { SDCT_O_MODE_EXACT = 0, SDCT_O_MODE_FAST = 1, SDCT_O_MODE_TENSOR = 2 };
-enum { SDCT_O_QUIRK_NONE = 0, SDCT_O_QUIRK_AVX_X3 = 1 };
+enum { SDCT_O_QUIRK_NONE = 0, SDCT_O_QUIRK_AVX_X3 = 1, SDCT_O_QUIRK_SSE = 2 /* layout C: the SSE encoders' arithmetic incl. their X1 sign, :896-1103 */ };
 enum { SDCT_O_TAB_SCALAR = 0, SDCT_O_TAB_AVX = 1, SDCT_O_TAB_FAST = 2, SDCT_O_TAB_INVERSE = 3, SDCT_O_TAB_TENSOR = 4 };
 
 /* 8-point kernels --------------------------------------------------------------------- */
 void sdct_oracle_dct8_scalar(float v[8]);                 /* src/simd_dct.cpp:138-172 */
 void sdct_oracle_dct8_paired(float v[8], int quirk_x3);   /* src/simd_dct.cpp:2160-2183 */
+void sdct_oracle_dct8_sse(float v[8]);                     /* src/simd_dct.cpp:672-892 (with its X1 sign) */
 void sdct_oracle_dct8_fast(float v[8]);                   /* this repo: FMA form, unnormalised */
 void sdct_oracle_idct8(float v[8]);                       /* this repo, unnormalised */
 
@@ -97,6 +98,8 @@ int sdct_oracle_ref_encode_quantize_buffer(const uint8_t *from, uint8_t *to, con
 int sdct_oracle_ref_encode_quantize32_reorder_buffer(const uint8_t *from, uint8_t *to, const float *lut,
                                                      size_t size_x, size_t size_y, size_t start_y,
                                                      size_t end_y, int quirks);
+int sdct_oracle_ref_encode_quantize_reorder_stereo_buffer_q(const uint8_t *from, uint8_t *to, const float *lut, size_t size_x,
+                                                            size_t size_y, size_t start_y, size_t end_y, int quirks);
 int sdct_oracle_ref_encode_quantize_reorder_stereo_buffer(const uint8_t *from, uint8_t *to,
                                                           const float *lut, size_t size_x, size_t size_y,
                                                           size_t start_y, size_t end_y);

@@ -11,7 +11,7 @@ LIB_PATH = os.environ.get("SDCT_LIB") or os.path.join(HERE, "libsdct.so")
 
 OK, INVALID_PARAMETER, NOT_SUPPORTED, CUDA_ERROR, NO_DEVICE = range(5)
 LAYOUT_A, LAYOUT_B, LAYOUT_C = 0, 1, 2
-EXACT, FAST, QUIRK_AVX_X3, TENSOR, COLOR_YCBCR = 0, 1, 2, 4, 8
+EXACT, FAST, QUIRK_AVX_X3, TENSOR, COLOR_YCBCR, QUIRK_SSE = 0, 1, 2, 4, 8, 16
 
 
 class Job(C.Structure):

@@ -16,7 +16,7 @@ from typing import Optional
 import numpy as np
 
 from . import _lib
-from ._lib import COLOR_YCBCR, EXACT, FAST, LAYOUT_A, LAYOUT_B, LAYOUT_C, QUIRK_AVX_X3, TENSOR, Job, SdctError, check  # noqa: F401
+from ._lib import COLOR_YCBCR, EXACT, FAST, LAYOUT_A, LAYOUT_B, LAYOUT_C, QUIRK_AVX_X3, QUIRK_SSE, TENSOR, Job, SdctError, check  # noqa: F401
 
 sdr_Success, sdr_InvalidParameter, sdr_NotSupported = 0, 1, 2
 
@@ -75,6 +75,10 @@ def simdDCT_EncodeQuantize32ReorderBuffer(pFrom, pTo, pQuantizeLUT, sizeX, sizeY
 
 def set_reference_flags(flags: int) -> None:
     _lib.load().sdct_ref_set_flags(flags)
+
+
+def get_reference_flags() -> int:
+    return int(_lib.load().sdct_ref_get_flags())
 
 
 def last_error() -> str:

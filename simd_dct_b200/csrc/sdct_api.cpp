@@ -76,11 +76,13 @@ int build_tables(const sdct_job *j, const float *lut, int op, float2 tab[64], fl
     if (!lut) return fail(SDCT_INVALID_PARAMETER, "quantisation LUT is null");
     const bool fast = (j->flags & SDCT_FAST) != 0;
     const bool lb = j->layout == SDCT_LAYOUT_B;
+    const bool sse = j->layout == SDCT_LAYOUT_C && (j->flags & SDCT_QUIRK_SSE) && op != SDCT_K_OP_INVERSE;
     for (int i = 0; i < 64; i++) {
         const float d = lut[i] * 0.95f;                               // vr, src/simd_dct.cpp:191
         float f, cmax = 0.f;
         if (fast) { f = lb ? 0.125f * (255.0f / d) : 0.125f * (1.f / d); cmax = 16384.f; }
         else if (lb) { f = 255.0f / d; cmax = 2048.f; }               // :2236-2239
+        else if (sse) { f = 255.0f / d; cmax = 16.f; }                // :908-923 (coefficients of pixels / 255: |c| <= 8)
         else f = 1.f / d;                                             // :194-212
         const float inv = lb ? (d / 255.f) * 0.125f : d * 0.125f;     // -> pixel units after the unnormalised passes
         const float o = -(127.f * inv);
@@ -255,7 +257,11 @@ int run_device(sdct_context *ctx, int op, const sdct_job *j, const uint8_t *pixe
         cudaFreeAsync(scratch, st);
         return rc;
     }
-    if (tensor && (j->flags & (SDCT_FAST | SDCT_QUIRK_AVX_X3))) return fail(SDCT_INVALID_PARAMETER, "SDCT_TENSOR excludes SDCT_FAST and SDCT_QUIRK_AVX_X3");
+    if (tensor && (j->flags & (SDCT_FAST | SDCT_QUIRK_AVX_X3 | SDCT_QUIRK_SSE))) return fail(SDCT_INVALID_PARAMETER, "SDCT_TENSOR excludes SDCT_FAST and the SDCT_QUIRK_* flags");
+    if (j->flags & SDCT_QUIRK_SSE) {   // the reference's SSE stereo encoders (src/simd_dct.cpp:896-1103): layout C, reference arithmetic only
+        if (j->layout != SDCT_LAYOUT_C || (j->flags & SDCT_FAST)) return fail(SDCT_INVALID_PARAMETER, "SDCT_QUIRK_SSE applies to layout C with SDCT_EXACT");
+        if (j->width & 15) return fail(SDCT_NOT_SUPPORTED, "SDCT_QUIRK_SSE needs width %% 16 == 0 (the reference's SSE encoders take two blocks at a time)");
+    }
     const bool tensor_inv = tensor && op == SDCT_K_OP_INVERSE;
     rc = (tensor && !tensor_inv) ? build_tc_tables(j, lut, p.tab) : build_tables(j, lut, op, p.tab, p.tab2, p.off);
     if (rc) return rc;
@@ -290,7 +296,8 @@ int run_device(sdct_context *ctx, int op, const sdct_job *j, const uint8_t *pixe
     DeviceScope dev(ctx->device);
     CU_TRY(dev.err);
     const int mode = (j->flags & SDCT_FAST) ? SDCT_K_FAST : SDCT_K_EXACT;
-    const int x3 = (j->flags & SDCT_QUIRK_AVX_X3) ? 1 : 0;
+    // the layout's reference-SIMD quirk: layout B the AVX2 path's X3 sign, layout C the SSE encoders' arithmetic
+    const int x3 = (j->layout == SDCT_LAYOUT_C ? (j->flags & SDCT_QUIRK_SSE) : (j->flags & SDCT_QUIRK_AVX_X3)) ? 1 : 0;
     if (tensor_inv) {
         // the tensor-core inverse moves whole 16-byte pieces on both sides; other geometries have no kernel (the fp32
         // inverse is a different arithmetic definition, so it is not substituted silently)

@@ -457,7 +457,10 @@ int ref_call(int layout, const uint8_t *from, uint8_t *to, const float *lut, siz
     if (rc) return rc;
     sdct_job j;
     const int eyes = layout == SDCT_LAYOUT_C ? 2 : 1;
-    sdct_job_dense(&j, layout, g_ref_flags.load(), 1, eyes, sx, bands * 8, 1);
+    int flags = g_ref_flags.load();   // each quirk belongs to one entry point: the X3 sign to layout B, the SSE arithmetic to layout C
+    if (layout != SDCT_LAYOUT_B) flags &= ~SDCT_QUIRK_AVX_X3;
+    if (layout != SDCT_LAYOUT_C) flags &= ~SDCT_QUIRK_SSE;
+    sdct_job_dense(&j, layout, flags, 1, eyes, sx, bands * 8, 1);
     if (layout == SDCT_LAYOUT_C) {
         j.eye_stride = sx * sy / 2;                   // :292
         j.coef_plane_stride = sx * sy / 64;           // :257

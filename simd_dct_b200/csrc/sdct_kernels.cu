@@ -143,7 +143,7 @@ SDCT_DEV void forward_pair(const uint32_t wp[16], const uint32_t wq[16], const f
         for (int r = 0; r < 8; r++) {
             const Stage1 a = stage1_pixels(wp[2 * r], wp[2 * r + 1], wq[2 * r], wq[2 * r + 1]);
             if (MODE == SDCT_K_FAST) dct8_fast_tail<1>(a, b + 8 * r);
-            else dct8_paired_tail<1, X3>(a, b + 8 * r);
+            else dct8_paired_tail<1, X3 ? 1 : 0>(a, b + 8 * r);
         }
     } else {
 #pragma unroll
@@ -156,7 +156,10 @@ SDCT_DEV void forward_pair(const uint32_t wp[16], const uint32_t wq[16], const f
 #else
             const F2 x = make_float2(byte_to_float(wp[i >> 2], i & 3), byte_to_float(wq[i >> 2], i & 3));
 #endif
-            b[i] = (MODE == SDCT_K_EXACT && LAYOUT != SDCT_K_LAYOUT_B) ? div255(x) : x;
+            // (layout C with the quirk flag = the reference's SSE encoders: x * (1.f / 255), :955-962 - a product, so the first
+            //  pass below takes the protected adds)
+            b[i] = (MODE == SDCT_K_EXACT && LAYOUT == SDCT_K_LAYOUT_C && X3) ? mulx<PFP>(x, SDCT_R255_HI)
+                 : (MODE == SDCT_K_EXACT && LAYOUT != SDCT_K_LAYOUT_B) ? div255(x) : x;
         }
     }
     if (MODE == SDCT_K_FAST) {
@@ -171,6 +174,11 @@ SDCT_DEV void forward_pair(const uint32_t wp[16], const uint32_t wq[16], const f
         for (int r = 0; r < 8; r++) dct8_scalar<1, false>(b + 8 * r);
 #pragma unroll
         for (int c = 0; c < 8; c++) dct8_scalar<8, true>(b + c);
+    } else if (LAYOUT == SDCT_K_LAYOUT_C && X3) {  // SSE encoders (:964-1007): columns, then rows, with inplace_dct8_sse41
+#pragma unroll
+        for (int c = 0; c < 8; c++) dct8_paired<8, true, 2>(b + c);
+#pragma unroll
+        for (int r = 0; r < 8; r++) dct8_paired<1, true, 2>(b + 8 * r);
     } else if (LAYOUT == SDCT_K_LAYOUT_C) {  // columns, then rows (:224-241)
 #pragma unroll
         for (int c = 0; c < 8; c++) dct8_scalar<8, false>(b + c);
@@ -179,15 +187,16 @@ SDCT_DEV void forward_pair(const uint32_t wp[16], const uint32_t wq[16], const f
     } else {                                 // layout B: rows, then columns (:2158-2215)
         if (!FOLD) {
 #pragma unroll
-            for (int r = 0; r < 8; r++) dct8_paired<1, false, X3>(b + 8 * r);
+            for (int r = 0; r < 8; r++) dct8_paired<1, false, X3 ? 1 : 0>(b + 8 * r);
         }
 #pragma unroll
-        for (int c = 0; c < 8; c++) dct8_paired<8, true, X3>(b + c);
+        for (int c = 0; c < 8; c++) dct8_paired<8, true, X3 ? 1 : 0>(b + c);
     }
 #pragma unroll
     for (int i = 0; i < 64; i++) {
         const F2 t = tab[tab_index<LAYOUT>(i)];
-        b[i] = (MODE == SDCT_K_EXACT && LAYOUT != SDCT_K_LAYOUT_B) ? quant_scalar(b[i], t) : quant_rne_c(b[i], t);
+        b[i] = (MODE == SDCT_K_EXACT && LAYOUT == SDCT_K_LAYOUT_C && X3) ? quant_sse(b[i], t)
+             : (MODE == SDCT_K_EXACT && LAYOUT != SDCT_K_LAYOUT_B) ? quant_scalar(b[i], t) : quant_rne_c(b[i], t);
     }
 }
 
@@ -769,7 +778,8 @@ __global__ void __launch_bounds__(SDCT_TB, 3) roundtrip_rgb_kernel(const __grid_
 #if SDCT_PART == 0
 // ---- self-test: the 8-point kernels on raw floats (bitwise oracle comparison in tests/) ----------
 // data: n vectors of 8 floats, transformed in place.  kind: 0 scalar, 1 paired, 2 paired+X3,
-// 3 fast, 4 idct, 5 = x/255 of element value (div255), +8 = "second pass" variant (scalar first stage)
+// 3 fast, 4 idct, 5 = x/255 of element value (div255), 6 = x * (1.f/255), +8 = "second pass" variant (scalar first stage),
+// 14 = the SSE form of the paired graph (X1 sign)
 __global__ void dct8_selftest_kernel(float *data, uint32_t n, int kind)
 {
     const uint32_t i = (blockIdx.x * blockDim.x + threadIdx.x) * 2;
@@ -781,10 +791,15 @@ __global__ void dct8_selftest_kernel(float *data, uint32_t n, int kind)
     switch (kind) {
     case 0: dct8_scalar<1, false>(v); break;
     case 8: dct8_scalar<1, true>(v); break;
-    case 1: dct8_paired<1, false, false>(v); break;
-    case 9: dct8_paired<1, true, false>(v); break;
-    case 2: dct8_paired<1, false, true>(v); break;
-    case 10: dct8_paired<1, true, true>(v); break;
+    case 1: dct8_paired<1, false, 0>(v); break;
+    case 9: dct8_paired<1, true, 0>(v); break;
+    case 2: dct8_paired<1, false, 1>(v); break;
+    case 10: dct8_paired<1, true, 1>(v); break;
+    case 14: dct8_paired<1, true, 2>(v); break;   // the SSE form (X1 sign), as both passes of the layout-C quirk use it
+    case 6:                                        // x * (1.f / 255) (the SSE encoders' conversion)
+#pragma unroll
+        for (int k = 0; k < 8; k++) v[k] = mulx<PFP>(v[k], SDCT_R255_HI);
+        break;
     case 3: dct8_fast<1>(v); break;
     case 4: idct8<1>(v); break;
     case 5:
@@ -919,7 +934,11 @@ SDCT_DECL(sdct_part_exact_b)
               : launch_fwd2<SDCT_K_LAYOUT_B, SDCT_K_EXACT, false>(op, p, grid, s);
 }
 #elif SDCT_PART == 3
-SDCT_DECL(sdct_part_exact_c) { (void)x3; return launch_fwd2<SDCT_K_LAYOUT_C, SDCT_K_EXACT, false>(op, p, grid, s); }
+SDCT_DECL(sdct_part_exact_c)   // x3 here: the layout's reference-SIMD quirk = the SSE stereo encoders' arithmetic (SDCT_QUIRK_SSE)
+{
+    return x3 ? launch_fwd2<SDCT_K_LAYOUT_C, SDCT_K_EXACT, true>(op, p, grid, s)
+              : launch_fwd2<SDCT_K_LAYOUT_C, SDCT_K_EXACT, false>(op, p, grid, s);
+}
 #elif SDCT_PART == 4
 SDCT_DECL(sdct_part_fast_a) { (void)x3; return launch_fwd2<SDCT_K_LAYOUT_A, SDCT_K_FAST, false>(op, p, grid, s); }
 #elif SDCT_PART == 5

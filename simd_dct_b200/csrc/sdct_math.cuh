@@ -181,24 +181,28 @@ SDCT_DEV void paired_even(F2 s07, F2 s16, F2 s25, F2 s34, F2 &x0, F2 &x2, F2 &x4
     x2 = mulx<PFP>(sadd<PFP>(mulx<PFP>(pm, SDCT_KB), mulx<PFP>(qm, SDCT_KE)), SDCT_KN);
     x6 = mulx<PFP>(ssub<PFP>(mulx<PFP>(pm, SDCT_KE), mulx<PFP>(qm, SDCT_KB)), SDCT_KN);
 }
-template <bool X3>
+// Q: the reference variant's sign defect - 0 none (the DCT), 1 = AVX2 / AVX-512VL X3 (:2181), 2 = SSE X1 (:788, :550; the
+// SSE forms' other sign flips and negative factors are exact negations, so their sums are these sums bit for bit)
+template <int Q>
 SDCT_DEV void paired_odd(F2 d07, F2 d61, F2 d25, F2 d43, F2 &x1, F2 &x3, F2 &x5, F2 &x7)
 {
+    constexpr bool X3 = Q == 1, X1 = Q == 2;
     // pairwise: (t0 op t1) op (t2 op t3); the outer add sees two sums -> packed
-    x1 = mulx<PFP>(add2(ssub<PFP>(mulx<PFP>(d07, SDCT_KA), mulx<PFP>(d61, SDCT_KC)), ssub<PFP>(mulx<PFP>(d25, SDCT_KD), mulx<PFP>(d43, SDCT_KF))), SDCT_KN);
+    const F2 x1r = X1 ? sadd<PFP>(mulx<PFP>(d25, SDCT_KD), mulx<PFP>(d43, SDCT_KF)) : ssub<PFP>(mulx<PFP>(d25, SDCT_KD), mulx<PFP>(d43, SDCT_KF));
+    x1 = mulx<PFP>(add2(ssub<PFP>(mulx<PFP>(d07, SDCT_KA), mulx<PFP>(d61, SDCT_KC)), x1r), SDCT_KN);
     const F2 x3r = X3 ? sadd<PFP>(mulx<PFP>(d25, SDCT_KA), mulx<PFP>(d43, SDCT_KD)) : ssub<PFP>(mulx<PFP>(d25, SDCT_KA), mulx<PFP>(d43, SDCT_KD));
     x3 = mulx<PFP>(sub2(sadd<PFP>(mulx<PFP>(d07, SDCT_KC), mulx<PFP>(d61, SDCT_KF)), x3r), SDCT_KN);
     x5 = mulx<PFP>(add2(sadd<PFP>(mulx<PFP>(d07, SDCT_KD), mulx<PFP>(d61, SDCT_KA)), ssub<PFP>(mulx<PFP>(d25, SDCT_KF), mulx<PFP>(d43, SDCT_KC))), SDCT_KN);
     x7 = mulx<PFP>(add2(sadd<PFP>(mulx<PFP>(d07, SDCT_KF), mulx<PFP>(d61, SDCT_KD)), sadd<PFP>(mulx<PFP>(d25, SDCT_KC), mulx<PFP>(d43, SDCT_KA))), SDCT_KN);
 }
-template <int S, bool X3>
+template <int S, int Q>
 SDCT_DEV void dct8_paired_tail(const Stage1 &a, F2 *v)
 {
     paired_even(a.s07, a.s16, a.s25, a.s34, v[0], v[2 * S], v[4 * S], v[6 * S]);
-    paired_odd<X3>(a.d07, a.d61, a.d25, a.d43, v[S], v[3 * S], v[5 * S], v[7 * S]);
+    paired_odd<Q>(a.d07, a.d61, a.d25, a.d43, v[S], v[3 * S], v[5 * S], v[7 * S]);
 }
-template <int S, bool PROD_IN, bool X3>
-SDCT_DEV void dct8_paired(F2 *v) { dct8_paired_tail<S, X3>(stage1_of<S, PROD_IN, PFP>(v), v); }
+template <int S, bool PROD_IN, int Q>
+SDCT_DEV void dct8_paired(F2 *v) { dct8_paired_tail<S, Q>(stage1_of<S, PROD_IN, PFP>(v), v); }
 
 // ---- 8-point forward, FAST (oracle/sdct_oracle.c: sdct_oracle_dct8_fast), unnormalised ---------
 // explicit FMAs; no multiply feeds a plain add, so there is nothing left for ptxas to contract
@@ -271,6 +275,11 @@ SDCT_DEV F2 div255(F2 x) { return fma2(x, splat(SDCT_R255_HI), mulk(x, SDCT_R255
 // saturating pack clamps to the same byte.  From 2^31 the reference's cvtps_epi32 returns INT_MIN (:2224): sdct_api.cpp
 // (build_tables) rejects tables under which |c*q| could get there.
 SDCT_DEV F2 quant_rne_c(F2 c, F2 q) { return fma2(mul2(c, q), splat(SDCT_NEG_DENORM_MIN), splat(SDCT_128_DENORM)); }
+
+// reference SSE stereo encoders (:1018-1024): min(255, max(0, cvtps_epi32(c * q + 127.f))) - product and sum rounded
+// separately (the sum is issued as fma(p, 1.0, 127): fl(p + 127) bit for bit, and p's multiply cannot be contracted into
+// it), then nearest even.  bits = the level itself; negative sums carry the sign bit and saturate to 0 in the pack.
+SDCT_DEV F2 quant_sse(F2 c, F2 q) { return mulk(sadd<2>(splat(127.0f), mul2(c, q)), SDCT_DENORM_MIN); }
 
 // reference scalar path (:245 / :362): (u8)roundf(clamp(c*rq + 127/255, 0, 1) * 255).
 // roundf (half away from zero) of y in [0,255] = floor(y + 0.5) with the sum rounded DOWN, which

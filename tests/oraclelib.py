@@ -17,7 +17,7 @@ REF_DIR = os.path.join(ROOT, "oracle", "_ref")
 
 LAYOUT_A, LAYOUT_B, LAYOUT_C = 0, 1, 2
 MODE_EXACT, MODE_FAST, MODE_TENSOR = 0, 1, 2
-QUIRK_NONE, QUIRK_AVX_X3 = 0, 1
+QUIRK_NONE, QUIRK_AVX_X3, QUIRK_SSE = 0, 1, 2
 TAB_SCALAR, TAB_AVX, TAB_FAST, TAB_INVERSE = 0, 1, 2, 3
 
 # the reference CLI's default quantisation LUT (src/main.cpp:179-189): the JPEG luminance
@@ -63,7 +63,7 @@ class Oracle:
         L.sdct_oracle_inverse_tensor.restype = None
         L.sdct_oracle_tables.argtypes = [_f32p, C.c_int, _f32p, C.c_int]
         L.sdct_oracle_tables.restype = None
-        for n in ("dct8_scalar", "dct8_fast", "idct8"):
+        for n in ("dct8_scalar", "dct8_fast", "idct8", "dct8_sse"):
             getattr(L, "sdct_oracle_" + n).argtypes = [_f32p]
             getattr(L, "sdct_oracle_" + n).restype = None
         L.sdct_oracle_dct8_paired.argtypes = [_f32p, C.c_int]
@@ -78,6 +78,7 @@ class Oracle:
         L.sdct_oracle_ref_encode_quantize_buffer.argtypes = sig
         L.sdct_oracle_ref_encode_quantize32_reorder_buffer.argtypes = sig + [C.c_int]
         L.sdct_oracle_ref_encode_quantize_reorder_stereo_buffer.argtypes = sig
+        L.sdct_oracle_ref_encode_quantize_reorder_stereo_buffer_q.argtypes = sig + [C.c_int]
 
     # ---- native semantics -------------------------------------------------------------
     def forward(self, layout, img, lut_, mode=MODE_EXACT, quirks=QUIRK_NONE, eyes=1, comp=None):
@@ -175,8 +176,8 @@ class Oracle:
             rc = self.lib.sdct_oracle_ref_encode_quantize32_reorder_buffer(_p8(buf), _p8(out), _pf(lut_), size_x,
                                                                            size_y, start_y, end_y, quirks)
         else:
-            rc = self.lib.sdct_oracle_ref_encode_quantize_reorder_stereo_buffer(_p8(buf), _p8(out), _pf(lut_),
-                                                                                size_x, size_y, start_y, end_y)
+            rc = self.lib.sdct_oracle_ref_encode_quantize_reorder_stereo_buffer_q(_p8(buf), _p8(out), _pf(lut_), size_x, size_y,
+                                                                                  start_y, end_y, quirks & QUIRK_SSE)
         return rc, out
 
 
@@ -220,6 +221,12 @@ class Reference:
             pass
         elif isa == "sse41":
             for n in ("sseSupported", "sse2Supported", "sse3Supported", "ssse3Supported", "sse41Supported"):
+                self._flag(n).value = True
+        elif isa == "ssse3":
+            for n in ("sseSupported", "sse2Supported", "sse3Supported", "ssse3Supported"):
+                self._flag(n).value = True
+        elif isa == "sse2":
+            for n in ("sseSupported", "sse2Supported"):
                 self._flag(n).value = True
         elif isa == "avx2":
             self._flag("avx2Supported").value = True

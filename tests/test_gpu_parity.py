@@ -52,7 +52,8 @@ def _dct8_inputs():
 
 
 @pytest.mark.parametrize("kind,name,quirk", [(0, "dct8_scalar", 0), (8, "dct8_scalar", 0), (1, "paired", 0), (9, "paired", 0),
-                                             (2, "paired", 1), (10, "paired", 1), (3, "dct8_fast", 0), (4, "idct8", 0)])
+                                             (2, "paired", 1), (10, "paired", 1), (3, "dct8_fast", 0), (4, "idct8", 0),
+                                             (14, "dct8_sse", 0)])
 def test_dct8_bitwise(ctx, oracle, kind, name, quirk):
     """the device 8-point kernels (packed fp32, sdct_math.cuh) reproduce the CPU restatement bit for
     bit - in particular no multiply-add contraction sneaks into the EXACT graphs."""
@@ -63,6 +64,70 @@ def test_dct8_bitwise(ctx, oracle, kind, name, quirk):
     want_all = oracle.dct8_many(name, x, quirk)
     bad = np.flatnonzero((got.view(np.uint32) != want_all.view(np.uint32)).any(axis=1))
     assert bad.size == 0, (bad[:5], got[bad[:1]], want_all[bad[:1]])
+
+
+def test_mul_inv255_bitwise(ctx):
+    """x * (1.f / 255) (the reference's SSE encoders, src/simd_dct.cpp:955-962): all 256 inputs"""
+    x = np.arange(256, dtype=np.float32).reshape(32, 8)
+    got = ctx.selftest_dct8(6, x)
+    assert np.array_equal(got.view(np.uint32), (x * (np.float32(1) / np.float32(255))).astype(np.float32).view(np.uint32))
+
+
+@pytest.mark.parametrize("kind", ["rand", "smooth"])
+@pytest.mark.parametrize("scale", [1, 8, 255])
+def test_layout_c_sse_quirk(ctx, oracle, kind, scale):
+    """SDCT_QUIRK_SSE: the bytes of the reference's SSE stereo encoders (restatement pinned against the compiled reference and
+    the golden vectors in test_oracle_pins.py): forward for one and two eyes, a band window, the reference-style call, and
+    the fused round trip = the fp32 inverse of those levels."""
+    flags = sd.EXACT | sd.QUIRK_SSE
+    for (h, w, eyes, window) in ((512, 512, 1, None), (128, 2112, 2, None), (96, 1040, 2, (3, 9))):
+        img = make_image(kind, h * eyes, w, seed=17)
+        lut = ol.lut(scale)
+        b0, b1 = window if window else (0, 0)
+        job = sd.dense_job(sd.LAYOUT_C, w, h, eyes=eyes, flags=flags, band_begin=b0, band_end=b1)
+        out = torch.full((eyes * h * w,), 0x5a, dtype=torch.uint8, device="cuda")
+        ctx.forward(dev(img), lut, job, out=out)
+        want_all = oracle.forward(ol.LAYOUT_C, img, lut, quirks=ol.QUIRK_SSE, eyes=eyes).reshape(64, h // 8, eyes * (w // 8))
+        want = np.full_like(want_all, 0x5a)
+        lo, hi = (b0, b1) if window else (0, h // 8)
+        want[:, lo:hi] = want_all[:, lo:hi]
+        assert np.array_equal(out.cpu().numpy().reshape(want.shape), want), (h, w, eyes, window)
+        assert not np.array_equal(want_all, oracle.forward(ol.LAYOUT_C, img, lut, eyes=eyes).reshape(want_all.shape)) or scale == 255
+    # round trip: the inverse does not depend on the quirk (levels mean the same coefficients)
+    h, w = 256, 512
+    lut = rt_lut(sd.LAYOUT_C)
+    img = make_image(kind, h, w, seed=18)
+    job = sd.dense_job(sd.LAYOUT_C, w, h, flags=flags)
+    coef = oracle.forward(ol.LAYOUT_C, img, lut, quirks=ol.QUIRK_SSE)
+    rt = ctx.roundtrip(dev(img), lut, job).cpu().numpy().reshape(h, w)
+    assert np.array_equal(rt, oracle.inverse(ol.LAYOUT_C, coef, w, h, lut))
+    # misuse
+    with pytest.raises(sd.SdctError):
+        ctx.forward(dev(img), lut, sd.dense_job(sd.LAYOUT_B, w, h, flags=flags))
+    with pytest.raises(sd.SdctError):
+        ctx.forward(dev(img[:, :504]), lut, sd.dense_job(sd.LAYOUT_C, 504, h, flags=flags))
+    with pytest.raises(sd.SdctError):
+        ctx.forward(dev(img), lut, sd.dense_job(sd.LAYOUT_C, w, h, flags=sd.TENSOR | sd.QUIRK_SSE))
+
+
+def test_reference_style_call_with_the_sse_quirk(oracle):
+    """sdct_ref_set_flags(SDCT_EXACT | SDCT_QUIRK_AVX_X3 | SDCT_QUIRK_SSE): every simd_dct.h entry point then returns what the
+    reference's SIMD dispatch returns on an x86-64 CPU with AVX2 (layout A: its scalar path - the SSE layout-A encoders are
+    the broken ones, never reproduced)"""
+    x, y = 256, 128
+    img = make_image("rand", y, x, seed=19)
+    lut = ol.lut(4)
+    old = sd.get_reference_flags() if hasattr(sd, "get_reference_flags") else None
+    sd.set_reference_flags(sd.EXACT | sd.QUIRK_AVX_X3 | sd.QUIRK_SSE)
+    try:
+        for name, fn in (("A", sd.simdDCT_EncodeQuantizeBuffer), ("B", sd.simdDCT_EncodeQuantize32ReorderBuffer), ("C", sd.simdDCT_EncodeQuantizeReorderStereoBuffer)):
+            for (s0, s1) in ((0, y), (32, 80)):
+                got = np.full(x * y, 0x11, dtype=np.uint8)
+                assert fn(img, got, lut, x, y, s0, s1) == sd.sdr_Success
+                rc, want = oracle.ref_call(name, img, lut, x, y, s0, s1, quirks=ol.QUIRK_AVX_X3 | ol.QUIRK_SSE, fill=0x11)
+                assert rc == 0 and np.array_equal(got, want), (name, s0, s1)
+    finally:
+        sd.set_reference_flags(old if old is not None else (sd.EXACT | sd.QUIRK_AVX_X3))
 
 
 def test_div255_bitwise(ctx):

@@ -33,6 +33,8 @@ def test_oracle_matches_golden_reference_output(oracle, gold, kind, scale):
     assert np.array_equal(a, gold[f"A_{kind}_x{scale}"])
     assert np.array_equal(b, gold[f"B_{kind}_x{scale}"])
     assert np.array_equal(c, gold[f"C_{kind}_x{scale}"])
+    c_sse = oracle.forward(ol.LAYOUT_C, img, lut, quirks=ol.QUIRK_SSE, eyes=2)   # the reference's SSE4.1 stereo encoder
+    assert np.array_equal(c_sse, gold[f"Csse_{kind}_x{scale}"])
 
 
 @pytest.mark.parametrize("name", ["A", "B", "C"])
@@ -118,3 +120,46 @@ def test_reference_simd_variants_have_the_surveyed_defects(oracle):
         _, avx = ref.call("B", img, lut, 128, 128)
         assert np.array_equal(avx, oracle.ref_call("B", img, lut, 128, 128, quirks=ol.QUIRK_AVX_X3)[1])
         assert not np.array_equal(avx, oracle.ref_call("B", img, lut, 128, 128, quirks=0)[1])
+
+
+@needs_ref
+@pytest.mark.parametrize("kind,scale", [("rand", 1), ("rand", 8), ("smooth", 1), ("smooth", 255)])
+def test_sse_quirk_is_byte_identical_to_the_reference_sse_stereo_encoders(oracle, kind, scale):
+    """quirks = SSE (layout C): the restatement of src/simd_dct.cpp:896-1103 / :672-892 against the reference's own SSE4.1,
+    SSSE3 and SSE2 stereo encoders (what its dispatcher runs on every x86-64 CPU, :78-83), whole image and a band window,
+    strict and fast-math builds."""
+    flags = ol.cpu_flags()
+    if "sse2" not in flags:
+        pytest.skip("no SSE2 on this host")
+    x, y = 256, 128
+    img = make_image(kind, y, x, seed=5)
+    lut = ol.lut(scale)
+    isas = [("sse41", "sse4_1"), ("ssse3", "ssse3"), ("sse2", "sse2")]
+    for build in ("strict", "fast"):
+        if not ol.have_reference(build):
+            continue
+        ref = ol.Reference(build)
+        for isa, flag in isas:
+            if flag not in flags:
+                continue
+            ref.set_isa(isa)
+            for (s0, s1) in ((0, y), (32, 80)):
+                rc, want = ref.call("C", img, lut, x, y, s0, s1, fill=0x11)
+                rc2, got = oracle.ref_call("C", img, lut, x, y, s0, s1, quirks=ol.QUIRK_SSE, fill=0x11)
+                assert rc == rc2 == 0
+                assert np.array_equal(got, want), (build, isa, s0, s1, int((got != want).sum()))
+    ref = ol.Reference("strict")
+    ref.set_isa("scalar")
+    if kind == "rand":   # ... and they are NOT the scalar path's bytes
+        assert np.mean(ref.call("C", img, lut, x, y)[1] != oracle.ref_call("C", img, lut, x, y, quirks=ol.QUIRK_SSE)[1]) > 0.005
+    # native semantics (both eyes of every band) = the reference call over the whole image
+    native = oracle.forward(ol.LAYOUT_C, img, lut, quirks=ol.QUIRK_SSE, eyes=2)
+    assert np.array_equal(native, oracle.ref_call("C", img, lut, x, y, quirks=ol.QUIRK_SSE)[1])
+
+
+def test_dct8_sse_is_the_paired_form_with_one_sign(oracle):
+    rng = np.random.default_rng(3)
+    for v in rng.standard_normal((200, 8)).astype(np.float32) * 50:
+        a, b = oracle.dct8("dct8_sse", v), oracle.dct8("paired", v, 0)
+        assert np.array_equal(np.delete(a, 1).view(np.uint32), np.delete(b, 1).view(np.uint32))
+        assert abs(float(a[1]) - float(b[1])) > 0 or v[4] == v[3]

@@ -7,7 +7,8 @@ mounted (the build container); the vectors travel with the repo, the reference d
 Contents: two seeded 64x128 u8 inputs, and for each input / LUT scale / entry point the bytes the
 reference wrote (through its public API, with its own call semantics: sizeY = stereo height, only
 rows below sizeY/2 visited for A and B).  Layout A and C come from the scalar path (all CPU feature
-bools false), layout B from the AVX2 path (avx2Supported = true only) - SURVEY.md section 8c."""
+bools false), layout B from the AVX2 path (avx2Supported = true only) - SURVEY.md section 8c; Csse_* are layout C from
+the SSE4.1 stereo encoder (the quirks = SSE restatement's pin)."""
 import os
 import sys
 
@@ -20,6 +21,7 @@ from conftest import make_image  # noqa: E402
 
 ref = ol.Reference("strict")
 assert "avx2" in ol.cpu_flags(), "the AVX2 path of the reference must be executable to make the layout-B vectors"
+assert "sse4_1" in ol.cpu_flags()
 out = {}
 W, H = 128, 64
 for kind in ("rand", "smooth"):
@@ -41,6 +43,11 @@ for kind in ("rand", "smooth"):
         rc, c = ref.call("C", img, lut, W, H, 0, H)
         assert rc == 0
         out[f"C_{kind}_x{scale}"] = c.copy()
+        # ... and the bytes of its SSE4.1 stereo encoder (the variant its dispatcher picks on x86-64; flag SDCT_QUIRK_SSE)
+        ref.set_isa("sse41")
+        rc, c = ref.call("C", img, lut, W, H, 0, H)
+        assert rc == 0
+        out[f"Csse_{kind}_x{scale}"] = c.copy()
     # window semantics (inclusive endY, 2y vs y comparison), scale 8
     lut = ol.lut(8)
     for name, isa in (("A", "scalar"), ("B", "avx2"), ("C", "scalar")):
