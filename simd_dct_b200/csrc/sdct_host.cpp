@@ -250,6 +250,21 @@ int run_chunks(sdct_context *ctx, Pipeline *pipe, int op, const sdct_job *job, c
         tev.push_back(e);
     };
 
+    // the slots' device buffers at the size of the call's largest chunk BEFORE anything is in flight: growing one inside the
+    // loop would free a buffer that the slot's previous chunk may still use (cudaFree waits for the whole device)
+    {
+        size_t max_pix = 0, max_coef = 0;
+        for (const Chunk &c : chunks) {
+            const Plan pl = plan_chunk(*job, g, c);
+            max_pix = std::max<size_t>(max_pix, pl.pix_bytes);
+            max_coef = std::max<size_t>(max_coef, pl.coef_bytes);
+        }
+        for (size_t i = 0; i < std::min<size_t>((size_t)depth, chunks.size()); i++) {
+            if ((rc = grow_device(&pipe->slots[i].d_pix, &pipe->slots[i].d_pix_cap, max_pix))) return rc;
+            if ((rc = grow_device(&pipe->slots[i].d_coef, &pipe->slots[i].d_coef_cap, max_coef))) return rc;
+        }
+    }
+
     for (size_t ci = 0; ci < chunks.size(); ci++) {
         const Plan plan = plan_chunk(*job, g, chunks[ci]);
         Slot &s = pipe->slots[ci % depth];

@@ -28,6 +28,34 @@ def rt_lut(layout):
     return (t * np.float32(255)).astype(np.float32) if layout == sd.LAYOUT_B else t
 
 
+@pytest.mark.parametrize("engine_streams", ["0", "1"])
+def test_pinned_batch_through_both_stream_plans(oracle, monkeypatch, engine_streams):
+    """the chunked pipeline on pinned caller memory with one stream per engine (default) and with one stream per slot
+    ($SDCT_HOST_ENGINE_STREAMS=0, read in sdct_create): many chunks (1 MB), every slot reused several times, forward and
+    inverse, twice in a row on the same context (buffers and events of the first call are reused by the second)"""
+    monkeypatch.setenv("SDCT_HOST_ENGINE_STREAMS", engine_streams)
+    monkeypatch.setenv("SDCT_HOST_CHUNK_MB", "1")
+    c = sd.Context(0)
+    try:
+        f, h, w = 24, 256, 512
+        layout = sd.LAYOUT_B
+        lut = rt_lut(layout)
+        job = sd.dense_job(layout, w, h, frames=f, flags=flags_for(layout))
+        for rep in range(2):
+            img = make_image("smooth", f * h, w, seed=60 + rep)
+            h_in = torch.from_numpy(img).pin_memory()
+            h_coef = torch.zeros(f * h * w, dtype=torch.uint8).pin_memory()
+            c.forward_host(h_in, lut, job, out=h_coef)
+            want = np.concatenate([oracle.forward(layout, img[k * h:(k + 1) * h], lut, quirks=ol.QUIRK_AVX_X3) for k in range(f)])
+            assert np.array_equal(h_coef.numpy(), want), (engine_streams, rep)
+            h_pix = torch.zeros(f * h, w, dtype=torch.uint8).pin_memory()
+            c.inverse_host(h_coef, lut, job, out=h_pix)
+            back = np.concatenate([oracle.inverse(layout, want[k * h * w:(k + 1) * h * w], w, h, lut) for k in range(f)])
+            assert np.array_equal(h_pix.numpy(), back), (engine_streams, rep)
+    finally:
+        c.close()
+
+
 @pytest.mark.parametrize("pinned", [False, True])
 @pytest.mark.parametrize("layout", LAYOUTS)
 def test_inverse_host_padded_pitch_leaves_padding_untouched(ctx, oracle, layout, pinned):
