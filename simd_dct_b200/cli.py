@@ -8,6 +8,8 @@ optional `--to` dump of the last output.
         --device <n | all | 0,1,..>   GPU(s) the call is sharded over ($SDCT_DEVICE / $SDCT_DEVICES)
         --flags exact | fast | tensor arithmetic (exact = the reference's bytes; enc-quant32 then carries the X3 quirk)
         --no-quirk                    exact arithmetic without the reference's X3 sign (the true DCT)
+        --sse-quirk                   enc-quant-stereo with the bytes of the reference's SSE stereo encoders (what its dispatcher
+                                      runs on an x86-64 CPU, src/simd_dct.cpp:78-83) instead of its scalar path's; X % 16 == 0
         --inverse                     decode the coefficients back to pixels after the (last) encode; --to then dumps
                                       the pixels (the reference has no inverse: this repo's definition)
         --resident                    also time the kernel alone on device-resident buffers (CUDA events)
@@ -57,6 +59,7 @@ def main(argv=None) -> int:
     ap.add_argument("--device", default=None)
     ap.add_argument("--flags", default="exact", choices=["exact", "fast", "tensor"])
     ap.add_argument("--no-quirk", action="store_true")
+    ap.add_argument("--sse-quirk", action="store_true")
     ap.add_argument("--inverse", action="store_true")
     ap.add_argument("--resident", action="store_true")
     a = ap.parse_args(argv)
@@ -106,6 +109,7 @@ def main(argv=None) -> int:
         fn = getattr(sd, fname)
         layout = {"A": sd.LAYOUT_A, "B": sd.LAYOUT_B, "C": sd.LAYOUT_C}[lname]
         mode_flags = flags | (sd.QUIRK_AVX_X3 if (a.flags == "exact" and layout == sd.LAYOUT_B and not a.no_quirk) else 0)
+        mode_flags |= sd.QUIRK_SSE if (a.flags == "exact" and layout == sd.LAYOUT_C and a.sse_quirk) else 0
         sd.set_reference_flags(mode_flags)
         blocks = (x // 8) * half_bands * (2 if lname == "C" else 1)
         ns = []

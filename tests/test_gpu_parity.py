@@ -426,13 +426,16 @@ def test_reference_cli_linked_against_libsdct(tmp_path, mode, simd):
 
 
 @pytest.mark.skipif(not os.path.exists(os.path.join(CLI_DIR, "simd_dct_cli_cpu")), reason="oracle/_ref CLIs not built")
-@pytest.mark.parametrize("mode,simd", [("enc-quant", "none"), ("enc-quant32", "avx2"), ("enc-quant-stereo", "none")])
+@pytest.mark.parametrize("mode,simd", [("enc-quant", "none"), ("enc-quant32", "avx2"), ("enc-quant-stereo", "none"), ("enc-quant-stereo", "sse4.1")])
 def test_python_cli_dump_equals_the_reference_cli(tmp_path, mode, simd):
     """SURVEY 8f f2: `python -m simd_dct_b200.cli` follows the reference CLI's workflow (src/main.cpp:84-102, :508-606);
     its --to dump equals the all-CPU reference binary's, and --inverse dumps pixels close to the input."""
     import sys
     if simd == "avx2" and "avx2" not in ol.cpu_flags():
         pytest.skip("host CPU has no AVX2: the reference cannot produce layout B here")
+    if simd == "sse4.1" and "sse4_1" not in ol.cpu_flags():
+        pytest.skip("host CPU has no SSE4.1")
+    sse = ["--sse-quirk"] if simd == "sse4.1" else []   # the reference's SSE stereo encoder against SDCT_QUIRK_SSE
     img = make_image("smooth", 512, 768, seed=6)
     raw = tmp_path / "img.raw"
     raw.write_bytes(img.tobytes())
@@ -441,7 +444,7 @@ def test_python_cli_dump_equals_the_reference_cli(tmp_path, mode, simd):
     r = subprocess.run([os.path.join(CLI_DIR, "simd_dct_cli_cpu")] + common + ["--max-simd", simd, "--to", str(ref_dump)], capture_output=True, text=True, timeout=120)
     assert r.returncode == 0, r.stdout + r.stderr
     root = os.path.dirname(os.path.dirname(CLI_DIR))
-    r = subprocess.run([sys.executable, "-m", "simd_dct_b200.cli"] + common + ["--to", str(my_dump), "--resident"], capture_output=True, text=True, timeout=300, cwd=root)
+    r = subprocess.run([sys.executable, "-m", "simd_dct_b200.cli"] + common + sse + ["--to", str(my_dump), "--resident"], capture_output=True, text=True, timeout=300, cwd=root)
     assert r.returncode == 0, r.stdout + r.stderr
     assert "MiB/s" in r.stdout and "blocks/s" in r.stdout and "kernel only" in r.stdout
     a, b = np.frombuffer(ref_dump.read_bytes(), dtype=np.uint8), np.frombuffer(my_dump.read_bytes(), dtype=np.uint8)
