@@ -134,7 +134,17 @@ constexpr int RING_BARS = cmax(cmax(TMA_RING, RT_RING), cmax(inv_ring<1>(), inv_
 //   a_empty[k % 4]          MMA commit -> producer warpgroup k % 2
 //   d_full[k % 2][k % 3]    MMA commit -> consumer warpgroup k % 2
 //   d_empty[k % 2][k % 3]   consumer k % 2 -> the MMA warp of tile k + 3   (128 arrivals)
-constexpr int BAR_A_FULL = 0, BAR_A_EMPTY = A_STAGES, BAR_D_FULL = 2 * A_STAGES, BAR_D_EMPTY = BAR_D_FULL + CONSUMER_WGS * D_STAGES;
+// the inverse kernel keeps its A operand in shared memory, so all of TMEM is free for D stages: experiment builds give it
+// four (-DSDCT_TC_INV_D_STAGES=4), with its own barrier period (the same one-waiter rule)
+#ifndef SDCT_TC_INV_D_STAGES
+#define SDCT_TC_INV_D_STAGES 3
+#endif
+constexpr int INV_D_STAGES = SDCT_TC_INV_D_STAGES;
+constexpr int INV_D_PERIOD = (INV_D_STAGES == 3) ? 6 : (CONSUMER_WGS == 3 ? 12 : 4);
+static_assert(INV_D_STAGES * D_COLS <= TMEM_COLS && INV_D_PERIOD % MMA_WARPS == 0 && INV_D_PERIOD % CONSUMER_WGS == 0 && INV_D_PERIOD % INV_D_STAGES == 0, "inverse D stages");
+__host__ __device__ constexpr uint32_t inv_d_bar(uint32_t k) { return k % INV_D_PERIOD; }
+constexpr int D_BARS = CONSUMER_WGS * D_STAGES > INV_D_PERIOD ? CONSUMER_WGS * D_STAGES : INV_D_PERIOD;
+constexpr int BAR_A_FULL = 0, BAR_A_EMPTY = A_STAGES, BAR_D_FULL = 2 * A_STAGES, BAR_D_EMPTY = BAR_D_FULL + D_BARS;
 // tile k's D barriers: index k % D_PERIOD.  Six of each, so that a barrier belongs to ONE MMA warp (tiles of one parity)
 // and ONE consumer warpgroup (D_PERIOD is a multiple of MMA_WARPS, CONSUMER_WGS and D_STAGES): with a period of 3 the
 // two MMA warps would alternate on a barrier, each seeing every other phase, and a parity wait cannot tell phase u from
@@ -142,6 +152,7 @@ constexpr int BAR_A_FULL = 0, BAR_A_EMPTY = A_STAGES, BAR_D_FULL = 2 * A_STAGES,
 constexpr int D_PERIOD = 6;
 static_assert(D_PERIOD % MMA_WARPS == 0 && D_PERIOD % CONSUMER_WGS == 0 && D_PERIOD % D_STAGES == 0 && D_PERIOD <= CONSUMER_WGS * D_STAGES, "D barrier period");
 __host__ __device__ constexpr uint32_t d_bar(uint32_t k) { return k % D_PERIOD; }
+
 // fused round trip (roundtrip_tc_kernel): its own barrier and TMEM plan.  TMEM holds the accumulators only, both
 // double-buffered: D2 (pixels) 2 x 128 columns, D1 (coefficients) 2 x 128; the A operands (pixels / levels as fp16) live in
 // shared memory as K-major core matrices (the inverse kernel's layout-A form: LBO 144, conflict-free 16-byte row stores).
@@ -157,7 +168,7 @@ constexpr int BAR_PRODUCER = 8, BAR_FLUSH = 9;    // named barriers (ids 1 .. CO
 //   ring_full[j % 6]        TMA (complete_tx) -> producer warpgroup; ring_empty[j % 6]: its four warps -> TMA thread
 // TMA ring slots hold two 8 KiB boxes: 8 rows x 1024 bytes of this / of the next block row
 constexpr int TMA_BOX_BYTES = 8 * TILE * 8, TMA_SLOT_BYTES = 2 * TMA_BOX_BYTES;
-constexpr int BAR_RING_FULL = BAR_D_EMPTY + CONSUMER_WGS * D_STAGES, BAR_RING_EMPTY = BAR_RING_FULL + RING_BARS;
+constexpr int BAR_RING_FULL = BAR_D_EMPTY + D_BARS, BAR_RING_EMPTY = BAR_RING_FULL + RING_BARS;
 constexpr int NUM_BARS = BAR_RING_EMPTY + RING_BARS;
 constexpr int SMEM_META_OFF = SMEM_BAR_OFF + NUM_BARS * 8 + 16;   // TMA ring: blocks of the tile that lie in the first box
 static_assert(SMEM_META_OFF + RING_BARS * 4 <= SMEM_BAR_REGION, "barrier region");
@@ -1162,13 +1173,13 @@ SDCT_DEV void inv_mma_role(const KParams &p, uint64_t *bars, uint32_t tmem_base,
     const uint64_t bd[4] = {bdesc, bdesc + (uint64_t)((2 * B_LBO) >> 4), bdesc + (uint64_t)((4 * B_LBO) >> 4), bdesc + (uint64_t)((6 * B_LBO) >> 4)};
     for (uint32_t k = m;; k += MMA_WARPS) {
         if (blockIdx.x + (k / CF) * gridDim.x >= p.tiles) break;
-        const uint32_t sa = k % A_STAGES, ua = k / A_STAGES, sd = k % D_STAGES;
+        const uint32_t sa = k % A_STAGES, ua = k / A_STAGES, sd = k % INV_D_STAGES;
         const bool tr = (ablate_bits(p) & 32) && blockIdx.x == 0;
         stamp(tr, 1, k, 0);
         mbar_wait(bars + BAR_A_FULL + sa, ua & 1);
         stamp(tr, 1, k, 1);
-        if (k >= D_STAGES)
-            mbar_wait(bars + BAR_D_EMPTY + d_bar(k - D_STAGES), ((k - D_STAGES) / D_PERIOD) & 1);
+        if (k >= INV_D_STAGES)
+            mbar_wait(bars + BAR_D_EMPTY + inv_d_bar(k - INV_D_STAGES), ((k - INV_D_STAGES) / INV_D_PERIOD) & 1);
         fence_after();
         stamp(tr, 1, k, 2);
         constexpr uint32_t INV_A_LBO = inv_lbo<LAYOUT>(), INV_A_SBO = inv_sbo<LAYOUT>();
@@ -1178,7 +1189,7 @@ SDCT_DEV void inv_mma_role(const KParams &p, uint64_t *bars, uint32_t tmem_base,
         for (int ks = 0; ks < 4; ks++)   // K = 16 levels per instruction: two core matrices along K
             if (!(ablate_bits(p) & 1)) mma_f16_ss(tD, ad + (uint64_t)((2 * ks * INV_A_LBO) >> 4), bd[ks], idesc, ks);
         mma_commit(bars + BAR_A_EMPTY + sa);
-        mma_commit(bars + BAR_D_FULL + d_bar(k));
+        mma_commit(bars + BAR_D_FULL + inv_d_bar(k));
         stamp(tr, 1, k, 3);
     }
 }
@@ -1252,8 +1263,8 @@ SDCT_DEV void inv_consumer_rows(const KParams &p, uint64_t *bars, uint32_t tmem_
     }
     for (uint32_t k = c;; k += CONSUMER_WGS) {
         if (wk.tile >= p.tiles) break;
-        const uint32_t sd = RT ? c : k % D_STAGES, ud = RT ? k / 2 : k / D_PERIOD;
-        uint64_t *d_full = bars + (RT ? RT_BAR_D2_FULL + c : BAR_D_FULL + d_bar(k)), *d_empty = bars + (RT ? RT_BAR_D2_EMPTY + c : BAR_D_EMPTY + d_bar(k));
+        const uint32_t sd = RT ? c : k % INV_D_STAGES, ud = RT ? k / 2 : k / INV_D_PERIOD;
+        uint64_t *d_full = bars + (RT ? RT_BAR_D2_FULL + c : BAR_D_FULL + inv_d_bar(k)), *d_empty = bars + (RT ? RT_BAR_D2_EMPTY + c : BAR_D_EMPTY + inv_d_bar(k));
         Tile ptile;             // CF == 3: the pixel tile of this tile
         uint8_t *img = nullptr; //          and this thread's row 0 in this component's image
         bool last_own = false;  //          this warpgroup's last component of the pixel tile
@@ -1390,8 +1401,8 @@ SDCT_DEV void inv_consumer_chunks(const KParams &p, uint64_t *bars, uint32_t tme
     if (CF == 1 && wk.tile < p.tiles) locate_tile(wk, cur);
     for (uint32_t k = c;; k += CONSUMER_WGS) {
         if (wk.tile >= p.tiles) break;
-        const uint32_t sd = RT ? c : k % D_STAGES, ud = RT ? k / 2 : k / D_PERIOD;
-        uint64_t *d_full = bars + (RT ? RT_BAR_D2_FULL + c : BAR_D_FULL + d_bar(k)), *d_empty = bars + (RT ? RT_BAR_D2_EMPTY + c : BAR_D_EMPTY + d_bar(k));
+        const uint32_t sd = RT ? c : k % INV_D_STAGES, ud = RT ? k / 2 : k / INV_D_PERIOD;
+        uint64_t *d_full = bars + (RT ? RT_BAR_D2_FULL + c : BAR_D_FULL + inv_d_bar(k)), *d_empty = bars + (RT ? RT_BAR_D2_EMPTY + c : BAR_D_EMPTY + inv_d_bar(k));
         Tile ptile;             // CF == 3: the pixel tile of this tile
         uint8_t *img = nullptr; //          and this component's image
         bool last_own = false;  //          this warpgroup's last component of the pixel tile
@@ -1509,7 +1520,7 @@ __global__ void __launch_bounds__(THREADS, 1) inverse_tc_kernel(const __grid_con
             mbar_init(bars + BAR_A_FULL + i, 128);
             mbar_init(bars + BAR_A_EMPTY + i, 1);
         }
-        for (int i = 0; i < CONSUMER_WGS * D_STAGES; i++) {
+        for (int i = 0; i < INV_D_PERIOD; i++) {
             mbar_init(bars + BAR_D_FULL + i, 1);
             mbar_init(bars + BAR_D_EMPTY + i, 128);
         }
