@@ -404,12 +404,36 @@ SDCT_DEV void forward_tiles(const KParams &p, uint8_t *smem)
 
 
 
+// profiling builds only (-DSDCT_TRACE_CTA=1): globaltimer at entry and exit of every warp of the first 1024 CTAs, and the SM
+#ifndef SDCT_TRACE_CTA
+#define SDCT_TRACE_CTA 0
+#endif
+__device__ unsigned long long g_warp_times[SDCT_TRACE_CTA ? 1024 * 4 * 3 : 1];
+SDCT_DEV void warp_stamp(int which)
+{
+#if SDCT_TRACE_CTA
+    if ((threadIdx.x & 31) == 0 && blockIdx.x < 1024) {
+        unsigned long long t;
+        unsigned sm;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+        asm volatile("mov.u32 %0, %%smid;" : "=r"(sm));
+        unsigned long long *q = g_warp_times + (blockIdx.x * 4 + (threadIdx.x >> 5)) * 3;
+        q[which] = t;
+        q[2] = sm;
+    }
+#else
+    (void)which;
+#endif
+}
+
 template <int LAYOUT, int MODE, bool X3, int COMPS, int VEC>
 __global__ void __launch_bounds__(SDCT_TB, 3) forward_kernel(const __grid_constant__ KParams p)
 {
     extern __shared__ __align__(16) uint8_t smem[];
+    warp_stamp(0);
     if (warp_local_coefs<LAYOUT>(p)) forward_tiles<LAYOUT, MODE, X3, COMPS, VEC, true>(p, smem);
     else forward_tiles<LAYOUT, MODE, X3, COMPS, VEC, false>(p, smem);
+    warp_stamp(1);
 }
 
 // ---- inverse ---------------------------------------------------------------------------------------
@@ -928,6 +952,9 @@ static cudaError_t launch_inv2(const KParams &p, unsigned grid, cudaStream_t s)
 #if SDCT_PART == 1
 SDCT_DECL(sdct_part_exact_a) { (void)x3; return launch_fwd2<SDCT_K_LAYOUT_A, SDCT_K_EXACT, false>(op, p, grid, s); }
 #elif SDCT_PART == 2
+#if SDCT_TRACE_CTA
+extern "C" int sdct_k_warp_times(unsigned long long *host) { return (int)cudaMemcpyFromSymbol(host, g_warp_times, sizeof(g_warp_times)); }
+#endif
 SDCT_DECL(sdct_part_exact_b)
 {
     return x3 ? launch_fwd2<SDCT_K_LAYOUT_B, SDCT_K_EXACT, true>(op, p, grid, s)
